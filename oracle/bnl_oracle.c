@@ -1,0 +1,494 @@
+/* bnl_oracle.c -- CPU restatement of the reference's statistics hot path
+ * (SURVEY.md section 8a), on plain arrays, no R objects.
+ *
+ * TEST INFRASTRUCTURE ONLY. Only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs may load this; the product
+ * library (bnlearn_b200/csrc) never links or calls it.
+ *
+ * Pinning: the reference ships no golden vectors for this path (SURVEY.md
+ * section 4), so this restatement is pinned against the reference's own C
+ * compiled here (oracle/_ref/libbnref.so; tests/test_oracle_vs_ref.py) and
+ * against fixtures generated from it (tests/golden/*.json, made by
+ * tests/golden/make_fixtures.py). The R nmath / LAPACK / LINPACK pieces under
+ * it are "parity unpinned" (see rmath_port.c, linpack_port.c).
+ *
+ * Citations are relative to /root/reference/. Data conventions follow the
+ * reference: factor codes are int, 1-based, NA = INT_MIN; numeric columns are
+ * double; everything column-major. */
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <float.h>
+#include <limits.h>
+
+#define ORC_NA INT_MIN
+#define ORC_TOL 1.4901161193847656e-08   /* sqrt(DBL_EPSILON): src/include/globals.h:21 */
+
+double Rf_lgammafn(double x);
+double Rf_pchisq(double x, double df, int lower_tail, int log_p);
+double Rf_pt(double x, double n, int lower_tail, int log_p);
+double Rf_pnorm5(double x, double mu, double sigma, int lower_tail, int log_p);
+double Rf_dnorm4(double x, double mu, double sigma, int give_log);
+void minir_f77_dqrdc2(double *x, int *ldx, int *n, int *p, double *tol,
+    int *rank, double *qraux, int *pivot, double *work);
+void minir_f77_dqrsl(double *x, int *ldx, int *n, int *k, double *qraux,
+    double *y, double *qy, double *qty, double *b, double *rsd, double *xb,
+    int *job, int *info);
+
+/* test_e (src/tests/tests.h:8-36) and score_e (src/scores/scores.h:9-60). */
+enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_COR = 20, T_ZF = 21, T_MI_G = 22 };
+enum { S_LOGLIK = 1, S_AIC = 3, S_BIC = 4, S_BDE = 6, S_BDS = 7,
+       S_LOGLIK_G = 100, S_AIC_G = 102, S_BIC_G = 103 };
+
+/* ------------------------------------------------------------------------
+ * a2: configuration index (src/core/sets.c:162-218). First column varies
+ * fastest; a row is NA if any member is NA; `offset` is added to non-NA rows.
+ * Returns the number of configurations, or -1 if it does not fit an int. */
+long long orc_config(const int *const *cols, int nrow, int ncol, const int *levels,
+    int *cfg, int offset) {
+  long long nl = 1;
+  for (int j = 0; j < ncol; j++) nl *= levels[j];
+  if (nl >= INT_MAX) return -1;
+  for (int i = 0; i < nrow; i++) {
+    long long c = 0, cum = 1;
+    int na = 0;
+    for (int j = 0; j < ncol; j++) {
+      int v = cols[j][i];
+      if (v == ORC_NA) { na = 1; break; }
+      c += (long long)(v - 1) * cum;
+      cum *= levels[j];
+    }
+    cfg[i] = na ? ORC_NA : (int)c + offset;
+  }
+  return nl;
+}
+
+/* a4: joint counts n[z][x][y], flattened as ((z * llx) + x) * lly + y, skipping
+ * rows with any NA (src/core/contingency.tables.c:20-34, 93-130, 198-223).
+ * y == NULL gives a (z, x) table, z == NULL a single stratum. */
+void orc_counts(const int *x, int llx, const int *y, int lly, const int *z, int llz,
+    int num, int *table) {
+  size_t cells = (size_t)llx * (y ? lly : 1) * (z ? llz : 1);
+  memset(table, 0, cells * sizeof(int));
+  int ly = y ? lly : 1;
+  for (int k = 0; k < num; k++) {
+    if (x[k] == ORC_NA) continue;
+    if (y && y[k] == ORC_NA) continue;
+    if (z && z[k] == ORC_NA) continue;
+    size_t zi = z ? (size_t)(z[k] - 1) : 0;
+    size_t yi = y ? (size_t)(y[k] - 1) : 0;
+    table[(zi * llx + (size_t)(x[k] - 1)) * ly + yi]++;
+  }
+}
+
+/* a10-a12: statistic and degrees of freedom from an n[z][x][y] table
+ * (src/tests/discrete/discrete.tests.c:5-8, 11-94, 97-192;
+ *  src/tests/discrete/df.adjust.c:4-90). */
+double orc_discrete_stat(const int *n, int llx, int lly, int llz, int test, double *df) {
+  int *ni = calloc((size_t)llz * llx, sizeof(int));
+  int *nj = calloc((size_t)llz * lly, sizeof(int));
+  int *nk = calloc((size_t)llz, sizeof(int));
+  long long nobs = 0;
+  for (int k = 0; k < llz; k++)
+    for (int i = 0; i < llx; i++)
+      for (int j = 0; j < lly; j++) {
+        int c = n[((size_t)k * llx + i) * lly + j];
+        ni[k * llx + i] += c; nj[k * lly + j] += c; nk[k] += c;
+      }
+  for (int k = 0; k < llz; k++) nobs += nk[k];
+
+  /* degrees of freedom. */
+  double d = 0;
+  if (test == T_MI || test == T_X2) {
+    d = (double)(llx - 1) * (double)(lly - 1) * (double)llz;
+  } else {
+    for (int k = 0; k < llz; k++) {
+      int alx = 0, aly = 0;
+      for (int i = 0; i < llx; i++) alx += ni[k * llx + i] > 0;
+      for (int j = 0; j < lly; j++) aly += nj[k * lly + j] > 0;
+      if (alx < 1) alx = 1;
+      if (aly < 1) aly = 1;
+      d += (double)(alx - 1) * (double)(aly - 1);
+    }
+  }
+  if (df) *df = d;
+
+  double res = 0;
+  int adf = (test == T_MI_ADF || test == T_X2_ADF);
+  if (nobs == 0) goto done;
+  if (adf && (double)nobs < 5.0 * llx * lly * llz) goto done;
+
+  long double acc = 0;
+  if (test == T_MI || test == T_MI_ADF) {
+    for (int k = 0; k < llz; k++)
+      for (int i = 0; i < llx; i++)
+        for (int j = 0; j < lly; j++) {
+          int c = n[((size_t)k * llx + i) * lly + j];
+          if (c != 0)
+            acc += (double)c * log((double)c * (double)nk[k] /
+                     ((double)ni[k * llx + i] * (double)nj[k * lly + j]));
+        }
+    res = (double)acc / (double)nobs;
+    res *= 2.0 * (double)nobs;
+  } else {
+    for (int k = 0; k < llz; k++) {
+      if (nk[k] == 0) continue;
+      for (int i = 0; i < llx; i++)
+        for (int j = 0; j < lly; j++) {
+          long double e = ni[k * llx + i] * (double)nj[k * lly + j] / nk[k];
+          int c = n[((size_t)k * llx + i) * lly + j];
+          if (e != 0) acc += (c - e) * (c - e) / e;
+        }
+    }
+    res = (double)acc;
+  }
+done:
+  free(ni); free(nj); free(nk);
+  return res;
+}
+
+/* a11 + a13: one discrete CI test of x vs y given the columns z[0..nz)
+ * (src/tests/patterns/ctest.c:11-55, utest.c:23-62): configuration of Z,
+ * table, statistic, df, p = pchisq(stat, df, upper). Returns 0, or -1 when the
+ * configuration count overflows (the reference raises an R error there,
+ * src/core/sets.c:182-183). */
+int orc_ci_discrete(int test, const int *x, int llx, const int *y, int lly,
+    const int *const *z, const int *zlev, int nz, int num,
+    double *stat, double *df, double *pvalue) {
+  int llz = 1, *cfg = NULL;
+  if (nz > 0) {
+    cfg = malloc((size_t)(num > 0 ? num : 1) * sizeof(int));
+    long long nl = orc_config(z, num, nz, zlev, cfg, 1);
+    if (nl < 0) { free(cfg); return -1; }
+    llz = (int)nl;
+  }
+  int *tab = malloc((size_t)llx * lly * llz * sizeof(int));
+  orc_counts(x, llx, y, lly, cfg, llz, num, tab);
+  *stat = orc_discrete_stat(tab, llx, lly, llz, test, df);
+  *pvalue = Rf_pchisq(*stat, *df, 0, 0);
+  free(tab); free(cfg);
+  return 0;
+}
+
+/* ------------------------------------------------------------------------
+ * a5-a7: discrete node scores.
+ *   loglik / aic / bic : src/scores/discrete.loglikelihood.c:7-74 and the
+ *                        penalty at src/scores/per.node.score.c:98-114
+ *   bde / bds          : src/scores/dirichlet.posterior.c:9-71, 74-149, with the
+ *                        parent configurations as a factor over ALL Pi(levels)
+ *                        codes (bde) or over the OBSERVED codes only (bds;
+ *                        :180, src/minimal/common.c:43-83).
+ * `arg` is k for aic/bic and iss for bde/bds. The uniform graph prior adds 0
+ * (src/scores/graph.priors.c:35-37). Returns NAN if the configuration count
+ * overflows an int. */
+double orc_score_discrete(int score, const int *x, int llx, const int *const *pa,
+    const int *plev, int np, int num, double arg, double *nparams) {
+  double res = 0, npar = 0;
+  if (np == 0) {
+    int *n = calloc((size_t)llx, sizeof(int));
+    if (score == S_BDE || score == S_BDS) {
+      /* dpost() does not skip NA: the front end refuses incomplete data. */
+      for (int i = 0; i < num; i++) n[x[i] - 1]++;
+      double alpha = arg / llx;
+      for (int i = 0; i < llx; i++)
+        res += Rf_lgammafn(n[i] + alpha) - Rf_lgammafn(alpha);
+      res += Rf_lgammafn(arg) - Rf_lgammafn(arg + num);
+    } else {
+      int nobs = 0;
+      for (int i = 0; i < num; i++) if (x[i] != ORC_NA) n[x[i] - 1]++;
+      for (int i = 0; i < llx; i++) nobs += n[i];
+      for (int i = 0; i < llx; i++)
+        if (n[i] != 0) res += (double)n[i] * log((double)n[i] / nobs);
+      npar = llx - 1;
+    }
+    free(n);
+  } else {
+    int *cfg = malloc((size_t)(num > 0 ? num : 1) * sizeof(int));
+    long long nl = orc_config(pa, num, np, plev, cfg, 1);
+    if (nl < 0) { free(cfg); return NAN; }
+    int lly = (int)nl;
+    int *n = calloc((size_t)llx * lly, sizeof(int));      /* n[x][cfg] */
+    int *nj = calloc((size_t)lly, sizeof(int));
+    if (score == S_BDE || score == S_BDS) {
+      for (int i = 0; i < num; i++) {
+        n[(size_t)(x[i] - 1) * lly + (cfg[i] - 1)]++;
+        nj[cfg[i] - 1]++;
+      }
+      int q = lly;
+      if (score == S_BDS) { q = 0; for (int j = 0; j < lly; j++) q += nj[j] > 0; }
+      double alpha = arg / ((double)llx * q);
+      for (int i = 0; i < llx; i++)
+        for (int j = 0; j < lly; j++) {
+          if (score == S_BDS && nj[j] == 0) continue;
+          res += Rf_lgammafn(n[(size_t)i * lly + j] + alpha) - Rf_lgammafn(alpha);
+        }
+      for (int j = 0; j < lly; j++) {
+        if (score == S_BDS && nj[j] == 0) continue;
+        res += Rf_lgammafn(arg / q) - Rf_lgammafn(nj[j] + arg / q);
+      }
+    } else {
+      for (int i = 0; i < num; i++)
+        if (x[i] != ORC_NA && cfg[i] != ORC_NA) {
+          n[(size_t)(x[i] - 1) * lly + (cfg[i] - 1)]++;
+          nj[cfg[i] - 1]++;
+        }
+      for (int i = 0; i < llx; i++)
+        for (int j = 0; j < lly; j++) {
+          int c = n[(size_t)i * lly + j];
+          if (c != 0) res += (double)c * log((double)c / nj[j]);
+        }
+      npar = (double)(llx - 1) * (double)lly;
+    }
+    free(n); free(nj); free(cfg);
+  }
+  if (score == S_AIC || score == S_BIC) res -= arg * npar;
+  if (nparams) *nparams = npar;
+  return res;
+}
+
+/* a8: robust score difference (src/learning/score/score.delta.c:234-258). */
+double orc_robust_difference(double old_score, double new_score) {
+  double delta = (fabs(new_score - old_score) < ORC_TOL) ? 0 : new_score - old_score;
+  if (old_score == -INFINITY)
+    delta = (new_score != -INFINITY) ? new_score : -INFINITY;
+  return delta;
+}
+
+/* ------------------------------------------------------------------------
+ * Gaussian side. a14: moments and covariance with extended-precision sums
+ * (src/core/moments.c:7-45, src/core/covariance.matrix.c:65-97). */
+static double orc_mean(const double *x, int n) {
+  long double s = 0;
+  for (int i = 0; i < n; i++) s += x[i];
+  s /= n;
+  return (double)s;
+}
+
+static double orc_sse(const double *x, double m, int n) {
+  long double s = 0;
+  for (int i = 0; i < n; i++) s += (x[i] - m) * (x[i] - m);
+  return (double)s;
+}
+
+void orc_covmat(const double *const *cols, int n, int p, double *mean, double *cov) {
+  for (int j = 0; j < p; j++) mean[j] = orc_mean(cols[j], n);
+  if (n <= 1) { memset(cov, 0, (size_t)p * p * sizeof(double)); return; }
+  for (int i = 0; i < p; i++)
+    for (int j = i; j < p; j++) {
+      long double t = 0;
+      for (int k = 0; k < n; k++)
+        t += (cols[i][k] - mean[i]) * (cols[j][k] - mean[j]);
+      cov[i + j * p] = cov[j + i * p] = (double)(t / (n - 1));
+    }
+}
+
+/* cyclic Jacobi eigen-decomposition of a symmetric p x p matrix (column-major,
+ * destroyed); eigenvalues in d, eigenvectors in the columns of v. Stands in for
+ * the LAPACK dgesdd the reference calls (src/math/linear.algebra.c:58-84): for
+ * a symmetric matrix the singular values are |eigenvalues| and u_i * vt_i is
+ * sign(lambda_i) q_i q_i'. */
+static void orc_jacobi(double *a, int p, double *d, double *v) {
+  for (int i = 0; i < p; i++)
+    for (int j = 0; j < p; j++) v[i + j * p] = (i == j);
+  for (int sweep = 0; sweep < 100; sweep++) {
+    double off = 0, diag = 0;
+    for (int i = 0; i < p; i++) {
+      diag += a[i + i * p] * a[i + i * p];
+      for (int j = i + 1; j < p; j++) off += a[i + j * p] * a[i + j * p];
+    }
+    if (off <= 1e-40 * diag || off == 0) break;
+    for (int r = 0; r < p - 1; r++)
+      for (int c = r + 1; c < p; c++) {
+        double apq = a[r + c * p];
+        if (apq == 0) continue;
+        double theta = (a[c + c * p] - a[r + r * p]) / (2 * apq);
+        double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1));
+        double cs = 1 / sqrt(t * t + 1), sn = t * cs;
+        for (int k = 0; k < p; k++) {
+          double akr = a[k + r * p], akc = a[k + c * p];
+          a[k + r * p] = cs * akr - sn * akc;
+          a[k + c * p] = sn * akr + cs * akc;
+        }
+        for (int k = 0; k < p; k++) {
+          double ark = a[r + k * p], ack = a[c + k * p];
+          a[r + k * p] = cs * ark - sn * ack;
+          a[c + k * p] = sn * ark + cs * ack;
+        }
+        for (int k = 0; k < p; k++) {
+          double vkr = v[k + r * p], vkc = v[k + c * p];
+          v[k + r * p] = cs * vkr - sn * vkc;
+          v[k + c * p] = sn * vkr + cs * vkc;
+        }
+      }
+  }
+  for (int i = 0; i < p; i++) d[i] = a[i + i * p];
+}
+
+/* a15: partial correlation of variables 0 and 1 given the rest, from the
+ * pseudo-inverse of the covariance matrix with singular values below
+ * dim * d_max * eps dropped (src/core/correlation.c:43-92). */
+double orc_pcor(const double *cov, int p, int *clamped) {
+  double *a = malloc((size_t)p * p * sizeof(double));
+  double *v = malloc((size_t)p * p * sizeof(double));
+  double *d = malloc((size_t)p * sizeof(double));
+  memcpy(a, cov, (size_t)p * p * sizeof(double));
+  orc_jacobi(a, p, d, v);
+  double dmax = 0;
+  for (int i = 0; i < p; i++) if (fabs(d[i]) > dmax) dmax = fabs(d[i]);
+  double sv_tol = p * dmax * ORC_TOL * ORC_TOL;
+  double k11 = 0, k12 = 0, k22 = 0;
+  for (int i = 0; i < p; i++)
+    if (fabs(d[i]) > sv_tol) {
+      k11 += v[0 + i * p] * v[0 + i * p] / d[i];
+      k12 += v[0 + i * p] * v[1 + i * p] / d[i];
+      k22 += v[1 + i * p] * v[1 + i * p] / d[i];
+    }
+  free(a); free(v); free(d);
+  double res = (k11 < ORC_TOL || k22 < ORC_TOL) ? 0 : -k12 / sqrt(k11 * k22);
+  if (clamped) *clamped = 0;
+  if (res > 1) { res = 1; if (clamped) *clamped = 1; }
+  else if (res < -1) { res = -1; if (clamped) *clamped = 1; }
+  return res;
+}
+
+/* a16-a17: one Gaussian CI test of cols[0] vs cols[1] given cols[2..p)
+ * (src/tests/patterns/utest.c:65-129, ctest.c:58-142;
+ *  src/tests/gaussian/gaussian.tests.c:4-22, df.adjust.c:4-28).
+ * Returns 1 if the zero-degrees-of-freedom branch was taken (an R warning in
+ * the reference), else 0. `stat` is what the htest object reports: the
+ * (partial) correlation for cor, the transformed statistic for zf and mi-g. */
+int orc_ci_gaussian(int test, const double *const *cols, int p, int n,
+    double *stat, double *df, double *pvalue) {
+  int nz = p - 2;
+  double d = (test == T_COR) ? n - nz - 2 : (test == T_ZF) ? n - nz - 3 : 1;
+  if (d < 1) { *df = 0; *stat = 0; *pvalue = 1; return 1; }
+  *df = d;
+  double r;
+  if (nz == 0) {
+    double xm = orc_mean(cols[0], n), ym = orc_mean(cols[1], n);
+    long double xsd = orc_sse(cols[0], xm, n), ysd = orc_sse(cols[1], ym, n), sum = 0;
+    for (int i = 0; i < n; i++) sum += (cols[0][i] - xm) * (cols[1][i] - ym);
+    sum = (xsd < ORC_TOL || ysd < ORC_TOL) ? 0 : sum / sqrtl(xsd * ysd);
+    if (sum > 1) sum = 1; else if (sum < -1) sum = -1;
+    r = (double)sum;
+  } else {
+    double *mean = malloc((size_t)p * sizeof(double));
+    double *cov = malloc((size_t)p * p * sizeof(double));
+    orc_covmat(cols, n, p, mean, cov);
+    r = orc_pcor(cov, p, NULL);
+    free(mean); free(cov);
+  }
+  if (test == T_COR) {
+    double t = r * sqrt(d) / sqrt(1 - r * r);
+    *stat = r;
+    *pvalue = 2 * Rf_pt(fabs(t), d, 0, 0);
+  } else if (test == T_ZF) {
+    *stat = log((1 + r) / (1 - r)) / 2 * sqrt(d);
+    *pvalue = 2 * Rf_pnorm5(fabs(*stat), 0, 1, 0, 0);
+  } else {
+    *stat = 2 * n * (-0.5 * log(1 - r * r));
+    *pvalue = Rf_pchisq(*stat, d, 0, 0);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------
+ * a18: Gaussian node score (src/scores/gaussian.loglikelihood.c:8-83 over
+ * src/math/least.squares.c:8-352 and src/math/linear.algebra.c:136-274):
+ * OLS of x on its parents (closed forms for 0/1/2 parents, R's pivoted
+ * Householder QR otherwise), residual sd with n - p - 1 degrees of freedom,
+ * loglik = sum_i dnorm(x_i, fitted_i, sd, log); -Inf when sd < sqrt(eps).
+ * `k` is the aic-g / bic-g penalty coefficient (per.node.score.c:137-153). */
+double orc_score_gaussian(int score, const double *x, const double *const *pa, int np,
+    int n, double k, double *nparams) {
+  double *fitted = malloc((size_t)(n > 0 ? n : 1) * sizeof(double));
+  double sd = 0, res = 0;
+
+  if (np == 0) {
+    /* glik(): the mean is a plain double sum here (:15-17). */
+    double xm = 0;
+    for (int i = 0; i < n; i++) xm += x[i];
+    xm /= n;
+    long double s = 0;
+    if (n == 0) s = NAN;
+    else if (n == 1) s = 0;
+    else { for (int i = 0; i < n; i++) s += (x[i] - xm) * (x[i] - xm); s = sqrtl(s / (n - 1)); }
+    sd = (double)s;
+    for (int i = 0; i < n; i++) fitted[i] = xm;
+    if (s < ORC_TOL) { free(fitted); if (nparams) *nparams = 2; res = -INFINITY; goto penalty; }
+  } else if (np == 1) {
+    const double *m[2] = { x, pa[0] };
+    double mean[2], cov[4];
+    orc_covmat(m, n, 2, mean, cov);
+    int singular = fabs(cov[3]) < ORC_TOL;
+    double b = singular ? NAN : cov[1] / cov[3];
+    double a = singular ? mean[0] : mean[0] - mean[1] * b;
+    for (int i = 0; i < n; i++) fitted[i] = singular ? a : a + b * pa[0][i];
+    if (n == 0) sd = NAN;
+    else if (n <= 2) sd = 0;
+    else {
+      long double sse = 0;
+      for (int i = 0; i < n; i++) sse += (x[i] - fitted[i]) * (x[i] - fitted[i]);
+      sd = sqrt(sse / (n - 2));
+    }
+  } else if (np == 2) {
+    const double *m[3] = { x, pa[0], pa[1] };
+    double mean[3], c[9], a, b1 = 0, b2 = 0;
+    orc_covmat(m, n, 3, mean, c);
+    int s1 = fabs(c[4]) < ORC_TOL;
+    int s2 = (fabs(c[8]) < ORC_TOL) || (fabs(c[5]) / sqrt(c[4] * c[8]) > 1 - ORC_TOL);
+    if (s1 && !s2) { b2 = c[2] / c[8]; a = mean[0] - b2 * mean[2]; }
+    else if (!s1 && s2) { b1 = c[1] / c[4]; a = mean[0] - b1 * mean[1]; }
+    else if (s1 && s2) { a = mean[0]; }
+    else {
+      double den = c[4] * c[8] - c[5] * c[5];
+      b1 = (c[8] * c[1] - c[5] * c[2]) / den;
+      b2 = (c[4] * c[2] - c[5] * c[1]) / den;
+      a = mean[0] - b1 * mean[1] - b2 * mean[2];
+    }
+    for (int i = 0; i < n; i++) {
+      if (s1 && !s2) fitted[i] = a + b2 * pa[1][i];
+      else if (!s1 && s2) fitted[i] = a + b1 * pa[0][i];
+      else if (s1 && s2) fitted[i] = a;
+      else fitted[i] = a + b1 * pa[0][i] + b2 * pa[1][i];
+    }
+    if (n == 0) sd = NAN;
+    else if (n <= 3) sd = 0;
+    else {
+      long double sse = 0;
+      for (int i = 0; i < n; i++) sse += (x[i] - fitted[i]) * (x[i] - fitted[i]);
+      sd = sqrt(sse / (n - 3));
+    }
+  } else {
+    /* c_olsp() -> c_qr(): design matrix [1, parents], dqrdc2 with tol sqrt(eps),
+     * fitted values and residuals from dqrsl, sd over n - ncol. */
+    int ncol = np + 1, rank = 0, info = 0, job = 11;
+    if (n == 1) { fitted[0] = x[0]; sd = 0; }
+    else {
+      double *qr = malloc((size_t)n * ncol * sizeof(double));
+      double *qraux = calloc((size_t)ncol, sizeof(double));
+      double *work = calloc((size_t)2 * ncol, sizeof(double));
+      double *rsd = calloc((size_t)n, sizeof(double));
+      int *pivot = malloc((size_t)ncol * sizeof(int));
+      double tol = ORC_TOL;
+      for (int i = 0; i < n; i++) qr[i] = 1.0;
+      for (int j = 0; j < np; j++) memcpy(qr + (size_t)(j + 1) * n, pa[j], (size_t)n * sizeof(double));
+      for (int j = 0; j < ncol; j++) pivot[j] = j + 1;
+      minir_f77_dqrdc2(qr, &n, &n, &ncol, &tol, &rank, qraux, pivot, work);
+      memcpy(fitted, x, (size_t)n * sizeof(double));
+      minir_f77_dqrsl(qr, &n, &n, &rank, qraux, fitted, NULL, fitted, NULL, rsd, fitted, &job, &info);
+      if (info != 0) { sd = 0; memcpy(fitted, x, (size_t)n * sizeof(double)); }
+      else if (n <= ncol) sd = 0;
+      else sd = sqrt(orc_sse(rsd, 0, n) / (n - ncol));
+      free(qr); free(qraux); free(work); free(rsd); free(pivot);
+    }
+  }
+
+  if (sd < ORC_TOL) res = -INFINITY;
+  else for (int i = 0; i < n; i++) res += Rf_dnorm4(x[i], fitted[i], sd, 1);
+  free(fitted);
+  if (nparams) *nparams = np + 2;
+penalty:
+  if (score == S_AIC_G || score == S_BIC_G) res -= k * (np + 2);
+  return res;
+}

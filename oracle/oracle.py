@@ -1,0 +1,157 @@
+"""ctypes front end of oracle/_build/liboracle.so (the C restatement in
+oracle/bnl_oracle.c). TEST INFRASTRUCTURE ONLY: imported by tests/,
+__graft_entry__.smoke() and bench.py's CPU-baseline legs, never by the product.
+
+Columns are passed as lists of numpy arrays in the reference's conventions:
+int32 1-based factor codes (INT_MIN = NA) or float64.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+NA_INT = np.iinfo(np.int32).min
+c_int_p = C.POINTER(C.c_int)
+c_dbl_p = C.POINTER(C.c_double)
+
+TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "cor": 20, "zf": 21, "mi-g": 22}
+SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7,
+          "loglik-g": 100, "aic-g": 102, "bic-g": 103}
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE, "oracle"])
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = os.path.join(_HERE, "_build", "liboracle.so")
+    if not os.path.exists(path):
+        build()
+    L = C.CDLL(path)
+    pp_i = C.POINTER(c_int_p)
+    pp_d = C.POINTER(c_dbl_p)
+    L.orc_config.restype = C.c_longlong
+    L.orc_config.argtypes = [pp_i, C.c_int, C.c_int, c_int_p, c_int_p, C.c_int]
+    L.orc_counts.restype = None
+    L.orc_counts.argtypes = [c_int_p, C.c_int, c_int_p, C.c_int, c_int_p, C.c_int, C.c_int, c_int_p]
+    L.orc_discrete_stat.restype = C.c_double
+    L.orc_discrete_stat.argtypes = [c_int_p, C.c_int, C.c_int, C.c_int, C.c_int, c_dbl_p]
+    L.orc_ci_discrete.restype = C.c_int
+    L.orc_ci_discrete.argtypes = [C.c_int, c_int_p, C.c_int, c_int_p, C.c_int, pp_i, c_int_p,
+                                  C.c_int, C.c_int, c_dbl_p, c_dbl_p, c_dbl_p]
+    L.orc_score_discrete.restype = C.c_double
+    L.orc_score_discrete.argtypes = [C.c_int, c_int_p, C.c_int, pp_i, c_int_p, C.c_int, C.c_int,
+                                     C.c_double, c_dbl_p]
+    L.orc_robust_difference.restype = C.c_double
+    L.orc_robust_difference.argtypes = [C.c_double, C.c_double]
+    L.orc_ci_gaussian.restype = C.c_int
+    L.orc_ci_gaussian.argtypes = [C.c_int, pp_d, C.c_int, C.c_int, c_dbl_p, c_dbl_p, c_dbl_p]
+    L.orc_score_gaussian.restype = C.c_double
+    L.orc_score_gaussian.argtypes = [C.c_int, c_dbl_p, pp_d, C.c_int, C.c_int, C.c_double, c_dbl_p]
+    L.orc_pcor.restype = C.c_double
+    L.orc_pcor.argtypes = [c_dbl_p, C.c_int, c_int_p]
+    for name, nargs in (("Rf_lgammafn", 1),):
+        getattr(L, name).restype = C.c_double
+        getattr(L, name).argtypes = [C.c_double] * nargs
+    L.Rf_pchisq.restype = C.c_double
+    L.Rf_pchisq.argtypes = [C.c_double, C.c_double, C.c_int, C.c_int]
+    L.Rf_pt.restype = C.c_double
+    L.Rf_pt.argtypes = [C.c_double, C.c_double, C.c_int, C.c_int]
+    L.Rf_pnorm5.restype = C.c_double
+    L.Rf_pnorm5.argtypes = [C.c_double, C.c_double, C.c_double, C.c_int, C.c_int]
+    _LIB = L
+    return L
+
+
+def _ip(a):
+    return a.ctypes.data_as(c_int_p)
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_dbl_p)
+
+
+def _icols(cols):
+    cs = [np.ascontiguousarray(c, dtype=np.int32) for c in cols]
+    return cs, (c_int_p * max(len(cs), 1))(*[_ip(c) for c in cs])
+
+
+def _dcols(cols):
+    cs = [np.ascontiguousarray(c, dtype=np.float64) for c in cols]
+    return cs, (c_dbl_p * max(len(cs), 1))(*[_dp(c) for c in cs])
+
+
+def config(cols, levels, offset=0):
+    cs, ptrs = _icols(cols)
+    n = len(cs[0])
+    out = np.empty(n, dtype=np.int32)
+    lv = np.asarray(levels, dtype=np.int32)
+    nl = lib().orc_config(ptrs, n, len(cs), _ip(lv), _ip(out), offset)
+    return out, nl
+
+
+def counts(x, llx, y=None, lly=1, zcols=(), zlev=()):
+    """n[z][x][y] as a (llz, llx, lly) int32 array."""
+    x = np.ascontiguousarray(x, dtype=np.int32)
+    n = len(x)
+    llz, cfg = 1, None
+    if len(zcols):
+        cfg, llz = config(zcols, zlev, 1)
+    yy = np.ascontiguousarray(y, dtype=np.int32) if y is not None else None
+    tab = np.zeros(llz * llx * (lly if y is not None else 1), dtype=np.int32)
+    lib().orc_counts(_ip(x), llx, _ip(yy) if yy is not None else None, lly,
+                     _ip(cfg) if cfg is not None else None, llz, n, _ip(tab))
+    return tab.reshape(llz, llx, lly if y is not None else 1)
+
+
+def ci_discrete(test, x, llx, y, lly, zcols=(), zlev=()):
+    """(statistic, df, p.value) of one discrete CI test."""
+    x = np.ascontiguousarray(x, dtype=np.int32)
+    y = np.ascontiguousarray(y, dtype=np.int32)
+    cs, ptrs = _icols(zcols)
+    lv = np.asarray(list(zlev) or [1], dtype=np.int32)
+    st, df, p = C.c_double(), C.c_double(), C.c_double()
+    rc = lib().orc_ci_discrete(TESTS[test], _ip(x), llx, _ip(y), lly, ptrs, _ip(lv), len(cs),
+                               len(x), C.byref(st), C.byref(df), C.byref(p))
+    if rc != 0:
+        raise OverflowError("configuration count does not fit an int")
+    return st.value, df.value, p.value
+
+
+def score_discrete(score, x, llx, pcols=(), plev=(), arg=0.0):
+    """(score, nparams) of one discrete node given its parents (in order)."""
+    x = np.ascontiguousarray(x, dtype=np.int32)
+    cs, ptrs = _icols(pcols)
+    lv = np.asarray(list(plev) or [1], dtype=np.int32)
+    npar = C.c_double()
+    v = lib().orc_score_discrete(SCORES[score], _ip(x), llx, ptrs, _ip(lv), len(cs), len(x),
+                                 float(arg), C.byref(npar))
+    return v, npar.value
+
+
+def ci_gaussian(test, cols):
+    """cols = [x, y, z1, ...]; returns (statistic, df, p.value, zero_df_warning)."""
+    cs, ptrs = _dcols(cols)
+    st, df, p = C.c_double(), C.c_double(), C.c_double()
+    w = lib().orc_ci_gaussian(TESTS[test], ptrs, len(cs), len(cs[0]), C.byref(st), C.byref(df),
+                              C.byref(p))
+    return st.value, df.value, p.value, bool(w)
+
+
+def score_gaussian(score, x, pcols=(), k=0.0):
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    cs, ptrs = _dcols(pcols)
+    npar = C.c_double()
+    v = lib().orc_score_gaussian(SCORES[score], _dp(x), ptrs, len(cs), len(x), float(k),
+                                 C.byref(npar))
+    return v, npar.value
+
+
+def robust_difference(old, new):
+    return lib().orc_robust_difference(float(old), float(new))

@@ -1,0 +1,195 @@
+"""High-level helpers over oracle/refbind.py: run the reference's own .Call
+entry points (compiled in oracle/_ref/libbnref.so) on numpy data.
+TEST INFRASTRUCTURE ONLY (tests/, smoke(), bench.py CPU legs).
+
+A RefData wraps a data set as the "R data frame" the reference receives, with
+int32 1-based factor codes (INT_MIN = NA) or float64 columns.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import refbind as rb
+
+
+class RefData:
+    def __init__(self, columns, nlevels=None, names=None):
+        self.ncols = len(columns)
+        self.names = names or ["V%d" % i for i in range(self.ncols)]
+        self.nlevels = list(nlevels) if nlevels is not None else [0] * self.ncols
+        self.columns = [np.ascontiguousarray(c, dtype=np.int32 if self.nlevels[i] > 0 else np.float64)
+                        for i, c in enumerate(columns)]
+        self.nobs = len(self.columns[0]) if self.ncols else 0
+        self._df = None
+
+    def df(self):
+        if self._df is None:
+            self._df = rb.data_frame(self.names, self.columns, self.nlevels)
+        return self._df
+
+    def complete(self):
+        flags = []
+        for i, c in enumerate(self.columns):
+            if self.nlevels[i] > 0:
+                flags.append(int(not np.any(c == np.iinfo(np.int32).min)))
+            else:
+                flags.append(int(not np.any(np.isnan(c))))
+        s = rb.lglvec(np.array(flags, dtype=np.int32))
+        rb.set_names(s, self.names)
+        return s
+
+    def invalidate(self):
+        self._df = None
+
+
+def _extra(score=None, k=None, iss=None, B=None):
+    names, items = [], []
+    L = rb.lib()
+    if k is not None:
+        names.append("k"); items.append(L.Rf_ScalarReal(float(k)))
+    if iss is not None:
+        names.append("iss"); items.append(L.Rf_ScalarReal(float(iss)))
+        names.append("prior"); items.append(L.Rf_mkString(b"uniform"))
+    return rb.rlist(items, names)
+
+
+def per_node_score(data, parents, targets, score, k=None, iss=None):
+    """reference per_node_score (src/scores/per.node.score.c:31-48).
+    parents: {node name: [parent names, in order]}."""
+    L = rb.lib()
+    net = rb.network(data.names, parents)
+    res = L.per_node_score(net, data.df(), L.Rf_mkString(score.encode()),
+                           rb.strvec(list(targets)), _extra(k=k, iss=iss),
+                           L.Rf_ScalarLogical(0))
+    return rb.to_numpy(res)
+
+
+def indep_test(data, x, y, sx, test, alpha=0.05):
+    """reference indep_test(..., learning = TRUE) (src/tests/rinterface/indep.test.c:5-19):
+    x may be several names; returns the p-value vector. Bumps test_counter."""
+    L = rb.lib()
+    xs = [x] if isinstance(x, str) else list(x)
+    res = L.indep_test(rb.strvec(xs), rb.strvec([y]), rb.strvec(list(sx)), data.df(),
+                       L.Rf_mkString(test.encode()), L.Rf_ScalarReal(alpha),
+                       rb.rlist([], []), L.Rf_ScalarLogical(1), data.complete())
+    return rb.to_numpy(res)
+
+
+def ci_test(data, x, y, sx, test):
+    """reference indep_test(..., learning = FALSE): returns (statistic, df, p.value)
+    from the htest object (src/tests/rinterface/htest.c:6-89)."""
+    L = rb.lib()
+    res = L.indep_test(rb.strvec([x]), rb.strvec([y]), rb.strvec(list(sx)), data.df(),
+                       L.Rf_mkString(test.encode()), L.Rf_ScalarReal(0.05),
+                       rb.rlist([], []), L.Rf_ScalarLogical(0), data.complete())
+    n = L.Rf_length(res)
+    names = rb.to_numpy(rb.get_attr(res, "names"))
+    out = {}
+    for i in range(n):
+        el = L.VECTOR_ELT(res, i)
+        if L.TYPEOF(el) == rb.REALSXP:
+            out[names[i]] = float(rb.to_numpy(el)[0])
+    return out.get("statistic"), out.get("parameter"), out.get("p.value")
+
+
+def allsubs_test(data, x, y, sx, fixed, test, alpha, minsize, maxsize):
+    """reference allsubs_test (src/tests/rinterface/allsubs.test.c:10-210).
+    Returns (p.value, min.p.value, max.p.value, dsep.set or None)."""
+    L = rb.lib()
+    res = L.allsubs_test(rb.strvec([x]), rb.strvec([y]), rb.strvec(list(sx)),
+                         rb.strvec(list(fixed)), data.df(), L.Rf_mkString(test.encode()),
+                         L.Rf_ScalarReal(alpha), rb.rlist([], []),
+                         L.Rf_ScalarInteger(minsize), L.Rf_ScalarInteger(maxsize),
+                         data.complete(), L.Rf_ScalarLogical(0))
+    p = rb.to_numpy(res)
+    ds = rb.to_numpy(rb.get_attr(res, "dsep.set"))
+    return float(p[0]), float(p[1]), float(p[2]), ds
+
+
+def roundrobin_test(data, x, z, fixed, test, alpha):
+    """reference roundrobin_test (src/tests/rinterface/roundrobin.test.c:10-154)."""
+    L = rb.lib()
+    res = L.roundrobin_test(rb.strvec([x]), rb.strvec(list(z)), rb.strvec(list(fixed)),
+                            data.df(), L.Rf_mkString(test.encode()), L.Rf_ScalarReal(alpha),
+                            rb.rlist([], []), data.complete(), L.Rf_ScalarLogical(0))
+    return rb.to_numpy(res)
+
+
+def score_cache_fill(data, parents, score, reference, equivalence, updated, amat,
+                     cache, blmat, k=None, iss=None):
+    """reference score_cache_fill (src/learning/score/hc.cache.lookup.c:10-128).
+    amat/cache/blmat: column-major n x n numpy arrays (cache modified in place);
+    updated: 0-based node indices; reference: per-node scores."""
+    L = rb.lib()
+    n = data.ncols
+    net = rb.network(data.names, parents)
+    ref = rb.realvec(np.asarray(reference, dtype=np.float64))
+    rb.set_names(ref, data.names)
+    cache_f = np.asfortranarray(cache, dtype=np.float64)
+    cache_s = rb.lib().minir_vector_view(rb.REALSXP, cache_f.ctypes.data, n * n)
+    amat_s = rb.intvec(np.asfortranarray(amat, dtype=np.int32).ravel(order="F"))
+    bl_s = rb.intvec(np.asfortranarray(blmat, dtype=np.int32).ravel(order="F"))
+    L.score_cache_fill(rb.strvec(data.names), data.df(), net,
+                       L.Rf_mkString(score.encode()), _extra(k=k, iss=iss), ref,
+                       L.Rf_ScalarLogical(int(equivalence)), L.Rf_ScalarLogical(1),
+                       rb.intvec(np.asarray(updated, dtype=np.int32)), amat_s, cache_s,
+                       bl_s, L.Rf_ScalarLogical(0))
+    cache[...] = cache_f
+    return cache
+
+
+def hc_opt_step(names, amat, added, cache, reference, wlmat, blmat, nparents, maxp):
+    """reference hc_opt_step (src/learning/score/hc.cache.lookup.c:131-363).
+    Returns (op or None, from, to); `reference` is updated in place."""
+    L = rb.lib()
+    n = len(names)
+    f = lambda m: rb.intvec(np.asfortranarray(m, dtype=np.int32).ravel(order="F"))
+    ref_a = np.ascontiguousarray(reference, dtype=np.float64)
+    ref_s = L.minir_vector_view(rb.REALSXP, ref_a.ctypes.data, n)
+    cache_f = np.asfortranarray(cache, dtype=np.float64)
+    cache_s = L.minir_vector_view(rb.REALSXP, cache_f.ctypes.data, n * n)
+    res = L.hc_opt_step(f(amat), rb.strvec(names), f(added), cache_s, ref_s, f(wlmat),
+                        f(blmat), rb.realvec(np.asarray(nparents, dtype=np.float64)),
+                        rb.realvec(np.array([maxp], dtype=np.float64)), L.Rf_ScalarLogical(0))
+    reference[...] = ref_a
+    op = L.VECTOR_ELT(res, 0)
+    if L.TYPEOF(op) != rb.STRSXP:
+        return None, None, None
+    return (rb.to_numpy(op)[0], rb.to_numpy(L.VECTOR_ELT(res, 1))[0],
+            rb.to_numpy(L.VECTOR_ELT(res, 2))[0])
+
+
+# ------------------------------ kernel tier ------------------------------
+
+def _ip(a):
+    return a.ctypes.data_as(rb.c_int_p)
+
+
+def fast_config(columns, levels, offset=0):
+    """reference c_fast_config (src/core/sets.c:162-218)."""
+    L = rb.lib()
+    cols = [np.ascontiguousarray(c, dtype=np.int32) for c in columns]
+    n = len(cols[0])
+    ptrs = (rb.c_int_p * len(cols))(*[_ip(c) for c in cols])
+    lv = np.asarray(levels, dtype=np.int32)
+    out = np.empty(n, dtype=np.int32)
+    nl = C.c_int(0)
+    L.c_fast_config(ptrs, n, len(cols), _ip(lv), _ip(out), C.byref(nl), offset)
+    return out, nl.value
+
+
+def chisqtest(x, llx, y, lly, test_e, z=None, llz=0):
+    """reference c_chisqtest / c_cchisqtest (src/tests/discrete/discrete.tests.c:11-94):
+    returns (statistic, df) with the MI statistic scaled to G^2."""
+    L = rb.lib()
+    x = np.ascontiguousarray(x, dtype=np.int32)
+    y = np.ascontiguousarray(y, dtype=np.int32)
+    df = C.c_double(0)
+    scale = test_e in (1, 2)
+    if z is None:
+        st = L.c_chisqtest(_ip(x), llx, _ip(y), lly, len(x), C.byref(df), test_e, scale)
+    else:
+        z = np.ascontiguousarray(z, dtype=np.int32)
+        st = L.c_cchisqtest(_ip(x), llx, _ip(y), lly, _ip(z), llz, len(x), C.byref(df),
+                            test_e, scale)
+    return st, df.value

@@ -1,0 +1,2 @@
+/* shim header: see minir.h (test infrastructure only). */
+#include "../minir.h"

@@ -1,0 +1,210 @@
+"""Generate the committed fixtures under tests/golden/.
+
+Runs ONLY in the build container (needs /root/reference and
+oracle/_ref/libbnref.so): `python tests/golden/make_fixtures.py`.
+
+Outputs
+  data_<name>.npz       the reference's bundled data frames re-encoded as numpy
+                        (uint8 0-based codes + level counts, or float64), from
+                        /root/reference/data/<name>.rda via rda_reader.py
+  ref_outputs.json      outputs of the reference's OWN C entry points
+                        (per_node_score, indep_test, allsubs_test, roundrobin_test,
+                        score_cache_fill + test_counter) on those data sets
+  special_functions.json  mpmath values for lgamma / chi-square, t and normal
+                        upper tails on the decision-relevant ranges
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, HERE)
+
+from rda_reader import data_frame_columns, read_rda  # noqa: E402
+
+REF = "/root/reference"
+
+
+def export_datasets():
+    for name in ("learning.test", "alarm", "insurance", "gaussian.test"):
+        obj = read_rda(os.path.join(REF, "data", name + ".rda"))[name]
+        names, cols = data_frame_columns(obj)
+        out = os.path.join(HERE, "data_%s.npz" % name.replace(".", "_"))
+        if isinstance(cols[0], tuple):
+            codes = np.stack([c[0] for c in cols]).astype(np.int64) - 1
+            assert codes.min() >= 0 and codes.max() < 255
+            np.savez_compressed(out, names=np.array(names), codes=codes.astype(np.uint8),
+                                nlevels=np.array([len(c[1]) for c in cols], dtype=np.int32))
+        else:
+            np.savez_compressed(out, names=np.array(names),
+                                values=np.stack(cols).astype(np.float64))
+        print("wrote", out)
+
+
+def load_discrete(name):
+    z = np.load(os.path.join(HERE, "data_%s.npz" % name))
+    return [str(s) for s in z["names"]], z["codes"].astype(np.int32) + 1, z["nlevels"]
+
+
+def load_gaussian(name):
+    z = np.load(os.path.join(HERE, "data_%s.npz" % name))
+    return [str(s) for s in z["names"]], z["values"]
+
+
+def reference_outputs():
+    from oracle import refapi as ra, refbind as rb
+    out = {}
+    rng = np.random.default_rng(20261106)
+
+    # ---- discrete: learning.test and alarm -------------------------------
+    for ds in ("learning_test", "alarm"):
+        names, codes, nlev = load_discrete(ds)
+        data = ra.RefData(list(codes), list(nlev), names)
+        n, p = data.nobs, len(names)
+        rec = {"tests": [], "scores": [], "allsubs": [], "roundrobin": []}
+        # CI tests: random (x, y, S) with |S| in 0..3
+        for t in range(40 if ds == "alarm" else 30):
+            k = int(rng.integers(0, 4))
+            idx = rng.choice(p, size=2 + k, replace=False)
+            x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+            for test in ("mi", "x2", "mi-adf", "x2-adf"):
+                st, df, pv = ra.ci_test(data, names[x], names[y], [names[i] for i in s], test)
+                rec["tests"].append({"test": test, "x": x, "y": y, "z": s,
+                                     "stat": st, "df": df, "p": pv})
+            rb.reset()
+            data.invalidate()
+        # node scores: random parent sets with 0..3 parents
+        for t in range(30):
+            k = int(rng.integers(0, 4))
+            idx = rng.choice(p, size=1 + k, replace=False)
+            node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+            par = {names[node]: [names[i] for i in pa]}
+            for score, kw in (("loglik", {}), ("aic", {"k": 1.0}), ("bic", {"k": np.log(n) / 2}),
+                              ("bde", {"iss": 1.0}), ("bde", {"iss": 10.0}), ("bds", {"iss": 1.0})):
+                v = ra.per_node_score(data, par, [names[node]], score, **kw)[0]
+                rec["scores"].append({"score": score, "arg": list(kw.values())[0] if kw else 0.0,
+                                      "node": node, "parents": pa, "value": float(v)})
+            rb.reset()
+            data.invalidate()
+        # allsubs (with test counter) and round-robin
+        for t in range(12):
+            m = int(rng.integers(2, min(6, p - 2) + 1)) if p > 6 else int(rng.integers(2, p - 1))
+            idx = rng.choice(p, size=2 + m, replace=False)
+            x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+            nf = int(rng.integers(0, 2))
+            mn = int(rng.integers(0, 2))
+            mx = int(rng.integers(max(mn, 1), min(3, m - nf) + 1))
+            for test in ("mi", "x2"):
+                rb.reset_test_counter()
+                pv, pmin, pmax, ds_ = ra.allsubs_test(
+                    data, names[x], names[y], [names[i] for i in s], [names[i] for i in s[:nf]],
+                    test, 0.05, mn, mx)
+                rec["allsubs"].append({"test": test, "x": x, "y": y, "sx": s, "nfixed": nf,
+                                       "min": mn, "max": mx, "alpha": 0.05, "p": pv,
+                                       "pmin": pmin, "pmax": pmax,
+                                       "dsep": None if ds_ is None else [names.index(d) for d in ds_],
+                                       "counter": rb.test_counter()})
+                rb.reset_test_counter()
+                pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + s],
+                                         [names[i] for i in s[:nf]], test, 0.05)
+                rec["roundrobin"].append({"test": test, "x": x, "z": [y] + s, "nfixed": nf,
+                                          "alpha": 0.05, "p": [float(v) for v in pvs],
+                                          "counter": rb.test_counter()})
+            rb.reset()
+            data.invalidate()
+        out[ds] = rec
+
+    # ---- score cache fill on learning.test (empty graph, then one arc) ----
+    names, codes, nlev = load_discrete("learning_test")
+    data = ra.RefData(list(codes), list(nlev), names)
+    n, p = data.nobs, len(names)
+    rec = []
+    for score, kw in (("bic", {"k": np.log(n) / 2}), ("bde", {"iss": 1.0})):
+        for parents in ({}, {"B": ["A"], "D": ["A", "C"]}):
+            amat = np.zeros((p, p), dtype=np.int32)
+            for ch, pas in parents.items():
+                for pa in pas:
+                    amat[names.index(pa), names.index(ch)] = 1
+            ref = ra.per_node_score(data, parents, names, score, **kw)
+            cache = np.zeros((p, p), dtype=np.float64, order="F")
+            rb.reset_test_counter()
+            ra.score_cache_fill(data, parents, score, ref, True, list(range(p)), amat, cache,
+                                np.zeros((p, p), dtype=np.int32), **kw)
+            rec.append({"score": score, "arg": list(kw.values())[0],
+                        "parents": {k: v for k, v in parents.items()},
+                        "reference": [float(v) for v in ref],
+                        "cache": [[float(v) for v in row] for row in cache],
+                        "counter": rb.test_counter()})
+            rb.reset()
+            data.invalidate()
+    out["score_cache_fill"] = rec
+
+    # ---- Gaussian: gaussian.test ------------------------------------------
+    names, vals = load_gaussian("gaussian_test")
+    data = ra.RefData(list(vals), None, names)
+    n, p = data.nobs, len(names)
+    rec = {"tests": [], "scores": []}
+    for t in range(30):
+        k = int(rng.integers(0, 5))
+        idx = rng.choice(p, size=2 + k, replace=False)
+        x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+        for test in ("cor", "zf", "mi-g"):
+            st, df, pv = ra.ci_test(data, names[x], names[y], [names[i] for i in s], test)
+            rec["tests"].append({"test": test, "x": x, "y": y, "z": s, "stat": st, "df": df, "p": pv})
+        rb.reset()
+        data.invalidate()
+    for t in range(30):
+        k = int(rng.integers(0, 6))
+        idx = rng.choice(p, size=1 + k, replace=False)
+        node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+        par = {names[node]: [names[i] for i in pa]}
+        for score, kw in (("loglik-g", {}), ("aic-g", {"k": 1.0}), ("bic-g", {"k": np.log(n) / 2})):
+            v = ra.per_node_score(data, par, [names[node]], score, **kw)[0]
+            rec["scores"].append({"score": score, "arg": list(kw.values())[0] if kw else 0.0,
+                                  "node": node, "parents": pa, "value": float(v)})
+        rb.reset()
+        data.invalidate()
+    out["gaussian_test"] = rec
+
+    with open(os.path.join(HERE, "ref_outputs.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote ref_outputs.json")
+
+
+def special_function_fixtures():
+    import mpmath as mp
+    mp.mp.dps = 50
+    rec = {"lgamma": [], "pchisq_upper": [], "pt_upper2": [], "pnorm_upper2": []}
+    for x in [1e-3, 0.01, 0.05, 0.1, 1 / 3, 0.5, 0.9, 1.0, 1.5, 2.0, 2.5, 3.7, 9.99, 10.0, 10.5,
+              17.25, 100.125, 1234.5, 20000.0625, 1e6 + 1 / 81, 1e7 + 0.5, 3.3e8]:
+        rec["lgamma"].append([x, float(mp.loggamma(mp.mpf(x)))])
+    for df in [1, 2, 4, 9, 12, 36, 108, 243, 1024, 9216]:
+        for mult in [0.0, 0.1, 0.5, 0.9, 1.0, 1.1, 1.5, 2.0, 4.0, 10.0]:
+            x = df * mult
+            if x == 0 and df > 0:
+                v = 1.0
+            else:
+                v = float(mp.gammainc(mp.mpf(df) / 2, mp.mpf(x) / 2, mp.inf, regularized=True))
+            if v > 1e-300:
+                rec["pchisq_upper"].append([x, df, v])
+    for df in [1, 2, 3, 10, 30, 100, 4997, 19998, 999998, 9999997]:
+        for t in [0.0, 0.01, 0.5, 1.0, 1.96, 2.5, 5.0, 10.0, 30.0]:
+            x = mp.mpf(df) / (mp.mpf(df) + mp.mpf(t) ** 2)
+            v = float(mp.betainc(mp.mpf(df) / 2, mp.mpf(1) / 2, 0, x, regularized=True))
+            if v > 1e-300:
+                rec["pt_upper2"].append([t, df, v])
+    for z in [0.0, 0.1, 0.5, 1.0, 1.959963984540054, 3.0, 5.0, 8.0, 15.0, 30.0]:
+        rec["pnorm_upper2"].append([z, float(mp.erfc(mp.mpf(z) / mp.sqrt(2)))])
+    with open(os.path.join(HERE, "special_functions.json"), "w") as f:
+        json.dump(rec, f)
+    print("wrote special_functions.json")
+
+
+if __name__ == "__main__":
+    export_datasets()
+    special_function_fixtures()
+    reference_outputs()
