@@ -1,0 +1,268 @@
+// bnl_context.cu -- context, device resources and data-set registration
+// (packing R's int32 factor columns into the uint8 HBM layout).
+#include <stdarg.h>
+#include <string.h>
+
+#include "bnl_internal.h"
+
+int bnl_fail(bnl_ctx *ctx, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (ctx) {
+    std::lock_guard<std::mutex> lock(ctx->err_mutex);
+    ctx->err = buf;
+  }
+  return code;
+}
+
+// ---------------------------------------------------------------------------
+// pack_factors: int32 1-based codes (NA = INT_MIN) -> uint8 (code - 1, NA = 0xFF).
+// One thread converts 4 rows: one 128-bit load, one 32-bit store, both coalesced.
+// Codes outside [1, nlevels] raise the error flag (the reference would index
+// out of bounds there; we refuse the column instead).
+__global__ void __launch_bounds__(256)
+pack_factors_kernel(const int *__restrict__ src, uint8_t *__restrict__ dst, long long nobs,
+                    int nlevels, int *__restrict__ bad) {
+  const long long quads = (nobs + 3) / 4;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < quads;
+       q += (long long)gridDim.x * blockDim.x) {
+    const long long r = q * 4;
+    int v[4];
+    if (r + 3 < nobs) {
+      const int4 w = *reinterpret_cast<const int4 *>(src + r);
+      v[0] = w.x; v[1] = w.y; v[2] = w.z; v[3] = w.w;
+    } else {
+      for (int j = 0; j < 4; j++) v[j] = (r + j < nobs) ? src[r + j] : INT_MIN;
+    }
+    unsigned out = 0;
+    for (int j = 0; j < 4; j++) {
+      unsigned b;
+      if (v[j] == INT_MIN) b = BNL_NA_U8;
+      else if (v[j] < 1 || v[j] > nlevels) { b = BNL_NA_U8; *bad = 1; }
+      else b = (unsigned)(v[j] - 1);
+      out |= b << (8 * j);
+    }
+    *reinterpret_cast<unsigned *>(dst + r) = out;   // stride is padded: always in bounds
+  }
+}
+
+// ---------------------------------------------------------------------------
+
+extern "C" int bnl_init(bnl_ctx **out, const int *devices, int ndev) {
+  if (!out) return BNL_EINVAL;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  bnl_ctx *ctx = new bnl_ctx();
+  *out = ctx;   // returned even on failure so that bnl_last_error() can explain
+  if (e != cudaSuccess || count == 0)
+    return bnl_fail(ctx, BNL_ECUDA, "no CUDA device available (%s); this engine has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  std::vector<int> ids;
+  if (!devices || ndev <= 0) {
+    int cur = 0;
+    BNL_CUDA(ctx, cudaGetDevice(&cur));
+    ids.push_back(cur);
+  } else {
+    for (int i = 0; i < ndev; i++) {
+      if (devices[i] < 0 || devices[i] >= count)
+        return bnl_fail(ctx, BNL_EINVAL, "device %d out of range (have %d)", devices[i], count);
+      ids.push_back(devices[i]);
+    }
+  }
+  for (int id : ids) {
+    BnlDevice d;
+    d.id = id;
+    BNL_CUDA(ctx, cudaSetDevice(id));
+    BNL_CUDA(ctx, cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
+    BNL_CUDA(ctx, cudaEventCreate(&d.ev0));
+    BNL_CUDA(ctx, cudaEventCreate(&d.ev1));
+    BNL_CUDA(ctx, cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, id));
+    BNL_CUDA(ctx, cudaDeviceGetAttribute(&d.max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, id));
+    ctx->devs.push_back(d);
+  }
+  BNL_CUDA(ctx, cudaSetDevice(ids[0]));
+  return BNL_OK;
+}
+
+static void free_dataset(bnl_ctx *ctx, BnlDataSet &ds) {
+  for (size_t i = 0; i < ds.dev.size(); i++) {
+    cudaSetDevice(ctx->devs[i].id);
+    cudaFree(ds.dev[i].u8);
+    cudaFree(ds.dev[i].f64);
+    cudaFree(ds.dev[i].mean);
+    cudaFree(ds.dev[i].cov);
+  }
+  ds.dev.clear();
+}
+
+extern "C" void bnl_shutdown(bnl_ctx *ctx) {
+  if (!ctx) return;
+  for (auto &kv : ctx->data) free_dataset(ctx, kv.second);
+  for (auto &d : ctx->devs) {
+    cudaSetDevice(d.id);
+    cudaFree(d.d_units); cudaFree(d.d_tables); cudaFree(d.d_out); cudaFree(d.d_gidx);
+    cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_gidx);
+    if (d.ev0) cudaEventDestroy(d.ev0);
+    if (d.ev1) cudaEventDestroy(d.ev1);
+    if (d.stream) cudaStreamDestroy(d.stream);
+  }
+  delete ctx;
+}
+
+extern "C" const char *bnl_last_error(const bnl_ctx *ctx) {
+  return ctx ? ctx->err.c_str() : "null context";
+}
+
+extern "C" int bnl_last_call_stats(const bnl_ctx *ctx, double *device_ms, int *kernel_launches) {
+  if (!ctx) return BNL_EINVAL;
+  if (device_ms) *device_ms = ctx->last_ms;
+  if (kernel_launches) *kernel_launches = ctx->last_launches;
+  return BNL_OK;
+}
+
+static size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col,
+                                 const int *is_numeric, const int *nlevels, int64_t nobs,
+                                 bnl_data *handle) {
+  if (!ctx || ctx->devs.empty()) return BNL_EINVAL;
+  if (ncols <= 0 || !col || !is_numeric || !nlevels || !handle || nobs < 0)
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_register: bad arguments");
+  if (nobs >= (int64_t)INT32_MAX)
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_register: nobs must fit an int (R vectors on this path do)");
+
+  BnlDataSet ds;
+  ds.ncols = ncols;
+  ds.nobs = nobs;
+  ds.is_numeric.assign(is_numeric, is_numeric + ncols);
+  ds.nlevels.assign(nlevels, nlevels + ncols);
+  ds.slot.resize(ncols);
+  for (int i = 0; i < ncols; i++) {
+    if (is_numeric[i]) ds.slot[i] = ds.nc++;
+    else {
+      if (nlevels[i] < 1)
+        return bnl_fail(ctx, BNL_EINVAL, "column %d: a factor needs at least one level", i);
+      if (nlevels[i] > BNL_MAX_LEVELS)
+        return bnl_fail(ctx, BNL_EUNSUPPORTED, "column %d has %d levels; the uint8 layout holds at most %d",
+                        i, nlevels[i], BNL_MAX_LEVELS);
+      ds.slot[i] = ds.nd++;
+    }
+  }
+  ds.stride_u8 = round_up((size_t)nobs + 1, BNL_COL_ALIGN);
+  ds.stride_f64 = round_up((size_t)nobs + 1, 32);
+  ds.dev.resize(ctx->devs.size());
+
+  // device 0: upload (int32 staging -> pack kernel; doubles straight in).
+  BnlDevice &d0 = ctx->devs[0];
+  BnlDeviceData &dd0 = ds.dev[0];
+  BNL_CUDA(ctx, cudaSetDevice(d0.id));
+  int *stage = nullptr, *d_bad = nullptr;
+  int rc = BNL_OK;
+  auto cleanup = [&](int code) {
+    cudaFree(stage); cudaFree(d_bad);
+    if (code != BNL_OK) free_dataset(ctx, ds);
+    return code;
+  };
+#define REG_CUDA(call)                                                                     \
+  do {                                                                                     \
+    cudaError_t e__ = (call);                                                              \
+    if (e__ != cudaSuccess)                                                                \
+      return cleanup(bnl_fail(ctx, e__ == cudaErrorMemoryAllocation ? BNL_ENOMEM : BNL_ECUDA, \
+                              "%s failed: %s", #call, cudaGetErrorString(e__)));           \
+  } while (0)
+
+  if (ds.nd > 0) {
+    REG_CUDA(cudaMalloc((void **)&dd0.u8, ds.stride_u8 * ds.nd));
+    REG_CUDA(cudaMemsetAsync(dd0.u8, BNL_NA_U8, ds.stride_u8 * ds.nd, d0.stream));
+    REG_CUDA(cudaMalloc((void **)&stage, ((size_t)nobs + 4) * sizeof(int)));
+    REG_CUDA(cudaMalloc((void **)&d_bad, sizeof(int)));
+    REG_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), d0.stream));
+  }
+  if (ds.nc > 0) {
+    REG_CUDA(cudaMalloc((void **)&dd0.f64, ds.stride_f64 * ds.nc * sizeof(double)));
+    REG_CUDA(cudaMemsetAsync(dd0.f64, 0, ds.stride_f64 * ds.nc * sizeof(double), d0.stream));
+  }
+  for (int i = 0; i < ncols; i++) {
+    if (!col[i] && nobs > 0)
+      return cleanup(bnl_fail(ctx, BNL_EINVAL, "column %d is a null pointer", i));
+    if (nobs == 0) continue;
+    if (is_numeric[i]) {
+      REG_CUDA(cudaMemcpyAsync(dd0.f64 + ds.stride_f64 * ds.slot[i], col[i],
+                               (size_t)nobs * sizeof(double), cudaMemcpyHostToDevice, d0.stream));
+    } else {
+      REG_CUDA(cudaMemcpyAsync(stage, col[i], (size_t)nobs * sizeof(int), cudaMemcpyHostToDevice,
+                               d0.stream));
+      long long quads = (nobs + 3) / 4;
+      int grid = (int)((quads + 255) / 256);
+      if (grid > d0.sm_count * 16) grid = d0.sm_count * 16;
+      pack_factors_kernel<<<grid, 256, 0, d0.stream>>>(stage, dd0.u8 + ds.stride_u8 * ds.slot[i],
+                                                       nobs, nlevels[i], d_bad);
+      REG_CUDA(cudaGetLastError());
+    }
+  }
+  if (ds.nd > 0) {
+    int bad = 0;
+    REG_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, d0.stream));
+    REG_CUDA(cudaStreamSynchronize(d0.stream));
+    if (bad)
+      return cleanup(bnl_fail(ctx, BNL_EINVAL, "a factor column holds a code outside 1..nlevels"));
+  } else {
+    REG_CUDA(cudaStreamSynchronize(d0.stream));
+  }
+
+  // replicate on the other devices (peer copies; NVLink where available).
+  for (size_t i = 1; i < ctx->devs.size(); i++) {
+    BnlDevice &di = ctx->devs[i];
+    BnlDeviceData &ddi = ds.dev[i];
+    REG_CUDA(cudaSetDevice(di.id));
+    if (ds.nd > 0) {
+      REG_CUDA(cudaMalloc((void **)&ddi.u8, ds.stride_u8 * ds.nd));
+      REG_CUDA(cudaMemcpyPeerAsync(ddi.u8, di.id, dd0.u8, d0.id, ds.stride_u8 * ds.nd, di.stream));
+    }
+    if (ds.nc > 0) {
+      REG_CUDA(cudaMalloc((void **)&ddi.f64, ds.stride_f64 * ds.nc * sizeof(double)));
+      REG_CUDA(cudaMemcpyPeerAsync(ddi.f64, di.id, dd0.f64, d0.id,
+                                   ds.stride_f64 * ds.nc * sizeof(double), di.stream));
+    }
+  }
+  for (size_t i = 1; i < ctx->devs.size(); i++) {
+    REG_CUDA(cudaSetDevice(ctx->devs[i].id));
+    REG_CUDA(cudaStreamSynchronize(ctx->devs[i].stream));
+  }
+#undef REG_CUDA
+
+  // Gaussian moments (means + covariance), once per data set and device.
+  if (ds.nc > 0) {
+    for (size_t i = 0; i < ctx->devs.size(); i++) {
+      rc = bnl_gaussian_prepare(ctx, ds, (int)i);
+      if (rc != BNL_OK) return cleanup(rc);
+    }
+  }
+  cleanup(BNL_OK);
+  cudaSetDevice(d0.id);
+  *handle = ctx->next_handle++;
+  ctx->data[*handle] = ds;
+  return BNL_OK;
+}
+
+extern "C" int bnl_data_release(bnl_ctx *ctx, bnl_data handle) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(handle);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  free_dataset(ctx, it->second);
+  ctx->data.erase(it);
+  cudaSetDevice(ctx->devs[0].id);
+  return BNL_OK;
+}
+
+extern "C" int bnl_data_flush(bnl_ctx *ctx) {
+  if (!ctx) return BNL_EINVAL;
+  for (auto &kv : ctx->data) free_dataset(ctx, kv.second);
+  ctx->data.clear();
+  if (!ctx->devs.empty()) cudaSetDevice(ctx->devs[0].id);
+  return BNL_OK;
+}

@@ -1,0 +1,251 @@
+// bnl_discrete.cu -- host side of the discrete entry points: unit validation,
+// batching, multi-device dispatch, launches.
+#include <string.h>
+
+#include <algorithm>
+#include <thread>
+
+#include "bnl_discrete_kernels.cuh"
+
+namespace {
+
+const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
+const int kMaxBatchUnits = 1 << 16;
+
+BnlDataSet *find_data(bnl_ctx *ctx, bnl_data h) {
+  auto it = ctx->data.find(h);
+  return it == ctx->data.end() ? nullptr : &it->second;
+}
+
+// Build the kernel-side description of one unit. Columns: y (optional), x, then z.
+int make_unit(bnl_ctx *ctx, const BnlDataSet &ds, int x, int y, const int *z, int nz, BnlUnit *u) {
+  if (nz + 2 > BNL_MAXK)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "a unit may involve at most %d columns (got %d)",
+                    BNL_MAXK, nz + 2);
+  auto check = [&](int c) {
+    return c >= 0 && c < ds.ncols && !ds.is_numeric[c];
+  };
+  if (!check(x) || (y >= 0 && !check(y)))
+    return bnl_fail(ctx, BNL_EINVAL, "unit refers to column %d / %d: out of range or not a factor", x, y);
+  memset(u, 0, sizeof(*u));
+  int k = 0;
+  long long mul = 1;
+  u->llx = ds.nlevels[x];
+  u->lly = y >= 0 ? ds.nlevels[y] : 1;
+  if (y >= 0) { u->col[k] = ds.slot[y]; u->mul[k] = 1; k++; mul = u->lly; }
+  u->col[k] = ds.slot[x]; u->mul[k] = (int)mul; k++;
+  mul *= u->llx;
+  long long llz = 1;
+  for (int j = 0; j < nz; j++) {
+    if (!check(z[j]))
+      return bnl_fail(ctx, BNL_EINVAL, "unit refers to column %d: out of range or not a factor", z[j]);
+    llz *= ds.nlevels[z[j]];
+    // the reference refuses configuration counts that do not fit an int
+    // (src/core/sets.c:182-183).
+    if (llz >= INT32_MAX || mul * ds.nlevels[z[j]] >= INT32_MAX)
+      return bnl_fail(ctx, BNL_EOVERFLOW, "attempting to create a factor with more than INT_MAX levels");
+    u->col[k] = ds.slot[z[j]]; u->mul[k] = (int)mul; k++;
+    mul *= ds.nlevels[z[j]];
+  }
+  u->ncols = k;
+  u->llz = (int)llz;
+  u->cells = (int)mul;
+  if (mul > kMaxBatchCells)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "a single table of %lld cells exceeds the engine's scratch limit", mul);
+  return BNL_OK;
+}
+
+struct Request {
+  int kind;        // 0 tests, 1 scores, 2 raw tables
+  int code;
+  double arg;
+  int n;
+  std::vector<BnlUnit> units;
+  double *o0, *o1, *o2;          // per-unit outputs (may be null)
+  int32_t *tables;               // kind 2
+  const int64_t *table_off;
+};
+
+// Run units [b, e) of the request on device slot d, in sub-batches bounded by
+// the scratch size. Everything is queued on the device's stream; the caller
+// synchronises. Sub-batches reuse the pinned staging buffers, so each one is
+// synchronised before the next is staged.
+int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, float *ms, int *launches) {
+  BnlDevice &dev = ctx->devs[d];
+  BnlDeviceData &dd = ds.dev[d];
+  BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  if (!dev.attr_done) {
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_units_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 1024));
+    dev.attr_done = true;
+  }
+  const int smem_cap_cells = (dev.max_smem - 2048) / 4;
+  const long long groups = (ds.nobs + 15) / 16;
+  int pos = b;
+  while (pos < e) {
+    long long cells = 0;
+    int cnt = 0;
+    while (pos + cnt < e && cnt < kMaxBatchUnits && cells + rq.units[pos + cnt].cells <= kMaxBatchCells) {
+      cells += rq.units[pos + cnt].cells;
+      cnt++;
+    }
+    if (cnt == 0) return bnl_fail(ctx, BNL_EUNSUPPORTED, "table too large for the scratch buffer");
+    int rc;
+    if ((rc = bnl_reserve_pinned(ctx, &dev.h_units, &dev.h_units_cap, (size_t)cnt))) return rc;
+    if ((rc = bnl_reserve_device(ctx, &dev.d_units, &dev.units_cap, (size_t)cnt))) return rc;
+    if ((rc = bnl_reserve_device(ctx, &dev.d_tables, &dev.tables_cap, (size_t)cells))) return rc;
+    if ((rc = bnl_reserve_device(ctx, &dev.d_out, &dev.out_cap, (size_t)cnt * 4))) return rc;
+    if ((rc = bnl_reserve_pinned(ctx, &dev.h_out, &dev.h_out_cap, (size_t)cnt * 4))) return rc;
+
+    long long off = 0;
+    int smem_cells = 0;
+    for (int i = 0; i < cnt; i++) {
+      dev.h_units[i] = rq.units[pos + i];
+      dev.h_units[i].table_off = off;
+      off += dev.h_units[i].cells;
+      if (dev.h_units[i].cells <= smem_cap_cells) smem_cells = std::max(smem_cells, dev.h_units[i].cells);
+    }
+    // enough CTAs to fill the machine, but at least 4096 rows per CTA.
+    int chunks = (4 * dev.sm_count + cnt - 1) / cnt;
+    long long max_chunks = std::max(1ll, groups / 256);
+    if (chunks > max_chunks) chunks = (int)max_chunks;
+    if (chunks < 1) chunks = 1;
+
+    BNL_CUDA(ctx, cudaEventRecord(dev.ev0, dev.stream));
+    BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_units, dev.h_units, (size_t)cnt * sizeof(BnlUnit),
+                                  cudaMemcpyHostToDevice, dev.stream));
+    BNL_CUDA(ctx, cudaMemsetAsync(dev.d_tables, 0, (size_t)cells * sizeof(int), dev.stream));
+    if (groups > 0) {
+      count_units_kernel<<<cnt * chunks, BNL_CNT_THREADS, (size_t)smem_cells * sizeof(int), dev.stream>>>(
+          dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_tables, chunks, smem_cells);
+      BNL_CUDA(ctx, cudaGetLastError());
+      (*launches)++;
+    }
+    if (rq.kind == 2) {
+      BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
+      // tables straight back to the caller, unit by unit (offsets are the caller's).
+      for (int i = 0; i < cnt; i++)
+        BNL_CUDA(ctx, cudaMemcpyAsync(rq.tables + rq.table_off[pos + i], dev.d_tables + dev.h_units[i].table_off,
+                                      (size_t)dev.h_units[i].cells * sizeof(int), cudaMemcpyDeviceToHost,
+                                      dev.stream));
+      BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+    } else {
+      epilogue_kernel<<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
+                                                               rq.kind, rq.code, rq.arg);
+      BNL_CUDA(ctx, cudaGetLastError());
+      (*launches)++;
+      BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)cnt * 4 * sizeof(double),
+                                    cudaMemcpyDeviceToHost, dev.stream));
+      BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
+      BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+      for (int i = 0; i < cnt; i++) {
+        if (rq.o0) rq.o0[pos + i] = dev.h_out[4 * i + 0];
+        if (rq.o1) rq.o1[pos + i] = dev.h_out[4 * i + 1];
+        if (rq.o2) rq.o2[pos + i] = dev.h_out[4 * i + 2];
+      }
+    }
+    float t = 0.f;
+    BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.ev0, dev.ev1));
+    *ms += t;
+    pos += cnt;
+  }
+  return BNL_OK;
+}
+
+int run_request(bnl_ctx *ctx, BnlDataSet &ds, Request &rq) {
+  const int ndev = (int)ctx->devs.size();
+  ctx->last_ms = 0.0;
+  ctx->last_launches = 0;
+  if (rq.n == 0) return BNL_OK;
+  if (ndev == 1) {
+    float ms = 0.f; int launches = 0;
+    int rc = run_block(ctx, ds, 0, rq, 0, rq.n, &ms, &launches);
+    ctx->last_ms = ms; ctx->last_launches = launches;
+    return rc;
+  }
+  // several devices: contiguous blocks of units, one host thread per device so
+  // that the blocks overlap (each thread only touches its own device's state;
+  // bnl_fail() serialises writes to the error string).
+  std::vector<int> rcs(ndev, BNL_OK), launches(ndev, 0);
+  std::vector<float> ms(ndev, 0.f);
+  std::vector<std::thread> workers;
+  for (int d = 0; d < ndev; d++) {
+    int b, e;
+    bnl_block(rq.n, ndev, d, &b, &e);
+    if (b >= e) continue;
+    workers.emplace_back([&, d, b, e]() { rcs[d] = run_block(ctx, ds, d, rq, b, e, &ms[d], &launches[d]); });
+  }
+  for (auto &w : workers) w.join();
+  cudaSetDevice(ctx->devs[0].id);
+  for (int d = 0; d < ndev; d++) {
+    ctx->last_ms = std::max(ctx->last_ms, (double)ms[d]);
+    ctx->last_launches += launches[d];
+  }
+  for (int d = 0; d < ndev; d++)
+    if (rcs[d] != BNL_OK) return rcs[d];
+  return BNL_OK;
+}
+
+}  // namespace
+
+extern "C" int bnl_counts(bnl_ctx *ctx, bnl_data data, int n, const int *x, const int *y,
+                          const int *z_off, const int *z_idx, int32_t *tables,
+                          const int64_t *table_off) {
+  if (!ctx) return BNL_EINVAL;
+  BnlDataSet *ds = find_data(ctx, data);
+  if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  if (n < 0 || (n > 0 && (!x || !z_off || !tables || !table_off)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_counts: bad arguments");
+  Request rq{2, 0, 0.0, n, {}, nullptr, nullptr, nullptr, tables, table_off};
+  rq.units.resize(n);
+  for (int u = 0; u < n; u++) {
+    int nz = z_off[u + 1] - z_off[u];
+    int rc = make_unit(ctx, *ds, x[u], y ? y[u] : -1, z_idx ? z_idx + z_off[u] : nullptr, nz, &rq.units[u]);
+    if (rc) return rc;
+    if (table_off[u + 1] - table_off[u] < rq.units[u].cells)
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_counts: table_off leaves %lld cells for unit %d, which needs %d",
+                      (long long)(table_off[u + 1] - table_off[u]), u, rq.units[u].cells);
+  }
+  return run_request(ctx, *ds, rq);
+}
+
+extern "C" int bnl_ci_discrete(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x,
+                               const int *y, const int *z_off, const int *z_idx,
+                               double *stat, double *df, double *pvalue) {
+  if (!ctx) return BNL_EINVAL;
+  BnlDataSet *ds = find_data(ctx, data);
+  if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  if (test_e != BNL_MI && test_e != BNL_MI_ADF && test_e != BNL_X2 && test_e != BNL_X2_ADF)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a discrete asymptotic test handled here", test_e);
+  if (n < 0 || (n > 0 && (!x || !y || !z_off)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_discrete: bad arguments");
+  Request rq{0, test_e, 0.0, n, {}, stat, df, pvalue, nullptr, nullptr};
+  rq.units.resize(n);
+  for (int u = 0; u < n; u++) {
+    int nz = z_off[u + 1] - z_off[u];
+    int rc = make_unit(ctx, *ds, x[u], y[u], z_idx ? z_idx + z_off[u] : nullptr, nz, &rq.units[u]);
+    if (rc) return rc;
+  }
+  return run_request(ctx, *ds, rq);
+}
+
+extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
+                                  int n, const int *target, const int *pa_off,
+                                  const int *pa_idx, double *score, double *nparams) {
+  if (!ctx) return BNL_EINVAL;
+  BnlDataSet *ds = find_data(ctx, data);
+  if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  if (score_e != BNL_LOGLIK && score_e != BNL_AIC && score_e != BNL_BIC && score_e != BNL_BDE &&
+      score_e != BNL_BDS)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a discrete score handled here", score_e);
+  if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_score_discrete: bad arguments");
+  Request rq{1, score_e, k_or_iss, n, {}, score, nparams, nullptr, nullptr, nullptr};
+  rq.units.resize(n);
+  for (int u = 0; u < n; u++) {
+    int np = pa_off[u + 1] - pa_off[u];
+    int rc = make_unit(ctx, *ds, target[u], -1, pa_idx ? pa_idx + pa_off[u] : nullptr, np, &rq.units[u]);
+    if (rc) return rc;
+  }
+  return run_request(ctx, *ds, rq);
+}

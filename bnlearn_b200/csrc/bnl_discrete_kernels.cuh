@@ -1,0 +1,247 @@
+// bnl_discrete_kernels.cuh -- counting kernels and fused statistic epilogues for
+// discrete data (uint8 packed columns).
+//
+// count_units_kernel   joint count table of one unit per CTA (x row-chunk):
+//                      replaces c_fast_config + fill_{1,2,3}d_table
+//                      (src/core/sets.c:162-218, src/core/contingency.tables.c).
+// epilogue_kernel      margins, statistic / score, df and p-value per unit:
+//                      replaces mi/x2/cmi/cx2_kernel + discrete_(c)df + pchisq
+//                      (src/tests/discrete/*.c) and dlik/cdlik/dpost/cdpost
+//                      (src/scores/discrete.loglikelihood.c, dirichlet.posterior.c).
+#pragma once
+#include "bnl_internal.h"
+#include "bnl_special.cuh"
+
+#define BNL_CNT_THREADS 256
+#define BNL_EPI_THREADS 128
+#define BNL_EPI_WARPS (BNL_EPI_THREADS / 32)
+
+__device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+// ---------------------------------------------------------------------------
+// Generic counting: one CTA = (unit, row chunk). Each thread takes 16 rows at a
+// time (one 128-bit load per column), forms the 16 cell indices in registers and
+// updates the CTA's shared-memory table (or the global one when the table does
+// not fit). NA / padding bytes have bit 7 set and veto their row.
+__global__ void __launch_bounds__(BNL_CNT_THREADS)
+count_units_kernel(const uint8_t *__restrict__ u8, size_t stride, long long groups,
+                   const BnlUnit *__restrict__ units, int *__restrict__ tables,
+                   int chunks, int smem_cells) {
+  extern __shared__ int hist[];
+  __shared__ BnlUnit su;
+  const int u = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
+  if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
+    reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
+  __syncthreads();
+  const int cells = su.cells, ncols = su.ncols;
+  const bool in_smem = cells <= smem_cells;
+  int *gtab = tables + su.table_off;
+  int *tab = in_smem ? hist : gtab;
+  if (in_smem) {
+    for (int c = threadIdx.x; c < cells; c += blockDim.x) hist[c] = 0;
+    __syncthreads();
+  }
+
+  const long long per = (groups + chunks - 1) / chunks;
+  const long long g0 = per * chunk;
+  long long g1 = g0 + per;
+  if (g1 > groups) g1 = groups;
+
+  for (long long g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+    int idx[16];
+    unsigned na[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int j = 0; j < 16; j++) idx[j] = 0;
+    for (int k = 0; k < ncols; k++) {
+      const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
+      const int m = su.mul[k];
+      const unsigned ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        na[q] |= ww[q] & 0x80808080u;
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+          idx[q * 4 + j] += (int)__byte_perm(ww[q], 0, 0x4440 + j) * m;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (!(na[q] & (0x80u << (8 * j)))) atomicAdd(&tab[idx[q * 4 + j]], 1);
+  }
+
+  if (in_smem) {
+    __syncthreads();
+    for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+      const int v = hist[c];
+      if (v) atomicAdd(&gtab[c], v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Epilogue. kind 0: CI test (code = test_e); kind 1: node score (code = score_e).
+// One CTA per unit, one warp per stratum (configuration of Z / of the parents).
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ long long warp_sum_ll(long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void warp_merge_kahan(bnl::KahanSum &k) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double os = __shfl_xor_sync(0xffffffffu, k.s, o);
+    const double oc = __shfl_xor_sync(0xffffffffu, k.c, o);
+    k.merge(os, oc);
+  }
+}
+
+__global__ void __launch_bounds__(BNL_EPI_THREADS)
+epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ tables,
+                double *__restrict__ out, int kind, int code, double arg) {
+  __shared__ int s_marg[BNL_EPI_WARPS][2 * BNL_MAX_LEVELS + 2];
+  __shared__ double s_s[BNL_EPI_WARPS], s_c[BNL_EPI_WARPS], s_df[BNL_EPI_WARPS];
+  __shared__ long long s_n[BNL_EPI_WARPS];
+  __shared__ int s_q;
+
+  const BnlUnit U = units[blockIdx.x];
+  const int *T = tables + U.table_off;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int llx = U.llx, lly = U.lly, llz = U.llz, sl = llx * lly;
+  int *marg = s_marg[warp];
+
+  // BDs: the prior is spread over the OBSERVED parent configurations only
+  // (src/scores/dirichlet.posterior.c:180 -> all_levels = FALSE).
+  int q = llz;
+  if (kind == 1 && code == BNL_BDS) {
+    if (threadIdx.x == 0) s_q = 0;
+    __syncthreads();
+    int mine = 0;
+    for (int k = warp; k < llz; k += BNL_EPI_WARPS) {
+      long long nk = 0;
+      for (int c = lane; c < sl; c += 32) nk += T[(size_t)k * sl + c];
+      nk = warp_sum_ll(nk);
+      mine += nk > 0;
+    }
+    if (lane == 0 && mine) atomicAdd(&s_q, mine);
+    __syncthreads();
+    q = s_q;
+  }
+
+  bnl::KahanSum acc;
+  double dfacc = 0.0;
+  long long nobs = 0;
+  const bool is_bd = kind == 1 && (code == BNL_BDE || code == BNL_BDS);
+  const double alpha = is_bd && q > 0 ? arg / ((double)llx * (double)q) : 1.0;
+  const double aq = is_bd && q > 0 ? arg / (double)q : 1.0;
+  const double lg_alpha = is_bd ? bnl::lgamma_pos(alpha) : 0.0;
+  const double lg_aq = is_bd ? bnl::lgamma_pos(aq) : 0.0;
+
+  for (int k = warp; k < llz; k += BNL_EPI_WARPS) {
+    const int *S = T + (size_t)k * sl;
+    if (kind == 0) {
+      for (int i = lane; i < llx + lly; i += 32) marg[i] = 0;
+      __syncwarp();
+      long long nk = 0;
+      for (int c = lane; c < sl; c += 32) {
+        const int n = S[c];
+        if (n) {
+          atomicAdd(&marg[c / lly], n);
+          atomicAdd(&marg[llx + c % lly], n);
+          nk += n;
+        }
+      }
+      nk = warp_sum_ll(nk);
+      __syncwarp();
+      if (code == BNL_MI_ADF || code == BNL_X2_ADF) {
+        int alx = 0, aly = 0;
+        for (int i = lane; i < llx; i += 32) alx += marg[i] > 0;
+        for (int j = lane; j < lly; j += 32) aly += marg[llx + j] > 0;
+        alx = (int)warp_sum_ll(alx);
+        aly = (int)warp_sum_ll(aly);
+        if (alx < 1) alx = 1;
+        if (aly < 1) aly = 1;
+        if (lane == 0) dfacc += (double)(alx - 1) * (double)(aly - 1);
+      }
+      if (lane == 0) nobs += nk;
+      if (nk > 0) {
+        const double dnk = (double)nk;
+        if (code == BNL_MI || code == BNL_MI_ADF) {
+          for (int c = lane; c < sl; c += 32) {
+            const int n = S[c];
+            if (n) {
+              const double ni = (double)marg[c / lly], nj = (double)marg[llx + c % lly];
+              acc.add((double)n * log((double)n * dnk / (ni * nj)));
+            }
+          }
+        } else {
+          for (int c = lane; c < sl; c += 32) {
+            const double e = (double)marg[c / lly] * (double)marg[llx + c % lly] / dnk;
+            if (e != 0.0) {
+              const double d = (double)S[c] - e;
+              acc.add(d * d / e);
+            }
+          }
+        }
+      }
+      __syncwarp();
+    } else {
+      long long nk = 0;
+      for (int c = lane; c < sl; c += 32) nk += S[c];
+      nk = warp_sum_ll(nk);
+      if (lane == 0) nobs += nk;
+      if (is_bd) {
+        if (q == 0 || (code == BNL_BDS && nk == 0)) continue;
+        for (int c = lane; c < sl; c += 32)
+          acc.add(bnl::lgamma_pos((double)S[c] + alpha) - lg_alpha);
+        if (lane == 0) acc.add(lg_aq - bnl::lgamma_pos((double)nk + aq));
+      } else if (nk > 0) {
+        for (int c = lane; c < sl; c += 32) {
+          const int n = S[c];
+          if (n) acc.add((double)n * log((double)n / (double)nk));
+        }
+      }
+    }
+  }
+
+  warp_merge_kahan(acc);
+  dfacc = warp_sum_d(dfacc);
+  nobs = warp_sum_ll(nobs);
+  if (lane == 0) { s_s[warp] = acc.s; s_c[warp] = acc.c; s_df[warp] = dfacc; s_n[warp] = nobs; }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  bnl::KahanSum tot;
+  double df = 0.0;
+  long long n = 0;
+  for (int w = 0; w < BNL_EPI_WARPS; w++) { tot.merge(s_s[w], s_c[w]); df += s_df[w]; n += s_n[w]; }
+  double *o = out + (size_t)blockIdx.x * 4;
+  if (kind == 0) {
+    const bool adf = code == BNL_MI_ADF || code == BNL_X2_ADF;
+    if (!adf) df = (double)(llx - 1) * (double)(lly - 1) * (double)llz;
+    double stat = 0.0;
+    if (n > 0 && !(adf && (double)n < 5.0 * (double)llx * (double)lly * (double)llz)) {
+      if (code == BNL_MI || code == BNL_MI_ADF) stat = tot.value() / (double)n * (2.0 * (double)n);
+      else stat = tot.value();
+    }
+    o[0] = stat; o[1] = df; o[2] = bnl::pchisq_upper(stat, df); o[3] = (double)n;
+  } else {
+    const double nparams = (double)(llx - 1) * (double)llz;
+    double s = tot.value();
+    if (code == BNL_AIC || code == BNL_BIC) s -= arg * nparams;
+    o[0] = s; o[1] = nparams; o[2] = 0.0; o[3] = (double)n;
+  }
+}

@@ -1,0 +1,226 @@
+// bnl_gaussian.cu -- host side of the Gaussian entry points.
+#include <string.h>
+#include <algorithm>
+#include <thread>
+
+#include "bnl_gaussian_kernels.cuh"
+
+// Means and covariance of all numeric columns on one device; called once per
+// data set from bnl_data_register().
+int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
+  BnlDevice &dev = ctx->devs[di];
+  BnlDeviceData &dd = ds.dev[di];
+  const int p = ds.nc;
+  BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  BNL_CUDA(ctx, cudaMalloc((void **)&dd.mean, (size_t)p * sizeof(double)));
+  BNL_CUDA(ctx, cudaMalloc((void **)&dd.cov, (size_t)p * p * sizeof(double)));
+
+  // row slices: enough CTAs to fill the machine, at least 8192 rows per slice,
+  // and at most 256 MiB of partials.
+  const int ntile = (p + GRAM_TILE - 1) / GRAM_TILE;
+  const int ntri = ntile * (ntile + 1) / 2;
+  long long nsplit = (4ll * dev.sm_count + ntri - 1) / ntri;
+  nsplit = std::min(nsplit, std::max(1ll, ds.nobs / 8192));
+  nsplit = std::min(nsplit, std::max(1ll, (256ll << 20) / ((long long)p * p * 8)));
+  nsplit = std::max(nsplit, 1ll);
+  long long msplit = std::min<long long>(std::max(1ll, ds.nobs / 65536), 64);
+
+  double *partial = nullptr;
+  size_t pbytes = std::max((size_t)nsplit * p * p, (size_t)msplit * p) * sizeof(double);
+  cudaError_t e = cudaMalloc((void **)&partial, pbytes);
+  if (e != cudaSuccess)
+    return bnl_fail(ctx, BNL_ENOMEM, "cudaMalloc of %zu bytes for the Gram partials failed", pbytes);
+
+  col_sum_kernel<<<dim3(p, (unsigned)msplit), 256, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, p, partial);
+  col_mean_kernel<<<(p + 127) / 128, 128, 0, dev.stream>>>(partial, (int)msplit, p, ds.nobs, dd.mean);
+  gram_dmma_kernel<<<dim3(ntri, (unsigned)nsplit), GRAM_THREADS, 0, dev.stream>>>(
+      dd.f64, ds.stride_f64, ds.nobs, p, dd.mean, partial, ntile);
+  const long long elems = (long long)p * p;
+  gram_finish_kernel<<<(unsigned)((elems + 255) / 256), 256, 0, dev.stream>>>(partial, (int)nsplit, p,
+                                                                              ds.nobs, dd.cov);
+  e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(dev.stream);
+  cudaFree(partial);
+  if (e != cudaSuccess)
+    return bnl_fail(ctx, BNL_ECUDA, "Gaussian moments failed: %s", cudaGetErrorString(e));
+  if (di == 0) {
+    ds.h_mean.resize(p);
+    ds.h_cov.resize((size_t)p * p);
+    BNL_CUDA(ctx, cudaMemcpy(ds.h_mean.data(), dd.mean, (size_t)p * sizeof(double), cudaMemcpyDeviceToHost));
+    BNL_CUDA(ctx, cudaMemcpy(ds.h_cov.data(), dd.cov, (size_t)p * p * sizeof(double), cudaMemcpyDeviceToHost));
+  }
+  return BNL_OK;
+}
+
+namespace {
+
+struct GRequest {
+  int kind;              // 0 tests, 1 scores
+  int code;
+  double arg;
+  int n, kmax;
+  std::vector<int> gidx; // n * BNL_GW
+  double *o0, *o1, *o2;
+};
+
+int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, float *ms, int *launches) {
+  BnlDevice &dev = ctx->devs[d];
+  BnlDeviceData &dd = ds.dev[d];
+  BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  if (!dev.gattr_done) {
+    BNL_CUDA(ctx, cudaFuncSetAttribute(gauss_ci_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 1024));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(gauss_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 1024));
+    dev.gattr_done = true;
+  }
+  const int cnt = e - b;
+  int rc;
+  if ((rc = bnl_reserve_pinned(ctx, &dev.h_gidx, &dev.h_gidx_cap, (size_t)cnt * BNL_GW))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_gidx, &dev.gidx_cap, (size_t)cnt * BNL_GW))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_out, &dev.out_cap, (size_t)cnt * 4))) return rc;
+  if ((rc = bnl_reserve_pinned(ctx, &dev.h_out, &dev.h_out_cap, (size_t)cnt * 4))) return rc;
+  memcpy(dev.h_gidx, rq.gidx.data() + (size_t)b * BNL_GW, (size_t)cnt * BNL_GW * sizeof(int));
+
+  // threads per CTA: as many as the per-thread work matrices allow (tests need
+  // A and V, scores one matrix), between 32 and 128.
+  const int mats = rq.kind == 0 ? 2 : 1;
+  const size_t per_thread = (size_t)mats * rq.kmax * rq.kmax * sizeof(double);
+  int tpb = 128;
+  while (tpb > 32 && per_thread * tpb > (size_t)dev.max_smem - 2048) tpb >>= 1;
+  const size_t smem = per_thread * tpb;
+  if (smem > (size_t)dev.max_smem - 1024)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "unit with %d columns needs too much shared memory", rq.kmax);
+
+  BNL_CUDA(ctx, cudaEventRecord(dev.ev0, dev.stream));
+  BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_gidx, dev.h_gidx, (size_t)cnt * BNL_GW * sizeof(int),
+                                cudaMemcpyHostToDevice, dev.stream));
+  const int grid = (cnt + tpb - 1) / tpb;
+  if (rq.kind == 0)
+    gauss_ci_kernel<<<grid, tpb, smem, dev.stream>>>(dev.d_gidx, cnt, dd.cov, ds.nc, ds.nobs, rq.code,
+                                                     rq.kmax, dev.d_out);
+  else
+    gauss_score_kernel<<<grid, tpb, smem, dev.stream>>>(dev.d_gidx, cnt, dd.cov, dd.mean, ds.nc, ds.nobs,
+                                                        rq.code, rq.arg, rq.kmax, dev.d_out);
+  BNL_CUDA(ctx, cudaGetLastError());
+  (*launches)++;
+  BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)cnt * 4 * sizeof(double),
+                                cudaMemcpyDeviceToHost, dev.stream));
+  BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
+  BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+  for (int i = 0; i < cnt; i++) {
+    if (rq.o0) rq.o0[b + i] = dev.h_out[4 * i + 0];
+    if (rq.o1) rq.o1[b + i] = dev.h_out[4 * i + 1];
+    if (rq.o2) rq.o2[b + i] = dev.h_out[4 * i + 2];
+  }
+  BNL_CUDA(ctx, cudaEventElapsedTime(ms, dev.ev0, dev.ev1));
+  return BNL_OK;
+}
+
+int run_grequest(bnl_ctx *ctx, BnlDataSet &ds, GRequest &rq) {
+  const int ndev = (int)ctx->devs.size();
+  ctx->last_ms = 0.0;
+  ctx->last_launches = 0;
+  if (rq.n == 0) return BNL_OK;
+  std::vector<int> rcs(ndev, BNL_OK), launches(ndev, 0);
+  std::vector<float> ms(ndev, 0.f);
+  if (ndev == 1) {
+    rcs[0] = run_gblock(ctx, ds, 0, rq, 0, rq.n, &ms[0], &launches[0]);
+  } else {
+    std::vector<std::thread> workers;
+    for (int d = 0; d < ndev; d++) {
+      int b, e;
+      bnl_block(rq.n, ndev, d, &b, &e);
+      if (b >= e) continue;
+      workers.emplace_back([&, d, b, e]() { rcs[d] = run_gblock(ctx, ds, d, rq, b, e, &ms[d], &launches[d]); });
+    }
+    for (auto &w : workers) w.join();
+    cudaSetDevice(ctx->devs[0].id);
+  }
+  for (int d = 0; d < ndev; d++) {
+    ctx->last_ms = std::max(ctx->last_ms, (double)ms[d]);
+    ctx->last_launches += launches[d];
+  }
+  for (int d = 0; d < ndev; d++)
+    if (rcs[d] != BNL_OK) return rcs[d];
+  return BNL_OK;
+}
+
+int fill_gunit(bnl_ctx *ctx, const BnlDataSet &ds, int *g, int a, int b, const int *rest, int nrest, int *kmax) {
+  const int k = (b >= 0 ? 2 : 1) + nrest;
+  if (k > BNL_MAXK)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "a unit may involve at most %d columns (got %d)", BNL_MAXK, k);
+  auto slot = [&](int c) { return (c >= 0 && c < ds.ncols && ds.is_numeric[c]) ? ds.slot[c] : -1; };
+  int pos = 0;
+  g[pos++] = k;
+  int s = slot(a);
+  if (s < 0) return bnl_fail(ctx, BNL_EINVAL, "column %d: out of range or not numeric", a);
+  g[pos++] = s;
+  if (b >= 0) {
+    s = slot(b);
+    if (s < 0) return bnl_fail(ctx, BNL_EINVAL, "column %d: out of range or not numeric", b);
+    g[pos++] = s;
+  }
+  for (int j = 0; j < nrest; j++) {
+    s = slot(rest[j]);
+    if (s < 0) return bnl_fail(ctx, BNL_EINVAL, "column %d: out of range or not numeric", rest[j]);
+    g[pos++] = s;
+  }
+  *kmax = std::max(*kmax, k);
+  return BNL_OK;
+}
+
+}  // namespace
+
+extern "C" int bnl_ci_gaussian(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x,
+                               const int *y, const int *z_off, const int *z_idx,
+                               double *stat, double *df, double *pvalue) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  if (test_e != BNL_COR && test_e != BNL_ZF && test_e != BNL_MI_G)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a Gaussian test handled here", test_e);
+  if (n < 0 || (n > 0 && (!x || !y || !z_off)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_gaussian: bad arguments");
+  GRequest rq{0, test_e, 0.0, n, 2, {}, stat, df, pvalue};
+  rq.gidx.assign((size_t)n * BNL_GW, 0);
+  for (int u = 0; u < n; u++) {
+    int rc = fill_gunit(ctx, ds, &rq.gidx[(size_t)u * BNL_GW], x[u], y[u],
+                        z_idx ? z_idx + z_off[u] : nullptr, z_off[u + 1] - z_off[u], &rq.kmax);
+    if (rc) return rc;
+  }
+  return run_grequest(ctx, ds, rq);
+}
+
+extern "C" int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n,
+                                  const int *target, const int *pa_off, const int *pa_idx,
+                                  double *score, double *nparams) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  if (score_e != BNL_LOGLIK_G && score_e != BNL_AIC_G && score_e != BNL_BIC_G)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a Gaussian score handled here", score_e);
+  if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_score_gaussian: bad arguments");
+  GRequest rq{1, score_e, k, n, 1, {}, score, nparams, nullptr};
+  rq.gidx.assign((size_t)n * BNL_GW, 0);
+  for (int u = 0; u < n; u++) {
+    int rc = fill_gunit(ctx, ds, &rq.gidx[(size_t)u * BNL_GW], target[u], -1,
+                        pa_idx ? pa_idx + pa_off[u] : nullptr, pa_off[u + 1] - pa_off[u], &rq.kmax);
+    if (rc) return rc;
+  }
+  return run_grequest(ctx, ds, rq);
+}
+
+extern "C" int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, double *cov) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  if (ds.nc == 0) return bnl_fail(ctx, BNL_EINVAL, "the data set has no numeric columns");
+  if (mean) memcpy(mean, ds.h_mean.data(), ds.h_mean.size() * sizeof(double));
+  if (cov) memcpy(cov, ds.h_cov.data(), ds.h_cov.size() * sizeof(double));
+  return BNL_OK;
+}

@@ -1,0 +1,362 @@
+// bnl_gaussian_kernels.cuh -- Gaussian side: column means, the centred
+// cross-product (Gram) matrix on the fp64 tensor cores, and batched small
+// solves (partial correlations, OLS residual variances) served from it.
+//
+//   col_sum_kernel / gram_dmma_kernel / gram_finish_kernel
+//        replace c_meanvec + c_covmat recomputed per test from the raw columns
+//        (src/core/moments.c:34-45, src/core/covariance.matrix.c:65-97).
+//   gauss_ci_kernel    replaces c_fast_cor / c_fast_pcor + cor_*_trans + pt /
+//        pnorm / pchisq (src/core/correlation.c:22-92,
+//        src/tests/gaussian/gaussian.tests.c:4-22, df.adjust.c:4-28).
+//   gauss_score_kernel replaces glik / cglik over c_ols
+//        (src/scores/gaussian.loglikelihood.c:8-83, src/math/least.squares.c).
+#pragma once
+#include "bnl_internal.h"
+#include "bnl_special.cuh"
+
+#define GRAM_TILE 64          // C tile edge per CTA
+#define GRAM_KB 32            // rows staged per step
+#define GRAM_LD (GRAM_KB + 4) // smem row stride in doubles: conflict-free 64-bit fragment loads
+#define GRAM_THREADS 128
+#define BNL_GW (BNL_MAXK + 1) // ints per Gaussian unit descriptor: count, then column slots
+
+// ---------------------------------------------------------------------------
+// per-column partial sums: grid (nc, splits); partial[split * nc + col].
+__global__ void __launch_bounds__(256)
+col_sum_kernel(const double *__restrict__ X, size_t stride, long long nobs, int nc,
+               double *__restrict__ partial) {
+  __shared__ double ss[8], sc[8];
+  const int col = blockIdx.x, split = blockIdx.y, nsplit = gridDim.y;
+  const long long per = (nobs + nsplit - 1) / nsplit;
+  const long long r0 = per * split;
+  long long r1 = r0 + per;
+  if (r1 > nobs) r1 = nobs;
+  const double *x = X + (size_t)col * stride;
+  bnl::KahanSum acc;
+  for (long long r = r0 + threadIdx.x; r < r1; r += blockDim.x) acc.add(x[r]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double os = __shfl_xor_sync(0xffffffffu, acc.s, o);
+    const double oc = __shfl_xor_sync(0xffffffffu, acc.c, o);
+    acc.merge(os, oc);
+  }
+  if ((threadIdx.x & 31) == 0) { ss[threadIdx.x >> 5] = acc.s; sc[threadIdx.x >> 5] = acc.c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    bnl::KahanSum t;
+    for (int w = 0; w < 8; w++) t.merge(ss[w], sc[w]);
+    partial[(size_t)split * nc + col] = t.value();
+  }
+}
+
+__global__ void col_mean_kernel(const double *__restrict__ partial, int nsplit, int nc,
+                                long long nobs, double *__restrict__ mean) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= nc) return;
+  bnl::KahanSum t;
+  for (int s = 0; s < nsplit; s++) t.add(partial[(size_t)s * nc + col]);
+  mean[col] = nobs > 0 ? t.value() / (double)nobs : 0.0;
+}
+
+// ---------------------------------------------------------------------------
+// Gram matrix of the centred columns on the fp64 tensor cores (DMMA,
+// mma.sync.m8n8k4.f64; tcgen05 has no fp64 kind). One CTA = one upper-triangular
+// 64 x 64 tile of C over one slice of the rows; 4 warps, each a 32 x 32 sub-tile
+// = 4 x 4 DMMA tiles. Columns are centred as they are staged into shared memory
+// (the reference centres too, src/core/covariance.matrix.c:87), rows past nobs
+// and columns past p contribute zeros.
+__device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(GRAM_THREADS)
+gram_dmma_kernel(const double *__restrict__ X, size_t stride, long long nobs, int p,
+                 const double *__restrict__ mean, double *__restrict__ partial, int ntile) {
+  __shared__ __align__(16) double As[GRAM_TILE][GRAM_LD];
+  __shared__ __align__(16) double Bs[GRAM_TILE][GRAM_LD];
+
+  // linear upper-triangular tile index -> (ti, tj), ti <= tj.
+  int t = blockIdx.x, ti = 0;
+  while (t >= ntile - ti) { t -= ntile - ti; ti++; }
+  const int tj = ti + t;
+  const bool diag = ti == tj;
+  const int nsplit = gridDim.y, split = blockIdx.y;
+  const long long steps = (nobs + GRAM_KB - 1) / GRAM_KB;
+  const long long per = (steps + nsplit - 1) / nsplit;
+  const long long s0 = per * split;
+  long long s1 = s0 + per;
+  if (s1 > steps) s1 = steps;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+  const int g = lane >> 2, q = lane & 3;
+
+  double acc[4][4][2];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+  for (long long s = s0; s < s1; s++) {
+    const long long r0 = s * GRAM_KB;
+    // stage: 64 columns x 32 rows per operand, as double2 (16 per column).
+    for (int idx = threadIdx.x; idx < GRAM_TILE * (GRAM_KB / 2); idx += GRAM_THREADS) {
+      const int c = idx / (GRAM_KB / 2), r2 = (idx % (GRAM_KB / 2)) * 2;
+      const long long r = r0 + r2;
+      {
+        const int col = ti * GRAM_TILE + c;
+        double2 v = make_double2(0.0, 0.0);
+        if (col < p) {
+          const double m = mean[col];
+          const double2 w = *reinterpret_cast<const double2 *>(X + (size_t)col * stride + r);
+          v.x = r < nobs ? w.x - m : 0.0;
+          v.y = r + 1 < nobs ? w.y - m : 0.0;
+        }
+        *reinterpret_cast<double2 *>(&As[c][r2]) = v;
+      }
+      if (!diag) {
+        const int col = tj * GRAM_TILE + c;
+        double2 v = make_double2(0.0, 0.0);
+        if (col < p) {
+          const double m = mean[col];
+          const double2 w = *reinterpret_cast<const double2 *>(X + (size_t)col * stride + r);
+          v.x = r < nobs ? w.x - m : 0.0;
+          v.y = r + 1 < nobs ? w.y - m : 0.0;
+        }
+        *reinterpret_cast<double2 *>(&Bs[c][r2]) = v;
+      }
+    }
+    __syncthreads();
+    const double (*Bp)[GRAM_LD] = diag ? As : Bs;
+#pragma unroll
+    for (int kk = 0; kk < GRAM_KB; kk += 4) {
+      double a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) a[i] = As[wm + i * 8 + g][kk + q];
+#pragma unroll
+      for (int j = 0; j < 4; j++) b[j] = Bp[wn + j * 8 + g][kk + q];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) dmma_m8n8k4(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+    }
+    __syncthreads();
+  }
+
+  double *out = partial + (size_t)split * p * p;
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int row = ti * GRAM_TILE + wm + i * 8 + g;
+      const int col = tj * GRAM_TILE + wn + j * 8 + q * 2;
+      if (row < p && col < p) out[(size_t)row + (size_t)col * p] = acc[i][j][0];
+      if (row < p && col + 1 < p) out[(size_t)row + (size_t)(col + 1) * p] = acc[i][j][1];
+    }
+}
+
+// sum the row-slice partials, divide by nobs - 1, mirror the upper triangle.
+__global__ void gram_finish_kernel(const double *__restrict__ partial, int nsplit, int p,
+                                   long long nobs, double *__restrict__ cov) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= (long long)p * p) return;
+  const int i = (int)(e % p), j = (int)(e / p);
+  if (i / GRAM_TILE > j / GRAM_TILE) return;     // lower-triangular tiles are never written
+  bnl::KahanSum t;
+  for (int s = 0; s < nsplit; s++) t.add(partial[(size_t)s * p * p + e]);
+  const double v = nobs > 1 ? t.value() / (double)(nobs - 1) : 0.0;
+  cov[e] = v;
+  if (i / GRAM_TILE < j / GRAM_TILE) cov[(size_t)j + (size_t)i * p] = v;
+}
+
+// ---------------------------------------------------------------------------
+// Batched small solves. One thread per unit; its k x k work matrices live in
+// shared memory, interleaved across the CTA's threads (element e of thread t at
+// [e * blockDim.x + t]) so that every access is bank-conflict free.
+
+struct SmemMat {
+  double *base; int ld;   // ld = blockDim.x
+  __device__ __forceinline__ double &operator()(int e) const { return base[(size_t)e * ld]; }
+};
+
+// cyclic Jacobi eigen-decomposition of the symmetric k x k matrix A (destroyed:
+// its diagonal ends up holding the eigenvalues), eigenvectors in the columns of V.
+__device__ void jacobi_eigen(SmemMat A, SmemMat V, int k) {
+  for (int i = 0; i < k; i++)
+    for (int j = 0; j < k; j++) V(i + j * k) = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 60; sweep++) {
+    double off = 0.0, diag = 0.0;
+    for (int i = 0; i < k; i++) {
+      const double d = A(i + i * k);
+      diag += d * d;
+      for (int j = i + 1; j < k; j++) { const double o = A(i + j * k); off += o * o; }
+    }
+    if (off == 0.0 || off <= 1e-40 * diag) break;
+    for (int r = 0; r < k - 1; r++)
+      for (int c = r + 1; c < k; c++) {
+        const double apq = A(r + c * k);
+        if (apq == 0.0) continue;
+        const double theta = (A(c + c * k) - A(r + r * k)) / (2.0 * apq);
+        const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double cs = 1.0 / sqrt(t * t + 1.0), sn = t * cs;
+        for (int m = 0; m < k; m++) {
+          const double amr = A(m + r * k), amc = A(m + c * k);
+          A(m + r * k) = cs * amr - sn * amc;
+          A(m + c * k) = sn * amr + cs * amc;
+        }
+        for (int m = 0; m < k; m++) {
+          const double arm = A(r + m * k), acm = A(c + m * k);
+          A(r + m * k) = cs * arm - sn * acm;
+          A(c + m * k) = sn * arm + cs * acm;
+        }
+        for (int m = 0; m < k; m++) {
+          const double vmr = V(m + r * k), vmc = V(m + c * k);
+          V(m + r * k) = cs * vmr - sn * vmc;
+          V(m + c * k) = sn * vmr + cs * vmc;
+        }
+      }
+  }
+}
+
+// units: gidx[u * BNL_GW] = k, then k column slots (x, y, z...). out: 4 doubles.
+__global__ void gauss_ci_kernel(const int *__restrict__ gidx, int n, const double *__restrict__ cov,
+                                int p, long long nobs, int test, int kmax,
+                                double *__restrict__ out) {
+  extern __shared__ double gsm[];
+  const int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n) return;
+  const int *d = gidx + (size_t)u * BNL_GW;
+  const int k = d[0], nz = k - 2;
+  double *o = out + (size_t)u * 4;
+  const double tol = bnl::kSqrtEps;
+
+  double df = (test == BNL_COR) ? (double)(nobs - nz - 2)
+            : (test == BNL_ZF) ? (double)(nobs - nz - 3) : 1.0;
+  if (df < 1.0) { o[0] = 0.0; o[1] = 0.0; o[2] = 1.0; o[3] = 1.0; return; }   // o[3]: R warning
+
+  double r;
+  if (nz == 0) {
+    // c_fast_cor(): cov / sqrt(var_x var_y) with the guard on the SUMS of squares.
+    const double sxx = cov[(size_t)d[1] + (size_t)d[1] * p] * (double)(nobs - 1);
+    const double syy = cov[(size_t)d[2] + (size_t)d[2] * p] * (double)(nobs - 1);
+    const double sxy = cov[(size_t)d[1] + (size_t)d[2] * p] * (double)(nobs - 1);
+    r = (sxx < tol || syy < tol) ? 0.0 : sxy / sqrt(sxx * syy);
+  } else {
+    SmemMat A{gsm + threadIdx.x, (int)blockDim.x};
+    SmemMat V{gsm + (size_t)kmax * kmax * blockDim.x + threadIdx.x, (int)blockDim.x};
+    for (int i = 0; i < k; i++)
+      for (int j = 0; j < k; j++) A(i + j * k) = cov[(size_t)d[1 + i] + (size_t)d[1 + j] * p];
+    jacobi_eigen(A, V, k);
+    // pseudo-inverse entries with singular values <= dim * d_max * eps dropped
+    // (src/core/correlation.c:69-83).
+    double dmax = 0.0;
+    for (int i = 0; i < k; i++) dmax = fmax(dmax, fabs(A(i + i * k)));
+    const double sv_tol = (double)k * dmax * tol * tol;
+    double k11 = 0.0, k12 = 0.0, k22 = 0.0;
+    for (int i = 0; i < k; i++) {
+      const double lam = A(i + i * k);
+      if (fabs(lam) > sv_tol) {
+        const double v0 = V(0 + i * k), v1 = V(1 + i * k);
+        k11 += v0 * v0 / lam; k12 += v0 * v1 / lam; k22 += v1 * v1 / lam;
+      }
+    }
+    r = (k11 < tol || k22 < tol) ? 0.0 : -k12 / sqrt(k11 * k22);
+  }
+  double clamped = 0.0;
+  if (r > 1.0) { r = 1.0; clamped = 2.0; } else if (r < -1.0) { r = -1.0; clamped = 2.0; }
+
+  double stat, pv;
+  if (test == BNL_COR) {
+    const double t = r * sqrt(df) / sqrt(1.0 - r * r);
+    stat = r;
+    pv = bnl::pt_two_sided(t, df);
+  } else if (test == BNL_ZF) {
+    stat = log((1.0 + r) / (1.0 - r)) / 2.0 * sqrt(df);
+    pv = bnl::pnorm_two_sided(stat);
+  } else {
+    stat = 2.0 * (double)nobs * (-0.5 * log(1.0 - r * r));
+    pv = bnl::pchisq_upper(stat, df);
+  }
+  o[0] = stat; o[1] = df; o[2] = pv; o[3] = clamped;
+}
+
+// Gaussian node score from the moments. Unit: gidx = k, target, parents...
+// S(i, j) below is the centred cross-product (n - 1) * cov of the unit's columns.
+__global__ void gauss_score_kernel(const int *__restrict__ gidx, int n, const double *__restrict__ cov,
+                                   const double *__restrict__ mean, int p, long long nobs,
+                                   int score, double kpen, int kmax, double *__restrict__ out) {
+  extern __shared__ double gsm[];
+  const int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n) return;
+  const int *d = gidx + (size_t)u * BNL_GW;
+  const int k = d[0], np = k - 1;
+  double *o = out + (size_t)u * 4;
+  const double tol = bnl::kSqrtEps;
+  const double nm1 = (double)(nobs - 1);
+  auto C = [&](int i, int j) { return cov[(size_t)d[1 + i] + (size_t)d[1 + j] * p]; };
+
+  double sse = 0.0;      // residual sum of squares of the fit
+  double sd;
+  if (nobs == 0) sd = NAN;
+  else if (nobs <= np + 1) sd = 0.0;
+  else {
+    if (np == 0) {
+      sse = C(0, 0) * nm1;
+    } else if (np == 1) {
+      // c_ols1(): singular iff the regressor's variance is below sqrt(eps).
+      const bool singular = fabs(C(1, 1)) < tol;
+      sse = singular ? C(0, 0) * nm1 : (C(0, 0) - C(0, 1) / C(1, 1) * C(0, 1)) * nm1;
+    } else if (np == 2) {
+      // c_ols2(): the three collinearity cases of src/math/least.squares.c:171-173.
+      const double c11 = C(1, 1), c22 = C(2, 2), c12 = C(1, 2), c01 = C(0, 1), c02 = C(0, 2);
+      const bool s1 = fabs(c11) < tol;
+      const bool s2 = (fabs(c22) < tol) || (fabs(c12) / sqrt(c11 * c22) > 1.0 - tol);
+      double fit;
+      if (s1 && !s2) fit = c02 / c22 * c02;
+      else if (!s1 && s2) fit = c01 / c11 * c01;
+      else if (s1 && s2) fit = 0.0;
+      else {
+        const double den = c11 * c22 - c12 * c12;
+        const double b1 = (c22 * c01 - c12 * c02) / den, b2 = (c11 * c02 - c12 * c01) / den;
+        fit = b1 * c01 + b2 * c02;
+      }
+      sse = (C(0, 0) - fit) * nm1;
+    } else {
+      // general case: the reference runs R's dqrdc2 on [1, parents] with
+      // tolerance sqrt(eps) (src/math/linear.algebra.c:140, 197): a column whose
+      // norm after projecting out the accepted ones falls below tol * its
+      // original (uncentred) norm is set aside. Same rule here, as an outer-
+      // product Cholesky on the centred cross-products (the intercept is the
+      // centring), parents in order, target last.
+      SmemMat S{gsm + threadIdx.x, (int)blockDim.x};
+      for (int i = 0; i < k; i++)
+        for (int j = 0; j < k; j++) S(i + j * k) = C(i, j) * nm1;
+      for (int l = 1; l < k; l++) {
+        const double m = mean[d[1 + l]];
+        const double orig = sqrt(C(l, l) * nm1 + (double)nobs * m * m);
+        const double piv = S(l + l * k);
+        if (!(piv > 0.0) || sqrt(piv) < orig * tol) continue;     // dropped column
+        for (int i = 0; i < k; i++) {
+          if (i == l) continue;
+          const double f = S(i + l * k) / piv;
+          if (f == 0.0) continue;
+          for (int j = 0; j < k; j++)
+            if (j != l) S(i + j * k) -= f * S(l + j * k);
+        }
+        for (int i = 0; i < k; i++)
+          if (i != l) { S(i + l * k) = 0.0; S(l + i * k) = 0.0; }
+      }
+      sse = S(0);
+    }
+    if (sse < 0.0) sse = 0.0;
+    sd = sqrt(sse / (double)(nobs - np - 1));
+  }
+
+  double res;
+  if (!(sd >= tol)) res = (sd < tol) ? -INFINITY : NAN;
+  else res = -(double)nobs * (bnl::kLnSqrt2Pi + log(sd)) - 0.5 * sse / (sd * sd);
+  const double nparams = (double)(np + 2);
+  if (score == BNL_AIC_G || score == BNL_BIC_G) res -= kpen * nparams;
+  o[0] = res; o[1] = nparams; o[2] = 0.0; o[3] = 0.0;
+}

@@ -1,0 +1,122 @@
+// bnl_internal.h -- host-side state behind the C ABI (include/bnl_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/bnl_b200.h"
+
+#define BNL_MAXK 16            // columns per unit: x, y and up to 14 conditioning / 15 parents
+#define BNL_NA_U8 0xFFu        // NA and row padding in the packed uint8 layout
+#define BNL_MAX_LEVELS 127     // bit 7 of a packed code marks NA
+#define BNL_COL_ALIGN 256      // bytes; every packed column starts 256-byte aligned
+
+// one unit of discrete work as the kernels see it.
+struct BnlUnit {
+  long long table_off;    // offset (int32 elements) of this unit's table in the scratch
+  int cells;              // llx * lly * llz
+  int ncols;              // columns involved
+  int llx, lly, llz;      // table is n[z][x][y]
+  int pad;
+  int col[BNL_MAXK];      // packed-column slot, order: y (if any), x, z_1, z_2, ...
+  int mul[BNL_MAXK];      // contribution of each column to the cell index
+};
+
+// per-device resources.
+struct BnlDevice {
+  int id = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // grow-only scratch
+  BnlUnit *d_units = nullptr; size_t units_cap = 0;
+  int *d_tables = nullptr; size_t tables_cap = 0;        // int32 elements
+  double *d_out = nullptr; size_t out_cap = 0;           // doubles
+  int *d_gidx = nullptr; size_t gidx_cap = 0;            // Gaussian unit descriptors
+  BnlUnit *h_units = nullptr; size_t h_units_cap = 0;    // pinned
+  double *h_out = nullptr; size_t h_out_cap = 0;         // pinned
+  int *h_gidx = nullptr; size_t h_gidx_cap = 0;          // pinned
+  int sm_count = 148;
+  int max_smem = 48 * 1024;
+  bool attr_done = false;   // per-device kernel attributes set
+  bool gattr_done = false;
+};
+
+// one device's copy of a data set.
+struct BnlDeviceData {
+  uint8_t *u8 = nullptr;       // nd columns, stride_u8 bytes apart
+  double *f64 = nullptr;       // nc columns, stride_f64 doubles apart
+  double *mean = nullptr;      // nc
+  double *cov = nullptr;       // nc x nc, column-major, divisor nobs - 1
+};
+
+struct BnlDataSet {
+  int ncols = 0;
+  long long nobs = 0;
+  int nd = 0, nc = 0;                   // discrete / numeric column counts
+  size_t stride_u8 = 0, stride_f64 = 0;
+  std::vector<int> is_numeric, nlevels, slot;
+  std::vector<BnlDeviceData> dev;       // one per context device
+  std::vector<double> h_mean, h_cov;    // host copies of the Gaussian moments
+};
+
+struct bnl_ctx {
+  std::vector<BnlDevice> devs;
+  std::map<bnl_data, BnlDataSet> data;
+  bnl_data next_handle = 1;
+  std::string err;
+  std::mutex err_mutex;
+  double last_ms = 0.0;
+  int last_launches = 0;
+};
+
+int bnl_fail(bnl_ctx *ctx, int code, const char *fmt, ...);
+
+#define BNL_CUDA(ctx, call)                                                      \
+  do {                                                                           \
+    cudaError_t e__ = (call);                                                    \
+    if (e__ != cudaSuccess)                                                      \
+      return bnl_fail((ctx), BNL_ECUDA, "%s failed: %s (%s:%d)", #call,          \
+                      cudaGetErrorString(e__), __FILE__, __LINE__);              \
+  } while (0)
+
+// grow-only device / pinned buffers.
+template <typename T>
+int bnl_reserve_device(bnl_ctx *ctx, T **p, size_t *cap, size_t need) {
+  if (need <= *cap) return BNL_OK;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *cap = 0;
+  size_t want = need + need / 4 + 64;
+  cudaError_t e = cudaMalloc((void **)p, want * sizeof(T));
+  if (e != cudaSuccess)
+    return bnl_fail(ctx, BNL_ENOMEM, "cudaMalloc of %zu bytes failed: %s", want * sizeof(T),
+                    cudaGetErrorString(e));
+  *cap = want;
+  return BNL_OK;
+}
+
+template <typename T>
+int bnl_reserve_pinned(bnl_ctx *ctx, T **p, size_t *cap, size_t need) {
+  if (need <= *cap) return BNL_OK;
+  if (*p) cudaFreeHost(*p);
+  *p = nullptr; *cap = 0;
+  size_t want = need + need / 4 + 64;
+  cudaError_t e = cudaMallocHost((void **)p, want * sizeof(T));
+  if (e != cudaSuccess)
+    return bnl_fail(ctx, BNL_ENOMEM, "cudaMallocHost of %zu bytes failed: %s", want * sizeof(T),
+                    cudaGetErrorString(e));
+  *cap = want;
+  return BNL_OK;
+}
+
+// defined in bnl_gaussian.cu: forms means and the covariance matrix on a device.
+int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int dev_index);
+
+// split [0, n) into ndev contiguous blocks.
+static inline void bnl_block(int n, int ndev, int d, int *begin, int *end) {
+  long long b = (long long)n * d / ndev, e = (long long)n * (d + 1) / ndev;
+  *begin = (int)b; *end = (int)e;
+}

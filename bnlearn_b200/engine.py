@@ -1,0 +1,216 @@
+"""Python face of the C ABI (include/bnl_b200.h): Engine = bnl_ctx, DataSet =
+bnl_data. Everything here goes through libbnl_b200.so; numpy only marshals the
+caller's host buffers.
+
+Column conventions are the reference's: factor columns are int32, 1-based, with
+NA = INT_MIN; numeric columns are float64.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "cor": 20, "zf": 21, "mi-g": 22}
+SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7,
+          "loglik-g": 100, "aic-g": 102, "bic-g": 103}
+DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf")
+GAUSSIAN_TESTS = ("cor", "zf", "mi-g")
+DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds")
+GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g")
+NA_INT = np.iinfo(np.int32).min
+
+
+class BnlError(RuntimeError):
+    def __init__(self, code, message):
+        RuntimeError.__init__(self, "bnl error %d: %s" % (code, message))
+        self.code = code
+
+
+def _ip(a):
+    return a.ctypes.data_as(_lib.c_int_p)
+
+
+def _dp(a):
+    return a.ctypes.data_as(_lib.c_dbl_p)
+
+
+def csr(lists):
+    """list of index lists -> (offsets int32[n+1], indices int32[total])."""
+    off = np.zeros(len(lists) + 1, dtype=np.int32)
+    if len(lists):
+        off[1:] = np.cumsum([len(l) for l in lists])
+    idx = np.fromiter((i for l in lists for i in l), dtype=np.int32, count=int(off[-1]))
+    if idx.size == 0:
+        idx = np.zeros(1, dtype=np.int32)
+    return off, idx
+
+
+def _as_csr(z):
+    if isinstance(z, tuple) and len(z) == 2 and isinstance(z[0], np.ndarray):
+        return (np.ascontiguousarray(z[0], dtype=np.int32),
+                np.ascontiguousarray(z[1], dtype=np.int32))
+    return csr(z)
+
+
+class Engine:
+    """One bnl_ctx. devices: list of CUDA ordinals (None = the current device)."""
+
+    def __init__(self, devices=None):
+        self._lib = _lib.load()
+        self._ctx = C.c_void_p()
+        if devices is None:
+            rc = self._lib.bnl_init(C.byref(self._ctx), None, 0)
+        else:
+            d = np.asarray(devices, dtype=np.int32)
+            rc = self._lib.bnl_init(C.byref(self._ctx), _ip(d), len(d))
+        if rc != 0:
+            msg = self._lib.bnl_last_error(self._ctx).decode() if self._ctx else "bnl_init failed"
+            if self._ctx:
+                self._lib.bnl_shutdown(self._ctx)
+                self._ctx = None
+            raise BnlError(rc, msg)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise BnlError(rc, self._lib.bnl_last_error(self._ctx).decode())
+
+    def register(self, columns, nlevels=None):
+        """Upload a data frame. nlevels[i] > 0 marks column i as a factor."""
+        n = len(columns)
+        nlevels = [0] * n if nlevels is None else [int(v) for v in nlevels]
+        cols = []
+        for i, c in enumerate(columns):
+            cols.append(np.ascontiguousarray(c, dtype=np.int32 if nlevels[i] > 0 else np.float64))
+        nobs = len(cols[0]) if n else 0
+        for c in cols:
+            if len(c) != nobs:
+                raise ValueError("columns differ in length")
+        ptrs = (C.c_void_p * n)(*[c.ctypes.data for c in cols])
+        isnum = np.array([0 if v > 0 else 1 for v in nlevels], dtype=np.int32)
+        lv = np.array(nlevels, dtype=np.int32)
+        handle = C.c_uint64()
+        self._check(self._lib.bnl_data_register(self._ctx, n, ptrs, _ip(isnum), _ip(lv), nobs,
+                                                C.byref(handle)))
+        return DataSet(self, handle.value, nobs, nlevels)
+
+    def flush(self):
+        self._check(self._lib.bnl_data_flush(self._ctx))
+
+    def last_call_stats(self):
+        """(device milliseconds, kernel launches) of the most recent compute call."""
+        ms, launches = C.c_double(), C.c_int()
+        self._check(self._lib.bnl_last_call_stats(self._ctx, C.byref(ms), C.byref(launches)))
+        return ms.value, launches.value
+
+    def close(self):
+        if self._ctx:
+            self._lib.bnl_shutdown(self._ctx)
+            self._ctx = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DataSet:
+    def __init__(self, engine, handle, nobs, nlevels):
+        self.engine, self.handle, self.nobs, self.nlevels = engine, handle, nobs, list(nlevels)
+        self.ncols = len(nlevels)
+
+    def release(self):
+        if self.handle:
+            e = self.engine
+            e._check(e._lib.bnl_data_release(e._ctx, self.handle))
+            self.handle = 0
+
+    # ---- discrete ---------------------------------------------------------
+    def counts(self, x, y, z):
+        """Raw tables; returns a list of (llz, llx, lly) int32 arrays. y[u] = -1: no y."""
+        e = self.engine
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        zo, zi = _as_csr(z)
+        shapes, off = [], np.zeros(len(x) + 1, dtype=np.int64)
+        for u in range(len(x)):
+            llz = 1
+            for j in zi[zo[u]:zo[u + 1]]:
+                llz *= self.nlevels[j]
+            shp = (llz, self.nlevels[x[u]], self.nlevels[y[u]] if y[u] >= 0 else 1)
+            shapes.append(shp)
+            off[u + 1] = off[u] + shp[0] * shp[1] * shp[2]
+        tab = np.zeros(max(int(off[-1]), 1), dtype=np.int32)
+        e._check(e._lib.bnl_counts(e._ctx, self.handle, len(x), _ip(x), _ip(y), _ip(zo), _ip(zi),
+                                   tab.ctypes.data_as(_lib.c_i32_p),
+                                   off.ctypes.data_as(_lib.c_i64_p)))
+        return [tab[off[u]:off[u + 1]].reshape(shapes[u]) for u in range(len(x))]
+
+    def ci_discrete(self, test, x, y, z):
+        """Batch of discrete CI tests -> (statistic, df, p.value) arrays."""
+        e = self.engine
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        zo, zi = _as_csr(z)
+        n = len(x)
+        st, df, pv = (np.zeros(max(n, 1)) for _ in range(3))
+        e._check(e._lib.bnl_ci_discrete(e._ctx, self.handle, TESTS[test], n, _ip(x), _ip(y), _ip(zo),
+                                        _ip(zi), _dp(st), _dp(df), _dp(pv)))
+        return st[:n], df[:n], pv[:n]
+
+    def score_discrete(self, score, target, parents, arg=0.0):
+        """Batch of node scores -> (score, nparams); arg = k (aic/bic) or iss (bde/bds)."""
+        e = self.engine
+        t = np.ascontiguousarray(target, dtype=np.int32)
+        po, pi = _as_csr(parents)
+        n = len(t)
+        sc, npar = np.zeros(max(n, 1)), np.zeros(max(n, 1))
+        e._check(e._lib.bnl_score_discrete(e._ctx, self.handle, SCORES[score], float(arg), n, _ip(t),
+                                           _ip(po), _ip(pi), _dp(sc), _dp(npar)))
+        return sc[:n], npar[:n]
+
+    # ---- Gaussian ---------------------------------------------------------
+    def ci_gaussian(self, test, x, y, z):
+        e = self.engine
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        zo, zi = _as_csr(z)
+        n = len(x)
+        st, df, pv = (np.zeros(max(n, 1)) for _ in range(3))
+        e._check(e._lib.bnl_ci_gaussian(e._ctx, self.handle, TESTS[test], n, _ip(x), _ip(y), _ip(zo),
+                                        _ip(zi), _dp(st), _dp(df), _dp(pv)))
+        return st[:n], df[:n], pv[:n]
+
+    def score_gaussian(self, score, target, parents, k=0.0):
+        e = self.engine
+        t = np.ascontiguousarray(target, dtype=np.int32)
+        po, pi = _as_csr(parents)
+        n = len(t)
+        sc, npar = np.zeros(max(n, 1)), np.zeros(max(n, 1))
+        e._check(e._lib.bnl_score_gaussian(e._ctx, self.handle, SCORES[score], float(k), n, _ip(t),
+                                           _ip(po), _ip(pi), _dp(sc), _dp(npar)))
+        return sc[:n], npar[:n]
+
+    def moments(self):
+        """(means, covariance matrix) of the numeric columns, registration order."""
+        e = self.engine
+        p = sum(1 for v in self.nlevels if v <= 0)
+        mean, cov = np.zeros(p), np.zeros((p, p), order="F")
+        e._check(e._lib.bnl_gaussian_moments(e._ctx, self.handle, _dp(mean), _dp(cov)))
+        return mean, cov
+
+    # ---- generic dispatch on the test / score label -------------------------
+    def ci_test(self, test, x, y, z):
+        return self.ci_discrete(test, x, y, z) if test in DISCRETE_TESTS else self.ci_gaussian(test, x, y, z)
+
+    def score(self, score, target, parents, arg=0.0):
+        if score in DISCRETE_SCORES:
+            return self.score_discrete(score, target, parents, arg)
+        return self.score_gaussian(score, target, parents, arg)

@@ -1,0 +1,153 @@
+/* bnl_b200.h -- C ABI of libbnl_b200.so, the B200 (sm_100a) engine for bnlearn's
+ * structure-learning statistics (count tables, discrete/Gaussian node scores,
+ * conditional-independence tests).
+ *
+ * The reference has no FFI for this path: it sits behind ordinary C functions
+ * called from the .Call entry points. Each entry point
+ * below names the reference function(s) whose per-candidate loop it replaces;
+ * INTEGRATION.md shows the patched call sites. Paths are relative to the
+ * reference's root (cran/bnlearn 5.2.1).
+ *
+ * Conventions
+ *   - every function returns 0 on success or a BNL_E* code; the message is
+ *     available from bnl_last_error(). Nothing longjmps or throws across the
+ *     boundary (the reference's error() does, src/core/allocations.c:13-15).
+ *   - all pointers are HOST pointers owned by the caller; outputs are
+ *     pre-allocated by the caller. Data columns are only read during
+ *     bnl_data_register(); afterwards the data set lives in device memory.
+ *   - columns are identified by their 0-based position in the registered data
+ *     set. Factor columns are int32, 1-based, NA = INT_MIN (R's encoding);
+ *     numeric columns are double.
+ *   - the ORDER of parents / conditioning variables is significant: it fixes
+ *     the configuration index exactly as c_fast_config() does
+ *     (src/core/sets.c:162-218: first variable varies fastest).
+ *   - enum values are the reference's: test_e (src/tests/tests.h:8-36) and
+ *     score_e (src/scores/scores.h:9-60).
+ *   - a bnl_ctx is used by one host thread at a time (R is single-threaded).
+ *   - there is no CPU fallback: without a CUDA device bnl_init() fails.
+ */
+#ifndef BNL_B200_H
+#define BNL_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bnl_ctx bnl_ctx;   /* opaque; one per process (or per R worker) */
+typedef uint64_t bnl_data;        /* handle to a device-resident, packed data set */
+
+enum {
+  BNL_OK = 0,
+  BNL_EINVAL = 1,       /* bad argument (index out of range, wrong column type, ...) */
+  BNL_ECUDA = 2,        /* CUDA runtime error */
+  BNL_ENOMEM = 3,       /* host or device allocation failed */
+  BNL_EOVERFLOW = 4,    /* configuration count >= INT_MAX (src/core/sets.c:182-183) */
+  BNL_EUNSUPPORTED = 5  /* valid in the reference, not handled by this engine yet */
+};
+
+/* test_e values handled (src/tests/tests.h:8-36). */
+enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4,
+       BNL_COR = 20, BNL_ZF = 21, BNL_MI_G = 22 };
+/* score_e values handled (src/scores/scores.h:9-60). */
+enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7,
+       BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103 };
+
+/* ---- context ---------------------------------------------------------- */
+
+/* Create a context on `ndev` CUDA devices (devices == NULL: the current device).
+ * With ndev > 1 registered data is replicated on every device and each call's
+ * units are split into contiguous blocks, one per device;
+ * results do not depend on ndev. Replaces nothing in the reference (it has no
+ * device); plays the role of R's parallel cluster set-up (R/utils-cluster.R:31-37). */
+int bnl_init(bnl_ctx **ctx, const int *devices, int ndev);
+void bnl_shutdown(bnl_ctx *ctx);
+const char *bnl_last_error(const bnl_ctx *ctx);
+
+/* Device time (ms, CUDA events on the engine's stream, max over devices) and
+ * number of kernel launches of the most recent compute call; for benchmarks. */
+int bnl_last_call_stats(const bnl_ctx *ctx, double *device_ms, int *kernel_launches);
+
+/* ---- data set ---------------------------------------------------------- */
+
+/* Upload and pack a data frame. col[i] points to nobs int32 (is_numeric[i] == 0,
+ * nlevels[i] levels) or nobs double (is_numeric[i] != 0). Factors are repacked
+ * to uint8 (code - 1, NA -> 0xFF); at most 127 levels per factor (more returns
+ * BNL_EUNSUPPORTED: the uint16 layout is not built yet).
+ * Replaces the per-call column extraction of tabular_from_SEXP()
+ * (src/core/data.table.c:143-225) and c_dataframe_column()
+ * (src/minimal/data.frame.c:41). */
+int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col,
+                      const int *is_numeric, const int *nlevels, int64_t nobs,
+                      bnl_data *handle);
+int bnl_data_release(bnl_ctx *ctx, bnl_data handle);
+/* Drop every registered data set; meant to be called from reset_test_counter()
+ * (src/test.counter.c:26), which every learner calls first. */
+int bnl_data_flush(bnl_ctx *ctx);
+
+/* ---- discrete: tables, scores, tests ----------------------------------- */
+
+/* Raw contingency tables for n units. Unit u counts x[u] (rows), y[u] (columns;
+ * -1 for none) within the configurations of z_idx[z_off[u] .. z_off[u+1]).
+ * tables + table_off[u] receives n[z][x][y] as ((z * llx) + x) * lly + y;
+ * table_off has n + 1 entries. Rows with an NA in any involved column are
+ * skipped. Replaces fill_1d/2d/3d_table (src/core/contingency.tables.c:20-34,
+ * 93-130, 198-223) after c_fast_config (src/core/sets.c:162-218). */
+int bnl_counts(bnl_ctx *ctx, bnl_data data, int n, const int *x, const int *y,
+               const int *z_off, const int *z_idx, int32_t *tables,
+               const int64_t *table_off);
+
+/* Node scores for n (target, parent set) units; parents of unit u are
+ * pa_idx[pa_off[u] .. pa_off[u+1]). k_or_iss is the penalty coefficient k for
+ * AIC/BIC and the imaginary sample size for BDe/BDs (uniform graph prior).
+ * nparams may be NULL. Replaces c_per_node_score() for these score_e values
+ * (src/scores/per.node.score.c:51-534 -> loglik_dnode,
+ * src/scores/discrete.loglikelihood.c:76-118; dirichlet_node,
+ * src/scores/dirichlet.posterior.c:152-202), i.e. the body of the candidate
+ * loop in score_cache_fill() (src/learning/score/hc.cache.lookup.c:54-117). */
+int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
+                       int n, const int *target, const int *pa_off,
+                       const int *pa_idx, double *score, double *nparams);
+
+/* Discrete CI tests x[u] _||_ y[u] | z (mi, mi-adf, x2, x2-adf): statistic (MI
+ * scaled to G^2), degrees of freedom and p-value = pchisq(stat, df, upper).
+ * Replaces c_chisqtest / c_cchisqtest (src/tests/discrete/discrete.tests.c:11-94),
+ * discrete_df / discrete_cdf (src/tests/discrete/df.adjust.c:4-90) and the
+ * pchisq call in ut_discrete, ct_discrete, ast_discrete, rrd_discrete
+ * (src/tests/patterns/utest.c:23, ctest.c:11, allsubs.test.c:52,
+ * roundrobin.test.c:32). */
+int bnl_ci_discrete(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x,
+                    const int *y, const int *z_off, const int *z_idx,
+                    double *stat, double *df, double *pvalue);
+
+/* ---- Gaussian ---------------------------------------------------------- */
+
+/* Gaussian CI tests (cor, zf, mi-g), served from the centred cross-product
+ * matrix that bnl_data_register() forms once per data set. stat is the
+ * (partial) correlation for cor and the transformed statistic for zf / mi-g, as
+ * in the reference's htest. Replaces ut/ct/ast/rrd_gaustests_complete
+ * (src/tests/patterns/utest.c:65, ctest.c:58, allsubs.test.c:150,
+ * roundrobin.test.c:106) over c_covmat (src/core/covariance.matrix.c:65-97) and
+ * c_fast_pcor (src/core/correlation.c:43-92). */
+int bnl_ci_gaussian(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x,
+                    const int *y, const int *z_off, const int *z_idx,
+                    double *stat, double *df, double *pvalue);
+
+/* Gaussian node scores (loglik-g, aic-g, bic-g) from the same matrix. Replaces
+ * loglik_gnode (src/scores/gaussian.loglikelihood.c:85-114) over c_ols
+ * (src/math/least.squares.c:866-932). */
+int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n,
+                       const int *target, const int *pa_off, const int *pa_idx,
+                       double *score, double *nparams);
+
+/* Copy the p x p covariance matrix (divisor nobs - 1, column-major, p = number
+ * of numeric columns in registration order) and the column means to the host.
+ * Replaces c_meanvec + c_covmat over all numeric columns. */
+int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, double *cov);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

@@ -1,0 +1,49 @@
+"""CPU tests of the product's host-side pieces: the C-ABI library loads and
+exports every symbol the header declares; the fp64 special functions (host
+build of the very code the kernels run) match mpmath fixtures."""
+import json
+import os
+import re
+
+import pytest
+
+from util import GOLDEN, rel_close
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from bnlearn_b200 import _lib
+    lib = _lib.load()
+    header = open(os.path.join(ROOT, "include", "bnl_b200.h")).read()
+    declared = set(re.findall(r"\b(bnl_[a-z_0-9]+)\s*\(", header))
+    assert declared, "no declarations found in the header"
+    for name in declared:
+        assert hasattr(lib, name), "libbnl_b200.so does not export %s" % name
+    assert declared == set(_lib.SIGNATURES), (declared ^ set(_lib.SIGNATURES))
+
+
+def test_no_cpu_fallback_without_a_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    from bnlearn_b200 import BnlError, Engine
+    with pytest.raises(BnlError):
+        Engine()
+
+
+def test_device_special_functions_host_build_against_mpmath():
+    from bnlearn_b200 import _lib
+    L = _lib.load_special_host()
+    with open(os.path.join(GOLDEN, "special_functions.json")) as f:
+        sf = json.load(f)
+    for x, v in sf["lgamma"]:
+        assert rel_close(L.bnl_host_lgamma(x), v, 1e-12, 1e-14), x
+    for x, df, v in sf["pchisq_upper"]:
+        assert rel_close(L.bnl_host_pchisq_upper(x, df), v, 1e-12), (x, df)
+    for t, df, v in sf["pt_upper2"]:
+        assert rel_close(L.bnl_host_pt_two_sided(t, df), v, 1e-12), (t, df)
+    for z, v in sf["pnorm_upper2"]:
+        assert rel_close(L.bnl_host_pnorm_two_sided(z), v, 1e-12), z
+    assert L.bnl_host_pchisq_upper(0.0, 0.0) == 1.0      # df = 0: point mass at zero
+    assert L.bnl_host_pchisq_upper(3.0, 0.0) == 0.0
