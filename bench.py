@@ -1,0 +1,311 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark: conditional-independence tests per second on
+BASELINE.json configs[1] (pc.stable() + mi on alarm-shaped discrete data,
+37 factors x 10M rows), one process per GPU.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA engine
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's own C on the host cores
+
+A step = one pass of the hot path over one batch: every CI test pc.stable issues
+on this data at levels 0-2 (see bnlearn_b200/workloads.py), with the data set
+resident in HBM (`value`) or registered from pinned host memory inside the step
+(`e2e`). Rank 0 prints ONE JSON line. Timing rules: W >= 3 warm-up steps, the
+data set (370 MB packed) is larger than the 126 MB L2 so no explicit flush is
+needed, steps are bracketed by barrier + synchronize, max over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from bnlearn_b200 import synth, workloads  # noqa: E402
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=10_000_000)
+    ap.add_argument("--cpu-sample", type=int, default=0, help="tests in the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------
+# workload
+
+def load_data(rows, seed=20261106):
+    """alarm-shaped data (config B), cached on local disk between invocations."""
+    cache = os.path.join("/tmp", "bnl_bench_cache")
+    os.makedirs(cache, exist_ok=True)
+    path = os.path.join(cache, "alarm_%d_%d.npy" % (rows, seed))
+    if os.path.exists(path):
+        codes = np.load(path)
+    else:
+        _, cols, _ = synth.alarm_shaped(rows, seed)
+        codes = np.stack(cols).astype(np.int8)
+        tmp = path + ".%d.tmp.npy" % os.getpid()
+        np.save(tmp, codes)
+        os.replace(tmp, path)
+    return list(synth.ALARM_NAMES), codes, list(synth.ALARM_LEVELS)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc, self.lines, self.index = None, [], index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); smax.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(smax) if smax else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------
+# CPU legs: the reference's own C (oracle/_ref), forked over all host cores.
+
+_CPU = {}
+
+
+def _cpu_worker(args):
+    lo, hi = args
+    cols, lev, units = _CPU["cols"], _CPU["lev"], _CPU["units"]
+    if _CPU["kind"] == "reference":
+        from oracle import refapi as ra, refbind as rb
+        L = rb.lib()
+        for (x, y, z) in units[lo:hi]:
+            if z:
+                cfg, llz = ra.fast_config([cols[j] for j in z], [lev[j] for j in z], 1)
+                st, df = ra.chisqtest(cols[x], lev[x], cols[y], lev[y], 1, cfg, llz)
+            else:
+                st, df = ra.chisqtest(cols[x], lev[x], cols[y], lev[y], 1)
+            L.Rf_pchisq(st, df, 0, 0)
+    else:
+        from oracle import oracle as orc
+        for (x, y, z) in units[lo:hi]:
+            orc.ci_discrete("mi", cols[x], lev[x], cols[y], lev[y], [cols[j] for j in z],
+                            [lev[j] for j in z])
+    return hi - lo
+
+
+def cpu_run(cols32, lev, units, cores):
+    """Time `units` through the CPU implementation on `cores` forked workers."""
+    import multiprocessing as mp
+    from oracle import refbind
+    _CPU.update(cols=cols32, lev=lev, units=units,
+                kind="reference" if refbind.available() else "port")
+    per = (len(units) + cores - 1) // cores
+    spans = [(i, min(i + per, len(units))) for i in range(0, len(units), per)]
+    ctx = mp.get_context("fork")
+    t0 = time.perf_counter()
+    with ctx.Pool(cores) as pool:
+        done = sum(pool.map(_cpu_worker, spans))
+    dt = time.perf_counter() - t0
+    return done / dt, dt, _CPU["kind"]
+
+
+# --------------------------------------------------------------------------
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference" and rank != 0:
+        return 0
+
+    names, codes, lev = load_data(args.rows)
+    units = workloads.pc_stable_units(names, lev, max_level=2)
+    n_units = len(units)
+    workload = ("pc.stable(test='mi') CI-test batch, levels 0-2 (%d tests), alarm-shaped synthetic "
+                "37 factors x %d rows, seed 20261106" % (n_units, args.rows))
+    base = {"metric": "ci_tests_per_sec", "unit": "tests/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload, "rows": args.rows, "columns": len(names),
+                       "tests_per_step_per_gpu": n_units,
+                       "l2": "packed data set 370 MB > 126 MB L2, no explicit flush",
+                       "sharding": "weak: every rank runs the full test list on its own replica"}}
+
+    cores = os.cpu_count() or 1
+
+    # ---------------- reference arm: the reference's C on the host cores -----
+    if args.impl == "reference":
+        cols32 = [np.ascontiguousarray(c.astype(np.int32)) for c in codes]
+        sample = args.cpu_sample or max(cores * 8, 64)
+        rng = np.random.default_rng(1)
+        pick = [units[i] for i in rng.choice(n_units, size=min(sample, n_units), replace=False)]
+        for _ in range(args.warmup):
+            cpu_run(cols32, lev, pick[:cores], cores)
+        t0 = time.perf_counter()
+        kind = "reference"
+        for _ in range(args.steps):
+            _, _, kind = cpu_run(cols32, lev, pick, cores)
+        dt = (time.perf_counter() - t0) / args.steps
+        val = len(pick) / dt
+        line = dict(base)
+        line.update({"impl": "reference", "value": val, "ms_per_step": dt * 1e3, "n_gpus": args.gpus,
+                     "cpu_baseline": {"value": val, "unit": "tests/s", "cores": cores, "kind": kind,
+                                      "sample": "%d of the %d tests of one step, per step" % (len(pick), n_units)},
+                     "e2e": {"value": val, "unit": "tests/s", "h2d_bytes_per_step": 0,
+                             "d2h_bytes_per_step": 0},
+                     "gpu_launches": 0})
+        print(json.dumps(line))
+        return 0
+
+    # ---------------- our arm ------------------------------------------------
+    import torch
+    import torch.distributed as dist
+    from bnlearn_b200 import Engine, csr
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # host copy of the data frame as the reference holds it (int32 factors), pinned.
+    ncol, rows = codes.shape
+    pinned = torch.empty((ncol, rows), dtype=torch.int32, pin_memory=True)
+    host = pinned.numpy()
+    np.copyto(host, codes, casting="unsafe")
+    cols32 = [host[i] for i in range(ncol)]
+
+    # weak scaling: rank r runs the same list rotated by r (same work, different order).
+    rot = (rank * 97) % n_units
+    my_units = units[rot:] + units[:rot]
+    xs = np.array([u[0] for u in my_units], dtype=np.int32)
+    ys = np.array([u[1] for u in my_units], dtype=np.int32)
+    z = csr([u[2] for u in my_units])
+    algo_bytes = float(args.rows) * float(sum(2 + len(u[2]) for u in my_units))
+
+    eng = Engine([local_rank])
+    ds = eng.register(cols32, lev)
+    for _ in range(max(args.warmup, 3)):
+        ds.ci_discrete("mi", xs, ys, z)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    count_ms, launches = [], 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ds.ci_discrete("mi", xs, ys, z)
+        prof = eng.last_call_profile()
+        count_ms.append(prof["count_ms"])
+        launches += prof["launches"]
+    barrier()
+    dt = (time.perf_counter() - t0) / args.steps
+    clocks = sampler.stop()
+    ds.release()
+
+    # end to end: host buffers in, p-values out, H2D + packing inside the step.
+    for _ in range(1):
+        d2 = eng.register(cols32, lev); d2.ci_discrete("mi", xs, ys, z); d2.release()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        d2 = eng.register(cols32, lev)
+        st, df, pv = d2.ci_discrete("mi", xs, ys, z)
+        d2.release()
+    barrier()
+    dt_e2e = (time.perf_counter() - t0) / args.steps
+
+    if world > 1:
+        t = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt, dt_e2e = float(t[0]), float(t[1])
+        lt = torch.tensor([launches], dtype=torch.int64, device="cuda")
+        dist.all_reduce(lt)
+        launches = int(lt[0])
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except (OSError, ValueError):
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        kms = float(np.mean(count_ms))
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("count_kernel_bytes_per_launch")
+        except (OSError, ValueError):
+            pass
+        line = dict(base)
+        line.update({
+            "value": world * n_units / dt, "ms_per_step": dt * 1e3, "clocks": clocks,
+            "e2e": {"value": world * n_units / dt_e2e, "unit": "tests/s",
+                    "h2d_bytes_per_step": int(ncol * rows * 4 + xs.nbytes + ys.nbytes + z[0].nbytes + z[1].nbytes),
+                    "d2h_bytes_per_step": int(3 * 8 * n_units)},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "kernel": "count kernel (one launch per step)",
+                         "achieved": algo_bytes / (kms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": algo_bytes / (kms * 1e-3) / 1e9 / peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                         "kernel_ms": kms, "algorithmic_bytes_per_launch": algo_bytes,
+                         "traffic": traffic},
+        })
+        if world == 1 and not args.no_cpu_baseline:
+            sample = args.cpu_sample or max(cores * 8, 64)
+            rng = np.random.default_rng(1)
+            pick = [units[i] for i in rng.choice(n_units, size=min(sample, n_units), replace=False)]
+            val, secs, kind = cpu_run(cols32, lev, pick, cores)
+            line["cpu_baseline"] = {"value": val, "unit": "tests/s", "cores": cores, "kind": kind,
+                                    "sample": "%d of the %d tests of one step (%.1f s)" % (len(pick), n_units, secs)}
+        print(json.dumps(line))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -21,7 +21,7 @@ SIGNATURES = {
     "bnl_init": (C.c_int, [C.POINTER(C.c_void_p), c_int_p, C.c_int]),
     "bnl_shutdown": (None, [C.c_void_p]),
     "bnl_last_error": (C.c_char_p, [C.c_void_p]),
-    "bnl_last_call_stats": (C.c_int, [C.c_void_p, c_dbl_p, c_int_p]),
+    "bnl_last_call_profile": (C.c_int, [C.c_void_p, c_dbl_p, c_dbl_p, c_dbl_p, c_int_p]),
     "bnl_data_register": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), c_int_p, c_int_p,
                                     C.c_int64, C.POINTER(C.c_uint64)]),
     "bnl_data_release": (C.c_int, [C.c_void_p, C.c_uint64]),

@@ -80,6 +80,9 @@ extern "C" int bnl_init(bnl_ctx **out, const int *devices, int ndev) {
     BNL_CUDA(ctx, cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
     BNL_CUDA(ctx, cudaEventCreate(&d.ev0));
     BNL_CUDA(ctx, cudaEventCreate(&d.ev1));
+    BNL_CUDA(ctx, cudaEventCreate(&d.evc0));
+    BNL_CUDA(ctx, cudaEventCreate(&d.evc1));
+    BNL_CUDA(ctx, cudaEventCreate(&d.eve1));
     BNL_CUDA(ctx, cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, id));
     BNL_CUDA(ctx, cudaDeviceGetAttribute(&d.max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, id));
     ctx->devs.push_back(d);
@@ -108,6 +111,9 @@ extern "C" void bnl_shutdown(bnl_ctx *ctx) {
     cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_gidx);
     if (d.ev0) cudaEventDestroy(d.ev0);
     if (d.ev1) cudaEventDestroy(d.ev1);
+    if (d.evc0) cudaEventDestroy(d.evc0);
+    if (d.evc1) cudaEventDestroy(d.evc1);
+    if (d.eve1) cudaEventDestroy(d.eve1);
     if (d.stream) cudaStreamDestroy(d.stream);
   }
   delete ctx;
@@ -117,9 +123,12 @@ extern "C" const char *bnl_last_error(const bnl_ctx *ctx) {
   return ctx ? ctx->err.c_str() : "null context";
 }
 
-extern "C" int bnl_last_call_stats(const bnl_ctx *ctx, double *device_ms, int *kernel_launches) {
+extern "C" int bnl_last_call_profile(const bnl_ctx *ctx, double *total_ms, double *count_ms,
+                                     double *epilogue_ms, int *kernel_launches) {
   if (!ctx) return BNL_EINVAL;
-  if (device_ms) *device_ms = ctx->last_ms;
+  if (total_ms) *total_ms = ctx->last_ms;
+  if (count_ms) *count_ms = ctx->last_count_ms;
+  if (epilogue_ms) *epilogue_ms = ctx->last_epi_ms;
   if (kernel_launches) *kernel_launches = ctx->last_launches;
   return BNL_OK;
 }

@@ -70,7 +70,7 @@ struct Request {
 // the scratch size. Everything is queued on the device's stream; the caller
 // synchronises. Sub-batches reuse the pinned staging buffers, so each one is
 // synchronised before the next is staged.
-int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, float *ms, int *launches) {
+int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, BnlTiming *tm) {
   BnlDevice &dev = ctx->devs[d];
   BnlDeviceData &dd = ds.dev[d];
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
@@ -115,12 +115,14 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, fl
     BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_units, dev.h_units, (size_t)cnt * sizeof(BnlUnit),
                                   cudaMemcpyHostToDevice, dev.stream));
     BNL_CUDA(ctx, cudaMemsetAsync(dev.d_tables, 0, (size_t)cells * sizeof(int), dev.stream));
+    BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
     if (groups > 0) {
       count_units_kernel<<<cnt * chunks, BNL_CNT_THREADS, (size_t)smem_cells * sizeof(int), dev.stream>>>(
           dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_tables, chunks, smem_cells);
       BNL_CUDA(ctx, cudaGetLastError());
-      (*launches)++;
+      tm->launches++;
     }
+    BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
     if (rq.kind == 2) {
       BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
       // tables straight back to the caller, unit by unit (offsets are the caller's).
@@ -133,7 +135,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, fl
       epilogue_kernel<<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
                                                                rq.kind, rq.code, rq.arg);
       BNL_CUDA(ctx, cudaGetLastError());
-      (*launches)++;
+      tm->launches++;
+      BNL_CUDA(ctx, cudaEventRecord(dev.eve1, dev.stream));
       BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)cnt * 4 * sizeof(double),
                                     cudaMemcpyDeviceToHost, dev.stream));
       BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
@@ -146,7 +149,13 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, fl
     }
     float t = 0.f;
     BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.ev0, dev.ev1));
-    *ms += t;
+    tm->total += t;
+    BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.evc0, dev.evc1));
+    tm->count += t;
+    if (rq.kind != 2) {
+      BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.evc1, dev.eve1));
+      tm->epi += t;
+    }
     pos += cnt;
   }
   return BNL_OK;
@@ -154,32 +163,32 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, fl
 
 int run_request(bnl_ctx *ctx, BnlDataSet &ds, Request &rq) {
   const int ndev = (int)ctx->devs.size();
-  ctx->last_ms = 0.0;
+  ctx->last_ms = ctx->last_count_ms = ctx->last_epi_ms = 0.0;
   ctx->last_launches = 0;
   if (rq.n == 0) return BNL_OK;
+  std::vector<int> rcs(ndev, BNL_OK);
+  std::vector<BnlTiming> tm(ndev);
   if (ndev == 1) {
-    float ms = 0.f; int launches = 0;
-    int rc = run_block(ctx, ds, 0, rq, 0, rq.n, &ms, &launches);
-    ctx->last_ms = ms; ctx->last_launches = launches;
-    return rc;
+    rcs[0] = run_block(ctx, ds, 0, rq, 0, rq.n, &tm[0]);
+  } else {
+    // several devices: contiguous blocks of units, one host thread per device so
+    // that the blocks overlap (each thread only touches its own device's state;
+    // bnl_fail() serialises writes to the error string).
+    std::vector<std::thread> workers;
+    for (int d = 0; d < ndev; d++) {
+      int b, e;
+      bnl_block(rq.n, ndev, d, &b, &e);
+      if (b >= e) continue;
+      workers.emplace_back([&, d, b, e]() { rcs[d] = run_block(ctx, ds, d, rq, b, e, &tm[d]); });
+    }
+    for (auto &w : workers) w.join();
+    cudaSetDevice(ctx->devs[0].id);
   }
-  // several devices: contiguous blocks of units, one host thread per device so
-  // that the blocks overlap (each thread only touches its own device's state;
-  // bnl_fail() serialises writes to the error string).
-  std::vector<int> rcs(ndev, BNL_OK), launches(ndev, 0);
-  std::vector<float> ms(ndev, 0.f);
-  std::vector<std::thread> workers;
   for (int d = 0; d < ndev; d++) {
-    int b, e;
-    bnl_block(rq.n, ndev, d, &b, &e);
-    if (b >= e) continue;
-    workers.emplace_back([&, d, b, e]() { rcs[d] = run_block(ctx, ds, d, rq, b, e, &ms[d], &launches[d]); });
-  }
-  for (auto &w : workers) w.join();
-  cudaSetDevice(ctx->devs[0].id);
-  for (int d = 0; d < ndev; d++) {
-    ctx->last_ms = std::max(ctx->last_ms, (double)ms[d]);
-    ctx->last_launches += launches[d];
+    ctx->last_ms = std::max(ctx->last_ms, (double)tm[d].total);
+    ctx->last_count_ms = std::max(ctx->last_count_ms, (double)tm[d].count);
+    ctx->last_epi_ms = std::max(ctx->last_epi_ms, (double)tm[d].epi);
+    ctx->last_launches += tm[d].launches;
   }
   for (int d = 0; d < ndev; d++)
     if (rcs[d] != BNL_OK) return rcs[d];

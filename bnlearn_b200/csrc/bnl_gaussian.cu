@@ -63,7 +63,7 @@ struct GRequest {
   double *o0, *o1, *o2;
 };
 
-int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, float *ms, int *launches) {
+int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, BnlTiming *tm) {
   BnlDevice &dev = ctx->devs[d];
   BnlDeviceData &dd = ds.dev[d];
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
@@ -96,6 +96,7 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
   BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_gidx, dev.h_gidx, (size_t)cnt * BNL_GW * sizeof(int),
                                 cudaMemcpyHostToDevice, dev.stream));
   const int grid = (cnt + tpb - 1) / tpb;
+  BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
   if (rq.kind == 0)
     gauss_ci_kernel<<<grid, tpb, smem, dev.stream>>>(dev.d_gidx, cnt, dd.cov, ds.nc, ds.nobs, rq.code,
                                                      rq.kmax, dev.d_out);
@@ -103,7 +104,8 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
     gauss_score_kernel<<<grid, tpb, smem, dev.stream>>>(dev.d_gidx, cnt, dd.cov, dd.mean, ds.nc, ds.nobs,
                                                         rq.code, rq.arg, rq.kmax, dev.d_out);
   BNL_CUDA(ctx, cudaGetLastError());
-  (*launches)++;
+  tm->launches++;
+  BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
   BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)cnt * 4 * sizeof(double),
                                 cudaMemcpyDeviceToHost, dev.stream));
   BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
@@ -113,33 +115,35 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
     if (rq.o1) rq.o1[b + i] = dev.h_out[4 * i + 1];
     if (rq.o2) rq.o2[b + i] = dev.h_out[4 * i + 2];
   }
-  BNL_CUDA(ctx, cudaEventElapsedTime(ms, dev.ev0, dev.ev1));
+  BNL_CUDA(ctx, cudaEventElapsedTime(&tm->total, dev.ev0, dev.ev1));
+  BNL_CUDA(ctx, cudaEventElapsedTime(&tm->count, dev.evc0, dev.evc1));
   return BNL_OK;
 }
 
 int run_grequest(bnl_ctx *ctx, BnlDataSet &ds, GRequest &rq) {
   const int ndev = (int)ctx->devs.size();
-  ctx->last_ms = 0.0;
+  ctx->last_ms = ctx->last_count_ms = ctx->last_epi_ms = 0.0;
   ctx->last_launches = 0;
   if (rq.n == 0) return BNL_OK;
-  std::vector<int> rcs(ndev, BNL_OK), launches(ndev, 0);
-  std::vector<float> ms(ndev, 0.f);
+  std::vector<int> rcs(ndev, BNL_OK);
+  std::vector<BnlTiming> tm(ndev);
   if (ndev == 1) {
-    rcs[0] = run_gblock(ctx, ds, 0, rq, 0, rq.n, &ms[0], &launches[0]);
+    rcs[0] = run_gblock(ctx, ds, 0, rq, 0, rq.n, &tm[0]);
   } else {
     std::vector<std::thread> workers;
     for (int d = 0; d < ndev; d++) {
       int b, e;
       bnl_block(rq.n, ndev, d, &b, &e);
       if (b >= e) continue;
-      workers.emplace_back([&, d, b, e]() { rcs[d] = run_gblock(ctx, ds, d, rq, b, e, &ms[d], &launches[d]); });
+      workers.emplace_back([&, d, b, e]() { rcs[d] = run_gblock(ctx, ds, d, rq, b, e, &tm[d]); });
     }
     for (auto &w : workers) w.join();
     cudaSetDevice(ctx->devs[0].id);
   }
   for (int d = 0; d < ndev; d++) {
-    ctx->last_ms = std::max(ctx->last_ms, (double)ms[d]);
-    ctx->last_launches += launches[d];
+    ctx->last_ms = std::max(ctx->last_ms, (double)tm[d].total);
+    ctx->last_count_ms = std::max(ctx->last_count_ms, (double)tm[d].count);
+    ctx->last_launches += tm[d].launches;
   }
   for (int d = 0; d < ndev; d++)
     if (rcs[d] != BNL_OK) return rcs[d];

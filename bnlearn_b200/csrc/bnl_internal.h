@@ -30,7 +30,8 @@ struct BnlUnit {
 struct BnlDevice {
   int id = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;       // whole call
+  cudaEvent_t evc0 = nullptr, evc1 = nullptr, eve1 = nullptr;   // count kernel, epilogue
   // grow-only scratch
   BnlUnit *d_units = nullptr; size_t units_cap = 0;
   int *d_tables = nullptr; size_t tables_cap = 0;        // int32 elements
@@ -69,7 +70,7 @@ struct bnl_ctx {
   bnl_data next_handle = 1;
   std::string err;
   std::mutex err_mutex;
-  double last_ms = 0.0;
+  double last_ms = 0.0, last_count_ms = 0.0, last_epi_ms = 0.0;
   int last_launches = 0;
 };
 
@@ -114,6 +115,9 @@ int bnl_reserve_pinned(bnl_ctx *ctx, T **p, size_t *cap, size_t need) {
 
 // defined in bnl_gaussian.cu: forms means and the covariance matrix on a device.
 int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int dev_index);
+
+// per-call timing of one device block.
+struct BnlTiming { float total = 0.f, count = 0.f, epi = 0.f; int launches = 0; };
 
 // split [0, n) into ndev contiguous blocks.
 static inline void bnl_block(int n, int ndev, int d, int *begin, int *end) {

@@ -97,11 +97,13 @@ class Engine:
     def flush(self):
         self._check(self._lib.bnl_data_flush(self._ctx))
 
-    def last_call_stats(self):
-        """(device milliseconds, kernel launches) of the most recent compute call."""
-        ms, launches = C.c_double(), C.c_int()
-        self._check(self._lib.bnl_last_call_stats(self._ctx, C.byref(ms), C.byref(launches)))
-        return ms.value, launches.value
+    def last_call_profile(self):
+        """Device-side timing of the most recent compute call:
+        dict(total_ms, count_ms, epilogue_ms, launches)."""
+        t, c, e, n = C.c_double(), C.c_double(), C.c_double(), C.c_int()
+        self._check(self._lib.bnl_last_call_profile(self._ctx, C.byref(t), C.byref(c), C.byref(e),
+                                                    C.byref(n)))
+        return {"total_ms": t.value, "count_ms": c.value, "epilogue_ms": e.value, "launches": n.value}
 
     def close(self):
         if self._ctx:

@@ -65,9 +65,14 @@ int bnl_init(bnl_ctx **ctx, const int *devices, int ndev);
 void bnl_shutdown(bnl_ctx *ctx);
 const char *bnl_last_error(const bnl_ctx *ctx);
 
-/* Device time (ms, CUDA events on the engine's stream, max over devices) and
- * number of kernel launches of the most recent compute call; for benchmarks. */
-int bnl_last_call_stats(const bnl_ctx *ctx, double *device_ms, int *kernel_launches);
+/* Device-side timing of the most recent compute call, from CUDA events recorded
+ * on the engine's own stream (max over devices): total_ms spans descriptor
+ * upload .. result download; count_ms is the counting (or Gaussian solve)
+ * kernel alone, epilogue_ms the statistic kernel alone; kernel_launches counts
+ * this library's kernel launches in the call. Any pointer may be NULL. For
+ * benchmarks; no counterpart in the reference. */
+int bnl_last_call_profile(const bnl_ctx *ctx, double *total_ms, double *count_ms,
+                          double *epilogue_ms, int *kernel_launches);
 
 /* ---- data set ---------------------------------------------------------- */
 
