@@ -1,0 +1,364 @@
+// bnl_callsites.cu -- host-side drop-in bodies for the reference's call sites
+// (include/bnl_b200.h, "call sites"). They turn one reference call into batched
+// units for the kernels and then replay, on the host and in the reference's
+// order, the logic that consumes the numbers: early exit, min/max p-values,
+// separating sets, robust score differences and the test counter.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "bnl_internal.h"
+#include "bnl_special.cuh"
+
+namespace {
+
+bool is_discrete_test(int t) { return t == BNL_MI || t == BNL_MI_ADF || t == BNL_X2 || t == BNL_X2_ADF; }
+bool is_gaussian_test(int t) { return t == BNL_COR || t == BNL_ZF || t == BNL_MI_G; }
+bool is_discrete_score(int s) { return s == BNL_LOGLIK || s == BNL_AIC || s == BNL_BIC || s == BNL_BDE || s == BNL_BDS; }
+
+// one batch of CI tests through the matching kernel path.
+int run_tests(bnl_ctx *ctx, bnl_data data, int test_e, const std::vector<int> &x,
+              const std::vector<int> &y, const std::vector<int> &zoff, const std::vector<int> &zidx,
+              std::vector<double> &st, std::vector<double> &df, std::vector<double> &pv) {
+  const int n = (int)x.size();
+  st.assign(n, 0.0); df.assign(n, 0.0); pv.assign(n, 0.0);
+  if (n == 0) return BNL_OK;
+  const int *zi = zidx.empty() ? nullptr : zidx.data();
+  if (is_discrete_test(test_e))
+    return bnl_ci_discrete(ctx, data, test_e, n, x.data(), y.data(), zoff.data(), zi, st.data(),
+                           df.data(), pv.data());
+  if (is_gaussian_test(test_e))
+    return bnl_ci_gaussian(ctx, data, test_e, n, x.data(), y.data(), zoff.data(), zi, st.data(),
+                           df.data(), pv.data());
+  return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
+}
+
+// lexicographic subsets of {0..m-1} of size k (src/core/sets.c:9-55).
+bool next_subset(std::vector<int> &w, int m) {
+  const int k = (int)w.size();
+  int i = k - 1;
+  while (i >= 0 && w[i] == m - k + i) i--;
+  if (i < 0) return false;
+  w[i]++;
+  for (int j = i + 1; j < k; j++) w[j] = w[j - 1] + 1;
+  return true;
+}
+
+}  // namespace
+
+extern "C" int bnl_indep_test(bnl_ctx *ctx, bnl_data data, int test_e, int nx, const int *x, int y,
+                              const int *sx, int nsx, double *pvalue, double *stat, double *df,
+                              double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (nx < 0 || nsx < 0 || (nx > 0 && (!x || !pvalue)) || (nsx > 0 && !sx))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_indep_test: bad arguments");
+  std::vector<int> xs(x, x + nx), ys(nx, y), zoff(nx + 1), zidx;
+  for (int i = 0; i < nx; i++) {
+    zoff[i] = (int)zidx.size();
+    zidx.insert(zidx.end(), sx, sx + nsx);
+  }
+  zoff[nx] = (int)zidx.size();
+  std::vector<double> st, d, pv;
+  int rc = run_tests(ctx, data, test_e, xs, ys, zoff, zidx, st, d, pv);
+  if (rc) return rc;
+  for (int i = 0; i < nx; i++) pvalue[i] = pv[i];
+  if (nx > 0) { if (stat) *stat = st[nx - 1]; if (df) *df = d[nx - 1]; }
+  if (test_counter) *test_counter += nx;       // utest.c:95, ctest.c:134
+  return BNL_OK;
+}
+
+namespace {
+
+// state of one allsubs request while its subsets are being evaluated in rounds.
+struct AstReq {
+  int x, y, nf, m;                  // m = number of non-fixed candidates
+  const int *sx;                    // fixed first, then candidates
+  double p = 0.0, pmin = 1.0, pmax = 0.0;
+  bool done = false;
+  bool stage1 = false;              // finished by the test with no moving parts
+  int ndsep = -1;
+  std::vector<int> dsep;
+  int cursize = 0;
+  std::vector<int> subset;          // next subset to evaluate (positions in the candidates)
+  bool exhausted_size = true;       // need to move to the next size
+  double counter = 0.0;
+};
+
+void range(AstReq &r, double p) { r.pmin = std::min(r.pmin, p); r.pmax = std::max(r.pmax, p); }
+
+}  // namespace
+
+extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x,
+                                const int *y, const int *sx_off, const int *sx, const int *nfixed,
+                                int minsize, int maxsize, double alpha, double *out,
+                                const int *dsep_off, int *dsep, int *ndsep, double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (n < 0 || (n > 0 && (!x || !y || !sx_off || !out || !ndsep || !dsep_off)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_allsubs_test: bad arguments");
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  const long long nobs = it->second.nobs;
+  const bool gauss = is_gaussian_test(test_e);
+  if (!gauss && !is_discrete_test(test_e))
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
+
+  std::vector<AstReq> rq(n);
+  for (int r = 0; r < n; r++) {
+    rq[r].x = x[r]; rq[r].y = y[r];
+    rq[r].nf = nfixed ? nfixed[r] : 0;
+    rq[r].sx = sx + sx_off[r];
+    rq[r].m = sx_off[r + 1] - sx_off[r] - rq[r].nf;
+    if (rq[r].m < 0 || rq[r].nf < 0)
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_allsubs_test: request %d has more fixed than total variables", r);
+  }
+  std::vector<int> bx, by, boff, bidx, owner;
+  std::vector<double> st, df, pv;
+
+  // (1) minsize == 0: the test with no moving parts goes through indep_test()
+  // (rinterface/allsubs.test.c:23-64) and is counted twice.
+  if (minsize == 0) {
+    boff.assign(1, 0);
+    for (int r = 0; r < n; r++) {
+      bx.push_back(rq[r].x); by.push_back(rq[r].y);
+      bidx.insert(bidx.end(), rq[r].sx, rq[r].sx + rq[r].nf);
+      boff.push_back((int)bidx.size());
+    }
+    int rc = run_tests(ctx, data, test_e, bx, by, boff, bidx, st, df, pv);
+    if (rc) return rc;
+    for (int r = 0; r < n; r++) {
+      AstReq &q = rq[r];
+      q.p = pv[r];
+      range(q, q.p);
+      q.counter += 2.0;
+      if (q.p > alpha) {
+        q.done = q.stage1 = true;
+        q.ndsep = q.nf;
+        q.dsep.assign(q.sx, q.sx + q.nf);
+      } else if (std::min(maxsize, q.m) <= 0) {
+        q.done = q.stage1 = true;
+      }
+    }
+  }
+  // marginal-stage ranges are merged at the end (rinterface/allsubs.test.c:195-200);
+  // keep them apart from the subset-stage ranges, which restart from (1, 0).
+  std::vector<double> m_min(n, 1.0), m_max(n, 0.0), m_p(n, 0.0);
+  for (int r = 0; r < n; r++) {
+    m_min[r] = rq[r].pmin; m_max[r] = rq[r].pmax; m_p[r] = rq[r].p;
+    if (!rq[r].done) { rq[r].pmin = 1.0; rq[r].pmax = 0.0; rq[r].p = 0.0; }
+    rq[r].cursize = std::max(1, minsize) - 1;
+  }
+
+  // (2) subsets, size by size, in rounds: every live request contributes its
+  // next run of subsets (bounded), the batch is evaluated, and each request
+  // replays its results in order until its first p-value > alpha.
+  const int kPerReqCap = n > 64 ? 64 : 4096;
+  for (;;) {
+    bx.clear(); by.clear(); bidx.clear(); owner.clear();
+    boff.assign(1, 0);
+    std::vector<std::vector<int>> planned(n);   // flattened subsets per request, this round
+    bool any = false;
+    for (int r = 0; r < n; r++) {
+      AstReq &q = rq[r];
+      if (q.done) continue;
+      if (q.exhausted_size) {
+        q.cursize++;
+        const int mx = std::min(maxsize, q.m);
+        if (q.cursize > mx) { q.done = true; continue; }
+        if (gauss) {
+          // not enough degrees of freedom: independence, with the first
+          // cursize + nf variables as separating set (patterns/allsubs.test.c:169-194).
+          const int nz = q.cursize + q.nf;
+          const double d = test_e == BNL_COR ? (double)(nobs - nz - 2)
+                         : test_e == BNL_ZF ? (double)(nobs - nz - 3) : 1.0;
+          if (d < 1.0) {
+            q.p = q.pmin = q.pmax = 1.0;
+            q.done = true;
+            q.ndsep = nz;
+            q.dsep.assign(q.sx, q.sx + nz);
+            continue;
+          }
+        }
+        q.subset.resize(q.cursize);
+        for (int i = 0; i < q.cursize; i++) q.subset[i] = i;
+        q.exhausted_size = false;
+      }
+      int planned_n = 0;
+      std::vector<int> w = q.subset;
+      do {
+        bx.push_back(q.x); by.push_back(q.y); owner.push_back(r);
+        bidx.insert(bidx.end(), q.sx, q.sx + q.nf);
+        for (int i : w) bidx.push_back(q.sx[q.nf + i]);
+        boff.push_back((int)bidx.size());
+        planned[r].insert(planned[r].end(), w.begin(), w.end());
+        planned_n++;
+        if (!next_subset(w, q.m)) { q.exhausted_size = true; break; }
+      } while (planned_n < kPerReqCap);
+      if (!q.exhausted_size) q.subset = w;
+      any = true;
+    }
+    if (!any) break;
+    int rc = run_tests(ctx, data, test_e, bx, by, boff, bidx, st, df, pv);
+    if (rc) return rc;
+    // replay in order.
+    size_t u = 0;
+    while (u < owner.size()) {
+      const int r = owner[u];
+      AstReq &q = rq[r];
+      size_t e = u;
+      while (e < owner.size() && owner[e] == r) e++;
+      for (size_t t = u; t < e; t++) {
+        q.p = pv[t];
+        range(q, q.p);
+        q.counter += 1.0;                        // patterns/allsubs.test.c:110, 249
+        if (q.p > alpha) {
+          q.done = true;
+          q.ndsep = q.nf + q.cursize;
+          q.dsep.assign(q.sx, q.sx + q.nf);
+          const int *w = planned[r].data() + (t - u) * q.cursize;
+          for (int i = 0; i < q.cursize; i++) q.dsep.push_back(q.sx[q.nf + w[i]]);
+          break;
+        }
+      }
+      u = e;
+    }
+  }
+
+  double total = 0.0;
+  for (int r = 0; r < n; r++) {
+    AstReq &q = rq[r];
+    double p = q.p, pmin = q.pmin, pmax = q.pmax;
+    if (minsize == 0 && !q.stage1) { pmin = std::min(pmin, m_min[r]); pmax = std::max(pmax, m_max[r]); }
+    out[3 * r + 0] = p; out[3 * r + 1] = pmin; out[3 * r + 2] = pmax;
+    ndsep[r] = q.ndsep;
+    if (q.ndsep > 0) {
+      if (!dsep || dsep_off[r + 1] - dsep_off[r] < q.ndsep)
+        return bnl_fail(ctx, BNL_EINVAL, "bnl_allsubs_test: dsep buffer too small for request %d", r);
+      memcpy(dsep + dsep_off[r], q.dsep.data(), (size_t)q.ndsep * sizeof(int));
+    }
+    total += q.counter;
+  }
+  if (test_counter) *test_counter += total;
+  return BNL_OK;
+}
+
+extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int x, const int *z,
+                                   int nz, const int *is_fixed, double alpha, double *pvalue,
+                                   double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (nz < 0 || (nz > 0 && (!z || !pvalue)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_roundrobin_test: bad arguments");
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  const long long nobs = it->second.nobs;
+  const bool gauss = is_gaussian_test(test_e);
+  if (!gauss && !is_discrete_test(test_e))
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
+
+  int nfixed = 0;
+  for (int i = 0; i < nz; i++) nfixed += is_fixed && is_fixed[i];
+  for (int i = 0; i < nz - nfixed; i++) pvalue[i] = 0.0;   // rinterface/roundrobin.test.c:29
+  std::vector<char> dropped(nz, 0);
+  std::vector<int> xs(1), ys(1), zoff(2), zidx;
+  std::vector<double> st, df, pv;
+  int valid = nz, cur = 0;
+
+  // sequentially dependent: each step's conditioning set depends on the
+  // verdicts before it (patterns/roundrobin.test.c:92-96, 199-206).
+  for (int i = 0; i < nz; i++) {
+    if (valid < 2) break;
+    if (is_fixed && is_fixed[i]) continue;
+    zidx.clear();
+    for (int j = 0; j < nz; j++)
+      if (j != i && !dropped[j]) zidx.push_back(z[j]);
+    if (gauss) {
+      const int ncond = (int)zidx.size();
+      const double d = test_e == BNL_COR ? (double)(nobs - ncond - 2)
+                     : test_e == BNL_ZF ? (double)(nobs - ncond - 3) : 1.0;
+      if (d < 1.0) { pvalue[cur++] = 1.0; continue; }   // no drop (roundrobin.test.c:144-154)
+    }
+    xs[0] = x; ys[0] = z[i];
+    zoff[0] = 0; zoff[1] = (int)zidx.size();
+    int rc = run_tests(ctx, data, test_e, xs, ys, zoff, zidx, st, df, pv);
+    if (rc) return rc;
+    pvalue[cur] = pv[0];
+    if (pvalue[cur++] > alpha) { valid--; dropped[i] = 1; }
+  }
+  if (test_counter) *test_counter += nz - nfixed;        // rinterface/roundrobin.test.c:150
+  return BNL_OK;
+}
+
+extern "C" int bnl_score_cache_fill(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
+                                    int nnodes, const int *amat, const int *blmat,
+                                    const int *updated, int nupdated, int equivalence,
+                                    const double *reference, double *cache,
+                                    double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (nnodes <= 0 || !amat || !reference || !cache || nupdated < 0 || (nupdated > 0 && !updated))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_score_cache_fill: bad arguments");
+  if (nupdated == 0) return BNL_OK;
+  const size_t n = (size_t)nnodes;
+  auto A = [&](int i, int j) { return amat[(size_t)i + (size_t)j * n]; };
+  auto B = [&](int i, int j) { return blmat ? blmat[(size_t)i + (size_t)j * n] : 0; };
+
+  std::vector<char> upd(nnodes, 0);
+  for (int k = 0; k < nupdated; k++) {
+    if (updated[k] < 0 || updated[k] >= nnodes)
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_score_cache_fill: updated node %d out of range", updated[k]);
+    upd[updated[k]] = 1;
+  }
+  std::vector<int> colsum(nnodes, 0);
+  if (equivalence)
+    for (int j = 0; j < nnodes; j++)
+      for (int i = 0; i < nnodes; i++) colsum[j] += A(i, j);
+
+  // the candidates that are really scored, in the reference's (i outer, j inner)
+  // order; equivalence copies are applied afterwards, in the same order.
+  std::vector<int> target, pa_off(1, 0), pa_idx, ci, cj;
+  std::vector<std::pair<int, int>> copies;
+  std::vector<std::vector<int>> parents(nnodes);
+  for (int j = 0; j < nnodes; j++)
+    if (upd[j])
+      for (int i = 0; i < nnodes; i++)
+        if (A(i, j)) parents[j].push_back(i);
+  for (int i = 0; i < nnodes; i++)
+    for (int j = 0; j < nnodes; j++) {
+      if (i == j || !upd[j]) continue;
+      if (B(i, j) == 1) continue;
+      if (equivalence && i > j && colsum[i] + colsum[j] == 0 && B(j, i) == 0) {
+        copies.push_back(std::make_pair(i, j));
+        continue;
+      }
+      target.push_back(j);
+      if (A(i, j) == 0) {          // "set": old parents, then the new one last
+        pa_idx.insert(pa_idx.end(), parents[j].begin(), parents[j].end());
+        pa_idx.push_back(i);
+      } else {                     // "drop"
+        for (int p : parents[j]) if (p != i) pa_idx.push_back(p);
+      }
+      pa_off.push_back((int)pa_idx.size());
+      ci.push_back(i); cj.push_back(j);
+    }
+  const int m = (int)target.size();
+  std::vector<double> score(std::max(m, 1));
+  if (m > 0) {
+    const int *pi = pa_idx.empty() ? nullptr : pa_idx.data();
+    int rc = is_discrete_score(score_e)
+      ? bnl_score_discrete(ctx, data, score_e, k_or_iss, m, target.data(), pa_off.data(), pi, score.data(), nullptr)
+      : bnl_score_gaussian(ctx, data, score_e, k_or_iss, m, target.data(), pa_off.data(), pi, score.data(), nullptr);
+    if (rc) return rc;
+  }
+  const double tol = bnl::kSqrtEps;
+  for (int u = 0; u < m; u++) {
+    // robust_score_difference(): tiny differences are zero; -Inf - -Inf is -Inf.
+    const double old_s = reference[cj[u]], new_s = score[u];
+    double delta = fabs(new_s - old_s) < tol ? 0.0 : new_s - old_s;
+    if (old_s == -INFINITY) delta = (new_s != -INFINITY) ? new_s : -INFINITY;
+    cache[(size_t)ci[u] + (size_t)cj[u] * n] = delta;
+  }
+  for (auto &c : copies)
+    cache[(size_t)c.first + (size_t)c.second * n] = cache[(size_t)c.second + (size_t)c.first * n];
+  if (test_counter) *test_counter += m;                 // score.delta.c:278
+  return BNL_OK;
+}

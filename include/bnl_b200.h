@@ -151,6 +151,62 @@ int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n
  * Replaces c_meanvec + c_covmat over all numeric columns. */
 int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, double *cov);
 
+/* ---- call sites: drop-in bodies for the reference's per-call loops ----------
+ * These keep the reference's semantics that consume the numbers: evaluation
+ * order, early exit, min/max p-value tracking, and the exact test-counter
+ * arithmetic ("metrics" row). `test_counter` points to the
+ * caller's counter (the reference's global `double test_counter`,
+ * src/test.counter.c:4) and is incremented exactly as the reference would. */
+
+/* indep_test(..., learning = TRUE) (src/tests/rinterface/indep.test.c:5-19 ->
+ * utest.c:9-102 / ctest.c:10-141): nx variables x[] each tested against y given
+ * sx[0..nsx); pvalue[nx]. stat/df (may be NULL) receive the LAST test's values,
+ * as the htest path does. test_counter += nx. */
+int bnl_indep_test(bnl_ctx *ctx, bnl_data data, int test_e, int nx, const int *x, int y,
+                   const int *sx, int nsx, double *pvalue, double *stat, double *df,
+                   double *test_counter);
+
+/* allsubs_test (src/tests/rinterface/allsubs.test.c:10-210 over ast_discrete /
+ * ast_gaustests_complete, src/tests/patterns/allsubs.test.c:52-287) for n
+ * independent requests at once (n = 1 is the reference's call). Request r tests
+ * x[r] vs y[r] given every subset, of sizes minsize..maxsize, of the non-fixed
+ * part of sx[sx_off[r] .. sx_off[r+1]) (the first nfixed[r] entries are fixed
+ * and always conditioned on), in lexicographic order, stopping at the first
+ * p-value > alpha. out[3r..3r+2] = p.value, min.p.value, max.p.value;
+ * dsep[dsep_off[r]..] receives the separating set (column indices) and ndsep[r]
+ * its size, or -1 when none was found (dsep_off[r+1] - dsep_off[r] must be >=
+ * sx_off[r+1] - sx_off[r]). test_counter is advanced by exactly the number of
+ * tests the serial code would have run (the marginal test counts twice,
+ * rinterface/allsubs.test.c:23-30). */
+int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x, const int *y,
+                     const int *sx_off, const int *sx, const int *nfixed, int minsize,
+                     int maxsize, double alpha, double *out, const int *dsep_off, int *dsep,
+                     int *ndsep, double *test_counter);
+
+/* roundrobin_test (src/tests/rinterface/roundrobin.test.c:10-154 over rrd_discrete
+ * / rrd_gaustests_complete, src/tests/patterns/roundrobin.test.c:32-219): x vs
+ * each non-fixed z[i] given the other not-yet-dropped z; a variable found
+ * independent (p > alpha) is dropped from the later conditioning sets.
+ * is_fixed[nz] flags fixed variables; pvalue has nz - #fixed entries, zero for
+ * tests never run. test_counter += nz - #fixed. */
+int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int x, const int *z, int nz,
+                        const int *is_fixed, double alpha, double *pvalue,
+                        double *test_counter);
+
+/* score_cache_fill (src/learning/score/hc.cache.lookup.c:10-128): the score delta
+ * of adding (amat[i,j] == 0) or dropping (amat[i,j] == 1) arc i -> j for every
+ * j in updated[], i != j, not blacklisted, with the score-equivalence copy rule
+ * (:84-89) and robust_score_difference (src/learning/score/score.delta.c:234-258).
+ * Node v is data column v; amat, blmat and cache are nnodes x nnodes,
+ * column-major ([i + j * nnodes] is arc i -> j); cache is updated in place;
+ * reference[nnodes] holds the current per-node scores. Parents are taken in
+ * increasing node order with the candidate appended last (score.delta.c:44-51).
+ * test_counter += number of deltas actually scored (score.delta.c:278). */
+int bnl_score_cache_fill(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
+                         int nnodes, const int *amat, const int *blmat, const int *updated,
+                         int nupdated, int equivalence, const double *reference,
+                         double *cache, double *test_counter);
+
 #ifdef __cplusplus
 }
 #endif
