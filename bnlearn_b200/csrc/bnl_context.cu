@@ -107,8 +107,8 @@ extern "C" void bnl_shutdown(bnl_ctx *ctx) {
   for (auto &kv : ctx->data) free_dataset(ctx, kv.second);
   for (auto &d : ctx->devs) {
     cudaSetDevice(d.id);
-    cudaFree(d.d_units); cudaFree(d.d_tables); cudaFree(d.d_out); cudaFree(d.d_gidx);
-    cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_gidx);
+    cudaFree(d.d_units); cudaFree(d.d_tables); cudaFree(d.d_out); cudaFree(d.d_gidx); cudaFree(d.d_order);
+    cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_gidx); cudaFreeHost(d.h_order);
     if (d.ev0) cudaEventDestroy(d.ev0);
     if (d.ev1) cudaEventDestroy(d.ev1);
     if (d.evc0) cudaEventDestroy(d.evc0);

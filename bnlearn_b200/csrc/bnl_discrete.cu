@@ -77,6 +77,10 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
   if (!dev.attr_done) {
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_units_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 1024));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 1024));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 1024));
     dev.attr_done = true;
   }
   const int smem_cap_cells = (dev.max_smem - 2048) / 4;
@@ -98,29 +102,76 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_out, &dev.h_out_cap, (size_t)cnt * 4))) return rc;
 
     long long off = 0;
-    int smem_cells = 0;
     for (int i = 0; i < cnt; i++) {
       dev.h_units[i] = rq.units[pos + i];
       dev.h_units[i].table_off = off;
       off += dev.h_units[i].cells;
-      if (dev.h_units[i].cells <= smem_cap_cells) smem_cells = std::max(smem_cells, dev.h_units[i].cells);
     }
-    // enough CTAs to fill the machine, but at least 4096 rows per CTA.
-    int chunks = (4 * dev.sm_count + cnt - 1) / cnt;
-    long long max_chunks = std::max(1ll, groups / 256);
-    if (chunks > max_chunks) chunks = (int)max_chunks;
-    if (chunks < 1) chunks = 1;
+    // three size classes, one launch each (results keep the caller's order: the
+    // kernels reach their units through the `order` map).
+    //   S: <= 256 cells   lane-replicated table, byte-packed indices
+    //   M: <= lane_cap    lane-replicated table, 16-bit packed indices
+    //   L: the rest       one shared (or global) table per CTA, generic kernel
+    const int lane_cap = (dev.max_smem - 2048) / 128;
+    std::vector<int> cls[3];
+    int cmax[3] = {0, 0, 0};
+    for (int i = 0; i < cnt; i++) {
+      const int c = dev.h_units[i].cells;
+      const int k = c <= 256 ? 0 : (c <= lane_cap ? 1 : 2);
+      cls[k].push_back(i);
+      cmax[k] = std::max(cmax[k], c);
+    }
+    if ((rc = bnl_reserve_pinned(ctx, &dev.h_order, &dev.h_order_cap, (size_t)cnt))) return rc;
+    if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
+    {
+      int o = 0;
+      for (int k = 0; k < 3; k++) for (int i : cls[k]) dev.h_order[o++] = i;
+    }
+    auto pick_chunks = [&](int nunits, long long rows_per_cta) {
+      long long ch = (ds.nobs + rows_per_cta - 1) / rows_per_cta;
+      // few units: cut the rows finer so that the machine is full (>= 4096 rows per CTA).
+      const long long want = (8ll * dev.sm_count + nunits - 1) / nunits;
+      ch = std::max(ch, want);
+      ch = std::min(ch, std::max(1ll, groups / 256));
+      return (int)std::max(1ll, ch);
+    };
 
     BNL_CUDA(ctx, cudaEventRecord(dev.ev0, dev.stream));
     BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_units, dev.h_units, (size_t)cnt * sizeof(BnlUnit),
                                   cudaMemcpyHostToDevice, dev.stream));
+    BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_order, dev.h_order, (size_t)cnt * sizeof(int),
+                                  cudaMemcpyHostToDevice, dev.stream));
     BNL_CUDA(ctx, cudaMemsetAsync(dev.d_tables, 0, (size_t)cells * sizeof(int), dev.stream));
     BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
     if (groups > 0) {
-      count_units_kernel<<<cnt * chunks, BNL_CNT_THREADS, (size_t)smem_cells * sizeof(int), dev.stream>>>(
-          dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_tables, chunks, smem_cells);
-      BNL_CUDA(ctx, cudaGetLastError());
-      tm->launches++;
+      int base = 0;
+      if (!cls[0].empty()) {
+        const int ch = pick_chunks((int)cls[0].size(), 65536);
+        count_lane_kernel<false><<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 128, dev.stream>>>(
+            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, ch);
+        BNL_CUDA(ctx, cudaGetLastError());
+        tm->launches++;
+      }
+      base += (int)cls[0].size();
+      if (!cls[1].empty()) {
+        const int ch = pick_chunks((int)cls[1].size(), 524288);
+        count_lane_kernel<true><<<(unsigned)cls[1].size() * ch, BNL_CNT_THREADS, (size_t)cmax[1] * 128, dev.stream>>>(
+            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, ch);
+        BNL_CUDA(ctx, cudaGetLastError());
+        tm->launches++;
+      }
+      base += (int)cls[1].size();
+      if (!cls[2].empty()) {
+        int smem_cells = 0;
+        for (int i : cls[2])
+          if (dev.h_units[i].cells <= smem_cap_cells) smem_cells = std::max(smem_cells, dev.h_units[i].cells);
+        int ch = (4 * dev.sm_count + (int)cls[2].size() - 1) / (int)cls[2].size();
+        ch = (int)std::max(1ll, std::min<long long>(ch, std::max(1ll, groups / 256)));
+        count_units_kernel<<<(unsigned)cls[2].size() * ch, BNL_CNT_THREADS, (size_t)smem_cells * sizeof(int), dev.stream>>>(
+            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, ch, smem_cells);
+        BNL_CUDA(ctx, cudaGetLastError());
+        tm->launches++;
+      }
     }
     BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
     if (rq.kind == 2) {

@@ -30,11 +30,11 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
 // not fit). NA / padding bytes have bit 7 set and veto their row.
 __global__ void __launch_bounds__(BNL_CNT_THREADS)
 count_units_kernel(const uint8_t *__restrict__ u8, size_t stride, long long groups,
-                   const BnlUnit *__restrict__ units, int *__restrict__ tables,
-                   int chunks, int smem_cells) {
+                   const BnlUnit *__restrict__ units, const int *__restrict__ order,
+                   int *__restrict__ tables, int chunks, int smem_cells) {
   extern __shared__ int hist[];
   __shared__ BnlUnit su;
-  const int u = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
+  const int u = order[blockIdx.x / chunks], chunk = blockIdx.x % chunks;
   if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
     reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
   __syncthreads();
@@ -82,6 +82,106 @@ count_units_kernel(const uint8_t *__restrict__ u8, size_t stride, long long grou
       const int v = hist[c];
       if (v) atomicAdd(&gtab[c], v);
     }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Small tables (the common case: a handful of 2-5 level factors): one CTA =
+// (unit, row chunk) again, but the CTA's table is replicated 32 times in shared
+// memory, one copy per LANE, laid out cell-major: word (cell * 32 + lane). A warp's
+// 32 updates then always fall in 32 distinct banks, whatever the data, so every
+// warp-wide atomic is a single conflict-free wavefront (the generic kernel above
+// spends ~9.5 wavefronts per warp on same-address / same-bank collisions; see
+// profiles/). Cell indices for 4 rows are formed in one packed 32-bit register
+// (bytes when the table has <= 256 cells, 16-bit halves otherwise), so the
+// arithmetic is one IMAD per column per 4 (or 2) rows. Rows with an NA fall to a
+// scalar path. `order` maps the launch's CTA groups to unit slots.
+template <bool IDX16>
+__global__ void __launch_bounds__(BNL_CNT_THREADS)
+count_lane_kernel(const uint8_t *__restrict__ u8, size_t stride, long long groups,
+                  const BnlUnit *__restrict__ units, const int *__restrict__ order,
+                  int *__restrict__ tables, int chunks) {
+  extern __shared__ int hist[];
+  __shared__ BnlUnit su;
+  const int u = order[blockIdx.x / chunks], chunk = blockIdx.x % chunks;
+  if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
+    reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
+  __syncthreads();
+  const int cells = su.cells, ncols = su.ncols;
+  for (int c = threadIdx.x; c < cells * 32; c += blockDim.x) hist[c] = 0;
+  __syncthreads();
+  int *hl = hist + (threadIdx.x & 31);
+
+  const long long per = (groups + chunks - 1) / chunks;
+  const long long g0 = per * chunk;
+  long long g1 = g0 + per;
+  if (g1 > groups) g1 = groups;
+
+  for (long long g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+    constexpr int NI = IDX16 ? 8 : 4;
+    unsigned idx[NI];
+#pragma unroll
+    for (int j = 0; j < NI; j++) idx[j] = 0u;
+    unsigned na = 0u;
+    for (int kb = 0; kb < ncols; kb += 4) {
+      uint4 w[4];
+#pragma unroll
+      for (int kk = 0; kk < 4; kk++)
+        if (kb + kk < ncols)
+          w[kk] = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[kb + kk] * stride) + g);
+#pragma unroll
+      for (int kk = 0; kk < 4; kk++)
+        if (kb + kk < ncols) {
+          const unsigned m = (unsigned)su.mul[kb + kk];
+          na |= (w[kk].x | w[kk].y | w[kk].z | w[kk].w) & 0x80808080u;
+          const unsigned ww[4] = {w[kk].x, w[kk].y, w[kk].z, w[kk].w};
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            if (IDX16) {
+              idx[2 * q] += __byte_perm(ww[q], 0, 0x4140) * m;
+              idx[2 * q + 1] += __byte_perm(ww[q], 0, 0x4342) * m;
+            } else {
+              idx[q] += ww[q] * m;
+            }
+          }
+        }
+    }
+    if (na == 0u) {
+#pragma unroll
+      for (int j = 0; j < NI; j++) {
+        if (IDX16) {
+          atomicAdd(hl + ((idx[j] & 0xFFFFu) << 5), 1);
+          atomicAdd(hl + ((idx[j] >> 16) << 5), 1);
+        } else {
+          atomicAdd(hl + ((idx[j] & 0xFFu) << 5), 1);
+          atomicAdd(hl + (((idx[j] >> 8) & 0xFFu) << 5), 1);
+          atomicAdd(hl + (((idx[j] >> 16) & 0xFFu) << 5), 1);
+          atomicAdd(hl + ((idx[j] >> 24) << 5), 1);
+        }
+      }
+    } else {
+      // some row of this group has an NA (or is padding): redo the 16 rows one by
+      // one; the packed sums above may have carried across lanes.
+      for (int r = 0; r < 16; r++) {
+        int cell = 0;
+        bool bad = false;
+        for (int k = 0; k < ncols; k++) {
+          const unsigned b = u8[(size_t)su.col[k] * stride + (size_t)g * 16 + r];
+          bad |= b >= 0x80u;
+          cell += (int)b * su.mul[k];
+        }
+        if (!bad) atomicAdd(hl + (cell << 5), 1);
+      }
+    }
+  }
+
+  __syncthreads();
+  int *gtab = tables + su.table_off;
+  for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+    int sum = 0;
+#pragma unroll
+    for (int l = 0; l < 32; l++) sum += hist[c * 32 + ((l + threadIdx.x) & 31)];
+    if (sum) atomicAdd(&gtab[c], sum);
   }
 }
 

@@ -37,6 +37,8 @@ struct BnlDevice {
   int *d_tables = nullptr; size_t tables_cap = 0;        // int32 elements
   double *d_out = nullptr; size_t out_cap = 0;           // doubles
   int *d_gidx = nullptr; size_t gidx_cap = 0;            // Gaussian unit descriptors
+  int *d_order = nullptr; size_t order_cap = 0;          // launch order -> unit slot
+  int *h_order = nullptr; size_t h_order_cap = 0;        // pinned
   BnlUnit *h_units = nullptr; size_t h_units_cap = 0;    // pinned
   double *h_out = nullptr; size_t h_out_cap = 0;         // pinned
   int *h_gidx = nullptr; size_t h_gidx_cap = 0;          // pinned
