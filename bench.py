@@ -227,13 +227,15 @@ def main():
     z = csr([u[2] for u in my_units])
     algo_bytes = float(args.rows) * float(sum(2 + len(u[2]) for u in my_units))
 
+    # clocks are sampled from the warm-up to the end of the end-to-end loop (the
+    # timed steps alone can be shorter than one nvidia-smi sampling period).
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     eng = Engine([local_rank])
     ds = eng.register(cols32, lev)
     for _ in range(max(args.warmup, 3)):
         ds.ci_discrete("mi", xs, ys, z)
-    sampler = ClockSampler(local_rank)
     barrier()
-    sampler.start()
     count_ms, launches = [], 0
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -243,7 +245,6 @@ def main():
         launches += prof["launches"]
     barrier()
     dt = (time.perf_counter() - t0) / args.steps
-    clocks = sampler.stop()
     ds.release()
 
     # end to end: host buffers in, p-values out, H2D + packing inside the step.
@@ -257,6 +258,16 @@ def main():
         d2.release()
     barrier()
     dt_e2e = (time.perf_counter() - t0) / args.steps
+    clocks = sampler.stop()
+
+    # diagnostic: plain pinned host -> device copy rate of this box.
+    dev_buf = torch.empty((8, rows), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    dev_buf.copy_(pinned[:8], non_blocking=True)
+    torch.cuda.synchronize()
+    h2d_gbs = 8 * rows * 4 / (time.perf_counter() - t0) / 1e9
+    del dev_buf
 
     if world > 1:
         t = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
@@ -284,7 +295,8 @@ def main():
             "value": world * n_units / dt, "ms_per_step": dt * 1e3, "clocks": clocks,
             "e2e": {"value": world * n_units / dt_e2e, "unit": "tests/s",
                     "h2d_bytes_per_step": int(ncol * rows * 4 + xs.nbytes + ys.nbytes + z[0].nbytes + z[1].nbytes),
-                    "d2h_bytes_per_step": int(3 * 8 * n_units)},
+                    "d2h_bytes_per_step": int(3 * 8 * n_units), "ms_per_step": dt_e2e * 1e3,
+                    "pinned_h2d_gbs_probe": h2d_gbs},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": "count kernel (one launch per step)",
                          "achieved": algo_bytes / (kms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",

@@ -25,7 +25,7 @@ int bnl_fail(bnl_ctx *ctx, int code, const char *fmt, ...) {
 // out of bounds there; we refuse the column instead).
 __global__ void __launch_bounds__(256)
 pack_factors_kernel(const int *__restrict__ src, uint8_t *__restrict__ dst, long long nobs,
-                    int nlevels, int *__restrict__ bad) {
+                    int nlevels, int *__restrict__ bad, int *__restrict__ has_na) {
   const long long quads = (nobs + 3) / 4;
   for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < quads;
        q += (long long)gridDim.x * blockDim.x) {
@@ -40,7 +40,7 @@ pack_factors_kernel(const int *__restrict__ src, uint8_t *__restrict__ dst, long
     unsigned out = 0;
     for (int j = 0; j < 4; j++) {
       unsigned b;
-      if (v[j] == INT_MIN) b = BNL_NA_U8;
+      if (v[j] == INT_MIN) { b = BNL_NA_U8; if (r + j < nobs) *has_na = 1; }
       else if (v[j] < 1 || v[j] > nlevels) { b = BNL_NA_U8; *bad = 1; }
       else b = (unsigned)(v[j] - 1);
       out |= b << (8 * j);
@@ -188,8 +188,8 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
     REG_CUDA(cudaMalloc((void **)&dd0.u8, ds.stride_u8 * ds.nd));
     REG_CUDA(cudaMemsetAsync(dd0.u8, BNL_NA_U8, ds.stride_u8 * ds.nd, d0.stream));
     REG_CUDA(cudaMalloc((void **)&stage, ((size_t)nobs + 4) * sizeof(int)));
-    REG_CUDA(cudaMalloc((void **)&d_bad, sizeof(int)));
-    REG_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), d0.stream));
+    REG_CUDA(cudaMalloc((void **)&d_bad, (size_t)(1 + ds.nd) * sizeof(int)));
+    REG_CUDA(cudaMemsetAsync(d_bad, 0, (size_t)(1 + ds.nd) * sizeof(int), d0.stream));
   }
   if (ds.nc > 0) {
     REG_CUDA(cudaMalloc((void **)&dd0.f64, ds.stride_f64 * ds.nc * sizeof(double)));
@@ -209,14 +209,17 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
       int grid = (int)((quads + 255) / 256);
       if (grid > d0.sm_count * 16) grid = d0.sm_count * 16;
       pack_factors_kernel<<<grid, 256, 0, d0.stream>>>(stage, dd0.u8 + ds.stride_u8 * ds.slot[i],
-                                                       nobs, nlevels[i], d_bad);
+                                                       nobs, nlevels[i], d_bad, d_bad + 1 + ds.slot[i]);
       REG_CUDA(cudaGetLastError());
     }
   }
   if (ds.nd > 0) {
-    int bad = 0;
-    REG_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, d0.stream));
+    std::vector<int> flags(1 + ds.nd, 0);
+    REG_CUDA(cudaMemcpyAsync(flags.data(), d_bad, flags.size() * sizeof(int), cudaMemcpyDeviceToHost,
+                             d0.stream));
     REG_CUDA(cudaStreamSynchronize(d0.stream));
+    const int bad = flags[0];
+    ds.slot_has_na.assign(flags.begin() + 1, flags.end());
     if (bad)
       return cleanup(bnl_fail(ctx, BNL_EINVAL, "a factor column holds a code outside 1..nlevels"));
   } else {

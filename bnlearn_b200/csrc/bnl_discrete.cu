@@ -48,6 +48,8 @@ int make_unit(bnl_ctx *ctx, const BnlDataSet &ds, int x, int y, const int *z, in
     mul *= ds.nlevels[z[j]];
   }
   u->ncols = k;
+  for (int c = 0; c < k; c++)
+    if (!ds.slot_has_na.empty() && ds.slot_has_na[u->col[c]]) u->has_na = 1;
   u->llz = (int)llz;
   u->cells = (int)mul;
   if (mul > kMaxBatchCells)
@@ -77,7 +79,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
   if (!dev.attr_done) {
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_units_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 1024));
-    BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 1024));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 1024));
@@ -109,8 +111,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     }
     // three size classes, one launch each (results keep the caller's order: the
     // kernels reach their units through the `order` map).
-    //   S: <= 256 cells   lane-replicated table, byte-packed indices
-    //   M: <= lane_cap    lane-replicated table, 16-bit packed indices
+    //   S: <= 256 cells   64 lane counters per cell, byte-packed indices (count_small_kernel)
+    //   M: <= lane_cap    32 lane counters per cell, 16-bit packed indices (count_lane_kernel)
     //   L: the rest       one shared (or global) table per CTA, generic kernel
     const int lane_cap = (dev.max_smem - 2048) / 128;
     std::vector<int> cls[3];
@@ -147,8 +149,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       int base = 0;
       if (!cls[0].empty()) {
         const int ch = pick_chunks((int)cls[0].size(), 65536);
-        count_lane_kernel<false><<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 128, dev.stream>>>(
-            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, ch);
+        count_small_kernel<<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 256, dev.stream>>>(
+            dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[0].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
       }
@@ -156,7 +158,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       if (!cls[1].empty()) {
         const int ch = pick_chunks((int)cls[1].size(), 524288);
         count_lane_kernel<true><<<(unsigned)cls[1].size() * ch, BNL_CNT_THREADS, (size_t)cmax[1] * 128, dev.stream>>>(
-            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, ch);
+            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[1].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
       }
@@ -168,7 +170,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         int ch = (4 * dev.sm_count + (int)cls[2].size() - 1) / (int)cls[2].size();
         ch = (int)std::max(1ll, std::min<long long>(ch, std::max(1ll, groups / 256)));
         count_units_kernel<<<(unsigned)cls[2].size() * ch, BNL_CNT_THREADS, (size_t)smem_cells * sizeof(int), dev.stream>>>(
-            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, ch, smem_cells);
+            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[2].size(), ch,
+            smem_cells);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
       }

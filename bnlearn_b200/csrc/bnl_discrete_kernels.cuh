@@ -31,10 +31,10 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
 __global__ void __launch_bounds__(BNL_CNT_THREADS)
 count_units_kernel(const uint8_t *__restrict__ u8, size_t stride, long long groups,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
-                   int *__restrict__ tables, int chunks, int smem_cells) {
+                   int *__restrict__ tables, int nunits, int chunks, int smem_cells) {
   extern __shared__ int hist[];
   __shared__ BnlUnit su;
-  const int u = order[blockIdx.x / chunks], chunk = blockIdx.x % chunks;
+  const int chunk = blockIdx.x / nunits, u = order[blockIdx.x % nunits];
   if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
     reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
   __syncthreads();
@@ -100,10 +100,10 @@ template <bool IDX16>
 __global__ void __launch_bounds__(BNL_CNT_THREADS)
 count_lane_kernel(const uint8_t *__restrict__ u8, size_t stride, long long groups,
                   const BnlUnit *__restrict__ units, const int *__restrict__ order,
-                  int *__restrict__ tables, int chunks) {
+                  int *__restrict__ tables, int nunits, int chunks) {
   extern __shared__ int hist[];
   __shared__ BnlUnit su;
-  const int u = order[blockIdx.x / chunks], chunk = blockIdx.x % chunks;
+  const int chunk = blockIdx.x / nunits, u = order[blockIdx.x % nunits];
   if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
     reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
   __syncthreads();
@@ -181,6 +181,155 @@ count_lane_kernel(const uint8_t *__restrict__ u8, size_t stride, long long group
     int sum = 0;
 #pragma unroll
     for (int l = 0; l < 32; l++) sum += hist[c * 32 + ((l + threadIdx.x) & 31)];
+    if (sum) atomicAdd(&gtab[c], sum);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Tables of at most 256 cells -- almost every test and score delta on 2-5 level
+// factors -- get the tightest loop. Same lane-replicated idea, with three more
+// steps taken after profiling the kernel above (profiles/r1_v2_*):
+//   * a cell owns 256 bytes of shared memory (64 counters: lane 0..31 for even
+//     warps, 32..63 for odd warps), so the byte offset of a row's counter is
+//     (cell << 8) | (slot << 2): ONE byte-permute of the packed index register
+//     with the thread's constant slot byte, then the atomic. 2 instructions/row.
+//   * units whose columns hold no NA (flags computed when the data set is
+//     registered) skip the NA bookkeeping; only the last, partial 16-row group
+//     is done row by row.
+//   * CTAs are ordered chunk-major: neighbouring CTAs work on the same rows of
+//     different units, so a row chunk of every column is fetched from HBM once
+//     and then served from L2 to all units that touch it.
+__device__ __forceinline__ void small_bump(int *hist, unsigned v, unsigned slot4) {
+  // v holds 4 packed cell indices; selector 0x55j4: byte0 = slot byte, byte1 = cell.
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(v, slot4, 0x5504)), 1);
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(v, slot4, 0x5514)), 1);
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(v, slot4, 0x5524)), 1);
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(v, slot4, 0x5534)), 1);
+}
+
+__device__ __forceinline__ void small_rows_scalar(const uint8_t *__restrict__ u8, size_t stride,
+                                                  const BnlUnit &su, int *hist, unsigned slot4,
+                                                  long long row0, int nrows) {
+  for (int r = 0; r < nrows; r++) {
+    unsigned cell = 0;
+    bool bad = false;
+    for (int k = 0; k < su.ncols; k++) {
+      const unsigned b = u8[(size_t)su.col[k] * stride + (size_t)(row0 + r)];
+      bad |= b >= 0x80u;
+      cell += b * (unsigned)su.mul[k];
+    }
+    if (!bad) atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + ((cell << 8) | slot4)), 1);
+  }
+}
+
+template <int NC, bool NA>
+__device__ __forceinline__ void small_rows(const uint8_t *__restrict__ u8, size_t stride,
+                                           const BnlUnit &su, int *hist, unsigned slot4,
+                                           long long g0, long long g1) {
+  const uint4 *p[NC];
+  unsigned m[NC];
+#pragma unroll
+  for (int k = 0; k < NC; k++) {
+    p[k] = reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride);
+    m[k] = (unsigned)su.mul[k];
+  }
+  for (long long g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+    uint4 w[NC];
+#pragma unroll
+    for (int k = 0; k < NC; k++) w[k] = ldg_stream(p[k] + g);
+    uint4 v = w[0];                      // the first column always has multiplier 1
+    unsigned na = 0u;
+    if (NA) na = v.x | v.y | v.z | v.w;
+#pragma unroll
+    for (int k = 1; k < NC; k++) {
+      v.x += w[k].x * m[k]; v.y += w[k].y * m[k]; v.z += w[k].z * m[k]; v.w += w[k].w * m[k];
+      if (NA) na |= w[k].x | w[k].y | w[k].z | w[k].w;
+    }
+    if (!NA || (na & 0x80808080u) == 0u) {
+      small_bump(hist, v.x, slot4);
+      small_bump(hist, v.y, slot4);
+      small_bump(hist, v.z, slot4);
+      small_bump(hist, v.w, slot4);
+    } else {
+      small_rows_scalar(u8, stride, su, hist, slot4, g * 16, 16);
+    }
+  }
+}
+
+// generic column count (> 4 columns, still <= 256 cells).
+template <bool NA>
+__device__ __forceinline__ void small_rows_any(const uint8_t *__restrict__ u8, size_t stride,
+                                               const BnlUnit &su, int *hist, unsigned slot4,
+                                               long long g0, long long g1) {
+  const int ncols = su.ncols;
+  for (long long g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    unsigned na = 0u;
+    for (int k = 0; k < ncols; k++) {
+      const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
+      const unsigned m = (unsigned)su.mul[k];
+      v.x += w.x * m; v.y += w.y * m; v.z += w.z * m; v.w += w.w * m;
+      if (NA) na |= w.x | w.y | w.z | w.w;
+    }
+    if (!NA || (na & 0x80808080u) == 0u) {
+      small_bump(hist, v.x, slot4);
+      small_bump(hist, v.y, slot4);
+      small_bump(hist, v.z, slot4);
+      small_bump(hist, v.w, slot4);
+    } else {
+      small_rows_scalar(u8, stride, su, hist, slot4, g * 16, 16);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(BNL_CNT_THREADS)
+count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
+                   const BnlUnit *__restrict__ units, const int *__restrict__ order,
+                   int *__restrict__ tables, int nunits, int chunks) {
+  extern __shared__ __align__(256) int hist[];      // cells x 64 counters
+  __shared__ BnlUnit su;
+  const int chunk = blockIdx.x / nunits, u = order[blockIdx.x % nunits];
+  if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
+    reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
+  __syncthreads();
+  const int cells = su.cells;
+  for (int c = threadIdx.x; c < cells * 64; c += blockDim.x) hist[c] = 0;
+  __syncthreads();
+  const unsigned slot4 = ((threadIdx.x & 31u) + 32u * ((threadIdx.x >> 5) & 1u)) << 2;
+
+  const long long full = nobs / 16;                  // complete 16-row groups
+  const long long per = (full + chunks - 1) / chunks;
+  const long long g0 = per * chunk;
+  long long g1 = g0 + per;
+  if (g1 > full) g1 = full;
+
+  if (su.has_na) {
+    switch (su.ncols) {
+      case 1: small_rows<1, true>(u8, stride, su, hist, slot4, g0, g1); break;
+      case 2: small_rows<2, true>(u8, stride, su, hist, slot4, g0, g1); break;
+      case 3: small_rows<3, true>(u8, stride, su, hist, slot4, g0, g1); break;
+      case 4: small_rows<4, true>(u8, stride, su, hist, slot4, g0, g1); break;
+      default: small_rows_any<true>(u8, stride, su, hist, slot4, g0, g1);
+    }
+  } else {
+    switch (su.ncols) {
+      case 1: small_rows<1, false>(u8, stride, su, hist, slot4, g0, g1); break;
+      case 2: small_rows<2, false>(u8, stride, su, hist, slot4, g0, g1); break;
+      case 3: small_rows<3, false>(u8, stride, su, hist, slot4, g0, g1); break;
+      case 4: small_rows<4, false>(u8, stride, su, hist, slot4, g0, g1); break;
+      default: small_rows_any<false>(u8, stride, su, hist, slot4, g0, g1);
+    }
+  }
+  // the partial group at the end of the data, once.
+  if (chunk == chunks - 1 && threadIdx.x == 0 && full * 16 < nobs)
+    small_rows_scalar(u8, stride, su, hist, slot4, full * 16, (int)(nobs - full * 16));
+
+  __syncthreads();
+  int *gtab = tables + su.table_off;
+  for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+    int sum = 0;
+#pragma unroll
+    for (int l = 0; l < 64; l++) sum += hist[c * 64 + ((l + threadIdx.x) & 63)];
     if (sum) atomicAdd(&gtab[c], sum);
   }
 }

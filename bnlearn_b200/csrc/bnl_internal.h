@@ -21,7 +21,7 @@ struct BnlUnit {
   int cells;              // llx * lly * llz
   int ncols;              // columns involved
   int llx, lly, llz;      // table is n[z][x][y]
-  int pad;
+  int has_na;             // some involved column holds an NA
   int col[BNL_MAXK];      // packed-column slot, order: y (if any), x, z_1, z_2, ...
   int mul[BNL_MAXK];      // contribution of each column to the cell index
 };
@@ -62,6 +62,7 @@ struct BnlDataSet {
   int nd = 0, nc = 0;                   // discrete / numeric column counts
   size_t stride_u8 = 0, stride_f64 = 0;
   std::vector<int> is_numeric, nlevels, slot;
+  std::vector<int> slot_has_na;         // per packed factor column: any NA?
   std::vector<BnlDeviceData> dev;       // one per context device
   std::vector<double> h_mean, h_cov;    // host copies of the Gaussian moments
 };
