@@ -1,0 +1,131 @@
+"""End to end: the restated search loops (bnlearn_b200/learners.py) driven by the
+CUDA backend and by the reference's own C entry points must produce identical
+graphs, separating sets and test-counter totals (north_star: "identical learned
+graphs and test-counter totals")."""
+import numpy as np
+import pytest
+
+from util import load_discrete, load_gaussian
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from bnlearn_b200 import Engine
+    with Engine() as e:
+        yield e
+
+
+def _backends(engine, cols, nlev=None):
+    from bnlearn_b200.learners import GpuBackend
+    from refbackend import RefBackend
+    ds = engine.register(cols, nlev)
+    return GpuBackend(ds), RefBackend(cols, nlev), ds
+
+
+@pytest.mark.parametrize("ds,score,arg", [("learning_test", "bic", None), ("learning_test", "bde", 1.0),
+                                          ("alarm", "bic", None), ("alarm", "bde", 1.0)])
+def test_hc_identical_graph_and_counter(engine, ds, score, arg):
+    from bnlearn_b200 import learners
+    names, cols, nlev = load_discrete(ds)
+    n = len(cols[0])
+    if ds == "alarm":
+        cols = [c[:5000] for c in cols]      # keeps the reference-backend run short
+        n = 5000
+    arg = np.log(n) / 2 if arg is None else arg
+    gpu, ref, d = _backends(engine, cols, nlev)
+    a1, s1 = learners.hc(gpu, len(cols), score, arg)
+    a2, s2 = learners.hc(ref, len(cols), score, arg)
+    assert np.array_equal(a1, a2)
+    assert gpu.counter.value == ref.counter.value
+    assert np.allclose(s1, s2, rtol=1e-9, atol=0)
+    d.release()
+
+
+def test_tabu_identical_graph_and_counter(engine):
+    from bnlearn_b200 import learners
+    names, cols, nlev = load_discrete("learning_test")
+    gpu, ref, d = _backends(engine, cols, nlev)
+    a1, _ = learners.tabu(gpu, len(cols), "bde", 1.0, tabu=5)
+    a2, _ = learners.tabu(ref, len(cols), "bde", 1.0, tabu=5)
+    assert np.array_equal(a1, a2)
+    assert gpu.counter.value == ref.counter.value
+    d.release()
+
+
+def test_hc_bic_on_alarm_recovers_config_a(engine):
+    """Config A (hc + BIC on the bundled alarm data, all 20000 rows) runs on the
+    GPU path; the score of the learned DAG is reproduced by the oracle."""
+    from bnlearn_b200 import learners
+    from oracle import oracle as orc
+    names, cols, nlev = load_discrete("alarm")
+    n = len(cols[0])
+    ds = engine.register(cols, nlev)
+    be = learners.GpuBackend(ds)
+    amat, scores = learners.hc(be, len(cols), "bic", np.log(n) / 2)
+    assert 40 <= amat.sum() <= 60 and be.counter.value > 1000
+    total = 0.0
+    for j in range(len(cols)):
+        pa = [int(i) for i in np.flatnonzero(amat[:, j])]
+        total += orc.score_discrete("bic", cols[j], nlev[j], [cols[i] for i in pa], [nlev[i] for i in pa],
+                                    np.log(n) / 2)[0]
+    assert abs(total - scores.sum()) <= 1e-9 * abs(total)
+    ds.release()
+
+
+@pytest.mark.parametrize("ds,test", [("learning_test", "mi"), ("learning_test", "x2"), ("alarm", "mi")])
+def test_pc_stable_identical_skeleton_dsep_counter(engine, ds, test):
+    from bnlearn_b200 import learners
+    names, cols, nlev = load_discrete(ds)
+    if ds == "alarm":
+        cols = [c[:3000] for c in cols]
+    gpu, ref, d = _backends(engine, cols, nlev)
+    k1, d1, p1 = learners.pc_stable(gpu, len(cols), test, 0.05)
+    k2, d2, p2 = learners.pc_stable(ref, len(cols), test, 0.05)
+    assert k1 == k2 and d1 == d2
+    assert gpu.counter.value == ref.counter.value
+    for key in p1:
+        assert np.isclose(p1[key], p2[key], rtol=1e-9, atol=1e-300)
+    v1 = learners.vstructures(gpu, len(cols), None, None, test, 0.05, d1, p1) if False else None
+    d.release()
+
+
+@pytest.mark.parametrize("algo", ["mmpc", "si.hiton.pc", "iamb"])
+def test_local_discovery_identical(engine, algo):
+    from bnlearn_b200 import learners
+    names, cols, nlev = load_discrete("learning_test")
+    gpu, ref, d = _backends(engine, cols, nlev)
+    n1, m1 = learners.local_discovery(gpu, len(cols), algo, "mi", 0.05)
+    n2, m2 = learners.local_discovery(ref, len(cols), algo, "mi", 0.05)
+    assert n1 == n2 and m1 == m2
+    v1 = learners.vstructures(gpu, len(cols), n1, m1, "mi", 0.05)
+    v2 = learners.vstructures(ref, len(cols), n2, m2, "mi", 0.05)
+    assert [v[1:] for v in v1] == [v[1:] for v in v2]
+    assert gpu.counter.value == ref.counter.value
+    d.release()
+
+
+def test_pc_stable_gaussian_identical(engine):
+    from bnlearn_b200 import learners
+    names, cols = load_gaussian("gaussian_test")
+    gpu, ref, d = _backends(engine, cols)
+    for test in ("cor", "zf"):
+        gpu.counter.reset(); ref.counter.reset()
+        k1, d1, _ = learners.pc_stable(gpu, len(cols), test, 0.05)
+        k2, d2, _ = learners.pc_stable(ref, len(cols), test, 0.05)
+        assert k1 == k2 and d1 == d2
+        assert gpu.counter.value == ref.counter.value
+    a1, _ = learners.hc(gpu, len(cols), "bic-g", np.log(len(cols[0])) / 2)
+    a2, _ = learners.hc(ref, len(cols), "bic-g", np.log(len(cols[0])) / 2)
+    assert np.array_equal(a1, a2)
+    d.release()
+
+
+def test_boot_strength_runs_and_is_deterministic(engine):
+    from bnlearn_b200 import learners
+    names, cols, nlev = load_discrete("learning_test")
+    s1, d1, t1 = learners.boot_strength(engine, cols, nlev, 8, "bde", 1.0, seed=20261109)
+    s2, d2, t2 = learners.boot_strength(engine, cols, nlev, 8, "bde", 1.0, seed=20261109)
+    assert np.array_equal(s1, s2) and np.array_equal(d1, d2) and t1 == t2
+    assert s1[0, 1] == 1.0        # A - B is in every replicate of learning.test
