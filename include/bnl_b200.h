@@ -207,6 +207,37 @@ int bnl_score_cache_fill(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_i
                          int nupdated, int equivalence, const double *reference,
                          double *cache, double *test_counter);
 
+/* ---- allocation-free entry point --------------------------------------------
+ * This one has no counterpart in the reference. It is for callers that must not
+ * let a library allocate device memory: code running inside a framework that
+ * owns the card through its own pool (PyTorch's caching allocator, RMM, a
+ * serving process that reserved all memory up front), where a hidden cudaMalloc
+ * can fail or, at best, synchronises the whole device; and tight loops that
+ * cannot afford that synchronisation. Such callers keep their data on the device
+ * already, so everything here is a DEVICE pointer they own.
+ *
+ * One discrete CI test (mi, mi-adf, x2, x2-adf) of column 0 (x) against column 1
+ * (y) given columns 2..k-1. d_cols is a HOST array of k device pointers to
+ * packed uint8 columns (level code - 1, NA = 0xFF; 16-byte aligned, nobs bytes
+ * each); nlevels is a host array. d_out receives 4 doubles on the device:
+ * statistic, df, p-value, number of complete rows. The work is queued on
+ * `stream` (a cudaStream_t, or NULL) and is NOT synchronised. On error the
+ * message goes to errbuf.
+ *
+ * The count table lives in a fixed array inside the library instead of a
+ * cudaMalloc'ed buffer, hence:
+ *   - at most 65536 table cells (llx * lly * prod(levels of z)); larger tests
+ *     return BNL_EUNSUPPORTED -- use bnl_ci_discrete();
+ *   - each GPU that loads the library holds that array (256 KiB) until exit;
+ *   - all calls share it: it is cleared at the start of every call, and calls
+ *     whose GPU work may overlap (other streams, other threads) race on it, so
+ *     keep them ordered;
+ *   - the first call on each device looks up the array's device address; issue
+ *     that first call outside any CUDA stream capture.
+ * No cudaMalloc, cudaFree or allocating library routine is called. */
+int bnl_ci_discrete_noalloc(int test_e, int k, const uint8_t *const *d_cols, const int *nlevels,
+                            int64_t nobs, double *d_out, void *stream, char *errbuf, int errlen);
+
 #ifdef __cplusplus
 }
 #endif
