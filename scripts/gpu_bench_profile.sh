@@ -8,7 +8,7 @@ python bench.py --steps 5 --warmup 3 > gpurun_out/bench_${TAG}.json 2> gpurun_ou
 echo "bench rc=$?"; tail -c 2500 gpurun_out/bench_${TAG}.json
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_${TAG}.json 2> gpurun_out/bench_ref_${TAG}.err
 echo "ref rc=$?"; tail -c 1200 gpurun_out/bench_ref_${TAG}.json
-CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras"
 $CMD > gpurun_out/plain_${TAG}.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv \
     --log-file gpurun_out/launches_${TAG}.csv $CMD > gpurun_out/ncu_launches_${TAG}.log 2>&1
