@@ -113,19 +113,27 @@ def per_node_score(ds, targets, parents, score, arg=0.0):
     return ds.score(score, targets, parents, arg)[0]
 
 
+def _f_int32(a):
+    return a if (a.dtype == np.int32 and a.flags.f_contiguous) else np.asfortranarray(a, dtype=np.int32)
+
+
 def score_cache_fill(ds, score, arg, amat, blmat, updated, equivalence, reference, cache, counter):
     """score_cache_fill(): amat / blmat / cache are n x n arrays indexed [from, to];
-    cache is updated in place and returned."""
+    cache is updated in place and returned. Fortran-ordered int32 / float64 arrays
+    are passed straight through (the reference's matrices are column-major too);
+    anything else is converted, which costs a copy per call."""
     e = ds.engine
     n = amat.shape[0]
-    a = np.asfortranarray(amat, dtype=np.int32)
-    b = np.asfortranarray(blmat, dtype=np.int32)
-    c = np.asfortranarray(cache, dtype=np.float64)
+    a = _f_int32(amat)
+    b = _f_int32(blmat)
+    direct = cache.dtype == np.float64 and cache.flags.f_contiguous
+    c = cache if direct else np.asfortranarray(cache, dtype=np.float64)
     upd = np.ascontiguousarray(updated, dtype=np.int32)
     ref = np.ascontiguousarray(reference, dtype=np.float64)
     e._check(e._lib.bnl_score_cache_fill(
         e._ctx, ds.handle, SCORES[score], float(arg), n, a.ctypes.data_as(_lib.c_int_p),
         b.ctypes.data_as(_lib.c_int_p), _ip(upd) if len(upd) else None, len(upd), int(bool(equivalence)),
         _dp(ref), c.ctypes.data_as(_lib.c_dbl_p), counter.ref()))
-    cache[...] = c
+    if not direct:
+        cache[...] = c
     return cache

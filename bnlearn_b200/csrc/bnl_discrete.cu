@@ -79,7 +79,9 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
   if (!dev.attr_done) {
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_units_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 1024));
-    BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 1024));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 1024));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 1024));
@@ -109,17 +111,19 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       dev.h_units[i].table_off = off;
       off += dev.h_units[i].cells;
     }
-    // three size classes, one launch each (results keep the caller's order: the
+    // four size classes, one launch each (results keep the caller's order: the
     // kernels reach their units through the `order` map).
-    //   S: <= 256 cells   64 lane counters per cell, byte-packed indices (count_small_kernel)
-    //   M: <= lane_cap    32 lane counters per cell, 16-bit packed indices (count_lane_kernel)
-    //   L: the rest       one shared (or global) table per CTA, generic kernel
+    //   S : <= 256 cells    64 lane counters per cell, byte-packed indices   (count_small_kernel<false>)
+    //   M1: <= mid_cap      64 lane counters per cell, 16-bit packed indices (count_small_kernel<true>)
+    //   M2: <= lane_cap     32 lane counters per cell, 16-bit packed indices (count_lane_kernel<true>)
+    //   L : the rest        one shared (or global) table per CTA             (count_units_kernel)
+    const int mid_cap = (dev.max_smem - 2048) / 256;
     const int lane_cap = (dev.max_smem - 2048) / 128;
-    std::vector<int> cls[3];
-    int cmax[3] = {0, 0, 0};
+    std::vector<int> cls[4];
+    int cmax[4] = {0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
       const int c = dev.h_units[i].cells;
-      const int k = c <= 256 ? 0 : (c <= lane_cap ? 1 : 2);
+      const int k = c <= 256 ? 0 : (c <= mid_cap ? 1 : (c <= lane_cap ? 2 : 3));
       cls[k].push_back(i);
       cmax[k] = std::max(cmax[k], c);
     }
@@ -127,7 +131,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
     {
       int o = 0;
-      for (int k = 0; k < 3; k++) for (int i : cls[k]) dev.h_order[o++] = i;
+      for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
     }
     auto pick_chunks = [&](int nunits, long long rows_per_cta) {
       long long ch = (ds.nobs + rows_per_cta - 1) / rows_per_cta;
@@ -149,28 +153,36 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       int base = 0;
       if (!cls[0].empty()) {
         const int ch = pick_chunks((int)cls[0].size(), 65536);
-        count_small_kernel<<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 256, dev.stream>>>(
+        count_small_kernel<false><<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 256, dev.stream>>>(
             dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[0].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
       }
       base += (int)cls[0].size();
       if (!cls[1].empty()) {
-        const int ch = pick_chunks((int)cls[1].size(), 524288);
-        count_lane_kernel<true><<<(unsigned)cls[1].size() * ch, BNL_CNT_THREADS, (size_t)cmax[1] * 128, dev.stream>>>(
-            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[1].size(), ch);
+        const int ch = pick_chunks((int)cls[1].size(), 262144);
+        count_small_kernel<true><<<(unsigned)cls[1].size() * ch, 512, (size_t)cmax[1] * 256, dev.stream>>>(
+            dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[1].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
       }
       base += (int)cls[1].size();
       if (!cls[2].empty()) {
+        const int ch = pick_chunks((int)cls[2].size(), 524288);
+        count_lane_kernel<true><<<(unsigned)cls[2].size() * ch, BNL_CNT_THREADS, (size_t)cmax[2] * 128, dev.stream>>>(
+            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[2].size(), ch);
+        BNL_CUDA(ctx, cudaGetLastError());
+        tm->launches++;
+      }
+      base += (int)cls[2].size();
+      if (!cls[3].empty()) {
         int smem_cells = 0;
-        for (int i : cls[2])
+        for (int i : cls[3])
           if (dev.h_units[i].cells <= smem_cap_cells) smem_cells = std::max(smem_cells, dev.h_units[i].cells);
-        int ch = (4 * dev.sm_count + (int)cls[2].size() - 1) / (int)cls[2].size();
+        int ch = (4 * dev.sm_count + (int)cls[3].size() - 1) / (int)cls[3].size();
         ch = (int)std::max(1ll, std::min<long long>(ch, std::max(1ll, groups / 256)));
-        count_units_kernel<<<(unsigned)cls[2].size() * ch, BNL_CNT_THREADS, (size_t)smem_cells * sizeof(int), dev.stream>>>(
-            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[2].size(), ch,
+        count_units_kernel<<<(unsigned)cls[3].size() * ch, BNL_CNT_THREADS, (size_t)smem_cells * sizeof(int), dev.stream>>>(
+            dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[3].size(), ch,
             smem_cells);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;

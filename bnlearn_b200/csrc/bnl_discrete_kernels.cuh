@@ -186,8 +186,8 @@ count_lane_kernel(const uint8_t *__restrict__ u8, size_t stride, long long group
 }
 
 // ---------------------------------------------------------------------------
-// Tables of at most 256 cells -- almost every test and score delta on 2-5 level
-// factors -- get the tightest loop. Same lane-replicated idea, with three more
+// Tables of at most 256 cells (byte-packed indices) or 880 cells (16-bit packed)
+// -- almost every test and score delta on 2-5 level factors -- get the tightest loop. Same lane-replicated idea, with three more
 // steps taken after profiling the kernel above (profiles/r1_v2_*):
 //   * a cell owns 256 bytes of shared memory (64 counters: lane 0..31 for even
 //     warps, 32..63 for odd warps), so the byte offset of a row's counter is
@@ -222,7 +222,14 @@ __device__ __forceinline__ void small_rows_scalar(const uint8_t *__restrict__ u8
   }
 }
 
-template <int NC, bool NA>
+// 16-bit variant of small_bump for tables of 257..880 cells: v holds 2 packed
+// indices; the offset is (index << 8) | slot byte, still one PRMT.
+__device__ __forceinline__ void mid_bump(int *hist, unsigned v, unsigned slot4) {
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(v, slot4, 0x5104)), 1);
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(v, slot4, 0x5324)), 1);
+}
+
+template <int NC, bool NA, bool W16>
 __device__ __forceinline__ void small_rows(const uint8_t *__restrict__ u8, size_t stride,
                                            const BnlUnit &su, int *hist, unsigned slot4,
                                            long long g0, long long g1) {
@@ -237,52 +244,102 @@ __device__ __forceinline__ void small_rows(const uint8_t *__restrict__ u8, size_
     uint4 w[NC];
 #pragma unroll
     for (int k = 0; k < NC; k++) w[k] = ldg_stream(p[k] + g);
-    uint4 v = w[0];                      // the first column always has multiplier 1
     unsigned na = 0u;
-    if (NA) na = v.x | v.y | v.z | v.w;
+    if (NA) {
 #pragma unroll
-    for (int k = 1; k < NC; k++) {
-      v.x += w[k].x * m[k]; v.y += w[k].y * m[k]; v.z += w[k].z * m[k]; v.w += w[k].w * m[k];
-      if (NA) na |= w[k].x | w[k].y | w[k].z | w[k].w;
+      for (int k = 0; k < NC; k++) na |= w[k].x | w[k].y | w[k].z | w[k].w;
     }
-    if (!NA || (na & 0x80808080u) == 0u) {
+    if (NA && (na & 0x80808080u) != 0u) {
+      small_rows_scalar(u8, stride, su, hist, slot4, g * 16, 16);
+      continue;
+    }
+    if (!W16) {
+      uint4 v = w[0];                    // the first column always has multiplier 1
+#pragma unroll
+      for (int k = 1; k < NC; k++) {
+        v.x += w[k].x * m[k]; v.y += w[k].y * m[k]; v.z += w[k].z * m[k]; v.w += w[k].w * m[k];
+      }
       small_bump(hist, v.x, slot4);
       small_bump(hist, v.y, slot4);
       small_bump(hist, v.z, slot4);
       small_bump(hist, v.w, slot4);
     } else {
-      small_rows_scalar(u8, stride, su, hist, slot4, g * 16, 16);
+      unsigned v[8];
+      const unsigned w0[4] = {w[0].x, w[0].y, w[0].z, w[0].w};
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        v[2 * q] = __byte_perm(w0[q], 0, 0x4140);
+        v[2 * q + 1] = __byte_perm(w0[q], 0, 0x4342);
+      }
+#pragma unroll
+      for (int k = 1; k < NC; k++) {
+        const unsigned wk[4] = {w[k].x, w[k].y, w[k].z, w[k].w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          v[2 * q] += __byte_perm(wk[q], 0, 0x4140) * m[k];
+          v[2 * q + 1] += __byte_perm(wk[q], 0, 0x4342) * m[k];
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; j++) mid_bump(hist, v[j], slot4);
     }
   }
 }
 
-// generic column count (> 4 columns, still <= 256 cells).
-template <bool NA>
+// generic column count (> 4 columns).
+template <bool NA, bool W16>
 __device__ __forceinline__ void small_rows_any(const uint8_t *__restrict__ u8, size_t stride,
                                                const BnlUnit &su, int *hist, unsigned slot4,
                                                long long g0, long long g1) {
   const int ncols = su.ncols;
   for (long long g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    unsigned v[W16 ? 8 : 4];
+#pragma unroll
+    for (int j = 0; j < (W16 ? 8 : 4); j++) v[j] = 0u;
     unsigned na = 0u;
     for (int k = 0; k < ncols; k++) {
       const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
       const unsigned m = (unsigned)su.mul[k];
-      v.x += w.x * m; v.y += w.y * m; v.z += w.z * m; v.w += w.w * m;
+      const unsigned ww[4] = {w.x, w.y, w.z, w.w};
       if (NA) na |= w.x | w.y | w.z | w.w;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        if (W16) {
+          v[2 * q] += __byte_perm(ww[q], 0, 0x4140) * m;
+          v[2 * q + 1] += __byte_perm(ww[q], 0, 0x4342) * m;
+        } else {
+          v[q] += ww[q] * m;
+        }
+      }
     }
-    if (!NA || (na & 0x80808080u) == 0u) {
-      small_bump(hist, v.x, slot4);
-      small_bump(hist, v.y, slot4);
-      small_bump(hist, v.z, slot4);
-      small_bump(hist, v.w, slot4);
-    } else {
+    if (NA && (na & 0x80808080u) != 0u) {
       small_rows_scalar(u8, stride, su, hist, slot4, g * 16, 16);
+      continue;
+    }
+#pragma unroll
+    for (int j = 0; j < (W16 ? 8 : 4); j++) {
+      if (W16) mid_bump(hist, v[j], slot4); else small_bump(hist, v[j], slot4);
     }
   }
 }
 
-__global__ void __launch_bounds__(BNL_CNT_THREADS)
+template <bool NA, bool W16>
+__device__ __forceinline__ void small_dispatch(const uint8_t *__restrict__ u8, size_t stride,
+                                               const BnlUnit &su, int *hist, unsigned slot4,
+                                               long long g0, long long g1) {
+  switch (su.ncols) {
+    case 1: small_rows<1, NA, W16>(u8, stride, su, hist, slot4, g0, g1); break;
+    case 2: small_rows<2, NA, W16>(u8, stride, su, hist, slot4, g0, g1); break;
+    case 3: small_rows<3, NA, W16>(u8, stride, su, hist, slot4, g0, g1); break;
+    case 4: small_rows<4, NA, W16>(u8, stride, su, hist, slot4, g0, g1); break;
+    default: small_rows_any<NA, W16>(u8, stride, su, hist, slot4, g0, g1);
+  }
+}
+
+// W16 = false: tables <= 256 cells, 256 threads. W16 = true: 257..880 cells (the
+// table fills most of the SM's shared memory, so one CTA of 512 threads per SM).
+template <bool W16>
+__global__ void __launch_bounds__(W16 ? 512 : BNL_CNT_THREADS)
 count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
                    int *__restrict__ tables, int nunits, int chunks) {
@@ -303,23 +360,8 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   long long g1 = g0 + per;
   if (g1 > full) g1 = full;
 
-  if (su.has_na) {
-    switch (su.ncols) {
-      case 1: small_rows<1, true>(u8, stride, su, hist, slot4, g0, g1); break;
-      case 2: small_rows<2, true>(u8, stride, su, hist, slot4, g0, g1); break;
-      case 3: small_rows<3, true>(u8, stride, su, hist, slot4, g0, g1); break;
-      case 4: small_rows<4, true>(u8, stride, su, hist, slot4, g0, g1); break;
-      default: small_rows_any<true>(u8, stride, su, hist, slot4, g0, g1);
-    }
-  } else {
-    switch (su.ncols) {
-      case 1: small_rows<1, false>(u8, stride, su, hist, slot4, g0, g1); break;
-      case 2: small_rows<2, false>(u8, stride, su, hist, slot4, g0, g1); break;
-      case 3: small_rows<3, false>(u8, stride, su, hist, slot4, g0, g1); break;
-      case 4: small_rows<4, false>(u8, stride, su, hist, slot4, g0, g1); break;
-      default: small_rows_any<false>(u8, stride, su, hist, slot4, g0, g1);
-    }
-  }
+  if (su.has_na) small_dispatch<true, W16>(u8, stride, su, hist, slot4, g0, g1);
+  else small_dispatch<false, W16>(u8, stride, su, hist, slot4, g0, g1);
   // the partial group at the end of the data, once.
   if (chunk == chunks - 1 && threadIdx.x == 0 && full * 16 < nobs)
     small_rows_scalar(u8, stride, su, hist, slot4, full * 16, (int)(nobs - full * 16));

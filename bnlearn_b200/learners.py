@@ -187,10 +187,11 @@ def _fix_singular(backend, amat, op, cache, reference, score, arg):
 
 def hc(backend, nnodes, score, arg=0.0, maxp=np.inf, max_iter=np.inf, start=None):
     """hill.climbing(optimized = TRUE, restart = 0). Returns (amat, per-node scores)."""
-    amat = np.zeros((nnodes, nnodes), dtype=np.int32) if start is None else start.copy()
-    blmat = np.zeros((nnodes, nnodes), dtype=np.int32)
-    wlmat = np.zeros((nnodes, nnodes), dtype=np.int32)
-    cache = np.zeros((nnodes, nnodes))
+    amat = (np.zeros((nnodes, nnodes), dtype=np.int32, order="F") if start is None
+            else np.asfortranarray(start, dtype=np.int32).copy(order="F"))
+    blmat = np.zeros((nnodes, nnodes), dtype=np.int32, order="F")
+    wlmat = np.zeros((nnodes, nnodes), dtype=np.int32, order="F")
+    cache = np.zeros((nnodes, nnodes), order="F")
     equivalence = score in SCORE_EQUIVALENT
     reference = np.array(backend.per_node_score(list(range(nnodes)), _parents(amat), score, arg), dtype=float)
     updated = list(range(nnodes))
@@ -223,10 +224,10 @@ def _robust(new, old):
 def tabu(backend, nnodes, score, arg=0.0, maxp=np.inf, max_iter=np.inf, tabu=10, max_tabu=None):
     """tabu.search(optimized = TRUE). Returns (amat, per-node scores of the last network)."""
     max_tabu = tabu if max_tabu is None else max_tabu
-    amat = np.zeros((nnodes, nnodes), dtype=np.int32)
+    amat = np.zeros((nnodes, nnodes), dtype=np.int32, order="F")
     blmat = np.zeros_like(amat)
     wlmat = np.zeros_like(amat)
-    cache = np.zeros((nnodes, nnodes))
+    cache = np.zeros((nnodes, nnodes), order="F")
     equivalence = score in SCORE_EQUIVALENT
     reference = np.array(backend.per_node_score(list(range(nnodes)), _parents(amat), score, arg), dtype=float)
     updated = list(range(nnodes))

@@ -246,3 +246,37 @@ def test_special_functions_on_device_match_host_build(engine):
             _check(st[i], rs, (test, "stat", i), rtol=1e-9, atol=1e-13)
             _check(pv[i], rp, (test, "p", i))
     d.release()
+
+
+@pytest.mark.parametrize("with_na", [False, True])
+def test_every_table_size_class(engine, with_na):
+    """One unit per counting path: <= 256 cells, <= 880, <= ~1800, shared-memory
+    table, global-memory table; with and without NAs; ragged row count."""
+    from oracle import oracle as orc
+    rng = np.random.default_rng(17)
+    n = 70001
+    lev = [5, 4, 5, 5, 6, 3, 7, 2, 9]
+    cols = [rng.integers(1, l + 1, n).astype(np.int32) for l in lev]
+    if with_na:
+        for c in cols:
+            c[rng.random(n) < 0.01] = orc.NA_INT
+    d = engine.register(cols, lev)
+    units = [(0, 1, [5]),                 # 60 cells
+             (0, 1, [2, 3]),              # 500 cells
+             (0, 1, [2, 3, 5]),           # 1500 cells
+             (0, 1, [2, 3, 4, 7]),        # 6000 cells
+             (0, 1, [2, 3, 4, 6, 8]),     # 189000 cells: beyond shared memory
+             (6, 8, [0, 1, 2, 3, 4, 5])]  # 6 conditioning columns, generic column loop
+    xs, ys, zs = [u[0] for u in units], [u[1] for u in units], [u[2] for u in units]
+    tabs = d.counts(xs, ys, zs)
+    for (x, y, z), t in zip(units, tabs):
+        ref = orc.counts(cols[x], lev[x], cols[y], lev[y], [cols[i] for i in z], [lev[i] for i in z])
+        assert np.array_equal(t, ref), (x, y, z)
+    st, df, pv = d.ci_discrete("mi", xs, ys, zs)
+    for i, (x, y, z) in enumerate(units):
+        rs, rdf, rp = orc.ci_discrete("mi", cols[x], lev[x], cols[y], lev[y], [cols[j] for j in z],
+                                      [lev[j] for j in z])
+        assert df[i] == rdf
+        _check(st[i], rs, ("stat", i), atol=1e-11)
+        _check(pv[i], rp, ("p", i), atol=1e-300)
+    d.release()
