@@ -231,6 +231,81 @@ def config_c_extras(eng, rows=1_000_000, nnodes=1000, seed=20261107, reps=5):
 
 
 # --------------------------------------------------------------------------
+# secondary metric: Gaussian CI tests per second on the config-D shape
+# (pc.stable + cor, 2000 numeric columns x 1M rows): one Gram matrix on the fp64
+# tensor cores at registration, then batched solves served from it.
+
+def config_d_extras(eng, rows=1_000_000, nvars=2000, seed=20261108):
+    import torch
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed)
+    cpu = np.random.Generator(np.random.PCG64(seed))
+    x = torch.empty((nvars, rows), dtype=torch.float64, device="cuda")
+    for i in range(nvars):
+        k = min(int(cpu.poisson(1.5)), 5, i)
+        pa = [int(j) for j in cpu.choice(i, size=k, replace=False)] if k else []
+        x[i] = torch.randn(rows, generator=g, device="cuda", dtype=torch.float64) * float(cpu.uniform(0.5, 1.5))
+        for j in pa:
+            x[i] += float(cpu.uniform(0.3, 1.0) * cpu.choice([-1.0, 1.0])) * x[j]
+    host = x.cpu().numpy()
+    del x
+    torch.cuda.empty_cache()
+    # fp64 GEMM probe for the DMMA roofline denominator (cuBLAS DGEMM, 8192^3).
+    a = torch.randn((8192, 8192), dtype=torch.float64, device="cuda")
+    torch.matmul(a, a)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    torch.matmul(a, a)
+    torch.cuda.synchronize()
+    dgemm_tf = 2 * 8192 ** 3 / (time.perf_counter() - t0) / 1e12
+    del a
+    torch.cuda.empty_cache()
+
+    t0 = time.perf_counter()
+    ds = eng.register([host[i] for i in range(nvars)])
+    reg_s = time.perf_counter() - t0
+    gram_ms = eng.last_call_profile()["count_ms"]
+    flops = float(rows) * nvars * (nvars + 1)
+    out = {"shape": "%d numeric columns x %d rows" % (nvars, rows), "register_s": reg_s,
+           "gram": {"kernel_ms": gram_ms, "algorithmic_flops": flops,
+                    "achieved_tflops": flops / (gram_ms * 1e-3) / 1e12,
+                    "dgemm_probe_tflops": dgemm_tf,
+                    "frac_of_dgemm_probe": flops / (gram_ms * 1e-3) / 1e12 / dgemm_tf}}
+    iu = np.triu_indices(nvars, 1)
+    xs, ys = iu[0].astype(np.int32), iu[1].astype(np.int32)
+    empty = (np.zeros(len(xs) + 1, dtype=np.int32), np.zeros(1, dtype=np.int32))
+    for test in ("cor", "zf"):
+        best = None
+        for _ in range(3):
+            t0 = time.perf_counter()
+            st, df, pv = ds.ci_gaussian(test, xs, ys, empty)
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        out["level0_" + test] = {"tests": len(xs), "ms": best * 1e3, "tests_per_sec": len(xs) / best,
+                                 "kernel_ms": eng.last_call_profile()["count_ms"],
+                                 "edges_kept_at_0.05": int((pv < 0.05).sum())}
+    rng = np.random.default_rng(5)
+    for k in (1, 3):
+        n = 400000
+        idx = np.stack([rng.permutation(nvars)[:2 + k] for _ in range(n)]).astype(np.int32)
+        off = np.arange(0, (n + 1) * k, k, dtype=np.int32)
+        zi = np.ascontiguousarray(idx[:, 2:]).ravel()
+        t0 = time.perf_counter()
+        ds.ci_gaussian("cor", idx[:, 0].copy(), idx[:, 1].copy(), (off, zi))
+        dt = time.perf_counter() - t0
+        out["cond_size_%d" % k] = {"tests": n, "ms": dt * 1e3, "tests_per_sec": n / dt,
+                                   "kernel_ms": eng.last_call_profile()["count_ms"]}
+    ds.release()
+    # the reference recomputes the covariance from the raw columns for every test.
+    from oracle import oracle as orc
+    t0 = time.perf_counter()
+    for i in range(8):
+        orc.ci_gaussian("cor", [host[2 * i], host[2 * i + 1]])
+    out["cpu_port_level0_tests_per_sec_per_core"] = 8 / (time.perf_counter() - t0)
+    return out
+
+
+# --------------------------------------------------------------------------
 
 def main():
     args = parse_args()
@@ -398,6 +473,10 @@ def main():
                 line["score_deltas"] = config_c_extras(eng)
             except Exception as exc:                      # the headline line must still be printed
                 line["score_deltas"] = {"error": repr(exc)}
+            try:
+                line["gaussian"] = config_d_extras(eng)
+            except Exception as exc:
+                line["gaussian"] = {"error": repr(exc)}
         if world == 1 and not args.no_cpu_baseline:
             sample = args.cpu_sample or max(cores * 8, 64)
             rng = np.random.default_rng(1)
