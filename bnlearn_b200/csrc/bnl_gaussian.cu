@@ -15,13 +15,13 @@ int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
   BNL_CUDA(ctx, cudaMalloc((void **)&dd.mean, (size_t)p * sizeof(double)));
   BNL_CUDA(ctx, cudaMalloc((void **)&dd.cov, (size_t)p * p * sizeof(double)));
 
-  // row slices: enough CTAs to fill the machine, at least 8192 rows per slice,
-  // and at most 256 MiB of partials.
+  // row slices: enough CTAs for several waves, at least 8192 rows per slice,
+  // and at most 512 MiB of partials.
   const int ntile = (p + GRAM_TILE - 1) / GRAM_TILE;
   const int ntri = ntile * (ntile + 1) / 2;
-  long long nsplit = (4ll * dev.sm_count + ntri - 1) / ntri;
+  long long nsplit = (12ll * dev.sm_count + ntri - 1) / ntri;
   nsplit = std::min(nsplit, std::max(1ll, ds.nobs / 8192));
-  nsplit = std::min(nsplit, std::max(1ll, (256ll << 20) / ((long long)p * p * 8)));
+  nsplit = std::min(nsplit, std::max(1ll, (512ll << 20) / ((long long)p * p * 8)));
   nsplit = std::max(nsplit, 1ll);
   long long msplit = std::min<long long>(std::max(1ll, ds.nobs / 65536), 64);
 
@@ -34,7 +34,8 @@ int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
   cudaEventRecord(dev.evc0, dev.stream);
   col_sum_kernel<<<dim3(p, (unsigned)msplit), 256, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, p, partial);
   col_mean_kernel<<<(p + 127) / 128, 128, 0, dev.stream>>>(partial, (int)msplit, p, ds.nobs, dd.mean);
-  gram_dmma_kernel<<<dim3(ntri, (unsigned)nsplit), GRAM_THREADS, 0, dev.stream>>>(
+  cudaFuncSetAttribute(gram_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GRAM_SMEM);
+  gram_dmma_kernel<<<dim3(ntri, (unsigned)nsplit), GRAM_THREADS, GRAM_SMEM, dev.stream>>>(
       dd.f64, ds.stride_f64, ds.nobs, p, dd.mean, partial, ntile);
   const long long elems = (long long)p * p;
   gram_finish_kernel<<<(unsigned)((elems + 255) / 256), 256, 0, dev.stream>>>(partial, (int)nsplit, p,

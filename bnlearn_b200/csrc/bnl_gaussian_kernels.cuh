@@ -14,10 +14,12 @@
 #include "bnl_internal.h"
 #include "bnl_special.cuh"
 
-#define GRAM_TILE 64          // C tile edge per CTA
-#define GRAM_KB 32            // rows staged per step
+#define GRAM_TILE 128         // C tile edge per CTA
+#define GRAM_KB 16            // rows staged per pipeline stage
 #define GRAM_LD (GRAM_KB + 4) // smem row stride in doubles: conflict-free 64-bit fragment loads
-#define GRAM_THREADS 128
+#define GRAM_STAGES 4
+#define GRAM_THREADS 512
+#define GRAM_SMEM (GRAM_STAGES * 2 * GRAM_TILE * GRAM_LD * 8)
 #define BNL_GW (BNL_MAXK + 1) // ints per Gaussian unit descriptor: count, then column slots
 
 // ---------------------------------------------------------------------------
@@ -60,23 +62,35 @@ __global__ void col_mean_kernel(const double *__restrict__ partial, int nsplit, 
 
 // ---------------------------------------------------------------------------
 // Gram matrix of the centred columns on the fp64 tensor cores (DMMA,
-// mma.sync.m8n8k4.f64; tcgen05 has no fp64 kind). One CTA = one upper-triangular
-// 64 x 64 tile of C over one slice of the rows; 4 warps, each a 32 x 32 sub-tile
-// = 4 x 4 DMMA tiles. Columns are centred as they are staged into shared memory
-// (the reference centres too, src/core/covariance.matrix.c:87), rows past nobs
-// and columns past p contribute zeros.
+// mma.sync.m8n8k4.f64; tcgen05 has no fp64 kind). The reference centres too
+// (src/core/covariance.matrix.c:87); rows past nobs and columns past p
+// contribute nothing.
 __device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-__global__ void __launch_bounds__(GRAM_THREADS)
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N)); }
+
+// One CTA = one upper-triangular 128 x 128 tile of C over one slice of the rows;
+// 16 warps in a 4 x 4 grid, each a 32 x 32 sub-tile = 4 x 4 DMMA tiles. Raw
+// columns stream into a 4-stage cp.async ring (16 rows per stage); they are
+// centred when the fragments are read from shared memory (means in registers),
+// and rows past nobs are masked to zero in the last stage only.
+__global__ void __launch_bounds__(GRAM_THREADS, 1)
 gram_dmma_kernel(const double *__restrict__ X, size_t stride, long long nobs, int p,
                  const double *__restrict__ mean, double *__restrict__ partial, int ntile) {
-  __shared__ __align__(16) double As[GRAM_TILE][GRAM_LD];
-  __shared__ __align__(16) double Bs[GRAM_TILE][GRAM_LD];
+  extern __shared__ __align__(16) double gsm_tiles[];
+  typedef double (*tile_t)[GRAM_TILE][GRAM_LD];
+  tile_t As = reinterpret_cast<tile_t>(gsm_tiles);
+  tile_t Bs = reinterpret_cast<tile_t>(gsm_tiles + (size_t)GRAM_STAGES * GRAM_TILE * GRAM_LD);
 
-  // linear upper-triangular tile index -> (ti, tj), ti <= tj.
   int t = blockIdx.x, ti = 0;
   while (t >= ntile - ti) { t -= ntile - ti; ti++; }
   const int tj = ti + t;
@@ -87,62 +101,76 @@ gram_dmma_kernel(const double *__restrict__ X, size_t stride, long long nobs, in
   const long long s0 = per * split;
   long long s1 = s0 + per;
   if (s1 > steps) s1 = steps;
+  const int nst = (int)(s1 > s0 ? s1 - s0 : 0);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+  const int wm = (warp >> 2) * 32, wn = (warp & 3) * 32;
   const int g = lane >> 2, q = lane & 3;
 
+  // this thread's share of a stage: 128 columns x 8 double2 per operand = 1024
+  // 16-byte copies per operand, 2 per thread.
+  auto issue = [&](int s_local) {
+    const long long r0 = (s0 + s_local) * GRAM_KB;
+    const int buf = s_local % GRAM_STAGES;
+#pragma unroll
+    for (int rep = 0; rep < 2; rep++) {
+      const int idx = threadIdx.x + rep * GRAM_THREADS;
+      const int c = idx >> 3, r2 = (idx & 7) * 2;
+      int col = ti * GRAM_TILE + c;
+      if (col >= p) col = p - 1;
+      cp_async16(&As[buf][c][r2], X + (size_t)col * stride + r0 + r2);
+      if (!diag) {
+        col = tj * GRAM_TILE + c;
+        if (col >= p) col = p - 1;
+        cp_async16(&Bs[buf][c][r2], X + (size_t)col * stride + r0 + r2);
+      }
+    }
+  };
+
+  double ma[4], mb[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    int col = ti * GRAM_TILE + wm + i * 8 + g;
+    ma[i] = mean[col < p ? col : p - 1];
+    col = tj * GRAM_TILE + wn + i * 8 + g;
+    mb[i] = mean[col < p ? col : p - 1];
+  }
   double acc[4][4][2];
 #pragma unroll
   for (int i = 0; i < 4; i++)
 #pragma unroll
     for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-  for (long long s = s0; s < s1; s++) {
-    const long long r0 = s * GRAM_KB;
-    // stage: 64 columns x 32 rows per operand, as double2 (16 per column).
-    for (int idx = threadIdx.x; idx < GRAM_TILE * (GRAM_KB / 2); idx += GRAM_THREADS) {
-      const int c = idx / (GRAM_KB / 2), r2 = (idx % (GRAM_KB / 2)) * 2;
-      const long long r = r0 + r2;
-      {
-        const int col = ti * GRAM_TILE + c;
-        double2 v = make_double2(0.0, 0.0);
-        if (col < p) {
-          const double m = mean[col];
-          const double2 w = *reinterpret_cast<const double2 *>(X + (size_t)col * stride + r);
-          v.x = r < nobs ? w.x - m : 0.0;
-          v.y = r + 1 < nobs ? w.y - m : 0.0;
-        }
-        *reinterpret_cast<double2 *>(&As[c][r2]) = v;
-      }
-      if (!diag) {
-        const int col = tj * GRAM_TILE + c;
-        double2 v = make_double2(0.0, 0.0);
-        if (col < p) {
-          const double m = mean[col];
-          const double2 w = *reinterpret_cast<const double2 *>(X + (size_t)col * stride + r);
-          v.x = r < nobs ? w.x - m : 0.0;
-          v.y = r + 1 < nobs ? w.y - m : 0.0;
-        }
-        *reinterpret_cast<double2 *>(&Bs[c][r2]) = v;
-      }
-    }
+#pragma unroll
+  for (int s = 0; s < GRAM_STAGES - 1; s++) {
+    if (s < nst) issue(s);
+    cp_async_commit();
+  }
+  for (int s = 0; s < nst; s++) {
+    cp_async_wait<GRAM_STAGES - 2>();
     __syncthreads();
-    const double (*Bp)[GRAM_LD] = diag ? As : Bs;
+    if (s + GRAM_STAGES - 1 < nst) issue(s + GRAM_STAGES - 1);
+    cp_async_commit();
+    const int buf = s % GRAM_STAGES;
+    const double (*Ap)[GRAM_LD] = As[buf];
+    const double (*Bp)[GRAM_LD] = diag ? As[buf] : Bs[buf];
+    const long long r0 = (s0 + s) * GRAM_KB;
+    const bool ragged = r0 + GRAM_KB > nobs;
 #pragma unroll
     for (int kk = 0; kk < GRAM_KB; kk += 4) {
       double a[4], b[4];
+      const bool live = !ragged || (r0 + kk + q < nobs);
 #pragma unroll
-      for (int i = 0; i < 4; i++) a[i] = As[wm + i * 8 + g][kk + q];
+      for (int i = 0; i < 4; i++) a[i] = live ? Ap[wm + i * 8 + g][kk + q] - ma[i] : 0.0;
 #pragma unroll
-      for (int j = 0; j < 4; j++) b[j] = Bp[wn + j * 8 + g][kk + q];
+      for (int j = 0; j < 4; j++) b[j] = live ? Bp[wn + j * 8 + g][kk + q] - mb[j] : 0.0;
 #pragma unroll
       for (int i = 0; i < 4; i++)
 #pragma unroll
         for (int j = 0; j < 4; j++) dmma_m8n8k4(acc[i][j][0], acc[i][j][1], a[i], b[j]);
     }
-    __syncthreads();
   }
+  cp_async_wait<0>();
 
   double *out = partial + (size_t)split * p * p;
 #pragma unroll
