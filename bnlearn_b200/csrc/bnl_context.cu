@@ -91,13 +91,57 @@ extern "C" int bnl_init(bnl_ctx **out, const int *devices, int ndev) {
   return BNL_OK;
 }
 
+// Released data-set blocks are kept (a few, bounded) and handed out again to the
+// next registration of a similar size instead of going through cudaFree/cudaMalloc.
+static const size_t kPoolBlocks = 6;
+static const size_t kPoolBytes = 24ull << 30;
+
+int bnl_pool_alloc(bnl_ctx *ctx, BnlDevice &dev, void **p, size_t bytes) {
+  *p = nullptr;
+  if (bytes == 0) return BNL_OK;
+  int best = -1;
+  for (size_t i = 0; i < dev.pool.size(); i++)
+    if (dev.pool[i].second >= bytes && dev.pool[i].second <= bytes + bytes / 4 + 4096 &&
+        (best < 0 || dev.pool[i].second < dev.pool[best].second))
+      best = (int)i;
+  if (best >= 0) {
+    *p = dev.pool[best].first;
+    dev.pool.erase(dev.pool.begin() + best);
+    return BNL_OK;
+  }
+  cudaError_t e = cudaMalloc(p, bytes);
+  if (e != cudaSuccess) {
+    // give cached blocks back and retry once.
+    for (auto &b : dev.pool) cudaFree(b.first);
+    dev.pool.clear();
+    e = cudaMalloc(p, bytes);
+  }
+  if (e != cudaSuccess)
+    return bnl_fail(ctx, BNL_ENOMEM, "cudaMalloc of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+  return BNL_OK;
+}
+
+void bnl_pool_free(BnlDevice &dev, void *p, size_t bytes) {
+  if (!p) return;
+  dev.pool.push_back(std::make_pair(p, bytes));
+  size_t total = 0;
+  for (auto &b : dev.pool) total += b.second;
+  while (dev.pool.size() > kPoolBlocks || total > kPoolBytes) {
+    total -= dev.pool.front().second;
+    cudaFree(dev.pool.front().first);
+    dev.pool.erase(dev.pool.begin());
+  }
+}
+
 static void free_dataset(bnl_ctx *ctx, BnlDataSet &ds) {
   for (size_t i = 0; i < ds.dev.size(); i++) {
     cudaSetDevice(ctx->devs[i].id);
-    cudaFree(ds.dev[i].u8);
-    cudaFree(ds.dev[i].f64);
-    cudaFree(ds.dev[i].mean);
-    cudaFree(ds.dev[i].cov);
+    BnlDeviceData &d = ds.dev[i];
+    bnl_pool_free(ctx->devs[i], d.u8, d.u8_bytes);
+    bnl_pool_free(ctx->devs[i], d.f64, d.f64_bytes);
+    bnl_pool_free(ctx->devs[i], d.mean, d.mean_bytes);
+    bnl_pool_free(ctx->devs[i], d.cov, d.cov_bytes);
+    d = BnlDeviceData();
   }
   ds.dev.clear();
 }
@@ -107,6 +151,9 @@ extern "C" void bnl_shutdown(bnl_ctx *ctx) {
   for (auto &kv : ctx->data) free_dataset(ctx, kv.second);
   for (auto &d : ctx->devs) {
     cudaSetDevice(d.id);
+    for (auto &b : d.pool) cudaFree(b.first);
+    d.pool.clear();
+    cudaFree(d.stage); cudaFree(d.d_flags);
     cudaFree(d.d_units); cudaFree(d.d_tables); cudaFree(d.d_out); cudaFree(d.d_gidx); cudaFree(d.d_order);
     cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_gidx); cudaFreeHost(d.h_order);
     if (d.ev0) cudaEventDestroy(d.ev0);
@@ -172,7 +219,6 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
   int *stage = nullptr, *d_bad = nullptr;
   int rc = BNL_OK;
   auto cleanup = [&](int code) {
-    cudaFree(stage); cudaFree(d_bad);
     if (code != BNL_OK) free_dataset(ctx, ds);
     return code;
   };
@@ -185,14 +231,18 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
   } while (0)
 
   if (ds.nd > 0) {
-    REG_CUDA(cudaMalloc((void **)&dd0.u8, ds.stride_u8 * ds.nd));
+    dd0.u8_bytes = ds.stride_u8 * ds.nd;
+    if ((rc = bnl_pool_alloc(ctx, d0, (void **)&dd0.u8, dd0.u8_bytes))) return cleanup(rc);
     REG_CUDA(cudaMemsetAsync(dd0.u8, BNL_NA_U8, ds.stride_u8 * ds.nd, d0.stream));
-    REG_CUDA(cudaMalloc((void **)&stage, ((size_t)nobs + 4) * sizeof(int)));
-    REG_CUDA(cudaMalloc((void **)&d_bad, (size_t)(1 + ds.nd) * sizeof(int)));
+    if ((rc = bnl_reserve_device(ctx, &d0.stage, &d0.stage_cap, (size_t)nobs + 4))) return cleanup(rc);
+    if ((rc = bnl_reserve_device(ctx, &d0.d_flags, &d0.flags_cap, (size_t)(1 + ds.nd)))) return cleanup(rc);
+    stage = d0.stage;
+    d_bad = d0.d_flags;
     REG_CUDA(cudaMemsetAsync(d_bad, 0, (size_t)(1 + ds.nd) * sizeof(int), d0.stream));
   }
   if (ds.nc > 0) {
-    REG_CUDA(cudaMalloc((void **)&dd0.f64, ds.stride_f64 * ds.nc * sizeof(double)));
+    dd0.f64_bytes = ds.stride_f64 * ds.nc * sizeof(double);
+    if ((rc = bnl_pool_alloc(ctx, d0, (void **)&dd0.f64, dd0.f64_bytes))) return cleanup(rc);
     REG_CUDA(cudaMemsetAsync(dd0.f64, 0, ds.stride_f64 * ds.nc * sizeof(double), d0.stream));
   }
   for (int i = 0; i < ncols; i++) {
@@ -232,11 +282,13 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
     BnlDeviceData &ddi = ds.dev[i];
     REG_CUDA(cudaSetDevice(di.id));
     if (ds.nd > 0) {
-      REG_CUDA(cudaMalloc((void **)&ddi.u8, ds.stride_u8 * ds.nd));
+      ddi.u8_bytes = dd0.u8_bytes;
+      if ((rc = bnl_pool_alloc(ctx, di, (void **)&ddi.u8, ddi.u8_bytes))) return cleanup(rc);
       REG_CUDA(cudaMemcpyPeerAsync(ddi.u8, di.id, dd0.u8, d0.id, ds.stride_u8 * ds.nd, di.stream));
     }
     if (ds.nc > 0) {
-      REG_CUDA(cudaMalloc((void **)&ddi.f64, ds.stride_f64 * ds.nc * sizeof(double)));
+      ddi.f64_bytes = dd0.f64_bytes;
+      if ((rc = bnl_pool_alloc(ctx, di, (void **)&ddi.f64, ddi.f64_bytes))) return cleanup(rc);
       REG_CUDA(cudaMemcpyPeerAsync(ddi.f64, di.id, dd0.f64, d0.id,
                                    ds.stride_f64 * ds.nc * sizeof(double), di.stream));
     }

@@ -12,8 +12,11 @@ int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
   BnlDeviceData &dd = ds.dev[di];
   const int p = ds.nc;
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
-  BNL_CUDA(ctx, cudaMalloc((void **)&dd.mean, (size_t)p * sizeof(double)));
-  BNL_CUDA(ctx, cudaMalloc((void **)&dd.cov, (size_t)p * p * sizeof(double)));
+  int prc;
+  dd.mean_bytes = (size_t)p * sizeof(double);
+  dd.cov_bytes = (size_t)p * p * sizeof(double);
+  if ((prc = bnl_pool_alloc(ctx, dev, (void **)&dd.mean, dd.mean_bytes))) return prc;
+  if ((prc = bnl_pool_alloc(ctx, dev, (void **)&dd.cov, dd.cov_bytes))) return prc;
 
   // row slices: enough CTAs for several waves, at least 8192 rows per slice,
   // and at most 512 MiB of partials.
@@ -27,9 +30,8 @@ int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
 
   double *partial = nullptr;
   size_t pbytes = std::max((size_t)nsplit * p * p, (size_t)msplit * p) * sizeof(double);
-  cudaError_t e = cudaMalloc((void **)&partial, pbytes);
-  if (e != cudaSuccess)
-    return bnl_fail(ctx, BNL_ENOMEM, "cudaMalloc of %zu bytes for the Gram partials failed", pbytes);
+  if ((prc = bnl_pool_alloc(ctx, dev, (void **)&partial, pbytes))) return prc;
+  cudaError_t e;
 
   cudaEventRecord(dev.evc0, dev.stream);
   col_sum_kernel<<<dim3(p, (unsigned)msplit), 256, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, p, partial);
@@ -43,7 +45,7 @@ int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
   cudaEventRecord(dev.evc1, dev.stream);
   e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaStreamSynchronize(dev.stream);
-  cudaFree(partial);
+  bnl_pool_free(dev, partial, pbytes);
   if (e == cudaSuccess && di == 0) {
     // bnl_last_call_profile() after a registration reports the moments kernels.
     float ms = 0.f;

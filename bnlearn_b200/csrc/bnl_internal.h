@@ -42,6 +42,13 @@ struct BnlDevice {
   BnlUnit *h_units = nullptr; size_t h_units_cap = 0;    // pinned
   double *h_out = nullptr; size_t h_out_cap = 0;         // pinned
   int *h_gidx = nullptr; size_t h_gidx_cap = 0;          // pinned
+  // registration scratch (grow-only) and a small cache of released data-set
+  // buffers: cudaMalloc / cudaFree synchronise the device and can cost tens of
+  // milliseconds for hundreds of MB, which would dominate re-registration
+  // (boot.strength registers a fresh data frame per replicate).
+  int *stage = nullptr; size_t stage_cap = 0;            // one int32 column
+  int *d_flags = nullptr; size_t flags_cap = 0;          // bad-code flag + per-column NA flags
+  std::vector<std::pair<void *, size_t>> pool;           // released blocks (pointer, bytes)
   int sm_count = 148;
   int max_smem = 48 * 1024;
   bool attr_done = false;   // per-device kernel attributes set
@@ -54,6 +61,7 @@ struct BnlDeviceData {
   double *f64 = nullptr;       // nc columns, stride_f64 doubles apart
   double *mean = nullptr;      // nc
   double *cov = nullptr;       // nc x nc, column-major, divisor nobs - 1
+  size_t u8_bytes = 0, f64_bytes = 0, mean_bytes = 0, cov_bytes = 0;
 };
 
 struct BnlDataSet {
@@ -115,6 +123,10 @@ int bnl_reserve_pinned(bnl_ctx *ctx, T **p, size_t *cap, size_t need) {
   *cap = want;
   return BNL_OK;
 }
+
+// pooled device blocks (bnl_context.cu).
+int bnl_pool_alloc(bnl_ctx *ctx, BnlDevice &dev, void **p, size_t bytes);
+void bnl_pool_free(BnlDevice &dev, void *p, size_t bytes);
 
 // defined in bnl_gaussian.cu: forms means and the covariance matrix on a device.
 int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int dev_index);
