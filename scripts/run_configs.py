@@ -1,0 +1,122 @@
+#!/usr/bin/env python
+"""Wall-clock runs of the BASELINE.json configurations through the restated
+search loops (bnlearn_b200/learners.py) on the CUDA engine, next to the same
+loops driven by the reference's own C entry points (oracle/_ref) on one host
+core -- the reference has no parallel mode for hc/tabu and its cluster mode for
+pc.stable splits node pairs over R workers (R/pcalgo.R:24-28), which the
+forked CPU leg of bench.py measures. Results (JSON) go to stdout / --out.
+
+    python scripts/run_configs.py --configs A,B,E [--rows-b 10000000] [--out profiles/x.json]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from bnlearn_b200 import Engine, learners, synth  # noqa: E402
+
+
+def load_golden(name):
+    z = np.load(os.path.join(ROOT, "tests", "golden", "data_%s.npz" % name))
+    return [np.ascontiguousarray(c) for c in z["codes"].astype(np.int32) + 1], [int(v) for v in z["nlevels"]]
+
+
+def timed(fn):
+    t0 = time.perf_counter()
+    out = fn()
+    return out, time.perf_counter() - t0
+
+
+def config_a(eng, with_ref):
+    cols, lev = load_golden("alarm")
+    n = len(cols[0])
+    k = np.log(n) / 2
+    ds, t_reg = timed(lambda: eng.register(cols, lev))
+    be = learners.GpuBackend(ds)
+    (amat, scores), t = timed(lambda: learners.hc(be, len(cols), "bic", k))
+    rec = {"config": "A: hc + BIC, bundled alarm (37 x 20000)", "gpu_wall_s": t, "register_s": t_reg,
+           "arcs": int(amat.sum()), "score": float(scores.sum()), "ntests": be.counter.value,
+           "deltas_per_sec": be.counter.value / t}
+    ds.release()
+    if with_ref:
+        from refbackend import RefBackend
+        rb = RefBackend(cols, lev)
+        (amat2, scores2), t2 = timed(lambda: learners.hc(rb, len(cols), "bic", k))
+        rec.update(ref_wall_s=t2, identical_graph=bool(np.array_equal(amat, amat2)),
+                   identical_ntests=bool(rb.counter.value == be.counter.value))
+    return rec
+
+
+def config_b(eng, rows, with_ref):
+    names, cols, lev = synth.alarm_shaped(rows)
+    ds, t_reg = timed(lambda: eng.register(cols, lev))
+    be = learners.GpuBackend(ds)
+    (skel, dsep, pv), t = timed(lambda: learners.pc_stable(be, len(cols), "mi", 0.05))
+    rec = {"config": "B: pc.stable + mi, alarm-shaped (37 x %d)" % rows, "gpu_wall_s": t,
+           "register_s": t_reg, "edges": len(skel), "ntests": be.counter.value,
+           "tests_per_sec": be.counter.value / t}
+    ds.release()
+    if with_ref:
+        from refbackend import RefBackend
+        rb = RefBackend(cols, lev)
+        (skel2, dsep2, _), t2 = timed(lambda: learners.pc_stable(rb, len(cols), "mi", 0.05))
+        rec.update(ref_wall_s=t2, identical_skeleton=bool(skel == skel2), identical_dsep=bool(dsep == dsep2),
+                   identical_ntests=bool(rb.counter.value == be.counter.value))
+    return rec
+
+
+def config_e(eng, replicates, with_ref):
+    names, cols, lev = synth.insurance_shaped(20000)
+    (res, t) = timed(lambda: learners.boot_strength(eng, cols, lev, replicates, "bde", 1.0, seed=20261109))
+    strength, direction, tests = res
+    rec = {"config": "E: boot.strength R=%d x hc(bde), insurance-shaped (27 x 20000), 1 GPU" % replicates,
+           "gpu_wall_s": t, "replicates_per_sec": replicates / t, "ntests": tests,
+           "arcs_with_strength_over_0.85": int((strength > 0.85).sum() // 2)}
+    if with_ref:
+        from refbackend import RefBackend
+        rng = np.random.Generator(np.random.PCG64(20261109))
+        rows = rng.integers(0, 20000, 20000)
+        sub = [c[rows] for c in cols]
+        ds = eng.register(sub, lev)
+        be = learners.GpuBackend(ds)
+        a1, _ = learners.hc(be, len(cols), "bde", 1.0)
+        rb = RefBackend(sub, lev)
+        (a2, _), t2 = timed(lambda: learners.hc(rb, len(cols), "bde", 1.0))
+        rec.update(ref_wall_s_per_replicate=t2, identical_graph_replicate0=bool(np.array_equal(a1, a2)),
+                   identical_ntests_replicate0=bool(rb.counter.value == be.counter.value))
+        ds.release()
+    return rec
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", default="A,B,E")
+    ap.add_argument("--rows-b", type=int, default=10_000_000)
+    ap.add_argument("--replicates", type=int, default=256)
+    ap.add_argument("--no-ref", action="store_true")
+    ap.add_argument("--out", default=None)
+    args = ap.parse_args()
+    out = []
+    with Engine() as eng:
+        for c in args.configs.split(","):
+            if c == "A":
+                out.append(config_a(eng, not args.no_ref))
+            elif c == "B":
+                out.append(config_b(eng, args.rows_b, not args.no_ref))
+            elif c == "E":
+                out.append(config_e(eng, args.replicates, not args.no_ref))
+            print(json.dumps(out[-1]), flush=True)
+    if args.out:
+        with open(args.out, "w") as f:
+            json.dump(out, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()
