@@ -73,10 +73,13 @@ struct GRequest {
   int code;
   double arg;
   int n, kmax;
-  std::vector<int> gidx; // n * BNL_GW
+  const int *a, *b;      // x[] and y[] (tests) or target[] (scores; b unused)
+  const int *off, *idx;  // CSR conditioning sets / parents
   double *o0, *o1, *o2;
 };
 
+// Units [b, e) on device slot d: the caller's arrays go to the device as they
+// are (no per-unit descriptor is built on the host).
 int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, BnlTiming *tm) {
   BnlDevice &dev = ctx->devs[d];
   BnlDeviceData &dd = ds.dev[d];
@@ -89,15 +92,22 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
     dev.gattr_done = true;
   }
   const int cnt = e - b;
+  const int i0 = rq.off[b], nidx = rq.off[e] - i0;
+  // device layout of the staged inputs: a | b | off (cnt + 1) | idx | slot map | err
+  const size_t n_a = cnt, n_b = rq.kind == 0 ? cnt : 0, n_off = (size_t)cnt + 1, n_idx = nidx;
+  const size_t total = n_a + n_b + n_off + n_idx + ds.ncols + 1;
   int rc;
-  if ((rc = bnl_reserve_pinned(ctx, &dev.h_gidx, &dev.h_gidx_cap, (size_t)cnt * BNL_GW))) return rc;
-  if ((rc = bnl_reserve_device(ctx, &dev.d_gidx, &dev.gidx_cap, (size_t)cnt * BNL_GW))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_gidx, &dev.gidx_cap, total))) return rc;
+  if ((rc = bnl_reserve_pinned(ctx, &dev.h_gidx, &dev.h_gidx_cap, n_off + ds.ncols + 1))) return rc;
   if ((rc = bnl_reserve_device(ctx, &dev.d_out, &dev.out_cap, (size_t)cnt * 4))) return rc;
   if ((rc = bnl_reserve_pinned(ctx, &dev.h_out, &dev.h_out_cap, (size_t)cnt * 4))) return rc;
-  memcpy(dev.h_gidx, rq.gidx.data() + (size_t)b * BNL_GW, (size_t)cnt * BNL_GW * sizeof(int));
+  int *d_a = dev.d_gidx, *d_b = d_a + n_a, *d_off = d_b + n_b, *d_idx = d_off + n_off;
+  int *d_slot = d_idx + n_idx, *d_err = d_slot + ds.ncols;
+  // offsets rebased to this block; slot map; cleared error flag.
+  for (int i = 0; i <= cnt; i++) dev.h_gidx[i] = rq.off[b + i] - i0;
+  for (int c = 0; c < ds.ncols; c++) dev.h_gidx[n_off + c] = ds.is_numeric[c] ? ds.slot[c] : -1;
+  dev.h_gidx[n_off + ds.ncols] = 0;
 
-  // threads per CTA: as many as the per-thread work matrices allow (tests need
-  // A and V, scores one matrix), between 32 and 128.
   const int mats = rq.kind == 0 ? 2 : 1;
   const size_t per_thread = (size_t)mats * rq.kmax * rq.kmax * sizeof(double);
   int tpb = 128;
@@ -107,23 +117,34 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "unit with %d columns needs too much shared memory", rq.kmax);
 
   BNL_CUDA(ctx, cudaEventRecord(dev.ev0, dev.stream));
-  BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_gidx, dev.h_gidx, (size_t)cnt * BNL_GW * sizeof(int),
+  BNL_CUDA(ctx, cudaMemcpyAsync(d_a, rq.a + b, n_a * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+  if (n_b)
+    BNL_CUDA(ctx, cudaMemcpyAsync(d_b, rq.b + b, n_b * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+  BNL_CUDA(ctx, cudaMemcpyAsync(d_off, dev.h_gidx, n_off * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+  if (n_idx)
+    BNL_CUDA(ctx, cudaMemcpyAsync(d_idx, rq.idx + i0, n_idx * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+  BNL_CUDA(ctx, cudaMemcpyAsync(d_slot, dev.h_gidx + n_off, (size_t)(ds.ncols + 1) * sizeof(int),
                                 cudaMemcpyHostToDevice, dev.stream));
   const int grid = (cnt + tpb - 1) / tpb;
   BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
   if (rq.kind == 0)
-    gauss_ci_kernel<<<grid, tpb, smem, dev.stream>>>(dev.d_gidx, cnt, dd.cov, ds.nc, ds.nobs, rq.code,
-                                                     rq.kmax, dev.d_out);
+    gauss_ci_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_b, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, ds.nc,
+                                                     ds.nobs, rq.code, rq.kmax, dev.d_out, d_err);
   else
-    gauss_score_kernel<<<grid, tpb, smem, dev.stream>>>(dev.d_gidx, cnt, dd.cov, dd.mean, ds.nc, ds.nobs,
-                                                        rq.code, rq.arg, rq.kmax, dev.d_out);
+    gauss_score_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, dd.mean,
+                                                        ds.nc, ds.nobs, rq.code, rq.arg, rq.kmax, dev.d_out, d_err);
   BNL_CUDA(ctx, cudaGetLastError());
   tm->launches++;
   BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
   BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)cnt * 4 * sizeof(double),
                                 cudaMemcpyDeviceToHost, dev.stream));
+  int err = 0;
+  BNL_CUDA(ctx, cudaMemcpyAsync(&err, d_err, sizeof(int), cudaMemcpyDeviceToHost, dev.stream));
   BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
   BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+  if (err)
+    return bnl_fail(ctx, BNL_EINVAL, "unit %d refers to a column that is out of range or not numeric",
+                    b + err - 1);
   for (int i = 0; i < cnt; i++) {
     if (rq.o0) rq.o0[b + i] = dev.h_out[4 * i + 0];
     if (rq.o1) rq.o1[b + i] = dev.h_out[4 * i + 1];
@@ -139,6 +160,17 @@ int run_grequest(bnl_ctx *ctx, BnlDataSet &ds, GRequest &rq) {
   ctx->last_ms = ctx->last_count_ms = ctx->last_epi_ms = 0.0;
   ctx->last_launches = 0;
   if (rq.n == 0) return BNL_OK;
+  // widest unit (sizes the per-thread work matrices) and a sanity check of the CSR.
+  const int extra = rq.kind == 0 ? 2 : 1;
+  rq.kmax = extra;
+  for (int u = 0; u < rq.n; u++) {
+    const int k = rq.off[u + 1] - rq.off[u];
+    if (k < 0) return bnl_fail(ctx, BNL_EINVAL, "offsets must be non-decreasing (unit %d)", u);
+    if (k + extra > BNL_MAXK)
+      return bnl_fail(ctx, BNL_EUNSUPPORTED, "a unit may involve at most %d columns (got %d)", BNL_MAXK, k + extra);
+    rq.kmax = std::max(rq.kmax, k + extra);
+  }
+  if (rq.off[rq.n] > 0 && !rq.idx) return bnl_fail(ctx, BNL_EINVAL, "index array missing");
   std::vector<int> rcs(ndev, BNL_OK);
   std::vector<BnlTiming> tm(ndev);
   if (ndev == 1) {
@@ -164,30 +196,6 @@ int run_grequest(bnl_ctx *ctx, BnlDataSet &ds, GRequest &rq) {
   return BNL_OK;
 }
 
-int fill_gunit(bnl_ctx *ctx, const BnlDataSet &ds, int *g, int a, int b, const int *rest, int nrest, int *kmax) {
-  const int k = (b >= 0 ? 2 : 1) + nrest;
-  if (k > BNL_MAXK)
-    return bnl_fail(ctx, BNL_EUNSUPPORTED, "a unit may involve at most %d columns (got %d)", BNL_MAXK, k);
-  auto slot = [&](int c) { return (c >= 0 && c < ds.ncols && ds.is_numeric[c]) ? ds.slot[c] : -1; };
-  int pos = 0;
-  g[pos++] = k;
-  int s = slot(a);
-  if (s < 0) return bnl_fail(ctx, BNL_EINVAL, "column %d: out of range or not numeric", a);
-  g[pos++] = s;
-  if (b >= 0) {
-    s = slot(b);
-    if (s < 0) return bnl_fail(ctx, BNL_EINVAL, "column %d: out of range or not numeric", b);
-    g[pos++] = s;
-  }
-  for (int j = 0; j < nrest; j++) {
-    s = slot(rest[j]);
-    if (s < 0) return bnl_fail(ctx, BNL_EINVAL, "column %d: out of range or not numeric", rest[j]);
-    g[pos++] = s;
-  }
-  *kmax = std::max(*kmax, k);
-  return BNL_OK;
-}
-
 }  // namespace
 
 extern "C" int bnl_ci_gaussian(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x,
@@ -201,13 +209,8 @@ extern "C" int bnl_ci_gaussian(bnl_ctx *ctx, bnl_data data, int test_e, int n, c
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a Gaussian test handled here", test_e);
   if (n < 0 || (n > 0 && (!x || !y || !z_off)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_gaussian: bad arguments");
-  GRequest rq{0, test_e, 0.0, n, 2, {}, stat, df, pvalue};
-  rq.gidx.assign((size_t)n * BNL_GW, 0);
-  for (int u = 0; u < n; u++) {
-    int rc = fill_gunit(ctx, ds, &rq.gidx[(size_t)u * BNL_GW], x[u], y[u],
-                        z_idx ? z_idx + z_off[u] : nullptr, z_off[u + 1] - z_off[u], &rq.kmax);
-    if (rc) return rc;
-  }
+  if (ds.nc == 0) return bnl_fail(ctx, BNL_EINVAL, "the data set has no numeric columns");
+  GRequest rq{0, test_e, 0.0, n, 2, x, y, z_off, z_idx, stat, df, pvalue};
   return run_grequest(ctx, ds, rq);
 }
 
@@ -222,13 +225,8 @@ extern "C" int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, doub
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a Gaussian score handled here", score_e);
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_gaussian: bad arguments");
-  GRequest rq{1, score_e, k, n, 1, {}, score, nparams, nullptr};
-  rq.gidx.assign((size_t)n * BNL_GW, 0);
-  for (int u = 0; u < n; u++) {
-    int rc = fill_gunit(ctx, ds, &rq.gidx[(size_t)u * BNL_GW], target[u], -1,
-                        pa_idx ? pa_idx + pa_off[u] : nullptr, pa_off[u + 1] - pa_off[u], &rq.kmax);
-    if (rc) return rc;
-  }
+  if (ds.nc == 0) return bnl_fail(ctx, BNL_EINVAL, "the data set has no numeric columns");
+  GRequest rq{1, score_e, k, n, 1, target, nullptr, pa_off, pa_idx, score, nparams, nullptr};
   return run_grequest(ctx, ds, rq);
 }
 

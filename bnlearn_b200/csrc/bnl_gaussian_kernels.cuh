@@ -247,17 +247,31 @@ __device__ void jacobi_eigen(SmemMat A, SmemMat V, int k) {
   }
 }
 
-// units: gidx[u * BNL_GW] = k, then k column slots (x, y, z...). out: 4 doubles.
-__global__ void gauss_ci_kernel(const int *__restrict__ gidx, int n, const double *__restrict__ cov,
-                                int p, long long nobs, int test, int kmax,
-                                double *__restrict__ out) {
+// Units arrive exactly as the caller passed them (x[], y[], CSR z): `slot` maps a
+// data-set column to its numeric slot (-1 for factors). A bad column raises *err
+// (1 + unit index) and the unit is skipped. out: 4 doubles per unit.
+__global__ void gauss_ci_kernel(const int *__restrict__ ux, const int *__restrict__ uy,
+                                const int *__restrict__ zoff, const int *__restrict__ zidx,
+                                const int *__restrict__ slot, int ncols, int n,
+                                const double *__restrict__ cov, int p, long long nobs, int test,
+                                int kmax, double *__restrict__ out, int *__restrict__ err) {
   extern __shared__ double gsm[];
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= n) return;
-  const int *d = gidx + (size_t)u * BNL_GW;
-  const int k = d[0], nz = k - 2;
+  const int z0 = zoff[u], nz = zoff[u + 1] - z0, k = nz + 2;
   double *o = out + (size_t)u * 4;
   const double tol = bnl::kSqrtEps;
+  int d[BNL_MAXK + 1];
+  bool bad = k > BNL_MAXK || nz < 0;
+  if (!bad) {
+    for (int i = 0; i < k; i++) {
+      const int c = i == 0 ? ux[u] : (i == 1 ? uy[u] : zidx[z0 + i - 2]);
+      const int sl = (c >= 0 && c < ncols) ? slot[c] : -1;
+      bad |= sl < 0;
+      d[1 + i] = sl;
+    }
+  }
+  if (bad) { atomicCAS(err, 0, u + 1); o[0] = o[1] = o[2] = o[3] = 0.0; return; }
 
   double df = (test == BNL_COR) ? (double)(nobs - nz - 2)
             : (test == BNL_ZF) ? (double)(nobs - nz - 3) : 1.0;
@@ -309,18 +323,31 @@ __global__ void gauss_ci_kernel(const int *__restrict__ gidx, int n, const doubl
   o[0] = stat; o[1] = df; o[2] = pv; o[3] = clamped;
 }
 
-// Gaussian node score from the moments. Unit: gidx = k, target, parents...
+// Gaussian node score from the moments. Unit u: target[u] and the CSR parent list.
 // S(i, j) below is the centred cross-product (n - 1) * cov of the unit's columns.
-__global__ void gauss_score_kernel(const int *__restrict__ gidx, int n, const double *__restrict__ cov,
+__global__ void gauss_score_kernel(const int *__restrict__ target, const int *__restrict__ poff,
+                                   const int *__restrict__ pidx, const int *__restrict__ slot,
+                                   int ncols, int n, const double *__restrict__ cov,
                                    const double *__restrict__ mean, int p, long long nobs,
-                                   int score, double kpen, int kmax, double *__restrict__ out) {
+                                   int score, double kpen, int kmax, double *__restrict__ out,
+                                   int *__restrict__ err) {
   extern __shared__ double gsm[];
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= n) return;
-  const int *d = gidx + (size_t)u * BNL_GW;
-  const int k = d[0], np = k - 1;
+  const int p0 = poff[u], np = poff[u + 1] - p0, k = np + 1;
   double *o = out + (size_t)u * 4;
   const double tol = bnl::kSqrtEps;
+  int d[BNL_MAXK + 1];
+  bool bad = k > BNL_MAXK || np < 0;
+  if (!bad) {
+    for (int i = 0; i < k; i++) {
+      const int c = i == 0 ? target[u] : pidx[p0 + i - 1];
+      const int sl = (c >= 0 && c < ncols) ? slot[c] : -1;
+      bad |= sl < 0;
+      d[1 + i] = sl;
+    }
+  }
+  if (bad) { atomicCAS(err, 0, u + 1); o[0] = o[1] = o[2] = o[3] = 0.0; return; }
   const double nm1 = (double)(nobs - 1);
   auto C = [&](int i, int j) { return cov[(size_t)d[1 + i] + (size_t)d[1 + j] * p]; };
 

@@ -21,6 +21,7 @@ class RefData:
                         for i, c in enumerate(columns)]
         self.nobs = len(self.columns[0]) if self.ncols else 0
         self._df = None
+        self._complete_flags = None
 
     def df(self):
         if self._df is None:
@@ -28,12 +29,15 @@ class RefData:
         return self._df
 
     def complete(self):
-        flags = []
-        for i, c in enumerate(self.columns):
-            if self.nlevels[i] > 0:
-                flags.append(int(not np.any(c == np.iinfo(np.int32).min)))
-            else:
-                flags.append(int(not np.any(np.isnan(c))))
+        if self._complete_flags is None:       # one pass over the data, like check.data() in R
+            flags = []
+            for i, c in enumerate(self.columns):
+                if self.nlevels[i] > 0:
+                    flags.append(int(not np.any(c == np.iinfo(np.int32).min)))
+                else:
+                    flags.append(int(not np.any(np.isnan(c))))
+            self._complete_flags = flags
+        flags = self._complete_flags
         s = rb.lglvec(np.array(flags, dtype=np.int32))
         rb.set_names(s, self.names)
         return s
