@@ -16,7 +16,9 @@ namespace {
 
 bool is_discrete_test(int t) { return t == BNL_MI || t == BNL_MI_ADF || t == BNL_X2 || t == BNL_X2_ADF; }
 bool is_gaussian_test(int t) { return t == BNL_COR || t == BNL_ZF || t == BNL_MI_G; }
-bool is_discrete_score(int s) { return s == BNL_LOGLIK || s == BNL_AIC || s == BNL_BIC || s == BNL_BDE || s == BNL_BDS; }
+bool is_discrete_score(int s) {
+  return s == BNL_LOGLIK || s == BNL_AIC || s == BNL_BIC || s == BNL_BDE || s == BNL_BDS || s == BNL_BDJ || s == BNL_K2;
+}
 
 // one batch of CI tests through the matching kernel path.
 int run_tests(bnl_ctx *ctx, bnl_data data, int test_e, const std::vector<int> &x,

@@ -311,7 +311,7 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
   BnlDataSet *ds = find_data(ctx, data);
   if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   if (score_e != BNL_LOGLIK && score_e != BNL_AIC && score_e != BNL_BIC && score_e != BNL_BDE &&
-      score_e != BNL_BDS)
+      score_e != BNL_BDS && score_e != BNL_BDJ && score_e != BNL_K2)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a discrete score handled here", score_e);
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_discrete: bad arguments");

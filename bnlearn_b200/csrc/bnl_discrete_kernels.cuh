@@ -436,9 +436,16 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   bnl::KahanSum acc;
   double dfacc = 0.0;
   long long nobs = 0;
-  const bool is_bd = kind == 1 && (code == BNL_BDE || code == BNL_BDS);
-  const double alpha = is_bd && q > 0 ? arg / ((double)llx * (double)q) : 1.0;
-  const double aq = is_bd && q > 0 ? arg / (double)q : 1.0;
+  const bool per_cell = kind == 1 && (code == BNL_BDJ || code == BNL_K2);
+  const bool is_bd = kind == 1 && (code == BNL_BDE || code == BNL_BDS || per_cell);
+  // BDe / BDs: alpha = iss / (llx q), prior mass iss / q per parent configuration.
+  // BDJ / K2 (per-cell hyperparameter a = 1/2 or 1): alpha = a and a * llx per
+  // configuration -- except that for a node WITHOUT parents the reference uses
+  // llx itself, whatever a is (src/scores/dirichlet.posterior.c:19-25 vs :81-88).
+  const double pc = code == BNL_K2 ? 1.0 : 0.5;
+  double alpha = 1.0, aq = 1.0;
+  if (per_cell) { alpha = pc; aq = U.ncols == 1 ? (double)llx : pc * (double)llx; }
+  else if (is_bd && q > 0) { alpha = arg / ((double)llx * (double)q); aq = arg / (double)q; }
   const double lg_alpha = is_bd ? bnl::lgamma_pos(alpha) : 0.0;
   const double lg_aq = is_bd ? bnl::lgamma_pos(aq) : 0.0;
 

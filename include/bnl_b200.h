@@ -51,7 +51,7 @@ enum {
 enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4,
        BNL_COR = 20, BNL_ZF = 21, BNL_MI_G = 22 };
 /* score_e values handled (src/scores/scores.h:9-60). */
-enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7,
+enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
        BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103 };
 
 /* ---- context ---------------------------------------------------------- */
@@ -105,7 +105,9 @@ int bnl_counts(bnl_ctx *ctx, bnl_data data, int n, const int *x, const int *y,
 
 /* Node scores for n (target, parent set) units; parents of unit u are
  * pa_idx[pa_off[u] .. pa_off[u+1]). k_or_iss is the penalty coefficient k for
- * AIC/BIC and the imaginary sample size for BDe/BDs (uniform graph prior).
+ * AIC/BIC and the imaginary sample size for BDe/BDs (uniform graph prior); it is
+ * ignored for BDJ and K2, whose per-cell hyperparameter is fixed (1/2 and 1,
+ * src/scores/per.node.score.c:233-246).
  * nparams may be NULL. Replaces c_per_node_score() for these score_e values
  * (src/scores/per.node.score.c:51-534 -> loglik_dnode,
  * src/scores/discrete.loglikelihood.c:76-118; dirichlet_node,

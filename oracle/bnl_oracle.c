@@ -37,7 +37,7 @@ void minir_f77_dqrsl(double *x, int *ldx, int *n, int *k, double *qraux,
 
 /* test_e (src/tests/tests.h:8-36) and score_e (src/scores/scores.h:9-60). */
 enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_COR = 20, T_ZF = 21, T_MI_G = 22 };
-enum { S_LOGLIK = 1, S_AIC = 3, S_BIC = 4, S_BDE = 6, S_BDS = 7,
+enum { S_LOGLIK = 1, S_AIC = 3, S_BIC = 4, S_BDE = 6, S_BDS = 7, S_BDJ = 8, S_K2 = 9,
        S_LOGLIK_G = 100, S_AIC_G = 102, S_BIC_G = 103 };
 
 /* ------------------------------------------------------------------------
@@ -186,13 +186,17 @@ double orc_score_discrete(int score, const int *x, int llx, const int *const *pa
   double res = 0, npar = 0;
   if (np == 0) {
     int *n = calloc((size_t)llx, sizeof(int));
-    if (score == S_BDE || score == S_BDS) {
+    if (score == S_BDE || score == S_BDS || score == S_BDJ || score == S_K2) {
       /* dpost() does not skip NA: the front end refuses incomplete data. */
       for (int i = 0; i < num; i++) n[x[i] - 1]++;
-      double alpha = arg / llx;
+      /* per-cell scores (K2: 1, BDJ: 1/2; per.node.score.c:233-246): alpha is
+       * the constant and the "imaginary sample size" is llx (:19-25). */
+      int per_cell = (score == S_BDJ || score == S_K2);
+      double imaginary = per_cell ? llx : arg;
+      double alpha = per_cell ? (score == S_K2 ? 1.0 : 0.5) : arg / llx;
       for (int i = 0; i < llx; i++)
         res += Rf_lgammafn(n[i] + alpha) - Rf_lgammafn(alpha);
-      res += Rf_lgammafn(arg) - Rf_lgammafn(arg + num);
+      res += Rf_lgammafn(imaginary) - Rf_lgammafn(imaginary + num);
     } else {
       int nobs = 0;
       for (int i = 0; i < num; i++) if (x[i] != ORC_NA) n[x[i] - 1]++;
@@ -209,7 +213,7 @@ double orc_score_discrete(int score, const int *x, int llx, const int *const *pa
     int lly = (int)nl;
     int *n = calloc((size_t)llx * lly, sizeof(int));      /* n[x][cfg] */
     int *nj = calloc((size_t)lly, sizeof(int));
-    if (score == S_BDE || score == S_BDS) {
+    if (score == S_BDE || score == S_BDS || score == S_BDJ || score == S_K2) {
       for (int i = 0; i < num; i++) {
         n[(size_t)(x[i] - 1) * lly + (cfg[i] - 1)]++;
         nj[cfg[i] - 1]++;
@@ -217,6 +221,11 @@ double orc_score_discrete(int score, const int *x, int llx, const int *const *pa
       int q = lly;
       if (score == S_BDS) { q = 0; for (int j = 0; j < lly; j++) q += nj[j] > 0; }
       double alpha = arg / ((double)llx * q);
+      if (score == S_BDJ || score == S_K2) {
+        /* cdpost() with per_cell: alpha fixed, imaginary = alpha * llx * lly (:81-88). */
+        alpha = (score == S_K2) ? 1.0 : 0.5;
+        arg = alpha * (double)llx * q;
+      }
       for (int i = 0; i < llx; i++)
         for (int j = 0; j < lly; j++) {
           if (score == S_BDS && nj[j] == 0) continue;

@@ -84,7 +84,8 @@ def reference_outputs():
             node, pa = int(idx[0]), [int(i) for i in idx[1:]]
             par = {names[node]: [names[i] for i in pa]}
             for score, kw in (("loglik", {}), ("aic", {"k": 1.0}), ("bic", {"k": np.log(n) / 2}),
-                              ("bde", {"iss": 1.0}), ("bde", {"iss": 10.0}), ("bds", {"iss": 1.0})):
+                              ("bde", {"iss": 1.0}), ("bde", {"iss": 10.0}), ("bds", {"iss": 1.0}),
+                              ("k2", {}), ("bdj", {})):
                 v = ra.per_node_score(data, par, [names[node]], score, **kw)[0]
                 rec["scores"].append({"score": score, "arg": list(kw.values())[0] if kw else 0.0,
                                       "node": node, "parents": pa, "value": float(v)})
