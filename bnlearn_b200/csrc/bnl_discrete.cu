@@ -122,10 +122,13 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     std::vector<int> cls[4];
     int cmax[4] = {0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
-      const int c = dev.h_units[i].cells;
+      BnlUnit &hu = dev.h_units[i];
+      const int c = hu.cells;
       const int k = c <= 256 ? 0 : (c <= mid_cap ? 1 : (c <= lane_cap ? 2 : 3));
+      // tiny tables without NA count row pairs (16 x 16 pair table = 256 slots).
+      hu.mode = (c <= 16 && !hu.has_na && ds.nobs >= 4096) ? 1 : 0;
       cls[k].push_back(i);
-      cmax[k] = std::max(cmax[k], c);
+      cmax[k] = std::max(cmax[k], hu.mode ? 256 : c);
     }
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_order, &dev.h_order_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
@@ -152,7 +155,9 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     if (groups > 0) {
       int base = 0;
       if (!cls[0].empty()) {
-        const int ch = pick_chunks((int)cls[0].size(), 65536);
+        // zeroing and collapsing the lane copies costs cells x 64 words per CTA:
+        // give bigger tables more rows to amortise it over.
+        const int ch = pick_chunks((int)cls[0].size(), cmax[0] > 64 ? 262144 : 65536);
         count_small_kernel<false><<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 256, dev.stream>>>(
             dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[0].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());

@@ -222,6 +222,16 @@ __device__ __forceinline__ void small_rows_scalar(const uint8_t *__restrict__ u8
   }
 }
 
+// Row-pair variant for tables of at most 16 cells: two consecutive rows share one
+// update of a 16 x 16 "pair table" (index = cell_a + 16 * cell_b), which halves
+// the shared-memory atomics -- the resource that bounds this kernel. v | (v >> 4)
+// leaves the pair indices of rows (0,1) and (2,3) in bytes 0 and 2.
+__device__ __forceinline__ void pair_bump(int *hist, unsigned v, unsigned slot4) {
+  const unsigned t = v | (v >> 4);
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(t, slot4, 0x5504)), 1);
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(t, slot4, 0x5524)), 1);
+}
+
 // 16-bit variant of small_bump for tables of 257..880 cells: v holds 2 packed
 // indices; the offset is (index << 8) | slot byte, still one PRMT.
 __device__ __forceinline__ void mid_bump(int *hist, unsigned v, unsigned slot4) {
@@ -229,7 +239,7 @@ __device__ __forceinline__ void mid_bump(int *hist, unsigned v, unsigned slot4) 
   atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + __byte_perm(v, slot4, 0x5324)), 1);
 }
 
-template <int NC, bool NA, bool W16>
+template <int NC, bool NA, bool W16, bool PAIR>
 __device__ __forceinline__ void small_rows(const uint8_t *__restrict__ u8, size_t stride,
                                            const BnlUnit &su, int *hist, unsigned slot4,
                                            long long g0, long long g1) {
@@ -259,10 +269,17 @@ __device__ __forceinline__ void small_rows(const uint8_t *__restrict__ u8, size_
       for (int k = 1; k < NC; k++) {
         v.x += w[k].x * m[k]; v.y += w[k].y * m[k]; v.z += w[k].z * m[k]; v.w += w[k].w * m[k];
       }
-      small_bump(hist, v.x, slot4);
-      small_bump(hist, v.y, slot4);
-      small_bump(hist, v.z, slot4);
-      small_bump(hist, v.w, slot4);
+      if (PAIR) {
+        pair_bump(hist, v.x, slot4);
+        pair_bump(hist, v.y, slot4);
+        pair_bump(hist, v.z, slot4);
+        pair_bump(hist, v.w, slot4);
+      } else {
+        small_bump(hist, v.x, slot4);
+        small_bump(hist, v.y, slot4);
+        small_bump(hist, v.z, slot4);
+        small_bump(hist, v.w, slot4);
+      }
     } else {
       unsigned v[8];
       const unsigned w0[4] = {w[0].x, w[0].y, w[0].z, w[0].w};
@@ -287,7 +304,7 @@ __device__ __forceinline__ void small_rows(const uint8_t *__restrict__ u8, size_
 }
 
 // generic column count (> 4 columns).
-template <bool NA, bool W16>
+template <bool NA, bool W16, bool PAIR>
 __device__ __forceinline__ void small_rows_any(const uint8_t *__restrict__ u8, size_t stride,
                                                const BnlUnit &su, int *hist, unsigned slot4,
                                                long long g0, long long g1) {
@@ -318,21 +335,23 @@ __device__ __forceinline__ void small_rows_any(const uint8_t *__restrict__ u8, s
     }
 #pragma unroll
     for (int j = 0; j < (W16 ? 8 : 4); j++) {
-      if (W16) mid_bump(hist, v[j], slot4); else small_bump(hist, v[j], slot4);
+      if (W16) mid_bump(hist, v[j], slot4);
+      else if (PAIR) pair_bump(hist, v[j], slot4);
+      else small_bump(hist, v[j], slot4);
     }
   }
 }
 
-template <bool NA, bool W16>
+template <bool NA, bool W16, bool PAIR>
 __device__ __forceinline__ void small_dispatch(const uint8_t *__restrict__ u8, size_t stride,
                                                const BnlUnit &su, int *hist, unsigned slot4,
                                                long long g0, long long g1) {
   switch (su.ncols) {
-    case 1: small_rows<1, NA, W16>(u8, stride, su, hist, slot4, g0, g1); break;
-    case 2: small_rows<2, NA, W16>(u8, stride, su, hist, slot4, g0, g1); break;
-    case 3: small_rows<3, NA, W16>(u8, stride, su, hist, slot4, g0, g1); break;
-    case 4: small_rows<4, NA, W16>(u8, stride, su, hist, slot4, g0, g1); break;
-    default: small_rows_any<NA, W16>(u8, stride, su, hist, slot4, g0, g1);
+    case 1: small_rows<1, NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1); break;
+    case 2: small_rows<2, NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1); break;
+    case 3: small_rows<3, NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1); break;
+    case 4: small_rows<4, NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1); break;
+    default: small_rows_any<NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1);
   }
 }
 
@@ -350,7 +369,9 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
   __syncthreads();
   const int cells = su.cells;
-  for (int c = threadIdx.x; c < cells * 64; c += blockDim.x) hist[c] = 0;
+  const bool pair = !W16 && su.mode == 1;            // pair table: 256 entries whatever `cells`
+  const int slots = pair ? 256 : cells;
+  for (int c = threadIdx.x; c < slots * 64; c += blockDim.x) hist[c] = 0;
   __syncthreads();
   const unsigned slot4 = ((threadIdx.x & 31u) + 32u * ((threadIdx.x >> 5) & 1u)) << 2;
 
@@ -359,19 +380,47 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   const long long g0 = per * chunk;
   long long g1 = g0 + per;
   if (g1 > full) g1 = full;
+  int *gtab = tables + su.table_off;
 
-  if (su.has_na) small_dispatch<true, W16>(u8, stride, su, hist, slot4, g0, g1);
-  else small_dispatch<false, W16>(u8, stride, su, hist, slot4, g0, g1);
-  // the partial group at the end of the data, once.
-  if (chunk == chunks - 1 && threadIdx.x == 0 && full * 16 < nobs)
-    small_rows_scalar(u8, stride, su, hist, slot4, full * 16, (int)(nobs - full * 16));
+  if (pair) small_dispatch<false, false, true>(u8, stride, su, hist, slot4, g0, g1);
+  else if (su.has_na) small_dispatch<true, W16, false>(u8, stride, su, hist, slot4, g0, g1);
+  else small_dispatch<false, W16, false>(u8, stride, su, hist, slot4, g0, g1);
+  // the partial group at the end of the data, once (pair mode: straight into the
+  // global table, its shared table does not hold single rows).
+  if (chunk == chunks - 1 && threadIdx.x == 0 && full * 16 < nobs) {
+    if (pair) {
+      for (long long r = full * 16; r < nobs; r++) {
+        int cell = 0;
+        for (int k = 0; k < su.ncols; k++) cell += (int)u8[(size_t)su.col[k] * stride + (size_t)r] * su.mul[k];
+        atomicAdd(&gtab[cell], 1);
+      }
+    } else {
+      small_rows_scalar(u8, stride, su, hist, slot4, full * 16, (int)(nobs - full * 16));
+    }
+  }
 
   __syncthreads();
-  int *gtab = tables + su.table_off;
-  for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+  if (!pair) {
+    for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+      int sum = 0;
+#pragma unroll
+      for (int l = 0; l < 64; l++) sum += hist[c * 64 + ((l + threadIdx.x) & 63)];
+      if (sum) atomicAdd(&gtab[c], sum);
+    }
+    return;
+  }
+  // pair mode: collapse the lane copies, then each row of a pair adds its margin.
+  __shared__ int psum[256];
+  for (int c = threadIdx.x; c < 256; c += blockDim.x) {
     int sum = 0;
 #pragma unroll
     for (int l = 0; l < 64; l++) sum += hist[c * 64 + ((l + threadIdx.x) & 63)];
+    psum[c] = sum;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+    int sum = 0;
+    for (int o = 0; o < 16; o++) sum += psum[c + 16 * o] + psum[o + 16 * c];
     if (sum) atomicAdd(&gtab[c], sum);
   }
 }

@@ -22,6 +22,8 @@ struct BnlUnit {
   int ncols;              // columns involved
   int llx, lly, llz;      // table is n[z][x][y]
   int has_na;             // some involved column holds an NA
+  int mode;               // 1: count ROW PAIRS (tables of <= 16 cells, no NA), see count_small_kernel
+  int pad;
   int col[BNL_MAXK];      // packed-column slot, order: y (if any), x, z_1, z_2, ...
   int mul[BNL_MAXK];      // contribution of each column to the cell index
 };
