@@ -78,16 +78,16 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
   if (!dev.attr_done) {
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_units_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       dev.max_smem - 1024));
+                                       dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       dev.max_smem - 1024));
+                                       dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       dev.max_smem - 1024));
+                                       dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       dev.max_smem - 1024));
+                                       dev.max_smem - 4096));
     dev.attr_done = true;
   }
-  const int smem_cap_cells = (dev.max_smem - 2048) / 4;
+  const int smem_cap_cells = (dev.max_smem - 8192) / 4;
   const long long groups = (ds.nobs + 15) / 16;
   int pos = b;
   while (pos < e) {
@@ -117,8 +117,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     //   M1: <= mid_cap      64 lane counters per cell, 16-bit packed indices (count_small_kernel<true>)
     //   M2: <= lane_cap     32 lane counters per cell, 16-bit packed indices (count_lane_kernel<true>)
     //   L : the rest        one shared (or global) table per CTA             (count_units_kernel)
-    const int mid_cap = (dev.max_smem - 2048) / 256;
-    const int lane_cap = (dev.max_smem - 2048) / 128;
+    const int mid_cap = (dev.max_smem - 8192) / 256;
+    const int lane_cap = (dev.max_smem - 8192) / 128;
     std::vector<int> cls[4];
     int cmax[4] = {0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
