@@ -136,7 +136,22 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       int o = 0;
       for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
     }
-    auto pick_chunks = [&](int nunits, long long rows_per_cta) {
+    // CTAs run chunk-major, so the rows [chunk] of every column a launch touches
+    // should stay in L2 while all its units pass over them: cap the chunk so that
+    // (distinct columns) x (rows per chunk) stays within ~48 MB of the 126 MB L2.
+    std::vector<char> seen(ds.nd);
+    auto distinct_cols = [&](const std::vector<int> &members) {
+      std::fill(seen.begin(), seen.end(), 0);
+      int nd = 0;
+      for (int i : members)
+        for (int k = 0; k < dev.h_units[i].ncols; k++)
+          if (!seen[dev.h_units[i].col[k]]) { seen[dev.h_units[i].col[k]] = 1; nd++; }
+      return std::max(nd, 1);
+    };
+    auto pick_chunks = [&](const std::vector<int> &members, long long rows_per_cta) {
+      const int nunits = (int)members.size();
+      const long long l2_rows = std::max(16384ll, (48ll << 20) / distinct_cols(members));
+      rows_per_cta = std::min(rows_per_cta, l2_rows);
       long long ch = (ds.nobs + rows_per_cta - 1) / rows_per_cta;
       // few units: cut the rows finer so that the machine is full (>= 4096 rows per CTA).
       const long long want = (8ll * dev.sm_count + nunits - 1) / nunits;
@@ -157,7 +172,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       if (!cls[0].empty()) {
         // zeroing and collapsing the lane copies costs cells x 64 words per CTA:
         // give bigger tables more rows to amortise it over.
-        const int ch = pick_chunks((int)cls[0].size(), cmax[0] > 64 ? 262144 : 65536);
+        const int ch = pick_chunks(cls[0], cmax[0] > 64 ? 262144 : 65536);
         count_small_kernel<false><<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 256, dev.stream>>>(
             dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[0].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
@@ -165,7 +180,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       }
       base += (int)cls[0].size();
       if (!cls[1].empty()) {
-        const int ch = pick_chunks((int)cls[1].size(), 262144);
+        const int ch = pick_chunks(cls[1], 262144);
         count_small_kernel<true><<<(unsigned)cls[1].size() * ch, 512, (size_t)cmax[1] * 256, dev.stream>>>(
             dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[1].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
@@ -173,7 +188,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       }
       base += (int)cls[1].size();
       if (!cls[2].empty()) {
-        const int ch = pick_chunks((int)cls[2].size(), 524288);
+        const int ch = pick_chunks(cls[2], 524288);
         count_lane_kernel<true><<<(unsigned)cls[2].size() * ch, BNL_CNT_THREADS, (size_t)cmax[2] * 128, dev.stream>>>(
             dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[2].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());

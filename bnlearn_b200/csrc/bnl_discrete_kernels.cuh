@@ -369,9 +369,16 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
   __syncthreads();
   const int cells = su.cells;
-  const bool pair = !W16 && su.mode == 1;            // pair table: 256 entries whatever `cells`
-  const int slots = pair ? 256 : cells;
-  for (int c = threadIdx.x; c < slots * 64; c += blockDim.x) hist[c] = 0;
+  const bool pair = !W16 && su.mode == 1;            // pair table: slot a + 16 b, a, b < cells
+  if (pair) {
+    // only the cells x cells corner of the 16 x 16 pair table is ever touched.
+    for (int e = threadIdx.x; e < cells * cells * 64; e += blockDim.x) {
+      const int pc = e >> 6, a = pc % cells, b = pc / cells;
+      hist[(a + 16 * b) * 64 + (e & 63)] = 0;
+    }
+  } else {
+    for (int c = threadIdx.x; c < cells * 64; c += blockDim.x) hist[c] = 0;
+  }
   __syncthreads();
   const unsigned slot4 = ((threadIdx.x & 31u) + 32u * ((threadIdx.x >> 5) & 1u)) << 2;
 
@@ -411,7 +418,8 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   }
   // pair mode: collapse the lane copies, then each row of a pair adds its margin.
   __shared__ int psum[256];
-  for (int c = threadIdx.x; c < 256; c += blockDim.x) {
+  for (int e = threadIdx.x; e < cells * cells; e += blockDim.x) {
+    const int c = (e % cells) + 16 * (e / cells);
     int sum = 0;
 #pragma unroll
     for (int l = 0; l < 64; l++) sum += hist[c * 64 + ((l + threadIdx.x) & 63)];
@@ -420,7 +428,7 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   __syncthreads();
   for (int c = threadIdx.x; c < cells; c += blockDim.x) {
     int sum = 0;
-    for (int o = 0; o < 16; o++) sum += psum[c + 16 * o] + psum[o + 16 * c];
+    for (int o = 0; o < cells; o++) sum += psum[c + 16 * o] + psum[o + 16 * c];
     if (sum) atomicAdd(&gtab[c], sum);
   }
 }
