@@ -1,5 +1,6 @@
 // bnl_discrete.cu -- host side of the discrete entry points: unit validation,
 // batching, multi-device dispatch, launches.
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -8,6 +9,17 @@
 #include "bnl_discrete_kernels.cuh"
 
 namespace {
+
+// tuning knobs for experiments (read once): BNL_PAIR=0 disables row-pair
+// counting, BNL_CHUNK_ROWS overrides the rows per CTA of the small-table kernel,
+// BNL_L2_MB the L2 budget of the chunking rule.
+long long env_ll(const char *name, long long dflt) {
+  const char *v = getenv(name);
+  return (v && *v) ? atoll(v) : dflt;
+}
+const long long kKnobPair = env_ll("BNL_PAIR", 1);
+const long long kKnobChunkRows = env_ll("BNL_CHUNK_ROWS", 0);
+const long long kKnobL2MB = env_ll("BNL_L2_MB", 48);
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
 const int kMaxBatchUnits = 1 << 16;
@@ -126,7 +138,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       const int c = hu.cells;
       const int k = c <= 256 ? 0 : (c <= mid_cap ? 1 : (c <= lane_cap ? 2 : 3));
       // tiny tables without NA count row pairs (16 x 16 pair table = 256 slots).
-      hu.mode = (c <= 16 && !hu.has_na && ds.nobs >= 4096) ? 1 : 0;
+      hu.mode = (kKnobPair && c <= 16 && !hu.has_na && ds.nobs >= 4096) ? 1 : 0;
       cls[k].push_back(i);
       cmax[k] = std::max(cmax[k], hu.mode ? 256 : c);
     }
@@ -150,7 +162,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     };
     auto pick_chunks = [&](const std::vector<int> &members, long long rows_per_cta) {
       const int nunits = (int)members.size();
-      const long long l2_rows = std::max(16384ll, (48ll << 20) / distinct_cols(members));
+      const long long l2_rows = std::max(16384ll, (kKnobL2MB << 20) / distinct_cols(members));
       rows_per_cta = std::min(rows_per_cta, l2_rows);
       long long ch = (ds.nobs + rows_per_cta - 1) / rows_per_cta;
       // few units: cut the rows finer so that the machine is full (>= 4096 rows per CTA).
@@ -172,7 +184,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       if (!cls[0].empty()) {
         // zeroing and collapsing the lane copies costs cells x 64 words per CTA:
         // give bigger tables more rows to amortise it over.
-        const int ch = pick_chunks(cls[0], cmax[0] > 64 ? 262144 : 65536);
+        const int ch = pick_chunks(cls[0], kKnobChunkRows ? kKnobChunkRows : (cmax[0] > 64 ? 262144 : 65536));
         count_small_kernel<false><<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 256, dev.stream>>>(
             dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[0].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
