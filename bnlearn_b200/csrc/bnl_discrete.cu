@@ -19,7 +19,7 @@ long long env_ll(const char *name, long long dflt) {
 }
 const long long kKnobPair = env_ll("BNL_PAIR", 1);
 const long long kKnobChunkRows = env_ll("BNL_CHUNK_ROWS", 0);
-const long long kKnobL2MB = env_ll("BNL_L2_MB", 48);
+const long long kKnobL2MB = env_ll("BNL_L2_MB", 192);
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
 const int kMaxBatchUnits = 1 << 16;
@@ -148,26 +148,33 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       int o = 0;
       for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
     }
-    // CTAs run chunk-major, so the rows [chunk] of every column a launch touches
-    // should stay in L2 while all its units pass over them: cap the chunk so that
-    // (distinct columns) x (rows per chunk) stays within ~48 MB of the 126 MB L2.
-    std::vector<char> seen(ds.nd);
-    auto distinct_cols = [&](const std::vector<int> &members) {
-      std::fill(seen.begin(), seen.end(), 0);
-      int nd = 0;
+    // Rows per CTA. Every CTA pays a fixed price (clearing and collapsing its
+    // replicated table), so chunks should be as long as load balance allows: aim
+    // for ~8 waves of CTAs. CTAs run chunk-major, so the rows [chunk] of the
+    // columns that several units share should survive in L2 between their uses;
+    // columns used by a single unit just stream through. The kernels are bound by
+    // shared-memory atomics, not DRAM, so the L2 budget is deliberately loose
+    // (scripts/microbench_c.py).
+    std::vector<unsigned char> uses(ds.nd);
+    auto shared_cols = [&](const std::vector<int> &members) {
+      std::fill(uses.begin(), uses.end(), 0);
       for (int i : members)
-        for (int k = 0; k < dev.h_units[i].ncols; k++)
-          if (!seen[dev.h_units[i].col[k]]) { seen[dev.h_units[i].col[k]] = 1; nd++; }
-      return std::max(nd, 1);
+        for (int k = 0; k < dev.h_units[i].ncols; k++) {
+          unsigned char &u = uses[dev.h_units[i].col[k]];
+          if (u < 2) u++;
+        }
+      int n = 0;
+      for (unsigned char u : uses) n += u >= 2;
+      return std::max(n, 1);
     };
-    auto pick_chunks = [&](const std::vector<int> &members, long long rows_per_cta) {
-      const int nunits = (int)members.size();
-      const long long l2_rows = std::max(16384ll, (kKnobL2MB << 20) / distinct_cols(members));
-      rows_per_cta = std::min(rows_per_cta, l2_rows);
-      long long ch = (ds.nobs + rows_per_cta - 1) / rows_per_cta;
-      // few units: cut the rows finer so that the machine is full (>= 4096 rows per CTA).
-      const long long want = (8ll * dev.sm_count + nunits - 1) / nunits;
-      ch = std::max(ch, want);
+    auto pick_chunks = [&](const std::vector<int> &members, int ctas_per_sm) {
+      const long long nunits = (long long)members.size();
+      const long long want = (8ll * dev.sm_count * ctas_per_sm + nunits - 1) / nunits;
+      long long rows = std::max(16384ll, ds.nobs / std::max(1ll, want));
+      if (kKnobChunkRows) rows = kKnobChunkRows;
+      const long long l2_rows = std::max(16384ll, (kKnobL2MB << 20) / shared_cols(members));
+      rows = std::min(rows, l2_rows);
+      long long ch = (ds.nobs + rows - 1) / rows;
       ch = std::min(ch, std::max(1ll, groups / 256));
       return (int)std::max(1ll, ch);
     };
@@ -182,9 +189,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     if (groups > 0) {
       int base = 0;
       if (!cls[0].empty()) {
-        // zeroing and collapsing the lane copies costs cells x 64 words per CTA:
-        // give bigger tables more rows to amortise it over.
-        const int ch = pick_chunks(cls[0], kKnobChunkRows ? kKnobChunkRows : (cmax[0] > 64 ? 262144 : 65536));
+        const int ch = pick_chunks(cls[0], 3);
         count_small_kernel<false><<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 256, dev.stream>>>(
             dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[0].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
@@ -192,7 +197,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       }
       base += (int)cls[0].size();
       if (!cls[1].empty()) {
-        const int ch = pick_chunks(cls[1], 262144);
+        const int ch = pick_chunks(cls[1], 1);
         count_small_kernel<true><<<(unsigned)cls[1].size() * ch, 512, (size_t)cmax[1] * 256, dev.stream>>>(
             dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[1].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
@@ -200,7 +205,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       }
       base += (int)cls[1].size();
       if (!cls[2].empty()) {
-        const int ch = pick_chunks(cls[2], 524288);
+        const int ch = pick_chunks(cls[2], 1);
         count_lane_kernel<true><<<(unsigned)cls[2].size() * ch, BNL_CNT_THREADS, (size_t)cmax[2] * 128, dev.stream>>>(
             dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[2].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
