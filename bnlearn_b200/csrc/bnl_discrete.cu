@@ -131,22 +131,23 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     //   L : the rest        one shared (or global) table per CTA             (count_units_kernel)
     const int mid_cap = (dev.max_smem - 8192) / 256;
     const int lane_cap = (dev.max_smem - 8192) / 128;
-    std::vector<int> cls[4];
-    int cmax[4] = {0, 0, 0, 0};
+    std::vector<int> cls[5];               // [4]: row-pair units, launched on their own
+    int cmax[5] = {0, 0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
       BnlUnit &hu = dev.h_units[i];
       const int c = hu.cells;
       const int k = c <= 256 ? 0 : (c <= mid_cap ? 1 : (c <= lane_cap ? 2 : 3));
       // tiny tables without NA count row pairs (16 x 16 pair table = 256 slots).
       hu.mode = (kKnobPair && c <= 16 && !hu.has_na && ds.nobs >= 4096) ? 1 : 0;
-      cls[k].push_back(i);
-      cmax[k] = std::max(cmax[k], hu.mode ? 256 : c);
+      const int kk = hu.mode ? 4 : k;
+      cls[kk].push_back(i);
+      cmax[kk] = std::max(cmax[kk], hu.mode ? 256 : c);
     }
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_order, &dev.h_order_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
     {
       int o = 0;
-      for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
+      for (int k = 0; k < 5; k++) for (int i : cls[k]) dev.h_order[o++] = i;
     }
     // Rows per CTA. Every CTA pays a fixed price (clearing and collapsing its
     // replicated table), so chunks should be as long as load balance allows: aim
@@ -212,6 +213,14 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         tm->launches++;
       }
       base += (int)cls[2].size();
+      if (!cls[4].empty()) {
+        const int pbase = base + (int)cls[3].size();
+        const int ch = pick_chunks(cls[4], 3);
+        count_small_kernel<false><<<(unsigned)cls[4].size() * ch, BNL_CNT_THREADS, (size_t)256 * 256, dev.stream>>>(
+            dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + pbase, dev.d_tables, (int)cls[4].size(), ch);
+        BNL_CUDA(ctx, cudaGetLastError());
+        tm->launches++;
+      }
       if (!cls[3].empty()) {
         int smem_cells = 0;
         for (int i : cls[3])
