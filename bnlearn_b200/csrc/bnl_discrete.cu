@@ -20,6 +20,7 @@ long long env_ll(const char *name, long long dflt) {
 const long long kKnobPair = env_ll("BNL_PAIR", 1);
 const long long kKnobChunkRows = env_ll("BNL_CHUNK_ROWS", 0);
 const long long kKnobL2MB = env_ll("BNL_L2_MB", 192);
+const int kKnobMidThreads = (int)env_ll("BNL_MID_THREADS", 1024);
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
 const int kMaxBatchUnits = 1 << 16;
@@ -131,23 +132,34 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     //   L : the rest        one shared (or global) table per CTA             (count_units_kernel)
     const int mid_cap = (dev.max_smem - 8192) / 256;
     const int lane_cap = (dev.max_smem - 8192) / 128;
-    std::vector<int> cls[5];               // [4]: row-pair units, launched on their own
-    int cmax[5] = {0, 0, 0, 0, 0};
+    std::vector<int> cls[4];
+    int cmax[4] = {0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
       BnlUnit &hu = dev.h_units[i];
       const int c = hu.cells;
       const int k = c <= 256 ? 0 : (c <= mid_cap ? 1 : (c <= lane_cap ? 2 : 3));
-      // tiny tables without NA count row pairs (16 x 16 pair table = 256 slots).
-      hu.mode = (kKnobPair && c <= 16 && !hu.has_na && ds.nobs >= 4096) ? 1 : 0;
-      const int kk = hu.mode ? 4 : k;
-      cls[kk].push_back(i);
-      cmax[kk] = std::max(cmax[kk], hu.mode ? 256 : c);
+      hu.mode = 0;
+      cls[k].push_back(i);
+      cmax[k] = std::max(cmax[k], c);
+    }
+    // tiny tables without NA count row pairs (16 x 16 pair table = 256 slots per
+    // CTA). Worth it when they make up most of the small-table launch; a few of
+    // them among bigger tables would only cost an extra launch or extra shared
+    // memory (scripts/microbench_c.py).
+    if (kKnobPair && ds.nobs >= 4096 && !cls[0].empty()) {
+      size_t eligible = 0;
+      for (int i : cls[0]) eligible += dev.h_units[i].cells <= 16 && !dev.h_units[i].has_na;
+      if (eligible * 5 >= cls[0].size() * 4) {
+        for (int i : cls[0])
+          if (dev.h_units[i].cells <= 16 && !dev.h_units[i].has_na) dev.h_units[i].mode = 1;
+        cmax[0] = 256;
+      }
     }
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_order, &dev.h_order_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
     {
       int o = 0;
-      for (int k = 0; k < 5; k++) for (int i : cls[k]) dev.h_order[o++] = i;
+      for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
     }
     // Rows per CTA. Every CTA pays a fixed price (clearing and collapsing its
     // replicated table), so chunks should be as long as load balance allows: aim
@@ -199,7 +211,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       base += (int)cls[0].size();
       if (!cls[1].empty()) {
         const int ch = pick_chunks(cls[1], 1);
-        count_small_kernel<true><<<(unsigned)cls[1].size() * ch, 512, (size_t)cmax[1] * 256, dev.stream>>>(
+        count_small_kernel<true><<<(unsigned)cls[1].size() * ch, kKnobMidThreads, (size_t)cmax[1] * 256, dev.stream>>>(
             dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[1].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
@@ -207,20 +219,12 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       base += (int)cls[1].size();
       if (!cls[2].empty()) {
         const int ch = pick_chunks(cls[2], 1);
-        count_lane_kernel<true><<<(unsigned)cls[2].size() * ch, BNL_CNT_THREADS, (size_t)cmax[2] * 128, dev.stream>>>(
+        count_lane_kernel<true><<<(unsigned)cls[2].size() * ch, kKnobMidThreads, (size_t)cmax[2] * 128, dev.stream>>>(
             dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[2].size(), ch);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
       }
       base += (int)cls[2].size();
-      if (!cls[4].empty()) {
-        const int pbase = base + (int)cls[3].size();
-        const int ch = pick_chunks(cls[4], 3);
-        count_small_kernel<false><<<(unsigned)cls[4].size() * ch, BNL_CNT_THREADS, (size_t)256 * 256, dev.stream>>>(
-            dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + pbase, dev.d_tables, (int)cls[4].size(), ch);
-        BNL_CUDA(ctx, cudaGetLastError());
-        tm->launches++;
-      }
       if (!cls[3].empty()) {
         int smem_cells = 0;
         for (int i : cls[3])

@@ -97,7 +97,7 @@ count_units_kernel(const uint8_t *__restrict__ u8, size_t stride, long long grou
 // arithmetic is one IMAD per column per 4 (or 2) rows. Rows with an NA fall to a
 // scalar path. `order` maps the launch's CTA groups to unit slots.
 template <bool IDX16>
-__global__ void __launch_bounds__(BNL_CNT_THREADS)
+__global__ void __launch_bounds__(1024)
 count_lane_kernel(const uint8_t *__restrict__ u8, size_t stride, long long groups,
                   const BnlUnit *__restrict__ units, const int *__restrict__ order,
                   int *__restrict__ tables, int nunits, int chunks) {
@@ -356,9 +356,9 @@ __device__ __forceinline__ void small_dispatch(const uint8_t *__restrict__ u8, s
 }
 
 // W16 = false: tables <= 256 cells, 256 threads. W16 = true: 257..880 cells (the
-// table fills most of the SM's shared memory, so one CTA of 512 threads per SM).
+// table fills most of the SM's shared memory, so one CTA of 1024 threads per SM).
 template <bool W16>
-__global__ void __launch_bounds__(W16 ? 512 : BNL_CNT_THREADS)
+__global__ void __launch_bounds__(W16 ? 1024 : BNL_CNT_THREADS)
 count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
                    int *__restrict__ tables, int nunits, int chunks) {

@@ -41,8 +41,7 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "child":
         child()
     else:
-        settings = [{}, {"BNL_L2_MB": "96"}, {"BNL_L2_MB": "1000"}, {"BNL_PAIR": "0"},
-                    {"BNL_CHUNK_ROWS": "262144"}, {"BNL_CHUNK_ROWS": "1000000"}]
+        settings = [{}, {"BNL_MID_THREADS": "512"}, {"BNL_MID_THREADS": "256"}]
         for st in settings:
             env = dict(os.environ); env.update(st)
             r = subprocess.run([sys.executable, __file__, "child"], env=env, capture_output=True, text=True)
