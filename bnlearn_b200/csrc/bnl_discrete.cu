@@ -143,13 +143,13 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       cmax[k] = std::max(cmax[k], c);
     }
     // tiny tables without NA count row pairs (16 x 16 pair table = 256 slots per
-    // CTA). Worth it when they make up most of the small-table launch; a few of
+    // CTA). Worth it when they make up at least half of the small-table launch; a few of
     // them among bigger tables would only cost an extra launch or extra shared
     // memory (scripts/microbench_c.py).
     if (kKnobPair && ds.nobs >= 4096 && !cls[0].empty()) {
       size_t eligible = 0;
       for (int i : cls[0]) eligible += dev.h_units[i].cells <= 16 && !dev.h_units[i].has_na;
-      if (eligible * 5 >= cls[0].size() * 4) {
+      if (eligible * 2 >= cls[0].size()) {
         for (int i : cls[0])
           if (dev.h_units[i].cells <= 16 && !dev.h_units[i].has_na) dev.h_units[i].mode = 1;
         cmax[0] = 256;
