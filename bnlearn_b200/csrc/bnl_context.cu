@@ -1,7 +1,11 @@
 // bnl_context.cu -- context, device resources and data-set registration
 // (packing R's int32 factor columns into the uint8 HBM layout).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
+
+#include <atomic>
+#include <thread>
 
 #include "bnl_internal.h"
 
@@ -78,6 +82,9 @@ extern "C" int bnl_init(bnl_ctx **out, const int *devices, int ndev) {
     d.id = id;
     BNL_CUDA(ctx, cudaSetDevice(id));
     BNL_CUDA(ctx, cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
+    BNL_CUDA(ctx, cudaStreamCreateWithFlags(&d.stream2, cudaStreamNonBlocking));
+    BNL_CUDA(ctx, cudaEventCreateWithFlags(&d.ev_stage[0], cudaEventDisableTiming));
+    BNL_CUDA(ctx, cudaEventCreateWithFlags(&d.ev_stage[1], cudaEventDisableTiming));
     BNL_CUDA(ctx, cudaEventCreate(&d.ev0));
     BNL_CUDA(ctx, cudaEventCreate(&d.ev1));
     BNL_CUDA(ctx, cudaEventCreate(&d.evc0));
@@ -154,6 +161,10 @@ extern "C" void bnl_shutdown(bnl_ctx *ctx) {
     for (auto &b : d.pool) cudaFree(b.first);
     d.pool.clear();
     cudaFree(d.stage); cudaFree(d.d_flags);
+    cudaFreeHost(d.h_pack);
+    if (d.ev_stage[0]) cudaEventDestroy(d.ev_stage[0]);
+    if (d.ev_stage[1]) cudaEventDestroy(d.ev_stage[1]);
+    if (d.stream2) cudaStreamDestroy(d.stream2);
     cudaFree(d.d_units); cudaFree(d.d_tables); cudaFree(d.d_out); cudaFree(d.d_gidx); cudaFree(d.d_order);
     cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_gidx); cudaFreeHost(d.h_order);
     if (d.ev0) cudaEventDestroy(d.ev0);
@@ -181,6 +192,126 @@ extern "C" int bnl_last_call_profile(const bnl_ctx *ctx, double *total_ms, doubl
 }
 
 static size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+extern "C" void bnl_host_pack_slice(const int *src, uint8_t *dst, long long n, int nlevels, int *bad,
+                                    int *has_na);
+
+// Upload of the factor columns of a LARGE data frame. Two routes share the work
+// and the PCIe link:
+//   raw route   int32 column -> device staging (2 buffers) -> pack_factors_kernel
+//   host route  host threads pack 1M-row blocks of a column into a pinned ring;
+//               whoever finishes a column's last block sends its uint8 copy
+// Columns are claimed dynamically: the host route walks the columns upwards, the
+// raw route downwards, until they meet, so the split adapts to the box (PCIe
+// rate, core count, pageable vs pinned source). 4x fewer bytes cross the link for
+// host-packed columns. dcols[s] is the data-frame column of packed slot s.
+static int upload_factors_hybrid(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, BnlDeviceData &dd0,
+                                 const void *const *col, const int *nlevels,
+                                 const std::vector<int> &dcols, int *d_flags, std::vector<int> &host_flags) {
+  const long long nobs = ds.nobs;
+  const int nd = ds.nd;
+  const long long kBlock = 1 << 20;
+  const int nblocks = (int)((nobs + kBlock - 1) / kBlock);
+  const int kSlots = 6;
+  unsigned hw = std::thread::hardware_concurrency();
+  int nthreads = (int)(hw ? hw : 8);
+  if (const char *v = getenv("BNL_PACK_THREADS")) nthreads = atoi(v);
+  nthreads = std::max(0, std::min(nthreads, 32) - 1);           // the caller's thread feeds the raw route
+
+  int rc;
+  const size_t stage_ints = ((size_t)nobs + 4 + 63) & ~(size_t)63;     // keeps both buffers 16-byte aligned
+  if ((rc = bnl_reserve_device(ctx, &d0.stage, &d0.stage_cap, 2 * stage_ints))) return rc;
+  if (nthreads > 0 && (rc = bnl_reserve_pinned(ctx, &d0.h_pack, &d0.h_pack_cap, (size_t)kSlots * ds.stride_u8)))
+    return rc;
+
+  // the device buffer was filled with 0xFF on the main stream: order stream2 after it.
+  BNL_CUDA(ctx, cudaEventRecord(d0.ev_stage[0], d0.stream));
+  BNL_CUDA(ctx, cudaStreamWaitEvent(d0.stream2, d0.ev_stage[0], 0));
+
+  // columns [0, cpu_next) belong to the host route, [gpu_next, nd) to the raw route.
+  std::mutex claim;
+  int cpu_next = 0, cpu_cur = -1, cpu_blk = 0, gpu_next = nd;
+  std::vector<std::atomic<int>> done(nd), enq(nd);
+  for (int i = 0; i < nd; i++) { done[i] = 0; enq[i] = 0; }
+  std::vector<cudaEvent_t> ev(nd, nullptr);
+  std::atomic<int> failed(0);
+  host_flags.assign(1 + nd, 0);
+
+  auto claim_cpu = [&](int *c, int *b) {
+    std::lock_guard<std::mutex> lock(claim);
+    if (cpu_cur < 0 || cpu_blk >= nblocks) {
+      if (cpu_next >= gpu_next) return false;
+      cpu_cur = cpu_next++;
+      cpu_blk = 0;
+    }
+    *c = cpu_cur; *b = cpu_blk++;
+    return true;
+  };
+  auto claim_raw = [&]() {
+    std::lock_guard<std::mutex> lock(claim);
+    return gpu_next - 1 < cpu_next ? -1 : --gpu_next;
+  };
+
+  auto packer = [&]() {
+    cudaSetDevice(d0.id);
+    int c, b;
+    while (!failed.load() && claim_cpu(&c, &b)) {
+      const int slot = c % kSlots;
+      if (c >= kSlots) {                                        // the ring slot must have left the host
+        while (!enq[c - kSlots].load() && !failed.load()) std::this_thread::yield();
+        if (failed.load()) break;
+        if (cudaEventSynchronize(ev[c - kSlots]) != cudaSuccess) { failed = 1; break; }
+      }
+      const long long r0 = (long long)b * kBlock, r1 = std::min(nobs, r0 + kBlock);
+      const int dc = dcols[c];
+      int bad = 0, na = 0;
+      bnl_host_pack_slice(static_cast<const int *>(col[dc]) + r0, d0.h_pack + (size_t)slot * ds.stride_u8 + r0,
+                          r1 - r0, nlevels[dc], &bad, &na);
+      if (bad) host_flags[0] = 1;
+      if (na) host_flags[1 + c] = 1;
+      if (done[c].fetch_add(1) + 1 == nblocks) {
+        cudaError_t e = cudaEventCreateWithFlags(&ev[c], cudaEventDisableTiming);
+        if (e == cudaSuccess)
+          e = cudaMemcpyAsync(dd0.u8 + ds.stride_u8 * c, d0.h_pack + (size_t)slot * ds.stride_u8, (size_t)nobs,
+                              cudaMemcpyHostToDevice, d0.stream2);
+        if (e == cudaSuccess) e = cudaEventRecord(ev[c], d0.stream2);
+        if (e != cudaSuccess) failed = 1;
+        enq[c] = 1;
+      }
+    }
+  };
+  std::vector<std::thread> workers;
+  for (int t = 0; t < nthreads; t++) workers.emplace_back(packer);
+
+  // raw route, on the caller's thread.
+  int fed = 0, c;
+  cudaError_t ge = cudaSuccess;
+  while (ge == cudaSuccess && !failed.load() && (c = claim_raw()) >= 0) {
+    const int k = fed & 1;
+    if (fed >= 2) ge = cudaEventSynchronize(d0.ev_stage[k]);
+    int *st = d0.stage + (size_t)k * stage_ints;
+    const int dc = dcols[c];
+    if (ge == cudaSuccess)
+      ge = cudaMemcpyAsync(st, col[dc], (size_t)nobs * sizeof(int), cudaMemcpyHostToDevice, d0.stream);
+    if (ge == cudaSuccess) {
+      long long quads = (nobs + 3) / 4;
+      int grid = (int)std::min<long long>((quads + 255) / 256, (long long)d0.sm_count * 16);
+      pack_factors_kernel<<<grid, 256, 0, d0.stream>>>(st, dd0.u8 + ds.stride_u8 * c, nobs, nlevels[dc], d_flags,
+                                                       d_flags + 1 + c);
+      ge = cudaGetLastError();
+    }
+    if (ge == cudaSuccess) ge = cudaEventRecord(d0.ev_stage[k], d0.stream);
+    fed++;
+  }
+  if (ge != cudaSuccess) failed = 1;
+  for (auto &w : workers) w.join();
+  cudaError_t e2 = cudaStreamSynchronize(d0.stream2);
+  for (cudaEvent_t e : ev) if (e) cudaEventDestroy(e);
+  if (failed.load() || e2 != cudaSuccess)
+    return bnl_fail(ctx, BNL_ECUDA, "uploading the factor columns failed: %s",
+                    cudaGetErrorString(ge != cudaSuccess ? ge : (e2 != cudaSuccess ? e2 : cudaGetLastError())));
+  return BNL_OK;
+}
 
 extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col,
                                  const int *is_numeric, const int *nlevels, int64_t nobs,
@@ -234,7 +365,7 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
     dd0.u8_bytes = ds.stride_u8 * ds.nd;
     if ((rc = bnl_pool_alloc(ctx, d0, (void **)&dd0.u8, dd0.u8_bytes))) return cleanup(rc);
     REG_CUDA(cudaMemsetAsync(dd0.u8, BNL_NA_U8, ds.stride_u8 * ds.nd, d0.stream));
-    if ((rc = bnl_reserve_device(ctx, &d0.stage, &d0.stage_cap, (size_t)nobs + 4))) return cleanup(rc);
+    if ((rc = bnl_reserve_device(ctx, &d0.stage, &d0.stage_cap, 2 * ((size_t)nobs + 68)))) return cleanup(rc);
     if ((rc = bnl_reserve_device(ctx, &d0.d_flags, &d0.flags_cap, (size_t)(1 + ds.nd)))) return cleanup(rc);
     stage = d0.stage;
     d_bad = d0.d_flags;
@@ -245,10 +376,21 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
     if ((rc = bnl_pool_alloc(ctx, d0, (void **)&dd0.f64, dd0.f64_bytes))) return cleanup(rc);
     REG_CUDA(cudaMemsetAsync(dd0.f64, 0, ds.stride_f64 * ds.nc * sizeof(double), d0.stream));
   }
-  for (int i = 0; i < ncols; i++) {
+  for (int i = 0; i < ncols; i++)
     if (!col[i] && nobs > 0)
       return cleanup(bnl_fail(ctx, BNL_EINVAL, "column %d is a null pointer", i));
+  // big data frames: host cores and the copy engine share the factor columns.
+  std::vector<int> host_flags;
+  const bool hybrid = ds.nd > 0 && (long long)ds.nd * nobs >= (8ll << 20) && !getenv("BNL_NO_HOST_PACK");
+  if (hybrid) {
+    std::vector<int> dcols(ds.nd);
+    for (int i = 0; i < ncols; i++) if (!is_numeric[i]) dcols[ds.slot[i]] = i;
+    if ((rc = upload_factors_hybrid(ctx, ds, d0, dd0, col, nlevels, dcols, d_bad, host_flags)))
+      return cleanup(rc);
+  }
+  for (int i = 0; i < ncols; i++) {
     if (nobs == 0) continue;
+    if (hybrid && !is_numeric[i]) continue;
     if (is_numeric[i]) {
       REG_CUDA(cudaMemcpyAsync(dd0.f64 + ds.stride_f64 * ds.slot[i], col[i],
                                (size_t)nobs * sizeof(double), cudaMemcpyHostToDevice, d0.stream));
@@ -268,6 +410,7 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
     REG_CUDA(cudaMemcpyAsync(flags.data(), d_bad, flags.size() * sizeof(int), cudaMemcpyDeviceToHost,
                              d0.stream));
     REG_CUDA(cudaStreamSynchronize(d0.stream));
+    for (size_t i = 0; i < host_flags.size() && i < flags.size(); i++) flags[i] |= host_flags[i];
     const int bad = flags[0];
     ds.slot_has_na.assign(flags.begin() + 1, flags.end());
     if (bad)

@@ -48,7 +48,10 @@ struct BnlDevice {
   // buffers: cudaMalloc / cudaFree synchronise the device and can cost tens of
   // milliseconds for hundreds of MB, which would dominate re-registration
   // (boot.strength registers a fresh data frame per replicate).
-  int *stage = nullptr; size_t stage_cap = 0;            // one int32 column
+  int *stage = nullptr; size_t stage_cap = 0;            // two int32 columns (double buffer)
+  cudaStream_t stream2 = nullptr;                        // host-packed columns travel here
+  cudaEvent_t ev_stage[2] = {nullptr, nullptr};
+  uint8_t *h_pack = nullptr; size_t h_pack_cap = 0;      // pinned ring of host-packed columns
   int *d_flags = nullptr; size_t flags_cap = 0;          // bad-code flag + per-column NA flags
   std::vector<std::pair<void *, size_t>> pool;           // released blocks (pointer, bytes)
   int sm_count = 148;

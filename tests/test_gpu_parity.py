@@ -307,3 +307,38 @@ def test_multi_device_context_gives_identical_results():
     for a, b in zip(out[0], out[1]):
         for u, v in zip(a, b):
             assert np.array_equal(u, v)
+
+
+@pytest.mark.parametrize("threads", [None, "0", "3"])
+def test_large_registration_hybrid_upload(engine, threads, monkeypatch):
+    """Data frames above 8M values are uploaded by two cooperating routes (host
+    cores packing into a pinned ring + raw copies packed on the device); whatever
+    the split, the packed data -- hence every count -- must be identical, NA
+    flags included, and a bad code must still be refused."""
+    from bnlearn_b200 import BnlError
+    if threads is not None:
+        monkeypatch.setenv("BNL_PACK_THREADS", threads)
+    rng = np.random.default_rng(31)
+    n = 2_100_003
+    lev = [3, 4, 2, 5, 3]
+    cols = [rng.integers(1, l + 1, n).astype(np.int32) for l in lev]
+    cols[1][rng.random(n) < 0.001] = np.iinfo(np.int32).min
+    cols[4][-1] = np.iinfo(np.int32).min
+    d = engine.register(cols, lev)
+    xs, ys, zs = [0, 1, 3, 4], [2, 0, 1, 3], [[], [2], [0, 2], [0, 1, 2]]
+    tabs = d.counts(xs, ys, zs)
+    for x, y, z, t in zip(xs, ys, zs, tabs):
+        keep = np.ones(n, dtype=bool)
+        for c in [x, y] + z:
+            keep &= cols[c] != np.iinfo(np.int32).min
+        key = np.zeros(n, dtype=np.int64)
+        mul = 1
+        for c in [y, x] + z:
+            key += (cols[c].astype(np.int64) - 1) * mul
+            mul *= lev[c]
+        ref = np.bincount(key[keep], minlength=t.size)
+        assert np.array_equal(t.ravel(), ref), (x, y, z)
+    d.release()
+    cols[2][1_500_000] = 7
+    with pytest.raises(BnlError):
+        engine.register(cols, lev)
