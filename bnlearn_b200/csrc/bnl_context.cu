@@ -215,7 +215,7 @@ static int upload_factors_hybrid(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, Bn
   const int kSlots = 6;
   unsigned hw = std::thread::hardware_concurrency();
   int nthreads = (int)(hw ? hw : 8);
-  if (const char *v = getenv("BNL_PACK_THREADS")) nthreads = atoi(v);
+  if (const char *v = getenv("BNL_PACK_THREADS")) if (*v) nthreads = atoi(v);
   nthreads = std::max(0, std::min(nthreads, 32) - 1);           // the caller's thread feeds the raw route
 
   int rc;
