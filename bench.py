@@ -307,11 +307,29 @@ def config_d_extras(eng, rows=1_000_000, nvars=2000, seed=20261108):
 
 # --------------------------------------------------------------------------
 
+def emit(line):
+    """The JSON line is the ONLY thing written to the real stdout: libraries that
+    print from C (NCCL's version banner) had fd 1 redirected to stderr in main()."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+    # ranks share the host cores: give each its share of the packing threads
+    # (bnl_data_register would otherwise start one per core in every rank).
+    if "BNL_PACK_THREADS" not in os.environ:
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+        os.environ["BNL_PACK_THREADS"] = str(max(1, (os.cpu_count() or 8) // max(1, local_world)))
 
     if args.impl == "reference" and rank != 0:
         return 0
@@ -352,7 +370,7 @@ def main():
                      "e2e": {"value": val, "unit": "tests/s", "h2d_bytes_per_step": 0,
                              "d2h_bytes_per_step": 0},
                      "gpu_launches": 0})
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     # ---------------- our arm ------------------------------------------------
@@ -484,7 +502,7 @@ def main():
             val, secs, kind = cpu_run(cols32, lev, pick, cores)
             line["cpu_baseline"] = {"value": val, "unit": "tests/s", "cores": cores, "kind": kind,
                                     "sample": "%d of the %d tests of one step (%.1f s)" % (len(pick), n_units, secs)}
-        print(json.dumps(line))
+        emit(line)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
