@@ -21,6 +21,7 @@ const long long kKnobPair = env_ll("BNL_PAIR", 1);
 const long long kKnobChunkRows = env_ll("BNL_CHUNK_ROWS", 0);
 const long long kKnobL2MB = env_ll("BNL_L2_MB", 192);
 const int kKnobMidThreads = (int)env_ll("BNL_MID_THREADS", 1024);
+const long long kKnobGroup = env_ll("BNL_GROUP", 1);
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
 const int kMaxBatchUnits = 1 << 16;
@@ -96,6 +97,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     dev.attr_done = true;
@@ -132,13 +135,49 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     //   L : the rest        one shared (or global) table per CTA             (count_units_kernel)
     const int mid_cap = (dev.max_smem - 8192) / 256;
     const int lane_cap = (dev.max_smem - 8192) / 128;
+    // candidate groups: runs of consecutive units that share every column but the
+    // last (score_cache_fill's candidates of one node), small tables, no NA. They
+    // are cut into tiles of up to BNL_GROUP_MAX units whose tables fit one SM.
+    std::vector<char> grouped(cnt, 0);
+    std::vector<int2> tiles;
+    std::vector<int> gorder;
+    const int group_smem = dev.max_smem - 8192;
+    if (kKnobGroup && ds.nobs >= 65536) {
+      auto same_base = [&](const BnlUnit &a, const BnlUnit &b) {
+        if (a.ncols != b.ncols || a.ncols < 2 || a.has_na || b.has_na) return false;
+        for (int k = 0; k + 1 < a.ncols; k++)
+          if (a.col[k] != b.col[k] || a.mul[k] != b.mul[k]) return false;
+        return a.mul[a.ncols - 1] == b.mul[b.ncols - 1];
+      };
+      int i = 0;
+      while (i < cnt) {
+        int j = i + 1;
+        while (j < cnt && dev.h_units[j].cells <= 256 && dev.h_units[i].cells <= 256 &&
+               same_base(dev.h_units[i], dev.h_units[j])) j++;
+        if (j - i >= 4) {
+          int t0 = i;
+          while (t0 < j) {
+            int t1 = t0, bytes = 0;
+            while (t1 < j && t1 - t0 < BNL_GROUP_MAX && bytes + dev.h_units[t1].cells * 256 <= group_smem) {
+              bytes += dev.h_units[t1].cells * 256;
+              t1++;
+            }
+            tiles.push_back(make_int2((int)gorder.size(), t1 - t0));
+            for (int u = t0; u < t1; u++) { gorder.push_back(u); grouped[u] = 1; }
+            t0 = t1;
+          }
+        }
+        i = j;
+      }
+    }
     std::vector<int> cls[4];
     int cmax[4] = {0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
       BnlUnit &hu = dev.h_units[i];
+      hu.mode = 0;
+      if (grouped[i]) continue;
       const int c = hu.cells;
       const int k = c <= 256 ? 0 : (c <= mid_cap ? 1 : (c <= lane_cap ? 2 : 3));
-      hu.mode = 0;
       cls[k].push_back(i);
       cmax[k] = std::max(cmax[k], c);
     }
@@ -157,9 +196,17 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     }
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_order, &dev.h_order_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
+    int n_ungrouped = 0;
     {
       int o = 0;
       for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
+      n_ungrouped = o;
+      for (int i : gorder) dev.h_order[o++] = i;       // group members follow, in tile order
+    }
+    if (!tiles.empty()) {
+      if ((rc = bnl_reserve_pinned(ctx, &dev.h_tiles, &dev.h_tiles_cap, tiles.size()))) return rc;
+      if ((rc = bnl_reserve_device(ctx, &dev.d_tiles, &dev.tiles_cap, tiles.size()))) return rc;
+      memcpy(dev.h_tiles, tiles.data(), tiles.size() * sizeof(int2));
     }
     // Rows per CTA. Every CTA pays a fixed price (clearing and collapsing its
     // replicated table), so chunks should be as long as load balance allows: aim
@@ -197,8 +244,29 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                   cudaMemcpyHostToDevice, dev.stream));
     BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_order, dev.h_order, (size_t)cnt * sizeof(int),
                                   cudaMemcpyHostToDevice, dev.stream));
+    if (!tiles.empty())
+      BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_tiles, dev.h_tiles, tiles.size() * sizeof(int2),
+                                    cudaMemcpyHostToDevice, dev.stream));
     BNL_CUDA(ctx, cudaMemsetAsync(dev.d_tables, 0, (size_t)cells * sizeof(int), dev.stream));
     BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
+    if (groups > 0 && !tiles.empty()) {
+      // one CTA per SM (its tables fill the shared memory): ~8 waves of CTAs.
+      int smem = 0;
+      for (const int2 &t : tiles) {
+        int b = 0;
+        for (int u = 0; u < t.y; u++) b += dev.h_units[gorder[t.x + u]].cells * 256;
+        smem = std::max(smem, b);
+      }
+      const long long want = (8ll * dev.sm_count + (long long)tiles.size() - 1) / (long long)tiles.size();
+      long long rows = std::max(65536ll, ds.nobs / std::max(1ll, want));
+      if (kKnobChunkRows) rows = kKnobChunkRows;
+      int ch = (int)std::max(1ll, std::min((ds.nobs + rows - 1) / rows, std::max(1ll, groups / 1024)));
+      count_group_kernel<<<(unsigned)tiles.size() * ch, 1024, (size_t)smem, dev.stream>>>(
+          dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + n_ungrouped, dev.d_tiles, dev.d_tables,
+          (int)tiles.size(), ch);
+      BNL_CUDA(ctx, cudaGetLastError());
+      tm->launches++;
+    }
     if (groups > 0) {
       int base = 0;
       if (!cls[0].empty()) {

@@ -434,6 +434,104 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 }
 
 // ---------------------------------------------------------------------------
+// Candidate groups. A score_cache_fill batch evaluates parents(t) + i for every
+// candidate i: the units share every column but the last (the candidate, whose
+// multiplier is the number of base cells). One CTA takes up to BNL_GROUP_MAX such
+// units over a row chunk: the shared columns are loaded and combined into a packed
+// base index ONCE per 16 rows, then each candidate costs one 128-bit load, four
+// IMADs and the 16 (PRMT + ATOMS) updates of its own lane-replicated table. This
+// removes the repeated loads of the target / parent columns -- load wavefronts are
+// what the per-unit kernel spends on top of its atomics -- and is what lifts the
+// candidate batch past half of the HBM roofline.
+// tiles[] = {first position in `order`, number of units}; tables sit back to back
+// in shared memory (unit j at tile_off[j] bytes).
+#define BNL_GROUP_MAX 8
+
+__global__ void __launch_bounds__(1024)
+count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
+                   const BnlUnit *__restrict__ units, const int *__restrict__ order,
+                   const int2 *__restrict__ tiles, int *__restrict__ tables, int ntiles, int chunks) {
+  extern __shared__ __align__(256) int hist[];
+  __shared__ BnlUnit su;                               // first unit of the tile: the shared columns
+  __shared__ int s_col[BNL_GROUP_MAX], s_cells[BNL_GROUP_MAX], s_off[BNL_GROUP_MAX + 1];
+  __shared__ long long s_tab[BNL_GROUP_MAX];
+  const int chunk = blockIdx.x / ntiles;
+  const int2 tile = tiles[blockIdx.x % ntiles];
+  const int nu = tile.y;
+  if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
+    reinterpret_cast<int *>(&su)[threadIdx.x] =
+        reinterpret_cast<const int *>(&units[order[tile.x]])[threadIdx.x];
+  if (threadIdx.x < nu) {
+    const BnlUnit &uj = units[order[tile.x + threadIdx.x]];
+    s_col[threadIdx.x] = uj.col[uj.ncols - 1];
+    s_cells[threadIdx.x] = uj.cells;
+    s_tab[threadIdx.x] = uj.table_off;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int o = 0;
+    for (int j = 0; j < nu; j++) { s_off[j] = o; o += s_cells[j] * 256; }
+    s_off[nu] = o;
+  }
+  __syncthreads();
+  const int total_words = s_off[nu] >> 2;
+  for (int c = threadIdx.x; c < total_words; c += blockDim.x) hist[c] = 0;
+  __syncthreads();
+
+  const unsigned slot4 = ((threadIdx.x & 31u) + 32u * ((threadIdx.x >> 5) & 1u)) << 2;
+  const int nbase = su.ncols - 1;                      // shared columns
+  const unsigned cmul = (unsigned)su.mul[nbase];       // = number of base cells
+  const long long full = nobs / 16;
+  const long long per = (full + chunks - 1) / chunks;
+  const long long g0 = per * chunk;
+  long long g1 = g0 + per;
+  if (g1 > full) g1 = full;
+
+  for (long long g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+    uint4 vb = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[0] * stride) + g);
+    for (int k = 1; k < nbase; k++) {
+      const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
+      const unsigned m = (unsigned)su.mul[k];
+      vb.x += w.x * m; vb.y += w.y * m; vb.z += w.z * m; vb.w += w.w * m;
+    }
+    uint4 wc[BNL_GROUP_MAX];
+#pragma unroll
+    for (int j = 0; j < BNL_GROUP_MAX; j++)
+      if (j < nu) wc[j] = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)s_col[j] * stride) + g);
+#pragma unroll
+    for (int j = 0; j < BNL_GROUP_MAX; j++)
+      if (j < nu) {
+        int *hj = reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + s_off[j]);
+        small_bump(hj, vb.x + wc[j].x * cmul, slot4);
+        small_bump(hj, vb.y + wc[j].y * cmul, slot4);
+        small_bump(hj, vb.z + wc[j].z * cmul, slot4);
+        small_bump(hj, vb.w + wc[j].w * cmul, slot4);
+      }
+  }
+  // the partial group at the end of the data, once, straight into the global tables.
+  if (chunk == chunks - 1 && threadIdx.x < nu && full * 16 < nobs) {
+    const int j = threadIdx.x;
+    for (long long r = full * 16; r < nobs; r++) {
+      int cell = 0;
+      for (int k = 0; k < nbase; k++) cell += (int)u8[(size_t)su.col[k] * stride + (size_t)r] * su.mul[k];
+      cell += (int)u8[(size_t)s_col[j] * stride + (size_t)r] * (int)cmul;
+      atomicAdd(&tables[s_tab[j] + cell], 1);
+    }
+  }
+  __syncthreads();
+  for (int j = 0; j < nu; j++) {
+    const int *hj = reinterpret_cast<const int *>(reinterpret_cast<const char *>(hist) + s_off[j]);
+    int *gtab = tables + s_tab[j];
+    for (int c = threadIdx.x; c < s_cells[j]; c += blockDim.x) {
+      int sum = 0;
+#pragma unroll
+      for (int l = 0; l < 64; l++) sum += hj[c * 64 + ((l + threadIdx.x) & 63)];
+      if (sum) atomicAdd(&gtab[c], sum);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // Epilogue. kind 0: CI test (code = test_e); kind 1: node score (code = score_e).
 // One CTA per unit, one warp per stratum (configuration of Z / of the parents).
 

@@ -41,6 +41,8 @@ struct BnlDevice {
   int *d_gidx = nullptr; size_t gidx_cap = 0;            // Gaussian unit descriptors
   int *d_order = nullptr; size_t order_cap = 0;          // launch order -> unit slot
   int *h_order = nullptr; size_t h_order_cap = 0;        // pinned
+  int2 *d_tiles = nullptr; size_t tiles_cap = 0;         // candidate-group tiles
+  int2 *h_tiles = nullptr; size_t h_tiles_cap = 0;       // pinned
   BnlUnit *h_units = nullptr; size_t h_units_cap = 0;    // pinned
   double *h_out = nullptr; size_t h_out_cap = 0;         // pinned
   int *h_gidx = nullptr; size_t h_gidx_cap = 0;          // pinned

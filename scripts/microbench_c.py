@@ -41,7 +41,7 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "child":
         child()
     else:
-        settings = [{}]
+        settings = [{}, {"BNL_GROUP": "0"}]
         for st in settings:
             env = dict(os.environ); env.update(st)
             r = subprocess.run([sys.executable, __file__, "child"], env=env, capture_output=True, text=True)
