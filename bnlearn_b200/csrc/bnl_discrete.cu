@@ -144,7 +144,10 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     const int group_smem = dev.max_smem - 8192;
     if (kKnobGroup && ds.nobs >= 65536) {
       auto same_base = [&](const BnlUnit &a, const BnlUnit &b) {
-        if (a.ncols != b.ncols || a.ncols < 2 || a.has_na || b.has_na) return false;
+        // at least three shared columns (a node with two or more parents): below
+        // that the per-unit kernel, with its row-pair mode, is as fast or faster
+        // (scripts/microbench_c.py).
+        if (a.ncols != b.ncols || a.ncols < 4 || a.has_na || b.has_na) return false;
         for (int k = 0; k + 1 < a.ncols; k++)
           if (a.col[k] != b.col[k] || a.mul[k] != b.mul[k]) return false;
         return a.mul[a.ncols - 1] == b.mul[b.ncols - 1];
