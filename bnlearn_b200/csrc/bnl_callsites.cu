@@ -17,7 +17,7 @@ namespace {
 bool is_discrete_test(int t) { return t == BNL_MI || t == BNL_MI_ADF || t == BNL_X2 || t == BNL_X2_ADF; }
 bool is_gaussian_test(int t) { return t == BNL_COR || t == BNL_ZF || t == BNL_MI_G; }
 bool is_discrete_score(int s) {
-  return s == BNL_LOGLIK || s == BNL_AIC || s == BNL_BIC || s == BNL_BDE || s == BNL_BDS || s == BNL_BDJ || s == BNL_K2;
+  return s == BNL_LOGLIK || s == BNL_AIC || s == BNL_BIC || s == BNL_BDE || s == BNL_BDS || s == BNL_BDJ || s == BNL_K2 || s == BNL_NAL || s == BNL_PNAL;
 }
 
 // one batch of CI tests through the matching kernel path.
@@ -243,6 +243,37 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
   }
   if (test_counter) *test_counter += total;
   return BNL_OK;
+}
+
+extern "C" int bnl_mi_matrix(bnl_ctx *ctx, bnl_data data, int estimator_e, int ncols,
+                             const int *cols, int cond, double *out) {
+  if (!ctx) return BNL_EINVAL;
+  if (estimator_e != BNL_MI && estimator_e != BNL_MI_G)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "estimator %d is neither mi nor mi-g", estimator_e);
+  if (ncols < 0 || (ncols > 0 && !cols) || (ncols > 1 && !out))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_mi_matrix: bad arguments");
+  if (estimator_e == BNL_MI_G && cond >= 0)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "a conditioning variable is only defined for the discrete estimator");
+  const long long np = (long long)ncols * (ncols - 1) / 2;
+  if (np <= 0) return BNL_OK;
+  if (np > INT32_MAX) return bnl_fail(ctx, BNL_EOVERFLOW, "too many column pairs");
+  // every pair is one unit; the batch goes through the same kernels as a level of
+  // pc.stable (the counting kernel groups units by table size, not by caller).
+  std::vector<int> x((size_t)np), y((size_t)np), zoff((size_t)np + 1), zidx;
+  if (cond >= 0) zidx.assign((size_t)np, cond);
+  size_t k = 0;
+  for (int i = 0; i < ncols; i++)
+    for (int j = i + 1; j < ncols; j++, k++) {
+      x[k] = cols[i]; y[k] = cols[j];
+      zoff[k] = cond >= 0 ? (int)k : 0;
+    }
+  zoff[(size_t)np] = cond >= 0 ? (int)np : 0;
+  std::vector<double> df((size_t)np), pv((size_t)np);
+  if (estimator_e == BNL_MI)
+    return bnl_ci_discrete_any(ctx, data, BNL_MI_COEF, (int)np, x.data(), y.data(), zoff.data(),
+                               zidx.data(), out, df.data(), pv.data());
+  return bnl_ci_gaussian_any(ctx, data, BNL_MI_G_COEF, (int)np, x.data(), y.data(), zoff.data(),
+                             zidx.data(), out, df.data(), pv.data());
 }
 
 extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int x, const int *z,

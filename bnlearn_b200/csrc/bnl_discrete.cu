@@ -320,7 +320,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
     } else {
       epilogue_kernel<<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
-                                                               rq.kind, rq.code, rq.arg);
+                                                               rq.kind, rq.code, rq.arg, ds.nobs);
       BNL_CUDA(ctx, cudaGetLastError());
       tm->launches++;
       BNL_CUDA(ctx, cudaEventRecord(dev.eve1, dev.stream));
@@ -413,6 +413,15 @@ extern "C" int bnl_ci_discrete(bnl_ctx *ctx, bnl_data data, int test_e, int n, c
   if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   if (test_e != BNL_MI && test_e != BNL_MI_ADF && test_e != BNL_X2 && test_e != BNL_X2_ADF)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a discrete asymptotic test handled here", test_e);
+  return bnl_ci_discrete_any(ctx, data, test_e, n, x, y, z_off, z_idx, stat, df, pvalue);
+}
+
+// Same request with the library-internal statistic codes allowed (BNL_MI_COEF).
+int bnl_ci_discrete_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x, const int *y,
+                        const int *z_off, const int *z_idx, double *stat, double *df,
+                        double *pvalue) {
+  BnlDataSet *ds = find_data(ctx, data);
+  if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   if (n < 0 || (n > 0 && (!x || !y || !z_off)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_discrete: bad arguments");
   Request rq{0, test_e, 0.0, n, {}, stat, df, pvalue, nullptr, nullptr};
@@ -432,7 +441,8 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
   BnlDataSet *ds = find_data(ctx, data);
   if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   if (score_e != BNL_LOGLIK && score_e != BNL_AIC && score_e != BNL_BIC && score_e != BNL_BDE &&
-      score_e != BNL_BDS && score_e != BNL_BDJ && score_e != BNL_K2)
+      score_e != BNL_BDS && score_e != BNL_BDJ && score_e != BNL_K2 && score_e != BNL_NAL &&
+      score_e != BNL_PNAL)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a discrete score handled here", score_e);
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_discrete: bad arguments");

@@ -558,7 +558,7 @@ __device__ __forceinline__ void warp_merge_kahan(bnl::KahanSum &k) {
 
 __global__ void __launch_bounds__(BNL_EPI_THREADS)
 epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ tables,
-                double *__restrict__ out, int kind, int code, double arg) {
+                double *__restrict__ out, int kind, int code, double arg, long long nrows) {
   __shared__ int s_marg[BNL_EPI_WARPS][2 * BNL_MAX_LEVELS + 2];
   __shared__ double s_s[BNL_EPI_WARPS], s_c[BNL_EPI_WARPS], s_df[BNL_EPI_WARPS];
   __shared__ long long s_n[BNL_EPI_WARPS];
@@ -633,7 +633,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
       if (lane == 0) nobs += nk;
       if (nk > 0) {
         const double dnk = (double)nk;
-        if (code == BNL_MI || code == BNL_MI_ADF) {
+        if (code == BNL_MI || code == BNL_MI_ADF || code == BNL_MI_COEF) {
           for (int c = lane; c < sl; c += 32) {
             const int n = S[c];
             if (n) {
@@ -688,6 +688,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
     double stat = 0.0;
     if (n > 0 && !(adf && (double)n < 5.0 * (double)llx * (double)lly * (double)llz)) {
       if (code == BNL_MI || code == BNL_MI_ADF) stat = tot.value() / (double)n * (2.0 * (double)n);
+      else if (code == BNL_MI_COEF) stat = tot.value() / (double)n;   // mi_kernel() / nobs
       else stat = tot.value();
     }
     o[0] = stat; o[1] = df; o[2] = bnl::pchisq_upper(stat, df); o[3] = (double)n;
@@ -695,6 +696,9 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
     const double nparams = (double)(llx - 1) * (double)llz;
     double s = tot.value();
     if (code == BNL_AIC || code == BNL_BIC) s -= arg * nparams;
+    // node-average likelihood: per locally complete row, penalty per data row.
+    if (code == BNL_NAL || code == BNL_PNAL)
+      s = n == 0 ? -INFINITY : s / (double)n - (code == BNL_PNAL ? arg : 0.0) / (double)nrows * nparams;
     o[0] = s; o[1] = nparams; o[2] = 0.0; o[3] = (double)n;
   }
 }

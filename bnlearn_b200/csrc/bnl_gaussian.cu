@@ -207,6 +207,16 @@ extern "C" int bnl_ci_gaussian(bnl_ctx *ctx, bnl_data data, int test_e, int n, c
   BnlDataSet &ds = it->second;
   if (test_e != BNL_COR && test_e != BNL_ZF && test_e != BNL_MI_G)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a Gaussian test handled here", test_e);
+  return bnl_ci_gaussian_any(ctx, data, test_e, n, x, y, z_off, z_idx, stat, df, pvalue);
+}
+
+// Same request with the library-internal statistic codes allowed (BNL_MI_G_COEF).
+int bnl_ci_gaussian_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x, const int *y,
+                        const int *z_off, const int *z_idx, double *stat, double *df,
+                        double *pvalue) {
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
   if (n < 0 || (n > 0 && (!x || !y || !z_off)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_gaussian: bad arguments");
   if (ds.nc == 0) return bnl_fail(ctx, BNL_EINVAL, "the data set has no numeric columns");

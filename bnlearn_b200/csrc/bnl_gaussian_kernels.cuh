@@ -316,6 +316,9 @@ __global__ void gauss_ci_kernel(const int *__restrict__ ux, const int *__restric
   } else if (test == BNL_ZF) {
     stat = log((1.0 + r) / (1.0 - r)) / 2.0 * sqrt(df);
     pv = bnl::pnorm_two_sided(stat);
+  } else if (test == BNL_MI_G_COEF) {     // cor_mi_trans() alone, for the coefficient matrix
+    stat = -0.5 * log(1.0 - r * r);
+    pv = 0.0;
   } else {
     stat = 2.0 * (double)nobs * (-0.5 * log(1.0 - r * r));
     pv = bnl::pchisq_upper(stat, df);

@@ -138,6 +138,15 @@ void bnl_pool_free(BnlDevice &dev, void *p, size_t bytes);
 // defined in bnl_gaussian.cu: forms means and the covariance matrix on a device.
 int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int dev_index);
 
+// statistic codes used inside the library only (bnl_mi_matrix): the mutual
+// information COEFFICIENT instead of the G^2 statistic.
+#define BNL_MI_COEF 90
+#define BNL_MI_G_COEF 91
+int bnl_ci_discrete_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x, const int *y,
+                        const int *z_off, const int *z_idx, double *stat, double *df, double *pvalue);
+int bnl_ci_gaussian_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x, const int *y,
+                        const int *z_off, const int *z_idx, double *stat, double *df, double *pvalue);
+
 // per-call timing of one device block.
 struct BnlTiming { float total = 0.f, count = 0.f, epi = 0.f; int launches = 0; };
 

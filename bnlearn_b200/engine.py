@@ -12,11 +12,11 @@ import numpy as np
 from . import _lib
 
 TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "cor": 20, "zf": 21, "mi-g": 22}
-SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9,
+SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103}
 DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf")
 GAUSSIAN_TESTS = ("cor", "zf", "mi-g")
-DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds", "bdj", "k2")
+DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds", "bdj", "k2", "nal", "pnal")
 GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g")
 NA_INT = np.iinfo(np.int32).min
 
@@ -199,6 +199,19 @@ class DataSet:
         e._check(e._lib.bnl_score_gaussian(e._ctx, self.handle, SCORES[score], float(k), n, _ip(t),
                                            _ip(po), _ip(pi), _dp(sc), _dp(npar)))
         return sc[:n], npar[:n]
+
+    def mi_matrix(self, estimator, cols, cond=-1):
+        """Pairwise mutual-information coefficients of `cols` (optionally given the
+        factor `cond`) as a symmetric matrix with a zero diagonal."""
+        e = self.engine
+        c = np.ascontiguousarray(cols, dtype=np.int32)
+        p = len(c)
+        tri = np.zeros(max(p * (p - 1) // 2, 1))
+        e._check(e._lib.bnl_mi_matrix(e._ctx, self.handle, TESTS[estimator], p, _ip(c), int(cond), _dp(tri)))
+        m = np.zeros((p, p))
+        iu = np.triu_indices(p, 1)
+        m[iu] = tri[:len(iu[0])]
+        return m + m.T
 
     def moments(self):
         """(means, covariance matrix) of the numeric columns, registration order."""

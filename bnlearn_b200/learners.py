@@ -528,3 +528,72 @@ def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, 
     with np.errstate(invalid="ignore", divide="ignore"):
         direction = np.where(strength > 0, prob / strength, 0.0)
     return strength, direction, tests
+
+
+# ------------------------ pairwise mutual information -----------------------
+
+def aracne(ds, nnodes, estimator="mi"):
+    """ARACNE (src/learning/local/mi.matrix.c:255-412, no white/blacklist): the edge
+    i - j is dropped when some k has MI(i, j) < min(MI(i, k), MI(j, k)). The
+    coefficient matrix comes from one engine call. Returns sorted (i, j), i < j."""
+    mi = ds.mi_matrix(estimator, list(range(nnodes)))
+    keep = []
+    for i in range(nnodes):
+        for j in range(i + 1, nnodes):
+            weaker = (mi[i, j] < mi[i]) & (mi[i, j] < mi[j])
+            weaker[i] = weaker[j] = False
+            if not weaker.any():
+                keep.append((i, j))
+    return keep
+
+
+def chow_liu(ds, nnodes, estimator="mi", cols=None, cond=-1):
+    """Chow-Liu tree (src/learning/local/mi.matrix.c:425-594): edges in decreasing
+    order of mutual information, skipping those that would close a cycle, until
+    nnodes - 1 are in. `cols`/`cond` serve TAN (features given the class). The
+    reference sorts with R_qsort_I and walks the result backwards; coefficients
+    that tie exactly could come out in another order here."""
+    cols = list(range(nnodes)) if cols is None else list(cols)
+    p = len(cols)
+    mi = ds.mi_matrix(estimator, cols, cond)
+    iu, ju = np.triu_indices(p, 1)
+    order = np.argsort(mi[iu, ju], kind="stable")[::-1]
+    comp = list(range(p))                      # union-find: a path exists iff same component
+
+    def find(a):
+        while comp[a] != a:
+            comp[a] = comp[comp[a]]
+            a = comp[a]
+        return a
+    edges = []
+    for o in order:
+        if len(edges) >= p - 1:
+            break
+        a, b = find(int(iu[o])), find(int(ju[o]))
+        if a == b:
+            continue
+        comp[a] = b
+        edges.append((int(iu[o]), int(ju[o])))
+    if len(edges) != p - 1:
+        raise ValueError("learned %d arcs instead of %d, this is not a tree spanning all the nodes."
+                         % (len(edges), p - 1))
+    return sorted(edges)
+
+
+def tree_directions(edges, nnodes, root):
+    """Orient a tree away from `root` (src/learning/local/mi.matrix.c:597-676)."""
+    adj = {i: [] for i in range(nnodes)}
+    for a, b in edges:
+        adj[a].append(b)
+        adj[b].append(a)
+    depth = {root: 1}
+    frontier = [root]
+    while frontier:
+        nxt = []
+        for a in frontier:
+            for b in adj[a]:
+                if b not in depth:
+                    depth[b] = depth[a] + 1
+                    nxt.append(b)
+        frontier = nxt
+    return sorted((a, b) if depth[a] < depth[b] else (b, a) for a, b in edges)

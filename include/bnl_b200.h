@@ -52,6 +52,7 @@ enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4,
        BNL_COR = 20, BNL_ZF = 21, BNL_MI_G = 22 };
 /* score_e values handled (src/scores/scores.h:9-60). */
 enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
+       BNL_NAL = 13, BNL_PNAL = 14,
        BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103 };
 
 /* ---- context ---------------------------------------------------------- */
@@ -107,7 +108,9 @@ int bnl_counts(bnl_ctx *ctx, bnl_data data, int n, const int *x, const int *y,
  * pa_idx[pa_off[u] .. pa_off[u+1]). k_or_iss is the penalty coefficient k for
  * AIC/BIC and the imaginary sample size for BDe/BDs (uniform graph prior); it is
  * ignored for BDJ and K2, whose per-cell hyperparameter is fixed (1/2 and 1,
- * src/scores/per.node.score.c:233-246).
+ * src/scores/per.node.score.c:233-246). NAL / PNAL (the scores bnlearn switches
+ * to on incomplete data, src/scores/discrete.nal.c:8-68) average the
+ * log-likelihood over the locally complete rows; k_or_iss is PNAL's k.
  * nparams may be NULL. Replaces c_per_node_score() for these score_e values
  * (src/scores/per.node.score.c:51-534 -> loglik_dnode,
  * src/scores/discrete.loglikelihood.c:76-118; dirichlet_node,
@@ -184,6 +187,17 @@ int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *
                      const int *sx_off, const int *sx, const int *nfixed, int minsize,
                      int maxsize, double alpha, double *out, const int *dsep_off, int *dsep,
                      int *ndsep, double *test_counter);
+
+/* estimate_mi_matrix (src/learning/local/mi.matrix.c:184-252 over
+ * mi_matrix_discrete :40-137 / mi_matrix_gaussian :141-181), the coefficient
+ * matrix behind aracne() and chow.liu(): for the ncols listed columns (all
+ * factors with estimator BNL_MI, all numeric with BNL_MI_G) the pairwise mutual
+ * information mi_kernel()/nobs, cmi_kernel()/nobs given the factor column `cond`
+ * (TAN's class variable; -1 for none), or -log(1 - r^2)/2. out has
+ * ncols (ncols - 1) / 2 entries, pair (i, j > i) at the position UTREL() gives it
+ * (row-major over the strict upper triangle, src/core/uppertriangular.h:32-43). */
+int bnl_mi_matrix(bnl_ctx *ctx, bnl_data data, int estimator_e, int ncols, const int *cols,
+                  int cond, double *out);
 
 /* roundrobin_test (src/tests/rinterface/roundrobin.test.c:10-154 over rrd_discrete
  * / rrd_gaustests_complete, src/tests/patterns/roundrobin.test.c:32-219): x vs

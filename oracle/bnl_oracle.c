@@ -38,6 +38,7 @@ void minir_f77_dqrsl(double *x, int *ldx, int *n, int *k, double *qraux,
 /* test_e (src/tests/tests.h:8-36) and score_e (src/scores/scores.h:9-60). */
 enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_COR = 20, T_ZF = 21, T_MI_G = 22 };
 enum { S_LOGLIK = 1, S_AIC = 3, S_BIC = 4, S_BDE = 6, S_BDS = 7, S_BDJ = 8, S_K2 = 9,
+       S_NAL = 13, S_PNAL = 14,
        S_LOGLIK_G = 100, S_AIC_G = 102, S_BIC_G = 103 };
 
 /* ------------------------------------------------------------------------
@@ -204,6 +205,10 @@ double orc_score_discrete(int score, const int *x, int llx, const int *const *pa
       for (int i = 0; i < llx; i++)
         if (n[i] != 0) res += (double)n[i] * log((double)n[i] / nobs);
       npar = llx - 1;
+      /* node-average likelihood over the locally complete rows, penalty scaled by
+       * the full sample size (src/scores/discrete.nal.c:8-37). */
+      if (score == S_NAL || score == S_PNAL)
+        res = nobs == 0 ? -INFINITY : res / nobs - (score == S_PNAL ? arg : 0.0) / num * npar;
     }
     free(n);
   } else {
@@ -247,6 +252,11 @@ double orc_score_discrete(int score, const int *x, int llx, const int *const *pa
           if (c != 0) res += (double)c * log((double)c / nj[j]);
         }
       npar = (double)(llx - 1) * (double)lly;
+      if (score == S_NAL || score == S_PNAL) {      /* src/scores/discrete.nal.c:39-68 */
+        long long nobs = 0;
+        for (int j = 0; j < lly; j++) nobs += nj[j];
+        res = nobs == 0 ? -INFINITY : res / nobs - (score == S_PNAL ? arg : 0.0) / num * npar;
+      }
     }
     free(n); free(nj); free(cfg);
   }

@@ -163,6 +163,34 @@ def hc_opt_step(names, amat, added, cache, reference, wlmat, blmat, nparents, ma
             rb.to_numpy(L.VECTOR_ELT(res, 2))[0])
 
 
+def _arcs(res, names):
+    """(2m x 2) character matrix of both directions -> sorted list of (i, j), i < j."""
+    flat = rb.to_numpy(res)
+    m = len(flat) // 2
+    pairs = {tuple(sorted((names.index(flat[i]), names.index(flat[i + m])))) for i in range(m)}
+    return sorted(pairs)
+
+
+def aracne(data, estimator="mi"):
+    """reference aracne (src/learning/local/mi.matrix.c:255-412), no white/blacklist."""
+    L = rb.lib()
+    nil = rb.nil()
+    res = L.aracne(data.df(), L.Rf_mkString(estimator.encode()), nil, nil, data.complete(),
+                   L.Rf_ScalarLogical(0))
+    return _arcs(res, data.names)
+
+
+def chow_liu(data, estimator="mi", conditional=None, clevels=0):
+    """reference chow_liu (src/learning/local/mi.matrix.c:425-594); `conditional` is
+    the class variable of TAN (int32 1-based codes) or None."""
+    L = rb.lib()
+    nil = rb.nil()
+    cond = nil if conditional is None else rb.factor(np.ascontiguousarray(conditional, dtype=np.int32), clevels)
+    res = L.chow_liu(data.df(), rb.strvec(data.names), L.Rf_mkString(estimator.encode()), nil, nil,
+                     data.complete(), cond, L.Rf_ScalarLogical(0))
+    return _arcs(res, data.names)
+
+
 # ------------------------------ kernel tier ------------------------------
 
 def _ip(a):

@@ -97,6 +97,8 @@ def lib():
         "indep_test": (vp, [vp] * 9),
         "allsubs_test": (vp, [vp] * 12),
         "roundrobin_test": (vp, [vp] * 9),
+        "aracne": (vp, [vp] * 6),
+        "chow_liu": (vp, [vp] * 8),
         "reset_test_counter": (vp, []),
         "get_test_counter": (vp, []),
     }

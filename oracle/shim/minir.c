@@ -419,3 +419,32 @@ void minir_f77_dgemm(const char *transa, const char *transb, const int *m,
   if (!fn) fn = (fn_t)lapack_sym("scipy_dgemm_");
   fn(transa, transb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, 1, 1);
 }
+
+/* R_qsort_I(v, I, i, j): sort v[i-1 .. j-1] increasingly and permute I alongside
+ * (R's sort.c / qsort-body.c, Singleton's CACM 347 variant; not in the tree).
+ * This stand-in is a bottom-up merge sort, so the order of EQUAL keys is by
+ * original position and may differ from R's unstable quicksort: the only caller
+ * on the compiled path is chow_liu()'s d_sort over the mutual-information
+ * coefficients (src/learning/local/mi.matrix.c:499), and the fixtures use data
+ * without tied coefficients. */
+void R_qsort_I(double *v, int *I, int i, int j) {
+  int n = j - i + 1;
+  if (n < 2) return;
+  double *a = v + (i - 1), *tv = (double *)malloc(sizeof(double) * (size_t)n);
+  int *b = I + (i - 1), *ti = (int *)malloc(sizeof(int) * (size_t)n);
+  for (int w = 1; w < n; w *= 2) {
+    for (int lo = 0; lo < n; lo += 2 * w) {
+      int mid = lo + w < n ? lo + w : n, hi = lo + 2 * w < n ? lo + 2 * w : n;
+      int p = lo, q = mid, o = lo;
+      while (p < mid && q < hi) {
+        if (a[q] < a[p]) { tv[o] = a[q]; ti[o++] = b[q++]; }
+        else { tv[o] = a[p]; ti[o++] = b[p++]; }
+      }
+      while (p < mid) { tv[o] = a[p]; ti[o++] = b[p++]; }
+      while (q < hi) { tv[o] = a[q]; ti[o++] = b[q++]; }
+    }
+    memcpy(a, tv, sizeof(double) * (size_t)n);
+    memcpy(b, ti, sizeof(int) * (size_t)n);
+  }
+  free(tv); free(ti);
+}

@@ -183,6 +183,9 @@ void PutRNGstate(void);
 #define fmax2 Rf_fmax2
 #define fmin2 Rf_fmin2
 #define fround Rf_fround
+#ifndef M_LN_SQRT_PI
+#define M_LN_SQRT_PI 0.572364942924700087071713675677   /* log(sqrt(pi)) */
+#endif
 #ifndef M_LN_SQRT_2PI
 #define M_LN_SQRT_2PI 0.918938533204672741780329736406
 #endif

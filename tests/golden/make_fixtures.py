@@ -176,6 +176,96 @@ def reference_outputs():
     print("wrote ref_outputs.json")
 
 
+def incomplete_outputs():
+    """learning.test with 8% of the cells of every column set to NA (seeded), then
+    the reference's NA-aware arms: discrete CI tests on locally complete rows and
+    the node-average likelihood scores. Separate file and RNG so that the
+    complete-data fixtures above keep their values."""
+    from oracle import refapi as ra, refbind as rb
+    rng = np.random.default_rng(20261107)
+    names, codes, nlev = load_discrete("learning_test")
+    codes = codes.astype(np.int64) - 1
+    mask = rng.random(codes.shape) < 0.08
+    packed = np.where(mask, 255, codes).astype(np.uint8)
+    np.savez_compressed(os.path.join(HERE, "data_learning_test_na.npz"), names=np.array(names),
+                        codes=packed, nlevels=np.asarray(nlev, dtype=np.int32))
+    cols = [np.where(packed[i] == 255, np.iinfo(np.int32).min, packed[i].astype(np.int32) + 1)
+            .astype(np.int32) for i in range(len(names))]
+    data = ra.RefData(cols, list(nlev), names)
+    n, p = data.nobs, len(names)
+    rec = {"tests": [], "scores": [], "allsubs": [], "roundrobin": []}
+    for t in range(24):
+        k = int(rng.integers(0, 4))
+        idx = rng.choice(p, size=2 + k, replace=False)
+        x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+        for test in ("mi", "x2", "mi-adf", "x2-adf"):
+            st, df, pv = ra.ci_test(data, names[x], names[y], [names[i] for i in s], test)
+            rec["tests"].append({"test": test, "x": x, "y": y, "z": s, "stat": st, "df": df, "p": pv})
+        rb.reset()
+        data.invalidate()
+    # the *_with_missing call-site patterns (allsubs.test.c:290-448, roundrobin.test.c:222-344)
+    for t in range(8):
+        m = int(rng.integers(2, p - 1))
+        idx = rng.choice(p, size=2 + m, replace=False)
+        x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+        nf = int(rng.integers(0, 2))
+        mn = int(rng.integers(0, 2))
+        mx = int(rng.integers(max(mn, 1), min(3, m - nf) + 1))
+        for test in ("mi", "x2"):
+            rb.reset_test_counter()
+            pv, pmin, pmax, ds_ = ra.allsubs_test(
+                data, names[x], names[y], [names[i] for i in s], [names[i] for i in s[:nf]],
+                test, 0.05, mn, mx)
+            rec["allsubs"].append({"test": test, "x": x, "y": y, "sx": s, "nfixed": nf,
+                                   "min": mn, "max": mx, "alpha": 0.05, "p": pv,
+                                   "pmin": pmin, "pmax": pmax,
+                                   "dsep": None if ds_ is None else [names.index(d) for d in ds_],
+                                   "counter": rb.test_counter()})
+            rb.reset_test_counter()
+            pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + s],
+                                     [names[i] for i in s[:nf]], test, 0.05)
+            rec["roundrobin"].append({"test": test, "x": x, "z": [y] + s, "nfixed": nf,
+                                      "alpha": 0.05, "p": [float(v) for v in pvs],
+                                      "counter": rb.test_counter()})
+        rb.reset()
+        data.invalidate()
+    for t in range(24):
+        k = int(rng.integers(0, 4))
+        idx = rng.choice(p, size=1 + k, replace=False)
+        node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+        par = {names[node]: [names[i] for i in pa]}
+        for score, kw in (("nal", {}), ("pnal", {"k": np.log(n) / 2}), ("pnal", {"k": 0.25})):
+            v = ra.per_node_score(data, par, [names[node]], score, **kw)[0]
+            rec["scores"].append({"score": score, "arg": list(kw.values())[0] if kw else 0.0,
+                                  "node": node, "parents": pa, "value": float(v)})
+        rb.reset()
+        data.invalidate()
+    with open(os.path.join(HERE, "ref_incomplete.json"), "w") as f:
+        json.dump({"learning_test_na": rec}, f)
+    print("wrote ref_incomplete.json")
+
+
+def mi_matrix_outputs():
+    """aracne / chow.liu (and the TAN flavour of chow.liu, given a class variable)
+    from the reference on the bundled data sets; own file, no RNG."""
+    from oracle import refapi as ra, refbind as rb
+    out = {}
+    for ds in ("learning_test", "alarm", "insurance"):
+        names, codes, nlev = load_discrete(ds)
+        data = ra.RefData(list(codes), list(nlev), names)
+        rec = {"aracne": ra.aracne(data), "chow_liu": ra.chow_liu(data)}
+        sub = ra.RefData(list(codes[1:]), list(nlev[1:]), names[1:])
+        rec["chow_liu_given_first"] = ra.chow_liu(sub, conditional=codes[0], clevels=int(nlev[0]))
+        out[ds] = rec
+        rb.reset()
+    names, vals = load_gaussian("gaussian_test")
+    data = ra.RefData(list(vals), None, names)
+    out["gaussian_test"] = {"aracne": ra.aracne(data, "mi-g"), "chow_liu": ra.chow_liu(data, "mi-g")}
+    with open(os.path.join(HERE, "ref_mi_matrix.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote ref_mi_matrix.json")
+
+
 def special_function_fixtures():
     import mpmath as mp
     mp.mp.dps = 50
@@ -209,3 +299,5 @@ if __name__ == "__main__":
     export_datasets()
     special_function_fixtures()
     reference_outputs()
+    incomplete_outputs()
+    mi_matrix_outputs()

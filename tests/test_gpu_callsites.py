@@ -16,7 +16,7 @@ def engine():
         yield e
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm"])
+@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
 def test_allsubs_against_reference(engine, golden, ds):
     from bnlearn_b200 import callsites as cs
     names, cols, nlev = load_discrete(ds)
@@ -44,7 +44,7 @@ def test_allsubs_against_reference(engine, golden, ds):
     d.release()
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm"])
+@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
 def test_roundrobin_against_reference(engine, golden, ds):
     from bnlearn_b200 import callsites as cs
     names, cols, nlev = load_discrete(ds)

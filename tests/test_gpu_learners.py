@@ -132,3 +132,50 @@ def test_boot_strength_runs_and_is_deterministic(engine):
     s2, d2, t2 = learners.boot_strength(engine, cols, nlev, 8, "bde", 1.0, seed=20261109)
     assert np.array_equal(s1, s2) and np.array_equal(d1, d2) and t1 == t2
     assert s1[0, 1] == 1.0        # A - B is in every replicate of learning.test
+
+
+@pytest.mark.parametrize("ds", ["learning_test", "alarm", "insurance", "gaussian_test"])
+def test_aracne_and_chow_liu_against_reference_golden(engine, ds):
+    """Committed outputs of the reference's aracne() / chow_liu() (tests/golden/
+    ref_mi_matrix.json); the coefficient matrix comes from bnl_mi_matrix."""
+    import json
+    import os
+    from bnlearn_b200 import learners
+    from util import GOLDEN
+    with open(os.path.join(GOLDEN, "ref_mi_matrix.json")) as f:
+        g = json.load(f)[ds]
+    if ds == "gaussian_test":
+        names, cols = load_gaussian(ds)
+        d, est = engine.register(cols), "mi-g"
+    else:
+        names, cols, nlev = load_discrete(ds)
+        d, est = engine.register(cols, nlev), "mi"
+    p = len(names)
+    assert learners.aracne(d, p, est) == [tuple(a) for a in g["aracne"]]
+    tree = learners.chow_liu(d, p, est)
+    assert tree == [tuple(a) for a in g["chow_liu"]]
+    directed = learners.tree_directions(tree, p, 0)
+    assert len(directed) == p - 1 and len({b for _, b in directed}) == p - 1 and all(b != 0 for _, b in directed)
+    if "chow_liu_given_first" in g:
+        got = learners.chow_liu(d, p, est, cols=list(range(1, p)), cond=0)
+        assert got == [tuple(a) for a in g["chow_liu_given_first"]]
+    d.release()
+
+
+def test_mi_matrix_against_oracle(engine):
+    from oracle import oracle as orc
+    names, cols, nlev = load_discrete("alarm")
+    d = engine.register(cols, nlev)
+    sel = [3, 7, 12, 20, 33]
+    m = d.mi_matrix("mi", sel)
+    mc = d.mi_matrix("mi", sel, cond=5)
+    n = len(cols[0])
+    for a in range(len(sel)):
+        for b in range(a + 1, len(sel)):
+            i, j = sel[a], sel[b]
+            st, _, _ = orc.ci_discrete("mi", cols[i], nlev[i], cols[j], nlev[j])
+            assert abs(m[a, b] - st / (2 * n)) <= 1e-12 * max(1.0, abs(m[a, b])) and m[a, b] == m[b, a]
+            st, _, _ = orc.ci_discrete("mi", cols[i], nlev[i], cols[j], nlev[j], [cols[5]], [nlev[5]])
+            assert abs(mc[a, b] - st / (2 * n)) <= 1e-12 * max(1.0, abs(mc[a, b]))
+    assert d.mi_matrix("mi", [4]).shape == (1, 1)
+    d.release()

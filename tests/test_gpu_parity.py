@@ -25,7 +25,7 @@ def _check(a, b, what, rtol=RTOL, atol=0.0):
     assert rel_close(a, b, rtol, atol), "%s: got %r, reference %r" % (what, a, b)
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm"])
+@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
 def test_discrete_ci_against_reference_golden(engine, golden, ds):
     names, cols, nlev = load_discrete(ds)
     d = engine.register(cols, nlev)
@@ -40,7 +40,7 @@ def test_discrete_ci_against_reference_golden(engine, golden, ds):
     d.release()
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm"])
+@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
 def test_discrete_scores_against_reference_golden(engine, golden, ds):
     names, cols, nlev = load_discrete(ds)
     d = engine.register(cols, nlev)
@@ -51,6 +51,16 @@ def test_discrete_scores_against_reference_golden(engine, golden, ds):
         sc, _ = d.score_discrete(score, [r["node"] for r in rs], [r["parents"] for r in rs], arg)
         for i, r in enumerate(rs):
             _check(sc[i], r["value"], ("score", r))
+    d.release()
+
+
+def test_nal_of_a_column_without_observed_values(engine):
+    """-Inf, as nal_dnode_root / nal_dnode_parents return for nobs == 0
+    (src/scores/discrete.nal.c:21-22, 52-53)."""
+    empty = [np.full(64, np.iinfo(np.int32).min, dtype=np.int32), np.ones(64, dtype=np.int32)]
+    d = engine.register(empty, [2, 2])
+    sc, _ = d.score_discrete("nal", [0, 1], [[], [0]], 0.0)
+    assert sc[0] == -np.inf and sc[1] == -np.inf
     d.release()
 
 

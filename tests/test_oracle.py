@@ -14,7 +14,7 @@ from util import GOLDEN, load_discrete, load_gaussian, rel_close
 RTOL = 1e-9
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm"])
+@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
 def test_discrete_ci_tests_match_reference(golden, ds):
     names, cols, nlev = load_discrete(ds)
     for rec in golden[ds]["tests"]:
@@ -26,7 +26,7 @@ def test_discrete_ci_tests_match_reference(golden, ds):
         assert rel_close(p, rec["p"], RTOL, 1e-300), (rec, p)
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm"])
+@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
 def test_discrete_scores_match_reference(golden, ds):
     names, cols, nlev = load_discrete(ds)
     for rec in golden[ds]["scores"]:
