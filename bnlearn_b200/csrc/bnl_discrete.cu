@@ -411,7 +411,7 @@ extern "C" int bnl_ci_discrete(bnl_ctx *ctx, bnl_data data, int test_e, int n, c
   if (!ctx) return BNL_EINVAL;
   BnlDataSet *ds = find_data(ctx, data);
   if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
-  if (test_e != BNL_MI && test_e != BNL_MI_ADF && test_e != BNL_X2 && test_e != BNL_X2_ADF)
+  if (!bnl_is_discrete_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a discrete asymptotic test handled here", test_e);
   return bnl_ci_discrete_any(ctx, data, test_e, n, x, y, z_off, z_idx, stat, df, pvalue);
 }

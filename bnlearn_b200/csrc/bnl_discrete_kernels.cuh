@@ -588,6 +588,42 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
     q = s_q;
   }
 
+  // mi-sh: the James-Stein shrinkage intensity needs the whole table first
+  // (mi_lambda, src/tests/discrete/shrinkage.c:138-184): two block-wide passes,
+  // the complete-row count, then sum (n/N)^2 and sum (target - n/N)^2.
+  double sh_lambda = 0.0, sh_target = 0.0, sh_n = 0.0;
+  if (kind == 0 && code == BNL_MI_SH) {
+    const long long cells = (long long)sl * llz;
+    long long loc = 0;
+    for (long long c = threadIdx.x; c < cells; c += BNL_EPI_THREADS) loc += T[c];
+    loc = warp_sum_ll(loc);
+    if (lane == 0) s_n[warp] = loc;
+    __syncthreads();
+    long long ntot = 0;
+    for (int w = 0; w < BNL_EPI_WARPS; w++) ntot += s_n[w];
+    __syncthreads();
+    sh_n = (double)ntot;
+    sh_target = 1.0 / ((double)llx * (double)lly * (double)llz);
+    bnl::KahanSum lnum, lden;
+    if (ntot > 1) {
+      for (long long c = threadIdx.x; c < cells; c += BNL_EPI_THREADS) {
+        const double f = (double)T[c] / sh_n;
+        lnum.add(f * f);
+        lden.add((sh_target - f) * (sh_target - f));
+      }
+    }
+    warp_merge_kahan(lnum);
+    warp_merge_kahan(lden);
+    if (lane == 0) { s_s[warp] = lnum.s; s_c[warp] = lnum.c; s_df[warp] = lden.value(); }
+    __syncthreads();
+    bnl::KahanSum tn;
+    double td = 0.0;
+    for (int w = 0; w < BNL_EPI_WARPS; w++) { tn.merge(s_s[w], s_c[w]); td += s_df[w]; }
+    __syncthreads();
+    sh_lambda = td == 0.0 ? 1.0 : (1.0 - tn.value()) / ((sh_n - 1.0) * td);
+    sh_lambda = fmin(fmax(sh_lambda, 0.0), 1.0);
+  }
+
   bnl::KahanSum acc;
   double dfacc = 0.0;
   long long nobs = 0;
@@ -631,6 +667,70 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
         if (lane == 0) dfacc += (double)(alx - 1) * (double)(aly - 1);
       }
       if (lane == 0) nobs += nk;
+      if (code == BNL_JT) {
+        // Jonckheere-Terpstra (src/tests/discrete/jonckheere.c:98-172): the pair
+        // (i > j) of x levels is one lane's work, with a running prefix over the
+        // y levels instead of the reference's inner re-summation. Every partial
+        // value is a multiple of 1/4, so the sums are exact below 2^51.
+        if (nk > 0) {
+          double st = 0.0;
+          const int npairs = llx * (llx - 1) / 2;
+          for (int pr = lane; pr < npairs; pr += 32) {
+            int i = (int)((1.0 + sqrt(1.0 + 8.0 * (double)pr)) * 0.5);
+            while (i * (i - 1) / 2 > pr) i--;
+            while ((i + 1) * i / 2 <= pr) i++;
+            const int j = pr - i * (i - 1) / 2;
+            double w = 0.0, wi = 0.0;
+            for (int t = 0; t < lly; t++) {
+              const double a = (double)S[i * lly + t], b = (double)S[j * lly + t];
+              w += (wi + (a + b + 1.0) / 2.0) * a;
+              wi += a + b;
+            }
+            const double ni = (double)marg[i];
+            st += w - ni * (ni + 1.0) / 2.0;
+          }
+          st = warp_sum_d(st);
+          if (lane == 0) {
+            const double dn = (double)nk;
+            double mean = dn * dn;       // in double: the reference's int product overflows past 46340 rows
+            for (int i = 0; i < llx; i++) mean -= (double)marg[i] * (double)marg[i];
+            mean /= 4.0;
+            double U1 = dn * (dn - 1.0) * (2.0 * dn + 5.0), U2a = 0.0, U2b = 0.0, U3a = 0.0, U3b = 0.0;
+            for (int i = 0; i < llx; i++) { const double v = (double)marg[i]; U1 -= v * (v - 1.0) * (2.0 * v + 5.0); }
+            for (int j = 0; j < lly; j++) { const double v = (double)marg[llx + j]; U1 -= v * (v - 1.0) * (2.0 * v + 5.0); }
+            for (int i = 0; i < llx; i++) { const double v = (double)marg[i]; U2a += v * (v - 1.0) * (v - 2.0); U3a += v * (v - 1.0); }
+            for (int j = 0; j < lly; j++) { const double v = (double)marg[llx + j]; U2b += v * (v - 1.0) * (v - 2.0); U3b += v * (v - 1.0); }
+            const double var = U1 / 72.0 + U2a * U2b / (36.0 * dn * (dn - 1.0) * (dn - 2.0)) +
+                               U3a * U3b / (8.0 * dn * (dn - 1.0));
+            acc.add(st - mean);
+            // c_jt() divides by the variance as it is; c_cjt() leaves out NaN and
+            // tiny per-stratum variances (:64-65).
+            if (U.ncols == 2 || (!isnan(var) && var > bnl::kSqrtEps)) dfacc += var;
+          }
+        }
+        __syncwarp();
+        continue;
+      }
+      if (code == BNL_MI_SH) {
+        // shrunk cell probabilities lambda * target + (1 - lambda) n / N and their
+        // margins (src/tests/discrete/shrinkage.c:45-66, 112-150).
+        if (sh_n > 1.0) {
+          const double lt = sh_lambda * sh_target, om = (1.0 - sh_lambda) / sh_n;
+          const double pk = (double)sl * lt + om * (double)nk;
+          const bool cond = U.ncols > 2;
+          if (!(cond && pk == 0.0)) {
+            for (int c = lane; c < sl; c += 32) {
+              const double pc = lt + om * (double)S[c];
+              const double pi = (double)lly * lt + om * (double)marg[c / lly];
+              const double pj = (double)llx * lt + om * (double)marg[llx + c % lly];
+              if (cond) { if (pc > 0.0) acc.add(pc * log(pc * pk / (pi * pj))); }
+              else if (pc != 0.0) acc.add(pc * log(pc / (pi * pj)));
+            }
+          }
+        }
+        __syncwarp();
+        continue;
+      }
       if (nk > 0) {
         const double dnk = (double)nk;
         if (code == BNL_MI || code == BNL_MI_ADF || code == BNL_MI_COEF) {
@@ -684,6 +784,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   double *o = out + (size_t)blockIdx.x * 4;
   if (kind == 0) {
     const bool adf = code == BNL_MI_ADF || code == BNL_X2_ADF;
+    const double chan = df;
     if (!adf) df = (double)(llx - 1) * (double)(lly - 1) * (double)llz;
     double stat = 0.0;
     if (n > 0 && !(adf && (double)n < 5.0 * (double)llx * (double)lly * (double)llz)) {
@@ -691,6 +792,15 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
       else if (code == BNL_MI_COEF) stat = tot.value() / (double)n;   // mi_kernel() / nobs
       else stat = tot.value();
     }
+    if (code == BNL_JT) {
+      // standardised statistic, two-sided normal p-value (patterns/utest.c:50-55).
+      const double tv = chan;          // the variance travelled in the df channel
+      if (U.ncols == 2) stat = n <= 1 ? 0.0 : (tv < bnl::kSqrtEps ? 0.0 : tot.value() / sqrt(tv));
+      else stat = tv < bnl::kSqrtEps ? 0.0 : tot.value() / sqrt(tv);
+      o[0] = stat; o[1] = 0.0; o[2] = bnl::pnorm_two_sided(stat); o[3] = (double)n;
+      return;
+    }
+    if (code == BNL_MI_SH) stat = n <= 1 ? 0.0 : tot.value() * (2.0 * (double)n);
     o[0] = stat; o[1] = df; o[2] = bnl::pchisq_upper(stat, df); o[3] = (double)n;
   } else {
     const double nparams = (double)(llx - 1) * (double)llz;

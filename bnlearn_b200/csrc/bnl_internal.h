@@ -138,6 +138,12 @@ void bnl_pool_free(BnlDevice &dev, void *p, size_t bytes);
 // defined in bnl_gaussian.cu: forms means and the covariance matrix on a device.
 int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int dev_index);
 
+// discrete tests computed from the count tables by epilogue_kernel.
+static inline bool bnl_is_discrete_test(int t) {
+  return t == BNL_MI || t == BNL_MI_ADF || t == BNL_X2 || t == BNL_X2_ADF || t == BNL_JT ||
+         t == BNL_MI_SH;
+}
+
 // statistic codes used inside the library only (bnl_mi_matrix): the mutual
 // information COEFFICIENT instead of the G^2 statistic.
 #define BNL_MI_COEF 90

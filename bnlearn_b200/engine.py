@@ -11,10 +11,10 @@ import numpy as np
 
 from . import _lib
 
-TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "cor": 20, "zf": 21, "mi-g": 22}
+TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22}
 SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103}
-DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf")
+DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf", "jt", "mi-sh")
 GAUSSIAN_TESTS = ("cor", "zf", "mi-g")
 DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds", "bdj", "k2", "nal", "pnal")
 GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g")

@@ -36,7 +36,7 @@ void minir_f77_dqrsl(double *x, int *ldx, int *n, int *k, double *qraux,
     int *job, int *info);
 
 /* test_e (src/tests/tests.h:8-36) and score_e (src/scores/scores.h:9-60). */
-enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_COR = 20, T_ZF = 21, T_MI_G = 22 };
+enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_JT = 10, T_MI_SH = 40, T_COR = 20, T_ZF = 21, T_MI_G = 22 };
 enum { S_LOGLIK = 1, S_AIC = 3, S_BIC = 4, S_BDE = 6, S_BDS = 7, S_BDJ = 8, S_K2 = 9,
        S_NAL = 13, S_PNAL = 14,
        S_LOGLIK_G = 100, S_AIC_G = 102, S_BIC_G = 103 };
@@ -153,6 +153,92 @@ done:
  * table, statistic, df, p = pchisq(stat, df, upper). Returns 0, or -1 when the
  * configuration count overflows (the reference raises an R error there,
  * src/core/sets.c:182-183). */
+/* Jonckheere-Terpstra, standardised (src/tests/discrete/jonckheere.c:12-96 for
+ * the two drivers, :98-172 for mean, variance and the statistic). tab is
+ * n[z][x][y]; `conditional` selects c_cjt's handling of unusable strata. The
+ * reference forms num * num in int (:101), which overflows past 46340 complete
+ * rows; this restatement (like the engine) stays in double. */
+static double orc_jt(const int *tab, int llx, int lly, int llz, int conditional) {
+  double centred = 0, tvar = 0;
+  long long nobs = 0;
+  for (int k = 0; k < llz; k++) {
+    const int *n = tab + (size_t)k * llx * lly;
+    double *ni = calloc((size_t)llx, sizeof(double)), *nj = calloc((size_t)lly, sizeof(double));
+    double nk = 0;
+    for (int i = 0; i < llx; i++)
+      for (int j = 0; j < lly; j++) { ni[i] += n[i * lly + j]; nj[j] += n[i * lly + j]; nk += n[i * lly + j]; }
+    nobs += (long long)nk;
+    if (nk > 0) {
+      double stat = 0;
+      for (int i = 1; i < llx; i++)
+        for (int j = 0; j < i; j++) {
+          double w = 0;
+          for (int s = 0; s < lly; s++) {
+            double below = 0;
+            for (int t = 0; t < s; t++) below += n[i * lly + t] + n[j * lly + t];
+            w += (below + ((double)n[i * lly + s] + (double)n[j * lly + s] + 1) / 2) * (double)n[i * lly + s];
+          }
+          stat += w - ni[i] * (ni[i] + 1) / 2;
+        }
+      double mean = nk * nk;
+      for (int i = 0; i < llx; i++) mean -= ni[i] * ni[i];
+      mean /= 4;
+      double U1 = nk * (nk - 1) * (2 * nk + 5), U2a = 0, U2b = 0, U3a = 0, U3b = 0;
+      for (int i = 0; i < llx; i++) U1 -= ni[i] * (ni[i] - 1) * (2 * ni[i] + 5);
+      for (int j = 0; j < lly; j++) U1 -= nj[j] * (nj[j] - 1) * (2 * nj[j] + 5);
+      for (int i = 0; i < llx; i++) { U2a += ni[i] * (ni[i] - 1) * (ni[i] - 2); U3a += ni[i] * (ni[i] - 1); }
+      for (int j = 0; j < lly; j++) { U2b += nj[j] * (nj[j] - 1) * (nj[j] - 2); U3b += nj[j] * (nj[j] - 1); }
+      double var = U1 / 72 + U2a * U2b / (36 * nk * (nk - 1) * (nk - 2)) + U3a * U3b / (8 * nk * (nk - 1));
+      centred += stat - mean;
+      if (!conditional || (!isnan(var) && var > ORC_TOL)) tvar += var;
+    }
+    free(ni); free(nj);
+  }
+  if (!conditional && nobs <= 1) return 0;
+  return tvar < ORC_TOL ? 0 : centred / sqrt(tvar);
+}
+
+/* shrinkage mutual information, scaled to G^2 (src/tests/discrete/shrinkage.c:
+ * 15-76 unconditional, :79-161 conditional, :164-207 for lambda). */
+static double orc_shmi(const int *tab, int llx, int lly, int llz, int conditional) {
+  size_t cells = (size_t)llx * lly * llz;
+  double num = 0, target = 1.0 / ((double)llx * lly * llz);
+  for (size_t c = 0; c < cells; c++) num += tab[c];
+  if (num <= 1) return 0;
+  double lnum = 0, lden = 0;
+  for (size_t c = 0; c < cells; c++) {
+    double f = tab[c] / num;
+    lnum += f * f;
+    lden += (target - f) * (target - f);
+  }
+  double lambda = lden == 0 ? 1 : (1 - lnum) / ((num - 1) * lden);
+  if (lambda > 1) lambda = 1;
+  if (lambda < 0) lambda = 0;
+  double res = 0;
+  double *p = malloc(sizeof(double) * (size_t)llx * lly);
+  double *pi = malloc(sizeof(double) * (size_t)llx), *pj = malloc(sizeof(double) * (size_t)lly);
+  for (int k = 0; k < llz; k++) {
+    const int *n = tab + (size_t)k * llx * lly;
+    double pk = 0;
+    memset(pi, 0, sizeof(double) * (size_t)llx);
+    memset(pj, 0, sizeof(double) * (size_t)lly);
+    for (int i = 0; i < llx; i++)
+      for (int j = 0; j < lly; j++) {
+        double v = lambda * target + (1 - lambda) * n[i * lly + j] / num;
+        p[i * lly + j] = v; pi[i] += v; pj[j] += v; pk += v;
+      }
+    if (conditional && pk == 0) continue;
+    for (int i = 0; i < llx; i++)
+      for (int j = 0; j < lly; j++) {
+        double v = p[i * lly + j];
+        if (conditional) { if (v > 0) res += v * log(v * pk / (pi[i] * pj[j])); }
+        else if (v != 0) res += v * log(v / (pi[i] * pj[j]));
+      }
+  }
+  free(p); free(pi); free(pj);
+  return res * 2 * num;
+}
+
 int orc_ci_discrete(int test, const int *x, int llx, const int *y, int lly,
     const int *const *z, const int *zlev, int nz, int num,
     double *stat, double *df, double *pvalue) {
@@ -165,8 +251,18 @@ int orc_ci_discrete(int test, const int *x, int llx, const int *y, int lly,
   }
   int *tab = malloc((size_t)llx * lly * llz * sizeof(int));
   orc_counts(x, llx, y, lly, cfg, llz, num, tab);
-  *stat = orc_discrete_stat(tab, llx, lly, llz, test, df);
-  *pvalue = Rf_pchisq(*stat, *df, 0, 0);
+  if (test == T_JT) {
+    *stat = orc_jt(tab, llx, lly, llz, nz > 0);
+    *df = 0;
+    *pvalue = 2 * Rf_pnorm5(fabs(*stat), 0, 1, 0, 0);
+  } else if (test == T_MI_SH) {
+    *stat = orc_shmi(tab, llx, lly, llz, nz > 0);
+    *df = (double)(llx - 1) * (double)(lly - 1) * (double)llz;
+    *pvalue = Rf_pchisq(*stat, *df, 0, 0);
+  } else {
+    *stat = orc_discrete_stat(tab, llx, lly, llz, test, df);
+    *pvalue = Rf_pchisq(*stat, *df, 0, 0);
+  }
   free(tab); free(cfg);
   return 0;
 }

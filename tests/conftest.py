@@ -20,4 +20,7 @@ def golden():
     # learning.test with missing cells: the reference's *_with_missing arms and NAL / PNAL
     with open(os.path.join(ROOT, "tests", "golden", "ref_incomplete.json")) as f:
         out.update(json.load(f))
+    # Jonckheere-Terpstra and shrinkage MI on complete data ("data" names the data set)
+    with open(os.path.join(ROOT, "tests", "golden", "ref_jt_shrinkage.json")) as f:
+        out.update(json.load(f))
     return out

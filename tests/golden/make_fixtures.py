@@ -198,9 +198,10 @@ def incomplete_outputs():
         k = int(rng.integers(0, 4))
         idx = rng.choice(p, size=2 + k, replace=False)
         x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
-        for test in ("mi", "x2", "mi-adf", "x2-adf"):
+        for test in ("mi", "x2", "mi-adf", "x2-adf", "jt", "mi-sh"):
             st, df, pv = ra.ci_test(data, names[x], names[y], [names[i] for i in s], test)
-            rec["tests"].append({"test": test, "x": x, "y": y, "z": s, "stat": st, "df": df, "p": pv})
+            rec["tests"].append({"test": test, "x": x, "y": y, "z": s, "stat": st,
+                                 "df": 0.0 if df is None else df, "p": pv})
         rb.reset()
         data.invalidate()
     # the *_with_missing call-site patterns (allsubs.test.c:290-448, roundrobin.test.c:222-344)
@@ -243,6 +244,57 @@ def incomplete_outputs():
     with open(os.path.join(HERE, "ref_incomplete.json"), "w") as f:
         json.dump({"learning_test_na": rec}, f)
     print("wrote ref_incomplete.json")
+
+
+def jt_shrinkage_outputs():
+    """Jonckheere-Terpstra and shrinkage-MI tests on complete data (own file and RNG)."""
+    from oracle import refapi as ra, refbind as rb
+    rng = np.random.default_rng(20261108)
+    out = {}
+    for ds in ("learning_test", "alarm"):
+        names, codes, nlev = load_discrete(ds)
+        data = ra.RefData(list(codes), list(nlev), names)
+        p = len(names)
+        rec = {"data": ds, "tests": [], "scores": [], "allsubs": [], "roundrobin": []}
+        for t in range(30):
+            k = int(rng.integers(0, 4))
+            idx = rng.choice(p, size=2 + k, replace=False)
+            x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+            for test in ("jt", "mi-sh"):
+                st, df, pv = ra.ci_test(data, names[x], names[y], [names[i] for i in s], test)
+                rec["tests"].append({"test": test, "x": x, "y": y, "z": s, "stat": st,
+                                     "df": 0.0 if df is None else df, "p": pv})
+            rb.reset()
+            data.invalidate()
+        for t in range(6):
+            m = int(rng.integers(2, min(5, p - 2) + 1))
+            idx = rng.choice(p, size=2 + m, replace=False)
+            x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+            nf = int(rng.integers(0, 2))
+            mn = int(rng.integers(0, 2))
+            mx = int(rng.integers(max(mn, 1), min(3, m - nf) + 1))
+            for test in ("jt", "mi-sh"):
+                rb.reset_test_counter()
+                pv, pmin, pmax, ds_ = ra.allsubs_test(
+                    data, names[x], names[y], [names[i] for i in s], [names[i] for i in s[:nf]],
+                    test, 0.05, mn, mx)
+                rec["allsubs"].append({"test": test, "x": x, "y": y, "sx": s, "nfixed": nf,
+                                       "min": mn, "max": mx, "alpha": 0.05, "p": pv,
+                                       "pmin": pmin, "pmax": pmax,
+                                       "dsep": None if ds_ is None else [names.index(d) for d in ds_],
+                                       "counter": rb.test_counter()})
+                rb.reset_test_counter()
+                pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + s],
+                                         [names[i] for i in s[:nf]], test, 0.05)
+                rec["roundrobin"].append({"test": test, "x": x, "z": [y] + s, "nfixed": nf,
+                                          "alpha": 0.05, "p": [float(v) for v in pvs],
+                                          "counter": rb.test_counter()})
+            rb.reset()
+            data.invalidate()
+        out[ds + "_jt_sh"] = rec
+    with open(os.path.join(HERE, "ref_jt_shrinkage.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote ref_jt_shrinkage.json")
 
 
 def mi_matrix_outputs():
@@ -300,4 +352,5 @@ if __name__ == "__main__":
     special_function_fixtures()
     reference_outputs()
     incomplete_outputs()
+    jt_shrinkage_outputs()
     mi_matrix_outputs()

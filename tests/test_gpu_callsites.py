@@ -4,6 +4,7 @@ reference's own allsubs_test / roundrobin_test / score_cache_fill."""
 import numpy as np
 import pytest
 
+DISCRETE_SETS = ["learning_test", "alarm", "learning_test_na", "learning_test_jt_sh", "alarm_jt_sh"]
 from util import load_discrete, load_gaussian, rel_close
 
 pytestmark = pytest.mark.gpu
@@ -16,10 +17,10 @@ def engine():
         yield e
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
+@pytest.mark.parametrize("ds", DISCRETE_SETS)
 def test_allsubs_against_reference(engine, golden, ds):
     from bnlearn_b200 import callsites as cs
-    names, cols, nlev = load_discrete(ds)
+    names, cols, nlev = load_discrete(golden[ds].get("data", ds))
     d = engine.register(cols, nlev)
     counter = cs.TestCounter()
     for r in golden[ds]["allsubs"]:
@@ -44,10 +45,10 @@ def test_allsubs_against_reference(engine, golden, ds):
     d.release()
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
+@pytest.mark.parametrize("ds", DISCRETE_SETS)
 def test_roundrobin_against_reference(engine, golden, ds):
     from bnlearn_b200 import callsites as cs
-    names, cols, nlev = load_discrete(ds)
+    names, cols, nlev = load_discrete(golden[ds].get("data", ds))
     d = engine.register(cols, nlev)
     counter = cs.TestCounter()
     for r in golden[ds]["roundrobin"]:

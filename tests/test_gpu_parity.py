@@ -8,6 +8,7 @@ import os
 import numpy as np
 import pytest
 
+DISCRETE_SETS = ["learning_test", "alarm", "learning_test_na", "learning_test_jt_sh", "alarm_jt_sh"]
 from util import GOLDEN, load_discrete, load_gaussian, rel_close
 
 pytestmark = pytest.mark.gpu
@@ -25,12 +26,12 @@ def _check(a, b, what, rtol=RTOL, atol=0.0):
     assert rel_close(a, b, rtol, atol), "%s: got %r, reference %r" % (what, a, b)
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
+@pytest.mark.parametrize("ds", DISCRETE_SETS)
 def test_discrete_ci_against_reference_golden(engine, golden, ds):
-    names, cols, nlev = load_discrete(ds)
+    names, cols, nlev = load_discrete(golden[ds].get("data", ds))
     d = engine.register(cols, nlev)
     recs = golden[ds]["tests"]
-    for test in ("mi", "x2", "mi-adf", "x2-adf"):
+    for test in sorted({r["test"] for r in recs}):
         rs = [r for r in recs if r["test"] == test]
         st, df, pv = d.ci_discrete(test, [r["x"] for r in rs], [r["y"] for r in rs], [r["z"] for r in rs])
         for i, r in enumerate(rs):
@@ -40,9 +41,9 @@ def test_discrete_ci_against_reference_golden(engine, golden, ds):
     d.release()
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
+@pytest.mark.parametrize("ds", DISCRETE_SETS)
 def test_discrete_scores_against_reference_golden(engine, golden, ds):
-    names, cols, nlev = load_discrete(ds)
+    names, cols, nlev = load_discrete(golden[ds].get("data", ds))
     d = engine.register(cols, nlev)
     recs = golden[ds]["scores"]
     keys = sorted({(r["score"], r["arg"]) for r in recs})

@@ -9,14 +9,15 @@ import numpy as np
 import pytest
 
 from oracle import oracle as orc
+DISCRETE_SETS = ["learning_test", "alarm", "learning_test_na", "learning_test_jt_sh", "alarm_jt_sh"]
 from util import GOLDEN, load_discrete, load_gaussian, rel_close
 
 RTOL = 1e-9
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
+@pytest.mark.parametrize("ds", DISCRETE_SETS)
 def test_discrete_ci_tests_match_reference(golden, ds):
-    names, cols, nlev = load_discrete(ds)
+    names, cols, nlev = load_discrete(golden[ds].get("data", ds))
     for rec in golden[ds]["tests"]:
         st, df, p = orc.ci_discrete(rec["test"], cols[rec["x"]], nlev[rec["x"]], cols[rec["y"]],
                                     nlev[rec["y"]], [cols[i] for i in rec["z"]],
@@ -26,9 +27,9 @@ def test_discrete_ci_tests_match_reference(golden, ds):
         assert rel_close(p, rec["p"], RTOL, 1e-300), (rec, p)
 
 
-@pytest.mark.parametrize("ds", ["learning_test", "alarm", "learning_test_na"])
+@pytest.mark.parametrize("ds", DISCRETE_SETS)
 def test_discrete_scores_match_reference(golden, ds):
-    names, cols, nlev = load_discrete(ds)
+    names, cols, nlev = load_discrete(golden[ds].get("data", ds))
     for rec in golden[ds]["scores"]:
         v, _ = orc.score_discrete(rec["score"], cols[rec["node"]], nlev[rec["node"]],
                                   [cols[i] for i in rec["parents"]],
