@@ -200,6 +200,29 @@ class DataSet:
                                            _ip(po), _ip(pi), _dp(sc), _dp(npar)))
         return sc[:n], npar[:n]
 
+    def hc(self, score, arg=0.0, nnodes=None, start=None, blmat=None, wlmat=None, maxp=np.inf,
+           max_iter=0, counter=None):
+        """bnl_hc: the whole greedy search in one library call. Returns
+        (amat, per-node scores, iterations); `counter` (callsites.TestCounter) is
+        advanced by the number of score deltas computed."""
+        e = self.engine
+        n = len(self.nlevels) if nnodes is None else int(nnodes)
+
+        def mat(m):
+            return None if m is None else np.asfortranarray(m, dtype=np.int32)
+        s, b, w = mat(start), mat(blmat), mat(wlmat)
+        amat = np.zeros((n, n), dtype=np.int32, order="F")
+        scores = np.zeros(n)
+        iters = C.c_longlong(0)
+        cnt = C.c_double(0.0)
+        e._check(e._lib.bnl_hc(e._ctx, self.handle, SCORES[score], float(arg), n,
+                               None if s is None else _ip(s), None if b is None else _ip(b),
+                               None if w is None else _ip(w), float(maxp), int(max_iter), _ip(amat),
+                               _dp(scores), C.byref(iters), C.byref(cnt)))
+        if counter is not None:
+            counter.value += cnt.value
+        return amat, scores, iters.value
+
     def mi_matrix(self, estimator, cols, cond=-1):
         """Pairwise mutual-information coefficients of `cols` (optionally given the
         factor `cond`) as a symmetric matrix with a zero diagonal."""

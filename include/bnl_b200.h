@@ -188,6 +188,25 @@ int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *
                      int maxsize, double alpha, double *out, const int *dsep_off, int *dsep,
                      int *ndsep, double *test_counter);
 
+/* The whole of hill.climbing(optimized = TRUE, restart = 0) in one call
+ * (R/hill-climbing.R:2-318: the repeat loop around score_cache_fill and
+ * hc_opt_step, src/learning/score/hc.cache.lookup.c:10-363, with
+ * arcs.to.be.added -> hc_to_be_added :373-489): the score cache lives in the
+ * library between iterations and only the deltas of the nodes touched by the
+ * last move are recomputed. The first nnodes registered columns are the nodes.
+ * start / blmat / wlmat: nnodes x nnodes column-major 0/1 matrices (NULL = empty
+ * graph / no blacklist / no whitelist); maxp: maximum number of parents
+ * (INFINITY for none); max_iter <= 0: no limit. Outputs: amat (column-major),
+ * node_scores[nnodes] (the reference scores of the last network), iterations,
+ * and test_counter advanced as score_delta() would (score.delta.c:278). Moves,
+ * ties (first candidate better by more than sqrt(eps) wins, additions before
+ * removals before reversals) and the rescoring of singular nodes
+ * (R/hill-climbing.R:229-256) follow the reference. */
+int bnl_hc(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss, int nnodes,
+           const int *start, const int *blmat, const int *wlmat, double maxp,
+           long long max_iter, int *amat, double *node_scores, long long *iterations,
+           double *test_counter);
+
 /* estimate_mi_matrix (src/learning/local/mi.matrix.c:184-252 over
  * mi_matrix_discrete :40-137 / mi_matrix_gaussian :141-181), the coefficient
  * matrix behind aracne() and chow.liu(): for the ncols listed columns (all

