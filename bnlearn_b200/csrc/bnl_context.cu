@@ -53,6 +53,43 @@ pack_factors_kernel(const int *__restrict__ src, uint8_t *__restrict__ dst, long
   }
 }
 
+// Row gather for bnl_data_resample: out[c][r] = in[c][rows[r]] for every packed
+// factor column c (blockIdx.y). Reads are random bytes, writes coalesced. A row
+// index outside the source raises flags[0]; an NA that lands in the replicate
+// raises the column's flag so that the NA-free fast paths stay valid.
+__global__ void __launch_bounds__(256)
+gather_u8_kernel(const uint8_t *__restrict__ src, size_t src_stride, long long src_nobs,
+                 uint8_t *__restrict__ dst, size_t dst_stride, const int *__restrict__ rows,
+                 long long nrows, int *__restrict__ flags) {
+  const int c = blockIdx.y;
+  const uint8_t *in = src + src_stride * c;
+  uint8_t *out = dst + dst_stride * c;
+  int saw_na = 0, bad = 0;
+  for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < nrows;
+       r += (long long)gridDim.x * blockDim.x) {
+    const int k = rows[r];
+    if (k < 0 || k >= src_nobs) { bad = 1; continue; }
+    const uint8_t v = in[k];
+    saw_na |= v == BNL_NA_U8;
+    out[r] = v;
+  }
+  if (bad) flags[0] = 1;
+  if (saw_na) flags[1 + c] = 1;
+}
+
+__global__ void __launch_bounds__(256)
+gather_f64_kernel(const double *__restrict__ src, size_t src_stride, long long src_nobs,
+                  double *__restrict__ dst, size_t dst_stride, const int *__restrict__ rows,
+                  long long nrows, int *__restrict__ flags) {
+  const int c = blockIdx.y;
+  for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < nrows;
+       r += (long long)gridDim.x * blockDim.x) {
+    const int k = rows[r];
+    if (k < 0 || k >= src_nobs) { flags[0] = 1; continue; }
+    dst[dst_stride * c + r] = src[src_stride * c + k];
+  }
+}
+
 // ---------------------------------------------------------------------------
 
 extern "C" int bnl_init(bnl_ctx **out, const int *devices, int ndev) {
@@ -451,6 +488,88 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
   }
   cleanup(BNL_OK);
   cudaSetDevice(d0.id);
+  *handle = ctx->next_handle++;
+  ctx->data[*handle] = ds;
+  return BNL_OK;
+}
+
+extern "C" int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, const int *rows,
+                                 bnl_data *handle) {
+  if (!ctx || ctx->devs.empty()) return BNL_EINVAL;
+  if (!handle || nrows < 0 || (nrows > 0 && !rows) || nrows >= (int64_t)INT32_MAX)
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_resample: bad arguments");
+  auto it = ctx->data.find(source);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  const BnlDataSet &src = it->second;
+  if (src.nobs == 0 && nrows > 0)
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_resample: the source data set has no rows");
+
+  BnlDataSet ds;
+  ds.ncols = src.ncols; ds.nd = src.nd; ds.nc = src.nc;
+  ds.nobs = nrows;
+  ds.is_numeric = src.is_numeric; ds.nlevels = src.nlevels; ds.slot = src.slot;
+  ds.stride_u8 = round_up((size_t)nrows + 1, BNL_COL_ALIGN);
+  ds.stride_f64 = round_up((size_t)nrows + 1, 32);
+  ds.dev.resize(ctx->devs.size());
+  ds.slot_has_na.assign(ds.nd, 0);
+  int rc = BNL_OK;
+  auto fail = [&](int code) { free_dataset(ctx, ds); return code; };
+#define RS_CUDA(call)                                                                      \
+  do {                                                                                     \
+    cudaError_t e__ = (call);                                                              \
+    if (e__ != cudaSuccess)                                                                \
+      return fail(bnl_fail(ctx, e__ == cudaErrorMemoryAllocation ? BNL_ENOMEM : BNL_ECUDA, \
+                           "%s failed: %s", #call, cudaGetErrorString(e__)));              \
+  } while (0)
+
+  // every device gathers from its own replica; the row list goes to each of them.
+  std::vector<std::vector<int>> flags(ctx->devs.size(), std::vector<int>(1 + ds.nd, 0));
+  for (size_t d = 0; d < ctx->devs.size(); d++) {
+    BnlDevice &dev = ctx->devs[d];
+    BnlDeviceData &dd = ds.dev[d];
+    const BnlDeviceData &sd = src.dev[d];
+    RS_CUDA(cudaSetDevice(dev.id));
+    if ((rc = bnl_reserve_device(ctx, &dev.stage, &dev.stage_cap, (size_t)nrows + 64))) return fail(rc);
+    if ((rc = bnl_reserve_device(ctx, &dev.d_flags, &dev.flags_cap, (size_t)(1 + ds.nd)))) return fail(rc);
+    RS_CUDA(cudaMemsetAsync(dev.d_flags, 0, (size_t)(1 + ds.nd) * sizeof(int), dev.stream));
+    if (nrows > 0)
+      RS_CUDA(cudaMemcpyAsync(dev.stage, rows, (size_t)nrows * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+    int gx = (int)std::min<long long>((nrows + 255) / 256, (long long)dev.sm_count * 8);
+    if (gx < 1) gx = 1;
+    if (ds.nd > 0) {
+      dd.u8_bytes = ds.stride_u8 * ds.nd;
+      if ((rc = bnl_pool_alloc(ctx, dev, (void **)&dd.u8, dd.u8_bytes))) return fail(rc);
+      RS_CUDA(cudaMemsetAsync(dd.u8, BNL_NA_U8, dd.u8_bytes, dev.stream));
+      if (nrows > 0) {
+        gather_u8_kernel<<<dim3(gx, ds.nd), 256, 0, dev.stream>>>(sd.u8, src.stride_u8, src.nobs, dd.u8,
+                                                                 ds.stride_u8, dev.stage, nrows, dev.d_flags);
+        RS_CUDA(cudaGetLastError());
+      }
+    }
+    if (ds.nc > 0) {
+      dd.f64_bytes = ds.stride_f64 * ds.nc * sizeof(double);
+      if ((rc = bnl_pool_alloc(ctx, dev, (void **)&dd.f64, dd.f64_bytes))) return fail(rc);
+      RS_CUDA(cudaMemsetAsync(dd.f64, 0, dd.f64_bytes, dev.stream));
+      if (nrows > 0) {
+        gather_f64_kernel<<<dim3(gx, ds.nc), 256, 0, dev.stream>>>(sd.f64, src.stride_f64, src.nobs, dd.f64,
+                                                                  ds.stride_f64, dev.stage, nrows, dev.d_flags);
+        RS_CUDA(cudaGetLastError());
+      }
+    }
+    RS_CUDA(cudaMemcpyAsync(flags[d].data(), dev.d_flags, flags[d].size() * sizeof(int),
+                            cudaMemcpyDeviceToHost, dev.stream));
+  }
+  for (size_t d = 0; d < ctx->devs.size(); d++) {
+    RS_CUDA(cudaSetDevice(ctx->devs[d].id));
+    RS_CUDA(cudaStreamSynchronize(ctx->devs[d].stream));
+  }
+#undef RS_CUDA
+  if (flags[0][0]) return fail(bnl_fail(ctx, BNL_EINVAL, "bnl_data_resample: a row index is outside the source data set"));
+  for (int c = 0; c < ds.nd; c++) ds.slot_has_na[c] = flags[0][1 + c];
+  if (ds.nc > 0)
+    for (size_t d = 0; d < ctx->devs.size(); d++)
+      if ((rc = bnl_gaussian_prepare(ctx, ds, (int)d)) != BNL_OK) return fail(rc);
+  cudaSetDevice(ctx->devs[0].id);
   *handle = ctx->next_handle++;
   ctx->data[*handle] = ds;
   return BNL_OK;

@@ -128,6 +128,15 @@ class DataSet:
         self.engine, self.handle, self.nobs, self.nlevels = engine, handle, nobs, list(nlevels)
         self.ncols = len(nlevels)
 
+    def resample(self, rows):
+        """A new DataSet holding rows[...] (0-based, with repeats) of this one,
+        gathered on the device (bnl_data_resample)."""
+        e = self.engine
+        r = np.ascontiguousarray(rows, dtype=np.int32)
+        h = C.c_uint64(0)
+        e._check(e._lib.bnl_data_resample(e._ctx, self.handle, len(r), _ip(r), C.byref(h)))
+        return DataSet(e, h.value, len(r), self.nlevels)
+
     def release(self):
         if self.handle:
             e = self.engine

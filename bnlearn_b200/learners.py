@@ -505,24 +505,38 @@ def vstructures(backend, nnodes, nbr, mb, test, alpha, dsep=None, pvals=None, ma
     return out
 
 
-def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, maxp=np.inf):
+def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, maxp=np.inf,
+                  native=True):
     """boot.strength(algorithm = "hc", cpdag = FALSE): arc strength / direction
     from hc() on bootstrap resamples (R/arc.strength.R:123-227). Resampling uses
     numpy PCG64 streams seed + r (R's own sample() stream needs R). Returns
-    (strength, direction) matrices indexed [from, to] and the total test count."""
+    (strength, direction) matrices indexed [from, to] and the total test count.
+    native: the data frame is uploaded once, each replicate is a device-side row
+    gather (bnl_data_resample) searched by bnl_hc; otherwise every replicate is
+    resampled on the host, registered and searched one call-site at a time."""
+    from .callsites import TestCounter
     n = len(columns)
     nobs = len(columns[0])
     arcs = np.zeros((n, n))
     tests = 0.0
+    src = engine.register(columns, nlevels) if native else None
     for r in range(replicates):
         rng = np.random.Generator(np.random.PCG64(seed + r))
         rows = rng.integers(0, nobs, nobs)
-        ds = engine.register([c[rows] for c in columns], nlevels)
-        be = GpuBackend(ds)
-        amat, _ = hc(be, n, score, arg, maxp)
-        tests += be.counter.value
+        if native:
+            ds = src.resample(rows)
+            counter = TestCounter()
+            amat, _, _ = ds.hc(score, arg, maxp=maxp, counter=counter)
+            tests += counter.value
+        else:
+            ds = engine.register([c[rows] for c in columns], nlevels)
+            be = GpuBackend(ds)
+            amat, _ = hc(be, n, score, arg, maxp)
+            tests += be.counter.value
         arcs += amat
         ds.release()
+    if native:
+        src.release()
     prob = arcs / replicates
     strength = prob + prob.T
     with np.errstate(invalid="ignore", divide="ignore"):

@@ -87,6 +87,13 @@ int bnl_last_call_profile(const bnl_ctx *ctx, double *total_ms, double *count_ms
 int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col,
                       const int *is_numeric, const int *nlevels, int64_t nobs,
                       bnl_data *handle);
+/* A new data set made of rows[0..nrows) (0-based, repeats allowed) of a
+ * registered one, gathered on the device: the bootstrap replicate
+ * `data[resampling, , drop = FALSE]` of bootstrap.backend (R/bootstrap.R:19-36)
+ * and arc.strength.boot (R/arc.strength.R:144-162) without the host-side copy and
+ * the upload of a whole data frame per replicate. Only the row list crosses PCIe. */
+int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, const int *rows,
+                      bnl_data *handle);
 int bnl_data_release(bnl_ctx *ctx, bnl_data handle);
 /* Drop every registered data set; meant to be called from reset_test_counter()
  * (src/test.counter.c:26), which every learner calls first. */

@@ -41,9 +41,12 @@ def config_a(eng, with_ref):
     ds, t_reg = timed(lambda: eng.register(cols, lev))
     be = learners.GpuBackend(ds)
     (amat, scores), t = timed(lambda: learners.hc(be, len(cols), "bic", k))
+    (namat, nscores, niter), tn = timed(lambda: ds.hc("bic", k))
+    (namat, nscores, niter), tn = timed(lambda: ds.hc("bic", k))          # second call: warm
     rec = {"config": "A: hc + BIC, bundled alarm (37 x 20000)", "gpu_wall_s": t, "register_s": t_reg,
            "arcs": int(amat.sum()), "score": float(scores.sum()), "ntests": be.counter.value,
-           "deltas_per_sec": be.counter.value / t}
+           "deltas_per_sec": be.counter.value / t, "native_hc_wall_s": tn,
+           "native_identical_graph": bool(np.array_equal(namat, amat))}
     ds.release()
     if with_ref:
         from refbackend import RefBackend
@@ -91,11 +94,15 @@ def config_c(eng, max_iter):
         return r
     be.score_cache_fill = wrapped
     (amat, scores), t = timed(lambda: learners.hc(be, len(cols), "bde", 1.0, maxp=5, max_iter=max_iter))
+    (namat, _, niter), tn = timed(lambda: ds.hc("bde", 1.0, maxp=5, max_iter=max_iter))
+    (famat, _, fiter), tf = timed(lambda: ds.hc("bde", 1.0, maxp=5))     # to convergence
     true_arcs = sum(len(v) for v in parents.values())
     rec = {"config": "C: hc + BDe, synthetic 1000 factors x 1M rows, maxp 5, max.iter %d" % max_iter,
            "gpu_wall_s": t, "register_s": t_reg, "score_cache_fill_s": dev_ms[0] / 1e3,
            "arcs": int(amat.sum()), "true_arcs": true_arcs, "ntests": be.counter.value,
-           "deltas_per_sec_inside_score_cache_fill": be.counter.value / (dev_ms[0] / 1e3)}
+           "deltas_per_sec_inside_score_cache_fill": be.counter.value / (dev_ms[0] / 1e3),
+           "native_hc_wall_s": tn, "native_identical_graph": bool(np.array_equal(namat, amat)),
+           "native_hc_to_convergence": {"wall_s": tf, "iterations": int(fiter), "arcs": int(famat.sum())}}
     ds.release()
     return rec
 

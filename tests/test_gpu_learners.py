@@ -215,3 +215,42 @@ def test_native_hc_matches_the_stepwise_loop(engine, ds, score, arg, maxp):
     a3, _, it3 = d.hc(score, arg, start=start, blmat=bl, wlmat=wl, maxp=maxp, max_iter=4)
     assert it3 <= 4 and a3[0, 1] == 0 and a3[1, 0] == 0 and (a3[2, 3] == 1 or a3[3, 2] == 1)
     d.release()
+
+
+def test_device_resample_equals_host_resample(engine):
+    """bnl_data_resample (row gather on the device) gives the tables and the search
+    result of registering the host-resampled data frame, with and without NA."""
+    from bnlearn_b200 import learners
+    for name in ("learning_test", "learning_test_na"):
+        names, cols, nlev = load_discrete(name)
+        rows = np.random.default_rng(5).integers(0, len(cols[0]), 4000)
+        src = engine.register(cols, nlev)
+        a = src.resample(rows)
+        b = engine.register([c[rows] for c in cols], nlev)
+        x, y, z = [0, 1, 2], [3, 4, 5], [[1], [], [0, 1]]
+        for ta, tb in zip(a.counts(x, y, z), b.counts(x, y, z)):
+            assert np.array_equal(ta, tb)
+        score = "bic" if name == "learning_test" else "pnal"
+        ra, sa, ia = a.hc(score, 4.0)
+        rb_, sb, ib = b.hc(score, 4.0)
+        assert np.array_equal(ra, rb_) and np.array_equal(sa, sb) and ia == ib
+        with pytest.raises(Exception):
+            src.resample([0, len(cols[0])])
+        for d in (a, b, src):
+            d.release()
+    names, cols = load_gaussian("gaussian_test")
+    rows = np.random.default_rng(6).integers(0, len(cols[0]), 3000)
+    src = engine.register(cols)
+    a, b = src.resample(rows), engine.register([c[rows] for c in cols])
+    ma, mb = a.moments(), b.moments()
+    assert np.array_equal(ma[0], mb[0]) and np.array_equal(ma[1], mb[1])
+    for d in (a, b, src):
+        d.release()
+
+
+def test_boot_strength_native_equals_stepwise(engine):
+    from bnlearn_b200 import learners
+    names, cols, nlev = load_discrete("learning_test")
+    s1 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=True)
+    s2 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=False)
+    assert np.array_equal(s1[0], s2[0]) and np.array_equal(s1[1], s2[1]) and s1[2] == s2[2]
