@@ -327,6 +327,16 @@ extern "C" int bnl_score_cache_fill(bnl_ctx *ctx, bnl_data data, int score_e, do
                                     const int *updated, int nupdated, int equivalence,
                                     const double *reference, double *cache,
                                     double *test_counter) {
+  return bnl_score_cache_fill_np(ctx, data, score_e, k_or_iss, nnodes, amat, blmat, updated, nupdated,
+                                 equivalence, reference, cache, test_counter, nullptr);
+}
+
+// The same with the parent counts supplied by a caller that tracks them (bnl_hc),
+// which saves the n^2 column sums per call.
+int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss, int nnodes,
+                            const int *amat, const int *blmat, const int *updated, int nupdated,
+                            int equivalence, const double *reference, double *cache,
+                            double *test_counter, const int *nparents) {
   if (!ctx) return BNL_EINVAL;
   if (nnodes <= 0 || !amat || !reference || !cache || nupdated < 0 || (nupdated > 0 && !updated))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_cache_fill: bad arguments");
@@ -342,9 +352,12 @@ extern "C" int bnl_score_cache_fill(bnl_ctx *ctx, bnl_data data, int score_e, do
     upd[updated[k]] = 1;
   }
   std::vector<int> colsum(nnodes, 0);
-  if (equivalence)
-    for (int j = 0; j < nnodes; j++)
-      for (int i = 0; i < nnodes; i++) colsum[j] += A(i, j);
+  if (equivalence) {
+    if (nparents) colsum.assign(nparents, nparents + nnodes);
+    else
+      for (int j = 0; j < nnodes; j++)
+        for (int i = 0; i < nnodes; i++) colsum[j] += A(i, j);
+  }
 
   // the candidates that are really scored, in the reference's (i outer, j inner)
   // order; equivalence copies are applied afterwards, in the same order.

@@ -153,6 +153,11 @@ int bnl_ci_discrete_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const in
 int bnl_ci_gaussian_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x, const int *y,
                         const int *z_off, const int *z_idx, double *stat, double *df, double *pvalue);
 
+int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss, int nnodes,
+                            const int *amat, const int *blmat, const int *updated, int nupdated,
+                            int equivalence, const double *reference, double *cache,
+                            double *test_counter, const int *nparents);
+
 // per-call timing of one device block.
 struct BnlTiming { float total = 0.f, count = 0.f, epi = 0.f; int launches = 0; };
 

@@ -229,7 +229,7 @@ class DataSet:
                                None if w is None else _ip(w), float(maxp), int(max_iter), _ip(amat),
                                _dp(scores), C.byref(iters), C.byref(cnt)))
         if counter is not None:
-            counter.value += cnt.value
+            counter.add(cnt.value)
         return amat, scores, iters.value
 
     def mi_matrix(self, estimator, cols, cond=-1):
