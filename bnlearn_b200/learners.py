@@ -506,37 +506,65 @@ def vstructures(backend, nnodes, nbr, mb, test, alpha, dsep=None, pvals=None, ma
 
 
 def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, maxp=np.inf,
-                  native=True):
+                  native=True, workers=4):
     """boot.strength(algorithm = "hc", cpdag = FALSE): arc strength / direction
     from hc() on bootstrap resamples (R/arc.strength.R:123-227). Resampling uses
     numpy PCG64 streams seed + r (R's own sample() stream needs R). Returns
     (strength, direction) matrices indexed [from, to] and the total test count.
     native: the data frame is uploaded once, each replicate is a device-side row
-    gather (bnl_data_resample) searched by bnl_hc; otherwise every replicate is
-    resampled on the host, registered and searched one call-site at a time."""
+    gather (bnl_data_resample) searched by bnl_hc, and `workers` host threads, each
+    with its own context (so its own stream), keep several replicates in flight:
+    one replicate's kernels are far too small to fill the GPU. Otherwise every
+    replicate is resampled on the host, registered and searched one call-site at
+    a time. The result does not depend on `workers`."""
     from .callsites import TestCounter
     n = len(columns)
     nobs = len(columns[0])
-    arcs = np.zeros((n, n))
-    tests = 0.0
-    src = engine.register(columns, nlevels) if native else None
-    for r in range(replicates):
-        rng = np.random.Generator(np.random.PCG64(seed + r))
-        rows = rng.integers(0, nobs, nobs)
-        if native:
-            ds = src.resample(rows)
-            counter = TestCounter()
-            amat, _, _ = ds.hc(score, arg, maxp=maxp, counter=counter)
-            tests += counter.value
-        else:
+
+    def rows_of(r):
+        return np.random.Generator(np.random.PCG64(seed + r)).integers(0, nobs, nobs)
+
+    if not native:
+        arcs, tests = np.zeros((n, n)), 0.0
+        for r in range(replicates):
+            rows = rows_of(r)
             ds = engine.register([c[rows] for c in columns], nlevels)
             be = GpuBackend(ds)
             amat, _ = hc(be, n, score, arg, maxp)
             tests += be.counter.value
-        arcs += amat
-        ds.release()
-    if native:
-        src.release()
+            arcs += amat
+            ds.release()
+    else:
+        from .engine import Engine
+
+        def run(engine_w, share):
+            src = engine_w.register(columns, nlevels)
+            acc, cnt = np.zeros((n, n)), 0.0
+            for r in share:
+                ds = src.resample(rows_of(r))
+                counter = TestCounter()
+                amat, _, _ = ds.hc(score, arg, maxp=maxp, counter=counter)
+                cnt += counter.value
+                acc += amat
+                ds.release()
+            src.release()
+            return acc, cnt
+
+        workers = max(1, min(int(workers), replicates))
+        if workers == 1:
+            arcs, tests = run(engine, range(replicates))
+        else:
+            from concurrent.futures import ThreadPoolExecutor
+            extra = [Engine() for _ in range(workers - 1)]
+            try:
+                with ThreadPoolExecutor(workers) as pool:
+                    parts = list(pool.map(lambda w: run(([engine] + extra)[w], range(w, replicates, workers)),
+                                          range(workers)))
+            finally:
+                for e in extra:
+                    e.close()
+            arcs = sum(p[0] for p in parts)
+            tests = sum(p[1] for p in parts)
     prob = arcs / replicates
     strength = prob + prob.T
     with np.errstate(invalid="ignore", divide="ignore"):

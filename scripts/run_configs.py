@@ -109,10 +109,16 @@ def config_c(eng, max_iter):
 
 def config_e(eng, replicates, with_ref):
     names, cols, lev = synth.insurance_shaped(20000)
-    (res, t) = timed(lambda: learners.boot_strength(eng, cols, lev, replicates, "bde", 1.0, seed=20261109))
+    by_workers = {}
+    for w in (1, 4, 8):
+        (res, t) = timed(lambda: learners.boot_strength(eng, cols, lev, replicates, "bde", 1.0,
+                                                        seed=20261109, workers=w))
+        by_workers[w] = t
     strength, direction, tests = res
+    t = min(by_workers.values())
     rec = {"config": "E: boot.strength R=%d x hc(bde), insurance-shaped (27 x 20000), 1 GPU" % replicates,
            "gpu_wall_s": t, "replicates_per_sec": replicates / t, "ntests": tests,
+           "wall_s_by_host_workers": by_workers,
            "arcs_with_strength_over_0.85": int((strength > 0.85).sum() // 2)}
     if with_ref:
         from refbackend import RefBackend

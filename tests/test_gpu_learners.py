@@ -251,6 +251,8 @@ def test_device_resample_equals_host_resample(engine):
 def test_boot_strength_native_equals_stepwise(engine):
     from bnlearn_b200 import learners
     names, cols, nlev = load_discrete("learning_test")
-    s1 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=True)
+    s1 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=True, workers=3)
+    s3 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=True, workers=1)
+    assert np.array_equal(s1[0], s3[0]) and s1[2] == s3[2]
     s2 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=False)
     assert np.array_equal(s1[0], s2[0]) and np.array_equal(s1[1], s2[1]) and s1[2] == s2[2]
