@@ -1,5 +1,6 @@
 // bnl_gaussian.cu -- host side of the Gaussian entry points.
 #include <string.h>
+#include <cmath>
 #include <algorithm>
 #include <thread>
 
@@ -62,6 +63,10 @@ int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
     ds.h_cov.resize((size_t)p * p);
     BNL_CUDA(ctx, cudaMemcpy(ds.h_mean.data(), dd.mean, (size_t)p * sizeof(double), cudaMemcpyDeviceToHost));
     BNL_CUDA(ctx, cudaMemcpy(ds.h_cov.data(), dd.cov, (size_t)p * p * sizeof(double), cudaMemcpyDeviceToHost));
+    // a column with a missing value has a NaN mean: such data sets take the
+    // per-unit complete-row moments instead of the global matrix (run_gblock).
+    ds.any_nan = false;
+    for (int c = 0; c < p; c++) if (std::isnan(ds.h_mean[c])) ds.any_nan = true;
   }
   return BNL_OK;
 }
@@ -84,6 +89,24 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
   BnlDevice &dev = ctx->devs[d];
   BnlDeviceData &dd = ds.dev[d];
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  // incomplete data: per-unit moments need scratch proportional to units x row
+  // chunks, so long requests are cut into sub-blocks (also: grid.y <= 65535).
+  const bool masked = ds.any_nan;
+  const int m_kb = rq.kmax <= 4 ? 4 : (rq.kmax <= 8 ? 8 : 16);
+  const int m_np = m_kb * (m_kb + 1) / 2;
+  const int m_chunks = (int)std::max(1ll, std::min(256ll, (ds.nobs + 4095) / 4096));
+  const size_t m_per_unit = ((size_t)m_chunks * (BNL_MAXK + 1 + m_np) + (size_t)rq.kmax * (rq.kmax + 1) + 1) *
+                            sizeof(double);
+  if (masked) {
+    const long long max_units = std::max(1ll, std::min(65535ll, (long long)((256ull << 20) / m_per_unit)));
+    if (e - b > max_units) {
+      for (int s = b; s < e; s += (int)max_units) {
+        const int rc = run_gblock(ctx, ds, d, rq, s, std::min(e, s + (int)max_units), tm);
+        if (rc) return rc;
+      }
+      return BNL_OK;
+    }
+  }
   if (!dev.gattr_done) {
     BNL_CUDA(ctx, cudaFuncSetAttribute(gauss_ci_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 1024));
@@ -127,13 +150,48 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
                                 cudaMemcpyHostToDevice, dev.stream));
   const int grid = (cnt + tpb - 1) / tpb;
   BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
+  double *mblock = nullptr, *ucov = nullptr, *umean = nullptr;
+  long long *unobs = nullptr;
+  const size_t mbytes = m_per_unit * (size_t)cnt;
+  if (masked) {
+    if ((rc = bnl_pool_alloc(ctx, dev, (void **)&mblock, mbytes))) return rc;
+    double *part1 = mblock, *part2 = part1 + (size_t)cnt * m_chunks * (BNL_MAXK + 1);
+    umean = part2 + (size_t)cnt * m_chunks * m_np;
+    ucov = umean + (size_t)cnt * rq.kmax;
+    unobs = reinterpret_cast<long long *>(ucov + (size_t)cnt * rq.kmax * rq.kmax);
+    const long long chunk_rows = (ds.nobs + m_chunks - 1) / m_chunks;
+    const int *d_b_or_null = rq.kind == 0 ? d_b : nullptr;
+    const dim3 mg((unsigned)m_chunks, (unsigned)cnt);
+    masked_sums_kernel<<<mg, BNL_MASK_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, chunk_rows, d_a,
+                                                                d_b_or_null, d_off, d_idx, d_slot, ds.ncols, part1);
+    masked_means_kernel<<<(cnt * (rq.kmax + 1) + 127) / 128, 128, 0, dev.stream>>>(part1, m_chunks, cnt, rq.kmax,
+                                                                                   umean, unobs);
+    if (m_kb == 4)
+      masked_cross_kernel<4><<<mg, BNL_MASK_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, chunk_rows,
+          d_a, d_b_or_null, d_off, d_idx, d_slot, ds.ncols, rq.kmax, umean, part2);
+    else if (m_kb == 8)
+      masked_cross_kernel<8><<<mg, BNL_MASK_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, chunk_rows,
+          d_a, d_b_or_null, d_off, d_idx, d_slot, ds.ncols, rq.kmax, umean, part2);
+    else
+      masked_cross_kernel<16><<<mg, BNL_MASK_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, chunk_rows,
+          d_a, d_b_or_null, d_off, d_idx, d_slot, ds.ncols, rq.kmax, umean, part2);
+    masked_cov_kernel<<<(cnt * m_np + 127) / 128, 128, 0, dev.stream>>>(part2, m_chunks, cnt, rq.kmax, m_kb, unobs,
+                                                                        ucov);
+    tm->launches += 4;
+  }
   if (rq.kind == 0)
     gauss_ci_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_b, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, ds.nc,
-                                                     ds.nobs, rq.code, rq.kmax, dev.d_out, d_err);
+                                                     ds.nobs, rq.code, rq.kmax, dev.d_out, d_err, ucov, unobs);
   else
     gauss_score_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, dd.mean,
-                                                        ds.nc, ds.nobs, rq.code, rq.arg, rq.kmax, dev.d_out, d_err);
-  BNL_CUDA(ctx, cudaGetLastError());
+                                                        ds.nc, ds.nobs, rq.code, rq.arg, rq.kmax, dev.d_out, d_err,
+                                                        ucov, umean, unobs);
+  cudaError_t launch_err = cudaGetLastError();
+  if (launch_err != cudaSuccess) {
+    cudaStreamSynchronize(dev.stream);
+    bnl_pool_free(dev, mblock, mbytes);
+    return bnl_fail(ctx, BNL_ECUDA, "Gaussian kernels failed to launch: %s", cudaGetErrorString(launch_err));
+  }
   tm->launches++;
   BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
   BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)cnt * 4 * sizeof(double),
@@ -141,7 +199,10 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
   int err = 0;
   BNL_CUDA(ctx, cudaMemcpyAsync(&err, d_err, sizeof(int), cudaMemcpyDeviceToHost, dev.stream));
   BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
-  BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+  const cudaError_t sync_err = cudaStreamSynchronize(dev.stream);
+  bnl_pool_free(dev, mblock, mbytes);
+  if (sync_err != cudaSuccess)
+    return bnl_fail(ctx, BNL_ECUDA, "Gaussian kernels failed: %s", cudaGetErrorString(sync_err));
   if (err)
     return bnl_fail(ctx, BNL_EINVAL, "unit %d refers to a column that is out of range or not numeric",
                     b + err - 1);
@@ -231,7 +292,8 @@ extern "C" int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, doub
   auto it = ctx->data.find(data);
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   BnlDataSet &ds = it->second;
-  if (score_e != BNL_LOGLIK_G && score_e != BNL_AIC_G && score_e != BNL_BIC_G)
+  if (score_e != BNL_LOGLIK_G && score_e != BNL_AIC_G && score_e != BNL_BIC_G && score_e != BNL_NAL_G &&
+      score_e != BNL_PNAL_G)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a Gaussian score handled here", score_e);
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_gaussian: bad arguments");

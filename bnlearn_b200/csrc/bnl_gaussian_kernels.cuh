@@ -254,7 +254,8 @@ __global__ void gauss_ci_kernel(const int *__restrict__ ux, const int *__restric
                                 const int *__restrict__ zoff, const int *__restrict__ zidx,
                                 const int *__restrict__ slot, int ncols, int n,
                                 const double *__restrict__ cov, int p, long long nobs, int test,
-                                int kmax, double *__restrict__ out, int *__restrict__ err) {
+                                int kmax, double *__restrict__ out, int *__restrict__ err,
+                                const double *__restrict__ ucov, const long long *__restrict__ unobs) {
   extern __shared__ double gsm[];
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= n) return;
@@ -272,6 +273,12 @@ __global__ void gauss_ci_kernel(const int *__restrict__ ux, const int *__restric
     }
   }
   if (bad) { atomicCAS(err, 0, u + 1); o[0] = o[1] = o[2] = o[3] = 0.0; return; }
+  // incomplete data: this unit's own covariance over its complete rows
+  // (ct_gaustests_with_missing, src/tests/patterns/ctest.c:144-229).
+  if (ucov) {
+    cov = ucov + (size_t)u * kmax * kmax; p = kmax; nobs = unobs[u];
+    for (int i = 0; i < k; i++) d[1 + i] = i;
+  }
 
   double df = (test == BNL_COR) ? (double)(nobs - nz - 2)
             : (test == BNL_ZF) ? (double)(nobs - nz - 3) : 1.0;
@@ -333,10 +340,13 @@ __global__ void gauss_score_kernel(const int *__restrict__ target, const int *__
                                    int ncols, int n, const double *__restrict__ cov,
                                    const double *__restrict__ mean, int p, long long nobs,
                                    int score, double kpen, int kmax, double *__restrict__ out,
-                                   int *__restrict__ err) {
+                                   int *__restrict__ err, const double *__restrict__ ucov,
+                                   const double *__restrict__ umean,
+                                   const long long *__restrict__ unobs) {
   extern __shared__ double gsm[];
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= n) return;
+  const long long nrows = nobs;        // the penalty of nal-g / pnal-g uses the full row count
   const int p0 = poff[u], np = poff[u + 1] - p0, k = np + 1;
   double *o = out + (size_t)u * 4;
   const double tol = bnl::kSqrtEps;
@@ -351,6 +361,10 @@ __global__ void gauss_score_kernel(const int *__restrict__ target, const int *__
     }
   }
   if (bad) { atomicCAS(err, 0, u + 1); o[0] = o[1] = o[2] = o[3] = 0.0; return; }
+  if (ucov) {                          // moments over this unit's complete rows (c_ols(..., missing = TRUE))
+    cov = ucov + (size_t)u * kmax * kmax; mean = umean + (size_t)u * kmax; p = kmax; nobs = unobs[u];
+    for (int i = 0; i < k; i++) d[1 + i] = i;
+  }
   const double nm1 = (double)(nobs - 1);
   auto C = [&](int i, int j) { return cov[(size_t)d[1 + i] + (size_t)d[1 + j] * p]; };
 
@@ -416,5 +430,167 @@ __global__ void gauss_score_kernel(const int *__restrict__ target, const int *__
   else res = -(double)nobs * (bnl::kLnSqrt2Pi + log(sd)) - 0.5 * sse / (sd * sd);
   const double nparams = (double)(np + 2);
   if (score == BNL_AIC_G || score == BNL_BIC_G) res -= kpen * nparams;
+  // node-average likelihood (src/scores/gaussian.nal.c:8-78): singular or empty -> -Inf.
+  if (score == BNL_NAL_G || score == BNL_PNAL_G)
+    res = (nobs == 0 || !(sd >= tol)) ? -INFINITY
+          : res / (double)nobs - (score == BNL_PNAL_G ? kpen : 0.0) / (double)nrows * nparams;
   o[0] = res; o[1] = nparams; o[2] = 0.0; o[3] = 0.0;
+}
+
+// ---------------------------------------------------------------------------
+// Incomplete numeric data: moments over the rows that are complete for the
+// columns of ONE unit (c_covmat_with_missing, src/core/covariance.matrix.c:
+// 100-184; c_cor_with_missing, src/core/correlation.c:96-155). Two passes per
+// unit, as in the reference: count + sums -> means, then centred cross-products.
+// A CTA handles (row chunk, unit); partial results are reduced in chunk order by
+// a second kernel, so the result does not depend on scheduling.
+
+#define BNL_MASK_THREADS 256
+
+// columns of unit u in the order the consumers use: x, y, z... (tests) or
+// target, parents... (scores). Returns k, or -1 for a bad unit.
+__device__ __forceinline__ int masked_unit_cols(int u, const int *ua, const int *ub, const int *off,
+                                                const int *idx, const int *slot, int ncols,
+                                                int *cols) {
+  const int lead = ub ? 2 : 1;
+  const int o0 = off[u], nz = off[u + 1] - o0, k = nz + lead;
+  if (nz < 0 || k > BNL_MAXK) return -1;
+  for (int i = 0; i < k; i++) {
+    const int c = i == 0 ? ua[u] : ((ub && i == 1) ? ub[u] : idx[o0 + i - lead]);
+    const int sl = (c >= 0 && c < ncols) ? slot[c] : -1;
+    if (sl < 0) return -1;
+    cols[i] = sl;
+  }
+  return k;
+}
+
+__device__ __forceinline__ double block_sum_256(double v, double *sm) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0.0;
+  if (threadIdx.x < 32) {
+    t = threadIdx.x < BNL_MASK_THREADS / 32 ? sm[threadIdx.x] : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  }
+  return t;      // valid in thread 0
+}
+
+// pass 1: partial[(u * nchunks + chunk) * (BNL_MAXK + 1) + {0: count, 1 + i: sum of column i}]
+__global__ void __launch_bounds__(BNL_MASK_THREADS)
+masked_sums_kernel(const double *__restrict__ data, size_t stride, long long nobs, long long chunk_rows,
+                   const int *__restrict__ ua, const int *__restrict__ ub, const int *__restrict__ off,
+                   const int *__restrict__ idx, const int *__restrict__ slot, int ncols,
+                   double *__restrict__ partial) {
+  __shared__ double sm[BNL_MASK_THREADS / 32];
+  const int u = blockIdx.y, chunk = blockIdx.x, nchunks = gridDim.x;
+  int cols[BNL_MAXK];
+  const int k = masked_unit_cols(u, ua, ub, off, idx, slot, ncols, cols);
+  double *out = partial + ((size_t)u * nchunks + chunk) * (BNL_MAXK + 1);
+  if (k < 0) { if (threadIdx.x <= BNL_MAXK) out[threadIdx.x] = 0.0; return; }
+  const long long r0 = chunk * chunk_rows, r1 = min(nobs, r0 + chunk_rows);
+  double cnt = 0.0, sum[BNL_MAXK];
+#pragma unroll
+  for (int i = 0; i < BNL_MAXK; i++) sum[i] = 0.0;
+  for (long long r = r0 + threadIdx.x; r < r1; r += BNL_MASK_THREADS) {
+    double v[BNL_MAXK];
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < BNL_MAXK; i++)
+      if (i < k) { v[i] = data[stride * cols[i] + r]; ok &= !isnan(v[i]); }
+    if (!ok) continue;
+    cnt += 1.0;
+#pragma unroll
+    for (int i = 0; i < BNL_MAXK; i++) if (i < k) sum[i] += v[i];
+  }
+  double t = block_sum_256(cnt, sm);
+  if (threadIdx.x == 0) out[0] = t;
+#pragma unroll
+  for (int i = 0; i < BNL_MAXK; i++) {
+    if (i < k) {                       // k is uniform over the CTA
+      t = block_sum_256(sum[i], sm);
+      if (threadIdx.x == 0) out[1 + i] = t;
+    }
+  }
+}
+
+// means and complete-row counts from the pass-1 partials (chunk order).
+__global__ void masked_means_kernel(const double *__restrict__ partial, int nchunks, int n, int kmax,
+                                    double *__restrict__ umean, long long *__restrict__ unobs) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int u = t / (kmax + 1), i = t % (kmax + 1);
+  if (u >= n) return;
+  double s = 0.0;
+  for (int c = 0; c < nchunks; c++) s += partial[((size_t)u * nchunks + c) * (BNL_MAXK + 1) + i];
+  if (i == 0) { unobs[u] = (long long)s; return; }
+  double nc = 0.0;
+  for (int c = 0; c < nchunks; c++) nc += partial[((size_t)u * nchunks + c) * (BNL_MAXK + 1)];
+  umean[(size_t)u * kmax + i - 1] = nc > 0.0 ? s / nc : 0.0;
+}
+
+// pass 2: centred cross-products of the complete rows; KB bounds the unit width
+// so that the KB (KB + 1) / 2 accumulators stay in registers for the common
+// narrow units. partial2[(u * nchunks + chunk) * npairs + pair(i <= j)].
+template <int KB>
+__global__ void __launch_bounds__(BNL_MASK_THREADS)
+masked_cross_kernel(const double *__restrict__ data, size_t stride, long long nobs, long long chunk_rows,
+                    const int *__restrict__ ua, const int *__restrict__ ub, const int *__restrict__ off,
+                    const int *__restrict__ idx, const int *__restrict__ slot, int ncols, int kmax,
+                    const double *__restrict__ umean, double *__restrict__ partial2) {
+  __shared__ double sm[BNL_MASK_THREADS / 32];
+  constexpr int NP = KB * (KB + 1) / 2;
+  const int u = blockIdx.y, chunk = blockIdx.x, nchunks = gridDim.x;
+  int cols[BNL_MAXK];
+  const int k = masked_unit_cols(u, ua, ub, off, idx, slot, ncols, cols);
+  double *out = partial2 + ((size_t)u * nchunks + chunk) * NP;
+  if (k < 0 || k > KB) { for (int p = threadIdx.x; p < NP; p += BNL_MASK_THREADS) out[p] = 0.0; return; }
+  double m[KB], acc[NP];
+#pragma unroll
+  for (int i = 0; i < KB; i++) m[i] = i < k ? umean[(size_t)u * kmax + i] : 0.0;
+#pragma unroll
+  for (int p = 0; p < NP; p++) acc[p] = 0.0;
+  const long long r0 = chunk * chunk_rows, r1 = min(nobs, r0 + chunk_rows);
+  for (long long r = r0 + threadIdx.x; r < r1; r += BNL_MASK_THREADS) {
+    double d[KB];
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < KB; i++) {
+      d[i] = 0.0;
+      if (i < k) { const double v = data[stride * cols[i] + r]; ok &= !isnan(v); d[i] = v - m[i]; }
+    }
+    if (!ok) continue;
+    int p = 0;
+#pragma unroll
+    for (int i = 0; i < KB; i++)
+#pragma unroll
+      for (int j = i; j < KB; j++, p++) acc[p] += d[i] * d[j];
+  }
+#pragma unroll
+  for (int p = 0; p < NP; p++) {
+    const double t = block_sum_256(acc[p], sm);
+    if (threadIdx.x == 0) out[p] = t;
+  }
+}
+
+// covariance (divisor nc - 1, as the reference: 0 / 0 when a single row is
+// complete) of every unit, column-major kmax x kmax.
+__global__ void masked_cov_kernel(const double *__restrict__ partial2, int nchunks, int n, int kmax, int kb,
+                                  const long long *__restrict__ unobs, double *__restrict__ ucov) {
+  const int np = kb * (kb + 1) / 2;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int u = t / np, p = t % np;
+  if (u >= n) return;
+  int i = 0, rem = p;
+  while (rem >= kb - i) { rem -= kb - i; i++; }
+  const int j = i + rem;
+  if (j >= kmax) return;
+  double s = 0.0;
+  for (int c = 0; c < nchunks; c++) s += partial2[((size_t)u * nchunks + c) * np + p];
+  const long long nc = unobs[u];
+  const double v = nc == 0 ? 0.0 : s / (double)(nc - 1);
+  ucov[(size_t)u * kmax * kmax + i + (size_t)j * kmax] = v;
+  ucov[(size_t)u * kmax * kmax + j + (size_t)i * kmax] = v;
 }

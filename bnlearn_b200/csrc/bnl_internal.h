@@ -80,6 +80,7 @@ struct BnlDataSet {
   std::vector<int> slot_has_na;         // per packed factor column: any NA?
   std::vector<BnlDeviceData> dev;       // one per context device
   std::vector<double> h_mean, h_cov;    // host copies of the Gaussian moments
+  bool any_nan = false;                 // some numeric column holds a missing value
 };
 
 struct bnl_ctx {

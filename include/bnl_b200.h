@@ -53,7 +53,7 @@ enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4, BNL_JT = 10, BNL_
 /* score_e values handled (src/scores/scores.h:9-60). */
 enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
        BNL_NAL = 13, BNL_PNAL = 14,
-       BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103 };
+       BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103, BNL_NAL_G = 106, BNL_PNAL_G = 107 };
 
 /* ---- context ---------------------------------------------------------- */
 

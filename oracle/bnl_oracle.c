@@ -38,7 +38,7 @@ void minir_f77_dqrsl(double *x, int *ldx, int *n, int *k, double *qraux,
 /* test_e (src/tests/tests.h:8-36) and score_e (src/scores/scores.h:9-60). */
 enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_JT = 10, T_MI_SH = 40, T_COR = 20, T_ZF = 21, T_MI_G = 22 };
 enum { S_LOGLIK = 1, S_AIC = 3, S_BIC = 4, S_BDE = 6, S_BDS = 7, S_BDJ = 8, S_K2 = 9,
-       S_NAL = 13, S_PNAL = 14,
+       S_NAL = 13, S_PNAL = 14, S_NAL_G = 106, S_PNAL_G = 107,
        S_LOGLIK_G = 100, S_AIC_G = 102, S_BIC_G = 103 };
 
 /* ------------------------------------------------------------------------
@@ -472,7 +472,46 @@ double orc_pcor(const double *cov, int p, int *clamped) {
  * Returns 1 if the zero-degrees-of-freedom branch was taken (an R warning in
  * the reference), else 0. `stat` is what the htest object reports: the
  * (partial) correlation for cor, the transformed statistic for zf and mi-g. */
+static int orc_ci_gaussian_complete(int test, const double *const *cols, int p, int n,
+    double *stat, double *df, double *pvalue);
+
+/* rows on which all the p columns are observed, copied out contiguously: what
+ * c_covmat_with_missing (src/core/covariance.matrix.c:100-184) and
+ * c_cor_with_missing (src/core/correlation.c:96-155) restrict themselves to.
+ * Returns the number of complete rows; *out is NULL when nothing is missing. */
+static int orc_complete_rows(const double *const *cols, int p, int n, double ***out) {
+  int nc = 0;
+  char *keep = malloc((size_t)(n > 0 ? n : 1));
+  for (int i = 0; i < n; i++) {
+    keep[i] = 1;
+    for (int j = 0; j < p; j++) if (isnan(cols[j][i])) { keep[i] = 0; break; }
+    nc += keep[i];
+  }
+  *out = NULL;
+  if (nc < n) {
+    double **c = malloc((size_t)p * sizeof(double *));
+    for (int j = 0; j < p; j++) {
+      c[j] = malloc((size_t)(nc > 0 ? nc : 1) * sizeof(double));
+      for (int i = 0, k = 0; i < n; i++) if (keep[i]) c[j][k++] = cols[j][i];
+    }
+    *out = c;
+  }
+  free(keep);
+  return nc;
+}
+
 int orc_ci_gaussian(int test, const double *const *cols, int p, int n,
+    double *stat, double *df, double *pvalue) {
+  double **sub = NULL;
+  int nc = orc_complete_rows(cols, p, n, &sub);
+  if (!sub) return orc_ci_gaussian_complete(test, cols, p, n, stat, df, pvalue);
+  int rc = orc_ci_gaussian_complete(test, (const double *const *)sub, p, nc, stat, df, pvalue);
+  for (int j = 0; j < p; j++) free(sub[j]);
+  free(sub);
+  return rc;
+}
+
+static int orc_ci_gaussian_complete(int test, const double *const *cols, int p, int n,
     double *stat, double *df, double *pvalue) {
   int nz = p - 2;
   double d = (test == T_COR) ? n - nz - 2 : (test == T_ZF) ? n - nz - 3 : 1;
@@ -514,8 +553,34 @@ int orc_ci_gaussian(int test, const double *const *cols, int p, int n,
  * Householder QR otherwise), residual sd with n - p - 1 degrees of freedom,
  * loglik = sum_i dnorm(x_i, fitted_i, sd, log); -Inf when sd < sqrt(eps).
  * `k` is the aic-g / bic-g penalty coefficient (per.node.score.c:137-153). */
+static double orc_score_gaussian_complete(int score, const double *x, const double *const *pa,
+    int np, int n, double k, double *nparams);
+
+/* nal-g / pnal-g (src/scores/gaussian.nal.c:8-78): the log-likelihood of the
+ * locally complete rows, averaged over them, with the penalty scaled by the full
+ * sample size; -Inf for singular fits and for nodes without complete rows. The
+ * other scores go straight to the complete-data code. */
 double orc_score_gaussian(int score, const double *x, const double *const *pa, int np,
     int n, double k, double *nparams) {
+  if (score != S_NAL_G && score != S_PNAL_G)
+    return orc_score_gaussian_complete(score, x, pa, np, n, k, nparams);
+  const double **cols = malloc((size_t)(np + 1) * sizeof(double *));
+  cols[0] = x;
+  for (int j = 0; j < np; j++) cols[1 + j] = pa[j];
+  double **sub = NULL;
+  int nc = orc_complete_rows(cols, np + 1, n, &sub);
+  const double *const *use = sub ? (const double *const *)sub : cols;
+  double ll = nc == 0 ? -INFINITY
+            : orc_score_gaussian_complete(S_LOGLIK_G, use[0], use + 1, np, nc, 0, nparams);
+  if (nparams) *nparams = np + 2;
+  if (sub) { for (int j = 0; j <= np; j++) free(sub[j]); free(sub); }
+  free(cols);
+  if (ll == -INFINITY) return ll;
+  return ll / nc - (score == S_PNAL_G ? k : 0.0) / n * (np + 2);
+}
+
+static double orc_score_gaussian_complete(int score, const double *x, const double *const *pa,
+    int np, int n, double k, double *nparams) {
   double *fitted = malloc((size_t)(n > 0 ? n : 1) * sizeof(double));
   double sd = 0, res = 0;
 

@@ -241,8 +241,37 @@ def incomplete_outputs():
                                   "node": node, "parents": pa, "value": float(v)})
         rb.reset()
         data.invalidate()
+    # ---- gaussian.test (first 2000 rows) with 6% missing cells ----------------
+    gnames, vals = load_gaussian("gaussian_test")
+    vals = vals[:, :2000].copy()
+    vals[rng.random(vals.shape) < 0.06] = np.nan
+    np.savez_compressed(os.path.join(HERE, "data_gaussian_test_na.npz"), names=np.array(gnames),
+                        values=vals)
+    gdata = ra.RefData(list(vals), None, gnames)
+    gp, gn = len(gnames), vals.shape[1]
+    grec = {"tests": [], "scores": []}
+    for t in range(24):
+        k = int(rng.integers(0, 5))
+        idx = rng.choice(gp, size=2 + k, replace=False)
+        x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+        for test in ("cor", "zf", "mi-g"):
+            st, df, pv = ra.ci_test(gdata, gnames[x], gnames[y], [gnames[i] for i in s], test)
+            grec["tests"].append({"test": test, "x": x, "y": y, "z": s, "stat": st, "df": df, "p": pv})
+        rb.reset()
+        gdata.invalidate()
+    for t in range(24):
+        k = int(rng.integers(0, 6))
+        idx = rng.choice(gp, size=1 + k, replace=False)
+        node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+        par = {gnames[node]: [gnames[i] for i in pa]}
+        for score, kw in (("nal-g", {}), ("pnal-g", {"k": np.log(gn) / 2})):
+            v = ra.per_node_score(gdata, par, [gnames[node]], score, **kw)[0]
+            grec["scores"].append({"score": score, "arg": list(kw.values())[0] if kw else 0.0,
+                                   "node": node, "parents": pa, "value": float(v)})
+        rb.reset()
+        gdata.invalidate()
     with open(os.path.join(HERE, "ref_incomplete.json"), "w") as f:
-        json.dump({"learning_test_na": rec}, f)
+        json.dump({"learning_test_na": rec, "gaussian_test_na": grec}, f)
     print("wrote ref_incomplete.json")
 
 

@@ -169,10 +169,11 @@ def test_error_paths(engine):
     big.release()
 
 
-def test_gaussian_ci_against_reference_golden(engine, golden):
-    names, cols = load_gaussian("gaussian_test")
+@pytest.mark.parametrize("ds", ["gaussian_test", "gaussian_test_na"])
+def test_gaussian_ci_against_reference_golden(engine, golden, ds):
+    names, cols = load_gaussian(ds)
     d = engine.register(cols)
-    recs = golden["gaussian_test"]["tests"]
+    recs = golden[ds]["tests"]
     for test in ("cor", "zf", "mi-g"):
         rs = [r for r in recs if r["test"] == test]
         st, df, pv = d.ci_gaussian(test, [r["x"] for r in rs], [r["y"] for r in rs], [r["z"] for r in rs])
@@ -183,16 +184,54 @@ def test_gaussian_ci_against_reference_golden(engine, golden):
     d.release()
 
 
-def test_gaussian_scores_against_reference_golden(engine, golden):
-    names, cols = load_gaussian("gaussian_test")
+@pytest.mark.parametrize("ds", ["gaussian_test", "gaussian_test_na"])
+def test_gaussian_scores_against_reference_golden(engine, golden, ds):
+    names, cols = load_gaussian(ds)
     d = engine.register(cols)
-    recs = golden["gaussian_test"]["scores"]
+    recs = golden[ds]["scores"]
     keys = sorted({(r["score"], r["arg"]) for r in recs})
     for score, arg in keys:
         rs = [r for r in recs if r["score"] == score and r["arg"] == arg]
         sc, _ = d.score_gaussian(score, [r["node"] for r in rs], [r["parents"] for r in rs], arg)
         for i, r in enumerate(rs):
             _check(sc[i], r["value"], ("score", r))
+    d.release()
+
+
+def test_gaussian_incomplete_wide_units_and_edge_cases(engine):
+    """Per-unit complete-row moments: units wider than 8 columns (the spilled
+    variant), a column with no observed value, NAL-G on complete data."""
+    from oracle import oracle as orc
+    rng = np.random.default_rng(21)
+    n, p = 3000, 12
+    base = rng.normal(size=(n, 3))
+    cols = [base @ rng.normal(size=3) + rng.normal(size=n) for _ in range(p)]
+    for c in cols[:6]:
+        c[rng.random(n) < 0.03] = np.nan
+    cols.append(np.full(n, np.nan))
+    d = engine.register(cols)
+    x, y = [0, 1, 2, 12], [3, 4, 5, 0]
+    z = [[6, 7, 8, 9, 10, 11, 1, 2], [0], [], [1]]
+    for test in ("cor", "zf", "mi-g"):
+        st, df, pv = d.ci_gaussian(test, x, y, z)
+        for i in range(len(x)):
+            o = orc.ci_gaussian(test, [cols[x[i]], cols[y[i]]] + [cols[j] for j in z[i]])
+            assert df[i] == o[1]
+            _check(st[i], o[0], (test, i, "stat"), atol=1e-12)
+            _check(pv[i], o[2], (test, i, "p"), atol=1e-300)
+    tg, pa = [0, 7, 12, 3], [[1, 2, 3, 4, 5, 6, 7, 8, 9], [], [], [12]]
+    sc, _ = d.score_gaussian("pnal-g", tg, pa, 2.0)
+    for i in range(len(tg)):
+        o = orc.score_gaussian("pnal-g", cols[tg[i]], [cols[j] for j in pa[i]], 2.0)[0]
+        _check(sc[i], o, ("pnal-g", i))
+    assert sc[2] == -np.inf and sc[3] == -np.inf
+    d.release()
+    names, full = load_gaussian("gaussian_test")
+    d = engine.register(full)
+    sc, _ = d.score_gaussian("nal-g", [0, 5], [[], [0, 1, 2]], 0.0)
+    ll, _ = d.score_gaussian("loglik-g", [0, 5], [[], [0, 1, 2]], 0.0)
+    for a, b in zip(sc, ll):
+        _check(a, b / len(full[0]), "nal-g on complete data")
     d.release()
 
 

@@ -37,9 +37,13 @@ def test_discrete_scores_match_reference(golden, ds):
         assert rel_close(v, rec["value"], RTOL), (rec, v)
 
 
-def test_gaussian_ci_tests_match_reference(golden):
-    names, cols = load_gaussian("gaussian_test")
-    for rec in golden["gaussian_test"]["tests"]:
+GAUSSIAN_SETS = ["gaussian_test", "gaussian_test_na"]
+
+
+@pytest.mark.parametrize("ds", GAUSSIAN_SETS)
+def test_gaussian_ci_tests_match_reference(golden, ds):
+    names, cols = load_gaussian(ds)
+    for rec in golden[ds]["tests"]:
         st, df, p, _ = orc.ci_gaussian(rec["test"], [cols[rec["x"]], cols[rec["y"]]] +
                                        [cols[i] for i in rec["z"]])
         assert df == rec["df"]
@@ -47,9 +51,10 @@ def test_gaussian_ci_tests_match_reference(golden):
         assert rel_close(p, rec["p"], RTOL, 1e-300), (rec, p)
 
 
-def test_gaussian_scores_match_reference(golden):
-    names, cols = load_gaussian("gaussian_test")
-    for rec in golden["gaussian_test"]["scores"]:
+@pytest.mark.parametrize("ds", GAUSSIAN_SETS)
+def test_gaussian_scores_match_reference(golden, ds):
+    names, cols = load_gaussian(ds)
+    for rec in golden[ds]["scores"]:
         v, _ = orc.score_gaussian(rec["score"], cols[rec["node"]],
                                   [cols[i] for i in rec["parents"]], rec["arg"])
         assert rel_close(v, rec["value"], RTOL), (rec, v)
