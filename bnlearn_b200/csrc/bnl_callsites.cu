@@ -105,6 +105,14 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
   const bool gauss = is_gaussian_test(test_e);
   if (!gauss && !is_discrete_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
+  // The subset loops below follow the complete-data patterns. On incomplete
+  // numeric data the reference switches to *_with_missing variants whose
+  // degrees-of-freedom exit depends on each subset's complete rows and whose
+  // early exit is disabled in the source (patterns/allsubs.test.c:419); those are
+  // not restated, single tests (bnl_indep_test / bnl_ci_gaussian) are.
+  if (gauss && it->second.any_nan)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED,
+                    "subset patterns for Gaussian tests on incomplete data are not handled by this engine");
 
   std::vector<AstReq> rq(n);
   for (int r = 0; r < n; r++) {
@@ -288,6 +296,14 @@ extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int 
   const bool gauss = is_gaussian_test(test_e);
   if (!gauss && !is_discrete_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
+  // The subset loops below follow the complete-data patterns. On incomplete
+  // numeric data the reference switches to *_with_missing variants whose
+  // degrees-of-freedom exit depends on each subset's complete rows and whose
+  // early exit is disabled in the source (patterns/allsubs.test.c:419); those are
+  // not restated, single tests (bnl_indep_test / bnl_ci_gaussian) are.
+  if (gauss && it->second.any_nan)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED,
+                    "subset patterns for Gaussian tests on incomplete data are not handled by this engine");
 
   int nfixed = 0;
   for (int i = 0; i < nz; i++) nfixed += is_fixed && is_fixed[i];
