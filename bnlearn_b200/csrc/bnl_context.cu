@@ -185,6 +185,7 @@ static void free_dataset(bnl_ctx *ctx, BnlDataSet &ds) {
     bnl_pool_free(ctx->devs[i], d.f64, d.f64_bytes);
     bnl_pool_free(ctx->devs[i], d.mean, d.mean_bytes);
     bnl_pool_free(ctx->devs[i], d.cov, d.cov_bytes);
+    bnl_pool_free(ctx->devs[i], d.bge_nu, d.nu_bytes);
     d = BnlDeviceData();
   }
   ds.dev.clear();
@@ -508,6 +509,7 @@ extern "C" int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, c
   ds.ncols = src.ncols; ds.nd = src.nd; ds.nc = src.nc;
   ds.nobs = nrows;
   ds.is_numeric = src.is_numeric; ds.nlevels = src.nlevels; ds.slot = src.slot;
+  ds.bge_mu = src.bge_mu; ds.bge_w = src.bge_w;      // nu falls back to the replicate's own means
   ds.stride_u8 = round_up((size_t)nrows + 1, BNL_COL_ALIGN);
   ds.stride_f64 = round_up((size_t)nrows + 1, 32);
   ds.dev.resize(ctx->devs.size());

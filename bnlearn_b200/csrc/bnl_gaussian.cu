@@ -184,8 +184,11 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
                                                      ds.nobs, rq.code, rq.kmax, dev.d_out, d_err, ucov, unobs);
   else
     gauss_score_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, dd.mean,
-                                                        ds.nc, ds.nobs, rq.code, rq.arg, rq.kmax, dev.d_out, d_err,
-                                                        ucov, umean, unobs);
+                                                        ds.nc, ds.nobs, rq.code,
+                                                        rq.code == BNL_BGE ? ds.bge_mu : rq.arg, rq.kmax,
+                                                        dev.d_out, d_err, ucov, umean, unobs,
+                                                        ds.bge_w > 0.0 ? ds.bge_w : (double)(ds.ncols + 2),
+                                                        dd.bge_nu ? dd.bge_nu : dd.mean);
   cudaError_t launch_err = cudaGetLastError();
   if (launch_err != cudaSuccess) {
     cudaStreamSynchronize(dev.stream);
@@ -293,13 +296,51 @@ extern "C" int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, doub
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   BnlDataSet &ds = it->second;
   if (score_e != BNL_LOGLIK_G && score_e != BNL_AIC_G && score_e != BNL_BIC_G && score_e != BNL_NAL_G &&
-      score_e != BNL_PNAL_G)
+      score_e != BNL_PNAL_G && score_e != BNL_BGE)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a Gaussian score handled here", score_e);
+  if (score_e == BNL_BGE && ds.any_nan)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "bge needs complete data (as in the reference's front end)");
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_gaussian: bad arguments");
   if (ds.nc == 0) return bnl_fail(ctx, BNL_EINVAL, "the data set has no numeric columns");
   GRequest rq{1, score_e, k, n, 1, target, nullptr, pa_off, pa_idx, score, nparams, nullptr};
   return run_grequest(ctx, ds, rq);
+}
+
+extern "C" int bnl_set_bge_prior(bnl_ctx *ctx, bnl_data data, double iss_mu, double iss_w,
+                                 const double *nu) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  if (!(iss_mu > 0.0)) return bnl_fail(ctx, BNL_EINVAL, "iss.mu must be positive");
+  // the prior matrix T = t I needs t > 0, i.e. iss.w > ncol + 1 (check.iss.w,
+  // R/sanitization-scores.R:274-291).
+  if (iss_w > 0.0 && !(iss_w > (double)ds.ncols + 1.0))
+    return bnl_fail(ctx, BNL_EINVAL, "iss.w must be larger than the number of columns + 1");
+  ds.bge_mu = iss_mu;
+  ds.bge_w = iss_w;
+  std::vector<double> by_slot(std::max(ds.nc, 1), 0.0);
+  if (nu)
+    for (int c = 0; c < ds.ncols; c++) if (ds.is_numeric[c]) by_slot[ds.slot[c]] = nu[c];
+  for (size_t d = 0; d < ctx->devs.size(); d++) {
+    BnlDevice &dev = ctx->devs[d];
+    BnlDeviceData &dd = ds.dev[d];
+    BNL_CUDA(ctx, cudaSetDevice(dev.id));
+    if (!nu || ds.nc == 0) {
+      bnl_pool_free(dev, dd.bge_nu, dd.nu_bytes);
+      dd.bge_nu = nullptr; dd.nu_bytes = 0;
+      continue;
+    }
+    if (!dd.bge_nu) {
+      dd.nu_bytes = (size_t)ds.nc * sizeof(double);
+      int rc = bnl_pool_alloc(ctx, dev, (void **)&dd.bge_nu, dd.nu_bytes);
+      if (rc) return rc;
+    }
+    BNL_CUDA(ctx, cudaMemcpy(dd.bge_nu, by_slot.data(), (size_t)ds.nc * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  cudaSetDevice(ctx->devs[0].id);
+  return BNL_OK;
 }
 
 extern "C" int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, double *cov) {

@@ -342,7 +342,8 @@ __global__ void gauss_score_kernel(const int *__restrict__ target, const int *__
                                    int score, double kpen, int kmax, double *__restrict__ out,
                                    int *__restrict__ err, const double *__restrict__ ucov,
                                    const double *__restrict__ umean,
-                                   const long long *__restrict__ unobs) {
+                                   const long long *__restrict__ unobs, double bge_w,
+                                   const double *__restrict__ bge_nu) {
   extern __shared__ double gsm[];
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= n) return;
@@ -367,6 +368,52 @@ __global__ void gauss_score_kernel(const int *__restrict__ target, const int *__
   }
   const double nm1 = (double)(nobs - 1);
   auto C = [&](int i, int j) { return cov[(size_t)d[1 + i] + (size_t)d[1 + j] * p]; };
+
+  if (score == BNL_BGE) {
+    // Bayesian Gaussian equivalent score (wpost / cwpost, src/scores/
+    // wishart.posterior.c:10-106): kpen = iss.mu, bge_w = iss.w, bge_nu = prior
+    // means by numeric slot; ncols columns in the data frame. The reference takes
+    // log|R| and log|R~| (R without the node's row and column) from two LU
+    // factorisations; both are SPD here, so one Cholesky with the node LAST gives
+    // log|R~| from the leading block and log|R| = log|R~| + log(Schur complement).
+    const double N = (double)nobs, amu = kpen, aw = bge_w, nc = (double)ncols, pp = (double)np;
+    const double t = amu * (aw - nc - 1.0) / (amu + 1.0);
+    const double shrink = N * amu / (N + amu);
+    double lp = 0.5 * (log(amu) - log(N + amu));
+    lp += bnl::lgamma_pos(0.5 * (N + aw - nc + pp + 1.0)) - bnl::lgamma_pos(0.5 * (aw - nc + pp + 1.0));
+    lp -= 0.5 * N * 1.1447298858494001741434273513531;       // log(pi)
+    if (np == 0) {
+      const double dm = mean[d[1]] - bge_nu[d[1]];
+      const double r = t + C(0, 0) * nm1 + shrink * dm * dm;
+      lp += 0.5 * (aw - nc + 1.0) * log(t) - 0.5 * (N + aw - nc + 1.0) * log(r);
+    } else {
+      lp += 0.5 * (aw - nc + pp + 1.0) * (pp + 1.0) * log(t) - 0.5 * (aw - nc + pp) * pp * log(t);
+      SmemMat R{gsm + threadIdx.x, (int)blockDim.x};
+      auto at = [&](int i) { return i == k - 1 ? 0 : i + 1; };     // position i of R -> unit column
+      for (int i = 0; i < k; i++)
+        for (int j = 0; j < k; j++) {
+          const int a = at(i), b = at(j);
+          R(i + j * k) = C(a, b) * nm1 + (i == j ? t : 0.0) +
+                         shrink * (mean[d[1 + a]] - bge_nu[d[1 + a]]) * (mean[d[1 + b]] - bge_nu[d[1 + b]]);
+        }
+      double ld_tilde = 0.0, ld_last = 0.0;
+      bool singular = false;
+      for (int j = 0; j < k; j++) {                                 // right-looking Cholesky, lower part
+        double piv = R(j + j * k);
+        if (!(piv > 0.0)) { singular = true; break; }
+        if (j < k - 1) ld_tilde += log(piv); else ld_last = log(piv);
+        const double inv = 1.0 / piv;
+        for (int i = j + 1; i < k; i++) {
+          const double f = R(i + j * k) * inv;
+          for (int l = j + 1; l <= i; l++) R(i + l * k) -= f * R(l + j * k);
+        }
+      }
+      if (singular) lp = -INFINITY;
+      else lp += 0.5 * (N + aw - nc + pp) * ld_tilde - 0.5 * (N + aw - nc + pp + 1.0) * (ld_tilde + ld_last);
+    }
+    o[0] = lp; o[1] = (double)(np + 2); o[2] = 0.0; o[3] = 0.0;
+    return;
+  }
 
   double sse = 0.0;      // residual sum of squares of the fit
   double sd;

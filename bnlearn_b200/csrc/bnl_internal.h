@@ -68,7 +68,8 @@ struct BnlDeviceData {
   double *f64 = nullptr;       // nc columns, stride_f64 doubles apart
   double *mean = nullptr;      // nc
   double *cov = nullptr;       // nc x nc, column-major, divisor nobs - 1
-  size_t u8_bytes = 0, f64_bytes = 0, mean_bytes = 0, cov_bytes = 0;
+  double *bge_nu = nullptr;    // nc prior means of the BGe score (null: the column means)
+  size_t u8_bytes = 0, f64_bytes = 0, mean_bytes = 0, cov_bytes = 0, nu_bytes = 0;
 };
 
 struct BnlDataSet {
@@ -81,6 +82,7 @@ struct BnlDataSet {
   std::vector<BnlDeviceData> dev;       // one per context device
   std::vector<double> h_mean, h_cov;    // host copies of the Gaussian moments
   bool any_nan = false;                 // some numeric column holds a missing value
+  double bge_mu = 1.0, bge_w = -1.0;    // BGe imaginary sample sizes (bge_w < 0: ncols + 2)
 };
 
 struct bnl_ctx {

@@ -13,11 +13,11 @@ from . import _lib
 
 TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22}
 SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "nal": 13, "pnal": 14,
-          "loglik-g": 100, "aic-g": 102, "bic-g": 103, "nal-g": 106, "pnal-g": 107}
+          "loglik-g": 100, "aic-g": 102, "bic-g": 103, "bge": 105, "nal-g": 106, "pnal-g": 107}
 DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf", "jt", "mi-sh")
 GAUSSIAN_TESTS = ("cor", "zf", "mi-g")
 DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds", "bdj", "k2", "nal", "pnal")
-GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g", "nal-g", "pnal-g")
+GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g", "bge", "nal-g", "pnal-g")
 NA_INT = np.iinfo(np.int32).min
 
 
@@ -244,6 +244,13 @@ class DataSet:
         iu = np.triu_indices(p, 1)
         m[iu] = tri[:len(iu[0])]
         return m + m.T
+
+    def set_bge_prior(self, iss_mu=1.0, iss_w=0.0, nu=None):
+        """BGe hyper-parameters (iss_w <= 0: ncol + 2; nu None: the column means)."""
+        e = self.engine
+        v = None if nu is None else np.ascontiguousarray(nu, dtype=np.float64)
+        e._check(e._lib.bnl_set_bge_prior(e._ctx, self.handle, float(iss_mu), float(iss_w),
+                                          None if v is None else _dp(v)))
 
     def moments(self):
         """(means, covariance matrix) of the numeric columns, registration order."""

@@ -53,7 +53,8 @@ enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4, BNL_JT = 10, BNL_
 /* score_e values handled (src/scores/scores.h:9-60). */
 enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
        BNL_NAL = 13, BNL_PNAL = 14,
-       BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103, BNL_NAL_G = 106, BNL_PNAL_G = 107 };
+       BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103, BNL_BGE = 105, BNL_NAL_G = 106,
+       BNL_PNAL_G = 107 };
 
 /* ---- context ---------------------------------------------------------- */
 
@@ -87,6 +88,15 @@ int bnl_last_call_profile(const bnl_ctx *ctx, double *total_ms, double *count_ms
 int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col,
                       const int *is_numeric, const int *nlevels, int64_t nobs,
                       bnl_data *handle);
+/* Hyper-parameters of the BGe score (BNL_BGE) for later calls on this data set:
+ * the extra arguments iss.mu, iss.w and nu that per_node_score hands to
+ * wishart_node (src/scores/per.node.score.c:250-266, src/scores/
+ * wishart.posterior.c:108-160). iss_w <= 0 selects the front end's default
+ * ncol(data) + 2, nu == NULL its default colMeans(data) (nu has one entry per
+ * registered column; entries of factor columns are ignored). Uniform graph
+ * prior. The k argument of bnl_score_gaussian is ignored for BNL_BGE. */
+int bnl_set_bge_prior(bnl_ctx *ctx, bnl_data data, double iss_mu, double iss_w, const double *nu);
+
 /* A new data set made of rows[0..nrows) (0-based, repeats allowed) of a
  * registered one, gathered on the device: the bootstrap replicate
  * `data[resampling, , drop = FALSE]` of bootstrap.backend (R/bootstrap.R:19-36)

@@ -672,3 +672,60 @@ penalty:
   if (score == S_AIC_G || score == S_BIC_G) res -= k * (np + 2);
   return res;
 }
+
+/* ------------------------------------------------------------------------
+ * BGe node score (wpost / cwpost, src/scores/wishart.posterior.c:10-106), uniform
+ * graph prior. cols[0] is the node, cols[1..np] its parents, nu[] their prior
+ * means in the same order, data_ncols the width of the whole data frame. The
+ * reference takes the two log-determinants from LAPACK dgetrf
+ * (src/math/linear.algebra.c:9-56); plain Gaussian elimination with partial
+ * pivoting in long double here. */
+static long double orc_logdet(long double *m, int k) {
+  long double ld = 0;
+  for (int c = 0; c < k; c++) {
+    int piv = c;
+    for (int r = c + 1; r < k; r++) if (fabsl(m[r + c * k]) > fabsl(m[piv + c * k])) piv = r;
+    if (m[piv + c * k] == 0) return -INFINITY;
+    if (piv != c)
+      for (int j = 0; j < k; j++) { long double t = m[c + j * k]; m[c + j * k] = m[piv + j * k]; m[piv + j * k] = t; }
+    ld += logl(fabsl(m[c + c * k]));
+    for (int r = c + 1; r < k; r++) {
+      long double f = m[r + c * k] / m[c + c * k];
+      for (int j = c; j < k; j++) m[r + j * k] -= f * m[c + j * k];
+    }
+  }
+  return ld;
+}
+
+double orc_score_bge(const double *const *cols, int np, int n, int data_ncols, double iss_mu,
+    double iss_w, const double *nu) {
+  int k = np + 1;
+  double N = n, t = iss_mu * (iss_w - data_ncols - 1) / (iss_mu + 1);
+  long double lp = 0.5 * (log(iss_mu) - log(N + iss_mu));
+  lp += Rf_lgammafn(0.5 * (N + iss_w - data_ncols + np + 1)) - Rf_lgammafn(0.5 * (iss_w - data_ncols + np + 1));
+  lp -= 0.5 * N * log(M_PI);
+  double *mean = malloc((size_t)k * sizeof(double));
+  for (int j = 0; j < k; j++) mean[j] = orc_mean(cols[j], n);
+  if (np == 0) {
+    long double sse = orc_sse(cols[0], mean[0], n);
+    long double r = t + sse + N * iss_mu / (N + iss_mu) * (mean[0] - nu[0]) * (mean[0] - nu[0]);
+    lp += 0.5 * (iss_w - data_ncols + 1) * log(t) - 0.5 * (N + iss_w - data_ncols + 1) * logl(r);
+  } else {
+    lp += 0.5 * (iss_w - data_ncols + np + 1) * (np + 1) * log(t) - 0.5 * (iss_w - data_ncols + np) * np * log(t);
+    long double *R = malloc((size_t)k * k * sizeof(long double));
+    long double *Rt = malloc((size_t)np * np * sizeof(long double));
+    for (int i = 0; i < k; i++)
+      for (int j = 0; j < k; j++) {
+        long double s = 0;
+        for (int r = 0; r < n; r++) s += (cols[i][r] - mean[i]) * (cols[j][r] - mean[j]);
+        R[i + j * k] = s + (i == j ? t : 0) + N * iss_mu / (N + iss_mu) * (mean[i] - nu[i]) * (mean[j] - nu[j]);
+      }
+    for (int i = 1; i < k; i++)
+      for (int j = 1; j < k; j++) Rt[(i - 1) + (j - 1) * np] = R[i + j * k];
+    lp += 0.5 * (N + iss_w - data_ncols + np) * orc_logdet(Rt, np);
+    lp -= 0.5 * (N + iss_w - data_ncols + np + 1) * orc_logdet(R, k);
+    free(R); free(Rt);
+  }
+  free(mean);
+  return (double)lp;
+}

@@ -54,6 +54,8 @@ def lib():
     L.orc_ci_gaussian.argtypes = [C.c_int, pp_d, C.c_int, C.c_int, c_dbl_p, c_dbl_p, c_dbl_p]
     L.orc_score_gaussian.restype = C.c_double
     L.orc_score_gaussian.argtypes = [C.c_int, c_dbl_p, pp_d, C.c_int, C.c_int, C.c_double, c_dbl_p]
+    L.orc_score_bge.restype = C.c_double
+    L.orc_score_bge.argtypes = [pp_d, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, c_dbl_p]
     L.orc_pcor.restype = C.c_double
     L.orc_pcor.argtypes = [c_dbl_p, C.c_int, c_int_p]
     for name, nargs in (("Rf_lgammafn", 1),):
@@ -151,6 +153,14 @@ def score_gaussian(score, x, pcols=(), k=0.0):
     v = lib().orc_score_gaussian(SCORES[score], _dp(x), ptrs, len(cs), len(x), float(k),
                                  C.byref(npar))
     return v, npar.value
+
+
+def score_bge(x, pcols, data_ncols, iss_mu, iss_w, nu):
+    """BGe score of one node; nu = prior means of [x] + parents."""
+    cs, ptrs = _dcols([x] + list(pcols))
+    nu = np.ascontiguousarray(nu, dtype=np.float64)
+    return lib().orc_score_bge(ptrs, len(cs) - 1, len(cs[0]), int(data_ncols), float(iss_mu),
+                               float(iss_w), _dp(nu))
 
 
 def robust_difference(old, new):

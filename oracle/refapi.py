@@ -46,9 +46,16 @@ class RefData:
         self._df = None
 
 
-def _extra(score=None, k=None, iss=None, B=None):
+def _extra(score=None, k=None, iss=None, B=None, bge=None):
     names, items = [], []
     L = rb.lib()
+    if bge is not None:                       # (iss.mu, iss.w, nu vector, node names)
+        iss_mu, iss_w, nu, nodes = bge
+        nu_s = rb.realvec(np.asarray(nu, dtype=np.float64))
+        rb.set_names(nu_s, list(nodes))
+        names += ["iss.mu", "iss.w", "nu", "prior"]
+        items += [L.Rf_ScalarReal(float(iss_mu)), L.Rf_ScalarReal(float(iss_w)), nu_s,
+                  L.Rf_mkString(b"uniform")]
     if k is not None:
         names.append("k"); items.append(L.Rf_ScalarReal(float(k)))
     if iss is not None:
@@ -57,13 +64,15 @@ def _extra(score=None, k=None, iss=None, B=None):
     return rb.rlist(items, names)
 
 
-def per_node_score(data, parents, targets, score, k=None, iss=None):
+def per_node_score(data, parents, targets, score, k=None, iss=None, bge=None):
     """reference per_node_score (src/scores/per.node.score.c:31-48).
-    parents: {node name: [parent names, in order]}."""
+    parents: {node name: [parent names, in order]}; bge = (iss.mu, iss.w, nu)."""
     L = rb.lib()
     net = rb.network(data.names, parents)
+    if bge is not None:
+        bge = (bge[0], bge[1], bge[2], data.names)
     res = L.per_node_score(net, data.df(), L.Rf_mkString(score.encode()),
-                           rb.strvec(list(targets)), _extra(k=k, iss=iss),
+                           rb.strvec(list(targets)), _extra(k=k, iss=iss, bge=bge),
                            L.Rf_ScalarLogical(0))
     return rb.to_numpy(res)
 

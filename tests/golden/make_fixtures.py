@@ -326,6 +326,33 @@ def jt_shrinkage_outputs():
     print("wrote ref_jt_shrinkage.json")
 
 
+def bge_outputs():
+    """BGe scores on gaussian.test with the front end's default hyper-parameters
+    (iss.mu = 1, iss.w = ncol + 2, nu = column means) and with arbitrary ones."""
+    from oracle import refapi as ra, refbind as rb
+    rng = np.random.default_rng(20261110)
+    names, vals = load_gaussian("gaussian_test")
+    data = ra.RefData(list(vals), None, names)
+    p = len(names)
+    recs = []
+    settings = [(1.0, float(p + 2), [float(v.mean()) for v in vals]),
+                (3.0, float(p + 5), [float(x) for x in rng.normal(size=p)])]
+    for iss_mu, iss_w, nu in settings:
+        for t in range(20):
+            k = int(rng.integers(0, 6))
+            idx = rng.choice(p, size=1 + k, replace=False)
+            node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+            v = ra.per_node_score(data, {names[node]: [names[i] for i in pa]}, [names[node]], "bge",
+                                  bge=(iss_mu, iss_w, nu))[0]
+            recs.append({"iss_mu": iss_mu, "iss_w": iss_w, "nu": nu, "node": node, "parents": pa,
+                         "value": float(v)})
+        rb.reset()
+        data.invalidate()
+    with open(os.path.join(HERE, "ref_bge.json"), "w") as f:
+        json.dump({"gaussian_test": recs}, f)
+    print("wrote ref_bge.json")
+
+
 def mi_matrix_outputs():
     """aracne / chow.liu (and the TAN flavour of chow.liu, given a class variable)
     from the reference on the bundled data sets; own file, no RNG."""
@@ -382,4 +409,5 @@ if __name__ == "__main__":
     reference_outputs()
     incomplete_outputs()
     jt_shrinkage_outputs()
+    bge_outputs()
     mi_matrix_outputs()

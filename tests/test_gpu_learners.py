@@ -183,7 +183,8 @@ def test_mi_matrix_against_oracle(engine):
 
 @pytest.mark.parametrize("ds,score,arg,maxp", [("learning_test", "bic", None, np.inf), ("alarm", "bde", 1.0, np.inf),
                                                ("alarm", "bic", None, 2), ("insurance", "k2", 0.0, 3),
-                                               ("gaussian_test", "bic-g", None, np.inf)])
+                                               ("gaussian_test", "bic-g", None, np.inf),
+                                               ("gaussian_test", "bge", 0.0, np.inf)])
 def test_native_hc_matches_the_stepwise_loop(engine, ds, score, arg, maxp):
     """bnl_hc (the whole search inside the library) against the same search driven
     one .Call-equivalent at a time (learners.hc, itself held to the reference's

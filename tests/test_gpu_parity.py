@@ -198,6 +198,27 @@ def test_gaussian_scores_against_reference_golden(engine, golden, ds):
     d.release()
 
 
+def test_bge_against_reference_golden(engine):
+    with open(os.path.join(GOLDEN, "ref_bge.json")) as f:
+        recs = json.load(f)["gaussian_test"]
+    names, cols = load_gaussian("gaussian_test")
+    d = engine.register(cols)
+    default = [r for r in recs if r["iss_mu"] == 1.0]
+    custom = [r for r in recs if r["iss_mu"] != 1.0]
+    for rs, configure in ((default, lambda: None),
+                          (custom, lambda: d.set_bge_prior(custom[0]["iss_mu"], custom[0]["iss_w"], custom[0]["nu"]))):
+        configure()
+        sc, _ = d.score_gaussian("bge", [r["node"] for r in rs], [r["parents"] for r in rs])
+        for i, r in enumerate(rs):
+            _check(sc[i], r["value"], ("bge", r["node"], r["parents"]))
+    d.set_bge_prior()                                  # back to the defaults
+    sc, _ = d.score_gaussian("bge", [default[0]["node"]], [default[0]["parents"]])
+    _check(sc[0], default[0]["value"], "bge defaults restored")
+    with pytest.raises(Exception):
+        d.set_bge_prior(1.0, len(names))               # iss.w must exceed ncol + 1
+    d.release()
+
+
 def test_gaussian_incomplete_wide_units_and_edge_cases(engine):
     """Per-unit complete-row moments: units wider than 8 columns (the spilled
     variant), a column with no observed value, NAL-G on complete data."""

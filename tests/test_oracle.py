@@ -60,6 +60,16 @@ def test_gaussian_scores_match_reference(golden, ds):
         assert rel_close(v, rec["value"], RTOL), (rec, v)
 
 
+def test_bge_matches_reference():
+    with open(os.path.join(GOLDEN, "ref_bge.json")) as f:
+        recs = json.load(f)["gaussian_test"]
+    names, cols = load_gaussian("gaussian_test")
+    for r in recs:
+        v = orc.score_bge(cols[r["node"]], [cols[i] for i in r["parents"]], len(names), r["iss_mu"],
+                          r["iss_w"], [r["nu"][r["node"]]] + [r["nu"][i] for i in r["parents"]])
+        assert rel_close(v, r["value"], RTOL), (r["node"], r["parents"], v, r["value"])
+
+
 def test_counts_are_bincounts():
     names, cols, nlev = load_discrete("alarm")
     x, y, z1, z2 = 3, 12, 33, 7
