@@ -22,6 +22,10 @@ const long long kKnobChunkRows = env_ll("BNL_CHUNK_ROWS", 0);
 const long long kKnobL2MB = env_ll("BNL_L2_MB", 192);
 const int kKnobMidThreads = (int)env_ll("BNL_MID_THREADS", 1024);
 const long long kKnobGroup = env_ll("BNL_GROUP", 1);
+const long long kKnobGroupThreads = env_ll("BNL_GROUP_THREADS", 512);
+const long long kKnobGroupMinCols = env_ll("BNL_GROUP_MINCOLS", 3);
+const long long kKnobGroupWaves = env_ll("BNL_GROUP_WAVES", 2);
+const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
 const int kMaxBatchUnits = 1 << 16;
@@ -97,7 +101,11 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
-    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<384>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
@@ -144,33 +152,53 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     const int group_smem = dev.max_smem - 8192;
     if (kKnobGroup && ds.nobs >= 65536) {
       auto same_base = [&](const BnlUnit &a, const BnlUnit &b) {
-        // at least three shared columns (a node with two or more parents): below
-        // that the per-unit kernel, with its row-pair mode, is as fast or faster
-        // (scripts/microbench_c.py).
-        if (a.ncols != b.ncols || a.ncols < 4 || a.has_na || b.has_na) return false;
+        // at least two shared columns (a node with one or more parents): for
+        // two-column units the per-unit kernel with its row-pair mode is faster
+        // (scripts/group_sweep.sh: 0.244 vs 0.297 ms on 999 candidates x 1 M rows).
+        if (a.ncols != b.ncols || a.ncols < kKnobGroupMinCols || a.has_na || b.has_na) return false;
         for (int k = 0; k + 1 < a.ncols; k++)
           if (a.col[k] != b.col[k] || a.mul[k] != b.mul[k]) return false;
         return a.mul[a.ncols - 1] == b.mul[b.ncols - 1];
       };
+      // runs of units with the same base columns
+      std::vector<std::pair<int, int>> runs;
       int i = 0;
       while (i < cnt) {
         int j = i + 1;
         while (j < cnt && dev.h_units[j].cells <= 256 && dev.h_units[i].cells <= 256 &&
                same_base(dev.h_units[i], dev.h_units[j])) j++;
-        if (j - i >= 4) {
-          int t0 = i;
-          while (t0 < j) {
-            int t1 = t0, bytes = 0;
-            while (t1 < j && t1 - t0 < BNL_GROUP_MAX && bytes + dev.h_units[t1].cells * 256 <= group_smem) {
-              bytes += dev.h_units[t1].cells * 256;
-              t1++;
-            }
-            tiles.push_back(make_int2((int)gorder.size(), t1 - t0));
-            for (int u = t0; u < t1; u++) { gorder.push_back(u); grouped[u] = 1; }
-            t0 = t1;
-          }
-        }
+        if (j - i >= 4) runs.push_back(std::make_pair(i, j));
         i = j;
+      }
+      // units per tile: more units share more loads, but the CTAs (tiles x row
+      // chunks, one per SM at a time) should also fill whole waves -- 999
+      // candidates make 125 tiles of 8 (84 % of 148 SMs) or 143 tiles of 7 (97 %).
+      int best_u = (int)kKnobGroupUnits;
+      if (!getenv("BNL_GROUP_UNITS") && !runs.empty()) {
+        double best_cost = 1e300;
+        for (int u = BNL_GROUP_MAX; u >= 5; u--) {
+          long long nt = 0;
+          for (auto &r : runs) nt += (r.second - r.first + u - 1) / u;
+          const long long ch = std::max(1ll, (kKnobGroupWaves * dev.sm_count + nt / 2) / nt);
+          const long long ctas = nt * ch;
+          const double eff = (double)ctas / (double)(((ctas + dev.sm_count - 1) / dev.sm_count) * dev.sm_count);
+          const double cost = (1.0 + 0.08 * (double)(BNL_GROUP_MAX - u)) / eff;
+          if (cost < best_cost) { best_cost = cost; best_u = u; }
+        }
+      }
+      for (auto &r : runs) {
+        int t0 = r.first;
+        const int j = r.second;
+        while (t0 < j) {
+          int t1 = t0, bytes = 0;
+          while (t1 < j && t1 - t0 < best_u && bytes + dev.h_units[t1].cells * 256 <= group_smem) {
+            bytes += dev.h_units[t1].cells * 256;
+            t1++;
+          }
+          tiles.push_back(make_int2((int)gorder.size(), t1 - t0));
+          for (int u = t0; u < t1; u++) { gorder.push_back(u); grouped[u] = 1; }
+          t0 = t1;
+        }
       }
     }
     std::vector<int> cls[4];
@@ -260,13 +288,21 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         for (int u = 0; u < t.y; u++) b += dev.h_units[gorder[t.x + u]].cells * 256;
         smem = std::max(smem, b);
       }
-      const long long want = (8ll * dev.sm_count + (long long)tiles.size() - 1) / (long long)tiles.size();
-      long long rows = std::max(65536ll, ds.nobs / std::max(1ll, want));
-      if (kKnobChunkRows) rows = kKnobChunkRows;
-      int ch = (int)std::max(1ll, std::min((ds.nobs + rows - 1) / rows, std::max(1ll, groups / 1024)));
-      count_group_kernel<<<(unsigned)tiles.size() * ch, 1024, (size_t)smem, dev.stream>>>(
-          dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + n_ungrouped, dev.d_tiles, dev.d_tables,
-          (int)tiles.size(), ch);
+      const long long nt = (long long)tiles.size();
+      long long want = std::max(1ll, (kKnobGroupWaves * dev.sm_count + nt / 2) / nt);
+      if (kKnobChunkRows) want = (ds.nobs + kKnobChunkRows - 1) / kKnobChunkRows;
+      // at least 32 groups of 16 rows per thread-pass and chunk, so that clearing and
+      // collapsing the tables stays a small part of a CTA's life.
+      int ch = (int)std::max(1ll, std::min(want, std::max(1ll, groups / (32 * 512))));
+      const unsigned ggrid = (unsigned)tiles.size() * ch;
+#define BNL_GROUP_LAUNCH(NT)                                                                          \
+      count_group_kernel<NT><<<ggrid, NT, (size_t)smem, dev.stream>>>(                                  \
+          dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + n_ungrouped, dev.d_tiles, dev.d_tables, \
+          (int)tiles.size(), ch)
+      if (kKnobGroupThreads == 1024) BNL_GROUP_LAUNCH(1024);
+      else if (kKnobGroupThreads == 384) BNL_GROUP_LAUNCH(384);
+      else BNL_GROUP_LAUNCH(512);
+#undef BNL_GROUP_LAUNCH
       BNL_CUDA(ctx, cudaGetLastError());
       tm->launches++;
     }
@@ -319,8 +355,12 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                       dev.stream));
       BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
     } else {
-      epilogue_kernel<<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
-                                                               rq.kind, rq.code, rq.arg, ds.nobs);
+      if (rq.kind == 0 && (rq.code == BNL_JT || rq.code == BNL_MI_SH))
+        epilogue_kernel<true><<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
+                                                                     rq.kind, rq.code, rq.arg, ds.nobs);
+      else
+        epilogue_kernel<false><<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
+                                                                      rq.kind, rq.code, rq.arg, ds.nobs);
       BNL_CUDA(ctx, cudaGetLastError());
       tm->launches++;
       BNL_CUDA(ctx, cudaEventRecord(dev.eve1, dev.stream));

@@ -447,7 +447,21 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 // in shared memory (unit j at tile_off[j] bytes).
 #define BNL_GROUP_MAX 8
 
-__global__ void __launch_bounds__(1024)
+// The loads of the next 16-row group are issued before the current group is
+// counted (software pipelining in registers): with the tables filling the shared
+// memory only one CTA fits an SM, and without the overlap every warp sat out a
+// full DRAM round trip per group (ncu: long-scoreboard stalls on top, LSU pipe
+// under 50 %). NT threads per CTA; fewer threads leave the registers for the
+// second set of loads. Up to BNL_GROUP_PB shared columns are prefetched raw.
+#define BNL_GROUP_PB 4
+
+struct GroupRegs {
+  uint4 base[BNL_GROUP_PB];
+  uint4 cand[BNL_GROUP_MAX];
+};
+
+template <int NT>
+__global__ void __launch_bounds__(NT)
 count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
                    const int2 *__restrict__ tiles, int *__restrict__ tables, int ntiles, int chunks) {
@@ -474,12 +488,13 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     s_off[nu] = o;
   }
   __syncthreads();
-  const int total_words = s_off[nu] >> 2;
-  for (int c = threadIdx.x; c < total_words; c += blockDim.x) hist[c] = 0;
+  const int total_quads = s_off[nu] >> 4;
+  for (int c = threadIdx.x; c < total_quads; c += NT) reinterpret_cast<uint4 *>(hist)[c] = make_uint4(0, 0, 0, 0);
   __syncthreads();
 
   const unsigned slot4 = ((threadIdx.x & 31u) + 32u * ((threadIdx.x >> 5) & 1u)) << 2;
   const int nbase = su.ncols - 1;                      // shared columns
+  const int npre = nbase < BNL_GROUP_PB ? nbase : BNL_GROUP_PB;
   const unsigned cmul = (unsigned)su.mul[nbase];       // = number of base cells
   const long long full = nobs / 16;
   const long long per = (full + chunks - 1) / chunks;
@@ -487,26 +502,44 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   long long g1 = g0 + per;
   if (g1 > full) g1 = full;
 
-  for (long long g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
-    uint4 vb = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[0] * stride) + g);
-    for (int k = 1; k < nbase; k++) {
+  auto load = [&](GroupRegs &R, long long g) {
+#pragma unroll
+    for (int k = 0; k < BNL_GROUP_PB; k++)
+      if (k < npre) R.base[k] = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
+#pragma unroll
+    for (int j = 0; j < BNL_GROUP_MAX; j++)
+      if (j < nu) R.cand[j] = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)s_col[j] * stride) + g);
+  };
+
+  GroupRegs cur, nxt;
+  long long g = g0 + threadIdx.x;
+  if (g < g1) load(cur, g);
+  while (g < g1) {
+    const long long gn = g + NT;
+    if (gn < g1) load(nxt, gn);
+    uint4 vb = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int k = 0; k < BNL_GROUP_PB; k++)
+      if (k < npre) {
+        const unsigned m = (unsigned)su.mul[k];
+        vb.x += cur.base[k].x * m; vb.y += cur.base[k].y * m; vb.z += cur.base[k].z * m; vb.w += cur.base[k].w * m;
+      }
+    for (int k = BNL_GROUP_PB; k < nbase; k++) {       // wide parent sets: the rest is loaded here
       const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
       const unsigned m = (unsigned)su.mul[k];
       vb.x += w.x * m; vb.y += w.y * m; vb.z += w.z * m; vb.w += w.w * m;
     }
-    uint4 wc[BNL_GROUP_MAX];
-#pragma unroll
-    for (int j = 0; j < BNL_GROUP_MAX; j++)
-      if (j < nu) wc[j] = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)s_col[j] * stride) + g);
 #pragma unroll
     for (int j = 0; j < BNL_GROUP_MAX; j++)
       if (j < nu) {
         int *hj = reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + s_off[j]);
-        small_bump(hj, vb.x + wc[j].x * cmul, slot4);
-        small_bump(hj, vb.y + wc[j].y * cmul, slot4);
-        small_bump(hj, vb.z + wc[j].z * cmul, slot4);
-        small_bump(hj, vb.w + wc[j].w * cmul, slot4);
+        small_bump(hj, vb.x + cur.cand[j].x * cmul, slot4);
+        small_bump(hj, vb.y + cur.cand[j].y * cmul, slot4);
+        small_bump(hj, vb.z + cur.cand[j].z * cmul, slot4);
+        small_bump(hj, vb.w + cur.cand[j].w * cmul, slot4);
       }
+    cur = nxt;
+    g = gn;
   }
   // the partial group at the end of the data, once, straight into the global tables.
   if (chunk == chunks - 1 && threadIdx.x < nu && full * 16 < nobs) {
@@ -522,7 +555,7 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   for (int j = 0; j < nu; j++) {
     const int *hj = reinterpret_cast<const int *>(reinterpret_cast<const char *>(hist) + s_off[j]);
     int *gtab = tables + s_tab[j];
-    for (int c = threadIdx.x; c < s_cells[j]; c += blockDim.x) {
+    for (int c = threadIdx.x; c < s_cells[j]; c += NT) {
       int sum = 0;
 #pragma unroll
       for (int l = 0; l < 64; l++) sum += hj[c * 64 + ((l + threadIdx.x) & 63)];
@@ -556,6 +589,9 @@ __device__ __forceinline__ void warp_merge_kahan(bnl::KahanSum &k) {
   }
 }
 
+// EXT compiles in the Jonckheere-Terpstra and shrinkage-MI branches; the common
+// statistics keep their own, leaner instantiation (the extra code costs registers).
+template <bool EXT>
 __global__ void __launch_bounds__(BNL_EPI_THREADS)
 epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ tables,
                 double *__restrict__ out, int kind, int code, double arg, long long nrows) {
@@ -592,7 +628,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   // (mi_lambda, src/tests/discrete/shrinkage.c:138-184): two block-wide passes,
   // the complete-row count, then sum (n/N)^2 and sum (target - n/N)^2.
   double sh_lambda = 0.0, sh_target = 0.0, sh_n = 0.0;
-  if (kind == 0 && code == BNL_MI_SH) {
+  if (EXT && kind == 0 && code == BNL_MI_SH) {
     const long long cells = (long long)sl * llz;
     long long loc = 0;
     for (long long c = threadIdx.x; c < cells; c += BNL_EPI_THREADS) loc += T[c];
@@ -640,7 +676,29 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   const double lg_alpha = is_bd ? bnl::lgamma_pos(alpha) : 0.0;
   const double lg_aq = is_bd ? bnl::lgamma_pos(aq) : 0.0;
 
-  for (int k = warp; k < llz; k += BNL_EPI_WARPS) {
+  // Scores of narrow nodes (a stratum = one parent configuration holds only llx
+  // cells): one LANE per stratum, otherwise a warp would run with 2-4 active lanes
+  // through the lgamma / log terms.
+  const bool lane_strata = kind == 1 && sl <= 16;
+  if (lane_strata) {
+    for (int k = threadIdx.x; k < llz; k += BNL_EPI_THREADS) {
+      const int *S = T + (size_t)k * sl;
+      long long nk = 0;
+      for (int c = 0; c < sl; c++) nk += S[c];
+      nobs += nk;
+      if (is_bd) {
+        if (q == 0 || (code == BNL_BDS && nk == 0)) continue;
+        for (int c = 0; c < sl; c++) acc.add(bnl::lgamma_pos((double)S[c] + alpha) - lg_alpha);
+        acc.add(lg_aq - bnl::lgamma_pos((double)nk + aq));
+      } else if (nk > 0) {
+        for (int c = 0; c < sl; c++) {
+          const int n = S[c];
+          if (n) acc.add((double)n * log((double)n / (double)nk));
+        }
+      }
+    }
+  }
+  for (int k = lane_strata ? llz : warp; k < llz; k += BNL_EPI_WARPS) {
     const int *S = T + (size_t)k * sl;
     if (kind == 0) {
       for (int i = lane; i < llx + lly; i += 32) marg[i] = 0;
@@ -667,7 +725,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
         if (lane == 0) dfacc += (double)(alx - 1) * (double)(aly - 1);
       }
       if (lane == 0) nobs += nk;
-      if (code == BNL_JT) {
+      if (EXT && code == BNL_JT) {
         // Jonckheere-Terpstra (src/tests/discrete/jonckheere.c:98-172): the pair
         // (i > j) of x levels is one lane's work, with a running prefix over the
         // y levels instead of the reference's inner re-summation. Every partial
@@ -711,7 +769,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
         __syncwarp();
         continue;
       }
-      if (code == BNL_MI_SH) {
+      if (EXT && code == BNL_MI_SH) {
         // shrunk cell probabilities lambda * target + (1 - lambda) n / N and their
         // margins (src/tests/discrete/shrinkage.c:45-66, 112-150).
         if (sh_n > 1.0) {
@@ -792,7 +850,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
       else if (code == BNL_MI_COEF) stat = tot.value() / (double)n;   // mi_kernel() / nobs
       else stat = tot.value();
     }
-    if (code == BNL_JT) {
+    if (EXT && code == BNL_JT) {
       // standardised statistic, two-sided normal p-value (patterns/utest.c:50-55).
       const double tv = chan;          // the variance travelled in the df channel
       if (U.ncols == 2) stat = n <= 1 ? 0.0 : (tv < bnl::kSqrtEps ? 0.0 : tot.value() / sqrt(tv));
@@ -800,7 +858,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
       o[0] = stat; o[1] = 0.0; o[2] = bnl::pnorm_two_sided(stat); o[3] = (double)n;
       return;
     }
-    if (code == BNL_MI_SH) stat = n <= 1 ? 0.0 : tot.value() * (2.0 * (double)n);
+    if (EXT && code == BNL_MI_SH) stat = n <= 1 ? 0.0 : tot.value() * (2.0 * (double)n);
     o[0] = stat; o[1] = df; o[2] = bnl::pchisq_upper(stat, df); o[3] = (double)n;
   } else {
     const double nparams = (double)(llx - 1) * (double)llz;
