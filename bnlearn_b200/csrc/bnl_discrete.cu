@@ -150,7 +150,11 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     std::vector<int2> tiles;
     std::vector<int> gorder;
     const int group_smem = dev.max_smem - 8192;
-    if (kKnobGroup && ds.nobs >= 65536) {
+    // Score requests only: on pc.stable's mixed test batches (many tiny tables that
+    // count row pairs, 29 units per distinct column kept hot in L2) the extra launch
+    // and the lost pair mode cost more than the shared loads save (config B: 2.58 ms
+    // ungrouped, 2.64-2.79 ms grouped).
+    if (kKnobGroup && rq.kind == 1 && ds.nobs >= 65536) {
       auto same_base = [&](const BnlUnit &a, const BnlUnit &b) {
         // at least two shared columns (a node with one or more parents): for
         // two-column units the per-unit kernel with its row-pair mode is faster
