@@ -351,7 +351,16 @@ __device__ __forceinline__ void small_dispatch(const uint8_t *__restrict__ u8, s
     case 2: small_rows<2, NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1); break;
     case 3: small_rows<3, NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1); break;
     case 4: small_rows<4, NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1); break;
-    default: small_rows_any<NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1);
+    default:
+      // nodes with 3-6 parents (mid-size tables only; in the small-table kernel the
+      // extra instantiations cost config B 1 ms, scripts/group_sweep.sh): all loads of
+      // a 16-row group issued together -- the generic loop uses each column as it
+      // arrives, one round trip after the other.
+      if (W16 && su.ncols == 5) small_rows<5, NA, W16, false>(u8, stride, su, hist, slot4, g0, g1);
+      else if (W16 && su.ncols == 6) small_rows<6, NA, W16, false>(u8, stride, su, hist, slot4, g0, g1);
+      else if (W16 && su.ncols == 7) small_rows<7, NA, W16, false>(u8, stride, su, hist, slot4, g0, g1);
+      else if (W16 && su.ncols == 8) small_rows<8, NA, W16, false>(u8, stride, su, hist, slot4, g0, g1);
+      else small_rows_any<NA, W16, PAIR>(u8, stride, su, hist, slot4, g0, g1);
   }
 }
 
