@@ -506,7 +506,7 @@ def vstructures(backend, nnodes, nbr, mb, test, alpha, dsep=None, pvals=None, ma
 
 
 def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, maxp=np.inf,
-                  native=True, workers=4):
+                  native=True, workers=4, devices=None):
     """boot.strength(algorithm = "hc", cpdag = FALSE): arc strength / direction
     from hc() on bootstrap resamples (R/arc.strength.R:123-227). Resampling uses
     numpy PCG64 streams seed + r (R's own sample() stream needs R). Returns
@@ -516,7 +516,11 @@ def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, 
     with its own context (so its own stream), keep several replicates in flight:
     one replicate's kernels are far too small to fill the GPU. Otherwise every
     replicate is resampled on the host, registered and searched one call-site at
-    a time. The result does not depend on `workers`."""
+    a time. `devices` (CUDA ordinals) spreads the workers over several GPUs --
+    replicate r goes to worker r mod workers, worker w to devices[w mod ndev]
+    (the reference gives each cluster slave ceil(R/s) replicates,
+    R/arc.strength.R:210) -- and `engine` is then only used when devices is None.
+    The result depends neither on `workers` nor on `devices`."""
     from .callsites import TestCounter
     n = len(columns)
     nobs = len(columns[0])
@@ -551,14 +555,18 @@ def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, 
             return acc, cnt
 
         workers = max(1, min(int(workers), replicates))
-        if workers == 1:
+        if workers == 1 and devices is None:
             arcs, tests = run(engine, range(replicates))
         else:
             from concurrent.futures import ThreadPoolExecutor
-            extra = [Engine() for _ in range(workers - 1)]
+            if devices is None:
+                pool_engines, extra = [engine], [Engine() for _ in range(workers - 1)]
+            else:
+                pool_engines, extra = [], [Engine([int(devices[w % len(devices)])]) for w in range(workers)]
+            pool_engines += extra
             try:
                 with ThreadPoolExecutor(workers) as pool:
-                    parts = list(pool.map(lambda w: run(([engine] + extra)[w], range(w, replicates, workers)),
+                    parts = list(pool.map(lambda w: run(pool_engines[w], range(w, replicates, workers)),
                                           range(workers)))
             finally:
                 for e in extra:

@@ -114,6 +114,12 @@ def config_e(eng, replicates, with_ref):
         (res, t) = timed(lambda: learners.boot_strength(eng, cols, lev, replicates, "bde", 1.0,
                                                         seed=20261109, workers=w))
         by_workers[w] = t
+    import torch
+    ndev = torch.cuda.device_count()
+    if ndev > 1:
+        (res, tm) = timed(lambda: learners.boot_strength(eng, cols, lev, replicates, "bde", 1.0, seed=20261109,
+                                                         workers=8 * ndev, devices=list(range(ndev))))
+        by_workers["%d gpus x 8" % ndev] = tm
     strength, direction, tests = res
     t = min(by_workers.values())
     rec = {"config": "E: boot.strength R=%d x hc(bde), insurance-shaped (27 x 20000), 1 GPU" % replicates,

@@ -255,5 +255,9 @@ def test_boot_strength_native_equals_stepwise(engine):
     s1 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=True, workers=3)
     s3 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=True, workers=1)
     assert np.array_equal(s1[0], s3[0]) and s1[2] == s3[2]
+    import torch
+    devs = list(range(torch.cuda.device_count()))
+    s4 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, workers=4, devices=devs)
+    assert np.array_equal(s1[0], s4[0]) and s1[2] == s4[2]
     s2 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=False)
     assert np.array_equal(s1[0], s2[0]) and np.array_equal(s1[1], s2[1]) and s1[2] == s2[2]
