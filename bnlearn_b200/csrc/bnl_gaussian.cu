@@ -91,11 +91,12 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
   // incomplete data: per-unit moments need scratch proportional to units x row
   // chunks, so long requests are cut into sub-blocks (also: grid.y <= 65535).
-  const bool masked = ds.any_nan;
+  const bool shrink = rq.kind == 0 && rq.code == BNL_MI_G_SH;     // needs a pass over the rows per unit
+  const bool masked = ds.any_nan || shrink;
   const int m_kb = rq.kmax <= 4 ? 4 : (rq.kmax <= 8 ? 8 : 16);
   const int m_np = m_kb * (m_kb + 1) / 2;
   const int m_chunks = (int)std::max(1ll, std::min(256ll, (ds.nobs + 4095) / 4096));
-  const size_t m_per_unit = ((size_t)m_chunks * (BNL_MAXK + 1 + m_np) + (size_t)rq.kmax * (rq.kmax + 1) + 1) *
+  const size_t m_per_unit = ((size_t)m_chunks * (BNL_MAXK + 1 + m_np + 1) + (size_t)rq.kmax * (rq.kmax + 1) + 1) *
                             sizeof(double);
   if (masked) {
     const long long max_units = std::max(1ll, std::min(65535ll, (long long)((256ull << 20) / m_per_unit)));
@@ -150,7 +151,7 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
                                 cudaMemcpyHostToDevice, dev.stream));
   const int grid = (cnt + tpb - 1) / tpb;
   BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
-  double *mblock = nullptr, *ucov = nullptr, *umean = nullptr;
+  double *mblock = nullptr, *ucov = nullptr, *umean = nullptr, *ushr = nullptr;
   long long *unobs = nullptr;
   const size_t mbytes = m_per_unit * (size_t)cnt;
   if (masked) {
@@ -159,6 +160,7 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
     umean = part2 + (size_t)cnt * m_chunks * m_np;
     ucov = umean + (size_t)cnt * rq.kmax;
     unobs = reinterpret_cast<long long *>(ucov + (size_t)cnt * rq.kmax * rq.kmax);
+    ushr = reinterpret_cast<double *>(unobs + cnt);
     const long long chunk_rows = (ds.nobs + m_chunks - 1) / m_chunks;
     const int *d_b_or_null = rq.kind == 0 ? d_b : nullptr;
     const dim3 mg((unsigned)m_chunks, (unsigned)cnt);
@@ -178,10 +180,23 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
     masked_cov_kernel<<<(cnt * m_np + 127) / 128, 128, 0, dev.stream>>>(part2, m_chunks, cnt, rq.kmax, m_kb, unobs,
                                                                         ucov);
     tm->launches += 4;
+    if (shrink) {
+      if (m_kb == 4)
+        masked_shrink_kernel<4><<<mg, BNL_MASK_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, chunk_rows,
+            d_a, d_b_or_null, d_off, d_idx, d_slot, ds.ncols, rq.kmax, umean, ucov, unobs, ushr);
+      else if (m_kb == 8)
+        masked_shrink_kernel<8><<<mg, BNL_MASK_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, chunk_rows,
+            d_a, d_b_or_null, d_off, d_idx, d_slot, ds.ncols, rq.kmax, umean, ucov, unobs, ushr);
+      else
+        masked_shrink_kernel<16><<<mg, BNL_MASK_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, ds.nobs, chunk_rows,
+            d_a, d_b_or_null, d_off, d_idx, d_slot, ds.ncols, rq.kmax, umean, ucov, unobs, ushr);
+      tm->launches++;
+    }
   }
   if (rq.kind == 0)
     gauss_ci_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_b, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, ds.nc,
-                                                     ds.nobs, rq.code, rq.kmax, dev.d_out, d_err, ucov, unobs);
+                                                     ds.nobs, rq.code, rq.kmax, dev.d_out, d_err, ucov, unobs,
+                                                     ushr, m_chunks);
   else
     gauss_score_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, dd.mean,
                                                         ds.nc, ds.nobs, rq.code,
@@ -269,7 +284,7 @@ extern "C" int bnl_ci_gaussian(bnl_ctx *ctx, bnl_data data, int test_e, int n, c
   auto it = ctx->data.find(data);
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   BnlDataSet &ds = it->second;
-  if (test_e != BNL_COR && test_e != BNL_ZF && test_e != BNL_MI_G)
+  if (test_e != BNL_COR && test_e != BNL_ZF && test_e != BNL_MI_G && test_e != BNL_MI_G_SH)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a Gaussian test handled here", test_e);
   return bnl_ci_gaussian_any(ctx, data, test_e, n, x, y, z_off, z_idx, stat, df, pvalue);
 }

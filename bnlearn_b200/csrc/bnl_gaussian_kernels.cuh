@@ -255,7 +255,8 @@ __global__ void gauss_ci_kernel(const int *__restrict__ ux, const int *__restric
                                 const int *__restrict__ slot, int ncols, int n,
                                 const double *__restrict__ cov, int p, long long nobs, int test,
                                 int kmax, double *__restrict__ out, int *__restrict__ err,
-                                const double *__restrict__ ucov, const long long *__restrict__ unobs) {
+                                const double *__restrict__ ucov, const long long *__restrict__ unobs,
+                                const double *__restrict__ ushr, int shr_chunks) {
   extern __shared__ double gsm[];
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= n) return;
@@ -282,7 +283,24 @@ __global__ void gauss_ci_kernel(const int *__restrict__ ux, const int *__restric
 
   double df = (test == BNL_COR) ? (double)(nobs - nz - 2)
             : (test == BNL_ZF) ? (double)(nobs - nz - 3) : 1.0;
-  if (df < 1.0) { o[0] = 0.0; o[1] = 0.0; o[2] = 1.0; o[3] = 1.0; return; }   // o[3]: R warning
+  if (df < 1.0 || (ucov && nobs == 0)) { o[0] = 0.0; o[1] = 0.0; o[2] = 1.0; o[3] = 1.0; return; }   // o[3]: R warning
+
+  // mi-g-sh: shrinkage intensity from the third pass (chunk order), on the log
+  // scale as the reference does (src/tests/gaussian/shrinkage.c:40-50, 88-99).
+  double lambda = 0.0;
+  if (test == BNL_MI_G_SH) {
+    double num = 0.0;
+    for (int c = 0; c < shr_chunks; c++) num += ushr[(size_t)u * shr_chunks + c];
+    double den = 0.0;
+    for (int i = 0; i < k; i++)
+      for (int j = i + 1; j < k; j++) { const double c = cov[(size_t)d[1 + i] + (size_t)d[1 + j] * p]; den += c * c; }
+    if (num > tol) {
+      const double nc = (double)nobs;
+      lambda = exp(log(num) - log(den) + log(nc) - 3.0 * log(nc - 1.0));
+      lambda = fmin(fmax(lambda, 0.0), 1.0);
+      if (isnan(lambda)) lambda = 0.0;
+    }
+  }
 
   double r;
   if (nz == 0) {
@@ -291,11 +309,16 @@ __global__ void gauss_ci_kernel(const int *__restrict__ ux, const int *__restric
     const double syy = cov[(size_t)d[2] + (size_t)d[2] * p] * (double)(nobs - 1);
     const double sxy = cov[(size_t)d[1] + (size_t)d[2] * p] * (double)(nobs - 1);
     r = (sxx < tol || syy < tol) ? 0.0 : sxy / sqrt(sxx * syy);
+    if (test == BNL_MI_G_SH) {          // ut_gaustests: the coefficient itself is shrunk (patterns/utest.c:110-116)
+      if (r > 1.0) r = 1.0; else if (r < -1.0) r = -1.0;
+      r *= 1.0 - lambda;
+    }
   } else {
     SmemMat A{gsm + threadIdx.x, (int)blockDim.x};
     SmemMat V{gsm + (size_t)kmax * kmax * blockDim.x + threadIdx.x, (int)blockDim.x};
     for (int i = 0; i < k; i++)
-      for (int j = 0; j < k; j++) A(i + j * k) = cov[(size_t)d[1 + i] + (size_t)d[1 + j] * p];
+      for (int j = 0; j < k; j++)       // covmat_shrink(): off-diagonal entries scaled by 1 - lambda
+        A(i + j * k) = cov[(size_t)d[1 + i] + (size_t)d[1 + j] * p] * (i == j ? 1.0 : 1.0 - lambda);
     jacobi_eigen(A, V, k);
     // pseudo-inverse entries with singular values <= dim * d_max * eps dropped
     // (src/core/correlation.c:69-83).
@@ -640,4 +663,49 @@ __global__ void masked_cov_kernel(const double *__restrict__ partial2, int nchun
   const double v = nc == 0 ? 0.0 : s / (double)(nc - 1);
   ucov[(size_t)u * kmax * kmax + i + (size_t)j * kmax] = v;
   ucov[(size_t)u * kmax * kmax + j + (size_t)i * kmax] = v;
+}
+
+// Third pass for the shrinkage test mi-g-sh: the sum over column pairs i < j and
+// complete rows of ((x_i - m_i)(x_j - m_j) - s_ij)^2, the numerator of the
+// James-Stein intensity. s_ij is the covariance with divisor nc for conditional
+// tests (covmat_lambda, src/tests/gaussian/shrinkage.c:60-106) and with divisor
+// nc - 1 for marginal ones (cor_lambda, :15-57). partial3[u * nchunks + chunk].
+template <int KB>
+__global__ void __launch_bounds__(BNL_MASK_THREADS)
+masked_shrink_kernel(const double *__restrict__ data, size_t stride, long long nobs, long long chunk_rows,
+                     const int *__restrict__ ua, const int *__restrict__ ub, const int *__restrict__ off,
+                     const int *__restrict__ idx, const int *__restrict__ slot, int ncols, int kmax,
+                     const double *__restrict__ umean, const double *__restrict__ ucov,
+                     const long long *__restrict__ unobs, double *__restrict__ partial3) {
+  __shared__ double sm[BNL_MASK_THREADS / 32];
+  const int u = blockIdx.y, chunk = blockIdx.x, nchunks = gridDim.x;
+  int cols[BNL_MAXK];
+  const int k = masked_unit_cols(u, ua, ub, off, idx, slot, ncols, cols);
+  double *out = partial3 + (size_t)u * nchunks + chunk;
+  if (k < 0 || k > KB) { if (threadIdx.x == 0) *out = 0.0; return; }
+  const double nc = (double)unobs[u];
+  const double scale = k == 2 ? 1.0 : (nc - 1.0) / nc;
+  double m[KB];
+#pragma unroll
+  for (int i = 0; i < KB; i++) m[i] = i < k ? umean[(size_t)u * kmax + i] : 0.0;
+  const double *cv = ucov + (size_t)u * kmax * kmax;
+  double acc = 0.0;
+  const long long r0 = chunk * chunk_rows, r1 = min(nobs, r0 + chunk_rows);
+  for (long long r = r0 + threadIdx.x; r < r1; r += BNL_MASK_THREADS) {
+    double d[KB];
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < KB; i++) {
+      d[i] = 0.0;
+      if (i < k) { const double v = data[stride * cols[i] + r]; ok &= !isnan(v); d[i] = v - m[i]; }
+    }
+    if (!ok) continue;
+#pragma unroll
+    for (int i = 0; i < KB; i++)
+#pragma unroll
+      for (int j = i + 1; j < KB; j++)
+        if (j < k) { const double t = d[i] * d[j] - cv[i + (size_t)j * kmax] * scale; acc += t * t; }
+  }
+  const double t = block_sum_256(acc, sm);
+  if (threadIdx.x == 0) *out = t;
 }

@@ -36,7 +36,7 @@ void minir_f77_dqrsl(double *x, int *ldx, int *n, int *k, double *qraux,
     int *job, int *info);
 
 /* test_e (src/tests/tests.h:8-36) and score_e (src/scores/scores.h:9-60). */
-enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_JT = 10, T_MI_SH = 40, T_COR = 20, T_ZF = 21, T_MI_G = 22 };
+enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_JT = 10, T_MI_SH = 40, T_COR = 20, T_ZF = 21, T_MI_G = 22, T_MI_G_SH = 41 };
 enum { S_LOGLIK = 1, S_AIC = 3, S_BIC = 4, S_BDE = 6, S_BDS = 7, S_BDJ = 8, S_K2 = 9,
        S_NAL = 13, S_PNAL = 14, S_NAL_G = 106, S_PNAL_G = 107,
        S_LOGLIK_G = 100, S_AIC_G = 102, S_BIC_G = 103 };
@@ -511,27 +511,54 @@ int orc_ci_gaussian(int test, const double *const *cols, int p, int n,
   return rc;
 }
 
+/* James-Stein shrinkage intensity of mi-g-sh (src/tests/gaussian/shrinkage.c:15-57
+ * for a marginal test, :60-106 for a conditional one): sum over pairs i < j and
+ * rows of (d_i d_j - s_ij)^2 against the sum of squared covariances, on the log
+ * scale; s_ij has divisor n for the matrix form and n - 1 for the pair form. */
+static double orc_shrink_lambda(const double *const *cols, int p, int n, const double *mean,
+    const double *cov) {
+  long double num = 0, den = 0;
+  double scale = p == 2 ? 1.0 : (double)(n - 1) / n;
+  for (int i = 0; i < p; i++)
+    for (int j = i + 1; j < p; j++) {
+      double c = cov[i + j * p];
+      for (int r = 0; r < n; r++) {
+        long double t = (cols[i][r] - mean[i]) * (cols[j][r] - mean[j]) - c * scale;
+        num += t * t;
+      }
+      den += (long double)c * c;
+    }
+  if (!(num > ORC_TOL)) return 0;
+  long double l = expl(logl(num) - logl(den) + logl((long double)n) - 3 * logl((long double)(n - 1)));
+  if (l > 1) l = 1;
+  if (l < 0) l = 0;
+  return (double)l;
+}
+
 static int orc_ci_gaussian_complete(int test, const double *const *cols, int p, int n,
     double *stat, double *df, double *pvalue) {
   int nz = p - 2;
   double d = (test == T_COR) ? n - nz - 2 : (test == T_ZF) ? n - nz - 3 : 1;
-  if (d < 1) { *df = 0; *stat = 0; *pvalue = 1; return 1; }
+  if (d < 1 || n == 0) { *df = 0; *stat = 0; *pvalue = 1; return 1; }
   *df = d;
   double r;
+  double *mean = malloc((size_t)p * sizeof(double));
+  double *cov = malloc((size_t)p * p * sizeof(double));
+  orc_covmat(cols, n, p, mean, cov);
+  double lambda = test == T_MI_G_SH ? orc_shrink_lambda(cols, p, n, mean, cov) : 0;
   if (nz == 0) {
     double xm = orc_mean(cols[0], n), ym = orc_mean(cols[1], n);
     long double xsd = orc_sse(cols[0], xm, n), ysd = orc_sse(cols[1], ym, n), sum = 0;
     for (int i = 0; i < n; i++) sum += (cols[0][i] - xm) * (cols[1][i] - ym);
     sum = (xsd < ORC_TOL || ysd < ORC_TOL) ? 0 : sum / sqrtl(xsd * ysd);
     if (sum > 1) sum = 1; else if (sum < -1) sum = -1;
-    r = (double)sum;
+    r = (double)sum * (1 - lambda);
   } else {
-    double *mean = malloc((size_t)p * sizeof(double));
-    double *cov = malloc((size_t)p * p * sizeof(double));
-    orc_covmat(cols, n, p, mean, cov);
+    for (int i = 0; i < p; i++)
+      for (int j = 0; j < p; j++) if (i != j) cov[i + j * p] *= 1 - lambda;
     r = orc_pcor(cov, p, NULL);
-    free(mean); free(cov);
   }
+  free(mean); free(cov);
   if (test == T_COR) {
     double t = r * sqrt(d) / sqrt(1 - r * r);
     *stat = r;

@@ -153,7 +153,7 @@ def reference_outputs():
         k = int(rng.integers(0, 5))
         idx = rng.choice(p, size=2 + k, replace=False)
         x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
-        for test in ("cor", "zf", "mi-g"):
+        for test in ("cor", "zf", "mi-g", "mi-g-sh"):
             st, df, pv = ra.ci_test(data, names[x], names[y], [names[i] for i in s], test)
             rec["tests"].append({"test": test, "x": x, "y": y, "z": s, "stat": st, "df": df, "p": pv})
         rb.reset()
@@ -254,7 +254,7 @@ def incomplete_outputs():
         k = int(rng.integers(0, 5))
         idx = rng.choice(gp, size=2 + k, replace=False)
         x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
-        for test in ("cor", "zf", "mi-g"):
+        for test in ("cor", "zf", "mi-g", "mi-g-sh"):
             st, df, pv = ra.ci_test(gdata, gnames[x], gnames[y], [gnames[i] for i in s], test)
             grec["tests"].append({"test": test, "x": x, "y": y, "z": s, "stat": st, "df": df, "p": pv})
         rb.reset()

@@ -174,7 +174,7 @@ def test_gaussian_ci_against_reference_golden(engine, golden, ds):
     names, cols = load_gaussian(ds)
     d = engine.register(cols)
     recs = golden[ds]["tests"]
-    for test in ("cor", "zf", "mi-g"):
+    for test in sorted({r["test"] for r in recs}):
         rs = [r for r in recs if r["test"] == test]
         st, df, pv = d.ci_gaussian(test, [r["x"] for r in rs], [r["y"] for r in rs], [r["z"] for r in rs])
         for i, r in enumerate(rs):
@@ -233,7 +233,7 @@ def test_gaussian_incomplete_wide_units_and_edge_cases(engine):
     d = engine.register(cols)
     x, y = [0, 1, 2, 12], [3, 4, 5, 0]
     z = [[6, 7, 8, 9, 10, 11, 1, 2], [0], [], [1]]
-    for test in ("cor", "zf", "mi-g"):
+    for test in ("cor", "zf", "mi-g", "mi-g-sh"):
         st, df, pv = d.ci_gaussian(test, x, y, z)
         for i in range(len(x)):
             o = orc.ci_gaussian(test, [cols[x[i]], cols[y[i]]] + [cols[j] for j in z[i]])
