@@ -7,7 +7,10 @@
 #include <atomic>
 #include <thread>
 
+#include <math.h>
+
 #include "bnl_internal.h"
+#include "bnl_special.cuh"
 
 int bnl_fail(bnl_ctx *ctx, int code, const char *fmt, ...) {
   char buf[512];
@@ -177,6 +180,37 @@ void bnl_pool_free(BnlDevice &dev, void *p, size_t bytes) {
   }
 }
 
+// log C(n, k) of the multinomial NML normaliser for n <= 1000 observations and
+// k <= 100 categories (get_regret_table, src/scores/nml.regret.table.c:44-69):
+// the k = 2 column by direct summation, the others by the linear recurrence
+// C(n, k) = C(n, k - 1) + n / (k - 2) C(n, k - 2). Entry (k, n) at k + n (K + 1).
+int bnl_regret_table(bnl_ctx *ctx, BnlDevice &dev) {
+  if (dev.d_regret) return BNL_OK;
+  const int N = BNL_REGRET_N, K = BNL_REGRET_K;
+  std::vector<double> logs(N + 1, 0.0), logfacs(N + 1, 0.0), tab((size_t)(N + 1) * (K + 1), 0.0);
+  for (int n = 1; n <= N; n++) { logs[n] = log((double)n); logfacs[n] = bnl::lgamma_pos((double)n + 1.0); }
+  for (int n = 1; n <= N; n++) {
+    double res = 0.0;
+    for (int m = 0; m <= n; m++) {
+      double term = logfacs[n] - logfacs[m] - logfacs[n - m];
+      if (m) term += m * (logs[m] - logs[n]);
+      if (n - m) term += (n - m) * (logs[n - m] - logs[n]);
+      res += exp(term);
+    }
+    tab[2 + (size_t)n * (K + 1)] = log(res);
+    double pp = 1.0, prev = exp(tab[2 + (size_t)n * (K + 1)]);      // read back, as fill_regrets_up_to_K does
+    for (int k = 3; k <= K; k++) {
+      const double rk = prev + pp / (double)(k - 2) * (double)n;
+      tab[k + (size_t)n * (K + 1)] = log(rk);
+      pp = prev; prev = rk;
+    }
+  }
+  BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  BNL_CUDA(ctx, cudaMalloc((void **)&dev.d_regret, tab.size() * sizeof(double)));
+  BNL_CUDA(ctx, cudaMemcpy(dev.d_regret, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
+  return BNL_OK;
+}
+
 static void free_dataset(bnl_ctx *ctx, BnlDataSet &ds) {
   for (size_t i = 0; i < ds.dev.size(); i++) {
     cudaSetDevice(ctx->devs[i].id);
@@ -198,7 +232,7 @@ extern "C" void bnl_shutdown(bnl_ctx *ctx) {
     cudaSetDevice(d.id);
     for (auto &b : d.pool) cudaFree(b.first);
     d.pool.clear();
-    cudaFree(d.stage); cudaFree(d.d_flags);
+    cudaFree(d.stage); cudaFree(d.d_flags); cudaFree(d.d_regret);
     cudaFreeHost(d.h_pack);
     if (d.ev_stage[0]) cudaEventDestroy(d.ev_stage[0]);
     if (d.ev_stage[1]) cudaEventDestroy(d.ev_stage[1]);

@@ -359,12 +359,16 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                       dev.stream));
       BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
     } else {
+      if (rq.kind == 1 && (rq.code == BNL_FNML || rq.code == BNL_QNML) && (rc = bnl_regret_table(ctx, dev)))
+        return rc;
       if (rq.kind == 0 && (rq.code == BNL_JT || rq.code == BNL_MI_SH))
         epilogue_kernel<true><<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
-                                                                     rq.kind, rq.code, rq.arg, ds.nobs);
+                                                                     rq.kind, rq.code, rq.arg, ds.nobs,
+                                                                     dev.d_regret);
       else
         epilogue_kernel<false><<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
-                                                                      rq.kind, rq.code, rq.arg, ds.nobs);
+                                                                      rq.kind, rq.code, rq.arg, ds.nobs,
+                                                                      dev.d_regret);
       BNL_CUDA(ctx, cudaGetLastError());
       tm->launches++;
       BNL_CUDA(ctx, cudaEventRecord(dev.eve1, dev.stream));
@@ -486,7 +490,7 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
   if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   if (score_e != BNL_LOGLIK && score_e != BNL_AIC && score_e != BNL_BIC && score_e != BNL_BDE &&
       score_e != BNL_BDS && score_e != BNL_BDJ && score_e != BNL_K2 && score_e != BNL_NAL &&
-      score_e != BNL_PNAL)
+      score_e != BNL_PNAL && score_e != BNL_FNML && score_e != BNL_QNML)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a discrete score handled here", score_e);
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_discrete: bad arguments");

@@ -598,12 +598,31 @@ __device__ __forceinline__ void warp_merge_kahan(bnl::KahanSum &k) {
   }
 }
 
+// Multinomial NML regret log C(n, k) (nml_regret, src/scores/nml.regret.c:36-62):
+// exact table for n <= 1000 and k <= 100, else the smaller of the two
+// Szpankowski-style approximations (:6-33).
+__device__ __forceinline__ double nml_regret(const double *__restrict__ tab, double n, double k) {
+  if (n == 1.0) return log(k);
+  if (k == 1.0 || n == 0.0) return 0.0;
+  if (n <= (double)BNL_REGRET_N && k <= (double)BNL_REGRET_K)
+    return tab[(int)k + (size_t)(int)n * (BNL_REGRET_K + 1)];
+  const double hK = 0.5 * k, hKh = hK - 0.5;
+  const double lg = bnl::lgamma_pos(hK), ratio = exp(lg - bnl::lgamma_pos(hKh));
+  const double gterm = 0.70710678118654752440 - ratio * k / 3.0 / sqrt(n);
+  const double a1 = hKh * (log(n) - 0.69314718055994530942) + 0.572364942924700087071713675677 - lg +
+                    0.5 - gterm * gterm + (3.0 + k * (k - 2.0) * (2.0 * k + 1.0)) / (36.0 * n);
+  const double a = k / n, Ca = 0.5 * (1.0 + sqrt(1.0 + 4.0 / a));
+  const double a2 = n * (log(a) + (a + 2.0) * log(Ca) - 1.0 / Ca) - 0.5 * log(Ca + 2.0 / a);
+  return a1 < a2 ? a1 : a2;
+}
+
 // EXT compiles in the Jonckheere-Terpstra and shrinkage-MI branches; the common
 // statistics keep their own, leaner instantiation (the extra code costs registers).
 template <bool EXT>
 __global__ void __launch_bounds__(BNL_EPI_THREADS)
 epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ tables,
-                double *__restrict__ out, int kind, int code, double arg, long long nrows) {
+                double *__restrict__ out, int kind, int code, double arg, long long nrows,
+                const double *__restrict__ regret) {
   __shared__ int s_marg[BNL_EPI_WARPS][2 * BNL_MAX_LEVELS + 2];
   __shared__ double s_s[BNL_EPI_WARPS], s_c[BNL_EPI_WARPS], s_df[BNL_EPI_WARPS];
   __shared__ long long s_n[BNL_EPI_WARPS];
@@ -700,9 +719,15 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
         for (int c = 0; c < sl; c++) acc.add(bnl::lgamma_pos((double)S[c] + alpha) - lg_alpha);
         acc.add(lg_aq - bnl::lgamma_pos((double)nk + aq));
       } else if (nk > 0) {
-        for (int c = 0; c < sl; c++) {
-          const int n = S[c];
-          if (n) acc.add((double)n * log((double)n / (double)nk));
+        if (code == BNL_QNML && U.ncols > 1) {          // cdlik_diff(): sum n log n - n_j log n_j
+          for (int c = 0; c < sl; c++) { const int n = S[c]; if (n) acc.add((double)n * log((double)n)); }
+          acc.add(-(double)nk * log((double)nk));
+        } else {
+          for (int c = 0; c < sl; c++) {
+            const int n = S[c];
+            if (n) acc.add((double)n * log((double)n / (double)nk));
+          }
+          if (code == BNL_FNML || code == BNL_QNML) acc.add(-nml_regret(regret, (double)nk, (double)llx));
         }
       }
     }
@@ -830,9 +855,16 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
           acc.add(bnl::lgamma_pos((double)S[c] + alpha) - lg_alpha);
         if (lane == 0) acc.add(lg_aq - bnl::lgamma_pos((double)nk + aq));
       } else if (nk > 0) {
-        for (int c = lane; c < sl; c += 32) {
-          const int n = S[c];
-          if (n) acc.add((double)n * log((double)n / (double)nk));
+        if (code == BNL_QNML && U.ncols > 1) {
+          for (int c = lane; c < sl; c += 32) { const int n = S[c]; if (n) acc.add((double)n * log((double)n)); }
+          if (lane == 0) acc.add(-(double)nk * log((double)nk));
+        } else {
+          for (int c = lane; c < sl; c += 32) {
+            const int n = S[c];
+            if (n) acc.add((double)n * log((double)n / (double)nk));
+          }
+          if (lane == 0 && (code == BNL_FNML || code == BNL_QNML))
+            acc.add(-nml_regret(regret, (double)nk, (double)llx));
         }
       }
     }
@@ -873,6 +905,10 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
     const double nparams = (double)(llx - 1) * (double)llz;
     double s = tot.value();
     if (code == BNL_AIC || code == BNL_BIC) s -= arg * nparams;
+    // qNML with parents: - regret(N, llx q) + regret(N, q) over ALL q parent
+    // configurations (cqnml, src/scores/normalized.maximum.likelihood.c:113-130).
+    if (code == BNL_QNML && U.ncols > 1)
+      s += nml_regret(regret, (double)n, (double)llz) - nml_regret(regret, (double)n, (double)llx * (double)llz);
     // node-average likelihood: per locally complete row, penalty per data row.
     if (code == BNL_NAL || code == BNL_PNAL)
       s = n == 0 ? -INFINITY : s / (double)n - (code == BNL_PNAL ? arg : 0.0) / (double)nrows * nparams;

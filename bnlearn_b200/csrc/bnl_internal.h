@@ -55,6 +55,7 @@ struct BnlDevice {
   cudaEvent_t ev_stage[2] = {nullptr, nullptr};
   uint8_t *h_pack = nullptr; size_t h_pack_cap = 0;      // pinned ring of host-packed columns
   int *d_flags = nullptr; size_t flags_cap = 0;          // bad-code flag + per-column NA flags
+  double *d_regret = nullptr;                            // NML regret table, (K + 1) x (N + 1), see bnl_regret_table()
   std::vector<std::pair<void *, size_t>> pool;           // released blocks (pointer, bytes)
   int sm_count = 148;
   int max_smem = 48 * 1024;
@@ -160,6 +161,12 @@ int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_o
                             const int *amat, const int *blmat, const int *updated, int nupdated,
                             int equivalence, const double *reference, double *cache,
                             double *test_counter, const int *nparents);
+
+// fNML / qNML: the multinomial regret table of src/scores/nml.regret.table.c
+// (n <= 1000, k <= 100), built on the host at first use and copied to `dev`.
+#define BNL_REGRET_N 1000
+#define BNL_REGRET_K 100
+int bnl_regret_table(bnl_ctx *ctx, BnlDevice &dev);
 
 // per-call timing of one device block.
 struct BnlTiming { float total = 0.f, count = 0.f, epi = 0.f; int launches = 0; };

@@ -184,10 +184,10 @@ extern "C" int bnl_hc(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
   // score equivalence decides whether score_cache_fill may copy the mirrored
   // delta (is.score.equivalent, R/sanitization-scores.R:74-97): loglik/aic/bic,
   // bde / bge with the uniform prior and the Gaussian forms are; nal/pnal only on
-  // complete data; bds, bdj, k2 are not.
+  // complete data; qnml is, fnml, bds, bdj, k2 are not.
   bool equivalence = score_e == BNL_LOGLIK || score_e == BNL_AIC || score_e == BNL_BIC ||
                      score_e == BNL_BDE || score_e == BNL_LOGLIK_G || score_e == BNL_AIC_G ||
-                     score_e == BNL_BIC_G || score_e == BNL_BGE;
+                     score_e == BNL_BIC_G || score_e == BNL_BGE || score_e == BNL_QNML;
   if (score_e == BNL_NAL || score_e == BNL_PNAL) {
     auto it = ctx->data.find(data);
     if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");

@@ -12,11 +12,11 @@ import numpy as np
 from . import _lib
 
 TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-g-sh": 41}
-SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "nal": 13, "pnal": 14,
+SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103, "bge": 105, "nal-g": 106, "pnal-g": 107}
 DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf", "jt", "mi-sh")
 GAUSSIAN_TESTS = ("cor", "zf", "mi-g", "mi-g-sh")
-DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds", "bdj", "k2", "nal", "pnal")
+DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds", "bdj", "k2", "fnml", "qnml", "nal", "pnal")
 GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g", "bge", "nal-g", "pnal-g")
 NA_INT = np.iinfo(np.int32).min
 

@@ -38,7 +38,7 @@ void minir_f77_dqrsl(double *x, int *ldx, int *n, int *k, double *qraux,
 /* test_e (src/tests/tests.h:8-36) and score_e (src/scores/scores.h:9-60). */
 enum { T_MI = 1, T_MI_ADF = 2, T_X2 = 3, T_X2_ADF = 4, T_JT = 10, T_MI_SH = 40, T_COR = 20, T_ZF = 21, T_MI_G = 22, T_MI_G_SH = 41 };
 enum { S_LOGLIK = 1, S_AIC = 3, S_BIC = 4, S_BDE = 6, S_BDS = 7, S_BDJ = 8, S_K2 = 9,
-       S_NAL = 13, S_PNAL = 14, S_NAL_G = 106, S_PNAL_G = 107,
+       S_FNML = 11, S_QNML = 12, S_NAL = 13, S_PNAL = 14, S_NAL_G = 106, S_PNAL_G = 107,
        S_LOGLIK_G = 100, S_AIC_G = 102, S_BIC_G = 103 };
 
 /* ------------------------------------------------------------------------
@@ -278,6 +278,47 @@ int orc_ci_discrete(int test, const int *x, int llx, const int *y, int lly,
  * `arg` is k for aic/bic and iss for bde/bds. The uniform graph prior adds 0
  * (src/scores/graph.priors.c:35-37). Returns NAN if the configuration count
  * overflows an int. */
+/* multinomial NML regret (src/scores/nml.regret.c:36-62 over the table of
+ * src/scores/nml.regret.table.c:6-69 and the two large-n / large-k
+ * approximations of nml.regret.c:6-33). */
+static double *orc_regret_tab = NULL;
+static double orc_regret(double n, double k) {
+  enum { N = 1000, K = 100 };
+  if (n == 1) return log(k);
+  if (k == 1 || n == 0) return 0;
+  if (n <= N && k <= K) {
+    if (!orc_regret_tab) {
+      double *t = calloc((size_t)(N + 1) * (K + 1), sizeof(double));
+      for (int m = 1; m <= N; m++) {
+        double sum = 0;
+        for (int h = 0; h <= m; h++) {
+          double term = Rf_lgammafn(m + 1.0) - Rf_lgammafn(h + 1.0) - Rf_lgammafn(m - h + 1.0);
+          if (h) term += h * (log((double)h) - log((double)m));
+          if (m - h) term += (m - h) * (log((double)(m - h)) - log((double)m));
+          sum += exp(term);
+        }
+        t[2 + (size_t)m * (K + 1)] = log(sum);
+        double c1 = 1, c2 = exp(t[2 + (size_t)m * (K + 1)]);
+        for (int kk = 3; kk <= K; kk++) {
+          double c3 = c2 + c1 / (kk - 2) * m;
+          t[kk + (size_t)m * (K + 1)] = log(c3);
+          c1 = c2; c2 = c3;
+        }
+      }
+      orc_regret_tab = t;
+    }
+    return orc_regret_tab[(int)k + (size_t)(int)n * (K + 1)];
+  }
+  double hk = 0.5 * k, hkh = hk - 0.5;
+  double ratio = exp(lgamma(hk) - lgamma(hkh));
+  double g = M_SQRT1_2 - ratio * k / 3 / sqrt(n);
+  double a1 = hkh * (log(n) - M_LN2) + 0.5 * log(M_PI) - lgamma(hk) + 0.5 - g * g +
+              (3 + k * (k - 2) * (2 * k + 1)) / (36.0 * n);
+  double a = k / n, ca = 0.5 * (1 + sqrt(1 + 4 / a));
+  double a2 = n * (log(a) + (a + 2) * log(ca) - 1 / ca) - 0.5 * log(ca + 2 / a);
+  return a1 < a2 ? a1 : a2;
+}
+
 double orc_score_discrete(int score, const int *x, int llx, const int *const *pa,
     const int *plev, int np, int num, double arg, double *nparams) {
   double res = 0, npar = 0;
@@ -305,6 +346,8 @@ double orc_score_discrete(int score, const int *x, int llx, const int *const *pa
        * the full sample size (src/scores/discrete.nal.c:8-37). */
       if (score == S_NAL || score == S_PNAL)
         res = nobs == 0 ? -INFINITY : res / nobs - (score == S_PNAL ? arg : 0.0) / num * npar;
+      /* fnml() / qnml() of a root node (normalized.maximum.likelihood.c:26-41, 107-111). */
+      if (score == S_FNML || score == S_QNML) res -= orc_regret(nobs, llx);
     }
     free(n);
   } else {
@@ -348,6 +391,23 @@ double orc_score_discrete(int score, const int *x, int llx, const int *const *pa
           if (c != 0) res += (double)c * log((double)c / nj[j]);
         }
       npar = (double)(llx - 1) * (double)lly;
+      if (score == S_FNML) {                        /* cfnml(), normalized.maximum.likelihood.c:44-63 */
+        for (int j = 0; j < lly; j++) if (nj[j] != 0) res -= orc_regret(nj[j], llx);
+      }
+      if (score == S_QNML) {                        /* cqnml() over cdlik_diff(), :10-24, 113-130 */
+        long long nobs = 0;
+        res = 0;
+        for (int j = 0; j < lly; j++) {
+          for (int i = 0; i < llx; i++) {
+            int c = n[(size_t)i * lly + j];
+            if (c != 0) res += (double)c * log((double)c);
+          }
+          if (nj[j] != 0) res -= (double)nj[j] * log((double)nj[j]);
+          nobs += nj[j];
+        }
+        res -= orc_regret((double)nobs, (double)llx * lly);
+        res += orc_regret((double)nobs, lly);
+      }
       if (score == S_NAL || score == S_PNAL) {      /* src/scores/discrete.nal.c:39-68 */
         long long nobs = 0;
         for (int j = 0; j < lly; j++) nobs += nj[j];

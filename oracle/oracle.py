@@ -18,7 +18,7 @@ c_int_p = C.POINTER(C.c_int)
 c_dbl_p = C.POINTER(C.c_double)
 
 TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-g-sh": 41}
-SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "nal": 13, "pnal": 14,
+SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103, "nal-g": 106, "pnal-g": 107}
 
 

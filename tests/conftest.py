@@ -23,4 +23,6 @@ def golden():
     # Jonckheere-Terpstra and shrinkage MI on complete data ("data" names the data set)
     with open(os.path.join(ROOT, "tests", "golden", "ref_jt_shrinkage.json")) as f:
         out.update(json.load(f))
+    with open(os.path.join(ROOT, "tests", "golden", "ref_nml.json")) as f:          # fNML / qNML scores
+        out.update(json.load(f))
     return out

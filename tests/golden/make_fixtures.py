@@ -326,6 +326,37 @@ def jt_shrinkage_outputs():
     print("wrote ref_jt_shrinkage.json")
 
 
+def nml_outputs():
+    """fNML / qNML scores: learning.test and alarm (large-n regret approximations)
+    and the first 600 rows of alarm (exact regret table, n <= 1000)."""
+    from oracle import refapi as ra, refbind as rb
+    rng = np.random.default_rng(20261111)
+    names, codes, nlev = load_discrete("alarm")
+    np.savez_compressed(os.path.join(HERE, "data_alarm_600.npz"), names=np.array(names),
+                        codes=(codes[:, :600] - 1).astype(np.uint8), nlevels=np.asarray(nlev, dtype=np.int32))
+    out = {}
+    for ds in ("learning_test", "alarm", "alarm_600"):
+        names, codes, nlev = load_discrete(ds)
+        data = ra.RefData(list(codes), list(nlev), names)
+        p = len(names)
+        rec = {"data": ds, "tests": [], "scores": [], "allsubs": [], "roundrobin": []}
+        for t in range(30):
+            k = int(rng.integers(0, 5))
+            idx = rng.choice(p, size=1 + k, replace=False)
+            node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+            par = {names[node]: [names[i] for i in pa]}
+            for score in ("fnml", "qnml"):
+                v = ra.per_node_score(data, par, [names[node]], score)[0]
+                rec["scores"].append({"score": score, "arg": 0.0, "node": node, "parents": pa,
+                                      "value": float(v)})
+            rb.reset()
+            data.invalidate()
+        out[ds + "_nml"] = rec
+    with open(os.path.join(HERE, "ref_nml.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote ref_nml.json")
+
+
 def bge_outputs():
     """BGe scores on gaussian.test with the front end's default hyper-parameters
     (iss.mu = 1, iss.w = ncol + 2, nu = column means) and with arbitrary ones."""
@@ -409,5 +440,6 @@ if __name__ == "__main__":
     reference_outputs()
     incomplete_outputs()
     jt_shrinkage_outputs()
+    nml_outputs()
     bge_outputs()
     mi_matrix_outputs()

@@ -4,7 +4,8 @@ reference's own allsubs_test / roundrobin_test / score_cache_fill."""
 import numpy as np
 import pytest
 
-DISCRETE_SETS = ["learning_test", "alarm", "learning_test_na", "learning_test_jt_sh", "alarm_jt_sh"]
+DISCRETE_SETS = ["learning_test", "alarm", "learning_test_na", "learning_test_jt_sh", "alarm_jt_sh",
+                 "learning_test_nml", "alarm_nml", "alarm_600_nml"]
 from util import load_discrete, load_gaussian, rel_close
 
 pytestmark = pytest.mark.gpu

@@ -9,7 +9,8 @@ import numpy as np
 import pytest
 
 from oracle import oracle as orc
-DISCRETE_SETS = ["learning_test", "alarm", "learning_test_na", "learning_test_jt_sh", "alarm_jt_sh"]
+DISCRETE_SETS = ["learning_test", "alarm", "learning_test_na", "learning_test_jt_sh", "alarm_jt_sh",
+                 "learning_test_nml", "alarm_nml", "alarm_600_nml"]
 from util import GOLDEN, load_discrete, load_gaussian, rel_close
 
 RTOL = 1e-9
