@@ -207,7 +207,11 @@ int bnl_regret_table(bnl_ctx *ctx, BnlDevice &dev) {
   }
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
   BNL_CUDA(ctx, cudaMalloc((void **)&dev.d_regret, tab.size() * sizeof(double)));
-  BNL_CUDA(ctx, cudaMemcpy(dev.d_regret, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice));
+  // on the device's own stream (the kernels run there and it does not wait for
+  // the legacy default stream), and complete before the host vector goes away.
+  BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_regret, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice,
+                                dev.stream));
+  BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
   return BNL_OK;
 }
 

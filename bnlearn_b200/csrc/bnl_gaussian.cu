@@ -352,7 +352,9 @@ extern "C" int bnl_set_bge_prior(bnl_ctx *ctx, bnl_data data, double iss_mu, dou
       int rc = bnl_pool_alloc(ctx, dev, (void **)&dd.bge_nu, dd.nu_bytes);
       if (rc) return rc;
     }
-    BNL_CUDA(ctx, cudaMemcpy(dd.bge_nu, by_slot.data(), (size_t)ds.nc * sizeof(double), cudaMemcpyHostToDevice));
+    BNL_CUDA(ctx, cudaMemcpyAsync(dd.bge_nu, by_slot.data(), (size_t)ds.nc * sizeof(double),
+                                  cudaMemcpyHostToDevice, dev.stream));
+    BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
   }
   cudaSetDevice(ctx->devs[0].id);
   return BNL_OK;
