@@ -18,6 +18,7 @@
 // what cannot win: rows whose best valid addition is not above the incumbent,
 // and, for removals and reversals, everything that is not an arc.
 #include <math.h>
+#include <stdint.h>
 #include <string.h>
 
 #include <algorithm>
@@ -46,6 +47,13 @@ struct Search {
   std::vector<double> reference;
   std::vector<int> stack;
   std::vector<char> seen;
+  // tabu search: the last `tabu` networks, as a Zobrist hash (xor of one random
+  // 64-bit key per arc) plus the full matrix for the rare hash match.
+  std::vector<uint64_t> zkey;              // n x n keys, empty for hill climbing
+  uint64_t hash = 0;                       // of the current network
+  std::vector<uint64_t> tabu_hash;
+  std::vector<std::vector<int>> tabu_net;
+  std::vector<char> tabu_used;
 
   Search(int n_, double maxp_, const int *bl_, const int *wl_)
       : n(n_), maxp(maxp_), bl(bl_), wl(wl_), a((size_t)n_ * n_, 0), r((size_t)n_ * n_, 0),
@@ -65,6 +73,44 @@ struct Search {
     if (v) ch.insert(std::lower_bound(ch.begin(), ch.end(), j), j);
     else ch.erase(std::lower_bound(ch.begin(), ch.end(), j));
     dirty[i] = dirty[j] = 1;               // (i, j) and (j, i) changed validity as additions
+    if (!zkey.empty()) hash ^= zkey[(size_t)i * n + j];
+  }
+
+  void enable_tabu(int len) {
+    zkey.resize((size_t)n * n);
+    uint64_t x = 0x9e3779b97f4a7c15ull;    // splitmix64
+    for (auto &k : zkey) {
+      x += 0x9e3779b97f4a7c15ull;
+      uint64_t z = x;
+      z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+      z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+      k = z ^ (z >> 31);
+    }
+    hash = 0;
+    for (int i = 0; i < n; i++) for (int j : children[i]) hash ^= zkey[(size_t)i * n + j];
+    tabu_hash.assign(len, 0);
+    tabu_net.assign(len, std::vector<int>());
+    tabu_used.assign(len, 0);
+  }
+  void remember(int slot) { tabu_hash[slot] = hash; tabu_net[slot] = a; tabu_used[slot] = 1; }
+
+  // would the network after `op` on i -> j be one of the remembered ones?
+  bool is_tabu(int op, int i, int j) {
+    if (zkey.empty()) return false;
+    uint64_t h = hash ^ zkey[(size_t)i * n + j];
+    if (op == 3) h ^= zkey[(size_t)j * n + i];
+    for (size_t t = 0; t < tabu_hash.size(); t++) {
+      if (!tabu_used[t] || tabu_hash[t] != h) continue;
+      const std::vector<int> &m = tabu_net[t];
+      // same hash: compare for real (apply the move, compare, undo).
+      const size_t ij = (size_t)i + (size_t)j * n, ji = (size_t)j + (size_t)i * n;
+      const int old_ij = a[ij], old_ji = a[ji];
+      if (op == 1) a[ij] = 1; else if (op == 2) a[ij] = 0; else { a[ij] = 0; a[ji] = 1; }
+      const bool same = (m == a);
+      a[ij] = old_ij; a[ji] = old_ji;
+      if (same) return true;
+    }
+    return false;
   }
 
   // may i -> j be proposed as an addition? (hc_to_be_added)
@@ -114,9 +160,14 @@ struct Search {
   }
 
   // Best addition, then removal, then reversal, in the reference's scan order.
-  Move opt_step() {
+  // Hill climbing: baseline 0, tiny reversal deltas zeroed. Tabu search
+  // (tabu_step, src/learning/score/tabu.c:93-435): moves into a remembered network
+  // are skipped, the baseline is 0 or -Inf (accept the least bad move) and
+  // reversal deltas are taken as they are.
+  Move opt_step(double baseline = 0.0) {
     const double tol = bnl::kSqrtEps;
-    double best = 0.0;
+    const bool tabu_mode = !zkey.empty();
+    double best = baseline;
     Move mv{0, -1, -1};
     for (int i = 0; i < n; i++) {
       if (dirty[i]) recompute_row(i);
@@ -124,7 +175,7 @@ struct Search {
       const double *row = cache_rm.data() + (size_t)i * n;
       for (int j = 0; j < n; j++) {
         if (!(row[j] - best > tol) || !valid_add(i, j)) continue;
-        if (!has_path(j, i, false)) { best = row[j]; mv = Move{1, i, j}; }
+        if (!has_path(j, i, false) && !is_tabu(1, i, j)) { best = row[j]; mv = Move{1, i, j}; }
       }
     }
     // removals: present arcs that are not whitelisted.
@@ -132,7 +183,7 @@ struct Search {
       for (int j : children[i]) {
         if (WL(i, j) == 1) continue;
         const double v = C(i, j);
-        if (v - best > tol) { best = v; mv = Move{2, i, j}; }
+        if (v - best > tol && !is_tabu(2, i, j)) { best = v; mv = Move{2, i, j}; }
       }
     // reversals: the reverse must not be blacklisted and the new child must have room.
     for (int i = 0; i < n; i++) {
@@ -140,8 +191,8 @@ struct Search {
       for (int j : children[i]) {
         if (BL(j, i) == 1) continue;
         double v = C(i, j) + C(j, i);
-        if (fabs(v) < tol) v = 0.0;
-        if (v - best > tol && !has_path(i, j, true)) { best = v; mv = Move{3, i, j}; }
+        if (!tabu_mode && fabs(v) < tol) v = 0.0;
+        if (v - best > tol && !has_path(i, j, true) && !is_tabu(3, i, j)) { best = v; mv = Move{3, i, j}; }
       }
     }
     if (mv.op) {
@@ -230,6 +281,98 @@ extern "C" int bnl_hc(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
     it++;
   }
   memcpy(amat, S.a.data(), sizeof(int) * (size_t)n * n);
+  if (node_scores_out) memcpy(node_scores_out, S.reference.data(), sizeof(double) * n);
+  if (iterations) *iterations = it;
+  return BNL_OK;
+}
+
+namespace {
+
+// robust.score.difference() (R/utils-misc.R:225-242) on network scores.
+double robust_diff(double new_s, double old_s) {
+  if (new_s == -INFINITY && old_s == -INFINITY) return -INFINITY;
+  if (new_s != -INFINITY && old_s == -INFINITY) return fabs(new_s);
+  const double d = new_s - old_s;
+  return fabs(d) < bnl::kSqrtEps ? 0.0 : d;
+}
+
+double total(const std::vector<double> &v) {
+  double s = 0.0;
+  for (double x : v) s += x;
+  return s;
+}
+
+}  // namespace
+
+extern "C" int bnl_tabu(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss, int nnodes,
+                        const int *start, const int *blmat, const int *wlmat, double maxp,
+                        long long max_iter, int tabu, int max_tabu, int *amat,
+                        double *node_scores_out, long long *iterations, double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (nnodes <= 0 || !amat || tabu < 1 || max_tabu < 0)
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_tabu: bad arguments");
+  const int n = nnodes;
+  Search S(n, maxp, blmat, wlmat);
+  if (start)
+    for (int j = 0; j < n; j++)
+      for (int i = 0; i < n; i++)
+        if (start[(size_t)i + (size_t)j * n]) S.set_arc(i, j, 1);
+  S.enable_tabu(tabu);
+  bool equivalence = score_e == BNL_LOGLIK || score_e == BNL_AIC || score_e == BNL_BIC ||
+                     score_e == BNL_BDE || score_e == BNL_LOGLIK_G || score_e == BNL_AIC_G ||
+                     score_e == BNL_BIC_G || score_e == BNL_BGE || score_e == BNL_QNML;
+  if (score_e == BNL_NAL || score_e == BNL_PNAL) {
+    auto it = ctx->data.find(data);
+    if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+    equivalence = true;
+    for (int f : it->second.slot_has_na) if (f) equivalence = false;
+  }
+  std::vector<int> updated(n);
+  for (int i = 0; i < n; i++) updated[i] = i;
+  int rc = node_scores(ctx, data, score_e, k_or_iss, S, updated, S.reference.data());
+  if (rc) return rc;
+
+  // The loop of tabu.search(optimized = TRUE) (R/tabu.R:66-300): remember the
+  // current network, take the best move that does not lead back into a remembered
+  // one; when nothing improves, take the least bad move for up to max_tabu
+  // iterations in a row, then return the best network seen. (The branch of
+  // tabu.R:74-117 that ranks networks with singular nodes is not restated.)
+  std::vector<int> best_net = S.a;
+  double best_score = -INFINITY;
+  int loss_iter = 0;
+  long long it = 1;
+  bool use_best = false;
+  for (;;) {
+    const int current = (int)((it - 1) % tabu);
+    const double now = total(S.reference);
+    if (robust_diff(now, best_score) > 0 || it == 1) { best_net = S.a; best_score = now; }
+    S.remember(current);
+    rc = bnl_score_cache_fill_np(ctx, data, score_e, k_or_iss, n, S.a.data(), blmat, updated.data(),
+                                 (int)updated.size(), equivalence ? 1 : 0, S.reference.data(),
+                                 S.cache.data(), test_counter, S.nparents.data());
+    if (rc) return rc;
+    S.columns_changed(updated);
+    Move mv = S.opt_step(0.0);
+    if (!mv.op) {
+      if (loss_iter >= max_tabu) { use_best = true; break; }
+      loss_iter++;
+      mv = S.opt_step(-INFINITY);
+      if (!mv.op) { use_best = loss_iter > 0; break; }
+    } else if (robust_diff(total(S.reference), best_score) > 0) {
+      loss_iter = 0;
+    }
+    updated.clear();
+    if (mv.op == 1) { S.set_arc(mv.from, mv.to, 1); updated.push_back(mv.to); }
+    else if (mv.op == 2) { S.set_arc(mv.from, mv.to, 0); updated.push_back(mv.to); }
+    else {
+      S.set_arc(mv.from, mv.to, 0); S.set_arc(mv.to, mv.from, 1);
+      updated.push_back(mv.from < mv.to ? mv.from : mv.to);
+      updated.push_back(mv.from < mv.to ? mv.to : mv.from);
+    }
+    if (max_iter > 0 && it >= max_iter) { use_best = loss_iter > 0; break; }
+    it++;
+  }
+  memcpy(amat, use_best ? best_net.data() : S.a.data(), sizeof(int) * (size_t)n * n);
   if (node_scores_out) memcpy(node_scores_out, S.reference.data(), sizeof(double) * n);
   if (iterations) *iterations = it;
   return BNL_OK;

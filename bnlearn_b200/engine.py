@@ -232,6 +232,28 @@ class DataSet:
             counter.add(cnt.value)
         return amat, scores, iters.value
 
+    def tabu(self, score, arg=0.0, nnodes=None, start=None, blmat=None, wlmat=None, maxp=np.inf,
+             max_iter=0, tabu=10, max_tabu=None, counter=None):
+        """bnl_tabu: tabu search in one library call; returns (amat, scores, iterations)."""
+        e = self.engine
+        n = len(self.nlevels) if nnodes is None else int(nnodes)
+
+        def mat(m):
+            return None if m is None else np.asfortranarray(m, dtype=np.int32)
+        s, b, w = mat(start), mat(blmat), mat(wlmat)
+        amat = np.zeros((n, n), dtype=np.int32, order="F")
+        scores = np.zeros(n)
+        iters = C.c_longlong(0)
+        cnt = C.c_double(0.0)
+        e._check(e._lib.bnl_tabu(e._ctx, self.handle, SCORES[score], float(arg), n,
+                                 None if s is None else _ip(s), None if b is None else _ip(b),
+                                 None if w is None else _ip(w), float(maxp), int(max_iter), int(tabu),
+                                 int(tabu if max_tabu is None else max_tabu), _ip(amat), _dp(scores),
+                                 C.byref(iters), C.byref(cnt)))
+        if counter is not None:
+            counter.add(cnt.value)
+        return amat, scores, iters.value
+
     def mi_matrix(self, estimator, cols, cond=-1):
         """Pairwise mutual-information coefficients of `cols` (optionally given the
         factor `cond`) as a symmetric matrix with a zero diagonal."""

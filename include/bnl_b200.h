@@ -224,6 +224,18 @@ int bnl_hc(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss, int nnodes
            long long max_iter, int *amat, double *node_scores, long long *iterations,
            double *test_counter);
 
+/* tabu.search(optimized = TRUE) in one call (R/tabu.R:2-300 around
+ * score_cache_fill and tabu_step, src/learning/score/tabu.c:93-435): arguments
+ * as bnl_hc plus the length of the tabu list and the number of consecutive
+ * non-improving iterations allowed (max.tabu). Returns the best network seen when
+ * the search ended on a non-improving stretch, like the reference; node_scores
+ * are those of the LAST network. Not restated: the ranking of networks that hold
+ * singular (-Inf) nodes, R/tabu.R:74-117. */
+int bnl_tabu(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss, int nnodes,
+             const int *start, const int *blmat, const int *wlmat, double maxp,
+             long long max_iter, int tabu, int max_tabu, int *amat, double *node_scores,
+             long long *iterations, double *test_counter);
+
 /* estimate_mi_matrix (src/learning/local/mi.matrix.c:184-252 over
  * mi_matrix_discrete :40-137 / mi_matrix_gaussian :141-181), the coefficient
  * matrix behind aracne() and chow.liu(): for the ncols listed columns (all

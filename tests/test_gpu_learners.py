@@ -261,3 +261,30 @@ def test_boot_strength_native_equals_stepwise(engine):
     assert np.array_equal(s1[0], s4[0]) and s1[2] == s4[2]
     s2 = learners.boot_strength(engine, cols, nlev, 6, "bde", 1.0, seed=11, native=False)
     assert np.array_equal(s1[0], s2[0]) and np.array_equal(s1[1], s2[1]) and s1[2] == s2[2]
+
+
+@pytest.mark.parametrize("ds,score,arg,tabu_len,max_iter", [("learning_test", "bde", 1.0, 5, np.inf),
+                                                            ("learning_test", "bic", None, 3, np.inf),
+                                                            ("alarm", "bic", None, 10, 40),
+                                                            ("gaussian_test", "bic-g", None, 4, np.inf)])
+def test_native_tabu_matches_the_stepwise_loop(engine, ds, score, arg, tabu_len, max_iter):
+    """bnl_tabu against learners.tabu on the same engine (learners.tabu itself is
+    held to the reference's backend above)."""
+    from bnlearn_b200 import callsites as cs, learners
+    if ds == "gaussian_test":
+        names, cols = load_gaussian(ds)
+        d = engine.register(cols)
+    else:
+        names, cols, nlev = load_discrete(ds)
+        d = engine.register(cols, nlev)
+    n = len(cols[0])
+    arg = np.log(n) / 2 if arg is None else arg
+    be = learners.GpuBackend(d)
+    a1, s1 = learners.tabu(be, len(cols), score, arg, max_iter=max_iter, tabu=tabu_len)
+    counter = cs.TestCounter()
+    a2, s2, iters = d.tabu(score, arg, max_iter=0 if max_iter == np.inf else max_iter, tabu=tabu_len,
+                           counter=counter)
+    assert np.array_equal(a1, a2)
+    assert counter.value == be.counter.value
+    assert np.allclose(s1, s2, rtol=1e-12, atol=0)
+    d.release()
