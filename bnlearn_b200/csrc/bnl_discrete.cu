@@ -24,7 +24,7 @@ const int kKnobMidThreads = (int)env_ll("BNL_MID_THREADS", 1024);
 const long long kKnobGroup = env_ll("BNL_GROUP", 1);
 const long long kKnobGroupThreads = env_ll("BNL_GROUP_THREADS", 512);
 const long long kKnobGroupMinCols = env_ll("BNL_GROUP_MINCOLS", 3);
-const long long kKnobGroupWaves = env_ll("BNL_GROUP_WAVES", 2);
+const long long kKnobGroupWaves = env_ll("BNL_GROUP_WAVES", 1);
 const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
@@ -149,6 +149,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     std::vector<char> grouped(cnt, 0);
     std::vector<int2> tiles;
     std::vector<int> gorder;
+    int gstride = 0;
     const int group_smem = dev.max_smem - 8192;
     // Score requests only: on pc.stable's mixed test batches (many tiny tables that
     // count row pairs, 29 units per distinct column kept hot in L2) the extra launch
@@ -169,7 +170,9 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       int i = 0;
       while (i < cnt) {
         int j = i + 1;
-        while (j < cnt && dev.h_units[j].cells <= 256 && dev.h_units[i].cells <= 256 &&
+        // tables small enough for at least four of them (at the launch-wide stride) per SM
+        const int gcap = group_smem / (4 * 256);
+        while (j < cnt && dev.h_units[j].cells <= gcap && dev.h_units[i].cells <= gcap &&
                same_base(dev.h_units[i], dev.h_units[j])) j++;
         if (j - i >= 4) runs.push_back(std::make_pair(i, j));
         i = j;
@@ -177,10 +180,15 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       // units per tile: more units share more loads, but the CTAs (tiles x row
       // chunks, one per SM at a time) should also fill whole waves -- 999
       // candidates make 125 tiles of 8 (84 % of 148 SMs) or 143 tiles of 7 (97 %).
-      int best_u = (int)kKnobGroupUnits;
+      // one table stride for the whole launch (count_group_kernel): the largest table.
+      for (auto &r : runs)
+        for (int u = r.first; u < r.second; u++) gstride = std::max(gstride, dev.h_units[u].cells * 256);
+      const int fit = gstride > 0 ? std::min(BNL_GROUP_MAX, group_smem / gstride) : 0;
+      if (fit < 4) runs.clear();               // tables too large to share an SM usefully
+      int best_u = std::min((int)kKnobGroupUnits, fit);
       if (!getenv("BNL_GROUP_UNITS") && !runs.empty()) {
         double best_cost = 1e300;
-        for (int u = BNL_GROUP_MAX; u >= 5; u--) {
+        for (int u = fit; u >= std::min(fit, 5); u--) {
           long long nt = 0;
           for (auto &r : runs) nt += (r.second - r.first + u - 1) / u;
           const long long ch = std::max(1ll, (kKnobGroupWaves * dev.sm_count + nt / 2) / nt);
@@ -194,11 +202,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         int t0 = r.first;
         const int j = r.second;
         while (t0 < j) {
-          int t1 = t0, bytes = 0;
-          while (t1 < j && t1 - t0 < best_u && bytes + dev.h_units[t1].cells * 256 <= group_smem) {
-            bytes += dev.h_units[t1].cells * 256;
-            t1++;
-          }
+          const int t1 = std::min(j, t0 + best_u);
           tiles.push_back(make_int2((int)gorder.size(), t1 - t0));
           for (int u = t0; u < t1; u++) { gorder.push_back(u); grouped[u] = 1; }
           t0 = t1;
@@ -287,11 +291,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     if (groups > 0 && !tiles.empty()) {
       // one CTA per SM (its tables fill the shared memory): ~8 waves of CTAs.
       int smem = 0;
-      for (const int2 &t : tiles) {
-        int b = 0;
-        for (int u = 0; u < t.y; u++) b += dev.h_units[gorder[t.x + u]].cells * 256;
-        smem = std::max(smem, b);
-      }
+      for (const int2 &t : tiles) smem = std::max(smem, t.y * gstride);
       const long long nt = (long long)tiles.size();
       long long want = std::max(1ll, (kKnobGroupWaves * dev.sm_count + nt / 2) / nt);
       if (kKnobChunkRows) want = (ds.nobs + kKnobChunkRows - 1) / kKnobChunkRows;
@@ -302,7 +302,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
 #define BNL_GROUP_LAUNCH(NT)                                                                          \
       count_group_kernel<NT><<<ggrid, NT, (size_t)smem, dev.stream>>>(                                  \
           dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + n_ungrouped, dev.d_tiles, dev.d_tables, \
-          (int)tiles.size(), ch)
+          (int)tiles.size(), ch, gstride)
       if (kKnobGroupThreads == 1024) BNL_GROUP_LAUNCH(1024);
       else if (kKnobGroupThreads == 384) BNL_GROUP_LAUNCH(384);
       else BNL_GROUP_LAUNCH(512);

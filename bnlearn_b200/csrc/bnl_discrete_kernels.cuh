@@ -449,11 +449,11 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 // units over a row chunk: the shared columns are loaded and combined into a packed
 // base index ONCE per 16 rows, then each candidate costs one 128-bit load, four
 // IMADs and the 16 (PRMT + ATOMS) updates of its own lane-replicated table. This
-// removes the repeated loads of the target / parent columns -- load wavefronts are
-// what the per-unit kernel spends on top of its atomics -- and is what lifts the
-// candidate batch past half of the HBM roofline.
-// tiles[] = {first position in `order`, number of units}; tables sit back to back
-// in shared memory (unit j at tile_off[j] bytes).
+// removes the repeated loads of the target / parent columns (every unit re-reading
+// its columns through L2 is what caps the per-unit kernel, at 86 % of the L2
+// fabric) and brings the candidate batch to 0.48 of the HBM roofline, from 0.41
+// (DESIGN.md section 3.1).
+// tiles[] = {first position in `order`, number of units}.
 #define BNL_GROUP_MAX 8
 
 // The loads of the next 16-row group are issued before the current group is
@@ -473,10 +473,14 @@ template <int NT>
 __global__ void __launch_bounds__(NT)
 count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
-                   const int2 *__restrict__ tiles, int *__restrict__ tables, int ntiles, int chunks) {
+                   const int2 *__restrict__ tiles, int *__restrict__ tables, int ntiles, int chunks,
+                   int tstride) {
+  // unit j's table starts at j * tstride bytes: the same stride for every tile of
+  // the launch (a kernel parameter, so the offset lives in a uniform register and
+  // the update is PRMT + ATOMS [R + UR] with no address add in between).
   extern __shared__ __align__(256) int hist[];
   __shared__ BnlUnit su;                               // first unit of the tile: the shared columns
-  __shared__ int s_col[BNL_GROUP_MAX], s_cells[BNL_GROUP_MAX], s_off[BNL_GROUP_MAX + 1];
+  __shared__ int s_col[BNL_GROUP_MAX], s_cells[BNL_GROUP_MAX];
   __shared__ long long s_tab[BNL_GROUP_MAX];
   const int chunk = blockIdx.x / ntiles;
   const int2 tile = tiles[blockIdx.x % ntiles];
@@ -491,13 +495,7 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     s_tab[threadIdx.x] = uj.table_off;
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int o = 0;
-    for (int j = 0; j < nu; j++) { s_off[j] = o; o += s_cells[j] * 256; }
-    s_off[nu] = o;
-  }
-  __syncthreads();
-  const int total_quads = s_off[nu] >> 4;
+  const int total_quads = (nu * tstride) >> 4;
   for (int c = threadIdx.x; c < total_quads; c += NT) reinterpret_cast<uint4 *>(hist)[c] = make_uint4(0, 0, 0, 0);
   __syncthreads();
 
@@ -541,7 +539,7 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 #pragma unroll
     for (int j = 0; j < BNL_GROUP_MAX; j++)
       if (j < nu) {
-        int *hj = reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + s_off[j]);
+        int *hj = reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + j * tstride);
         small_bump(hj, vb.x + cur.cand[j].x * cmul, slot4);
         small_bump(hj, vb.y + cur.cand[j].y * cmul, slot4);
         small_bump(hj, vb.z + cur.cand[j].z * cmul, slot4);
@@ -562,7 +560,7 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   }
   __syncthreads();
   for (int j = 0; j < nu; j++) {
-    const int *hj = reinterpret_cast<const int *>(reinterpret_cast<const char *>(hist) + s_off[j]);
+    const int *hj = reinterpret_cast<const int *>(reinterpret_cast<const char *>(hist) + j * tstride);
     int *gtab = tables + s_tab[j];
     for (int c = threadIdx.x; c < s_cells[j]; c += NT) {
       int sum = 0;
