@@ -451,7 +451,7 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 // IMADs and the 16 (PRMT + ATOMS) updates of its own lane-replicated table. This
 // removes the repeated loads of the target / parent columns (every unit re-reading
 // its columns through L2 is what caps the per-unit kernel, at 86 % of the L2
-// fabric) and brings the candidate batch to 0.48 of the HBM roofline, from 0.41
+// fabric) and brings the candidate batch to 0.57 of the HBM roofline, from 0.41
 // (DESIGN.md section 3.1).
 // tiles[] = {first position in `order`, number of units}.
 #define BNL_GROUP_MAX 8
