@@ -482,8 +482,10 @@ def main():
                          "compulsory_bytes_per_launch": float(ncol) * rows,
                          "note": "achieved = per-unit algorithmic bytes x units / kernel time (contract); the "
                                  "batch has %.0f units per distinct column, so L2 serves the reuse and DRAM "
-                                 "traffic (ncu) equals the compulsory bytes; the kernel is bound by the "
-                                 "shared-memory atomic rate (LSU data pipe 87%% busy in profiles/)"
+                                 "traffic (ncu) stays near the compulsory bytes; the kernel sits under two "
+                                 "ceilings: the shared-memory atomic rate (5.1e12 lane updates/s measured by "
+                                 "scripts/atom_probe.cu; LSU data pipe 85-87%% busy) and the L2-to-SM fabric "
+                                 "(the algorithmic rate above is ~86%% of its ~12.4 TB/s)"
                                  % (n_units / float(ncol))},
         })
         if world == 1 and not args.no_extras:
