@@ -414,3 +414,44 @@ def test_large_registration_hybrid_upload(engine, threads, monkeypatch):
     cols[2][1_500_000] = 7
     with pytest.raises(BnlError):
         engine.register(cols, lev)
+
+
+def test_full_size_properties(engine):
+    """Config B's full size (37 factors x 10 M rows), where the oracle would take
+    minutes: size-independent properties of the counts and statistics instead.
+    Tables sum to the row count; summing the conditional table over the strata
+    gives the marginal table; a test is symmetric in (x, y); counts are additive
+    over a row split and double when every row appears twice (device-side row
+    gathers)."""
+    from bnlearn_b200 import synth
+    rows = 10_000_000
+    names, cols, lev = synth.alarm_shaped(rows)
+    d = engine.register(cols, lev)
+    x, y, z = [3, 12, 30, 7], [17, 4, 2, 21], [[], [8], [5, 22], [1, 9, 14]]
+    tabs = d.counts(x, y, z)
+    marg = d.counts(x, y, [[]] * 4)
+    for t, m in zip(tabs, marg):
+        assert int(t.sum(dtype=np.int64)) == rows
+        assert np.array_equal(t.sum(axis=0, dtype=np.int64), m[0].astype(np.int64))
+    for test in ("mi", "x2"):
+        s1, d1, p1 = d.ci_discrete(test, x, y, z)
+        s2, d2, p2 = d.ci_discrete(test, y, x, z)
+        assert np.array_equal(d1, d2)
+        assert np.allclose(s1, s2, rtol=1e-12, atol=0) and np.allclose(p1, p2, rtol=1e-9, atol=1e-300)
+    # additivity over a row split, and doubling
+    cut = 3_333_337
+    lo = d.resample(np.arange(0, cut, dtype=np.int32))
+    hi = d.resample(np.arange(cut, rows, dtype=np.int32))
+    for t, a, b in zip(tabs, lo.counts(x, y, z), hi.counts(x, y, z)):
+        assert np.array_equal(t, a + b)
+    lo.release()
+    hi.release()
+    twice = d.resample(np.concatenate([np.arange(rows, dtype=np.int32)] * 2))
+    for t, t2 in zip(tabs, twice.counts(x, y, z)):
+        assert np.array_equal(2 * t, t2)
+    # G^2 scales with the sample size when every row is duplicated
+    s1, _, _ = d.ci_discrete("mi", x, y, z)
+    s2, _, _ = twice.ci_discrete("mi", x, y, z)
+    assert np.allclose(s2, 2 * s1, rtol=1e-11, atol=0)
+    twice.release()
+    d.release()
