@@ -453,6 +453,70 @@ extern "C" int bnl_counts(bnl_ctx *ctx, bnl_data data, int n, const int *x, cons
   return run_request(ctx, *ds, rq);
 }
 
+// Statistics from tables the caller already holds (device 0 only: the tables are
+// a few MB at most, the row pass that produced them is what shards).
+extern "C" int bnl_stat_from_tables(bnl_ctx *ctx, int kind, int code, double arg, int64_t nrows, int n,
+                                    const int *llx, const int *lly, const int *llz, const int *nz,
+                                    const int32_t *tables, const int64_t *table_off, double *o0,
+                                    double *o1, double *o2) {
+  if (!ctx || ctx->devs.empty()) return BNL_EINVAL;
+  if (n < 0 || (n > 0 && (!llx || !lly || !llz || !nz || !tables || !table_off || !o0)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_stat_from_tables: bad arguments");
+  if (kind == 0 ? !bnl_is_discrete_test(code)
+                : !(code == BNL_LOGLIK || code == BNL_AIC || code == BNL_BIC || code == BNL_BDE || code == BNL_BDS ||
+                    code == BNL_BDJ || code == BNL_K2 || code == BNL_FNML || code == BNL_QNML || code == BNL_NAL ||
+                    code == BNL_PNAL))
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "statistic %d (kind %d) is not computed from count tables here", code, kind);
+  if (n == 0) return BNL_OK;
+  BnlDevice &dev = ctx->devs[0];
+  BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  int rc;
+  long long cells = 0;
+  std::vector<BnlUnit> units(n);
+  for (int u = 0; u < n; u++) {
+    if (llx[u] < 1 || lly[u] < 1 || llz[u] < 1 || llx[u] > BNL_MAX_LEVELS || lly[u] > BNL_MAX_LEVELS || nz[u] < 0)
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_stat_from_tables: bad table shape for unit %d", u);
+    const long long c = (long long)llx[u] * lly[u] * llz[u];
+    if (table_off[u + 1] - table_off[u] < c || c > kMaxBatchCells)
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_stat_from_tables: table_off leaves too few cells for unit %d", u);
+    memset(&units[u], 0, sizeof(BnlUnit));
+    units[u].llx = llx[u]; units[u].lly = lly[u]; units[u].llz = llz[u];
+    units[u].cells = (int)c;
+    // the epilogue only asks whether the unit had conditioning columns / parents.
+    units[u].ncols = (kind == 0 ? 2 : 1) + nz[u];
+    units[u].table_off = cells;
+    cells += c;
+  }
+  if (cells > kMaxBatchCells)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "bnl_stat_from_tables: %lld cells exceed one batch; split the call", cells);
+  if ((rc = bnl_reserve_device(ctx, &dev.d_units, &dev.units_cap, (size_t)n))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_tables, &dev.tables_cap, (size_t)cells))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_out, &dev.out_cap, (size_t)n * 4))) return rc;
+  if ((code == BNL_FNML || code == BNL_QNML) && kind == 1 && (rc = bnl_regret_table(ctx, dev))) return rc;
+  BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_units, units.data(), (size_t)n * sizeof(BnlUnit), cudaMemcpyHostToDevice,
+                                dev.stream));
+  for (int u = 0; u < n; u++)
+    BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_tables + units[u].table_off, tables + table_off[u],
+                                  (size_t)units[u].cells * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+  if (kind == 0 && (code == BNL_JT || code == BNL_MI_SH))
+    epilogue_kernel<true><<<n, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out, kind, code,
+                                                               arg, nrows, dev.d_regret);
+  else
+    epilogue_kernel<false><<<n, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out, kind, code,
+                                                                arg, nrows, dev.d_regret);
+  BNL_CUDA(ctx, cudaGetLastError());
+  std::vector<double> out((size_t)n * 4);
+  BNL_CUDA(ctx, cudaMemcpyAsync(out.data(), dev.d_out, out.size() * sizeof(double), cudaMemcpyDeviceToHost,
+                                dev.stream));
+  BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+  for (int u = 0; u < n; u++) {
+    o0[u] = out[4 * (size_t)u];
+    if (o1) o1[u] = out[4 * (size_t)u + 1];
+    if (o2) o2[u] = out[4 * (size_t)u + 2];
+  }
+  return BNL_OK;
+}
+
 extern "C" int bnl_ci_discrete(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x,
                                const int *y, const int *z_off, const int *z_idx,
                                double *stat, double *df, double *pvalue) {

@@ -75,6 +75,29 @@ class Engine:
         if rc != 0:
             raise BnlError(rc, self._lib.bnl_last_error(self._ctx).decode())
 
+    def stat_from_tables(self, name, tables, nz, arg=0.0, nrows=0):
+        """Statistics from count tables shaped (llz, llx, lly) as DataSet.counts
+        returns them (bnl_stat_from_tables): name is a discrete test -> (stat, df,
+        p.value) or a discrete score -> (score, nparams). nz[u] = number of
+        conditioning columns / parents of unit u."""
+        kind = 0 if name in TESTS else 1
+        code = TESTS[name] if kind == 0 else SCORES[name]
+        n = len(tables)
+        shp = np.array([t.shape for t in tables], dtype=np.int32).reshape(n, 3)
+        llz, llx, lly = (np.ascontiguousarray(shp[:, i]) for i in range(3))
+        off = np.zeros(n + 1, dtype=np.int64)
+        off[1:] = np.cumsum([t.size for t in tables])
+        flat = np.concatenate([np.ascontiguousarray(t, dtype=np.int32).ravel() for t in tables]) if n else \
+            np.zeros(1, dtype=np.int32)
+        nzs = np.ascontiguousarray(nz, dtype=np.int32)
+        o = [np.zeros(max(n, 1)) for _ in range(3)]
+        self._check(self._lib.bnl_stat_from_tables(self._ctx, kind, code, float(arg), int(nrows), n, _ip(llx),
+                                                   _ip(lly), _ip(llz), _ip(nzs),
+                                                   flat.ctypes.data_as(_lib.c_i32_p),
+                                                   off.ctypes.data_as(_lib.c_i64_p), _dp(o[0]), _dp(o[1]),
+                                                   _dp(o[2])))
+        return (o[0][:n], o[1][:n], o[2][:n]) if kind == 0 else (o[0][:n], o[1][:n])
+
     def register(self, columns, nlevels=None):
         """Upload a data frame. nlevels[i] > 0 marks column i as a factor."""
         n = len(columns)

@@ -148,6 +148,23 @@ int bnl_ci_discrete(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x
                     const int *y, const int *z_off, const int *z_idx,
                     double *stat, double *df, double *pvalue);
 
+/* The statistics of bnl_ci_discrete (kind 0, code = test_e: stat / df / p-value
+ * in o0 / o1 / o2) or bnl_score_discrete (kind 1, code = score_e, arg = k or
+ * iss: score / nparams in o0 / o1) from tables the caller already holds, laid
+ * out as bnl_counts returns them: unit u has llx[u] x lly[u] x llz[u] cells at
+ * tables + table_off[u] (lly = 1 for scores), nz[u] conditioning columns or
+ * parents behind the llz[u] strata, and nrows is the row count of the data (the
+ * penalty of nal / pnal uses it). This is the second half of a row-sharded run:
+ * every GPU counts its block of rows with bnl_counts, the int32 tables are summed
+ * (ncclAllReduce over NVLink, or MPI, or on the host) and one rank turns them
+ * into statistics -- the same mi_kernel / cdlik / cdpost arithmetic on the same
+ * n[z][x][y], so the result is that of an unsharded run. Also the hook for
+ * callers that fill tables themselves (src/core/contingency.tables.c). */
+int bnl_stat_from_tables(bnl_ctx *ctx, int kind, int code, double arg, int64_t nrows, int n,
+                         const int *llx, const int *lly, const int *llz, const int *nz,
+                         const int32_t *tables, const int64_t *table_off, double *o0, double *o1,
+                         double *o2);
+
 /* ---- Gaussian ---------------------------------------------------------- */
 
 /* Gaussian CI tests (cor, zf, mi-g), served from the centred cross-product

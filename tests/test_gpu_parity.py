@@ -455,3 +455,36 @@ def test_full_size_properties(engine):
     assert np.allclose(s2, 2 * s1, rtol=1e-11, atol=0)
     twice.release()
     d.release()
+
+
+def test_row_sharded_tables_give_the_unsharded_statistics(engine):
+    """Rows split into three blocks (as ranks of a row-sharded run would hold
+    them): per-block bnl_counts tables summed, then bnl_stat_from_tables -- equal to
+    the statistics and scores of the whole data set."""
+    for name in ("alarm", "learning_test_na"):
+        names, cols, lev = load_discrete(name)
+        n = len(cols[0])
+        whole = engine.register(cols, lev)
+        cuts = [0, n // 3, n // 2 + 17, n]
+        shards = [engine.register([c[a:b] for c in cols], lev) for a, b in zip(cuts[:-1], cuts[1:])]
+        p = len(cols)
+        x, y, z = [0, 2, 4, 1], [1, 3, 5, 0], [[], [0], [1, 3], [2, 3, 4]]
+        summed = [sum(t.astype(np.int64) for t in ts).astype(np.int32)
+                  for ts in zip(*[s.counts(x, y, z) for s in shards])]
+        for t, w in zip(summed, whole.counts(x, y, z)):
+            assert np.array_equal(t, w)
+        for test in ("mi", "x2", "mi-adf", "jt", "mi-sh"):
+            got = engine.stat_from_tables(test, summed, [len(q) for q in z])
+            ref = whole.ci_discrete(test, x, y, z)
+            for g, r in zip(got, ref):
+                assert np.array_equal(g, r), test
+        # scores: node x[u] with parents z[u]
+        tabs = [sum(t.astype(np.int64) for t in ts).astype(np.int32)
+                for ts in zip(*[s.counts(x, [-1] * 4, z) for s in shards])]
+        for score, arg in (("bic", 4.2), ("bde", 1.0), ("bds", 2.0), ("k2", 0.0), ("fnml", 0.0), ("qnml", 0.0),
+                           ("pnal", 1.5)):
+            got = engine.stat_from_tables(score, tabs, [len(q) for q in z], arg, nrows=n)
+            ref = whole.score_discrete(score, x, z, arg)
+            assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]), score
+        for d in shards + [whole]:
+            d.release()

@@ -74,3 +74,38 @@ def test_block_partition_matches_the_library():
             edges = [_block(n, world, r) for r in range(world)]
             assert edges[0][0] == 0 and edges[-1][1] == n
             assert all(edges[r][1] == edges[r + 1][0] for r in range(world - 1))
+
+
+def _row_worker(rank, world, port, units, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import oracle as orc
+    names, cols, nlev = load_discrete("learning_test")
+    n = len(cols[0])
+    a, b = _block(n, world, rank)                       # this rank's block of ROWS
+    flat = []
+    for x, y, z in units:
+        t = orc.counts(cols[x][a:b], nlev[x], cols[y][a:b], nlev[y], [cols[j][a:b] for j in z],
+                       [nlev[j] for j in z])
+        flat.append(t.ravel())
+    buf = torch.from_numpy(np.concatenate(flat).astype(np.int32))
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM)           # what ncclAllReduce(sum, int32) does on the GPUs
+    if rank == 0:
+        np.save(out_path, buf.numpy())
+    dist.destroy_process_group()
+
+
+def test_row_sharding_allreduce_world_size_2(tmp_path):
+    """Rows sharded over two ranks: per-rank tables, one int32 sum all-reduce, and
+    the result is the table of the whole data set (the statistics then come from
+    bnl_stat_from_tables; tests/test_gpu_parity.py covers that half on the device)."""
+    from oracle import oracle as orc
+    names, cols, nlev = load_discrete("learning_test")
+    units = [(0, 1, []), (2, 3, [0]), (4, 5, [1, 2]), (1, 0, [3, 4, 5])]
+    out = str(tmp_path / "tables.npy")
+    mp.spawn(_row_worker, args=(2, _free_port(), units, out), nprocs=2, join=True)
+    got = np.load(out)
+    ref = np.concatenate([orc.counts(cols[x], nlev[x], cols[y], nlev[y], [cols[j] for j in z],
+                                     [nlev[j] for j in z]).ravel() for x, y, z in units])
+    assert np.array_equal(got, ref)
