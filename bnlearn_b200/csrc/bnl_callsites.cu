@@ -409,7 +409,9 @@ int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_o
   std::vector<double> score(std::max(m, 1));
   if (m > 0) {
     const int *pi = pa_idx.empty() ? nullptr : pa_idx.data();
-    int rc = is_discrete_score(score_e)
+    int rc = score_e >= BNL_LOGLIK_CG
+      ? bnl_score_cg(ctx, data, score_e, k_or_iss, m, target.data(), pa_off.data(), pi, score.data(), nullptr)
+      : is_discrete_score(score_e)
       ? bnl_score_discrete(ctx, data, score_e, k_or_iss, m, target.data(), pa_off.data(), pi, score.data(), nullptr)
       : bnl_score_gaussian(ctx, data, score_e, k_or_iss, m, target.data(), pa_off.data(), pi, score.data(), nullptr);
     if (rc) return rc;

@@ -370,3 +370,164 @@ extern "C" int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, d
   if (cov) memcpy(cov, ds.h_cov.data(), ds.h_cov.size() * sizeof(double));
   return BNL_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Conditional Gaussian scores (loglik-cg, aic-cg, bic-cg): loglik_cgnode
+// (src/scores/cg.loglikelihood.c:119-199) sends every node to the discrete code,
+// to the Gaussian code, or -- numeric node with at least one discrete parent --
+// to the conditional least squares of ccgloglik (:10-117); the same split here.
+
+namespace {
+
+int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units, double *score, double *npar) {
+  const int n = (int)units.size();
+  if (n == 0) return BNL_OK;
+  BnlDevice &dev = ctx->devs[0];
+  BnlDeviceData &dd = ds.dev[0];
+  BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  long long total = 0;
+  for (auto &u : units) {
+    u.off = total;
+    total += (long long)u.nconfig * (1 + u.K + u.K * (u.K + 1) / 2);
+  }
+  int rc;
+  double *mom = nullptr;
+  BnlCgUnit *d_units = nullptr;
+  double *d_out = nullptr;
+  int *d_err = nullptr;
+  const size_t mom_bytes = (size_t)total * sizeof(double), unit_bytes = (size_t)n * sizeof(BnlCgUnit);
+  const size_t out_bytes = (size_t)n * 4 * sizeof(double);
+  if ((rc = bnl_pool_alloc(ctx, dev, (void **)&mom, mom_bytes))) return rc;
+  if ((rc = bnl_pool_alloc(ctx, dev, (void **)&d_units, unit_bytes))) { bnl_pool_free(dev, mom, mom_bytes); return rc; }
+  if ((rc = bnl_pool_alloc(ctx, dev, (void **)&d_out, out_bytes + 256))) {
+    bnl_pool_free(dev, mom, mom_bytes); bnl_pool_free(dev, d_units, unit_bytes);
+    return rc;
+  }
+  d_err = reinterpret_cast<int *>(reinterpret_cast<char *>(d_out) + out_bytes);
+  std::vector<double> out((size_t)n * 4);
+  int err = 0;
+  cudaError_t e = cudaMemsetAsync(mom, 0, mom_bytes, dev.stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_err, 0, sizeof(int), dev.stream);
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(d_units, units.data(), unit_bytes, cudaMemcpyHostToDevice, dev.stream);
+  if (e == cudaSuccess) {
+    const int chunks = (int)std::max(1ll, std::min(128ll, (ds.nobs + 8191) / 8192));
+    const long long chunk_rows = (ds.nobs + chunks - 1) / chunks;
+    const dim3 g((unsigned)chunks, (unsigned)n);
+    const size_t smem = BNL_CG_SMEM_DOUBLES * sizeof(double);
+    cg_moments_kernel<1><<<g, BNL_CG_THREADS, smem, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8, ds.stride_u8,
+                                                                 ds.nobs, chunk_rows, d_units, mom, d_err);
+    cg_means_kernel<<<dim3(8, (unsigned)n), 128, 0, dev.stream>>>(d_units, n, mom);
+    cg_moments_kernel<2><<<g, BNL_CG_THREADS, smem, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8, ds.stride_u8,
+                                                                 ds.nobs, chunk_rows, d_units, mom, d_err);
+    cg_score_kernel<<<(n + 63) / 64, 64, 0, dev.stream>>>(d_units, n, mom, d_out);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(out.data(), d_out, out_bytes, cudaMemcpyDeviceToHost, dev.stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&err, d_err, sizeof(int), cudaMemcpyDeviceToHost, dev.stream);
+  const cudaError_t es = cudaStreamSynchronize(dev.stream);
+  bnl_pool_free(dev, mom, mom_bytes);
+  bnl_pool_free(dev, d_units, unit_bytes);
+  bnl_pool_free(dev, d_out, out_bytes + 256);
+  if (e != cudaSuccess || es != cudaSuccess)
+    return bnl_fail(ctx, BNL_ECUDA, "conditional Gaussian kernels failed: %s",
+                    cudaGetErrorString(e != cudaSuccess ? e : es));
+  if (err)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED,
+                    "conditional Gaussian scores need complete data (a missing value was met)");
+  for (int u = 0; u < n; u++) { score[u] = out[4 * (size_t)u]; npar[u] = out[4 * (size_t)u + 1]; }
+  return BNL_OK;
+}
+
+}  // namespace
+
+extern "C" int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n, const int *target,
+                            const int *pa_off, const int *pa_idx, double *score, double *nparams) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  if (score_e != BNL_LOGLIK_CG && score_e != BNL_AIC_CG && score_e != BNL_BIC_CG)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a conditional Gaussian score handled here", score_e);
+  if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_score_cg: bad arguments");
+  const int d_code = score_e == BNL_LOGLIK_CG ? BNL_LOGLIK : (score_e == BNL_AIC_CG ? BNL_AIC : BNL_BIC);
+  const int g_code = score_e == BNL_LOGLIK_CG ? BNL_LOGLIK_G : (score_e == BNL_AIC_CG ? BNL_AIC_G : BNL_BIC_G);
+  // three sub-requests in the caller's order, plus the nodes that cannot be scored.
+  std::vector<int> didx, gidx, cidx;
+  std::vector<int> dt, doff(1, 0), dpa, gt, goff(1, 0), gpa;
+  std::vector<BnlCgUnit> cg;
+  for (int u = 0; u < n; u++) {
+    const int t = target[u], p0 = pa_off[u], np = pa_off[u + 1] - p0;
+    if (t < 0 || t >= ds.ncols || np < 0)
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_score_cg: unit %d refers to a column out of range", u);
+    int ndp = 0;
+    for (int j = 0; j < np; j++) {
+      const int c = pa_idx[p0 + j];
+      if (c < 0 || c >= ds.ncols) return bnl_fail(ctx, BNL_EINVAL, "bnl_score_cg: unit %d refers to a column out of range", u);
+      ndp += !ds.is_numeric[c];
+    }
+    if (!ds.is_numeric[t]) {
+      if (ndp != np) {           // a discrete node cannot have numeric parents (:155-160)
+        score[u] = -INFINITY;
+        if (nparams) nparams[u] = 0.0;
+        continue;
+      }
+      didx.push_back(u); dt.push_back(t);
+      dpa.insert(dpa.end(), pa_idx + p0, pa_idx + p0 + np);
+      doff.push_back((int)dpa.size());
+    } else if (ndp == 0) {
+      gidx.push_back(u); gt.push_back(t);
+      gpa.insert(gpa.end(), pa_idx + p0, pa_idx + p0 + np);
+      goff.push_back((int)gpa.size());
+    } else {
+      BnlCgUnit cu;
+      memset(&cu, 0, sizeof(cu));
+      if (np - ndp + 1 > BNL_CG_MAXG || ndp > BNL_CG_MAXD)
+        return bnl_fail(ctx, BNL_EUNSUPPORTED, "unit %d: at most %d numeric and %d discrete parents", u,
+                        BNL_CG_MAXG - 1, BNL_CG_MAXD);
+      cu.gslot[cu.K++] = ds.slot[t];
+      long long nconfig = 1;
+      for (int j = 0; j < np; j++) {
+        const int c = pa_idx[p0 + j];
+        if (ds.is_numeric[c]) cu.gslot[cu.K++] = ds.slot[c];
+        else {
+          cu.dslot[cu.nd] = ds.slot[c];
+          cu.dmul[cu.nd++] = (int)nconfig;
+          nconfig *= ds.nlevels[c];
+          if (nconfig >= INT32_MAX / 64)
+            return bnl_fail(ctx, BNL_EOVERFLOW, "unit %d: too many configurations of the discrete parents", u);
+        }
+      }
+      cu.nconfig = (int)nconfig;
+      cidx.push_back(u);
+      cg.push_back(cu);
+    }
+  }
+  int rc;
+  std::vector<double> s, p;
+  auto scatter = [&](const std::vector<int> &idx) {
+    for (size_t i = 0; i < idx.size(); i++) { score[idx[i]] = s[i]; if (nparams) nparams[idx[i]] = p[i]; }
+  };
+  if (!didx.empty()) {
+    s.assign(didx.size(), 0.0); p.assign(didx.size(), 0.0);
+    if ((rc = bnl_score_discrete(ctx, data, d_code, k, (int)didx.size(), dt.data(), doff.data(),
+                                 dpa.empty() ? nullptr : dpa.data(), s.data(), p.data()))) return rc;
+    scatter(didx);
+  }
+  if (!gidx.empty()) {
+    s.assign(gidx.size(), 0.0); p.assign(gidx.size(), 0.0);
+    if ((rc = bnl_score_gaussian(ctx, data, g_code, k, (int)gidx.size(), gt.data(), goff.data(),
+                                 gpa.empty() ? nullptr : gpa.data(), s.data(), p.data()))) return rc;
+    scatter(gidx);
+  }
+  if (!cidx.empty()) {
+    s.assign(cidx.size(), 0.0); p.assign(cidx.size(), 0.0);
+    if ((rc = run_cg_units(ctx, ds, cg, s.data(), p.data()))) return rc;
+    if (score_e != BNL_LOGLIK_CG)
+      for (size_t i = 0; i < cidx.size(); i++) s[i] -= k * p[i];      // per.node.score.c: res - k * nparams
+    scatter(cidx);
+  }
+  return BNL_OK;
+}

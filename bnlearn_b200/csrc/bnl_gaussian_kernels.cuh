@@ -709,3 +709,177 @@ masked_shrink_kernel(const double *__restrict__ data, size_t stride, long long n
   const double t = block_sum_256(acc, sm);
   if (threadIdx.x == 0) *out = t;
 }
+
+// ---------------------------------------------------------------------------
+// Conditional Gaussian nodes (src/scores/cg.loglikelihood.c:10-117 over c_cls,
+// src/math/conditional.least.squares.c): a numeric node regressed on its numeric
+// parents separately within every configuration of its discrete parents. The
+// moments of every (unit, configuration) are gathered in two row passes -- counts
+// and sums, then centred cross-products -- into
+//   mom[off + s * M + 0]             rows of configuration s
+//   mom[off + s * M + 1 + i]         mean of numeric column i (0 = the node), sums until pass 1 is finalised
+//   mom[off + s * M + 1 + K + pair]  centred cross-products, pairs i <= j in row-major order
+// with K numeric columns and M = 1 + K + K (K + 1) / 2. A CTA works on one row
+// chunk of one unit and accumulates in shared memory when the unit's block fits
+// (BNL_CG_SMEM_DOUBLES), then adds its block to the global one; double atomics, so
+// the last bits depend on the order of arrival.
+
+#define BNL_CG_MAXG 8            // numeric columns per unit (node + 7 numeric parents)
+#define BNL_CG_MAXD 8            // discrete parents per unit
+#define BNL_CG_SMEM_DOUBLES 5120
+#define BNL_CG_THREADS 256
+
+struct BnlCgUnit {
+  long long off;                 // first double of the unit's block in `mom`
+  int nconfig, K, nd, pad;
+  int gslot[BNL_CG_MAXG];        // numeric slots, node first
+  int dslot[BNL_CG_MAXD];        // packed factor slots
+  int dmul[BNL_CG_MAXD];         // configuration multipliers (first parent fastest)
+};
+
+template <int PASS>
+__global__ void __launch_bounds__(BNL_CG_THREADS)
+cg_moments_kernel(const double *__restrict__ f64, size_t fstride, const uint8_t *__restrict__ u8,
+                  size_t ustride, long long nobs, long long chunk_rows,
+                  const BnlCgUnit *__restrict__ units, double *__restrict__ mom, int *__restrict__ err) {
+  extern __shared__ double cgsm[];
+  const BnlCgUnit U = units[blockIdx.y];
+  const int K = U.K, M = 1 + K + K * (K + 1) / 2;
+  const long long total = (long long)U.nconfig * M;
+  const bool staged = total <= BNL_CG_SMEM_DOUBLES;
+  double *acc = staged ? cgsm : mom + U.off;
+  if (staged) {
+    for (int i = threadIdx.x; i < (int)total; i += BNL_CG_THREADS) cgsm[i] = 0.0;
+    __syncthreads();
+  }
+  const double *gm = mom + U.off;           // finalised means (pass 2 only)
+  const long long r0 = blockIdx.x * chunk_rows, r1 = min(nobs, r0 + chunk_rows);
+  for (long long r = r0 + threadIdx.x; r < r1; r += BNL_CG_THREADS) {
+    int s = 0;
+    bool bad = false;
+    for (int j = 0; j < U.nd; j++) {
+      const unsigned b = u8[ustride * U.dslot[j] + r];
+      bad |= b >= 0x80u;
+      s += (int)b * U.dmul[j];
+    }
+    double v[BNL_CG_MAXG];
+#pragma unroll
+    for (int i = 0; i < BNL_CG_MAXG; i++)
+      if (i < K) { v[i] = f64[fstride * U.gslot[i] + r]; bad |= isnan(v[i]); }
+    if (bad) { *err = 1; continue; }        // the complete-data code path: missing values are refused
+    double *a = acc + (size_t)s * M;
+    if (PASS == 1) {
+      atomicAdd(a, 1.0);
+#pragma unroll
+      for (int i = 0; i < BNL_CG_MAXG; i++) if (i < K) atomicAdd(a + 1 + i, v[i]);
+    } else {
+      const double *m = gm + (size_t)s * M + 1;
+#pragma unroll
+      for (int i = 0; i < BNL_CG_MAXG; i++) if (i < K) v[i] -= m[i];
+      int p = 1 + K;
+#pragma unroll
+      for (int i = 0; i < BNL_CG_MAXG; i++)
+#pragma unroll
+        for (int j = i; j < BNL_CG_MAXG; j++)
+          if (j < K) atomicAdd(a + p++, v[i] * v[j]);
+    }
+  }
+  if (staged) {
+    __syncthreads();
+    double *g = mom + U.off;
+    for (int i = threadIdx.x; i < (int)total; i += BNL_CG_THREADS) {
+      const int w = i % M;
+      const bool mine = PASS == 1 ? w <= K : w > K;
+      if (mine && cgsm[i] != 0.0) atomicAdd(g + i, cgsm[i]);
+    }
+  }
+}
+
+// sums -> means, once per (unit, configuration).
+__global__ void cg_means_kernel(const BnlCgUnit *__restrict__ units, int n, double *__restrict__ mom) {
+  const int u = blockIdx.y;
+  if (u >= n) return;
+  const BnlCgUnit U = units[u];
+  const int K = U.K, M = 1 + K + K * (K + 1) / 2;
+  for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < U.nconfig; s += gridDim.x * blockDim.x) {
+    double *a = mom + U.off + (size_t)s * M;
+    if (a[0] > 0.0) for (int i = 0; i < K; i++) a[1 + i] /= a[0];
+  }
+}
+
+// Conditional least squares of one configuration from its moments: residual sum
+// of squares of node ~ 1 + numeric parents. c_cls1 / c_cls2 test collinearity on
+// the SUMS of squares (not on variances, unlike c_ols1 / c_ols2); three or more
+// regressors go through c_qr, i.e. dqrdc2's column-dropping rule as in
+// gauss_score_kernel. S is the K x K centred cross-product matrix (row-major,
+// K <= BNL_CG_MAXG), mean[] the column means, ns the rows of the configuration.
+__device__ double cg_stratum_sse(double *S, const double *mean, double ns, int K) {
+  const double tol = bnl::kSqrtEps;
+  const int np = K - 1;
+  auto A = [&](int i, int j) -> double & { return S[i * K + j]; };
+  if (np == 0) return A(0, 0);
+  if (np == 1) return fabs(A(1, 1)) < tol ? A(0, 0) : A(0, 0) - A(0, 1) / A(1, 1) * A(0, 1);
+  if (np == 2) {
+    const double c11 = A(1, 1), c22 = A(2, 2), c12 = A(1, 2), c01 = A(0, 1), c02 = A(0, 2);
+    const bool s1 = fabs(c11) < tol;
+    const bool s2 = (fabs(c22) < tol) || (fabs(c12) / sqrt(c11 * c22) > 1.0 - tol);
+    double fit;
+    if (s1 && !s2) fit = c02 / c22 * c02;
+    else if (!s1 && s2) fit = c01 / c11 * c01;
+    else if (s1 && s2) fit = 0.0;
+    else {
+      const double den = c11 * c22 - c12 * c12;
+      const double b1 = (c22 * c01 - c12 * c02) / den, b2 = (c11 * c02 - c12 * c01) / den;
+      fit = b1 * c01 + b2 * c02;
+    }
+    return A(0, 0) - fit;
+  }
+  for (int l = 1; l < K; l++) {
+    const double orig = sqrt(A(l, l) + ns * mean[l] * mean[l]);
+    const double piv = A(l, l);
+    if (!(piv > 0.0) || sqrt(piv) < orig * tol) continue;          // dropped column
+    for (int i = 0; i < K; i++) {
+      if (i == l) continue;
+      const double f = A(i, l) / piv;
+      if (f == 0.0) continue;
+      for (int j = 0; j < K; j++) if (j != l) A(i, j) -= f * A(l, j);
+    }
+    for (int i = 0; i < K; i++) if (i != l) { A(i, l) = 0.0; A(l, i) = 0.0; }
+  }
+  return A(0, 0);
+}
+
+// One thread per unit: log-likelihood = sum over the observed configurations;
+// -Inf as soon as one of them is singular (sd < sqrt(eps), which includes
+// configurations with no more rows than coefficients).
+__global__ void cg_score_kernel(const BnlCgUnit *__restrict__ units, int n, const double *__restrict__ mom,
+                                double *__restrict__ out) {
+  const int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n) return;
+  const BnlCgUnit U = units[u];
+  const int K = U.K, np = K - 1, M = 1 + K + K * (K + 1) / 2;
+  const double tol = bnl::kSqrtEps;
+  bnl::KahanSum tot;
+  bool singular = false;
+  double S[BNL_CG_MAXG * BNL_CG_MAXG], mean[BNL_CG_MAXG];
+  for (int s = 0; s < U.nconfig && !singular; s++) {
+    const double *a = mom + U.off + (size_t)s * M;
+    const double ns = a[0];
+    if (ns == 0.0) continue;                                       // sd = NA: no row refers to it
+    if (ns <= (double)(np + 1)) { singular = true; break; }       // sd = 0
+    int p = 1 + K;
+    for (int i = 0; i < K; i++) {
+      mean[i] = a[1 + i];
+      for (int j = i; j < K; j++) { S[i * K + j] = a[p]; S[j * K + i] = a[p]; p++; }
+    }
+    double sse = cg_stratum_sse(S, mean, ns, K);
+    if (sse < 0.0) sse = 0.0;
+    const double sd = sqrt(sse / (ns - (double)np - 1.0));
+    if (!(sd >= tol)) { singular = true; break; }
+    tot.add(-ns * (bnl::kLnSqrt2Pi + log(sd)) - 0.5 * sse / (sd * sd));
+  }
+  out[(size_t)u * 4 + 0] = singular ? -INFINITY : tot.value();
+  out[(size_t)u * 4 + 1] = (double)U.nconfig * (double)(np + 2);
+  out[(size_t)u * 4 + 2] = 0.0;
+  out[(size_t)u * 4 + 3] = 0.0;
+}

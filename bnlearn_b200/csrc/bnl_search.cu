@@ -213,6 +213,8 @@ int node_scores(bnl_ctx *ctx, bnl_data data, int score_e, double arg, const Sear
     off.push_back((int)idx.size());
   }
   const int *pi = idx.empty() ? nullptr : idx.data();
+  if (score_e >= BNL_LOGLIK_CG)
+    return bnl_score_cg(ctx, data, score_e, arg, (int)nodes.size(), nodes.data(), off.data(), pi, out, nullptr);
   return discrete_score(score_e)
     ? bnl_score_discrete(ctx, data, score_e, arg, (int)nodes.size(), nodes.data(), off.data(), pi, out, nullptr)
     : bnl_score_gaussian(ctx, data, score_e, arg, (int)nodes.size(), nodes.data(), off.data(), pi, out, nullptr);
@@ -245,6 +247,8 @@ extern "C" int bnl_hc(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
     equivalence = true;
     for (int f : it->second.slot_has_na) if (f) equivalence = false;
   }
+  // the -cg scores are not score equivalent (the conservative default of
+  // is.score.equivalent): equivalence stays false for them.
   std::vector<int> updated(n);
   for (int i = 0; i < n; i++) updated[i] = i;
   int rc = node_scores(ctx, data, score_e, k_or_iss, S, updated, S.reference.data());

@@ -13,7 +13,8 @@ from . import _lib
 
 TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-g-sh": 41}
 SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
-          "loglik-g": 100, "aic-g": 102, "bic-g": 103, "bge": 105, "nal-g": 106, "pnal-g": 107}
+          "loglik-g": 100, "aic-g": 102, "bic-g": 103, "bge": 105, "nal-g": 106, "pnal-g": 107,
+          "loglik-cg": 200, "aic-cg": 202, "bic-cg": 203}
 DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf", "jt", "mi-sh")
 GAUSSIAN_TESTS = ("cor", "zf", "mi-g", "mi-g-sh")
 DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds", "bdj", "k2", "fnml", "qnml", "nal", "pnal")
@@ -290,6 +291,17 @@ class DataSet:
         m[iu] = tri[:len(iu[0])]
         return m + m.T
 
+    def score_cg(self, score, target, parents, k=0.0):
+        """Conditional Gaussian node scores on mixed data (bnl_score_cg)."""
+        e = self.engine
+        t = np.ascontiguousarray(target, dtype=np.int32)
+        po, pi = _as_csr(parents)
+        n = len(t)
+        sc, npar = np.zeros(max(n, 1)), np.zeros(max(n, 1))
+        e._check(e._lib.bnl_score_cg(e._ctx, self.handle, SCORES[score], float(k), n, _ip(t), _ip(po), _ip(pi),
+                                     _dp(sc), _dp(npar)))
+        return sc[:n], npar[:n]
+
     def set_bge_prior(self, iss_mu=1.0, iss_w=0.0, nu=None):
         """BGe hyper-parameters (iss_w <= 0: ncol + 2; nu None: the column means)."""
         e = self.engine
@@ -312,4 +324,6 @@ class DataSet:
     def score(self, score, target, parents, arg=0.0):
         if score in DISCRETE_SCORES:
             return self.score_discrete(score, target, parents, arg)
+        if score.endswith("-cg"):
+            return self.score_cg(score, target, parents, arg)
         return self.score_gaussian(score, target, parents, arg)

@@ -54,7 +54,8 @@ enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4, BNL_JT = 10, BNL_
 enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
        BNL_FNML = 11, BNL_QNML = 12, BNL_NAL = 13, BNL_PNAL = 14,
        BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103, BNL_BGE = 105, BNL_NAL_G = 106,
-       BNL_PNAL_G = 107 };
+       BNL_PNAL_G = 107,
+       BNL_LOGLIK_CG = 200, BNL_AIC_CG = 202, BNL_BIC_CG = 203 };
 
 /* ---- context ---------------------------------------------------------- */
 
@@ -184,6 +185,18 @@ int bnl_ci_gaussian(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x
 int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n,
                        const int *target, const int *pa_off, const int *pa_idx,
                        double *score, double *nparams);
+
+/* Conditional Gaussian node scores (loglik-cg, aic-cg, bic-cg) on a data set
+ * that mixes factors and numeric columns: loglik_cgnode (src/scores/
+ * cg.loglikelihood.c:119-199). Discrete nodes with discrete parents take the
+ * discrete score, numeric nodes with numeric parents the Gaussian one, a
+ * discrete node with a numeric parent scores -Inf, and a numeric node with at
+ * least one discrete parent is regressed on its numeric parents within every
+ * configuration of the discrete ones (ccgloglik :10-117 over c_cls,
+ * src/math/conditional.least.squares.c): nparams = configurations x (numeric
+ * parents + 2). Complete data only; at most 7 numeric and 8 discrete parents. */
+int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n, const int *target,
+                 const int *pa_off, const int *pa_idx, double *score, double *nparams);
 
 /* Copy the p x p covariance matrix (divisor nobs - 1, column-major, p = number
  * of numeric columns in registration order) and the column means to the host.

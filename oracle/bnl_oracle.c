@@ -816,3 +816,91 @@ double orc_score_bge(const double *const *cols, int np, int n, int data_ncols, d
   free(mean);
   return (double)lp;
 }
+
+/* ------------------------------------------------------------------------
+ * Conditional Gaussian log-likelihood of a numeric node given numeric parents
+ * gp[0..ngp) within the configurations cfg[] (1-based, nconfig of them) of its
+ * discrete parents: c_fast_ccgloglik (src/scores/cg.loglikelihood.c:54-117) over
+ * c_cls (src/math/conditional.least.squares.c): per configuration the closed
+ * forms for 0 / 1 / 2 regressors -- with the collinearity guards applied to the
+ * sums of squares, :109, 262-265 -- or R's pivoted QR for more (c_clsp -> c_qr);
+ * sd = 0 when a configuration has no more rows than coefficients; any singular
+ * configuration makes the node -Inf. nparams = nconfig * (ngp + 2). */
+double orc_cg_loglik(const double *x, const double *const *gp, int ngp, const int *cfg, int nconfig,
+    int n, double *nparams) {
+  if (nparams) *nparams = (double)nconfig * (ngp + 2);
+  double res = 0;
+  int *rows = malloc((size_t)(n > 0 ? n : 1) * sizeof(int));
+  double *y = malloc((size_t)(n > 0 ? n : 1) * sizeof(double));
+  double **g = malloc((size_t)(ngp > 0 ? ngp : 1) * sizeof(double *));
+  for (int j = 0; j < ngp; j++) g[j] = malloc((size_t)(n > 0 ? n : 1) * sizeof(double));
+  double *fitted = malloc((size_t)(n > 0 ? n : 1) * sizeof(double));
+  for (int s = 1; s <= nconfig && res != -INFINITY; s++) {
+    int ns = 0;
+    for (int i = 0; i < n; i++) if (cfg[i] == s) rows[ns++] = i;
+    if (ns == 0) continue;
+    for (int r = 0; r < ns; r++) {
+      y[r] = x[rows[r]];
+      for (int j = 0; j < ngp; j++) g[j][r] = gp[j][rows[r]];
+    }
+    double sd = 0;
+    if (ns <= ngp + 1) { res = -INFINITY; break; }
+    long double my = 0, m1 = 0, m2 = 0;
+    for (int r = 0; r < ns; r++) my += y[r];
+    my /= ns;
+    if (ngp == 0) {
+      for (int r = 0; r < ns; r++) fitted[r] = (double)my;
+    } else if (ngp == 1) {
+      for (int r = 0; r < ns; r++) m1 += g[0][r];
+      m1 /= ns;
+      long double v = 0, c = 0;
+      for (int r = 0; r < ns; r++) { v += (g[0][r] - m1) * (g[0][r] - m1); c += (y[r] - my) * (g[0][r] - m1); }
+      double b = fabsl(v) < ORC_TOL ? 0 : (double)(c / v);
+      double a = (double)(my - m1 * b);
+      for (int r = 0; r < ns; r++) fitted[r] = a + g[0][r] * b;
+    } else if (ngp == 2) {
+      for (int r = 0; r < ns; r++) { m1 += g[0][r]; m2 += g[1][r]; }
+      m1 /= ns; m2 /= ns;
+      long double v1 = 0, v2 = 0, c01 = 0, c02 = 0, c12 = 0;
+      for (int r = 0; r < ns; r++) {
+        long double d0 = y[r] - my, d1 = g[0][r] - m1, d2 = g[1][r] - m2;
+        v1 += d1 * d1; v2 += d2 * d2; c01 += d0 * d1; c02 += d0 * d2; c12 += d1 * d2;
+      }
+      int s1 = fabsl(v1) < ORC_TOL;
+      int s2 = (fabsl(v2) < ORC_TOL) || (fabsl(c12) / sqrt((double)(v1 * v2)) > 1 - ORC_TOL);
+      double b1 = 0, b2 = 0;
+      if (s1 && !s2) b2 = (double)(c02 / v2);
+      else if (!s1 && s2) b1 = (double)(c01 / v1);
+      else if (!s1 && !s2) {
+        long double den = v1 * v2 - c12 * c12;
+        b1 = (double)((v2 * c01 - c12 * c02) / den);
+        b2 = (double)((v1 * c02 - c12 * c01) / den);
+      }
+      double a = (double)(my - m1 * b1 - m2 * b2);
+      for (int r = 0; r < ns; r++) fitted[r] = a + g[0][r] * b1 + g[1][r] * b2;
+    } else {
+      /* c_qr: intercept + regressors through dqrdc2 / dqrsl (job: fitted values). */
+      int ncol = ngp + 1, rank = 0, info = 0, job = 11;
+      double *qr = malloc((size_t)ns * ncol * sizeof(double));
+      double *qraux = calloc((size_t)ncol, sizeof(double)), *work = calloc((size_t)2 * ncol, sizeof(double));
+      int *pivot = malloc((size_t)ncol * sizeof(int));
+      double *rsd = malloc((size_t)ns * sizeof(double)), tol = ORC_TOL;
+      for (int r = 0; r < ns; r++) qr[r] = 1;
+      for (int j = 0; j < ngp; j++) for (int r = 0; r < ns; r++) qr[(size_t)(j + 1) * ns + r] = g[j][r];
+      for (int j = 0; j < ncol; j++) pivot[j] = j + 1;
+      minir_f77_dqrdc2(qr, &ns, &ns, &ncol, &tol, &rank, qraux, pivot, work);
+      memcpy(fitted, y, (size_t)ns * sizeof(double));
+      minir_f77_dqrsl(qr, &ns, &ns, &rank, qraux, fitted, NULL, fitted, NULL, rsd, fitted, &job, &info);
+      free(qr); free(qraux); free(work); free(pivot); free(rsd);
+      if (info != 0) { res = -INFINITY; break; }
+    }
+    long double ssr = 0;
+    for (int r = 0; r < ns; r++) ssr += (y[r] - fitted[r]) * (y[r] - fitted[r]);
+    sd = sqrt((double)(ssr / (ns - ngp - 1)));
+    if (sd < ORC_TOL) { res = -INFINITY; break; }
+    for (int r = 0; r < ns; r++) res += Rf_dnorm4(y[r], fitted[r], sd, 1);
+  }
+  for (int j = 0; j < ngp; j++) free(g[j]);
+  free(g); free(rows); free(y); free(fitted);
+  return res;
+}

@@ -56,6 +56,8 @@ def lib():
     L.orc_score_gaussian.argtypes = [C.c_int, c_dbl_p, pp_d, C.c_int, C.c_int, C.c_double, c_dbl_p]
     L.orc_score_bge.restype = C.c_double
     L.orc_score_bge.argtypes = [pp_d, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, c_dbl_p]
+    L.orc_cg_loglik.restype = C.c_double
+    L.orc_cg_loglik.argtypes = [c_dbl_p, pp_d, C.c_int, c_int_p, C.c_int, C.c_int, c_dbl_p]
     L.orc_pcor.restype = C.c_double
     L.orc_pcor.argtypes = [c_dbl_p, C.c_int, c_int_p]
     for name, nargs in (("Rf_lgammafn", 1),):
@@ -161,6 +163,28 @@ def score_bge(x, pcols, data_ncols, iss_mu, iss_w, nu):
     nu = np.ascontiguousarray(nu, dtype=np.float64)
     return lib().orc_score_bge(ptrs, len(cs) - 1, len(cs[0]), int(data_ncols), float(iss_mu),
                                float(iss_w), _dp(nu))
+
+
+def score_cg(score, x, xlev, pcols, plev, k=0.0):
+    """loglik-cg / aic-cg / bic-cg of one node (src/scores/cg.loglikelihood.c:119-199):
+    xlev / plev are the numbers of levels, 0 for numeric columns. Returns (score, nparams)."""
+    base = score[:-3]                                   # loglik / aic / bic
+    disc = [i for i, l in enumerate(plev) if l > 0]
+    cont = [i for i, l in enumerate(plev) if l == 0]
+    if xlev > 0:
+        if cont:
+            return -np.inf, 0.0
+        return score_discrete(base, x, xlev, pcols, plev, k)
+    if not disc:
+        return score_gaussian(base + "-g", x, pcols, k)
+    cfg, nconfig = config([pcols[i] for i in disc], [plev[i] for i in disc], 1)
+    xs, _ = _dcols([x])
+    gs, gptrs = _dcols([pcols[i] for i in cont])
+    npar = C.c_double()
+    v = lib().orc_cg_loglik(_dp(xs[0]), gptrs, len(cont), _ip(cfg), int(nconfig), len(xs[0]), C.byref(npar))
+    if base != "loglik":
+        v -= k * npar.value
+    return v, npar.value
 
 
 def robust_difference(old, new):

@@ -357,6 +357,53 @@ def nml_outputs():
     print("wrote ref_nml.json")
 
 
+def load_mixed(name):
+    """-> (names, columns, nlevels): int32 1-based codes for factors, float64 otherwise."""
+    z = np.load(os.path.join(HERE, "data_%s.npz" % name))
+    nlev = [int(v) for v in z["nlevels"]]
+    cols, fi, gi = [], 0, 0
+    for l in nlev:
+        if l > 0:
+            cols.append(z["codes"][fi].astype(np.int32) + 1)
+            fi += 1
+        else:
+            cols.append(np.ascontiguousarray(z["values"][gi]))
+            gi += 1
+    return [str(s) for s in z["names"]], cols, nlev
+
+
+def cg_outputs():
+    """Conditional Gaussian scores on the bundled mixed data set clgaussian.test
+    (4 factors, 4 numeric columns, 5000 rows); own file and RNG."""
+    from oracle import refapi as ra, refbind as rb
+    obj = read_rda(os.path.join(REF, "data", "clgaussian.test.rda"))["clgaussian.test"]
+    names, cols = data_frame_columns(obj)
+    nlev = [len(c[1]) if isinstance(c, tuple) else 0 for c in cols]
+    codes = np.stack([np.asarray(c[0], dtype=np.int64) - 1 for c in cols if isinstance(c, tuple)])
+    values = np.stack([np.asarray(c, dtype=np.float64) for c in cols if not isinstance(c, tuple)])
+    np.savez_compressed(os.path.join(HERE, "data_clgaussian_test.npz"), names=np.array(names),
+                        nlevels=np.asarray(nlev, dtype=np.int32), codes=codes.astype(np.uint8), values=values)
+    names, columns, nlev = load_mixed("clgaussian_test")
+    data = ra.RefData(columns, nlev, names)
+    rng = np.random.default_rng(20261112)
+    p, n = len(names), len(columns[0])
+    recs = []
+    for t in range(60):
+        k = int(rng.integers(0, 6))
+        idx = rng.choice(p, size=1 + k, replace=False)
+        node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+        par = {names[node]: [names[i] for i in pa]}
+        for score, kw in (("loglik-cg", {}), ("aic-cg", {"k": 1.0}), ("bic-cg", {"k": np.log(n) / 2})):
+            v = ra.per_node_score(data, par, [names[node]], score, **kw)[0]
+            recs.append({"score": score, "arg": list(kw.values())[0] if kw else 0.0, "node": node,
+                         "parents": pa, "value": float(v)})
+        rb.reset()
+        data.invalidate()
+    with open(os.path.join(HERE, "ref_cg.json"), "w") as f:
+        json.dump({"clgaussian_test": {"scores": recs}}, f)
+    print("wrote ref_cg.json")
+
+
 def bge_outputs():
     """BGe scores on gaussian.test with the front end's default hyper-parameters
     (iss.mu = 1, iss.w = ncol + 2, nu = column means) and with arbitrary ones."""
@@ -441,5 +488,6 @@ if __name__ == "__main__":
     incomplete_outputs()
     jt_shrinkage_outputs()
     nml_outputs()
+    cg_outputs()
     bge_outputs()
     mi_matrix_outputs()

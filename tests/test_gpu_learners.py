@@ -218,6 +218,35 @@ def test_native_hc_matches_the_stepwise_loop(engine, ds, score, arg, maxp):
     d.release()
 
 
+def test_hc_on_mixed_data_native_and_stepwise(engine):
+    """hc with bic-cg on clgaussian.test: bnl_hc and the stepwise loop agree, no
+    numeric node ends up as a parent of a factor (such arcs score -Inf), and the
+    node scores are reproduced by the oracle."""
+    from bnlearn_b200 import callsites as cs, learners
+    from oracle import oracle as orc
+    from util import load_mixed
+    names, cols, nlev = load_mixed("clgaussian_test")
+    n, p = len(cols[0]), len(cols)
+    d = engine.register(cols, nlev)
+    k = np.log(n) / 2
+    be = learners.GpuBackend(d)
+    a1, s1 = learners.hc(be, p, "bic-cg", k)
+    counter = cs.TestCounter()
+    a2, s2, _ = d.hc("bic-cg", k, counter=counter)
+    assert np.array_equal(a1, a2) and counter.value == be.counter.value
+    assert np.allclose(s1, s2, rtol=1e-12, atol=0)
+    assert a2.sum() >= 5
+    for i in range(p):
+        for j in range(p):
+            if a2[i, j]:
+                assert not (nlev[i] == 0 and nlev[j] > 0)
+    for j in range(p):
+        pa = [int(i) for i in np.flatnonzero(a2[:, j])]
+        v = orc.score_cg("bic-cg", cols[j], nlev[j], [cols[i] for i in pa], [nlev[i] for i in pa], k)[0]
+        assert abs(v - s2[j]) <= 1e-9 * abs(v)
+    d.release()
+
+
 def test_device_resample_equals_host_resample(engine):
     """bnl_data_resample (row gather on the device) gives the tables and the search
     result of registering the host-resampled data frame, with and without NA."""

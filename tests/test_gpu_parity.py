@@ -199,6 +199,38 @@ def test_gaussian_scores_against_reference_golden(engine, golden, ds):
     d.release()
 
 
+def test_conditional_gaussian_scores_against_reference_golden(engine):
+    """loglik-cg / aic-cg / bic-cg on the bundled mixed data set: discrete, Gaussian,
+    conditional-Gaussian and impossible (-Inf) nodes in one batch."""
+    from util import load_mixed
+    with open(os.path.join(GOLDEN, "ref_cg.json")) as f:
+        recs = json.load(f)["clgaussian_test"]["scores"]
+    names, cols, nlev = load_mixed("clgaussian_test")
+    d = engine.register(cols, nlev)
+    for score, arg in sorted({(r["score"], r["arg"]) for r in recs}):
+        rs = [r for r in recs if r["score"] == score and r["arg"] == arg]
+        sc, _ = d.score_cg(score, [r["node"] for r in rs], [r["parents"] for r in rs], arg)
+        for i, r in enumerate(rs):
+            _check(sc[i], r["value"], ("score", r))
+    # a configuration with too few rows makes the node singular; missing values are refused
+    from oracle import oracle as orc
+    n = 40
+    rng = np.random.default_rng(3)
+    f = np.array([1] * 37 + [2, 2, 3], dtype=np.int32)
+    g1, g2 = rng.normal(size=n), rng.normal(size=n)
+    small = engine.register([f, g1, g2], [3, 0, 0])
+    sc, npar = small.score_cg("loglik-cg", [1, 1], [[0], [0, 2]])
+    assert sc[0] == -np.inf and sc[1] == -np.inf and npar[0] == 6 and npar[1] == 9
+    assert orc.score_cg("loglik-cg", g1, 0, [f], [3])[0] == -np.inf
+    small.release()
+    g1[5] = np.nan
+    bad = engine.register([f, g1, g2], [3, 0, 0])
+    with pytest.raises(Exception):
+        bad.score_cg("loglik-cg", [1], [[0]])
+    bad.release()
+    d.release()
+
+
 def test_bge_against_reference_golden(engine):
     with open(os.path.join(GOLDEN, "ref_bge.json")) as f:
         recs = json.load(f)["gaussian_test"]

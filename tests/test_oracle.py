@@ -61,6 +61,17 @@ def test_gaussian_scores_match_reference(golden, ds):
         assert rel_close(v, rec["value"], RTOL), (rec, v)
 
 
+def test_conditional_gaussian_scores_match_reference():
+    from util import load_mixed
+    with open(os.path.join(GOLDEN, "ref_cg.json")) as f:
+        recs = json.load(f)["clgaussian_test"]["scores"]
+    names, cols, nlev = load_mixed("clgaussian_test")
+    for r in recs:
+        v, _ = orc.score_cg(r["score"], cols[r["node"]], nlev[r["node"]], [cols[i] for i in r["parents"]],
+                            [nlev[i] for i in r["parents"]], r["arg"])
+        assert rel_close(v, r["value"], RTOL), (r, v)
+
+
 def test_bge_matches_reference():
     with open(os.path.join(GOLDEN, "ref_bge.json")) as f:
         recs = json.load(f)["gaussian_test"]

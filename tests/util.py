@@ -21,6 +21,22 @@ def load_gaussian(name):
     return [str(s) for s in z["names"]], [np.ascontiguousarray(c) for c in z["values"]]
 
 
+def load_mixed(name):
+    """-> (names, columns, nlevels) of a data set with factors (int32 1-based codes)
+    and numeric columns (float64); nlevels is 0 for the numeric ones."""
+    z = np.load(os.path.join(GOLDEN, "data_%s.npz" % name))
+    nlev = [int(v) for v in z["nlevels"]]
+    cols, fi, gi = [], 0, 0
+    for l in nlev:
+        if l > 0:
+            cols.append(np.ascontiguousarray(z["codes"][fi].astype(np.int32) + 1))
+            fi += 1
+        else:
+            cols.append(np.ascontiguousarray(z["values"][gi]))
+            gi += 1
+    return [str(s) for s in z["names"]], cols, nlev
+
+
 def rel_close(a, b, rtol=1e-9, atol=0.0):
     a, b = float(a), float(b)
     if a == b:
