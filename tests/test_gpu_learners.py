@@ -234,7 +234,9 @@ def test_hc_on_mixed_data_native_and_stepwise(engine):
     counter = cs.TestCounter()
     a2, s2, _ = d.hc("bic-cg", k, counter=counter)
     assert np.array_equal(a1, a2) and counter.value == be.counter.value
-    assert np.allclose(s1, s2, rtol=1e-12, atol=0)
+    # the per-configuration moments are accumulated with double atomics: the last
+    # bits of a score depend on the order of arrival
+    assert np.allclose(s1, s2, rtol=1e-9, atol=0)
     assert a2.sum() >= 5
     for i in range(p):
         for j in range(p):
