@@ -48,6 +48,8 @@ SIGNATURES = {
     "bnl_stat_from_tables": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int64, C.c_int, c_int_p,
                                        c_int_p, c_int_p, c_int_p, c_int_p, C.POINTER(C.c_int64), c_dbl_p,
                                        c_dbl_p, c_dbl_p]),
+    "bnl_ci_cg": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, c_int_p, c_int_p, c_int_p, c_int_p, c_dbl_p, c_dbl_p,
+                            c_dbl_p]),
     "bnl_score_cg": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p, c_int_p, c_int_p,
                                c_dbl_p, c_dbl_p]),
     "bnl_tabu": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p, c_int_p, c_int_p,

@@ -35,6 +35,8 @@ int run_tests(bnl_ctx *ctx, bnl_data data, int test_e, const std::vector<int> &x
   if (is_gaussian_test(test_e))
     return bnl_ci_gaussian(ctx, data, test_e, n, x.data(), y.data(), zoff.data(), zi, st.data(),
                            df.data(), pv.data());
+  if (test_e == BNL_MI_CG)
+    return bnl_ci_cg(ctx, data, n, x.data(), y.data(), zoff.data(), zi, st.data(), df.data(), pv.data());
   return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
 }
 
@@ -427,5 +429,155 @@ int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_o
   for (auto &c : copies)
     cache[(size_t)c.first + (size_t)c.second * n] = cache[(size_t)c.second + (size_t)c.first * n];
   if (test_counter) *test_counter += m;                 // score.delta.c:278
+  return BNL_OK;
+}
+
+// ---------------------------------------------------------------------------
+// mi-cg: the conditional Gaussian mutual information test on mixed data
+// (ut_micg_complete, src/tests/patterns/utest.c:195-273; c_micg_chisq and
+// ct_micg_complete, src/tests/patterns/ctest.c:232-334; c_micg / c_cmicg /
+// c_cmicg_unroll, src/tests/conditional.gaussian/cg.mutual.information.c). Every
+// case is a difference of conditional Gaussian log-likelihoods L(node | numeric
+// regressors, discrete configuration) -- the units of bnl_score_cg -- plus, when x
+// and y are both factors, the discrete mutual information. All the
+// log-likelihoods of a call are evaluated in one batch, then combined here.
+
+namespace {
+
+struct CgTerms {
+  std::vector<int> target, off, idx;       // score units (CSR parents)
+  CgTerms() : off(1, 0) {}
+  int add(int t, const std::vector<int> &numeric, const std::vector<int> &discrete) {
+    target.push_back(t);
+    idx.insert(idx.end(), numeric.begin(), numeric.end());
+    idx.insert(idx.end(), discrete.begin(), discrete.end());
+    off.push_back((int)idx.size());
+    return (int)target.size() - 1;
+  }
+};
+
+}  // namespace
+
+extern "C" int bnl_ci_cg(bnl_ctx *ctx, bnl_data data, int n, const int *x, const int *y, const int *z_off,
+                         const int *z_idx, double *stat, double *df, double *pvalue) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  if (n < 0 || (n > 0 && (!x || !y || !z_off || !stat)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_cg: bad arguments");
+  const double N = (double)ds.nobs;
+
+  // plan: what each test needs
+  struct Plan {
+    int kind;                 // 0 discrete MI, 1 Gaussian (both numeric, no z), 2 difference of two terms, 3 unroll
+    int mi = -1;              // index into the discrete-MI batch
+    int num = -1, den = -1;   // kind 2: score-unit indices
+    std::vector<int> a, b, c, d;   // kind 3: per numeric z: lognum_i, logden_i (numerator), lognum'_i, logden'_i
+    double df = 0.0;
+  };
+  std::vector<Plan> plan(n);
+  CgTerms T;
+  std::vector<int> mx, my, moff(1, 0), midx;        // discrete MI units (statistic = G^2)
+  std::vector<int> gx, gy;                          // plain Gaussian mi-g units
+  std::vector<int> gwho;
+  for (int u = 0; u < n; u++) {
+    const int xu = x[u], yu = y[u];
+    if (xu < 0 || xu >= ds.ncols || yu < 0 || yu >= ds.ncols)
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_cg: test %d refers to a column out of range", u);
+    std::vector<int> zd, zc;
+    long long llz = 0;
+    for (int j = z_off[u]; j < z_off[u + 1]; j++) {
+      const int c = z_idx[j];
+      if (c < 0 || c >= ds.ncols) return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_cg: test %d refers to a column out of range", u);
+      if (ds.is_numeric[c]) zc.push_back(c);
+      else { zd.push_back(c); llz = (llz == 0 ? 1 : llz) * ds.nlevels[c]; }
+    }
+    const bool xd = !ds.is_numeric[xu], yd = !ds.is_numeric[yu];
+    Plan &P = plan[u];
+    const bool marginal = z_off[u + 1] == z_off[u];
+    if (xd && yd) {
+      P.mi = (int)mx.size();
+      mx.push_back(xu); my.push_back(yu);
+      midx.insert(midx.end(), zd.begin(), zd.end());
+      moff.push_back((int)midx.size());
+      if (zc.empty()) { P.kind = 0; continue; }
+      // c_cmicg_unroll: chain rule over the numeric conditioning variables.
+      P.kind = 3;
+      std::vector<int> ydz(1, yu);
+      ydz.insert(ydz.end(), zd.begin(), zd.end());
+      for (size_t i = 0; i < zc.size(); i++) {
+        std::vector<int> rest(zc.begin() + i + 1, zc.end());
+        P.a.push_back(T.add(zc[i], rest, std::vector<int>(1, xu)));   // numerator: alternative, configurations of x
+        P.b.push_back(T.add(zc[i], rest, zd));                        // numerator: null, configurations of Zd
+        P.c.push_back(P.a.back());                                    // denominator: alternative (the same model)
+        P.d.push_back(T.add(zc[i], rest, ydz));                       // denominator: null, configurations of (y, Zd)
+      }
+      const double ngp = (double)zc.size();
+      // llz stays 0 in ct_micg_complete when there is no discrete conditioning variable.
+      P.df = (double)llz * (ngp * (ngp + 3.0) / 2.0) * (double)(ds.nlevels[yu] - 1);
+    } else if (!xd && !yd) {
+      if (marginal) { P.kind = 1; gwho.push_back(u); gx.push_back(xu); gy.push_back(yu); continue; }
+      P.kind = 2;
+      std::vector<int> full(1, xu);
+      full.insert(full.end(), zc.begin(), zc.end());
+      P.den = T.add(yu, zc, zd);
+      P.num = T.add(yu, full, zd);
+      P.df = llz == 0 ? 1.0 : (double)llz;
+    } else {
+      // one factor, one numeric column: the numeric one is the response, the
+      // factor joins the discrete configuration under the alternative.
+      const int resp = xd ? yu : xu, fac = xd ? xu : yu;
+      std::vector<int> alt(1, fac);
+      alt.insert(alt.end(), zd.begin(), zd.end());
+      P.kind = 2;
+      P.den = T.add(resp, zc, zd);
+      P.num = T.add(resp, zc, alt);
+      P.df = marginal ? 2.0 * (double)(ds.nlevels[fac] - 1)
+                      : (double)(ds.nlevels[fac] - 1) * (llz == 0 ? 1.0 : (double)llz) * (double)(zc.size() + 2);
+    }
+  }
+  int rc;
+  std::vector<double> L(T.target.size()), mst(mx.size()), mdf(mx.size()), mpv(mx.size());
+  std::vector<double> gst(gx.size()), gdf(gx.size()), gpv(gx.size());
+  if (!T.target.empty() &&
+      (rc = bnl_score_cg(ctx, data, BNL_LOGLIK_CG, 0.0, (int)T.target.size(), T.target.data(), T.off.data(),
+                         T.idx.empty() ? nullptr : T.idx.data(), L.data(), nullptr))) return rc;
+  if (!mx.empty() &&
+      (rc = bnl_ci_discrete(ctx, data, BNL_MI, (int)mx.size(), mx.data(), my.data(), moff.data(),
+                            midx.empty() ? nullptr : midx.data(), mst.data(), mdf.data(), mpv.data()))) return rc;
+  if (!gx.empty()) {
+    std::vector<int> zo(gx.size() + 1, 0);
+    if ((rc = bnl_ci_gaussian(ctx, data, BNL_MI_G, (int)gx.size(), gx.data(), gy.data(), zo.data(), nullptr,
+                              gst.data(), gdf.data(), gpv.data()))) return rc;
+  }
+  size_t gi = 0;
+  for (int u = 0; u < n; u++) {
+    const Plan &P = plan[u];
+    double s, d;
+    if (P.kind == 0) { s = mst[P.mi]; d = mdf[P.mi]; }
+    else if (P.kind == 1) { s = gst[gi]; d = gdf[gi]; gi++; }
+    else if (P.kind == 2) {
+      const double num = L[P.num], den = L[P.den];
+      // a singular null model makes the alternative even more singular: independence.
+      s = (isfinite(num) && isfinite(den)) ? 2.0 * N * ((num - den) / N) : 0.0;
+      d = P.df;
+    } else {
+      // c_cmicg_unroll: every chain-rule term is (alternative - null) / n, or 0 when
+      // either model is singular; the remainder term is the discrete MI per row.
+      double lognum = mst[P.mi] / (2.0 * N), logden = 0.0;
+      for (size_t i = 0; i < P.a.size(); i++) {
+        const double a = L[P.a[i]], b = L[P.b[i]], c = L[P.c[i]], dd = L[P.d[i]];
+        lognum += (isfinite(a) && isfinite(b)) ? (a - b) / N : 0.0;
+        logden += (isfinite(c) && isfinite(dd)) ? (c - dd) / N : 0.0;
+      }
+      const double r = (isfinite(lognum) && isfinite(logden)) ? (lognum - logden) / N : 0.0;
+      s = 2.0 * N * N * r;
+      d = mdf[P.mi] + P.df;
+    }
+    stat[u] = s;
+    if (df) df[u] = d;
+    if (pvalue) pvalue[u] = bnl::pchisq_upper(s, d);
+  }
   return BNL_OK;
 }

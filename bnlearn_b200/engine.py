@@ -11,7 +11,7 @@ import numpy as np
 
 from . import _lib
 
-TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-g-sh": 41}
+TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-cg": 30, "mi-g-sh": 41}
 SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103, "bge": 105, "nal-g": 106, "pnal-g": 107,
           "loglik-cg": 200, "aic-cg": 202, "bic-cg": 203}
@@ -290,6 +290,18 @@ class DataSet:
         iu = np.triu_indices(p, 1)
         m[iu] = tri[:len(iu[0])]
         return m + m.T
+
+    def ci_cg(self, x, y, z):
+        """mi-cg tests on mixed data -> (statistic, df, p.value) arrays (bnl_ci_cg)."""
+        e = self.engine
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        zo, zi = _as_csr(z)
+        n = len(x)
+        st, df, pv = (np.zeros(max(n, 1)) for _ in range(3))
+        e._check(e._lib.bnl_ci_cg(e._ctx, self.handle, n, _ip(x), _ip(y), _ip(zo), _ip(zi), _dp(st), _dp(df),
+                                  _dp(pv)))
+        return st[:n], df[:n], pv[:n]
 
     def score_cg(self, score, target, parents, k=0.0):
         """Conditional Gaussian node scores on mixed data (bnl_score_cg)."""

@@ -48,7 +48,7 @@ enum {
 };
 
 /* test_e values handled (src/tests/tests.h:8-36). */
-enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4, BNL_JT = 10, BNL_MI_SH = 40,
+enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4, BNL_JT = 10, BNL_MI_CG = 30, BNL_MI_SH = 40,
        BNL_COR = 20, BNL_ZF = 21, BNL_MI_G = 22, BNL_MI_G_SH = 41 };
 /* score_e values handled (src/scores/scores.h:9-60). */
 enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
@@ -197,6 +197,17 @@ int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n
  * parents + 2). Complete data only; at most 7 numeric and 8 discrete parents. */
 int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n, const int *target,
                  const int *pa_off, const int *pa_idx, double *score, double *nparams);
+
+/* The conditional Gaussian mutual information test mi-cg on mixed data
+ * (ut_micg_complete, src/tests/patterns/utest.c:195-273; c_micg_chisq /
+ * ct_micg_complete, src/tests/patterns/ctest.c:232-334): x[u], y[u] and the
+ * conditioning columns may be factors or numeric. Two factors with discrete
+ * conditioning reduce to mi, two numeric columns without conditioning to mi-g;
+ * every other case is 2 (L1 - L0) for two conditional Gaussian log-likelihoods
+ * (or the chain rule of c_cmicg_unroll when two factors are tested given numeric
+ * columns), with the reference's degrees of freedom. Complete data only. */
+int bnl_ci_cg(bnl_ctx *ctx, bnl_data data, int n, const int *x, const int *y, const int *z_off,
+              const int *z_idx, double *stat, double *df, double *pvalue);
 
 /* Copy the p x p covariance matrix (divisor nobs - 1, column-major, p = number
  * of numeric columns in registration order) and the column means to the host.

@@ -17,7 +17,7 @@ NA_INT = np.iinfo(np.int32).min
 c_int_p = C.POINTER(C.c_int)
 c_dbl_p = C.POINTER(C.c_double)
 
-TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-g-sh": 41}
+TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-cg": 30, "mi-g-sh": 41}
 SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103, "nal-g": 106, "pnal-g": 107}
 
@@ -185,6 +185,48 @@ def score_cg(score, x, xlev, pcols, plev, k=0.0):
     if base != "loglik":
         v -= k * npar.value
     return v, npar.value
+
+
+def ci_cg(x, xlev, y, ylev, zcols=(), zlev=()):
+    """mi-cg on mixed data (src/tests/patterns/utest.c:195-273, ctest.c:232-334 over
+    src/tests/conditional.gaussian/cg.mutual.information.c): (statistic, df, p.value).
+    Levels are 0 for numeric columns."""
+    n = len(x)
+    zd = [i for i, l in enumerate(zlev) if l > 0]
+    zc = [i for i, l in enumerate(zlev) if l == 0]
+    llz = int(np.prod([zlev[i] for i in zd])) if zd else 0
+    dcols, dlev = [zcols[i] for i in zd], [zlev[i] for i in zd]
+    ccols = [zcols[i] for i in zc]
+
+    def L(node, regs, dc, dl):
+        return score_cg("loglik-cg", node, 0, list(regs) + list(dc), [0] * len(regs) + list(dl))[0]
+
+    def diff(num, den):
+        return (num - den) / n if (np.isfinite(num) and np.isfinite(den)) else 0.0
+
+    if xlev > 0 and ylev > 0:
+        st, df, _ = ci_discrete("mi", x, xlev, y, ylev, dcols, dlev)
+        if zc:
+            lognum, logden = st / (2.0 * n), 0.0
+            for i in range(len(ccols)):
+                rest = ccols[i + 1:]
+                alt = L(ccols[i], rest, [x], [xlev])
+                lognum += diff(alt, L(ccols[i], rest, dcols, dlev))
+                logden += diff(alt, L(ccols[i], rest, [y] + dcols, [ylev] + dlev))
+            r = (lognum - logden) / n if (np.isfinite(lognum) and np.isfinite(logden)) else 0.0
+            st = 2.0 * n * n * r
+            df = df + llz * (len(zc) * (len(zc) + 3) / 2.0) * (ylev - 1)
+    elif xlev == 0 and ylev == 0:
+        if not len(zcols):
+            st, df, _, _ = ci_gaussian("mi-g", [x, y])
+        else:
+            st = 2.0 * n * diff(L(y, [x] + ccols, dcols, dlev), L(y, ccols, dcols, dlev))
+            df = 1.0 if llz == 0 else float(llz)
+    else:
+        resp, fac, flev = (y, x, xlev) if xlev > 0 else (x, y, ylev)
+        st = 2.0 * n * diff(L(resp, ccols, [fac] + dcols, [flev] + dlev), L(resp, ccols, dcols, dlev))
+        df = 2.0 * (flev - 1) if not len(zcols) else (flev - 1) * (1 if llz == 0 else llz) * (len(zc) + 2.0)
+    return st, df, lib().Rf_pchisq(st, df, 0, 0)
 
 
 def robust_difference(old, new):

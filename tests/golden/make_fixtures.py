@@ -399,8 +399,18 @@ def cg_outputs():
                          "parents": pa, "value": float(v)})
         rb.reset()
         data.invalidate()
+    tests = []
+    for t in range(120):
+        k = int(rng.integers(0, 5))
+        idx = rng.choice(p, size=2 + k, replace=False)
+        x, y, s = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+        st, df, pv = ra.ci_test(data, names[x], names[y], [names[i] for i in s], "mi-cg")
+        tests.append({"test": "mi-cg", "x": x, "y": y, "z": s, "stat": st, "df": df, "p": pv})
+        if t % 10 == 9:
+            rb.reset()
+            data.invalidate()
     with open(os.path.join(HERE, "ref_cg.json"), "w") as f:
-        json.dump({"clgaussian_test": {"scores": recs}}, f)
+        json.dump({"clgaussian_test": {"scores": recs, "tests": tests}}, f)
     print("wrote ref_cg.json")
 
 

@@ -124,3 +124,19 @@ def test_gaussian_allsubs_and_roundrobin_run(engine):
     out = cs.roundrobin_test(d, 0, [1, 2, 3, 4], [], "zf", 0.05, counter)
     assert counter.value == 4 and len(out) == 4
     d.release()
+
+
+def test_indep_test_with_mi_cg(engine):
+    """mi-cg through the indep_test call site: p-values of the batched entry point,
+    counter advanced by one per test."""
+    from bnlearn_b200 import callsites as cs
+    from util import load_mixed
+    names, cols, nlev = load_mixed("clgaussian_test")
+    d = engine.register(cols, nlev)
+    counter = cs.TestCounter()
+    pv = cs.indep_test(d, [0, 3, 4], 6, [1, 7], "mi-cg", counter)
+    _, _, ref = d.ci_cg([0, 3, 4], [6, 6, 6], [[1, 7]] * 3)
+    assert counter.value == 3 and np.array_equal(pv, ref)
+    st, df, p = cs.ci_test(d, 3, 0, [], "mi-cg", counter)
+    assert counter.value == 4 and df == 2.0 and 0.0 <= p <= 1.0 and st > 0
+    d.release()

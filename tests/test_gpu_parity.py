@@ -231,6 +231,22 @@ def test_conditional_gaussian_scores_against_reference_golden(engine):
     d.release()
 
 
+def test_conditional_gaussian_tests_against_reference_golden(engine):
+    """mi-cg on the bundled mixed data: all 16 combinations of factor / numeric x, y
+    and conditioning sets, in one batched call."""
+    from util import load_mixed
+    with open(os.path.join(GOLDEN, "ref_cg.json")) as f:
+        recs = json.load(f)["clgaussian_test"]["tests"]
+    names, cols, nlev = load_mixed("clgaussian_test")
+    d = engine.register(cols, nlev)
+    st, df, pv = d.ci_cg([r["x"] for r in recs], [r["y"] for r in recs], [r["z"] for r in recs])
+    for i, r in enumerate(recs):
+        assert df[i] == r["df"], r
+        _check(st[i], r["stat"], ("stat", r), atol=1e-9)
+        _check(pv[i], r["p"], ("p", r), rtol=1e-8, atol=1e-300)
+    d.release()
+
+
 def test_bge_against_reference_golden(engine):
     with open(os.path.join(GOLDEN, "ref_bge.json")) as f:
         recs = json.load(f)["gaussian_test"]

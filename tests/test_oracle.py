@@ -72,6 +72,19 @@ def test_conditional_gaussian_scores_match_reference():
         assert rel_close(v, r["value"], RTOL), (r, v)
 
 
+def test_conditional_gaussian_tests_match_reference():
+    from util import load_mixed
+    with open(os.path.join(GOLDEN, "ref_cg.json")) as f:
+        recs = json.load(f)["clgaussian_test"]["tests"]
+    names, cols, nlev = load_mixed("clgaussian_test")
+    for r in recs:
+        st, df, p = orc.ci_cg(cols[r["x"]], nlev[r["x"]], cols[r["y"]], nlev[r["y"]],
+                              [cols[i] for i in r["z"]], [nlev[i] for i in r["z"]])
+        assert df == r["df"], r
+        assert rel_close(st, r["stat"], RTOL, 1e-9), (r, st)
+        assert rel_close(p, r["p"], 1e-8, 1e-300), (r, p)
+
+
 def test_bge_matches_reference():
     with open(os.path.join(GOLDEN, "ref_bge.json")) as f:
         recs = json.load(f)["gaussian_test"]
