@@ -883,141 +883,3 @@ __global__ void cg_score_kernel(const BnlCgUnit *__restrict__ units, int n, cons
   out[(size_t)u * 4 + 2] = 0.0;
   out[(size_t)u * 4 + 3] = 0.0;
 }
-
-// The same two passes without floating-point atomics, for units whose moment block
-// fits shared memory (shared-memory fp64 atomicAdd is a compare-and-swap loop on
-// this part, and the rows of a warp collide on a handful of configurations). A
-// CTA walks its row chunk in tiles of BNL_CG_TILE rows: configuration index per
-// row, counting sort of the tile's rows by configuration (integer atomics only),
-// then every configuration's run of rows is summed by ONE warp -- lanes stride
-// over the run, shuffle-reduce, lane 0 adds to the CTA's block -- so no two
-// warps ever touch the same accumulator.
-#define BNL_CG_TILE 2048
-
-template <int PASS>
-__global__ void __launch_bounds__(BNL_CG_THREADS)
-cg_moments_sorted_kernel(const double *__restrict__ f64, size_t fstride, const uint8_t *__restrict__ u8,
-                         size_t ustride, long long nobs, long long chunk_rows,
-                         const BnlCgUnit *__restrict__ units, double *__restrict__ mom,
-                         int *__restrict__ err) {
-  extern __shared__ double cgsm[];                    // [nconfig * M] accumulators, then the int scratch
-  __shared__ unsigned short s_sid[BNL_CG_TILE], s_perm[BNL_CG_TILE];
-  const BnlCgUnit U = units[blockIdx.y];
-  const int K = U.K, M = 1 + K + K * (K + 1) / 2, nconfig = U.nconfig;
-  const int total = nconfig * M;
-  int *s_start = reinterpret_cast<int *>(cgsm + total);      // nconfig + 1 run starts
-  int *s_fill = s_start + nconfig + 1;                       // nconfig scatter cursors
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = threadIdx.x; i < total; i += BNL_CG_THREADS) cgsm[i] = 0.0;
-  const double *gm = mom + U.off;                            // finalised means (pass 2)
-  const long long r0 = blockIdx.x * chunk_rows, r1 = min(nobs, r0 + chunk_rows);
-  for (long long t0 = r0; t0 < r1; t0 += BNL_CG_TILE) {
-    const int rows = (int)min((long long)BNL_CG_TILE, r1 - t0);
-    for (int i = threadIdx.x; i <= nconfig; i += BNL_CG_THREADS) s_start[i] = 0;
-    __syncthreads();
-    // 1. configuration of every row of the tile, histogram
-    for (int r = threadIdx.x; r < rows; r += BNL_CG_THREADS) {
-      int s = 0;
-      bool bad = false;
-      for (int j = 0; j < U.nd; j++) {
-        const unsigned b = u8[ustride * U.dslot[j] + t0 + r];
-        bad |= b >= 0x80u;
-        s += (int)b * U.dmul[j];
-      }
-      if (bad) { *err = 1; s_sid[r] = 0xFFFFu; continue; }
-      s_sid[r] = (unsigned short)s;
-      atomicAdd(&s_start[s + 1], 1);
-    }
-    __syncthreads();
-    // 2. run starts (inclusive scan by one warp, 32 configurations at a time)
-    if (warp == 0) {
-      int carry = 0;
-      for (int b = 0; b < nconfig; b += 32) {
-        const int i = b + lane;
-        int v = i < nconfig ? s_start[i + 1] : 0;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int n = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += n; }
-        if (i < nconfig) s_start[i + 1] = carry + v;
-        carry += __shfl_sync(0xffffffffu, v, 31);
-      }
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < nconfig; i += BNL_CG_THREADS) s_fill[i] = s_start[i];
-    __syncthreads();
-    // 3. scatter the rows into their runs
-    for (int r = threadIdx.x; r < rows; r += BNL_CG_THREADS) {
-      const unsigned s = s_sid[r];
-      if (s != 0xFFFFu) s_perm[atomicAdd(&s_fill[s], 1)] = (unsigned short)r;
-    }
-    __syncthreads();
-    // 4. one warp per configuration
-    for (int s = warp; s < nconfig; s += BNL_CG_THREADS / 32) {
-      const int a = s_start[s], b = s_start[s + 1];
-      if (a == b) continue;
-      double acc[PASS == 1 ? BNL_CG_MAXG + 1 : BNL_CG_MAXG * (BNL_CG_MAXG + 1) / 2];
-      constexpr int NA = PASS == 1 ? BNL_CG_MAXG + 1 : BNL_CG_MAXG * (BNL_CG_MAXG + 1) / 2;
-#pragma unroll
-      for (int i = 0; i < NA; i++) acc[i] = 0.0;
-      double m[BNL_CG_MAXG];
-      bool nan_seen = false;
-      if (PASS == 2) {
-#pragma unroll
-        for (int i = 0; i < BNL_CG_MAXG; i++) m[i] = i < K ? gm[(size_t)s * M + 1 + i] : 0.0;
-      }
-      for (int q = a + lane; q < b; q += 32) {
-        const long long r = t0 + s_perm[q];
-        double v[BNL_CG_MAXG];
-#pragma unroll
-        for (int i = 0; i < BNL_CG_MAXG; i++)
-          if (i < K) { v[i] = __ldg(f64 + fstride * U.gslot[i] + r); nan_seen |= isnan(v[i]); }
-        if (PASS == 1) {
-          acc[0] += 1.0;
-#pragma unroll
-          for (int i = 0; i < BNL_CG_MAXG; i++) if (i < K) acc[1 + i] += v[i];
-        } else {
-#pragma unroll
-          for (int i = 0; i < BNL_CG_MAXG; i++) if (i < K) v[i] -= m[i];
-          // accumulators at compile-time slots of the MAXG-wide triangle (registers)
-#pragma unroll
-          for (int i = 0; i < BNL_CG_MAXG; i++)
-#pragma unroll
-            for (int j = i; j < BNL_CG_MAXG; j++)
-              if (j < K) acc[i * BNL_CG_MAXG - i * (i - 1) / 2 + (j - i)] += v[i] * v[j];
-        }
-      }
-      if (nan_seen) *err = 1;
-      double *dst = cgsm + (size_t)s * M + (PASS == 1 ? 0 : 1 + K);
-      if (PASS == 1) {
-#pragma unroll
-        for (int i = 0; i < BNL_CG_MAXG + 1; i++) {
-          if (i < 1 + K) {
-            double t = acc[i];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-            if (lane == 0) dst[i] += t;
-          }
-        }
-      } else {
-        int p = 0;                          // position in the unit's own K-wide triangle
-#pragma unroll
-        for (int i = 0; i < BNL_CG_MAXG; i++)
-#pragma unroll
-          for (int j = i; j < BNL_CG_MAXG; j++)
-            if (j < K) {
-              double t = acc[i * BNL_CG_MAXG - i * (i - 1) / 2 + (j - i)];
-#pragma unroll
-              for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-              if (lane == 0) dst[p] += t;
-              p++;
-            }
-      }
-    }
-    __syncthreads();
-  }
-  double *g = mom + U.off;
-  for (int i = threadIdx.x; i < total; i += BNL_CG_THREADS) {
-    const int w = i % M;
-    const bool mine = PASS == 1 ? w <= K : w > K;
-    if (mine && cgsm[i] != 0.0) atomicAdd(g + i, cgsm[i]);
-  }
-}
