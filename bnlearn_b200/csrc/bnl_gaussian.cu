@@ -379,12 +379,21 @@ extern "C" int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, d
 
 namespace {
 
-int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units, double *score, double *npar) {
-  const int n = (int)units.size();
+int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units_in, double *score, double *npar) {
+  const int n = (int)units_in.size();
   if (n == 0) return BNL_OK;
   BnlDevice &dev = ctx->devs[0];
   BnlDeviceData &dd = ds.dev[0];
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  // Units with a handful of configurations take the register-accumulating kernel,
+  // the others the atomic one. A launch handles one kind: the device list holds
+  // the first kind, then the second; where[u] is the position of the caller's unit.
+  auto small = [](const BnlCgUnit &u) { return u.nconfig <= BNL_CG_SMALL_CFG && u.K <= BNL_CG_SMALL_K; };
+  std::vector<BnlCgUnit> units;
+  std::vector<int> where(n);
+  for (int u = 0; u < n; u++) if (small(units_in[u])) { where[u] = (int)units.size(); units.push_back(units_in[u]); }
+  const int nsmall = (int)units.size();
+  for (int u = 0; u < n; u++) if (!small(units_in[u])) { where[u] = (int)units.size(); units.push_back(units_in[u]); }
   long long total = 0;
   for (auto &u : units) {
     u.off = total;
@@ -413,13 +422,30 @@ int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units, do
   if (e == cudaSuccess) {
     const int chunks = (int)std::max(1ll, std::min(128ll, (ds.nobs + 8191) / 8192));
     const long long chunk_rows = (ds.nobs + chunks - 1) / chunks;
-    const dim3 g((unsigned)chunks, (unsigned)n);
     const size_t smem = BNL_CG_SMEM_DOUBLES * sizeof(double);
-    cg_moments_kernel<1><<<g, BNL_CG_THREADS, smem, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8, ds.stride_u8,
-                                                                 ds.nobs, chunk_rows, d_units, mom, d_err);
+    auto pass = [&](int which) {
+      if (nsmall > 0) {
+        const dim3 gs((unsigned)chunks, (unsigned)nsmall);
+        if (which == 1)
+          cg_moments_small_kernel<1><<<gs, BNL_CG_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8,
+              ds.stride_u8, ds.nobs, chunk_rows, d_units, mom, d_err);
+        else
+          cg_moments_small_kernel<2><<<gs, BNL_CG_THREADS, 0, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8,
+              ds.stride_u8, ds.nobs, chunk_rows, d_units, mom, d_err);
+      }
+      if (n - nsmall > 0) {
+        const dim3 ga((unsigned)chunks, (unsigned)(n - nsmall));
+        if (which == 1)
+          cg_moments_kernel<1><<<ga, BNL_CG_THREADS, smem, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8, ds.stride_u8,
+              ds.nobs, chunk_rows, d_units + nsmall, mom, d_err);
+        else
+          cg_moments_kernel<2><<<ga, BNL_CG_THREADS, smem, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8, ds.stride_u8,
+              ds.nobs, chunk_rows, d_units + nsmall, mom, d_err);
+      }
+    };
+    pass(1);
     cg_means_kernel<<<dim3(8, (unsigned)n), 128, 0, dev.stream>>>(d_units, n, mom);
-    cg_moments_kernel<2><<<g, BNL_CG_THREADS, smem, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8, ds.stride_u8,
-                                                                 ds.nobs, chunk_rows, d_units, mom, d_err);
+    pass(2);
     cg_score_kernel<<<(n + 63) / 64, 64, 0, dev.stream>>>(d_units, n, mom, d_out);
     e = cudaGetLastError();
   }
@@ -436,7 +462,10 @@ int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units, do
   if (err)
     return bnl_fail(ctx, BNL_EUNSUPPORTED,
                     "conditional Gaussian scores need complete data (a missing value was met)");
-  for (int u = 0; u < n; u++) { score[u] = out[4 * (size_t)u]; npar[u] = out[4 * (size_t)u + 1]; }
+  for (int u = 0; u < n; u++) {
+    score[u] = out[4 * (size_t)where[u]];
+    npar[u] = out[4 * (size_t)where[u] + 1];
+  }
   return BNL_OK;
 }
 

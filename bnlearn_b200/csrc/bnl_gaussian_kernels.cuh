@@ -883,3 +883,104 @@ __global__ void cg_score_kernel(const BnlCgUnit *__restrict__ units, int n, cons
   out[(size_t)u * 4 + 2] = 0.0;
   out[(size_t)u * 4 + 3] = 0.0;
 }
+
+// Units with at most BNL_CG_SMALL_CFG configurations and BNL_CG_SMALL_K numeric
+// columns (a numeric node with one small discrete parent -- most candidates of an
+// hc iteration on mixed data): the rows of a warp would collide on 2-4 addresses
+// in the atomic kernel, so here every thread keeps the accumulators of ALL the
+// configurations in registers and adds each row to its own configuration through
+// a predicate. One block reduction per CTA at the end, no atomics in the row loop.
+#define BNL_CG_SMALL_CFG 4
+#define BNL_CG_SMALL_K 4
+
+template <int PASS>
+__global__ void __launch_bounds__(BNL_CG_THREADS)
+cg_moments_small_kernel(const double *__restrict__ f64, size_t fstride, const uint8_t *__restrict__ u8,
+                        size_t ustride, long long nobs, long long chunk_rows,
+                        const BnlCgUnit *__restrict__ units, double *__restrict__ mom,
+                        int *__restrict__ err) {
+  constexpr int KS = BNL_CG_SMALL_K, NC = BNL_CG_SMALL_CFG;
+  constexpr int NA = PASS == 1 ? 1 + KS : KS * (KS + 1) / 2;
+  __shared__ double s_red[BNL_CG_THREADS / 32];
+  __shared__ double s_mean[NC * KS];
+  const BnlCgUnit U = units[blockIdx.y];
+  const int K = U.K, M = 1 + K + K * (K + 1) / 2, nconfig = U.nconfig;
+  if (PASS == 2) {
+    if (threadIdx.x < NC * KS) {
+      const int c = threadIdx.x / KS, i = threadIdx.x % KS;
+      s_mean[threadIdx.x] = (c < nconfig && i < K) ? mom[U.off + (size_t)c * M + 1 + i] : 0.0;
+    }
+    __syncthreads();
+  }
+  double acc[NC][NA];
+#pragma unroll
+  for (int c = 0; c < NC; c++)
+#pragma unroll
+    for (int a = 0; a < NA; a++) acc[c][a] = 0.0;
+  bool bad_any = false;
+  const long long r0 = blockIdx.x * chunk_rows, r1 = min(nobs, r0 + chunk_rows);
+  for (long long r = r0 + threadIdx.x; r < r1; r += BNL_CG_THREADS) {
+    int s = 0;
+    bool bad = false;
+    for (int j = 0; j < U.nd; j++) {
+      const unsigned b = u8[ustride * U.dslot[j] + r];
+      bad |= b >= 0x80u;
+      s += (int)b * U.dmul[j];
+    }
+    double v[KS];
+#pragma unroll
+    for (int i = 0; i < KS; i++) {
+      v[i] = 0.0;
+      if (i < K) { v[i] = f64[fstride * U.gslot[i] + r]; bad |= isnan(v[i]); }
+    }
+    if (bad) { bad_any = true; continue; }
+    if (PASS == 2) {
+#pragma unroll
+      for (int i = 0; i < KS; i++) v[i] -= s_mean[s * KS + i];     // columns beyond K stay 0
+    }
+#pragma unroll
+    for (int c = 0; c < NC; c++) {
+      const double w = s == c ? 1.0 : 0.0;
+      if (PASS == 1) {
+        acc[c][0] += w;
+#pragma unroll
+        for (int i = 0; i < KS; i++) acc[c][1 + i] += w * v[i];
+      } else {
+        int p = 0;
+#pragma unroll
+        for (int i = 0; i < KS; i++)
+#pragma unroll
+          for (int j = i; j < KS; j++, p++) acc[c][p] += w * (v[i] * v[j]);
+      }
+    }
+  }
+  if (bad_any) *err = 1;
+  // block reduction of every accumulator; thread 0 adds the CTA's share to the unit's block.
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int c = 0; c < NC; c++) {
+#pragma unroll
+    for (int a = 0; a < NA; a++) {
+      double t = acc[c][a];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+      __syncthreads();
+      if (lane == 0) s_red[warp] = t;
+      __syncthreads();
+      if (threadIdx.x == 0 && c < nconfig) {
+        double tot = 0.0;
+        for (int w = 0; w < BNL_CG_THREADS / 32; w++) tot += s_red[w];
+        // slot of accumulator `a` in the unit's own layout (K columns, not KS)
+        int dst = -1;
+        if (PASS == 1) { if (a <= K) dst = a; }
+        else {
+          int i = 0, rem = a;
+          while (rem >= KS - i) { rem -= KS - i; i++; }
+          const int j = i + rem;
+          if (j < K) dst = 1 + K + (i * K - i * (i - 1) / 2 + (j - i));
+        }
+        if (dst >= 0 && tot != 0.0) atomicAdd(mom + U.off + (size_t)c * M + dst, tot);
+      }
+    }
+  }
+}

@@ -28,7 +28,8 @@ with Engine() as eng:
     tg, pa = [], []
     for u in range(400):
         node = nf + int(rng.integers(0, ng))
-        dp = [int(i) for i in rng.choice(nf, size=int(rng.integers(1, 4)), replace=False)]
+        ndp = int(os.environ.get("NDP", 0)) or int(rng.integers(1, 4))
+        dp = [int(i) for i in rng.choice(nf, size=ndp, replace=False)]
         gp = [nf + int(i) for i in rng.choice([g for g in range(ng) if nf + g != node], size=int(rng.integers(0, 4)), replace=False)]
         tg.append(node); pa.append(gp + dp)
     d.score_cg("loglik-cg", tg, pa)
