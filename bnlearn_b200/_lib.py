@@ -44,6 +44,10 @@ SIGNATURES = {
                                    c_int_p, c_int_p, c_dbl_p]),
     "bnl_roundrobin_test": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, c_int_p, C.c_int,
                                       c_int_p, C.c_double, c_dbl_p, c_dbl_p]),
+    "bnl_data_alloc": (C.c_int, [C.c_void_p, C.c_int, c_int_p, c_int_p, C.c_int64, C.POINTER(C.c_uint64)]),
+    "bnl_data_device_view": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p),
+                                       C.POINTER(C.c_size_t), C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "bnl_data_commit": (C.c_int, [C.c_void_p, C.c_uint64]),
     "bnl_data_resample": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int64, c_int_p, C.POINTER(C.c_uint64)]),
     "bnl_stat_from_tables": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int64, C.c_int, c_int_p,
                                        c_int_p, c_int_p, c_int_p, c_int_p, C.POINTER(C.c_int64), c_dbl_p,

@@ -93,6 +93,26 @@ gather_f64_kernel(const double *__restrict__ src, size_t src_stride, long long s
   }
 }
 
+// bnl_data_commit: the packed columns were written by somebody else (a broadcast
+// from another GPU): find out which columns hold an NA (0xFF within the rows) and
+// refuse codes that are neither NA nor below the column's number of levels.
+__global__ void __launch_bounds__(256)
+scan_packed_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
+                   const int *__restrict__ nlev_by_slot, int *__restrict__ flags) {
+  const int c = blockIdx.y;
+  const uint8_t *col = u8 + stride * c;
+  const unsigned lv = (unsigned)nlev_by_slot[c];
+  int na = 0, bad = 0;
+  for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < nobs;
+       r += (long long)gridDim.x * blockDim.x) {
+    const unsigned b = col[r];
+    na |= b == BNL_NA_U8;
+    bad |= b != BNL_NA_U8 && b >= lv;
+  }
+  if (bad) flags[0] = 1;
+  if (na) flags[1 + c] = 1;
+}
+
 // ---------------------------------------------------------------------------
 
 extern "C" int bnl_init(bnl_ctx **out, const int *devices, int ndev) {
@@ -612,6 +632,99 @@ extern "C" int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, c
   cudaSetDevice(ctx->devs[0].id);
   *handle = ctx->next_handle++;
   ctx->data[*handle] = ds;
+  return BNL_OK;
+}
+
+extern "C" int bnl_data_alloc(bnl_ctx *ctx, int ncols, const int *is_numeric, const int *nlevels,
+                              int64_t nobs, bnl_data *handle) {
+  if (!ctx || ctx->devs.empty()) return BNL_EINVAL;
+  if (ncols <= 0 || !is_numeric || !nlevels || !handle || nobs < 0 || nobs >= (int64_t)INT32_MAX)
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_alloc: bad arguments");
+  BnlDataSet ds;
+  ds.ncols = ncols;
+  ds.nobs = nobs;
+  ds.is_numeric.assign(is_numeric, is_numeric + ncols);
+  ds.nlevels.assign(nlevels, nlevels + ncols);
+  ds.slot.resize(ncols);
+  for (int i = 0; i < ncols; i++) {
+    if (is_numeric[i]) ds.slot[i] = ds.nc++;
+    else {
+      if (nlevels[i] < 1 || nlevels[i] > BNL_MAX_LEVELS)
+        return bnl_fail(ctx, BNL_EUNSUPPORTED, "column %d: 1..%d levels per factor", i, BNL_MAX_LEVELS);
+      ds.slot[i] = ds.nd++;
+    }
+  }
+  ds.stride_u8 = round_up((size_t)nobs + 1, BNL_COL_ALIGN);
+  ds.stride_f64 = round_up((size_t)nobs + 1, 32);
+  ds.dev.resize(ctx->devs.size());
+  ds.slot_has_na.assign(ds.nd, 1);             // unknown until bnl_data_commit
+  ds.committed = false;
+  for (size_t d = 0; d < ctx->devs.size(); d++) {
+    BnlDevice &dev = ctx->devs[d];
+    BnlDeviceData &dd = ds.dev[d];
+    int rc;
+    if (cudaSetDevice(dev.id) != cudaSuccess) { free_dataset(ctx, ds); return bnl_fail(ctx, BNL_ECUDA, "cudaSetDevice failed"); }
+    if (ds.nd > 0) {
+      dd.u8_bytes = ds.stride_u8 * ds.nd;
+      if ((rc = bnl_pool_alloc(ctx, dev, (void **)&dd.u8, dd.u8_bytes))) { free_dataset(ctx, ds); return rc; }
+    }
+    if (ds.nc > 0) {
+      dd.f64_bytes = ds.stride_f64 * ds.nc * sizeof(double);
+      if ((rc = bnl_pool_alloc(ctx, dev, (void **)&dd.f64, dd.f64_bytes))) { free_dataset(ctx, ds); return rc; }
+    }
+  }
+  cudaSetDevice(ctx->devs[0].id);
+  *handle = ctx->next_handle++;
+  ctx->data[*handle] = ds;
+  return BNL_OK;
+}
+
+extern "C" int bnl_data_device_view(bnl_ctx *ctx, bnl_data data, int dev_index, void **u8, size_t *u8_bytes,
+                                    void **f64, size_t *f64_bytes) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  if (dev_index < 0 || dev_index >= (int)it->second.dev.size())
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_device_view: device index out of range");
+  const BnlDeviceData &dd = it->second.dev[dev_index];
+  if (u8) *u8 = dd.u8;
+  if (u8_bytes) *u8_bytes = dd.u8_bytes;
+  if (f64) *f64 = dd.f64;
+  if (f64_bytes) *f64_bytes = dd.f64_bytes;
+  return BNL_OK;
+}
+
+extern "C" int bnl_data_commit(bnl_ctx *ctx, bnl_data data) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  int rc;
+  if (ds.nd > 0) {
+    std::vector<int> lv(ds.nd, 0), flags(1 + ds.nd, 0);
+    for (int c = 0; c < ds.ncols; c++) if (!ds.is_numeric[c]) lv[ds.slot[c]] = ds.nlevels[c];
+    BnlDevice &dev = ctx->devs[0];
+    BNL_CUDA(ctx, cudaSetDevice(dev.id));
+    if ((rc = bnl_reserve_device(ctx, &dev.d_flags, &dev.flags_cap, (size_t)(2 + 2 * ds.nd)))) return rc;
+    int *d_lv = dev.d_flags + 1 + ds.nd;
+    BNL_CUDA(ctx, cudaMemsetAsync(dev.d_flags, 0, (size_t)(1 + ds.nd) * sizeof(int), dev.stream));
+    BNL_CUDA(ctx, cudaMemcpyAsync(d_lv, lv.data(), (size_t)ds.nd * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+    int gx = (int)std::min<long long>((ds.nobs + 255) / 256, (long long)dev.sm_count * 8);
+    if (gx < 1) gx = 1;
+    scan_packed_kernel<<<dim3(gx, ds.nd), 256, 0, dev.stream>>>(ds.dev[0].u8, ds.stride_u8, ds.nobs, d_lv,
+                                                                dev.d_flags);
+    BNL_CUDA(ctx, cudaGetLastError());
+    BNL_CUDA(ctx, cudaMemcpyAsync(flags.data(), dev.d_flags, flags.size() * sizeof(int), cudaMemcpyDeviceToHost,
+                                  dev.stream));
+    BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+    if (flags[0]) return bnl_fail(ctx, BNL_EINVAL, "a packed factor column holds a code outside 0..nlevels-1");
+    ds.slot_has_na.assign(flags.begin() + 1, flags.end());
+  }
+  if (ds.nc > 0)
+    for (size_t d = 0; d < ctx->devs.size(); d++)
+      if ((rc = bnl_gaussian_prepare(ctx, ds, (int)d)) != BNL_OK) return rc;
+  ds.committed = true;
+  cudaSetDevice(ctx->devs[0].id);
   return BNL_OK;
 }
 

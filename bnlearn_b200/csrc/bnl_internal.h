@@ -83,6 +83,7 @@ struct BnlDataSet {
   std::vector<BnlDeviceData> dev;       // one per context device
   std::vector<double> h_mean, h_cov;    // host copies of the Gaussian moments
   bool any_nan = false;                 // some numeric column holds a missing value
+  bool committed = true;                // false between bnl_data_alloc and bnl_data_commit
   double bge_mu = 1.0, bge_w = -1.0;    // BGe imaginary sample sizes (bge_w < 0: ncols + 2)
 };
 

@@ -118,6 +118,15 @@ class Engine:
                                                 C.byref(handle)))
         return DataSet(self, handle.value, nobs, nlevels)
 
+    def alloc(self, nlevels, nobs):
+        """A data set of the given shape whose packed columns the caller fills on the
+        device (bnl_data_alloc); see DataSet.device_view / commit."""
+        lv = np.array([int(v) for v in nlevels], dtype=np.int32)
+        isnum = np.array([0 if v > 0 else 1 for v in lv], dtype=np.int32)
+        handle = C.c_uint64()
+        self._check(self._lib.bnl_data_alloc(self._ctx, len(lv), _ip(isnum), _ip(lv), int(nobs), C.byref(handle)))
+        return DataSet(self, handle.value, int(nobs), [int(v) for v in lv])
+
     def flush(self):
         self._check(self._lib.bnl_data_flush(self._ctx))
 
@@ -160,6 +169,20 @@ class DataSet:
         h = C.c_uint64(0)
         e._check(e._lib.bnl_data_resample(e._ctx, self.handle, len(r), _ip(r), C.byref(h)))
         return DataSet(e, h.value, len(r), self.nlevels)
+
+    def device_view(self, dev_index=0):
+        """(u8 pointer, bytes, f64 pointer, bytes) of the packed blocks on one device."""
+        e = self.engine
+        u8, f64 = C.c_void_p(), C.c_void_p()
+        nu, nf = C.c_size_t(), C.c_size_t()
+        e._check(e._lib.bnl_data_device_view(e._ctx, self.handle, int(dev_index), C.byref(u8), C.byref(nu),
+                                             C.byref(f64), C.byref(nf)))
+        return u8.value or 0, nu.value, f64.value or 0, nf.value
+
+    def commit(self):
+        """Finish a data set made by Engine.alloc once its blocks are filled (bnl_data_commit)."""
+        e = self.engine
+        e._check(e._lib.bnl_data_commit(e._ctx, self.handle))
 
     def release(self):
         if self.handle:

@@ -105,6 +105,24 @@ int bnl_set_bge_prior(bnl_ctx *ctx, bnl_data data, double iss_mu, double iss_w, 
  * the upload of a whole data frame per replicate. Only the row list crosses PCIe. */
 int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, const int *rows,
                       bnl_data *handle);
+/* A data set whose packed columns are filled on the device by the caller instead
+ * of being uploaded: the way to replicate one data frame over the GPUs of a job
+ * with one process per GPU ("NCCL broadcast from GPU 0") --
+ * rank 0 registers the host data frame, every other rank allocates the same
+ * shape, the packed block travels over NVLink (ncclBroadcast on the pointers
+ * bnl_data_device_view returns, factor block and numeric block), and
+ * bnl_data_commit finds the NA flags, checks the codes and forms the Gaussian
+ * moments. Layout: factor column s (registration order among the factors) at
+ * u8 + s * stride, stride = u8_bytes / #factors, codes 0-based, NA and padding
+ * 0xFF; numeric column likewise in the f64 block. No counterpart in the
+ * reference (its cluster workers each receive the data frame from R). Requests
+ * on a data set that was allocated but not committed treat every factor as
+ * possibly holding NA. */
+int bnl_data_alloc(bnl_ctx *ctx, int ncols, const int *is_numeric, const int *nlevels, int64_t nobs,
+                   bnl_data *handle);
+int bnl_data_device_view(bnl_ctx *ctx, bnl_data data, int dev_index, void **u8, size_t *u8_bytes,
+                         void **f64, size_t *f64_bytes);
+int bnl_data_commit(bnl_ctx *ctx, bnl_data data);
 int bnl_data_release(bnl_ctx *ctx, bnl_data handle);
 /* Drop every registered data set; meant to be called from reset_test_counter()
  * (src/test.counter.c:26), which every learner calls first. */

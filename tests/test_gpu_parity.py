@@ -536,3 +536,51 @@ def test_row_sharded_tables_give_the_unsharded_statistics(engine):
             assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]), score
         for d in shards + [whole]:
             d.release()
+
+
+def test_alloc_fill_commit_equals_register(engine):
+    """bnl_data_alloc / device_view / commit: a data set whose packed blocks are
+    copied in on the device (what an NCCL broadcast does between ranks) answers like
+    the registered original, NA flags included; a bad code is refused at commit."""
+    import torch
+    from bnlearn_b200.replicate import _as_tensor
+    from util import load_mixed
+    names, cols, lev = load_discrete("learning_test_na")
+    src = engine.register(cols, lev)
+    dst = engine.alloc(lev, len(cols[0]))
+    su, nu, _, _ = src.device_view()
+    du, nu2, _, _ = dst.device_view()
+    assert nu == nu2 and nu > 0
+    _as_tensor(du, nu).copy_(_as_tensor(su, nu))
+    torch.cuda.synchronize()
+    dst.commit()
+    x, y, z = [0, 1, 2], [3, 4, 5], [[], [0], [1, 3]]
+    for a, b in zip(src.ci_discrete("mi", x, y, z), dst.ci_discrete("mi", x, y, z)):
+        assert np.array_equal(a, b)
+    for ta, tb in zip(src.counts(x, y, z), dst.counts(x, y, z)):
+        assert np.array_equal(ta, tb)
+    bad = engine.alloc(lev, len(cols[0]))
+    bu, nb, _, _ = bad.device_view()
+    t = _as_tensor(bu, nb)
+    t.copy_(_as_tensor(su, nu))
+    t[5] = 100
+    torch.cuda.synchronize()
+    with pytest.raises(Exception):
+        bad.commit()
+    for d in (src, dst, bad):
+        d.release()
+    # mixed data: both blocks, Gaussian moments formed at commit
+    names, cols, lev = load_mixed("clgaussian_test")
+    src = engine.register(cols, lev)
+    dst = engine.alloc(lev, len(cols[0]))
+    su, nu, sf, nf = src.device_view()
+    du, _, dfp, _ = dst.device_view()
+    _as_tensor(du, nu).copy_(_as_tensor(su, nu))
+    _as_tensor(dfp, nf).copy_(_as_tensor(sf, nf))
+    torch.cuda.synchronize()
+    dst.commit()
+    a = src.score_cg("bic-cg", [3, 6, 0], [[0, 7], [0, 3, 4], [1]], 4.0)[0]
+    b = dst.score_cg("bic-cg", [3, 6, 0], [[0, 7], [0, 3, 4], [1]], 4.0)[0]
+    assert np.allclose(a, b, rtol=1e-12, atol=0)
+    src.release()
+    dst.release()
