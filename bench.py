@@ -326,11 +326,13 @@ def main():
     sys.stdout.flush()
     _REAL_STDOUT = os.dup(1)
     os.dup2(2, 1)
-    # ranks share the host cores: give each its share of the packing threads
-    # (bnl_data_register would otherwise start one per core in every rank).
+    # In the timed end-to-end steps only rank 0 uploads (the others receive the
+    # packed columns by NCCL broadcast), so it gets every core for packing; the
+    # other ranks upload once, untimed, and take a share.
     if "BNL_PACK_THREADS" not in os.environ:
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
-        os.environ["BNL_PACK_THREADS"] = str(max(1, (os.cpu_count() or 8) // max(1, local_world)))
+        ncores = os.cpu_count() or 8
+        os.environ["BNL_PACK_THREADS"] = str(ncores if rank == 0 else max(1, ncores // max(1, local_world)))
 
     if args.impl == "reference" and rank != 0:
         return 0
