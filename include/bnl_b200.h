@@ -29,6 +29,7 @@
 #ifndef BNL_B200_H
 #define BNL_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus

@@ -15,7 +15,7 @@ static unsigned next(void) { s = s * 6364136223846793005ULL + 144269504088896340
 int main(int argc, char **argv) {
   long nobs = argc > 1 ? atol(argv[1]) : 1000;
   s = argc > 2 ? strtoull(argv[2], NULL, 10) : 1;
-  int nlev[4] = {3, 2, 4, 3}, isnum[5] = {0, 0, 0, 0, 1};
+  int isnum[5] = {0, 0, 0, 0, 1};
   int *col[4];
   double *g = malloc(sizeof(double) * nobs);
   for (int c = 0; c < 4; c++) col[c] = malloc(sizeof(int) * nobs);
