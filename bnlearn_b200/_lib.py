@@ -59,6 +59,7 @@ SIGNATURES = {
     "bnl_tabu": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p, c_int_p, c_int_p,
                            C.c_double, C.c_longlong, C.c_int, C.c_int, c_int_p, c_dbl_p,
                            C.POINTER(C.c_longlong), c_dbl_p]),
+    "bnl_set_ebic_gamma": (C.c_int, [C.c_void_p, C.c_uint64, C.c_double]),
     "bnl_set_bge_prior": (C.c_int, [C.c_void_p, C.c_uint64, C.c_double, C.c_double, c_dbl_p]),
     "bnl_hc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p, c_int_p, c_int_p,
                          C.c_double, C.c_longlong, c_int_p, c_dbl_p, C.POINTER(C.c_longlong), c_dbl_p]),

@@ -552,6 +552,15 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
   if (!ctx) return BNL_EINVAL;
   BnlDataSet *ds = find_data(ctx, data);
   if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  if (score_e == BNL_EBIC) {
+    // extended BIC (src/scores/per.node.score.c:116-134): BIC minus
+    // 4 gamma #parents log(ncol(data)); gamma comes from bnl_set_ebic_gamma.
+    int rc = bnl_score_discrete(ctx, data, BNL_BIC, k_or_iss, n, target, pa_off, pa_idx, score, nparams);
+    if (rc) return rc;
+    const double pen = 4.0 * ds->ebic_gamma * log((double)ds->ncols);
+    for (int u = 0; u < n; u++) score[u] -= pen * (double)(pa_off[u + 1] - pa_off[u]);
+    return BNL_OK;
+  }
   if (score_e != BNL_LOGLIK && score_e != BNL_AIC && score_e != BNL_BIC && score_e != BNL_BDE &&
       score_e != BNL_BDS && score_e != BNL_BDJ && score_e != BNL_K2 && score_e != BNL_NAL &&
       score_e != BNL_PNAL && score_e != BNL_FNML && score_e != BNL_QNML)

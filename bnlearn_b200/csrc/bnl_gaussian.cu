@@ -310,6 +310,13 @@ extern "C" int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, doub
   auto it = ctx->data.find(data);
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   BnlDataSet &ds = it->second;
+  if (score_e == BNL_EBIC_G) {            // per.node.score.c:155-173
+    int rc = bnl_score_gaussian(ctx, data, BNL_BIC_G, k, n, target, pa_off, pa_idx, score, nparams);
+    if (rc) return rc;
+    const double pen = 4.0 * ds.ebic_gamma * log((double)ds.ncols);
+    for (int u = 0; u < n; u++) score[u] -= pen * (double)(pa_off[u + 1] - pa_off[u]);
+    return BNL_OK;
+  }
   if (score_e != BNL_LOGLIK_G && score_e != BNL_AIC_G && score_e != BNL_BIC_G && score_e != BNL_NAL_G &&
       score_e != BNL_PNAL_G && score_e != BNL_BGE)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a Gaussian score handled here", score_e);
@@ -357,6 +364,15 @@ extern "C" int bnl_set_bge_prior(bnl_ctx *ctx, bnl_data data, double iss_mu, dou
     BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
   }
   cudaSetDevice(ctx->devs[0].id);
+  return BNL_OK;
+}
+
+extern "C" int bnl_set_ebic_gamma(bnl_ctx *ctx, bnl_data data, double gamma) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  if (!(gamma >= 0.0 && gamma <= 1.0)) return bnl_fail(ctx, BNL_EINVAL, "gamma must lie in [0, 1]");
+  it->second.ebic_gamma = gamma;
   return BNL_OK;
 }
 
@@ -477,6 +493,13 @@ extern "C" int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, 
   auto it = ctx->data.find(data);
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   BnlDataSet &ds = it->second;
+  if (score_e == BNL_EBIC_CG) {           // per.node.score.c:194-212
+    int rc = bnl_score_cg(ctx, data, BNL_BIC_CG, k, n, target, pa_off, pa_idx, score, nparams);
+    if (rc) return rc;
+    const double pen = 4.0 * ds.ebic_gamma * log((double)ds.ncols);
+    for (int u = 0; u < n; u++) score[u] -= pen * (double)(pa_off[u + 1] - pa_off[u]);
+    return BNL_OK;
+  }
   if (score_e != BNL_LOGLIK_CG && score_e != BNL_AIC_CG && score_e != BNL_BIC_CG)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a conditional Gaussian score handled here", score_e);
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))

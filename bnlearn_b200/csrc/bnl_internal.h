@@ -85,6 +85,7 @@ struct BnlDataSet {
   bool any_nan = false;                 // some numeric column holds a missing value
   bool committed = true;                // false between bnl_data_alloc and bnl_data_commit
   double bge_mu = 1.0, bge_w = -1.0;    // BGe imaginary sample sizes (bge_w < 0: ncols + 2)
+  double ebic_gamma = 0.5;              // extended BIC (the front end's default)
 };
 
 struct bnl_ctx {

@@ -240,7 +240,8 @@ extern "C" int bnl_hc(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
   // complete data; qnml is, fnml, bds, bdj, k2 are not.
   bool equivalence = score_e == BNL_LOGLIK || score_e == BNL_AIC || score_e == BNL_BIC ||
                      score_e == BNL_BDE || score_e == BNL_LOGLIK_G || score_e == BNL_AIC_G ||
-                     score_e == BNL_BIC_G || score_e == BNL_BGE || score_e == BNL_QNML;
+                     score_e == BNL_BIC_G || score_e == BNL_BGE || score_e == BNL_QNML || score_e == BNL_EBIC ||
+                     score_e == BNL_EBIC_G;
   if (score_e == BNL_NAL || score_e == BNL_PNAL) {
     auto it = ctx->data.find(data);
     if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
@@ -324,7 +325,8 @@ extern "C" int bnl_tabu(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_is
   S.enable_tabu(tabu);
   bool equivalence = score_e == BNL_LOGLIK || score_e == BNL_AIC || score_e == BNL_BIC ||
                      score_e == BNL_BDE || score_e == BNL_LOGLIK_G || score_e == BNL_AIC_G ||
-                     score_e == BNL_BIC_G || score_e == BNL_BGE || score_e == BNL_QNML;
+                     score_e == BNL_BIC_G || score_e == BNL_BGE || score_e == BNL_QNML || score_e == BNL_EBIC ||
+                     score_e == BNL_EBIC_G;
   if (score_e == BNL_NAL || score_e == BNL_PNAL) {
     auto it = ctx->data.find(data);
     if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");

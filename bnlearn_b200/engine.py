@@ -12,13 +12,13 @@ import numpy as np
 from . import _lib
 
 TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-cg": 30, "mi-g-sh": 41}
-SCORES = {"loglik": 1, "aic": 3, "bic": 4, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
-          "loglik-g": 100, "aic-g": 102, "bic-g": 103, "bge": 105, "nal-g": 106, "pnal-g": 107,
-          "loglik-cg": 200, "aic-cg": 202, "bic-cg": 203}
+SCORES = {"loglik": 1, "aic": 3, "bic": 4, "ebic": 5, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
+          "loglik-g": 100, "aic-g": 102, "bic-g": 103, "ebic-g": 104, "bge": 105, "nal-g": 106, "pnal-g": 107,
+          "loglik-cg": 200, "aic-cg": 202, "bic-cg": 203, "ebic-cg": 204}
 DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf", "jt", "mi-sh")
 GAUSSIAN_TESTS = ("cor", "zf", "mi-g", "mi-g-sh")
-DISCRETE_SCORES = ("loglik", "aic", "bic", "bde", "bds", "bdj", "k2", "fnml", "qnml", "nal", "pnal")
-GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g", "bge", "nal-g", "pnal-g")
+DISCRETE_SCORES = ("loglik", "aic", "bic", "ebic", "bde", "bds", "bdj", "k2", "fnml", "qnml", "nal", "pnal")
+GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g", "ebic-g", "bge", "nal-g", "pnal-g")
 NA_INT = np.iinfo(np.int32).min
 
 
@@ -336,6 +336,10 @@ class DataSet:
         e._check(e._lib.bnl_score_cg(e._ctx, self.handle, SCORES[score], float(k), n, _ip(t), _ip(po), _ip(pi),
                                      _dp(sc), _dp(npar)))
         return sc[:n], npar[:n]
+
+    def set_ebic_gamma(self, gamma):
+        e = self.engine
+        e._check(e._lib.bnl_set_ebic_gamma(e._ctx, self.handle, float(gamma)))
 
     def set_bge_prior(self, iss_mu=1.0, iss_w=0.0, nu=None):
         """BGe hyper-parameters (iss_w <= 0: ncol + 2; nu None: the column means)."""

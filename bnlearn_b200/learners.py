@@ -22,7 +22,7 @@ import numpy as np
 from . import callsites as cs
 
 TOL = math.sqrt(np.finfo(np.float64).eps)
-SCORE_EQUIVALENT = ("loglik", "aic", "bic", "bde", "qnml", "loglik-g", "aic-g", "bic-g", "bge")
+SCORE_EQUIVALENT = ("loglik", "aic", "bic", "ebic", "bde", "qnml", "loglik-g", "aic-g", "bic-g", "ebic-g", "bge")
 
 
 class GpuBackend:

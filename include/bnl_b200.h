@@ -52,11 +52,11 @@ enum {
 enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4, BNL_JT = 10, BNL_MI_CG = 30, BNL_MI_SH = 40,
        BNL_COR = 20, BNL_ZF = 21, BNL_MI_G = 22, BNL_MI_G_SH = 41 };
 /* score_e values handled (src/scores/scores.h:9-60). */
-enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
+enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_EBIC = 5, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
        BNL_FNML = 11, BNL_QNML = 12, BNL_NAL = 13, BNL_PNAL = 14,
-       BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103, BNL_BGE = 105, BNL_NAL_G = 106,
+       BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103, BNL_EBIC_G = 104, BNL_BGE = 105, BNL_NAL_G = 106,
        BNL_PNAL_G = 107,
-       BNL_LOGLIK_CG = 200, BNL_AIC_CG = 202, BNL_BIC_CG = 203 };
+       BNL_LOGLIK_CG = 200, BNL_AIC_CG = 202, BNL_BIC_CG = 203, BNL_EBIC_CG = 204 };
 
 /* ---- context ---------------------------------------------------------- */
 
@@ -98,6 +98,12 @@ int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col,
  * registered column; entries of factor columns are ignored). Uniform graph
  * prior. The k argument of bnl_score_gaussian is ignored for BNL_BGE. */
 int bnl_set_bge_prior(bnl_ctx *ctx, bnl_data data, double iss_mu, double iss_w, const double *nu);
+
+/* gamma of the extended BIC scores (BNL_EBIC, BNL_EBIC_G, BNL_EBIC_CG:
+ * BIC - 4 gamma #parents log(ncol(data)), src/scores/per.node.score.c:116-134,
+ * 155-173, 194-212) for later calls on this data set; 0.5 until set, the front
+ * end's default. The k argument of the score calls is the BIC coefficient. */
+int bnl_set_ebic_gamma(bnl_ctx *ctx, bnl_data data, double gamma);
 
 /* A new data set made of rows[0..nrows) (0-based, repeats allowed) of a
  * registered one, gathered on the device: the bootstrap replicate

@@ -46,9 +46,11 @@ class RefData:
         self._df = None
 
 
-def _extra(score=None, k=None, iss=None, B=None, bge=None):
+def _extra(score=None, k=None, iss=None, B=None, bge=None, gamma=None):
     names, items = [], []
     L = rb.lib()
+    if gamma is not None:
+        names.append("gamma"); items.append(L.Rf_ScalarReal(float(gamma)))
     if bge is not None:                       # (iss.mu, iss.w, nu vector, node names)
         iss_mu, iss_w, nu, nodes = bge
         nu_s = rb.realvec(np.asarray(nu, dtype=np.float64))
@@ -64,7 +66,7 @@ def _extra(score=None, k=None, iss=None, B=None, bge=None):
     return rb.rlist(items, names)
 
 
-def per_node_score(data, parents, targets, score, k=None, iss=None, bge=None):
+def per_node_score(data, parents, targets, score, k=None, iss=None, bge=None, gamma=None):
     """reference per_node_score (src/scores/per.node.score.c:31-48).
     parents: {node name: [parent names, in order]}; bge = (iss.mu, iss.w, nu)."""
     L = rb.lib()
@@ -72,7 +74,7 @@ def per_node_score(data, parents, targets, score, k=None, iss=None, bge=None):
     if bge is not None:
         bge = (bge[0], bge[1], bge[2], data.names)
     res = L.per_node_score(net, data.df(), L.Rf_mkString(score.encode()),
-                           rb.strvec(list(targets)), _extra(k=k, iss=iss, bge=bge),
+                           rb.strvec(list(targets)), _extra(k=k, iss=iss, bge=bge, gamma=gamma),
                            L.Rf_ScalarLogical(0))
     return rb.to_numpy(res)
 

@@ -414,6 +414,41 @@ def cg_outputs():
     print("wrote ref_cg.json")
 
 
+def ebic_outputs():
+    """Extended BIC (ebic, ebic-g, ebic-cg) with the default gamma = 0.5 and with 0.3."""
+    from oracle import refapi as ra, refbind as rb
+    rng = np.random.default_rng(20261113)
+    out = {}
+    for ds, score, loader in (("learning_test", "ebic", "d"), ("gaussian_test", "ebic-g", "g"),
+                              ("clgaussian_test", "ebic-cg", "m")):
+        if loader == "d":
+            names, codes, nlev = load_discrete(ds)
+            data = ra.RefData(list(codes), list(nlev), names)
+        elif loader == "g":
+            names, vals = load_gaussian(ds)
+            data = ra.RefData(list(vals), None, names)
+        else:
+            names, cols, nlev = load_mixed(ds)
+            data = ra.RefData(cols, nlev, names)
+        p, n = len(names), data.nobs
+        recs = []
+        for t in range(20):
+            k = int(rng.integers(0, 4))
+            idx = rng.choice(p, size=1 + k, replace=False)
+            node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+            for gamma in (0.5, 0.3):
+                v = ra.per_node_score(data, {names[node]: [names[i] for i in pa]}, [names[node]], score,
+                                      k=np.log(n) / 2, gamma=gamma)[0]
+                recs.append({"score": score, "arg": float(np.log(n) / 2), "gamma": gamma, "node": node,
+                             "parents": pa, "value": float(v)})
+            rb.reset()
+            data.invalidate()
+        out[ds] = recs
+    with open(os.path.join(HERE, "ref_ebic.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote ref_ebic.json")
+
+
 def bge_outputs():
     """BGe scores on gaussian.test with the front end's default hyper-parameters
     (iss.mu = 1, iss.w = ncol + 2, nu = column means) and with arbitrary ones."""
@@ -499,5 +534,6 @@ if __name__ == "__main__":
     jt_shrinkage_outputs()
     nml_outputs()
     cg_outputs()
+    ebic_outputs()
     bge_outputs()
     mi_matrix_outputs()

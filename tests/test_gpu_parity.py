@@ -247,6 +247,29 @@ def test_conditional_gaussian_tests_against_reference_golden(engine):
     d.release()
 
 
+def test_ebic_against_reference_golden(engine):
+    from util import load_mixed
+    with open(os.path.join(GOLDEN, "ref_ebic.json")) as f:
+        g = json.load(f)
+    for ds, recs in g.items():
+        if ds == "learning_test":
+            names, cols, nlev = load_discrete(ds)
+        elif ds == "gaussian_test":
+            names, cols = load_gaussian(ds)
+            nlev = None
+        else:
+            names, cols, nlev = load_mixed(ds)
+        d = engine.register(cols, nlev)
+        for gamma in (0.5, 0.3):
+            rs = [r for r in recs if r["gamma"] == gamma]
+            if gamma != 0.5:
+                d.set_ebic_gamma(gamma)                  # 0.5 is the default
+            sc, _ = d.score(rs[0]["score"], [r["node"] for r in rs], [r["parents"] for r in rs], rs[0]["arg"])
+            for i, r in enumerate(rs):
+                _check(sc[i], r["value"], ("ebic", ds, r))
+        d.release()
+
+
 def test_bge_against_reference_golden(engine):
     with open(os.path.join(GOLDEN, "ref_bge.json")) as f:
         recs = json.load(f)["gaussian_test"]

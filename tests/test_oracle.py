@@ -85,6 +85,27 @@ def test_conditional_gaussian_tests_match_reference():
         assert rel_close(p, r["p"], 1e-8, 1e-300), (r, p)
 
 
+def test_ebic_matches_reference():
+    """ebic = bic - 4 gamma #parents log(ncol) on top of the three bic flavours."""
+    from util import load_mixed
+    with open(os.path.join(GOLDEN, "ref_ebic.json")) as f:
+        g = json.load(f)
+    for ds, recs in g.items():
+        if ds == "learning_test":
+            names, cols, nlev = load_discrete(ds)
+        elif ds == "gaussian_test":
+            names, cols = load_gaussian(ds)
+            nlev = [0] * len(cols)
+        else:
+            names, cols, nlev = load_mixed(ds)
+        for r in recs:
+            node, pa = r["node"], r["parents"]
+            v = orc.score_cg("bic-cg", cols[node], nlev[node], [cols[i] for i in pa], [nlev[i] for i in pa],
+                             r["arg"])[0]
+            v -= 4.0 * r["gamma"] * len(pa) * np.log(len(cols))
+            assert rel_close(v, r["value"], RTOL), (ds, r, v)
+
+
 def test_bge_matches_reference():
     with open(os.path.join(GOLDEN, "ref_bge.json")) as f:
         recs = json.load(f)["gaussian_test"]
