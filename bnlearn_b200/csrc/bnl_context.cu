@@ -56,6 +56,21 @@ pack_factors_kernel(const int *__restrict__ src, uint8_t *__restrict__ dst, long
   }
 }
 
+// Factors with 128..32767 levels: int32 codes -> uint16 (code - 1, NA -> 0xFFFF).
+__global__ void __launch_bounds__(256)
+pack_factors16_kernel(const int *__restrict__ src, uint16_t *__restrict__ dst, long long nobs, int nlevels,
+                      int *__restrict__ bad, int *__restrict__ has_na) {
+  for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < nobs;
+       r += (long long)gridDim.x * blockDim.x) {
+    const int v = src[r];
+    unsigned b;
+    if (v == INT_MIN) { b = BNL_NA_U16; *has_na = 1; }
+    else if (v < 1 || v > nlevels) { b = BNL_NA_U16; *bad = 1; }
+    else b = (unsigned)(v - 1);
+    dst[r] = (uint16_t)b;
+  }
+}
+
 // Row gather for bnl_data_resample: out[c][r] = in[c][rows[r]] for every packed
 // factor column c (blockIdx.y). Reads are random bytes, writes coalesced. A row
 // index outside the source raises flags[0]; an NA that lands in the replicate
@@ -78,6 +93,23 @@ gather_u8_kernel(const uint8_t *__restrict__ src, size_t src_stride, long long s
   }
   if (bad) flags[0] = 1;
   if (saw_na) flags[1 + c] = 1;
+}
+
+__global__ void __launch_bounds__(256)
+gather_u16_kernel(const uint16_t *__restrict__ src, size_t src_stride, long long src_nobs,
+                  uint16_t *__restrict__ dst, size_t dst_stride, const int *__restrict__ rows,
+                  long long nrows, int *__restrict__ flags, int flag_base) {
+  const int c = blockIdx.y;
+  int saw_na = 0;
+  for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < nrows;
+       r += (long long)gridDim.x * blockDim.x) {
+    const int k = rows[r];
+    if (k < 0 || k >= src_nobs) { flags[0] = 1; continue; }
+    const uint16_t v = src[src_stride * c + k];
+    saw_na |= v == BNL_NA_U16;
+    dst[dst_stride * c + r] = v;
+  }
+  if (saw_na) flags[flag_base + c] = 1;
 }
 
 __global__ void __launch_bounds__(256)
@@ -240,6 +272,7 @@ static void free_dataset(bnl_ctx *ctx, BnlDataSet &ds) {
     cudaSetDevice(ctx->devs[i].id);
     BnlDeviceData &d = ds.dev[i];
     bnl_pool_free(ctx->devs[i], d.u8, d.u8_bytes);
+    bnl_pool_free(ctx->devs[i], d.u16, d.u16_bytes);
     bnl_pool_free(ctx->devs[i], d.f64, d.f64_bytes);
     bnl_pool_free(ctx->devs[i], d.mean, d.mean_bytes);
     bnl_pool_free(ctx->devs[i], d.cov, d.cov_bytes);
@@ -424,18 +457,21 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
   ds.is_numeric.assign(is_numeric, is_numeric + ncols);
   ds.nlevels.assign(nlevels, nlevels + ncols);
   ds.slot.resize(ncols);
+  ds.is_wide.assign(ncols, 0);
   for (int i = 0; i < ncols; i++) {
     if (is_numeric[i]) ds.slot[i] = ds.nc++;
     else {
       if (nlevels[i] < 1)
         return bnl_fail(ctx, BNL_EINVAL, "column %d: a factor needs at least one level", i);
-      if (nlevels[i] > BNL_MAX_LEVELS)
-        return bnl_fail(ctx, BNL_EUNSUPPORTED, "column %d has %d levels; the uint8 layout holds at most %d",
-                        i, nlevels[i], BNL_MAX_LEVELS);
-      ds.slot[i] = ds.nd++;
+      if (nlevels[i] > BNL_MAX_LEVELS_WIDE)
+        return bnl_fail(ctx, BNL_EUNSUPPORTED, "column %d has %d levels; the uint16 layout holds at most %d",
+                        i, nlevels[i], BNL_MAX_LEVELS_WIDE);
+      if (nlevels[i] > BNL_MAX_LEVELS) { ds.is_wide[i] = 1; ds.slot[i] = ds.nw++; }
+      else ds.slot[i] = ds.nd++;
     }
   }
   ds.stride_u8 = round_up((size_t)nobs + 1, BNL_COL_ALIGN);
+  ds.stride_u16 = round_up((size_t)nobs + 1, BNL_COL_ALIGN);
   ds.stride_f64 = round_up((size_t)nobs + 1, 32);
   ds.dev.resize(ctx->devs.size());
 
@@ -461,11 +497,19 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
     dd0.u8_bytes = ds.stride_u8 * ds.nd;
     if ((rc = bnl_pool_alloc(ctx, d0, (void **)&dd0.u8, dd0.u8_bytes))) return cleanup(rc);
     REG_CUDA(cudaMemsetAsync(dd0.u8, BNL_NA_U8, ds.stride_u8 * ds.nd, d0.stream));
+  }
+  if (ds.nw > 0) {
+    dd0.u16_bytes = ds.stride_u16 * ds.nw * sizeof(uint16_t);
+    if ((rc = bnl_pool_alloc(ctx, d0, (void **)&dd0.u16, dd0.u16_bytes))) return cleanup(rc);
+    REG_CUDA(cudaMemsetAsync(dd0.u16, 0xFF, dd0.u16_bytes, d0.stream));
+  }
+  const int nflags = 1 + ds.nd + ds.nw;             // bad code | NA per uint8 slot | NA per uint16 slot
+  if (ds.nd + ds.nw > 0) {
     if ((rc = bnl_reserve_device(ctx, &d0.stage, &d0.stage_cap, 2 * ((size_t)nobs + 68)))) return cleanup(rc);
-    if ((rc = bnl_reserve_device(ctx, &d0.d_flags, &d0.flags_cap, (size_t)(1 + ds.nd)))) return cleanup(rc);
+    if ((rc = bnl_reserve_device(ctx, &d0.d_flags, &d0.flags_cap, (size_t)nflags))) return cleanup(rc);
     stage = d0.stage;
     d_bad = d0.d_flags;
-    REG_CUDA(cudaMemsetAsync(d_bad, 0, (size_t)(1 + ds.nd) * sizeof(int), d0.stream));
+    REG_CUDA(cudaMemsetAsync(d_bad, 0, (size_t)nflags * sizeof(int), d0.stream));
   }
   if (ds.nc > 0) {
     dd0.f64_bytes = ds.stride_f64 * ds.nc * sizeof(double);
@@ -480,16 +524,24 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
   const bool hybrid = ds.nd > 0 && (long long)ds.nd * nobs >= (8ll << 20) && !getenv("BNL_NO_HOST_PACK");
   if (hybrid) {
     std::vector<int> dcols(ds.nd);
-    for (int i = 0; i < ncols; i++) if (!is_numeric[i]) dcols[ds.slot[i]] = i;
+    for (int i = 0; i < ncols; i++) if (!is_numeric[i] && !ds.is_wide[i]) dcols[ds.slot[i]] = i;
     if ((rc = upload_factors_hybrid(ctx, ds, d0, dd0, col, nlevels, dcols, d_bad, host_flags)))
       return cleanup(rc);
   }
   for (int i = 0; i < ncols; i++) {
     if (nobs == 0) continue;
-    if (hybrid && !is_numeric[i]) continue;
+    if (hybrid && !is_numeric[i] && !ds.is_wide[i]) continue;
     if (is_numeric[i]) {
       REG_CUDA(cudaMemcpyAsync(dd0.f64 + ds.stride_f64 * ds.slot[i], col[i],
                                (size_t)nobs * sizeof(double), cudaMemcpyHostToDevice, d0.stream));
+    } else if (ds.is_wide[i]) {
+      REG_CUDA(cudaMemcpyAsync(stage, col[i], (size_t)nobs * sizeof(int), cudaMemcpyHostToDevice,
+                               d0.stream));
+      int grid = (int)std::min<long long>((nobs + 255) / 256, (long long)d0.sm_count * 16);
+      if (grid < 1) grid = 1;
+      pack_factors16_kernel<<<grid, 256, 0, d0.stream>>>(stage, dd0.u16 + ds.stride_u16 * ds.slot[i], nobs,
+                                                         nlevels[i], d_bad, d_bad + 1 + ds.nd + ds.slot[i]);
+      REG_CUDA(cudaGetLastError());
     } else {
       REG_CUDA(cudaMemcpyAsync(stage, col[i], (size_t)nobs * sizeof(int), cudaMemcpyHostToDevice,
                                d0.stream));
@@ -501,14 +553,15 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
       REG_CUDA(cudaGetLastError());
     }
   }
-  if (ds.nd > 0) {
-    std::vector<int> flags(1 + ds.nd, 0);
+  if (ds.nd + ds.nw > 0) {
+    std::vector<int> flags(nflags, 0);
     REG_CUDA(cudaMemcpyAsync(flags.data(), d_bad, flags.size() * sizeof(int), cudaMemcpyDeviceToHost,
                              d0.stream));
     REG_CUDA(cudaStreamSynchronize(d0.stream));
-    for (size_t i = 0; i < host_flags.size() && i < flags.size(); i++) flags[i] |= host_flags[i];
+    for (size_t i = 0; i < host_flags.size() && i < (size_t)(1 + ds.nd); i++) flags[i] |= host_flags[i];
     const int bad = flags[0];
-    ds.slot_has_na.assign(flags.begin() + 1, flags.end());
+    ds.slot_has_na.assign(flags.begin() + 1, flags.begin() + 1 + ds.nd);
+    ds.wide_has_na.assign(flags.begin() + 1 + ds.nd, flags.end());
     if (bad)
       return cleanup(bnl_fail(ctx, BNL_EINVAL, "a factor column holds a code outside 1..nlevels"));
   } else {
@@ -524,6 +577,11 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
       ddi.u8_bytes = dd0.u8_bytes;
       if ((rc = bnl_pool_alloc(ctx, di, (void **)&ddi.u8, ddi.u8_bytes))) return cleanup(rc);
       REG_CUDA(cudaMemcpyPeerAsync(ddi.u8, di.id, dd0.u8, d0.id, ds.stride_u8 * ds.nd, di.stream));
+    }
+    if (ds.nw > 0) {
+      ddi.u16_bytes = dd0.u16_bytes;
+      if ((rc = bnl_pool_alloc(ctx, di, (void **)&ddi.u16, ddi.u16_bytes))) return cleanup(rc);
+      REG_CUDA(cudaMemcpyPeerAsync(ddi.u16, di.id, dd0.u16, d0.id, dd0.u16_bytes, di.stream));
     }
     if (ds.nc > 0) {
       ddi.f64_bytes = dd0.f64_bytes;
@@ -564,14 +622,17 @@ extern "C" int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, c
     return bnl_fail(ctx, BNL_EINVAL, "bnl_data_resample: the source data set has no rows");
 
   BnlDataSet ds;
-  ds.ncols = src.ncols; ds.nd = src.nd; ds.nc = src.nc;
+  ds.ncols = src.ncols; ds.nd = src.nd; ds.nc = src.nc; ds.nw = src.nw;
+  ds.is_wide = src.is_wide;
   ds.nobs = nrows;
   ds.is_numeric = src.is_numeric; ds.nlevels = src.nlevels; ds.slot = src.slot;
   ds.bge_mu = src.bge_mu; ds.bge_w = src.bge_w;      // nu falls back to the replicate's own means
   ds.stride_u8 = round_up((size_t)nrows + 1, BNL_COL_ALIGN);
   ds.stride_f64 = round_up((size_t)nrows + 1, 32);
+  ds.stride_u16 = round_up((size_t)nrows + 1, BNL_COL_ALIGN);
   ds.dev.resize(ctx->devs.size());
   ds.slot_has_na.assign(ds.nd, 0);
+  ds.wide_has_na.assign(ds.nw, 0);
   int rc = BNL_OK;
   auto fail = [&](int code) { free_dataset(ctx, ds); return code; };
 #define RS_CUDA(call)                                                                      \
@@ -583,15 +644,15 @@ extern "C" int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, c
   } while (0)
 
   // every device gathers from its own replica; the row list goes to each of them.
-  std::vector<std::vector<int>> flags(ctx->devs.size(), std::vector<int>(1 + ds.nd, 0));
+  std::vector<std::vector<int>> flags(ctx->devs.size(), std::vector<int>(1 + ds.nd + ds.nw, 0));
   for (size_t d = 0; d < ctx->devs.size(); d++) {
     BnlDevice &dev = ctx->devs[d];
     BnlDeviceData &dd = ds.dev[d];
     const BnlDeviceData &sd = src.dev[d];
     RS_CUDA(cudaSetDevice(dev.id));
     if ((rc = bnl_reserve_device(ctx, &dev.stage, &dev.stage_cap, (size_t)nrows + 64))) return fail(rc);
-    if ((rc = bnl_reserve_device(ctx, &dev.d_flags, &dev.flags_cap, (size_t)(1 + ds.nd)))) return fail(rc);
-    RS_CUDA(cudaMemsetAsync(dev.d_flags, 0, (size_t)(1 + ds.nd) * sizeof(int), dev.stream));
+    if ((rc = bnl_reserve_device(ctx, &dev.d_flags, &dev.flags_cap, (size_t)(1 + ds.nd + ds.nw)))) return fail(rc);
+    RS_CUDA(cudaMemsetAsync(dev.d_flags, 0, (size_t)(1 + ds.nd + ds.nw) * sizeof(int), dev.stream));
     if (nrows > 0)
       RS_CUDA(cudaMemcpyAsync(dev.stage, rows, (size_t)nrows * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
     int gx = (int)std::min<long long>((nrows + 255) / 256, (long long)dev.sm_count * 8);
@@ -603,6 +664,17 @@ extern "C" int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, c
       if (nrows > 0) {
         gather_u8_kernel<<<dim3(gx, ds.nd), 256, 0, dev.stream>>>(sd.u8, src.stride_u8, src.nobs, dd.u8,
                                                                  ds.stride_u8, dev.stage, nrows, dev.d_flags);
+        RS_CUDA(cudaGetLastError());
+      }
+    }
+    if (ds.nw > 0) {
+      dd.u16_bytes = ds.stride_u16 * ds.nw * sizeof(uint16_t);
+      if ((rc = bnl_pool_alloc(ctx, dev, (void **)&dd.u16, dd.u16_bytes))) return fail(rc);
+      RS_CUDA(cudaMemsetAsync(dd.u16, 0xFF, dd.u16_bytes, dev.stream));
+      if (nrows > 0) {
+        gather_u16_kernel<<<dim3(gx, ds.nw), 256, 0, dev.stream>>>(sd.u16, src.stride_u16, src.nobs, dd.u16,
+                                                                  ds.stride_u16, dev.stage, nrows, dev.d_flags,
+                                                                  1 + ds.nd);
         RS_CUDA(cudaGetLastError());
       }
     }
@@ -626,6 +698,7 @@ extern "C" int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, c
 #undef RS_CUDA
   if (flags[0][0]) return fail(bnl_fail(ctx, BNL_EINVAL, "bnl_data_resample: a row index is outside the source data set"));
   for (int c = 0; c < ds.nd; c++) ds.slot_has_na[c] = flags[0][1 + c];
+  for (int c = 0; c < ds.nw; c++) ds.wide_has_na[c] = flags[0][1 + ds.nd + c];
   if (ds.nc > 0)
     for (size_t d = 0; d < ctx->devs.size(); d++)
       if ((rc = bnl_gaussian_prepare(ctx, ds, (int)d)) != BNL_OK) return fail(rc);
@@ -646,6 +719,7 @@ extern "C" int bnl_data_alloc(bnl_ctx *ctx, int ncols, const int *is_numeric, co
   ds.is_numeric.assign(is_numeric, is_numeric + ncols);
   ds.nlevels.assign(nlevels, nlevels + ncols);
   ds.slot.resize(ncols);
+  ds.is_wide.assign(ncols, 0);
   for (int i = 0; i < ncols; i++) {
     if (is_numeric[i]) ds.slot[i] = ds.nc++;
     else {

@@ -48,11 +48,22 @@ int make_unit(bnl_ctx *ctx, const BnlDataSet &ds, int x, int y, const int *z, in
   memset(u, 0, sizeof(*u));
   int k = 0;
   long long mul = 1;
+  // packed slot of a column, with BNL_WIDE_BIT for the uint16 block; NA flag alongside
+  auto place = [&](int c, long long m) {
+    const bool wide = ds.is_wide[c] != 0;
+    u->col[k] = ds.slot[c] | (wide ? BNL_WIDE_BIT : 0);
+    u->mul[k] = (int)m;
+    k++;
+    if (wide) { u->pad = 1; if (!ds.wide_has_na.empty() && ds.wide_has_na[ds.slot[c]]) u->has_na = 1; }
+    else if (!ds.slot_has_na.empty() && ds.slot_has_na[ds.slot[c]]) u->has_na = 1;
+  };
   u->llx = ds.nlevels[x];
   u->lly = y >= 0 ? ds.nlevels[y] : 1;
-  if (y >= 0) { u->col[k] = ds.slot[y]; u->mul[k] = 1; k++; mul = u->lly; }
-  u->col[k] = ds.slot[x]; u->mul[k] = (int)mul; k++;
+  if (y >= 0) { place(y, 1); mul = u->lly; }
+  place(x, mul);
   mul *= u->llx;
+  if (mul >= INT32_MAX)
+    return bnl_fail(ctx, BNL_EOVERFLOW, "attempting to create a factor with more than INT_MAX levels");
   long long llz = 1;
   for (int j = 0; j < nz; j++) {
     if (!check(z[j]))
@@ -62,16 +73,36 @@ int make_unit(bnl_ctx *ctx, const BnlDataSet &ds, int x, int y, const int *z, in
     // (src/core/sets.c:182-183).
     if (llz >= INT32_MAX || mul * ds.nlevels[z[j]] >= INT32_MAX)
       return bnl_fail(ctx, BNL_EOVERFLOW, "attempting to create a factor with more than INT_MAX levels");
-    u->col[k] = ds.slot[z[j]]; u->mul[k] = (int)mul; k++;
+    place(z[j], mul);
     mul *= ds.nlevels[z[j]];
   }
   u->ncols = k;
-  for (int c = 0; c < k; c++)
-    if (!ds.slot_has_na.empty() && ds.slot_has_na[u->col[c]]) u->has_na = 1;
   u->llz = (int)llz;
   u->cells = (int)mul;
   if (mul > kMaxBatchCells)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "a single table of %lld cells exceeds the engine's scratch limit", mul);
+  return BNL_OK;
+}
+
+// shared memory of the epilogue: llx + lly margins per warp (tests only). Up to
+// kEpiMaxMargins ints per warp; the opt-in above 48 KB is set once per device.
+const int kEpiMaxMargins = 10240;
+template <typename Units>
+int epilogue_stride(bnl_ctx *ctx, BnlDevice &dev, const Units &units, int n, int kind, int *stride) {
+  int need = 2 * BNL_MAX_LEVELS + 2;
+  if (kind == 0)
+    for (int i = 0; i < n; i++) need = std::max(need, units[i].llx + units[i].lly);
+  if (need > kEpiMaxMargins)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "a test on factors with %d levels in total exceeds the epilogue's limit of %d",
+                    need, kEpiMaxMargins);
+  *stride = (need + 31) & ~31;
+  if ((size_t)*stride * BNL_EPI_WARPS * sizeof(int) > 48 * 1024 && !dev.epi_attr_done) {
+    BNL_CUDA(ctx, cudaFuncSetAttribute(epilogue_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       kEpiMaxMargins * BNL_EPI_WARPS * (int)sizeof(int)));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(epilogue_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       kEpiMaxMargins * BNL_EPI_WARPS * (int)sizeof(int)));
+    dev.epi_attr_done = true;
+  }
   return BNL_OK;
 }
 
@@ -160,7 +191,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         // at least two shared columns (a node with one or more parents): for
         // two-column units the per-unit kernel with its row-pair mode is faster
         // (scripts/group_sweep.sh: 0.244 vs 0.297 ms on 999 candidates x 1 M rows).
-        if (a.ncols != b.ncols || a.ncols < kKnobGroupMinCols || a.has_na || b.has_na) return false;
+        if (a.ncols != b.ncols || a.ncols < kKnobGroupMinCols || a.has_na || b.has_na || a.pad || b.pad) return false;
         for (int k = 0; k + 1 < a.ncols; k++)
           if (a.col[k] != b.col[k] || a.mul[k] != b.mul[k]) return false;
         return a.mul[a.ncols - 1] == b.mul[b.ncols - 1];
@@ -216,7 +247,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       hu.mode = 0;
       if (grouped[i]) continue;
       const int c = hu.cells;
-      const int k = c <= 256 ? 0 : (c <= mid_cap ? 1 : (c <= lane_cap ? 2 : 3));
+      // a unit with a uint16 column is counted by the generic kernel, whatever its size
+      const int k = hu.pad ? 3 : (c <= 256 ? 0 : (c <= mid_cap ? 1 : (c <= lane_cap ? 2 : 3)));
       cls[k].push_back(i);
       cmax[k] = std::max(cmax[k], c);
     }
@@ -344,7 +376,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         ch = (int)std::max(1ll, std::min<long long>(ch, std::max(1ll, groups / 256)));
         count_units_kernel<<<(unsigned)cls[3].size() * ch, BNL_CNT_THREADS, (size_t)smem_cells * sizeof(int), dev.stream>>>(
             dd.u8, ds.stride_u8, groups, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[3].size(), ch,
-            smem_cells);
+            smem_cells, dd.u16, ds.stride_u16);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
       }
@@ -361,14 +393,17 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     } else {
       if (rq.kind == 1 && (rq.code == BNL_FNML || rq.code == BNL_QNML) && (rc = bnl_regret_table(ctx, dev)))
         return rc;
+      int mstride = 0;
+      if ((rc = epilogue_stride(ctx, dev, dev.h_units, cnt, rq.kind, &mstride))) return rc;
+      const size_t esmem = (size_t)mstride * BNL_EPI_WARPS * sizeof(int);
       if (rq.kind == 0 && (rq.code == BNL_JT || rq.code == BNL_MI_SH))
-        epilogue_kernel<true><<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
-                                                                     rq.kind, rq.code, rq.arg, ds.nobs,
-                                                                     dev.d_regret);
+        epilogue_kernel<true><<<cnt, BNL_EPI_THREADS, esmem, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
+                                                                         rq.kind, rq.code, rq.arg, ds.nobs,
+                                                                         dev.d_regret, mstride);
       else
-        epilogue_kernel<false><<<cnt, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
-                                                                      rq.kind, rq.code, rq.arg, ds.nobs,
-                                                                      dev.d_regret);
+        epilogue_kernel<false><<<cnt, BNL_EPI_THREADS, esmem, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out,
+                                                                          rq.kind, rq.code, rq.arg, ds.nobs,
+                                                                          dev.d_regret, mstride);
       BNL_CUDA(ctx, cudaGetLastError());
       tm->launches++;
       BNL_CUDA(ctx, cudaEventRecord(dev.eve1, dev.stream));
@@ -474,7 +509,8 @@ extern "C" int bnl_stat_from_tables(bnl_ctx *ctx, int kind, int code, double arg
   long long cells = 0;
   std::vector<BnlUnit> units(n);
   for (int u = 0; u < n; u++) {
-    if (llx[u] < 1 || lly[u] < 1 || llz[u] < 1 || llx[u] > BNL_MAX_LEVELS || lly[u] > BNL_MAX_LEVELS || nz[u] < 0)
+    if (llx[u] < 1 || lly[u] < 1 || llz[u] < 1 || llx[u] > BNL_MAX_LEVELS_WIDE || lly[u] > BNL_MAX_LEVELS_WIDE ||
+        nz[u] < 0)
       return bnl_fail(ctx, BNL_EINVAL, "bnl_stat_from_tables: bad table shape for unit %d", u);
     const long long c = (long long)llx[u] * lly[u] * llz[u];
     if (table_off[u + 1] - table_off[u] < c || c > kMaxBatchCells)
@@ -498,12 +534,15 @@ extern "C" int bnl_stat_from_tables(bnl_ctx *ctx, int kind, int code, double arg
   for (int u = 0; u < n; u++)
     BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_tables + units[u].table_off, tables + table_off[u],
                                   (size_t)units[u].cells * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+  int mstride = 0;
+  if ((rc = epilogue_stride(ctx, dev, units, n, kind, &mstride))) return rc;
+  const size_t esmem = (size_t)mstride * BNL_EPI_WARPS * sizeof(int);
   if (kind == 0 && (code == BNL_JT || code == BNL_MI_SH))
-    epilogue_kernel<true><<<n, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out, kind, code,
-                                                               arg, nrows, dev.d_regret);
+    epilogue_kernel<true><<<n, BNL_EPI_THREADS, esmem, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out, kind,
+                                                                   code, arg, nrows, dev.d_regret, mstride);
   else
-    epilogue_kernel<false><<<n, BNL_EPI_THREADS, 0, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out, kind, code,
-                                                                arg, nrows, dev.d_regret);
+    epilogue_kernel<false><<<n, BNL_EPI_THREADS, esmem, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out, kind,
+                                                                    code, arg, nrows, dev.d_regret, mstride);
   BNL_CUDA(ctx, cudaGetLastError());
   std::vector<double> out((size_t)n * 4);
   BNL_CUDA(ctx, cudaMemcpyAsync(out.data(), dev.d_out, out.size() * sizeof(double), cudaMemcpyDeviceToHost,

@@ -31,7 +31,8 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
 __global__ void __launch_bounds__(BNL_CNT_THREADS)
 count_units_kernel(const uint8_t *__restrict__ u8, size_t stride, long long groups,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
-                   int *__restrict__ tables, int nunits, int chunks, int smem_cells) {
+                   int *__restrict__ tables, int nunits, int chunks, int smem_cells,
+                   const uint16_t *__restrict__ u16, size_t stride16) {
   extern __shared__ int hist[];
   __shared__ BnlUnit su;
   const int chunk = blockIdx.x / nunits, u = order[blockIdx.x % nunits];
@@ -58,8 +59,24 @@ count_units_kernel(const uint8_t *__restrict__ u8, size_t stride, long long grou
 #pragma unroll
     for (int j = 0; j < 16; j++) idx[j] = 0;
     for (int k = 0; k < ncols; k++) {
-      const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
       const int m = su.mul[k];
+      if (su.col[k] & BNL_WIDE_BIT) {
+        // uint16 column (128..32767 levels): 16 rows = two 128-bit loads; bit 15 marks NA
+        const uint4 *p16 = reinterpret_cast<const uint4 *>(u16 + (size_t)(su.col[k] & ~BNL_WIDE_BIT) * stride16) + 2 * g;
+        const uint4 a = ldg_stream(p16), b = ldg_stream(p16 + 1);
+        const unsigned hw[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int h = 0; h < 8; h++) {
+          const unsigned lo = hw[h] & 0xFFFFu, hi = hw[h] >> 16;
+          const int j0 = 2 * h, j1 = 2 * h + 1;
+          if (lo & 0x8000u) na[j0 >> 2] |= 0x80u << (8 * (j0 & 3));
+          if (hi & 0x8000u) na[j1 >> 2] |= 0x80u << (8 * (j1 & 3));
+          idx[j0] += (int)lo * m;
+          idx[j1] += (int)hi * m;
+        }
+        continue;
+      }
+      const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
       const unsigned ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
       for (int q = 0; q < 4; q++) {
@@ -620,8 +637,10 @@ template <bool EXT>
 __global__ void __launch_bounds__(BNL_EPI_THREADS)
 epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ tables,
                 double *__restrict__ out, int kind, int code, double arg, long long nrows,
-                const double *__restrict__ regret) {
-  __shared__ int s_marg[BNL_EPI_WARPS][2 * BNL_MAX_LEVELS + 2];
+                const double *__restrict__ regret, int marg_stride) {
+  // margins of one stratum per warp: llx + lly ints, in dynamic shared memory so
+  // that tests on factors with thousands of levels (uint16 columns) fit as well.
+  extern __shared__ int s_marg_dyn[];
   __shared__ double s_s[BNL_EPI_WARPS], s_c[BNL_EPI_WARPS], s_df[BNL_EPI_WARPS];
   __shared__ long long s_n[BNL_EPI_WARPS];
   __shared__ int s_q;
@@ -630,7 +649,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   const int *T = tables + U.table_off;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int llx = U.llx, lly = U.lly, llz = U.llz, sl = llx * lly;
-  int *marg = s_marg[warp];
+  int *marg = s_marg_dyn + (size_t)warp * marg_stride;
 
   // BDs: the prior is spread over the OBSERVED parent configurations only
   // (src/scores/dirichlet.posterior.c:180 -> all_levels = FALSE).

@@ -544,6 +544,9 @@ extern "C" int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, 
       for (int j = 0; j < np; j++) {
         const int c = pa_idx[p0 + j];
         if (ds.is_numeric[c]) cu.gslot[cu.K++] = ds.slot[c];
+        else if (ds.is_wide[c])
+          return bnl_fail(ctx, BNL_EUNSUPPORTED, "unit %d: discrete parents of a numeric node are limited to %d levels",
+                          u, BNL_MAX_LEVELS);
         else {
           cu.dslot[cu.nd] = ds.slot[c];
           cu.dmul[cu.nd++] = (int)nconfig;

@@ -13,6 +13,12 @@
 #define BNL_MAXK 16            // columns per unit: x, y and up to 14 conditioning / 15 parents
 #define BNL_NA_U8 0xFFu        // NA and row padding in the packed uint8 layout
 #define BNL_MAX_LEVELS 127     // bit 7 of a packed code marks NA
+// Factors with 128..32767 levels are kept as uint16 (bit 15 marks NA) in a block
+// of their own; a unit that touches one carries BNL_WIDE_BIT in that col[] entry
+// and is counted by the generic kernel.
+#define BNL_MAX_LEVELS_WIDE 32767
+#define BNL_WIDE_BIT (1 << 30)
+#define BNL_NA_U16 0xFFFFu
 #define BNL_COL_ALIGN 256      // bytes; every packed column starts 256-byte aligned
 
 // one unit of discrete work as the kernels see it.
@@ -61,6 +67,7 @@ struct BnlDevice {
   int max_smem = 48 * 1024;
   bool attr_done = false;   // per-device kernel attributes set
   bool gattr_done = false;
+  bool epi_attr_done = false;                            // epilogue opted in to > 48 KB of shared memory
 };
 
 // one device's copy of a data set.
@@ -69,6 +76,8 @@ struct BnlDeviceData {
   double *f64 = nullptr;       // nc columns, stride_f64 doubles apart
   double *mean = nullptr;      // nc
   double *cov = nullptr;       // nc x nc, column-major, divisor nobs - 1
+  uint16_t *u16 = nullptr;     // nw wide factor columns, stride_u16 elements apart
+  size_t u16_bytes = 0;
   double *bge_nu = nullptr;    // nc prior means of the BGe score (null: the column means)
   size_t u8_bytes = 0, f64_bytes = 0, mean_bytes = 0, cov_bytes = 0, nu_bytes = 0;
 };
@@ -76,10 +85,12 @@ struct BnlDeviceData {
 struct BnlDataSet {
   int ncols = 0;
   long long nobs = 0;
-  int nd = 0, nc = 0;                   // discrete / numeric column counts
-  size_t stride_u8 = 0, stride_f64 = 0;
+  int nd = 0, nc = 0, nw = 0;           // uint8 factor / numeric / uint16 factor column counts
+  size_t stride_u8 = 0, stride_f64 = 0, stride_u16 = 0;
   std::vector<int> is_numeric, nlevels, slot;
+  std::vector<int> is_wide;             // per column: a factor kept as uint16 (slot indexes that block)
   std::vector<int> slot_has_na;         // per packed factor column: any NA?
+  std::vector<int> wide_has_na;         // the same for the uint16 block
   std::vector<BnlDeviceData> dev;       // one per context device
   std::vector<double> h_mean, h_cov;    // host copies of the Gaussian moments
   bool any_nan = false;                 // some numeric column holds a missing value

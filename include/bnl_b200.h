@@ -82,8 +82,9 @@ int bnl_last_call_profile(const bnl_ctx *ctx, double *total_ms, double *count_ms
 
 /* Upload and pack a data frame. col[i] points to nobs int32 (is_numeric[i] == 0,
  * nlevels[i] levels) or nobs double (is_numeric[i] != 0). Factors are repacked
- * to uint8 (code - 1, NA -> 0xFF); at most 127 levels per factor (more returns
- * BNL_EUNSUPPORTED: the uint16 layout is not built yet).
+ * to uint8 (code - 1, NA -> 0xFF) when they have at most 127 levels and to
+ * uint16 (NA -> 0xFFFF) up to 32767 levels; units that touch a uint16 column
+ * are counted by the generic kernel.
  * Replaces the per-call column extraction of tabular_from_SEXP()
  * (src/core/data.table.c:143-225) and c_dataframe_column()
  * (src/minimal/data.frame.c:41). */

@@ -162,12 +162,61 @@ def test_error_paths(engine):
     with pytest.raises(BnlError):
         engine.register([np.array([1, 5], np.int32)], [3])       # code outside 1..nlevels
     with pytest.raises(BnlError):
-        engine.register([np.ones(4, np.int32)], [300])           # beyond the uint8 layout
+        engine.register([np.ones(4, np.int32)], [40000])         # beyond the uint16 layout
     big = engine.register([np.ones(4, np.int32)] * 8, [100] * 8)
     with pytest.raises(BnlError) as ei:
         big.ci_discrete("mi", [0], [1], [[2, 3, 4, 5, 6]])
     assert ei.value.code == 4                                    # BNL_EOVERFLOW
     big.release()
+
+
+@pytest.mark.parametrize("ds", ["gaussian_test", "gaussian_test_na"])
+def test_wide_factors_uint16_layout(engine):
+    """Factors with 128..32767 levels live in the uint16 block: counts bit-exact,
+    tests and scores against the oracle, in every role (x, y, conditioning variable,
+    node, parent), with NA, through a device-side resample, and next to uint8 columns."""
+    from oracle import oracle as orc
+    rng = np.random.default_rng(77)
+    n = 60_011
+    lev = [300, 3, 1500, 4, 130, 2]
+    cols = [rng.integers(1, l + 1, n).astype(np.int32) for l in lev]
+    cols[1] = (1 + (cols[0] + rng.integers(0, 2, n)) % 3).astype(np.int32)     # depends on the wide column
+    cols[4][rng.random(n) < 0.01] = np.iinfo(np.int32).min
+    cols[3][rng.random(n) < 0.01] = np.iinfo(np.int32).min
+    d = engine.register(cols, lev)
+    x, y = [0, 1, 3, 4, 5, 0], [1, 2, 5, 3, 1, 4]
+    z = [[], [], [0], [5], [4, 3], [3]]
+    for t, (a, b, c) in zip(d.counts(x, y, z), zip(x, y, z)):
+        ref = orc.counts(cols[a], lev[a], cols[b], lev[b], [cols[i] for i in c], [lev[i] for i in c])
+        assert np.array_equal(t, ref), (a, b, c)
+    for test in ("mi", "x2", "mi-adf", "jt", "mi-sh"):
+        st, df, pv = d.ci_discrete(test, x, y, z)
+        for i in range(len(x)):
+            if test == "jt" and lev[x[i]] * lev[y[i]] > 5000:
+                continue                                  # the oracle's JT is O(llx^2 lly^2)
+            o = orc.ci_discrete(test, cols[x[i]], lev[x[i]], cols[y[i]], lev[y[i]], [cols[j] for j in z[i]],
+                                [lev[j] for j in z[i]])
+            assert df[i] == o[1], (test, i)
+            _check(st[i], o[0], (test, i, "stat"), atol=1e-9)
+            _check(pv[i], o[2], (test, i, "p"), atol=1e-300)
+    tg, pa = [0, 1, 2, 5, 3], [[], [0], [5], [2, 1], [0, 5]]
+    complete = [c.copy() for c in cols]
+    for c, l in zip(complete, lev):
+        c[c == np.iinfo(np.int32).min] = 1
+    dc = engine.register(complete, lev)
+    for score, arg in (("loglik", 0.0), ("bic", 5.5), ("bde", 1.0), ("bds", 1.0), ("k2", 0.0), ("qnml", 0.0)):
+        sc, npar = dc.score_discrete(score, tg, pa, arg)
+        for i in range(len(tg)):
+            o = orc.score_discrete(score, complete[tg[i]], lev[tg[i]], [complete[j] for j in pa[i]],
+                                   [lev[j] for j in pa[i]], arg)
+            _check(sc[i], o[0], (score, i))
+    rows = rng.integers(0, n, 20_000)
+    rs = d.resample(rows)
+    rr = engine.register([c[rows] for c in cols], lev)
+    for ta, tb in zip(rs.counts(x, y, z), rr.counts(x, y, z)):
+        assert np.array_equal(ta, tb)
+    for q in (d, dc, rs, rr):
+        q.release()
 
 
 @pytest.mark.parametrize("ds", ["gaussian_test", "gaussian_test_na"])
