@@ -170,7 +170,6 @@ def test_error_paths(engine):
     big.release()
 
 
-@pytest.mark.parametrize("ds", ["gaussian_test", "gaussian_test_na"])
 def test_wide_factors_uint16_layout(engine):
     """Factors with 128..32767 levels live in the uint16 block: counts bit-exact,
     tests and scores against the oracle, in every role (x, y, conditioning variable,
