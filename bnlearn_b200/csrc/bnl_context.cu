@@ -291,6 +291,8 @@ extern "C" void bnl_shutdown(bnl_ctx *ctx) {
     d.pool.clear();
     cudaFree(d.stage); cudaFree(d.d_flags); cudaFree(d.d_regret);
     cudaFreeHost(d.h_pack);
+    cudaFreeHost(d.h_nstage);
+    for (auto &e : d.ev_nstage) cudaEventDestroy(e);
     if (d.ev_stage[0]) cudaEventDestroy(d.ev_stage[0]);
     if (d.ev_stage[1]) cudaEventDestroy(d.ev_stage[1]);
     if (d.stream2) cudaStreamDestroy(d.stream2);
@@ -442,6 +444,66 @@ static int upload_factors_hybrid(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, Bn
   return BNL_OK;
 }
 
+// Numeric columns of a large data frame that sits in PAGEABLE host memory (what R
+// hands over): cudaMemcpyAsync would bounce them through the driver's own small
+// staging buffer at 8-10 GB/s. Here host threads copy 4 MiB chunks into pinned
+// buffers of their own (two each, so the copy of one chunk overlaps the DMA of the
+// previous) and queue the transfers on stream2. Columns already in pinned memory go
+// straight through.
+static int upload_numeric_staged(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, BnlDeviceData &dd0,
+                                 const void *const *col, const std::vector<int> &ncols_idx) {
+  const size_t kChunk = 4u << 20;
+  unsigned hw = std::thread::hardware_concurrency();
+  int nthreads = (int)(hw ? hw : 8);
+  if (const char *v = getenv("BNL_PACK_THREADS")) if (*v) nthreads = atoi(v);
+  nthreads = std::max(1, std::min(nthreads, 16));
+  const size_t col_bytes = (size_t)ds.nobs * sizeof(double);
+  const long long chunks_per_col = (long long)((col_bytes + kChunk - 1) / kChunk);
+  const long long total = chunks_per_col * (long long)ncols_idx.size();
+  nthreads = (int)std::min<long long>(nthreads, total);
+  int rc;
+  if ((rc = bnl_reserve_pinned(ctx, &d0.h_nstage, &d0.h_nstage_cap, (size_t)2 * nthreads * kChunk))) return rc;
+  while ((int)d0.ev_nstage.size() < 2 * nthreads) {
+    cudaEvent_t e;
+    BNL_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    d0.ev_nstage.push_back(e);
+  }
+  // stream2 must see the zero fill of the block queued on the main stream.
+  BNL_CUDA(ctx, cudaEventRecord(d0.ev_stage[0], d0.stream));
+  BNL_CUDA(ctx, cudaStreamWaitEvent(d0.stream2, d0.ev_stage[0], 0));
+  std::atomic<long long> next(0);
+  std::atomic<int> failed(0);
+  auto worker = [&](int t) {
+    cudaSetDevice(d0.id);
+    long long k;
+    int used = 0;
+    while (!failed.load() && (k = next.fetch_add(1)) < total) {
+      const int c = ncols_idx[(size_t)(k / chunks_per_col)];
+      const size_t o = (size_t)(k % chunks_per_col) * kChunk;
+      const size_t len = std::min(kChunk, col_bytes - o);
+      const int slot = 2 * t + (used & 1);
+      if (used >= 2 && cudaEventSynchronize(d0.ev_nstage[slot]) != cudaSuccess) { failed = 1; break; }
+      uint8_t *buf = d0.h_nstage + (size_t)slot * kChunk;
+      memcpy(buf, (const uint8_t *)col[c] + o, len);
+      cudaError_t e = cudaMemcpyAsync((uint8_t *)(dd0.f64 + ds.stride_f64 * ds.slot[c]) + o, buf, len,
+                                      cudaMemcpyHostToDevice, d0.stream2);
+      if (e == cudaSuccess) e = cudaEventRecord(d0.ev_nstage[slot], d0.stream2);
+      if (e != cudaSuccess) { failed = 1; break; }
+      used++;
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < nthreads; t++) th.emplace_back(worker, t);
+  worker(0);
+  for (auto &x : th) x.join();
+  cudaSetDevice(d0.id);
+  if (failed.load()) return bnl_fail(ctx, BNL_ECUDA, "staged upload of the numeric columns failed");
+  // the main stream continues after everything queued on stream2.
+  BNL_CUDA(ctx, cudaEventRecord(d0.ev_stage[1], d0.stream2));
+  BNL_CUDA(ctx, cudaStreamWaitEvent(d0.stream, d0.ev_stage[1], 0));
+  return BNL_OK;
+}
+
 extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col,
                                  const int *is_numeric, const int *nlevels, int64_t nobs,
                                  bnl_data *handle) {
@@ -528,8 +590,23 @@ extern "C" int bnl_data_register(bnl_ctx *ctx, int ncols, const void *const *col
     if ((rc = upload_factors_hybrid(ctx, ds, d0, dd0, col, nlevels, dcols, d_bad, host_flags)))
       return cleanup(rc);
   }
+  // numeric columns in pageable memory: chunked through pinned buffers by host threads.
+  std::vector<char> staged(ncols, 0);
+  if (ds.nc > 0 && (long long)ds.nc * nobs >= (8ll << 20) && !getenv("BNL_NO_HOST_PACK")) {
+    std::vector<int> pageable;
+    for (int i = 0; i < ncols; i++) {
+      if (!is_numeric[i]) continue;
+      cudaPointerAttributes at;
+      const bool pinned = cudaPointerGetAttributes(&at, col[i]) == cudaSuccess &&
+                          (at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged);
+      cudaGetLastError();                       // unregistered host memory is not an error here
+      if (!pinned) { pageable.push_back(i); staged[i] = 1; }
+    }
+    if (!pageable.empty() && (rc = upload_numeric_staged(ctx, ds, d0, dd0, col, pageable))) return cleanup(rc);
+  }
   for (int i = 0; i < ncols; i++) {
     if (nobs == 0) continue;
+    if (staged[i]) continue;
     if (hybrid && !is_numeric[i] && !ds.is_wide[i]) continue;
     if (is_numeric[i]) {
       REG_CUDA(cudaMemcpyAsync(dd0.f64 + ds.stride_f64 * ds.slot[i], col[i],

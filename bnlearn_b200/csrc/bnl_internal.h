@@ -60,6 +60,8 @@ struct BnlDevice {
   cudaStream_t stream2 = nullptr;                        // host-packed columns travel here
   cudaEvent_t ev_stage[2] = {nullptr, nullptr};
   uint8_t *h_pack = nullptr; size_t h_pack_cap = 0;      // pinned ring of host-packed columns
+  uint8_t *h_nstage = nullptr; size_t h_nstage_cap = 0;  // pinned chunks for numeric columns from pageable memory
+  std::vector<cudaEvent_t> ev_nstage;                    // one per chunk
   int *d_flags = nullptr; size_t flags_cap = 0;          // bad-code flag + per-column NA flags
   double *d_regret = nullptr;                            // NML regret table, (K + 1) x (N + 1), see bnl_regret_table()
   std::vector<std::pair<void *, size_t>> pool;           // released blocks (pointer, bytes)

@@ -658,3 +658,32 @@ def test_alloc_fill_commit_equals_register(engine):
     assert np.allclose(a, b, rtol=1e-12, atol=0)
     src.release()
     dst.release()
+
+
+def test_large_numeric_registration_staged_upload(engine):
+    """Numeric data frames above 8 M values in pageable memory are uploaded in 4 MiB
+    chunks through pinned buffers by host threads; pinned sources go straight
+    through. Either way the resident columns -- hence the moments -- are the same."""
+    import torch
+    rng = np.random.default_rng(41)
+    n, p = 1_200_007, 8
+    cols = [rng.normal(size=n) * (1 + j) + j for j in range(p)]
+    cols[3] = cols[0] * 0.5 + cols[3]
+    d1 = engine.register(cols)
+    pinned = torch.empty((p, n), dtype=torch.float64, pin_memory=True)
+    host = pinned.numpy()
+    for j in range(p):
+        host[j] = cols[j]
+    d2 = engine.register([host[j] for j in range(p)])
+    m1, c1 = d1.moments()
+    m2, c2 = d2.moments()
+    assert np.array_equal(m1, m2) and np.array_equal(c1, c2)
+    X = np.stack(cols, axis=1)
+    assert np.allclose(m1, X.mean(axis=0), rtol=1e-12, atol=1e-12)
+    assert np.allclose(c1, np.cov(X, rowvar=False), rtol=1e-10, atol=1e-12)
+    a = d1.ci_gaussian("cor", [0, 1], [3, 2], [[], [4, 5]])
+    b = d2.ci_gaussian("cor", [0, 1], [3, 2], [[], [4, 5]])
+    for u, v in zip(a, b):
+        assert np.array_equal(u, v)
+    d1.release()
+    d2.release()
