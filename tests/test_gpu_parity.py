@@ -687,3 +687,34 @@ def test_large_numeric_registration_staged_upload(engine):
         assert np.array_equal(u, v)
     d1.release()
     d2.release()
+
+
+def test_no_device_memory_growth(engine):
+    """Register / test / score / resample / release in a loop: device memory in use
+    settles (pooled blocks are reused), it does not grow with the iteration count."""
+    import torch
+    names, cols, nlev = load_discrete("alarm")
+    gn, gcols = load_gaussian("gaussian_test")
+
+    def cycle():
+        d = engine.register(cols, nlev)
+        d.ci_discrete("mi", [0, 1, 2], [3, 4, 5], [[], [6], [7, 8]])
+        d.score_discrete("bde", [0, 1], [[2], [3, 4]], 1.0)
+        r = d.resample(np.arange(0, len(cols[0]), 2, dtype=np.int32))
+        r.hc("bic", 4.0, max_iter=3)
+        r.release()
+        d.release()
+        g = engine.register(gcols)
+        g.ci_gaussian("zf", [0, 1], [2, 3], [[4], []])
+        g.score_gaussian("bge", [0], [[1, 2]])
+        g.release()
+
+    for _ in range(5):
+        cycle()
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(40):
+        cycle()
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free0 - free1 < 32 << 20, (free0, free1)
