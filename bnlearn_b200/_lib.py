@@ -56,6 +56,8 @@ SIGNATURES = {
                             c_dbl_p]),
     "bnl_score_cg": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p, c_int_p, c_int_p,
                                c_dbl_p, c_dbl_p]),
+    "bnl_pc_stable": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, C.c_int, c_int_p, c_dbl_p,
+                                c_int_p, C.POINTER(C.c_longlong), c_int_p, C.c_longlong, c_dbl_p]),
     "bnl_tabu": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p, c_int_p, c_int_p,
                            C.c_double, C.c_longlong, C.c_int, C.c_int, c_int_p, c_dbl_p,
                            C.POINTER(C.c_longlong), c_dbl_p]),

@@ -383,3 +383,129 @@ extern "C" int bnl_tabu(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_is
   if (iterations) *iterations = it;
   return BNL_OK;
 }
+
+// ---------------------------------------------------------------------------
+// pc.stable: the skeleton phase in one call (pc.stable.backend, R/pcalgo.R:2-148).
+// At every level (size of the conditioning sets) all node pairs see the skeleton
+// frozen at the previous level, so the pairs of a level go to bnl_allsubs_test as
+// ONE batch: first every pair (x, y) conditioned on subsets of adj(x) \ y, then the
+// pairs still connected, as (y, x) on subsets of adj(y) \ x. Neighbour order, the
+// level-1 pruning of the second list, the stop rule and the counter are the
+// reference's.
+
+extern "C" int bnl_pc_stable(bnl_ctx *ctx, bnl_data data, int test_e, double alpha, int nnodes,
+                             int max_sx, int *adj, double *pvalue, int *ndsep, long long *dsep_off,
+                             int *dsep_idx, long long dsep_cap, double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (nnodes < 2 || !adj) return bnl_fail(ctx, BNL_EINVAL, "bnl_pc_stable: bad arguments");
+  const int n = nnodes;
+  const long long np = (long long)n * (n - 1) / 2;
+  if (np > INT32_MAX / 4) return bnl_fail(ctx, BNL_EOVERFLOW, "bnl_pc_stable: too many node pairs");
+  auto pid = [&](int i, int j) { return (long long)i * n - (long long)i * (i + 1) / 2 + (j - i - 1); };  // i < j
+  std::vector<int> pi((size_t)np), pj((size_t)np);
+  for (int i = 0, k = 0; i < n; i++) for (int j = i + 1; j < n; j++, k++) { pi[k] = i; pj[k] = j; }
+  std::vector<double> pval((size_t)np, 0.0);
+  std::vector<char> has_p((size_t)np, 0), sep((size_t)np, 0), in_skel((size_t)np, 1);
+  std::vector<int> max_adj((size_t)np, n - 1);
+  std::vector<std::vector<int>> sepset((size_t)np);
+  if (max_sx < 0 || max_sx > n - 2) max_sx = n - 2;
+
+  for (int level = 0; level <= max_sx; level++) {
+    // adjacency lists in the order of R/pcalgo.R:88-91: rows where the node is the
+    // second endpoint first, then those where it is the first.
+    std::vector<std::vector<int>> nb(n);
+    for (long long k = 0; k < np; k++) if (in_skel[k]) nb[pj[k]].push_back(pi[k]);
+    for (long long k = 0; k < np; k++) if (in_skel[k]) nb[pi[k]].push_back(pj[k]);
+    std::vector<long long> first, second, live;
+    std::vector<std::vector<int>> n1((size_t)np), n2((size_t)np);
+    std::vector<char> has_info((size_t)np, 0);
+    for (long long k = 0; k < np; k++) {
+      if (level > max_adj[k] || sep[k]) continue;
+      for (int v : nb[pi[k]]) if (v != pj[k]) n1[k].push_back(v);
+      for (int v : nb[pj[k]]) if (v != pi[k]) n2[k].push_back(v);
+      if ((int)n1[k].size() < level && (int)n2[k].size() < level) { max_adj[k] = 0; continue; }
+      has_info[k] = 1;
+      live.push_back(k);
+      if ((int)n1[k].size() >= level) first.push_back(k);
+    }
+    auto run = [&](const std::vector<long long> &list, bool swap, std::vector<char> &separated) -> int {
+      const int m = (int)list.size();
+      if (m == 0) return BNL_OK;
+      std::vector<int> xs(m), ys(m), off(m + 1, 0), sx, nfix(m, 0), doff(m + 1, 0), nds(m, -1);
+      for (int q = 0; q < m; q++) {
+        const long long k = list[q];
+        xs[q] = swap ? pj[k] : pi[k];
+        ys[q] = swap ? pi[k] : pj[k];
+        const std::vector<int> &c = swap ? n2[k] : n1[k];
+        sx.insert(sx.end(), c.begin(), c.end());
+        off[q + 1] = (int)sx.size();
+        doff[q + 1] = off[q + 1];
+      }
+      std::vector<double> out((size_t)m * 3);
+      std::vector<int> ds(std::max<size_t>(sx.size(), 1));
+      int rc = bnl_allsubs_test(ctx, data, test_e, m, xs.data(), ys.data(), off.data(),
+                                sx.empty() ? ds.data() : sx.data(), nfix.data(), level, level, alpha, out.data(),
+                                doff.data(), ds.data(), nds.data(), test_counter);
+      if (rc) return rc;
+      for (int q = 0; q < m; q++) {
+        const long long k = list[q];
+        if (out[(size_t)q * 3] > alpha) {
+          pval[k] = out[(size_t)q * 3]; has_p[k] = 1; sep[k] = 1; max_adj[k] = 0; separated[k] = 1;
+          sepset[k].assign(ds.begin() + doff[q], ds.begin() + doff[q] + std::max(nds[q], 0));
+        }
+      }
+      return BNL_OK;
+    };
+    std::vector<char> separated((size_t)np, 0);
+    int rc = run(first, false, separated);
+    if (rc) return rc;
+    for (long long k : live) {
+      if (separated[k]) continue;
+      if (level == 1) {               // drop from the second list what the first already tried
+        std::vector<int> keep;
+        for (int v : n2[k]) if (std::find(n1[k].begin(), n1[k].end(), v) == n1[k].end()) keep.push_back(v);
+        n2[k].swap(keep);
+      }
+      bool same = n1[k].size() == n2[k].size();
+      if (same) {
+        std::vector<int> a = n1[k], b = n2[k];
+        std::sort(a.begin(), a.end()); std::sort(b.begin(), b.end());
+        same = a == b;
+      }
+      if ((int)n2[k].size() >= level && level > 0 && !same) second.push_back(k);
+    }
+    rc = run(second, true, separated);
+    if (rc) return rc;
+    for (long long k : live)
+      if (!separated[k]) {
+        pval[k] = 0.0; has_p[k] = 1;
+        max_adj[k] = (int)std::max(n1[k].size(), n2[k].size());
+      }
+    bool done = true;
+    for (long long k = 0; k < np; k++) {
+      in_skel[k] = has_p[k] && pval[k] < alpha;
+      if (max_adj[k] > level) done = false;
+    }
+    if (done) break;
+  }
+  // outputs: symmetric adjacency, p-values, separating sets (CSR over the pairs i < j)
+  long long used = 0;
+  for (int i = 0; i < n; i++) adj[(size_t)i + (size_t)i * n] = 0;
+  for (long long k = 0; k < np; k++) {
+    const int i = pi[k], j = pj[k], e = in_skel[k] ? 1 : 0;
+    adj[(size_t)i + (size_t)j * n] = adj[(size_t)j + (size_t)i * n] = e;
+    if (pvalue) pvalue[(size_t)i + (size_t)j * n] = pvalue[(size_t)j + (size_t)i * n] = pval[k];
+    if (ndsep) ndsep[k] = sep[k] ? (int)sepset[k].size() : -1;
+    if (dsep_off) dsep_off[k] = used;
+    if (sep[k]) {
+      if (dsep_idx) {
+        if (used + (long long)sepset[k].size() > dsep_cap)
+          return bnl_fail(ctx, BNL_EINVAL, "bnl_pc_stable: dsep_idx too small (needs more than %lld entries)", dsep_cap);
+        for (int v : sepset[k]) dsep_idx[used++] = v;
+      } else used += (long long)sepset[k].size();
+    }
+  }
+  if (dsep_off) dsep_off[np] = used;
+  (void)pid;
+  return BNL_OK;
+}

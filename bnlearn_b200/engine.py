@@ -279,6 +279,37 @@ class DataSet:
             counter.add(cnt.value)
         return amat, scores, iters.value
 
+    def pc_stable(self, test, alpha=0.05, nnodes=None, max_sx=-1, counter=None):
+        """bnl_pc_stable: skeleton, p-values and separating sets in one call. Returns
+        (sorted edge list, {(i, j): separating set}, {(i, j): p-value}) like learners.pc_stable."""
+        e = self.engine
+        n = len(self.nlevels) if nnodes is None else int(nnodes)
+        npairs = n * (n - 1) // 2
+        adj = np.zeros((n, n), dtype=np.int32, order="F")
+        pv = np.zeros((n, n), order="F")
+        nds = np.zeros(max(npairs, 1), dtype=np.int32)
+        off = np.zeros(npairs + 1, dtype=np.int64)
+        cap = max(npairs * 4, 1024)
+        cnt = C.c_double(0.0)
+        while True:
+            idx = np.zeros(cap, dtype=np.int32)
+            cnt.value = 0.0
+            rc = e._lib.bnl_pc_stable(e._ctx, self.handle, TESTS[test], float(alpha), n, int(max_sx), _ip(adj),
+                                      _dp(pv), _ip(nds), off.ctypes.data_as(C.POINTER(C.c_longlong)), _ip(idx),
+                                      cap, C.byref(cnt))
+            if rc != 0 and b"dsep_idx too small" in e._lib.bnl_last_error(e._ctx) and cap < (1 << 28):
+                cap *= 8
+                continue
+            e._check(rc)
+            break
+        if counter is not None:
+            counter.add(cnt.value)
+        pairs = [(i, j) for i in range(n) for j in range(i + 1, n)]
+        skeleton = [p for k, p in enumerate(pairs) if adj[p[0], p[1]]]
+        dsep = {p: [int(v) for v in idx[off[k]:off[k + 1]]] for k, p in enumerate(pairs) if nds[k] >= 0}
+        pvals = {p: float(pv[p[0], p[1]]) for p in pairs}
+        return skeleton, dsep, pvals
+
     def tabu(self, score, arg=0.0, nnodes=None, start=None, blmat=None, wlmat=None, maxp=np.inf,
              max_iter=0, tabu=10, max_tabu=None, counter=None):
         """bnl_tabu: tabu search in one library call; returns (amat, scores, iterations)."""

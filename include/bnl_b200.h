@@ -303,6 +303,20 @@ int bnl_tabu(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss, int nnod
              long long max_iter, int tabu, int max_tabu, int *amat, double *node_scores,
              long long *iterations, double *test_counter);
 
+/* The skeleton phase of pc.stable in one call (pc.stable.backend,
+ * R/pcalgo.R:2-148, one allsubs_test .Call per node pair and level there): at
+ * every level all pairs see the skeleton of the previous level, so a level is
+ * two batched bnl_allsubs_test calls. The first nnodes registered columns are
+ * the nodes; max_sx < 0: no limit on the conditioning-set size. Outputs: adj
+ * (nnodes x nnodes, symmetric 0/1), pvalue (same shape, may be NULL), and for
+ * the pairs i < j in row-major order ndsep[pair] (-1: not separated) with the
+ * separating sets in dsep_idx[dsep_off[pair] .. dsep_off[pair + 1]) (dsep_off
+ * has npairs + 1 entries; dsep_cap entries are available in dsep_idx).
+ * test_counter advances as in the pair-by-pair loop. */
+int bnl_pc_stable(bnl_ctx *ctx, bnl_data data, int test_e, double alpha, int nnodes, int max_sx,
+                  int *adj, double *pvalue, int *ndsep, long long *dsep_off, int *dsep_idx,
+                  long long dsep_cap, double *test_counter);
+
 /* estimate_mi_matrix (src/learning/local/mi.matrix.c:184-252 over
  * mi_matrix_discrete :40-137 / mi_matrix_gaussian :141-181), the coefficient
  * matrix behind aracne() and chow.liu(): for the ncols listed columns (all

@@ -319,3 +319,29 @@ def test_native_tabu_matches_the_stepwise_loop(engine, ds, score, arg, tabu_len,
     assert counter.value == be.counter.value
     assert np.allclose(s1, s2, rtol=1e-12, atol=0)
     d.release()
+
+
+@pytest.mark.parametrize("ds,test", [("learning_test", "mi"), ("alarm", "x2"), ("gaussian_test", "cor"),
+                                     ("learning_test_na", "mi")])
+def test_native_pc_stable_matches_the_level_loop(engine, ds, test):
+    """bnl_pc_stable against learners.pc_stable on the same engine (itself held to the
+    reference's backend above): skeleton, separating sets, p-values, test counter."""
+    from bnlearn_b200 import callsites as cs, learners
+    if ds == "gaussian_test":
+        names, cols = load_gaussian(ds)
+        d = engine.register(cols)
+    else:
+        names, cols, nlev = load_discrete(ds)
+        if ds == "alarm":
+            cols = [c[:5000] for c in cols]
+        d = engine.register(cols, nlev)
+    be = learners.GpuBackend(d)
+    s1, d1, p1 = learners.pc_stable(be, len(cols), test, 0.05)
+    counter = cs.TestCounter()
+    s2, d2, p2 = d.pc_stable(test, 0.05, counter=counter)
+    assert s1 == s2
+    assert d1 == d2
+    assert counter.value == be.counter.value
+    for k in p1:
+        assert (p1[k] is None and p2[k] == 0.0) or p1[k] == p2[k], (k, p1[k], p2[k])
+    d.release()
