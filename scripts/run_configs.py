@@ -62,9 +62,12 @@ def config_b(eng, rows, with_ref):
     ds, t_reg = timed(lambda: eng.register(cols, lev))
     be = learners.GpuBackend(ds)
     (skel, dsep, pv), t = timed(lambda: learners.pc_stable(be, len(cols), "mi", 0.05))
+    (nskel, ndsep, _), tn = timed(lambda: ds.pc_stable("mi", 0.05))
+    (nskel, ndsep, _), tn = timed(lambda: ds.pc_stable("mi", 0.05))         # second call: warm
     rec = {"config": "B: pc.stable + mi, alarm-shaped (37 x %d)" % rows, "gpu_wall_s": t,
            "register_s": t_reg, "edges": len(skel), "ntests": be.counter.value,
-           "tests_per_sec": be.counter.value / t}
+           "tests_per_sec": be.counter.value / t, "native_pc_stable_wall_s": tn,
+           "native_identical": bool(nskel == skel and ndsep == dsep)}
     ds.release()
     if with_ref:
         from refbackend import RefBackend
