@@ -22,7 +22,6 @@ const long long kKnobChunkRows = env_ll("BNL_CHUNK_ROWS", 0);
 const long long kKnobL2MB = env_ll("BNL_L2_MB", 192);
 const int kKnobMidThreads = (int)env_ll("BNL_MID_THREADS", 1024);
 const long long kKnobGroup = env_ll("BNL_GROUP", 1);
-const long long kKnobGroupThreads = env_ll("BNL_GROUP_THREADS", 512);
 const long long kKnobGroupMinCols = env_ll("BNL_GROUP_MINCOLS", 3);
 const long long kKnobGroupWaves = env_ll("BNL_GROUP_WAVES", 1);
 const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
@@ -132,11 +131,11 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
-    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<512, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
-    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<512, 16384>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
-    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<384>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<512, 32768>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
@@ -214,7 +213,12 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       // one table stride for the whole launch (count_group_kernel): the largest table.
       for (auto &r : runs)
         for (int u = r.first; u < r.second; u++) gstride = std::max(gstride, dev.h_units[u].cells * 256);
-      const int fit = gstride > 0 ? std::min(BNL_GROUP_MAX, group_smem / gstride) : 0;
+      // rounded up to 16 or 32 KiB where possible: those strides are compiled in, which
+      // turns the table offset into an immediate of the atomics' address.
+      if (gstride > 0 && gstride <= 16384) gstride = 16384;
+      else if (gstride > 16384 && gstride <= 32768) gstride = 32768;
+      const bool small_block = (unsigned long long)ds.stride_u8 * (unsigned long long)ds.nd < (1ull << 35);
+      const int fit = gstride > 0 && small_block ? std::min(BNL_GROUP_MAX, group_smem / gstride) : 0;
       if (fit < 4) runs.clear();               // tables too large to share an SM usefully
       int best_u = std::min((int)kKnobGroupUnits, fit);
       if (!getenv("BNL_GROUP_UNITS") && !runs.empty()) {
@@ -331,13 +335,13 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       // collapsing the tables stays a small part of a CTA's life.
       int ch = (int)std::max(1ll, std::min(want, std::max(1ll, groups / (32 * 512))));
       const unsigned ggrid = (unsigned)tiles.size() * ch;
-#define BNL_GROUP_LAUNCH(NT)                                                                          \
-      count_group_kernel<NT><<<ggrid, NT, (size_t)smem, dev.stream>>>(                                  \
+#define BNL_GROUP_LAUNCH(TS)                                                                          \
+      count_group_kernel<512, TS><<<ggrid, 512, (size_t)smem, dev.stream>>>(                            \
           dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + n_ungrouped, dev.d_tiles, dev.d_tables, \
           (int)tiles.size(), ch, gstride)
-      if (kKnobGroupThreads == 1024) BNL_GROUP_LAUNCH(1024);
-      else if (kKnobGroupThreads == 384) BNL_GROUP_LAUNCH(384);
-      else BNL_GROUP_LAUNCH(512);
+      if (gstride == 16384) BNL_GROUP_LAUNCH(16384);
+      else if (gstride == 32768) BNL_GROUP_LAUNCH(32768);
+      else BNL_GROUP_LAUNCH(0);
 #undef BNL_GROUP_LAUNCH
       BNL_CUDA(ctx, cudaGetLastError());
       tm->launches++;

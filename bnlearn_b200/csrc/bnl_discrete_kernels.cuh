@@ -486,7 +486,7 @@ struct GroupRegs {
   uint4 cand[BNL_GROUP_MAX];
 };
 
-template <int NT>
+template <int NT, int TSTRIDE>
 __global__ void __launch_bounds__(NT)
 count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
@@ -497,8 +497,11 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   // the update is PRMT + ATOMS [R + UR] with no address add in between).
   extern __shared__ __align__(256) int hist[];
   __shared__ BnlUnit su;                               // first unit of the tile: the shared columns
-  __shared__ int s_col[BNL_GROUP_MAX], s_cells[BNL_GROUP_MAX];
+  __shared__ int s_cells[BNL_GROUP_MAX];
+  __shared__ unsigned s_q[BNL_GROUP_MAX], s_qb[BNL_GROUP_PB];   // column starts in 16-byte units
   __shared__ long long s_tab[BNL_GROUP_MAX];
+  if (TSTRIDE > 0) tstride = TSTRIDE;                    // compile-time stride: ATOMS [R + UR + imm]
+  const unsigned stride16 = (unsigned)(stride >> 4);
   const int chunk = blockIdx.x / ntiles;
   const int2 tile = tiles[blockIdx.x % ntiles];
   const int nu = tile.y;
@@ -507,11 +510,12 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
         reinterpret_cast<const int *>(&units[order[tile.x]])[threadIdx.x];
   if (threadIdx.x < nu) {
     const BnlUnit &uj = units[order[tile.x + threadIdx.x]];
-    s_col[threadIdx.x] = uj.col[uj.ncols - 1];
+    s_q[threadIdx.x] = (unsigned)uj.col[uj.ncols - 1] * stride16;
     s_cells[threadIdx.x] = uj.cells;
     s_tab[threadIdx.x] = uj.table_off;
   }
   __syncthreads();
+  if (threadIdx.x < BNL_GROUP_PB) s_qb[threadIdx.x] = (unsigned)su.col[threadIdx.x] * stride16;
   const int total_quads = (nu * tstride) >> 4;
   for (int c = threadIdx.x; c < total_quads; c += NT) reinterpret_cast<uint4 *>(hist)[c] = make_uint4(0, 0, 0, 0);
   __syncthreads();
@@ -526,13 +530,18 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   long long g1 = g0 + per;
   if (g1 > full) g1 = full;
 
+  // 32-bit offsets (16-byte units) from the start of the packed block: one add and
+  // one widening multiply-add per load instead of 64-bit pointer arithmetic per
+  // column and iteration (the host only groups when the block is below 64 GB).
+  const uint4 *base4 = reinterpret_cast<const uint4 *>(u8);
   auto load = [&](GroupRegs &R, long long g) {
+    const unsigned g32 = (unsigned)g;
 #pragma unroll
     for (int k = 0; k < BNL_GROUP_PB; k++)
-      if (k < npre) R.base[k] = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)su.col[k] * stride) + g);
+      if (k < npre) R.base[k] = ldg_stream(base4 + (s_qb[k] + g32));
 #pragma unroll
     for (int j = 0; j < BNL_GROUP_MAX; j++)
-      if (j < nu) R.cand[j] = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)s_col[j] * stride) + g);
+      if (j < nu) R.cand[j] = ldg_stream(base4 + (s_q[j] + g32));
   };
 
   GroupRegs cur, nxt;
@@ -571,7 +580,7 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     for (long long r = full * 16; r < nobs; r++) {
       int cell = 0;
       for (int k = 0; k < nbase; k++) cell += (int)u8[(size_t)su.col[k] * stride + (size_t)r] * su.mul[k];
-      cell += (int)u8[(size_t)s_col[j] * stride + (size_t)r] * (int)cmul;
+      cell += (int)u8[(size_t)s_q[j] * 16 + (size_t)r] * (int)cmul;
       atomicAdd(&tables[s_tab[j] + cell], 1);
     }
   }
