@@ -132,11 +132,11 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_small_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<512, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       dev.max_smem - 4096));
+                                       dev.max_smem - 1024));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<512, 16384>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       dev.max_smem - 4096));
+                                       dev.max_smem - 1024));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_group_kernel<512, 32768>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       dev.max_smem - 4096));
+                                       dev.max_smem - 1024));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     dev.attr_done = true;
@@ -180,7 +180,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     std::vector<int2> tiles;
     std::vector<int> gorder;
     int gstride = 0;
-    const int group_smem = dev.max_smem - 8192;
+    // seven 32 KiB tables must fit: the group kernel has ~0.5 KiB of static shared memory
+    const int group_smem = dev.max_smem - 1024;
     // Score requests only: on pc.stable's mixed test batches (many tiny tables that
     // count row pairs, 29 units per distinct column kept hot in L2) the extra launch
     // and the lost pair mode cost more than the shared loads save (config B: 2.58 ms
