@@ -23,8 +23,12 @@ const long long kKnobL2MB = env_ll("BNL_L2_MB", 192);
 const int kKnobMidThreads = (int)env_ll("BNL_MID_THREADS", 1024);
 const long long kKnobGroup = env_ll("BNL_GROUP", 1);
 const long long kKnobGroupMinCols = env_ll("BNL_GROUP_MINCOLS", 3);
-const long long kKnobGroupWaves = env_ll("BNL_GROUP_WAVES", 1);
+const long long kKnobGroupWaves = env_ll("BNL_GROUP_WAVES", 0);   // 0: pick row chunks by the cost model
 const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
+const long long kKnobBased = env_ll("BNL_BASED", 1);
+const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
+const long long kKnobBasedWaves = env_ll("BNL_BASED_WAVES", 0);
+const size_t kMaxBaseScratch = (size_t)1 << 30;   // bytes of base-index columns per launch
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
 const int kMaxBatchUnits = 1 << 16;
@@ -139,6 +143,14 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                        dev.max_smem - 1024));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 4, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<4, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<3, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
     dev.attr_done = true;
   }
   const int smem_cap_cells = (dev.max_smem - 8192) / 4;
@@ -177,6 +189,18 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     // last (score_cache_fill's candidates of one node), small tables, no NA. They
     // are cut into tiles of up to BNL_GROUP_MAX units whose tables fit one SM.
     std::vector<char> grouped(cnt, 0);
+    std::vector<std::vector<int>> runs, bruns;
+    // base-column classes: counters per cell / units per tile (count_based_kernel)
+    const int kBasedClasses = 5;
+    const int based_cap[kBasedClasses] = {(dev.max_smem - 8192) / 128 / 4, (dev.max_smem - 8192) / 128 / 2,
+                                          (dev.max_smem - 8192) / 128, (dev.max_smem - 8192) / 64,
+                                          (dev.max_smem - 8192) / 32};
+    const int based_nu[kBasedClasses] = {4, 2, 1, 1, 1};
+    std::vector<int> bcls[kBasedClasses], based_run(cnt, -1);
+    std::vector<int2> btiles[kBasedClasses];
+    int bmax[kBasedClasses] = {0, 0, 0, 0, 0};
+    const size_t bstride = (size_t)((ds.nobs + 15) / 16) * 16 + 128;   // uint16 elements per base column
+    const size_t brun_bytes = bstride * sizeof(uint16_t);
     std::vector<int2> tiles;
     std::vector<int> gorder;
     int gstride = 0;
@@ -186,6 +210,22 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     // count row pairs, 29 units per distinct column kept hot in L2) the extra launch
     // and the lost pair mode cost more than the shared loads save (config B: 2.58 ms
     // ungrouped, 2.64-2.79 ms grouped).
+    // Row chunks of the one-CTA-per-SM kernels: nt tiles of `upt` units each are cut
+    // into ch chunks; the launch takes waves x (tile time / ch + fixed cost of a CTA:
+    // clearing and collapsing ~200 KB of tables, ~4 us). 166 tiles in one chunk would
+    // run as two waves, the second with 18 CTAs.
+    auto model_chunks = [&](long long nt, double upt, long long maxch, double *cost) {
+      const double unit_us = (double)ds.nobs / 25e3, fixed_us = 4.0;    // ~25 G row-units/s per SM
+      long long best = 1;
+      double bc = 1e300;
+      for (long long ch = 1; ch <= std::max(1ll, maxch); ch++) {
+        const long long waves = (nt * ch + dev.sm_count - 1) / dev.sm_count;
+        const double c = (double)waves * (upt * unit_us / (double)ch + fixed_us);
+        if (c < bc) { bc = c; best = ch; }
+      }
+      if (cost) *cost = bc;
+      return best;
+    };
     if (kKnobGroup && rq.kind == 1 && ds.nobs >= 65536) {
       auto same_base = [&](const BnlUnit &a, const BnlUnit &b) {
         // at least two shared columns (a node with one or more parents): for
@@ -196,16 +236,26 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           if (a.col[k] != b.col[k] || a.mul[k] != b.mul[k]) return false;
         return a.mul[a.ncols - 1] == b.mul[b.ncols - 1];
       };
-      // runs of units with the same base columns
-      std::vector<std::pair<int, int>> runs;
+      // maximal runs of consecutive units with the same base columns; inside a run
+      // the small tables (at least four of them per SM) go to the group kernel, the
+      // mid-size ones to the base-column kernel (count_based_kernel).
+      const int gcap = group_smem / (4 * 256);
+      const int bcap = based_cap[kBasedClasses - 1];       // 8 lane counters per cell
       int i = 0;
       while (i < cnt) {
         int j = i + 1;
-        // tables small enough for at least four of them (at the launch-wide stride) per SM
-        const int gcap = group_smem / (4 * 256);
-        while (j < cnt && dev.h_units[j].cells <= gcap && dev.h_units[i].cells <= gcap &&
-               same_base(dev.h_units[i], dev.h_units[j])) j++;
-        if (j - i >= 4) runs.push_back(std::make_pair(i, j));
+        while (j < cnt && same_base(dev.h_units[i], dev.h_units[j])) j++;
+        if (j - i >= 4) {
+          std::vector<int> small, big;
+          for (int u = i; u < j; u++) {
+            const BnlUnit &hu = dev.h_units[u];
+            if (hu.cells <= gcap) small.push_back(u);
+            else if (kKnobBased && hu.ncols >= kKnobBasedMinCols && hu.cells <= bcap) big.push_back(u);
+          }
+          if (small.size() >= 4) runs.push_back(std::move(small));
+          // the base-index column costs 2 bytes per row of scratch and one extra pass
+          if (big.size() >= 4 && (bruns.size() + 1) * brun_bytes <= kMaxBaseScratch) bruns.push_back(std::move(big));
+        }
         i = j;
       }
       // units per tile: more units share more loads, but the CTAs (tiles x row
@@ -213,7 +263,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       // candidates make 125 tiles of 8 (84 % of 148 SMs) or 143 tiles of 7 (97 %).
       // one table stride for the whole launch (count_group_kernel): the largest table.
       for (auto &r : runs)
-        for (int u = r.first; u < r.second; u++) gstride = std::max(gstride, dev.h_units[u].cells * 256);
+        for (int u : r) gstride = std::max(gstride, dev.h_units[u].cells * 256);
       // rounded up to 16 or 32 KiB where possible: those strides are compiled in, which
       // turns the table offset into an immediate of the atomics' address.
       if (gstride > 0 && gstride <= 16384) gstride = 16384;
@@ -226,30 +276,54 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         double best_cost = 1e300;
         for (int u = fit; u >= std::min(fit, 5); u--) {
           long long nt = 0;
-          for (auto &r : runs) nt += (r.second - r.first + u - 1) / u;
-          const long long ch = std::max(1ll, (kKnobGroupWaves * dev.sm_count + nt / 2) / nt);
-          const long long ctas = nt * ch;
-          const double eff = (double)ctas / (double)(((ctas + dev.sm_count - 1) / dev.sm_count) * dev.sm_count);
-          const double cost = (1.0 + 0.08 * (double)(BNL_GROUP_MAX - u)) / eff;
+          for (auto &r : runs) nt += ((long long)r.size() + u - 1) / u;
+          double cost;
+          if (kKnobGroupWaves) {
+            const long long ch = std::max(1ll, (kKnobGroupWaves * dev.sm_count + nt / 2) / nt);
+            const long long ctas = nt * ch;
+            const double eff = (double)ctas / (double)(((ctas + dev.sm_count - 1) / dev.sm_count) * dev.sm_count);
+            cost = (1.0 + 0.08 * (double)(BNL_GROUP_MAX - u)) / eff;
+          } else {
+            // fewer units per tile: the shared columns are loaded more often per unit
+            model_chunks(nt, (double)u * (1.0 + 0.08 * (double)(BNL_GROUP_MAX - u)), std::max(1ll, groups / (32 * 512)), &cost);
+          }
           if (cost < best_cost) { best_cost = cost; best_u = u; }
         }
       }
       for (auto &r : runs) {
-        int t0 = r.first;
-        const int j = r.second;
-        while (t0 < j) {
-          const int t1 = std::min(j, t0 + best_u);
-          tiles.push_back(make_int2((int)gorder.size(), t1 - t0));
-          for (int u = t0; u < t1; u++) { gorder.push_back(u); grouped[u] = 1; }
+        size_t t0 = 0;
+        while (t0 < r.size()) {
+          const size_t t1 = std::min(r.size(), t0 + (size_t)best_u);
+          tiles.push_back(make_int2((int)gorder.size(), (int)(t1 - t0)));
+          for (size_t q = t0; q < t1; q++) { gorder.push_back(r[q]); grouped[r[q]] = 1; }
           t0 = t1;
         }
+      }
+      // base-column runs: per class, tiles of units of one run
+      for (size_t r = 0; r < bruns.size(); r++) {
+        std::vector<int> members[kBasedClasses];
+        for (int u : bruns[r]) {
+          const int c = dev.h_units[u].cells;
+          int k = 0;
+          while (c > based_cap[k]) k++;
+          members[k].push_back(u);
+          bmax[k] = std::max(bmax[k], c);
+          grouped[u] = 2;
+          based_run[u] = (int)r;
+        }
+        for (int k = 0; k < kBasedClasses; k++)
+          for (size_t t0 = 0; t0 < members[k].size(); t0 += based_nu[k]) {
+            const size_t t1 = std::min(members[k].size(), t0 + (size_t)based_nu[k]);
+            btiles[k].push_back(make_int2((int)bcls[k].size(), (int)(t1 - t0)));
+            for (size_t q = t0; q < t1; q++) bcls[k].push_back(members[k][q]);
+          }
       }
     }
     std::vector<int> cls[4];
     int cmax[4] = {0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
       BnlUnit &hu = dev.h_units[i];
-      hu.mode = 0;
+      hu.mode = grouped[i] == 2 ? 16 + based_run[i] : 0;   // base-column units name their run
       if (grouped[i]) continue;
       const int c = hu.cells;
       // a unit with a uint16 column is counted by the generic kernel, whatever its size
@@ -278,7 +352,16 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
       n_ungrouped = o;
       for (int i : gorder) dev.h_order[o++] = i;       // group members follow, in tile order
+      for (int k = 0; k < kBasedClasses; k++) for (int i : bcls[k]) dev.h_order[o++] = i;   // then the base-column classes
     }
+    if (!bruns.empty()) {
+      if ((rc = bnl_reserve_pinned(ctx, &dev.h_runfirst, &dev.h_runfirst_cap, bruns.size()))) return rc;
+      if ((rc = bnl_reserve_device(ctx, &dev.d_runfirst, &dev.runfirst_cap, bruns.size()))) return rc;
+      if ((rc = bnl_reserve_device(ctx, &dev.d_basecols, &dev.basecols_cap, bruns.size() * bstride))) return rc;
+      for (size_t r = 0; r < bruns.size(); r++) dev.h_runfirst[r] = bruns[r][0];
+    }
+    const size_t ngtiles = tiles.size();
+    for (int k = 0; k < kBasedClasses; k++) tiles.insert(tiles.end(), btiles[k].begin(), btiles[k].end());
     if (!tiles.empty()) {
       if ((rc = bnl_reserve_pinned(ctx, &dev.h_tiles, &dev.h_tiles_cap, tiles.size()))) return rc;
       if ((rc = bnl_reserve_device(ctx, &dev.d_tiles, &dev.tiles_cap, tiles.size()))) return rc;
@@ -323,23 +406,62 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     if (!tiles.empty())
       BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_tiles, dev.h_tiles, tiles.size() * sizeof(int2),
                                     cudaMemcpyHostToDevice, dev.stream));
+    if (!bruns.empty())
+      BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_runfirst, dev.h_runfirst, bruns.size() * sizeof(int),
+                                    cudaMemcpyHostToDevice, dev.stream));
     BNL_CUDA(ctx, cudaMemsetAsync(dev.d_tables, 0, (size_t)cells * sizeof(int), dev.stream));
     BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
-    if (groups > 0 && !tiles.empty()) {
+    if (groups > 0 && !bruns.empty()) {
+      // base indices of every run (complete 16-row groups), then one launch per class
+      const long long full = ds.nobs / 16;
+      const unsigned bx = (unsigned)std::max(1ll, std::min<long long>((full + 255) / 256,
+                                                                    (4ll * dev.sm_count * 8 + (long long)bruns.size() - 1) /
+                                                                        (long long)bruns.size()));
+      combine_base_kernel<<<dim3(bx, (unsigned)bruns.size()), 256, 0, dev.stream>>>(
+          dd.u8, ds.stride_u8, full, dev.d_units, dev.d_runfirst, dev.d_basecols, bstride);
+      BNL_CUDA(ctx, cudaGetLastError());
+      tm->launches++;
+      int bbase = n_ungrouped + (int)gorder.size();
+      size_t tbase = ngtiles;
+#define BNL_BASED_LAUNCH(K, LC, NU, NT)                                                                       \
+      if (!bcls[K].empty()) {                                                                                  \
+        const long long nt = (long long)btiles[K].size();                                                      \
+        long long ch = kKnobBasedWaves ? std::max(1ll, (kKnobBasedWaves * dev.sm_count + nt / 2) / nt)         \
+                                       : model_chunks(nt, (double)bcls[K].size() / (double)nt * 1.5,           \
+                                                      ds.nobs / 131072, nullptr);                              \
+        ch = std::max(1ll, std::min(ch, std::max(1ll, ds.nobs / 131072)));                                     \
+        const int ts = ((bmax[K] << (LC + 2)) + 255) & ~255;                                                   \
+        count_based_kernel<LC, NU, NT><<<(unsigned)(nt * ch), NT, (size_t)ts * based_nu[K], dev.stream>>>(      \
+            dd.u8, ds.stride_u8, ds.nobs, dev.d_basecols, bstride, dev.d_units, dev.d_order + bbase,           \
+            dev.d_tiles + tbase, dev.d_tables, (int)nt, (int)ch, ts);                                          \
+        BNL_CUDA(ctx, cudaGetLastError());                                                                     \
+        tm->launches++;                                                                                        \
+        bbase += (int)bcls[K].size();                                                                          \
+        tbase += btiles[K].size();                                                                             \
+      }
+      BNL_BASED_LAUNCH(0, 5, 4, 512)
+      BNL_BASED_LAUNCH(1, 5, 4, 512)
+      BNL_BASED_LAUNCH(2, 5, 1, 1024)
+      BNL_BASED_LAUNCH(3, 4, 1, 1024)
+      BNL_BASED_LAUNCH(4, 3, 1, 1024)
+#undef BNL_BASED_LAUNCH
+    }
+    if (groups > 0 && ngtiles > 0) {
       // one CTA per SM (its tables fill the shared memory): ~8 waves of CTAs.
       int smem = 0;
-      for (const int2 &t : tiles) smem = std::max(smem, t.y * gstride);
-      const long long nt = (long long)tiles.size();
-      long long want = std::max(1ll, (kKnobGroupWaves * dev.sm_count + nt / 2) / nt);
+      for (size_t t = 0; t < ngtiles; t++) smem = std::max(smem, tiles[t].y * gstride);
+      const long long nt = (long long)ngtiles;
+      long long want = kKnobGroupWaves ? std::max(1ll, (kKnobGroupWaves * dev.sm_count + nt / 2) / nt)
+                                       : model_chunks(nt, (double)gorder.size() / (double)nt, groups / (32 * 512), nullptr);
       if (kKnobChunkRows) want = (ds.nobs + kKnobChunkRows - 1) / kKnobChunkRows;
       // at least 32 groups of 16 rows per thread-pass and chunk, so that clearing and
       // collapsing the tables stays a small part of a CTA's life.
       int ch = (int)std::max(1ll, std::min(want, std::max(1ll, groups / (32 * 512))));
-      const unsigned ggrid = (unsigned)tiles.size() * ch;
+      const unsigned ggrid = (unsigned)ngtiles * ch;
 #define BNL_GROUP_LAUNCH(TS)                                                                          \
       count_group_kernel<512, TS><<<ggrid, 512, (size_t)smem, dev.stream>>>(                            \
           dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + n_ungrouped, dev.d_tiles, dev.d_tables, \
-          (int)tiles.size(), ch, gstride)
+          (int)ngtiles, ch, gstride)
       if (gstride == 16384) BNL_GROUP_LAUNCH(16384);
       else if (gstride == 32768) BNL_GROUP_LAUNCH(32768);
       else BNL_GROUP_LAUNCH(0);

@@ -598,6 +598,170 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 }
 
 // ---------------------------------------------------------------------------
+// Candidate runs with mid-size tables (a node that already has 2-5 parents: 257
+// to ~7000 cells). The tables are too large to share an SM, so the group kernel
+// above does not apply and every unit would re-read its 4-8 columns through L2.
+// Instead the shared columns are combined ONCE per run into a uint16 column of
+// base indices (the reference does the same for a test's conditioning set:
+// src/tests/patterns/ctest.c:18-19 forms the configuration of Z once for all x),
+// and each candidate becomes a two-column unit: 3 bytes per row instead of
+// ncols, one PRMT + IMAD per two rows of index arithmetic.
+__global__ void __launch_bounds__(256)
+combine_base_kernel(const uint8_t *__restrict__ u8, size_t stride, long long full,
+                    const BnlUnit *__restrict__ units, const int *__restrict__ run_first,
+                    uint16_t *__restrict__ basecols, size_t bstride) {
+  __shared__ int s_col[BNL_MAXK], s_mul[BNL_MAXK];
+  __shared__ int s_nbase;
+  const BnlUnit &un = units[run_first[blockIdx.y]];
+  if (threadIdx.x == 0) s_nbase = un.ncols - 1;
+  if (threadIdx.x < BNL_MAXK) { s_col[threadIdx.x] = un.col[threadIdx.x]; s_mul[threadIdx.x] = un.mul[threadIdx.x]; }
+  __syncthreads();
+  const int nbase = s_nbase;
+  uint4 *out = reinterpret_cast<uint4 *>(basecols + (size_t)blockIdx.y * bstride);
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < full;
+       g += (long long)gridDim.x * blockDim.x) {
+    unsigned v[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) v[j] = 0u;
+    for (int k = 0; k < nbase; k++) {
+      const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)s_col[k] * stride) + g);
+      const unsigned m = (unsigned)s_mul[k];
+      const unsigned ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        v[2 * q] += __byte_perm(ww[q], 0, 0x4140) * m;
+        v[2 * q + 1] += __byte_perm(ww[q], 0, 0x4342) * m;
+      }
+    }
+    out[2 * g] = make_uint4(v[0], v[1], v[2], v[3]);
+    out[2 * g + 1] = make_uint4(v[4], v[5], v[6], v[7]);
+  }
+}
+
+// LC = log2 of the lane counters per cell: 5 (one counter per lane, no bank
+// collisions; <= ~1780 cells), 4 or 3 (<= ~7000 cells; lanes 16 or 8 apart then
+// share a counter, still far fewer collisions than one shared table). A CTA takes
+// a tile of up to NUMAX units of one run (tables of <= ~445 cells: four per SM,
+// <= ~890: two), so the base column is loaded once per tile: (2 + nu) / nu bytes
+// per row-unit through L2. tiles[] = {first position in `order`, units}.
+#define BNL_BASED_MAX 4
+
+template <int LC>
+__device__ __forceinline__ void based_bump(int *hist, unsigned v, unsigned slot4) {
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + (((v & 0xFFFFu) << (LC + 2)) + slot4)), 1);
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + (((v >> 16) << (LC + 2)) + slot4)), 1);
+}
+
+template <int NUMAX>
+struct BasedRegs { uint4 b0, b1, c[NUMAX]; };
+
+// NT threads; the loads of the next TWO 16-row groups are in flight while the
+// current one is counted (one CTA per SM: nothing else hides the round trip, and
+// one group ahead left the kernel latency-bound at 40 GB/s per SM).
+template <int LC, int NUMAX, int NT>
+__global__ void __launch_bounds__(NT)
+count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
+                   const uint16_t *__restrict__ basecols, size_t bstride,
+                   const BnlUnit *__restrict__ units, const int *__restrict__ order,
+                   const int2 *__restrict__ tiles, int *__restrict__ tables, int ntiles, int chunks,
+                   int tstride) {
+  extern __shared__ __align__(256) int hist[];        // unit j: tstride bytes from j * tstride
+  __shared__ BnlUnit su;                               // first unit of the tile: run, shared columns
+  __shared__ int s_cells[BNL_BASED_MAX], s_col[BNL_BASED_MAX];
+  __shared__ long long s_tab[BNL_BASED_MAX];
+  const int chunk = blockIdx.x / ntiles;
+  const int2 tile = tiles[blockIdx.x % ntiles];
+  const int nu = NUMAX == 1 ? 1 : tile.y;
+  if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
+    reinterpret_cast<int *>(&su)[threadIdx.x] =
+        reinterpret_cast<const int *>(&units[order[tile.x]])[threadIdx.x];
+  if (threadIdx.x < nu) {
+    const BnlUnit &uj = units[order[tile.x + threadIdx.x]];
+    s_col[threadIdx.x] = uj.col[uj.ncols - 1];
+    s_cells[threadIdx.x] = uj.cells;
+    s_tab[threadIdx.x] = uj.table_off;
+  }
+  __syncthreads();
+  const int quads = (nu * tstride) >> 4;
+  for (int c = threadIdx.x; c < quads; c += NT) reinterpret_cast<uint4 *>(hist)[c] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  const unsigned slot4 = (threadIdx.x & ((1u << LC) - 1u)) << 2;
+  const int last = su.ncols - 1;
+  const unsigned cmul = (unsigned)su.mul[last];
+  const uint4 *bp = reinterpret_cast<const uint4 *>(basecols + (size_t)(su.mode - 16) * bstride);
+  const uint4 *cp[NUMAX];
+#pragma unroll
+  for (int j = 0; j < NUMAX; j++)
+    cp[j] = reinterpret_cast<const uint4 *>(u8 + (size_t)s_col[j < nu ? j : 0] * stride);
+
+  const long long full = nobs / 16;
+  const long long per = (full + chunks - 1) / chunks;
+  const long long g0 = per * chunk;
+  long long g1 = g0 + per;
+  if (g1 > full) g1 = full;
+
+  auto load = [&](BasedRegs<NUMAX> &R, long long g) {
+    R.b0 = ldg_stream(bp + 2 * g);
+    R.b1 = ldg_stream(bp + 2 * g + 1);
+#pragma unroll
+    for (int j = 0; j < NUMAX; j++)
+      if (j < nu) R.c[j] = ldg_stream(cp[j] + g);
+  };
+  auto count = [&](const BasedRegs<NUMAX> &R) {
+    const unsigned bw[8] = {R.b0.x, R.b0.y, R.b0.z, R.b0.w, R.b1.x, R.b1.y, R.b1.z, R.b1.w};
+#pragma unroll
+    for (int j = 0; j < NUMAX; j++)
+      if (j < nu) {
+        int *hj = reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + j * tstride);
+        const unsigned cw[4] = {R.c[j].x, R.c[j].y, R.c[j].z, R.c[j].w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          based_bump<LC>(hj, bw[2 * q] + __byte_perm(cw[q], 0, 0x4140) * cmul, slot4);
+          based_bump<LC>(hj, bw[2 * q + 1] + __byte_perm(cw[q], 0, 0x4342) * cmul, slot4);
+        }
+      }
+  };
+  BasedRegs<NUMAX> r0, r1, r2;
+  long long g = g0 + threadIdx.x;
+  if (g < g1) load(r0, g);
+  if (g + NT < g1) load(r1, g + NT);
+#define BNL_BASED_STEP(A, C)                  \
+  if (g < g1) {                               \
+    if (g + 2 * NT < g1) load(C, g + 2 * NT); \
+    count(A);                                 \
+    g += NT;                                  \
+  }
+  while (g < g1) {
+    BNL_BASED_STEP(r0, r2)
+    BNL_BASED_STEP(r1, r0)
+    BNL_BASED_STEP(r2, r1)
+  }
+#undef BNL_BASED_STEP
+  // the partial group at the end of the data, once, from the original columns.
+  if (chunk == chunks - 1 && threadIdx.x < nu && full * 16 < nobs) {
+    const int j = threadIdx.x;
+    for (long long r = full * 16; r < nobs; r++) {
+      int cell = 0;
+      for (int k = 0; k < last; k++) cell += (int)u8[(size_t)su.col[k] * stride + (size_t)r] * su.mul[k];
+      cell += (int)u8[(size_t)s_col[j] * stride + (size_t)r] * (int)cmul;
+      atomicAdd(&tables[s_tab[j] + cell], 1);
+    }
+  }
+  __syncthreads();
+  constexpr int NCNT = 1 << LC;
+  for (int j = 0; j < nu; j++) {
+    const int *hj = reinterpret_cast<const int *>(reinterpret_cast<const char *>(hist) + j * tstride);
+    int *gtab = tables + s_tab[j];
+    for (int c = threadIdx.x; c < s_cells[j]; c += NT) {
+      int sum = 0;
+#pragma unroll
+      for (int l = 0; l < NCNT; l++) sum += hj[c * NCNT + ((l + threadIdx.x) & (NCNT - 1))];
+      if (sum) atomicAdd(&gtab[c], sum);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // Epilogue. kind 0: CI test (code = test_e); kind 1: node score (code = score_e).
 // One CTA per unit, one warp per stratum (configuration of Z / of the parents).
 

@@ -49,6 +49,9 @@ struct BnlDevice {
   int *h_order = nullptr; size_t h_order_cap = 0;        // pinned
   int2 *d_tiles = nullptr; size_t tiles_cap = 0;         // candidate-group tiles
   int2 *h_tiles = nullptr; size_t h_tiles_cap = 0;       // pinned
+  uint16_t *d_basecols = nullptr; size_t basecols_cap = 0;  // base-index columns of candidate runs (count_based_kernel)
+  int *d_runfirst = nullptr; size_t runfirst_cap = 0;    // first unit of each such run
+  int *h_runfirst = nullptr; size_t h_runfirst_cap = 0;  // pinned
   BnlUnit *h_units = nullptr; size_t h_units_cap = 0;    // pinned
   double *h_out = nullptr; size_t h_out_cap = 0;         // pinned
   int *h_gidx = nullptr; size_t h_gidx_cap = 0;          // pinned

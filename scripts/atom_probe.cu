@@ -9,6 +9,9 @@
 #include <cstdlib>
 #include <cuda_runtime.h>
 
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
+    printf("%s failed: %s\n", #call, cudaGetErrorString(e_)); exit(1); } } while (0)
+
 template <int MODE>
 __global__ void __launch_bounds__(256) probe(int cells, int iters, int words, unsigned *sink) {
   extern __shared__ unsigned tab[];
@@ -46,8 +49,6 @@ void run(const char *name, int cells, int ctas_per_sm) {
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
   const int iters = 4096;
   const size_t smem = (size_t)cells * 64 * 4 * (MODE == 0 ? 1 : (MODE == 1 ? 4 : 2));
-#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
-    printf("%s failed: %s\n", #call, cudaGetErrorString(e_)); exit(1); } } while (0)
   CK(cudaFuncSetAttribute(probe<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   unsigned *sink = nullptr;
   CK(cudaMalloc(&sink, 4));
@@ -70,7 +71,69 @@ void run(const char *name, int cells, int ctas_per_sm) {
   cudaFree(sink);
 }
 
-int main() {
+// (D) address span: one CTA of NT threads per SM, a table of `cells` cells with
+// (1 << LC) lane counters each, random cells. Same-bank collisions cannot happen
+// for LC >= 5; what changes with `cells` is only how far apart the 32 addresses of
+// one warp-wide atomic lie.
+template <int LC, int NT>
+__global__ void __launch_bounds__(NT) span_probe(int cells, int iters, int words, unsigned *sink) {
+  extern __shared__ unsigned tab[];
+  for (int i = threadIdx.x; i < words; i += NT) tab[i] = 0;
+  __syncthreads();
+  unsigned s = threadIdx.x * 2654435761u + blockIdx.x;
+  const unsigned slot4 = (LC == 6 ? (threadIdx.x & 31u) + 32u * ((threadIdx.x >> 5) & 1u) : threadIdx.x & ((1u << LC) - 1u)) << 2;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+      // full-rate instructions only (IMAD.HI would cap the loop at ~13 lanes/clk/SM)
+      s = s * 1664525u + 1013904223u;
+      const unsigned u = __byte_perm(s, 0, 0x4432) * (unsigned)cells;       // (s >> 16) * cells
+      const unsigned off = ((u >> (14 - LC)) & (0xFFFFFFFFu << (LC + 2))) | slot4;
+      atomicAdd(reinterpret_cast<unsigned *>(reinterpret_cast<char *>(tab) + off), 1u);
+    }
+  }
+  __syncthreads();
+  unsigned acc = 0;
+  for (int i = threadIdx.x; i < words; i += NT) acc += tab[i];
+  if (acc == 0xdeadbeef) sink[0] = acc;
+}
+
+template <int LC, int NT>
+void run_span(int cells) {
+  int sms = 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+  const int iters = 2048;
+  const size_t smem = ((size_t)cells << LC) * 4;
+  if (smem > 226 * 1024) return;
+  CK(cudaFuncSetAttribute(span_probe<LC, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  unsigned *sink = nullptr;
+  CK(cudaMalloc(&sink, 4));
+  const int words = (int)(smem / 4);
+  span_probe<LC, NT><<<sms, NT, smem>>>(cells, 16, words, sink);
+  CK(cudaDeviceSynchronize());
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0);
+  span_probe<LC, NT><<<sms, NT, smem>>>(cells, iters, words, sink);
+  cudaEventRecord(e1);
+  CK(cudaEventSynchronize(e1));
+  float ms = 0;
+  CK(cudaEventElapsedTime(&ms, e0, e1));
+  const double updates = (double)sms * NT * iters * 16;
+  printf("span: %2d counters/cell %4d threads cells %5d table %7zu B: %8.3f ms  %.2f T updates/s\n", 1 << LC, NT, cells,
+         smem, ms, updates / ms / 1e9);
+  cudaFree(sink);
+}
+
+int main(int argc, char **argv) {
+  if (argc > 1) {
+    for (int cells : {32, 64, 128, 256, 384, 512, 768, 880}) run_span<6, 1024>(cells);
+    for (int cells : {64, 128, 256, 512, 768, 1024, 1400, 1750}) run_span<5, 1024>(cells);
+    for (int cells : {256, 512, 1024, 2048, 3500}) run_span<4, 1024>(cells);
+    for (int cells : {512, 1024, 2048, 4096, 7000}) run_span<3, 1024>(cells);
+    for (int cells : {256, 1024, 1750}) run_span<5, 512>(cells);
+    return 0;
+  }
   for (int cells : {16, 64, 128}) {
     for (int c : {2, 4, 8}) {
       run<0>("atomics, 4 warps per slot", cells, c);

@@ -476,6 +476,38 @@ def test_every_table_size_class(engine, with_na):
     d.release()
 
 
+def test_candidate_runs_with_mid_size_tables(engine):
+    """score_cache_fill's batch for a node that already has 2-3 parents: the
+    candidates share every column but the last, and their tables (240-3600 cells)
+    are too large for several to share an SM. Such runs go through the base-index
+    column (count_based_kernel, every counters-per-cell class); tables that stay
+    small go to the group kernel and a short run to the per-unit kernels. Ragged
+    row count, scores against the oracle."""
+    from oracle import oracle as orc
+    rng = np.random.default_rng(23)
+    n = 70003
+    lev = [3, 4, 5, 5, 2, 3, 4, 5, 6, 7, 9, 12, 4, 5, 6, 7, 3, 2]
+    cols = [rng.integers(1, l + 1, n).astype(np.int32) for l in lev]
+    # some dependence, so that the tables are not flat
+    cols[6] = ((cols[0] + cols[1] + rng.integers(0, 2, n)) % lev[6] + 1).astype(np.int32)
+    d = engine.register(cols, lev)
+    targets, parents = [], []
+    for base in ([1, 2], [1, 2, 3]):          # 60 and 300 base cells
+        for c in range(4, 18):
+            targets.append(0)
+            parents.append(base + [c])
+    for c in (4, 5, 6):                       # a run of three: too short, per-unit kernels
+        targets.append(1)
+        parents.append([2, 3, c])
+    for score, arg in (("loglik", 0.0), ("bde", 1.0)):
+        got, npar = d.score_discrete(score, targets, parents, arg)
+        for i, (t, pa) in enumerate(zip(targets, parents)):
+            ref, _ = orc.score_discrete(score, cols[t], lev[t], [cols[j] for j in pa], [lev[j] for j in pa], arg)
+            assert npar[i] == (lev[t] - 1) * int(np.prod([lev[j] for j in pa]))
+            _check(got[i], ref, (score, t, pa))
+    d.release()
+
+
 def test_multi_device_context_gives_identical_results():
     """A context on two devices splits the units in contiguous blocks; outputs must
     not change by a bit."""
