@@ -34,6 +34,14 @@ SIGNATURES = {
                                   c_int_p, c_int_p, c_dbl_p, c_dbl_p, c_dbl_p]),
     "bnl_ci_gaussian": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, c_int_p, c_int_p,
                                   c_int_p, c_int_p, c_dbl_p, c_dbl_p, c_dbl_p]),
+    "bnl_unif_splitmix64": (C.c_double, [C.c_void_p]),
+    "bnl_mc_from_tables": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, c_int_p, c_int_p, c_int_p,
+                                     c_i32_p, c_i64_p, C.c_void_p, C.c_void_p, c_dbl_p, c_dbl_p, c_dbl_p]),
+    "bnl_ci_gaussian_mc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_double, C.c_int, c_int_p,
+                                     c_int_p, c_int_p, c_int_p, C.c_void_p, C.c_void_p, c_dbl_p, c_dbl_p]),
+    "bnl_ci_discrete_mc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_double, C.c_int, c_int_p,
+                                     c_int_p, c_int_p, c_int_p, C.c_void_p, C.c_void_p, c_dbl_p, c_dbl_p,
+                                     c_dbl_p]),
     "bnl_score_gaussian": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p,
                                      c_int_p, c_int_p, c_dbl_p, c_dbl_p]),
     "bnl_gaussian_moments": (C.c_int, [C.c_void_p, C.c_uint64, c_dbl_p, c_dbl_p]),

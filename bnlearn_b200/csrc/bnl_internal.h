@@ -112,6 +112,7 @@ struct bnl_ctx {
   std::mutex err_mutex;
   double last_ms = 0.0, last_count_ms = 0.0, last_epi_ms = 0.0;
   int last_launches = 0;
+  std::vector<double> mc_fact;            // log(k!) for the permutation tests, grown on demand
 };
 
 int bnl_fail(bnl_ctx *ctx, int code, const char *fmt, ...);

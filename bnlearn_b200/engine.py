@@ -15,6 +15,8 @@ TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor
 SCORES = {"loglik": 1, "aic": 3, "bic": 4, "ebic": 5, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103, "ebic-g": 104, "bge": 105, "nal-g": 106, "pnal-g": 107,
           "loglik-cg": 200, "aic-cg": 202, "bic-cg": 203, "ebic-cg": 204}
+MC_TESTS = {"mc-mi": 50, "mc-x2": 51, "sp-mi": 52, "sp-x2": 53, "mc-jt": 54, "smc-mi": 60, "smc-x2": 61,
+            "smc-jt": 62, "mc-cor": 70, "mc-mi-g": 71, "mc-zf": 72, "smc-cor": 80, "smc-mi-g": 81, "smc-zf": 82}
 DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf", "jt", "mi-sh")
 GAUSSIAN_TESTS = ("cor", "zf", "mi-g", "mi-g-sh")
 DISCRETE_SCORES = ("loglik", "aic", "bic", "ebic", "bde", "bds", "bdj", "k2", "fnml", "qnml", "nal", "pnal")
@@ -222,6 +224,46 @@ class DataSet:
         e._check(e._lib.bnl_ci_discrete(e._ctx, self.handle, TESTS[test], n, _ip(x), _ip(y), _ip(zo),
                                         _ip(zi), _dp(st), _dp(df), _dp(pv)))
         return st[:n], df[:n], pv[:n]
+
+    def _unif(self, seed, unif):
+        """(function pointer, state pointer, keep-alive) of the uniform stream: a
+        ctypes callback `unif(state) -> float`, or the library's splitmix64 on `seed`."""
+        lib = self.engine._lib
+        if unif is not None:
+            cb = C.CFUNCTYPE(C.c_double, C.c_void_p)(unif)
+            return C.cast(cb, C.c_void_p), None, cb
+        state = C.c_uint64(int(seed))
+        return C.cast(lib.bnl_unif_splitmix64, C.c_void_p), C.cast(C.pointer(state), C.c_void_p), state
+
+    def ci_discrete_mc(self, test, x, y, z, B, alpha=1.0, seed=1, unif=None):
+        """Batch of discrete permutation / semiparametric tests -> (statistic, df,
+        p.value); the uniform stream is `unif` (a Python callable taking the state
+        pointer) or splitmix64 seeded with `seed`, consumed test after test."""
+        e = self.engine
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        zo, zi = _as_csr(z)
+        n = len(x)
+        st, df, pv = (np.zeros(max(n, 1)) for _ in range(3))
+        fn, state, keep = self._unif(seed, unif)
+        e._check(e._lib.bnl_ci_discrete_mc(e._ctx, self.handle, MC_TESTS[test], int(B), float(alpha), n, _ip(x),
+                                           _ip(y), _ip(zo), _ip(zi), fn, state, _dp(st), _dp(df), _dp(pv)))
+        del keep
+        return st[:n], df[:n], pv[:n]
+
+    def ci_gaussian_mc(self, test, x, y, z, B, alpha=1.0, seed=1, unif=None):
+        """Batch of Gaussian permutation tests -> (statistic, p.value)."""
+        e = self.engine
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        zo, zi = _as_csr(z)
+        n = len(x)
+        st, pv = np.zeros(max(n, 1)), np.zeros(max(n, 1))
+        fn, state, keep = self._unif(seed, unif)
+        e._check(e._lib.bnl_ci_gaussian_mc(e._ctx, self.handle, MC_TESTS[test], int(B), float(alpha), n, _ip(x),
+                                           _ip(y), _ip(zo), _ip(zi), fn, state, _dp(st), _dp(pv)))
+        del keep
+        return st[:n], pv[:n]
 
     def score_discrete(self, score, target, parents, arg=0.0):
         """Batch of node scores -> (score, nparams); arg = k (aic/bic) or iss (bde/bds)."""

@@ -50,7 +50,11 @@ enum {
 
 /* test_e values handled (src/tests/tests.h:8-36). */
 enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4, BNL_JT = 10, BNL_MI_CG = 30, BNL_MI_SH = 40,
-       BNL_COR = 20, BNL_ZF = 21, BNL_MI_G = 22, BNL_MI_G_SH = 41 };
+       BNL_COR = 20, BNL_ZF = 21, BNL_MI_G = 22, BNL_MI_G_SH = 41,
+       /* permutation, semiparametric and sequential permutation tests (tests.h:21-34) */
+       BNL_MC_MI = 50, BNL_MC_X2 = 51, BNL_SP_MI = 52, BNL_SP_X2 = 53, BNL_MC_JT = 54,
+       BNL_SMC_MI = 60, BNL_SMC_X2 = 61, BNL_SMC_JT = 62,
+       BNL_MC_COR = 70, BNL_MC_MI_G = 71, BNL_MC_ZF = 72, BNL_SMC_COR = 80, BNL_SMC_MI_G = 81, BNL_SMC_ZF = 82 };
 /* score_e values handled (src/scores/scores.h:9-60). */
 enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_EBIC = 5, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
        BNL_FNML = 11, BNL_QNML = 12, BNL_NAL = 13, BNL_PNAL = 14,
@@ -191,6 +195,55 @@ int bnl_stat_from_tables(bnl_ctx *ctx, int kind, int code, double arg, int64_t n
                          const int *llx, const int *lly, const int *llz, const int *nz,
                          const int32_t *tables, const int64_t *table_off, double *o0, double *o1,
                          double *o2);
+
+/* ---- permutation tests -------------------------------------------------- */
+
+/* The caller's uniform generator: returns the next U(0, 1) draw of its stream.
+ * In the reference this is R's unif_rand() between GetRNGstate() / PutRNGstate()
+ * (src/tests/permutation/discrete.monte.carlo.c:49, 144); the binding passes a
+ * one-line wrapper, so the library advances R's own stream draw by draw. */
+typedef double (*bnl_unif_fn)(void *state);
+
+/* A generator for callers without one: splitmix64 mapped to (0, 1); state is a
+ * uint64_t the caller seeds. */
+double bnl_unif_splitmix64(void *state);
+
+/* Discrete Monte Carlo permutation (mc-mi, mc-x2, mc-jt), sequential (smc-*) and
+ * semiparametric (sp-mi, sp-x2) tests. Replaces c_mcarlo / c_cmcarlo
+ * (src/tests/permutation/discrete.monte.carlo.c:16-159, 162-308) behind
+ * ut_dperm / ct_dperm (src/tests/patterns/utest.c:347, ctest.c). The observed
+ * tables of all n tests are counted in one device pass; the B random tables per
+ * test (Patefield's algorithm given the margins, c_rcont2 in
+ * src/core/contingency.tables.c:288) are drawn on the host from `unif`, test after
+ * test in the order given, which is the order the reference consumes its stream.
+ * alpha is the early-stopping threshold of the sequential tests (ignored otherwise,
+ * where the reference's callers pass 1). stat as in the reference's htest; df is
+ * the estimated one for sp-*, NaN otherwise (may be NULL). */
+int bnl_ci_discrete_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, double alpha, int n, const int *x,
+                       const int *y, const int *z_off, const int *z_idx, bnl_unif_fn unif,
+                       void *unif_state, double *stat, double *df, double *pvalue);
+
+/* The permutation stage alone, over count tables the caller already holds
+ * (n[z][x][y] per test, as bnl_counts returns them; nz[u] != 0 marks a conditional
+ * test): for rows sharded over GPUs -- bnl_counts per shard, all-reduce, then this
+ * on one rank. Runs on the host; ctx may be NULL. */
+int bnl_mc_from_tables(bnl_ctx *ctx, int test_e, int B, double alpha, int n, const int *llx, const int *lly,
+                       const int *nz, const int32_t *tables, const int64_t *table_off, bnl_unif_fn unif,
+                       void *unif_state, double *stat, double *df, double *pvalue);
+
+/* Gaussian permutation tests (mc-cor, mc-zf, mc-mi-g and their smc-* forms) on
+ * complete data. Replaces c_gauss_mcarlo / c_gauss_cmcarlo
+ * (src/tests/permutation/gaussian.monte.carlo.c:24-129, 132-273). Permutations of
+ * y are drawn on the host from `unif` exactly as RandomPermutation() draws them
+ * (src/core/sampling.c:12-28), in batches that never run past the reference's
+ * early exit, so the caller's stream ends where the reference leaves it; the
+ * permuted cross-products (the O(B n k) part) are formed on the device. The
+ * sums are reduced in parallel, so a permuted value equal to the observed one to
+ * the last bit may compare differently from the reference's sequential long
+ * double sum. stat as bnl_ci_gaussian returns it. */
+int bnl_ci_gaussian_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, double alpha, int n, const int *x,
+                       const int *y, const int *z_off, const int *z_idx, bnl_unif_fn unif,
+                       void *unif_state, double *stat, double *pvalue);
 
 /* ---- Gaussian ---------------------------------------------------------- */
 

@@ -7,9 +7,7 @@
 
 #define STUB(name) void name(void) { Rf_error("oracle/_ref: " #name "() is out of scope and not compiled in"); }
 
-STUB(R_qsort) STUB(R_qsort_int) STUB(R_qsort_int_I)
-STUB(c_cmcarlo) 
-STUB(c_gauss_cmcarlo) STUB(c_gauss_mcarlo) STUB(c_mcarlo) 
+STUB(R_qsort) STUB(R_qsort_int) STUB(R_qsort_int_I) STUB(revsort)
 STUB(custom_score_function) STUB(custom_test_function)
 STUB(em_irls_node) STUB(fitted_node_to_enum) 
 STUB(nal_cgnode) STUB(predictive_loglik_cgnode)

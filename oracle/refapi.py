@@ -208,6 +208,10 @@ def _ip(a):
     return a.ctypes.data_as(rb.c_int_p)
 
 
+def _dp(a):
+    return a.ctypes.data_as(rb.c_dbl_p)
+
+
 def fast_config(columns, levels, offset=0):
     """reference c_fast_config (src/core/sets.c:162-218)."""
     L = rb.lib()
@@ -236,3 +240,46 @@ def chisqtest(x, llx, y, lly, test_e, z=None, llz=0):
         st = L.c_cchisqtest(_ip(x), llx, _ip(y), lly, _ip(z), llz, len(x), C.byref(df),
                             test_e, scale)
     return st, df.value
+
+
+# test_e values of the permutation tests (src/tests/tests.h:21-34)
+MC_TESTS = {"mc-mi": 50, "mc-x2": 51, "sp-mi": 52, "sp-x2": 53, "mc-jt": 54,
+            "smc-mi": 60, "smc-x2": 61, "smc-jt": 62,
+            "mc-cor": 70, "mc-mi-g": 71, "mc-zf": 72, "smc-cor": 80, "smc-mi-g": 81, "smc-zf": 82}
+
+
+def mc_discrete(test, x, llx, y, lly, zcols=(), zlev=(), B=500, alpha=0.05, seed=1):
+    """reference c_mcarlo / c_cmcarlo (src/tests/permutation/discrete.monte.carlo.c:16-159,
+    162-308) on the shim's uniform stream seeded with `seed`.
+    Returns (statistic, df or nan, p-value)."""
+    L = rb.lib()
+    x = np.ascontiguousarray(x, dtype=np.int32)
+    y = np.ascontiguousarray(y, dtype=np.int32)
+    obs, pv, df = (np.full(1, np.nan) for _ in range(3))
+    if seed is not None:                      # None: carry on with the stream of the previous test
+        L.minir_rng_seed(int(seed))
+    if len(zcols) == 0:
+        L.c_mcarlo(_ip(x), llx, _ip(y), lly, len(x), int(B), _dp(obs), _dp(pv), float(alpha),
+                   MC_TESTS[test], _dp(df))
+    else:
+        z, llz = fast_config(zcols, zlev, 1)
+        L.c_cmcarlo(_ip(x), llx, _ip(y), lly, _ip(z), llz, len(x), int(B), _dp(obs), _dp(pv),
+                    float(alpha), MC_TESTS[test], _dp(df))
+    return float(obs[0]), float(df[0]), float(pv[0])
+
+
+def mc_gaussian(test, cols, B=500, alpha=0.05, seed=1):
+    """reference c_gauss_mcarlo / c_gauss_cmcarlo (src/tests/permutation/gaussian.monte.carlo.c):
+    cols = [x, y, z1, ...]; returns (statistic, p-value)."""
+    L = rb.lib()
+    cs = [np.array(c, dtype=np.float64) for c in cols]
+    n = len(cs[0])
+    obs, pv = np.full(1, np.nan), np.full(1, np.nan)
+    if seed is not None:
+        L.minir_rng_seed(int(seed))
+    if len(cs) == 2:
+        L.c_gauss_mcarlo(_dp(cs[0]), _dp(cs[1]), n, int(B), _dp(pv), float(alpha), MC_TESTS[test], _dp(obs))
+    else:
+        ptrs = (rb.c_dbl_p * len(cs))(*[_dp(c) for c in cs])
+        L.c_gauss_cmcarlo(ptrs, len(cs), n, 0, 1, int(B), _dp(obs), _dp(pv), float(alpha), MC_TESTS[test])
+    return float(obs[0]), float(pv[0])

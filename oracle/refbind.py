@@ -89,6 +89,15 @@ def lib():
                                     C.c_longdouble, C.c_longdouble]),
         "c_ols": (None, [C.POINTER(c_dbl_p), c_dbl_p, C.c_int, C.c_int, c_dbl_p,
                          c_dbl_p, c_dbl_p, c_dbl_p, c_int_p, C.c_bool]),
+        # permutation tests (src/tests/permutation/*.c); the uniform stream is the shim's
+        "minir_rng_seed": (None, [C.c_ulonglong]),
+        "c_mcarlo": (None, [c_int_p, C.c_int, c_int_p, C.c_int, C.c_int, C.c_int, c_dbl_p, c_dbl_p,
+                            C.c_double, C.c_int, c_dbl_p]),
+        "c_cmcarlo": (None, [c_int_p, C.c_int, c_int_p, C.c_int, c_int_p, C.c_int, C.c_int, C.c_int,
+                             c_dbl_p, c_dbl_p, C.c_double, C.c_int, c_dbl_p]),
+        "c_gauss_mcarlo": (None, [c_dbl_p, c_dbl_p, C.c_int, C.c_int, c_dbl_p, C.c_double, C.c_int, c_dbl_p]),
+        "c_gauss_cmcarlo": (None, [C.POINTER(c_dbl_p), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   c_dbl_p, c_dbl_p, C.c_double, C.c_int]),
         # call-site tier
         "per_node_score": (vp, [vp] * 6),
         "score_cache_fill": (vp, [vp] * 13),

@@ -377,7 +377,25 @@ double Rf_fmax2(double x, double y) { return (isnan(x) || isnan(y)) ? x + y : (x
 double Rf_fmin2(double x, double y) { return (isnan(x) || isnan(y)) ? x + y : (x < y ? x : y); }
 void GetRNGstate(void) {}
 void PutRNGstate(void) {}
-double unif_rand(void) { Rf_error("minir: R's RNG stream is not available"); }
+/* R's Mersenne-Twister stream is not available here. The permutation tests only
+ * need SOME uniform stream that the engine under test can be handed as well:
+ * splitmix64, top 53 bits, zero rejected (unif_rand() never returns 0 or 1).
+ * Unseeded use stays an error. */
+static unsigned long long minir_rng_state = 0;
+static int minir_rng_seeded = 0;
+void minir_rng_seed(unsigned long long seed) { minir_rng_state = seed; minir_rng_seeded = 1; }
+unsigned long long minir_rng_peek(void) { return minir_rng_state; }
+double unif_rand(void) {
+  if (!minir_rng_seeded) Rf_error("minir: unif_rand() before minir_rng_seed()");
+  for (;;) {
+    unsigned long long z = (minir_rng_state += 0x9E3779B97F4A7C15ULL);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    z ^= z >> 31;
+    const double u = (double)(z >> 11) * 0x1.0p-53;
+    if (u > 0.0) return u;
+  }
+}
 
 /* ------------------------------ LAPACK -------------------------------- */
 /* resolved lazily from scipy's bundled OpenBLAS, which the Python harness

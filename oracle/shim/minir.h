@@ -166,6 +166,8 @@ double Rf_fmax2(double x, double y);
 double Rf_fmin2(double x, double y);
 double Rf_fround(double x, double digits);
 double unif_rand(void);
+void minir_rng_seed(unsigned long long seed);      /* harness only */
+unsigned long long minir_rng_peek(void);
 void GetRNGstate(void);
 void PutRNGstate(void);
 #define lgammafn Rf_lgammafn

@@ -497,6 +497,50 @@ def mi_matrix_outputs():
     print("wrote ref_mi_matrix.json")
 
 
+def permutation_outputs():
+    """Permutation, sequential and semiparametric tests from the reference's
+    c_mcarlo / c_cmcarlo (and the Gaussian c_gauss_mcarlo / c_gauss_cmcarlo) with the
+    shim's splitmix64 stream: every batch is seeded once and its tests then share
+    the stream, as the tests of one R session do. Own file."""
+    from oracle import refapi as ra
+    out = {}
+    for ds in ("learning_test", "learning_test_na"):
+        names, codes, nlev = load_discrete(ds)
+        z = np.load(os.path.join(HERE, "data_%s.npz" % ds))
+        codes[z["codes"] == 255] = np.iinfo(np.int32).min      # missing cells
+        codes = [np.ascontiguousarray(c) for c in codes]
+        units = [(0, 1, []), (0, 5, []), (2, 5, []), (3, 4, []), (0, 1, [2]), (1, 4, [0, 2]), (5, 2, [3]),
+                 (0, 4, [1, 2, 3])]
+        batches = []
+        for test, B, alpha, seed in (("mc-mi", 150, 1.0, 11), ("mc-x2", 150, 1.0, 12), ("mc-jt", 150, 1.0, 13),
+                                     ("sp-mi", 100, 1.0, 14), ("sp-x2", 100, 1.0, 15), ("smc-mi", 400, 0.05, 16),
+                                     ("smc-x2", 400, 0.05, 17), ("smc-jt", 400, 0.01, 18)):
+            res = []
+            for k, (x, y, z) in enumerate(units):
+                st, df, p = ra.mc_discrete(test, codes[x], int(nlev[x]), codes[y], int(nlev[y]),
+                                           [codes[i] for i in z], [int(nlev[i]) for i in z], B=B, alpha=alpha,
+                                           seed=seed if k == 0 else None)
+                res.append({"x": x, "y": y, "z": z, "stat": st, "df": None if np.isnan(df) else df, "p": p})
+            batches.append({"test": test, "B": B, "alpha": alpha, "seed": seed, "results": res})
+        out[ds] = batches
+    names, vals = load_gaussian("gaussian_test")
+    vals = [np.ascontiguousarray(v) for v in vals]
+    units = [(0, 1, []), (0, 2, []), (3, 5, []), (0, 1, [2]), (1, 4, [0, 2]), (5, 6, [0, 1, 2, 3])]
+    batches = []
+    for test, B, alpha, seed in (("mc-cor", 120, 1.0, 21), ("mc-zf", 120, 1.0, 22), ("mc-mi-g", 120, 1.0, 23),
+                                 ("smc-cor", 300, 0.05, 24), ("smc-zf", 300, 0.05, 25), ("smc-mi-g", 300, 0.02, 26)):
+        res = []
+        for k, (x, y, z) in enumerate(units):
+            st, p = ra.mc_gaussian(test, [vals[x], vals[y]] + [vals[i] for i in z], B=B, alpha=alpha,
+                                   seed=seed if k == 0 else None)
+            res.append({"x": x, "y": y, "z": z, "stat": st, "p": p})
+        batches.append({"test": test, "B": B, "alpha": alpha, "seed": seed, "results": res})
+    out["gaussian_test"] = batches
+    with open(os.path.join(HERE, "ref_permutation.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote ref_permutation.json")
+
+
 def special_function_fixtures():
     import mpmath as mp
     mp.mp.dps = 50
@@ -537,3 +581,4 @@ if __name__ == "__main__":
     ebic_outputs()
     bge_outputs()
     mi_matrix_outputs()
+    permutation_outputs()
