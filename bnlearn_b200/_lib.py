@@ -30,6 +30,7 @@ SIGNATURES = {
                              c_i32_p, c_i64_p]),
     "bnl_score_discrete": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p,
                                      c_int_p, c_int_p, c_dbl_p, c_dbl_p]),
+    "bnl_data_set_interventions": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int]),
     "bnl_ci_discrete": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, c_int_p, c_int_p,
                                   c_int_p, c_int_p, c_dbl_p, c_dbl_p, c_dbl_p]),
     "bnl_ci_gaussian": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, c_int_p, c_int_p,

@@ -17,7 +17,7 @@ namespace {
 bool is_discrete_test(int t) { return bnl_is_discrete_test(t); }
 bool is_gaussian_test(int t) { return t == BNL_COR || t == BNL_ZF || t == BNL_MI_G || t == BNL_MI_G_SH; }
 bool is_discrete_score(int s) {
-  return s == BNL_LOGLIK || s == BNL_AIC || s == BNL_BIC || s == BNL_EBIC || s == BNL_BDE || s == BNL_BDS || s == BNL_BDJ || s == BNL_K2 || s == BNL_NAL || s == BNL_PNAL || s == BNL_FNML ||
+  return s == BNL_LOGLIK || s == BNL_AIC || s == BNL_BIC || s == BNL_EBIC || s == BNL_BDE || s == BNL_MBDE || s == BNL_BDS || s == BNL_BDJ || s == BNL_K2 || s == BNL_NAL || s == BNL_PNAL || s == BNL_FNML ||
          s == BNL_QNML;
 }
 

@@ -705,6 +705,8 @@ extern "C" int bnl_data_resample(bnl_ctx *ctx, bnl_data source, int64_t nrows, c
   ds.nobs = nrows;
   ds.is_numeric = src.is_numeric; ds.nlevels = src.nlevels; ds.slot = src.slot;
   ds.bge_mu = src.bge_mu; ds.bge_w = src.bge_w;      // nu falls back to the replicate's own means
+  ds.ebic_gamma = src.ebic_gamma;
+  ds.mask_col = src.mask_col;                         // intervention masks are columns: they follow the rows
   ds.stride_u8 = round_up((size_t)nrows + 1, BNL_COL_ALIGN);
   ds.stride_f64 = round_up((size_t)nrows + 1, 32);
   ds.stride_u16 = round_up((size_t)nrows + 1, BNL_COL_ALIGN);

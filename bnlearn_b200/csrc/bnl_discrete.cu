@@ -727,6 +727,22 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
     for (int u = 0; u < n; u++) score[u] -= pen * (double)(pa_off[u + 1] - pa_off[u]);
     return BNL_OK;
   }
+  if (score_e == BNL_MBDE) {
+    // mBDe: BDe over the rows on which the node was not intervened upon; the node's
+    // mask column (one level, NA on those rows) goes first among the parents, so that
+    // score_cache_fill's candidates still share every column but the last.
+    if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_score_discrete: bad arguments");
+    std::vector<int> off(n + 1, 0), idx;
+    for (int u = 0; u < n; u++) {
+      const int t = target[u];
+      if (t >= 0 && t < (int)ds->mask_col.size() && ds->mask_col[t] >= 0) idx.push_back(ds->mask_col[t]);
+      for (int k = pa_off[u]; k < pa_off[u + 1]; k++) idx.push_back(pa_idx[k]);
+      off[u + 1] = (int)idx.size();
+    }
+    return bnl_score_discrete(ctx, data, BNL_BDE, k_or_iss, n, target, off.data(), idx.empty() ? nullptr : idx.data(),
+                              score, nparams);
+  }
   if (score_e != BNL_LOGLIK && score_e != BNL_AIC && score_e != BNL_BIC && score_e != BNL_BDE &&
       score_e != BNL_BDS && score_e != BNL_BDJ && score_e != BNL_K2 && score_e != BNL_NAL &&
       score_e != BNL_PNAL && score_e != BNL_FNML && score_e != BNL_QNML)
@@ -741,4 +757,17 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
     if (rc) return rc;
   }
   return run_request(ctx, *ds, rq);
+}
+
+extern "C" int bnl_data_set_interventions(bnl_ctx *ctx, bnl_data data, int node, int mask_col) {
+  if (!ctx) return BNL_EINVAL;
+  BnlDataSet *ds = find_data(ctx, data);
+  if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  if (node < 0 || node >= ds->ncols || ds->is_numeric[node])
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_set_interventions: node %d is not a factor column", node);
+  if (mask_col >= 0 && (mask_col >= ds->ncols || ds->is_numeric[mask_col] || ds->nlevels[mask_col] != 1))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_set_interventions: the mask must be a factor column with one level");
+  if (ds->mask_col.empty()) ds->mask_col.assign(ds->ncols, -1);
+  ds->mask_col[node] = mask_col < 0 ? -1 : mask_col;
+  return BNL_OK;
 }

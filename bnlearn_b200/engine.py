@@ -12,14 +12,14 @@ import numpy as np
 from . import _lib
 
 TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-cg": 30, "mi-g-sh": 41}
-SCORES = {"loglik": 1, "aic": 3, "bic": 4, "ebic": 5, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
+SCORES = {"loglik": 1, "aic": 3, "bic": 4, "ebic": 5, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "mbde": 10, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103, "ebic-g": 104, "bge": 105, "nal-g": 106, "pnal-g": 107,
           "loglik-cg": 200, "aic-cg": 202, "bic-cg": 203, "ebic-cg": 204}
 MC_TESTS = {"mc-mi": 50, "mc-x2": 51, "sp-mi": 52, "sp-x2": 53, "mc-jt": 54, "smc-mi": 60, "smc-x2": 61,
             "smc-jt": 62, "mc-cor": 70, "mc-mi-g": 71, "mc-zf": 72, "smc-cor": 80, "smc-mi-g": 81, "smc-zf": 82}
 DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf", "jt", "mi-sh")
 GAUSSIAN_TESTS = ("cor", "zf", "mi-g", "mi-g-sh")
-DISCRETE_SCORES = ("loglik", "aic", "bic", "ebic", "bde", "bds", "bdj", "k2", "fnml", "qnml", "nal", "pnal")
+DISCRETE_SCORES = ("loglik", "aic", "bic", "ebic", "bde", "mbde", "bds", "bdj", "k2", "fnml", "qnml", "nal", "pnal")
 GAUSSIAN_SCORES = ("loglik-g", "aic-g", "bic-g", "ebic-g", "bge", "nal-g", "pnal-g")
 NA_INT = np.iinfo(np.int32).min
 
@@ -224,6 +224,12 @@ class DataSet:
         e._check(e._lib.bnl_ci_discrete(e._ctx, self.handle, TESTS[test], n, _ip(x), _ip(y), _ip(zo),
                                         _ip(zi), _dp(st), _dp(df), _dp(pv)))
         return st[:n], df[:n], pv[:n]
+
+    def set_interventions(self, node, mask_col):
+        """mBDe: `mask_col` (a one-level factor, NA on the rows where `node` was
+        intervened upon) masks every unit of `node`; -1 clears."""
+        e = self.engine
+        e._check(e._lib.bnl_data_set_interventions(e._ctx, self.handle, int(node), int(mask_col)))
 
     def _unif(self, seed, unif):
         """(function pointer, state pointer, keep-alive) of the uniform stream: a

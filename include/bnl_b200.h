@@ -57,6 +57,7 @@ enum { BNL_MI = 1, BNL_MI_ADF = 2, BNL_X2 = 3, BNL_X2_ADF = 4, BNL_JT = 10, BNL_
        BNL_MC_COR = 70, BNL_MC_MI_G = 71, BNL_MC_ZF = 72, BNL_SMC_COR = 80, BNL_SMC_MI_G = 81, BNL_SMC_ZF = 82 };
 /* score_e values handled (src/scores/scores.h:9-60). */
 enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_EBIC = 5, BNL_BDE = 6, BNL_BDS = 7, BNL_BDJ = 8, BNL_K2 = 9,
+       BNL_MBDE = 10,
        BNL_FNML = 11, BNL_QNML = 12, BNL_NAL = 13, BNL_PNAL = 14,
        BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103, BNL_EBIC_G = 104, BNL_BGE = 105, BNL_NAL_G = 106,
        BNL_PNAL_G = 107,
@@ -167,6 +168,16 @@ int bnl_counts(bnl_ctx *ctx, bnl_data data, int n, const int *x, const int *y,
 int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
                        int n, const int *target, const int *pa_off,
                        const int *pa_idx, double *score, double *nparams);
+
+/* Interventional data for BNL_MBDE (src/scores/dirichlet.posterior.c:39-60,
+ * 102-135: rows on which the node itself was intervened upon are left out of its
+ * counts). mask_col is a registered factor column with ONE level whose NA rows are
+ * the interventions on `node` (R: factor(ifelse(seq_len(n) %in% exp[[node]], NA, 1)));
+ * -1 clears it. bnl_score_discrete(BNL_MBDE, ...) then counts every unit of that
+ * node with the mask as an extra conditioning column -- a level-1 column adds
+ * nothing to the cell index and its NA rows are skipped like any other NA -- and
+ * scores the tables as BDe. Nodes without a mask score as plain BDe. */
+int bnl_data_set_interventions(bnl_ctx *ctx, bnl_data data, int node, int mask_col);
 
 /* Discrete CI tests x[u] _||_ y[u] | z (mi, mi-adf, x2, x2-adf): statistic (MI
  * scaled to G^2), degrees of freedom and p-value = pchisq(stat, df, upper).

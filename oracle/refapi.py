@@ -46,9 +46,13 @@ class RefData:
         self._df = None
 
 
-def _extra(score=None, k=None, iss=None, B=None, bge=None, gamma=None):
+def _extra(score=None, k=None, iss=None, B=None, bge=None, gamma=None, exp=None):
     names, items = [], []
     L = rb.lib()
+    if exp is not None:                       # {node name: sorted 1-based rows that were interventions on it}
+        names.append("exp")
+        items.append(rb.rlist([rb.intvec(np.asarray(v, dtype=np.int32), view=False) for v in exp.values()],
+                              list(exp.keys())))
     if gamma is not None:
         names.append("gamma"); items.append(L.Rf_ScalarReal(float(gamma)))
     if bge is not None:                       # (iss.mu, iss.w, nu vector, node names)
@@ -66,7 +70,7 @@ def _extra(score=None, k=None, iss=None, B=None, bge=None, gamma=None):
     return rb.rlist(items, names)
 
 
-def per_node_score(data, parents, targets, score, k=None, iss=None, bge=None, gamma=None):
+def per_node_score(data, parents, targets, score, k=None, iss=None, bge=None, gamma=None, exp=None):
     """reference per_node_score (src/scores/per.node.score.c:31-48).
     parents: {node name: [parent names, in order]}; bge = (iss.mu, iss.w, nu)."""
     L = rb.lib()
@@ -74,7 +78,7 @@ def per_node_score(data, parents, targets, score, k=None, iss=None, bge=None, ga
     if bge is not None:
         bge = (bge[0], bge[1], bge[2], data.names)
     res = L.per_node_score(net, data.df(), L.Rf_mkString(score.encode()),
-                           rb.strvec(list(targets)), _extra(k=k, iss=iss, bge=bge, gamma=gamma),
+                           rb.strvec(list(targets)), _extra(k=k, iss=iss, bge=bge, gamma=gamma, exp=exp),
                            L.Rf_ScalarLogical(0))
     return rb.to_numpy(res)
 

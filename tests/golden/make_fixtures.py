@@ -541,6 +541,35 @@ def permutation_outputs():
     print("wrote ref_permutation.json")
 
 
+def mbde_outputs():
+    """mBDe node scores from the reference's per_node_score (dirichlet_node with the
+    `exp` list, src/scores/dirichlet.posterior.c) on learning.test with made-up
+    interventions on three nodes. Own file and RNG."""
+    from oracle import refapi as ra, refbind as rb
+    names, codes, nlev = load_discrete("learning_test")
+    codes = [np.ascontiguousarray(c) for c in codes]
+    n = len(codes[0])
+    rng = np.random.default_rng(20261110)
+    exp = {0: np.arange(1, n + 1, 7), 3: np.sort(rng.choice(n, 300, replace=False)) + 1,
+           5: np.sort(rng.choice(n, n - 40, replace=False)) + 1}          # almost every row of F
+    data = ra.RefData(codes, [int(v) for v in nlev], names)
+    recs = []
+    for t in (0, 3, 5):
+        others = [i for i in range(len(names)) if i != t]
+        for pa in ([], others[:1], others[1:3], others[:4], others[::-1]):
+            par = {nm: [] for nm in names}
+            par[names[t]] = [names[i] for i in pa]
+            for iss in (1.0, 10.0):
+                v = ra.per_node_score(data, par, [names[t]], "mbde", iss=iss,
+                                      exp={names[k]: r for k, r in exp.items()})[0]
+                recs.append({"node": t, "parents": pa, "iss": iss, "value": float(v)})
+            rb.reset()
+            data.invalidate()
+    with open(os.path.join(HERE, "ref_mbde.json"), "w") as f:
+        json.dump({"learning_test": {"exp": {str(k): [int(i) for i in r] for k, r in exp.items()}, "scores": recs}}, f)
+    print("wrote ref_mbde.json")
+
+
 def special_function_fixtures():
     import mpmath as mp
     mp.mp.dps = 50
@@ -582,3 +611,4 @@ if __name__ == "__main__":
     bge_outputs()
     mi_matrix_outputs()
     permutation_outputs()
+    mbde_outputs()

@@ -476,6 +476,55 @@ def test_every_table_size_class(engine, with_na):
     d.release()
 
 
+def test_mbde_against_reference_golden(engine):
+    """mBDe = BDe over the rows on which the node was not intervened upon: the
+    interventions arrive as one-level mask columns (NA on those rows) registered
+    next to the data. Against per_node_score("mbde") of the reference; nodes
+    without a mask score as BDe; a resampled data set keeps its masks."""
+    from oracle import oracle as orc
+    with open(os.path.join(GOLDEN, "ref_mbde.json")) as f:
+        fx = json.load(f)["learning_test"]
+    names, cols, nlev = load_discrete("learning_test")
+    n, m = len(cols[0]), len(cols)
+    masks = {}
+    for node, rows in fx["exp"].items():
+        mk = np.ones(n, dtype=np.int32)
+        mk[np.asarray(rows) - 1] = orc.NA_INT
+        masks[int(node)] = mk
+    order = sorted(masks)
+    d = engine.register(cols + [masks[k] for k in order], nlev + [1] * len(order))
+    for j, k in enumerate(order):
+        d.set_interventions(k, m + j)
+    for iss in (1.0, 10.0):
+        rs = [r for r in fx["scores"] if r["iss"] == iss]
+        sc, npar = d.score_discrete("mbde", [r["node"] for r in rs], [r["parents"] for r in rs], iss)
+        for i, r in enumerate(rs):
+            _check(sc[i], r["value"], ("mbde", r["node"], r["parents"], iss))
+            assert npar[i] == (nlev[r["node"]] - 1) * int(np.prod([nlev[p] for p in r["parents"]]))
+    a, _ = d.score_discrete("mbde", [1, 2], [[0], [1, 3]], 1.0)           # no mask on B, C
+    b, _ = d.score_discrete("bde", [1, 2], [[0], [1, 3]], 1.0)
+    assert np.array_equal(a, b)
+    rows = np.arange(n, dtype=np.int32)[::-1].copy()                       # a permutation of the rows
+    r = d.resample(rows)
+    c, _ = r.score_discrete("mbde", [0, 3], [[1, 2], [0]], 1.0)
+    e, _ = d.score_discrete("mbde", [0, 3], [[1, 2], [0]], 1.0)
+    for i in range(2):
+        _check(c[i], e[i], ("resampled", i))
+    # the whole search on the six nodes (the masks are columns 6..8, never nodes):
+    # the node scores it returns are those of its final graph
+    amat, scores, iters = d.hc("mbde", 1.0, nnodes=m)
+    assert iters > 0 and amat.sum() > 0
+    pa = [[int(i) for i in np.nonzero(amat[:, j])[0]] for j in range(m)]
+    chk, _ = d.score_discrete("mbde", list(range(m)), pa, 1.0)
+    for j in range(m):
+        _check(scores[j], chk[j], ("hc node score", j))
+    from bnlearn_b200 import BnlError
+    with pytest.raises(BnlError):
+        d.set_interventions(0, 1)                                          # not a one-level column
+    r.release()
+    d.release()
+
+
 def test_candidate_runs_with_mid_size_tables(engine):
     """score_cache_fill's batch for a node that already has 2-3 parents: the
     candidates share every column but the last, and their tables (240-3600 cells)
