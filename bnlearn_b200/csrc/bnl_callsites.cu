@@ -83,6 +83,7 @@ struct AstReq {
   double p = 0.0, pmin = 1.0, pmax = 0.0;
   bool done = false;
   bool stage1 = false;              // finished by the test with no moving parts
+  bool missing = false;             // some column of the request holds missing values
   int ndsep = -1;
   std::vector<int> dsep;
   int cursize = 0;
@@ -108,14 +109,16 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
   const bool gauss = is_gaussian_test(test_e);
   if (!gauss && !is_discrete_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
-  // The subset loops below follow the complete-data patterns. On incomplete
-  // numeric data the reference switches to *_with_missing variants whose
-  // degrees-of-freedom exit depends on each subset's complete rows and whose
-  // early exit is disabled in the source (patterns/allsubs.test.c:419); those are
-  // not restated, single tests (bnl_indep_test / bnl_ci_gaussian) are.
-  if (gauss && it->second.any_nan)
-    return bnl_fail(ctx, BNL_EUNSUPPORTED,
-                    "subset patterns for Gaussian tests on incomplete data are not handled by this engine");
+  // A request whose columns are not all complete takes the reference's
+  // *_with_missing pattern (rinterface/allsubs.test.c:72, 103-113): every subset is
+  // tested on its own complete rows, there is NO early exit on p > alpha (disabled in
+  // the source, patterns/allsubs.test.c:419) and no separating set; only a subset
+  // without degrees of freedom (or without complete rows) ends the request.
+  const BnlDataSet &dsr = it->second;
+  auto col_incomplete = [&](int c) {
+    return gauss && c >= 0 && c < dsr.ncols && dsr.is_numeric[c] && dsr.slot[c] < (int)dsr.h_mean.size() &&
+           std::isnan(dsr.h_mean[dsr.slot[c]]);
+  };
 
   std::vector<AstReq> rq(n);
   for (int r = 0; r < n; r++) {
@@ -125,6 +128,8 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
     rq[r].m = sx_off[r + 1] - sx_off[r] - rq[r].nf;
     if (rq[r].m < 0 || rq[r].nf < 0)
       return bnl_fail(ctx, BNL_EINVAL, "bnl_allsubs_test: request %d has more fixed than total variables", r);
+    rq[r].missing = col_incomplete(x[r]) || col_incomplete(y[r]);
+    for (int k = sx_off[r]; k < sx_off[r + 1]; k++) rq[r].missing = rq[r].missing || col_incomplete(sx[k]);
   }
   std::vector<int> bx, by, boff, bidx, owner;
   std::vector<double> st, df, pv;
@@ -179,7 +184,7 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
         q.cursize++;
         const int mx = std::min(maxsize, q.m);
         if (q.cursize > mx) { q.done = true; continue; }
-        if (gauss) {
+        if (gauss && !q.missing) {
           // not enough degrees of freedom: independence, with the first
           // cursize + nf variables as separating set (patterns/allsubs.test.c:169-194).
           const int nz = q.cursize + q.nf;
@@ -222,6 +227,23 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
       size_t e = u;
       while (e < owner.size() && owner[e] == r) e++;
       for (size_t t = u; t < e; t++) {
+        if (q.missing) {
+          // patterns/allsubs.test.c:332-365: no degrees of freedom on this subset's
+          // complete rows ends the request (before the counter moves), with the FIRST
+          // cursize + nf variables reported; otherwise the subset is recorded and the
+          // scan goes on whatever its p-value.
+          if (df[t] == 0.0) {
+            q.p = q.pmin = q.pmax = 1.0;
+            q.done = true;
+            q.ndsep = q.nf + q.cursize;
+            q.dsep.assign(q.sx, q.sx + q.ndsep);
+            break;
+          }
+          q.p = pv[t];
+          range(q, q.p);
+          q.counter += 1.0;
+          continue;
+        }
         q.p = pv[t];
         range(q, q.p);
         q.counter += 1.0;                        // patterns/allsubs.test.c:110, 249
@@ -242,6 +264,9 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
   for (int r = 0; r < n; r++) {
     AstReq &q = rq[r];
     double p = q.p, pmin = q.pmin, pmax = q.pmax;
+    // the with-missing scan ends in ast_prepare_retval(p of the LAST subset, ..., NULL, 0):
+    // an empty separating set when that p-value happens to exceed alpha.
+    if (q.missing && !q.stage1 && q.ndsep < 0 && p > alpha) q.ndsep = 0;
     if (minsize == 0 && !q.stage1) { pmin = std::min(pmin, m_min[r]); pmax = std::max(pmax, m_max[r]); }
     out[3 * r + 0] = p; out[3 * r + 1] = pmin; out[3 * r + 2] = pmax;
     ndsep[r] = q.ndsep;
@@ -299,14 +324,19 @@ extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int 
   const bool gauss = is_gaussian_test(test_e);
   if (!gauss && !is_discrete_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
-  // The subset loops below follow the complete-data patterns. On incomplete
-  // numeric data the reference switches to *_with_missing variants whose
-  // degrees-of-freedom exit depends on each subset's complete rows and whose
-  // early exit is disabled in the source (patterns/allsubs.test.c:419); those are
-  // not restated, single tests (bnl_indep_test / bnl_ci_gaussian) are.
-  if (gauss && it->second.any_nan)
-    return bnl_fail(ctx, BNL_EUNSUPPORTED,
-                    "subset patterns for Gaussian tests on incomplete data are not handled by this engine");
+  // columns with missing values: rrd_gaustests_with_missing (each test on the rows
+  // complete for the variables still in play; a test without degrees of freedom gives
+  // p = 1 and does NOT drop its variable, patterns/roundrobin.test.c:264-276).
+  const BnlDataSet &dsr = it->second;
+  bool with_missing = false;
+  if (gauss) {
+    auto inc = [&](int c) {
+      return c >= 0 && c < dsr.ncols && dsr.is_numeric[c] && dsr.slot[c] < (int)dsr.h_mean.size() &&
+             std::isnan(dsr.h_mean[dsr.slot[c]]);
+    };
+    with_missing = inc(x);
+    for (int i = 0; i < nz; i++) with_missing = with_missing || inc(z[i]);
+  }
 
   int nfixed = 0;
   for (int i = 0; i < nz; i++) nfixed += is_fixed && is_fixed[i];
@@ -324,7 +354,7 @@ extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int 
     zidx.clear();
     for (int j = 0; j < nz; j++)
       if (j != i && !dropped[j]) zidx.push_back(z[j]);
-    if (gauss) {
+    if (gauss && !with_missing) {
       const int ncond = (int)zidx.size();
       const double d = test_e == BNL_COR ? (double)(nobs - ncond - 2)
                      : test_e == BNL_ZF ? (double)(nobs - ncond - 3) : 1.0;
@@ -334,6 +364,8 @@ extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int 
     zoff[0] = 0; zoff[1] = (int)zidx.size();
     int rc = run_tests(ctx, data, test_e, xs, ys, zoff, zidx, st, df, pv);
     if (rc) return rc;
+    // df == 0 comes back when the test's own complete rows leave no degrees of freedom
+    if (with_missing && df[0] == 0.0) { pvalue[cur++] = 1.0; continue; }
     pvalue[cur] = pv[0];
     if (pvalue[cur++] > alpha) { valid--; dropped[i] = 1; }
   }

@@ -497,6 +497,58 @@ def mi_matrix_outputs():
     print("wrote ref_mi_matrix.json")
 
 
+def incomplete_gaussian_patterns():
+    """allsubs / roundrobin on incomplete numeric data: the reference's
+    ast_gaustests_with_missing / rrd_gaustests_with_missing
+    (patterns/allsubs.test.c:290-448, roundrobin.test.c:222-344). Three data sets
+    built from data_gaussian_test_na.npz: every column incomplete; columns 0-2
+    complete (requests on those alone take the complete-data patterns); and the
+    first 9 rows only (degrees of freedom run out). Own file and RNG."""
+    from oracle import refapi as ra, refbind as rb
+    rng = np.random.default_rng(20261112)
+    z = np.load(os.path.join(HERE, "data_gaussian_test_na.npz"))
+    gnames, na = [str(v) for v in z["names"]], z["values"]
+    _, full = load_gaussian("gaussian_test")
+    mixed = na.copy()
+    mixed[:3] = full[:3, :na.shape[1]]
+    sets = {"all_incomplete": na, "mixed": mixed, "tiny": mixed[:, :9].copy()}
+    out = {}
+    p = len(gnames)
+    for key, vals in sets.items():
+        data = ra.RefData([np.ascontiguousarray(v) for v in vals], None, gnames)
+        rec = {"allsubs": [], "roundrobin": []}
+        for t in range(10):
+            m = int(rng.integers(2, p - 1))
+            idx = rng.choice(p, size=2 + m, replace=False)
+            if key == "mixed" and t < 3:
+                idx = rng.permutation(3)[:3]                 # complete columns only
+                idx = np.concatenate([idx, rng.choice(np.arange(3, p), size=0)])
+                m = 1
+            x, y, sx = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+            nf = int(rng.integers(0, 2)) if m > 1 else 0
+            mn = int(rng.integers(0, 2))
+            mx = int(rng.integers(max(mn, 1), min(3, m - nf) + 1))
+            for test in ("cor", "zf", "mi-g", "mi-g-sh"):
+                rb.reset_test_counter()
+                pv, pmin, pmax, ds_ = ra.allsubs_test(data, gnames[x], gnames[y], [gnames[i] for i in sx],
+                                                      [gnames[i] for i in sx[:nf]], test, 0.05, mn, mx)
+                rec["allsubs"].append({"test": test, "x": x, "y": y, "sx": sx, "nfixed": nf, "min": mn, "max": mx,
+                                       "alpha": 0.05, "p": pv, "pmin": pmin, "pmax": pmax,
+                                       "dsep": None if ds_ is None else [gnames.index(d) for d in ds_],
+                                       "counter": rb.test_counter()})
+                rb.reset_test_counter()
+                pvs = ra.roundrobin_test(data, gnames[x], [gnames[i] for i in [y] + sx],
+                                         [gnames[i] for i in sx[:nf]], test, 0.05)
+                rec["roundrobin"].append({"test": test, "x": x, "z": [y] + sx, "nfixed": nf, "alpha": 0.05,
+                                          "p": [float(v) for v in pvs], "counter": rb.test_counter()})
+            rb.reset()
+            data.invalidate()
+        out[key] = rec
+    with open(os.path.join(HERE, "ref_incomplete_gaussian_patterns.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote ref_incomplete_gaussian_patterns.json")
+
+
 def permutation_outputs():
     """Permutation, sequential and semiparametric tests from the reference's
     c_mcarlo / c_cmcarlo (and the Gaussian c_gauss_mcarlo / c_gauss_cmcarlo) with the
@@ -610,5 +662,6 @@ if __name__ == "__main__":
     ebic_outputs()
     bge_outputs()
     mi_matrix_outputs()
+    incomplete_gaussian_patterns()
     permutation_outputs()
     mbde_outputs()

@@ -126,6 +126,71 @@ def test_gaussian_allsubs_and_roundrobin_run(engine):
     d.release()
 
 
+@pytest.mark.parametrize("key", ["all_incomplete", "mixed", "tiny"])
+def test_gaussian_subset_patterns_on_incomplete_data(engine, key):
+    """allsubs / roundrobin with cor, zf, mi-g, mi-g-sh when some columns hold missing
+    values: the reference's *_with_missing patterns (every subset on its own complete
+    rows, no early exit, no separating set; a subset without degrees of freedom ends
+    the request) against tests/golden/ref_incomplete_gaussian_patterns.json. In
+    "mixed" the requests on complete columns alone keep the complete-data pattern."""
+    import json
+    import os
+    from bnlearn_b200 import callsites as cs
+    from util import GOLDEN
+    with open(os.path.join(GOLDEN, "ref_incomplete_gaussian_patterns.json")) as f:
+        rec = json.load(f)[key]
+    z = np.load(os.path.join(GOLDEN, "data_gaussian_test_na.npz"))
+    vals = z["values"].copy()
+    if key != "all_incomplete":
+        _, full = load_gaussian("gaussian_test")
+        for c in range(3):
+            vals[c] = full[c][:vals.shape[1]]
+    if key == "tiny":
+        vals = vals[:, :9]
+    d = engine.register([np.ascontiguousarray(v) for v in vals])
+    counter = cs.TestCounter()
+    for r in rec["allsubs"]:
+        counter.reset()
+        nf = r["nfixed"]
+        p, pmin, pmax, dsep = cs.allsubs_test(d, r["x"], r["y"], r["sx"][nf:], r["sx"][:nf], r["test"],
+                                              r["alpha"], r["min"], r["max"], counter)
+        assert counter.value == r["counter"], (r, counter.value)
+        assert dsep == r["dsep"], (r, dsep)
+        tol = 1e-6 if r["test"] == "mi-g-sh" else 1e-9
+        for got, ref in ((p, r["p"]), (pmin, r["pmin"]), (pmax, r["pmax"])):
+            assert rel_close(got, ref, tol, 1e-300), (r, got, ref)
+    for r in rec["roundrobin"]:
+        counter.reset()
+        zz = r["z"]
+        pv = cs.roundrobin_test(d, r["x"], zz, zz[1:1 + r["nfixed"]], r["test"], r["alpha"], counter)
+        assert counter.value == r["counter"]
+        assert len(pv) == len(r["p"])
+        tol = 1e-6 if r["test"] == "mi-g-sh" else 1e-9
+        # Up to and including the first variable that is dropped the reference is the
+        # yardstick. After a drop, rrd_gaustests_with_missing refills cov.mat for one
+        # column fewer but leaves cov.dim as it was (roundrobin.test.c:324-325, where the
+        # complete-data pattern calls covariance_drop_variable, :202), so c_fast_pcor
+        # reads the new matrix with the old leading dimension: its later p-values are
+        # not the tests' (1.0, 0.0, ... in the fixture). From there on the sequence is
+        # checked against direct evaluation of the intended tests.
+        first_drop = next((i for i, v in enumerate(r["p"]) if v > r["alpha"]), len(r["p"]))
+        for got, ref in zip(pv[:first_drop + 1], r["p"][:first_drop + 1]):
+            assert rel_close(got, ref, tol, 1e-300), (r, list(pv))
+        live, cur, nfx = list(zz), 0, r["nfixed"]
+        for i, zi in enumerate(zz):
+            if len(live) < 2:
+                break
+            if 1 <= i <= nfx:
+                continue
+            _, df1, p1 = d.ci_gaussian(r["test"], [r["x"]], [zi], [[v for v in live if v != zi]])
+            expect = 1.0 if df1[0] == 0.0 else p1[0]
+            assert rel_close(pv[cur], expect, 1e-12, 1e-300), (r, cur, list(pv))
+            if df1[0] != 0.0 and p1[0] > r["alpha"]:
+                live.remove(zi)
+            cur += 1
+    d.release()
+
+
 def test_indep_test_with_mi_cg(engine):
     """mi-cg through the indep_test call site: p-values of the batched entry point,
     counter advanced by one per test."""
