@@ -395,7 +395,8 @@ extern "C" int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, d
 
 namespace {
 
-int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units_in, double *score, double *npar) {
+int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units_in, double *score, double *npar,
+                 bool nal = false, double kpen = 0.0) {
   const int n = (int)units_in.size();
   if (n == 0) return BNL_OK;
   BnlDevice &dev = ctx->devs[0];
@@ -462,7 +463,7 @@ int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units_in,
     pass(1);
     cg_means_kernel<<<dim3(8, (unsigned)n), 128, 0, dev.stream>>>(d_units, n, mom);
     pass(2);
-    cg_score_kernel<<<(n + 63) / 64, 64, 0, dev.stream>>>(d_units, n, mom, d_out);
+    cg_score_kernel<<<(n + 63) / 64, 64, 0, dev.stream>>>(d_units, n, mom, d_out, nal ? 1 : 0, kpen, ds.nobs);
     e = cudaGetLastError();
   }
   if (e == cudaSuccess)
@@ -475,7 +476,7 @@ int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units_in,
   if (e != cudaSuccess || es != cudaSuccess)
     return bnl_fail(ctx, BNL_ECUDA, "conditional Gaussian kernels failed: %s",
                     cudaGetErrorString(e != cudaSuccess ? e : es));
-  if (err)
+  if (err && !nal)                      // nal-cg / pnal-cg are the scores for incomplete data: rows are skipped
     return bnl_fail(ctx, BNL_EUNSUPPORTED,
                     "conditional Gaussian scores need complete data (a missing value was met)");
   for (int u = 0; u < n; u++) {
@@ -500,12 +501,17 @@ extern "C" int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, 
     for (int u = 0; u < n; u++) score[u] -= pen * (double)(pa_off[u + 1] - pa_off[u]);
     return BNL_OK;
   }
-  if (score_e != BNL_LOGLIK_CG && score_e != BNL_AIC_CG && score_e != BNL_BIC_CG)
+  const bool nal = score_e == BNL_NAL_CG || score_e == BNL_PNAL_CG;
+  if (score_e == BNL_NAL_CG) k = 0.0;     // per.node.score.c:405-408
+  if (score_e != BNL_LOGLIK_CG && score_e != BNL_AIC_CG && score_e != BNL_BIC_CG && !nal)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a conditional Gaussian score handled here", score_e);
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_cg: bad arguments");
-  const int d_code = score_e == BNL_LOGLIK_CG ? BNL_LOGLIK : (score_e == BNL_AIC_CG ? BNL_AIC : BNL_BIC);
-  const int g_code = score_e == BNL_LOGLIK_CG ? BNL_LOGLIK_G : (score_e == BNL_AIC_CG ? BNL_AIC_G : BNL_BIC_G);
+  // nal_cgnode (src/scores/cg.nal.c:118-200) splits the nodes the same way over
+  // nal_dnode_*, glik / cglik_incomplete and ccgnal.
+  const int d_code = nal ? BNL_PNAL : score_e == BNL_LOGLIK_CG ? BNL_LOGLIK : (score_e == BNL_AIC_CG ? BNL_AIC : BNL_BIC);
+  const int g_code = nal ? BNL_PNAL_G
+                         : score_e == BNL_LOGLIK_CG ? BNL_LOGLIK_G : (score_e == BNL_AIC_CG ? BNL_AIC_G : BNL_BIC_G);
   // three sub-requests in the caller's order, plus the nodes that cannot be scored.
   std::vector<int> didx, gidx, cidx;
   std::vector<int> dt, doff(1, 0), dpa, gt, goff(1, 0), gpa;
@@ -579,8 +585,8 @@ extern "C" int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, 
   }
   if (!cidx.empty()) {
     s.assign(cidx.size(), 0.0); p.assign(cidx.size(), 0.0);
-    if ((rc = run_cg_units(ctx, ds, cg, s.data(), p.data()))) return rc;
-    if (score_e != BNL_LOGLIK_CG)
+    if ((rc = run_cg_units(ctx, ds, cg, s.data(), p.data(), nal, k))) return rc;
+    if (score_e != BNL_LOGLIK_CG && !nal)
       for (size_t i = 0; i < cidx.size(); i++) s[i] -= k * p[i];      // per.node.score.c: res - k * nparams
     scatter(cidx);
   }

@@ -853,7 +853,7 @@ __device__ double cg_stratum_sse(double *S, const double *mean, double ns, int K
 // -Inf as soon as one of them is singular (sd < sqrt(eps), which includes
 // configurations with no more rows than coefficients).
 __global__ void cg_score_kernel(const BnlCgUnit *__restrict__ units, int n, const double *__restrict__ mom,
-                                double *__restrict__ out) {
+                                double *__restrict__ out, int nal, double kpen, long long nobs) {
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= n) return;
   const BnlCgUnit U = units[u];
@@ -861,12 +861,19 @@ __global__ void cg_score_kernel(const BnlCgUnit *__restrict__ units, int n, cons
   const double tol = bnl::kSqrtEps;
   bnl::KahanSum tot;
   bool singular = false;
+  double nc = 0.0;
   double S[BNL_CG_MAXG * BNL_CG_MAXG], mean[BNL_CG_MAXG];
   for (int s = 0; s < U.nconfig && !singular; s++) {
     const double *a = mom + U.off + (size_t)s * M;
     const double ns = a[0];
-    if (ns == 0.0) continue;                                       // sd = NA: no row refers to it
+    if (ns == 0.0) {
+      // sd = NA: no row refers to it. The node-average likelihood refuses the node
+      // (c_fast_ccgnal, src/scores/cg.nal.c:52-58), the log-likelihood skips it.
+      if (nal) singular = true;
+      continue;
+    }
     if (ns <= (double)(np + 1)) { singular = true; break; }       // sd = 0
+    nc += ns;
     int p = 1 + K;
     for (int i = 0; i < K; i++) {
       mean[i] = a[1 + i];
@@ -878,8 +885,13 @@ __global__ void cg_score_kernel(const BnlCgUnit *__restrict__ units, int n, cons
     if (!(sd >= tol)) { singular = true; break; }
     tot.add(-ns * (bnl::kLnSqrt2Pi + log(sd)) - 0.5 * sse / (sd * sd));
   }
-  out[(size_t)u * 4 + 0] = singular ? -INFINITY : tot.value();
-  out[(size_t)u * 4 + 1] = (double)U.nconfig * (double)(np + 2);
+  const double npar = (double)U.nconfig * (double)(np + 2);
+  double res = singular ? -INFINITY : tot.value();
+  // nal-cg / pnal-cg: averaged over the locally complete rows, penalty scaled by the
+  // full row count (src/scores/cg.nal.c:68-71).
+  if (nal && !singular) res = res / nc - kpen / (double)nobs * npar;
+  out[(size_t)u * 4 + 0] = res;
+  out[(size_t)u * 4 + 1] = npar;
   out[(size_t)u * 4 + 2] = 0.0;
   out[(size_t)u * 4 + 3] = 0.0;
 }

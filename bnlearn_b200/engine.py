@@ -14,7 +14,7 @@ from . import _lib
 TESTS = {"mi": 1, "mi-adf": 2, "x2": 3, "x2-adf": 4, "jt": 10, "mi-sh": 40, "cor": 20, "zf": 21, "mi-g": 22, "mi-cg": 30, "mi-g-sh": 41}
 SCORES = {"loglik": 1, "aic": 3, "bic": 4, "ebic": 5, "bde": 6, "bds": 7, "bdj": 8, "k2": 9, "mbde": 10, "fnml": 11, "qnml": 12, "nal": 13, "pnal": 14,
           "loglik-g": 100, "aic-g": 102, "bic-g": 103, "ebic-g": 104, "bge": 105, "nal-g": 106, "pnal-g": 107,
-          "loglik-cg": 200, "aic-cg": 202, "bic-cg": 203, "ebic-cg": 204}
+          "loglik-cg": 200, "aic-cg": 202, "bic-cg": 203, "ebic-cg": 204, "nal-cg": 205, "pnal-cg": 206}
 MC_TESTS = {"mc-mi": 50, "mc-x2": 51, "sp-mi": 52, "sp-x2": 53, "mc-jt": 54, "smc-mi": 60, "smc-x2": 61,
             "smc-jt": 62, "mc-cor": 70, "mc-mi-g": 71, "mc-zf": 72, "smc-cor": 80, "smc-mi-g": 81, "smc-zf": 82}
 DISCRETE_TESTS = ("mi", "mi-adf", "x2", "x2-adf", "jt", "mi-sh")

@@ -61,7 +61,8 @@ enum { BNL_LOGLIK = 1, BNL_AIC = 3, BNL_BIC = 4, BNL_EBIC = 5, BNL_BDE = 6, BNL_
        BNL_FNML = 11, BNL_QNML = 12, BNL_NAL = 13, BNL_PNAL = 14,
        BNL_LOGLIK_G = 100, BNL_AIC_G = 102, BNL_BIC_G = 103, BNL_EBIC_G = 104, BNL_BGE = 105, BNL_NAL_G = 106,
        BNL_PNAL_G = 107,
-       BNL_LOGLIK_CG = 200, BNL_AIC_CG = 202, BNL_BIC_CG = 203, BNL_EBIC_CG = 204 };
+       BNL_LOGLIK_CG = 200, BNL_AIC_CG = 202, BNL_BIC_CG = 203, BNL_EBIC_CG = 204, BNL_NAL_CG = 205,
+       BNL_PNAL_CG = 206 };
 
 /* ---- context ---------------------------------------------------------- */
 

@@ -10,7 +10,7 @@
 STUB(R_qsort) STUB(R_qsort_int) STUB(R_qsort_int_I) STUB(revsort)
 STUB(custom_score_function) STUB(custom_test_function)
 STUB(em_irls_node) STUB(fitted_node_to_enum) 
-STUB(nal_cgnode) STUB(predictive_loglik_cgnode)
+STUB(predictive_loglik_cgnode)
 STUB(predictive_loglik_dnode) STUB(predictive_loglik_gnode)
 
 /* globals the reference keeps in src/globals.c:17 (not compiled here). */

@@ -414,6 +414,45 @@ def cg_outputs():
     print("wrote ref_cg.json")
 
 
+def inject_missing(cols, nlev, seed=20261113, frac=0.05):
+    """The incomplete version of a mixed data set used by ref_cg_nal.json (the
+    test re-creates it from the same seed)."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for c, l in zip(cols, nlev):
+        c = c.copy()
+        m = rng.random(len(c)) < frac
+        c[m] = np.iinfo(np.int32).min if l > 0 else np.nan
+        out.append(c)
+    return out
+
+
+def cg_nal_outputs():
+    """nal-cg / pnal-cg (nal_cgnode, src/scores/cg.nal.c) on clgaussian.test with
+    5 % of the cells missing; own file and RNG."""
+    from oracle import refapi as ra, refbind as rb
+    names, columns, nlev = load_mixed("clgaussian_test")
+    columns = inject_missing(columns, nlev)
+    data = ra.RefData(columns, nlev, names)
+    rng = np.random.default_rng(20261114)
+    p, n = len(names), len(columns[0])
+    recs = []
+    for t in range(60):
+        k = int(rng.integers(0, 6))
+        idx = rng.choice(p, size=1 + k, replace=False)
+        node, pa = int(idx[0]), [int(i) for i in idx[1:]]
+        par = {names[node]: [names[i] for i in pa]}
+        for score, kw in (("nal-cg", {}), ("pnal-cg", {"k": np.log(n) / 2}), ("pnal-cg", {"k": 0.3})):
+            v = ra.per_node_score(data, par, [names[node]], score, **kw)[0]
+            recs.append({"score": score, "arg": list(kw.values())[0] if kw else 0.0, "node": node,
+                         "parents": pa, "value": float(v)})
+        rb.reset()
+        data.invalidate()
+    with open(os.path.join(HERE, "ref_cg_nal.json"), "w") as f:
+        json.dump({"clgaussian_test_na": {"seed": 20261113, "frac": 0.05, "scores": recs}}, f)
+    print("wrote ref_cg_nal.json")
+
+
 def ebic_outputs():
     """Extended BIC (ebic, ebic-g, ebic-cg) with the default gamma = 0.5 and with 0.3."""
     from oracle import refapi as ra, refbind as rb
@@ -659,6 +698,7 @@ if __name__ == "__main__":
     jt_shrinkage_outputs()
     nml_outputs()
     cg_outputs()
+    cg_nal_outputs()
     ebic_outputs()
     bge_outputs()
     mi_matrix_outputs()

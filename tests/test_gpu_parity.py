@@ -282,6 +282,38 @@ def test_conditional_gaussian_scores_against_reference_golden(engine):
     d.release()
 
 
+def test_conditional_gaussian_nal_scores_on_incomplete_data(engine):
+    """nal-cg / pnal-cg on clgaussian.test with 5 % of the cells missing (re-created
+    from the fixture's seed): discrete nodes (nal), Gaussian nodes with numeric parents
+    only (nal-g), mixed parents (c_fast_ccgnal over the conditional least squares on
+    locally complete rows) and the -Inf cases, against nal_cgnode of the reference."""
+    from util import load_mixed
+    with open(os.path.join(GOLDEN, "ref_cg_nal.json")) as f:
+        fx = json.load(f)["clgaussian_test_na"]
+    names, cols, nlev = load_mixed("clgaussian_test")
+    rng = np.random.default_rng(fx["seed"])
+    na = []
+    for c, l in zip(cols, nlev):
+        c = c.copy()
+        m = rng.random(len(c)) < fx["frac"]
+        c[m] = np.iinfo(np.int32).min if l > 0 else np.nan
+        na.append(c)
+    d = engine.register(na, nlev)
+    recs = fx["scores"]
+    for score, arg in sorted({(r["score"], r["arg"]) for r in recs}):
+        rs = [r for r in recs if r["score"] == score and r["arg"] == arg]
+        sc, _ = d.score_cg(score, [r["node"] for r in rs], [r["parents"] for r in rs], arg)
+        for i, r in enumerate(rs):
+            _check(sc[i], r["value"], ("score", r))
+    # the whole search runs on these scores (the data has missing values everywhere)
+    amat, scores, iters = d.hc("pnal-cg", np.log(len(cols[0])) / 2)
+    pa = [[int(i) for i in np.nonzero(amat[:, j])[0]] for j in range(len(cols))]
+    chk, _ = d.score_cg("pnal-cg", list(range(len(cols))), pa, np.log(len(cols[0])) / 2)
+    for j in range(len(cols)):
+        _check(scores[j], chk[j], ("hc node score", j))
+    d.release()
+
+
 def test_conditional_gaussian_tests_against_reference_golden(engine):
     """mi-cg on the bundled mixed data: all 16 combinations of factor / numeric x, y
     and conditioning sets, in one batched call."""
