@@ -109,3 +109,56 @@ def test_row_sharding_allreduce_world_size_2(tmp_path):
     ref = np.concatenate([orc.counts(cols[x], nlev[x], cols[y], nlev[y], [cols[j] for j in z],
                                      [nlev[j] for j in z]).ravel() for x, y, z in units])
     assert np.array_equal(got, ref)
+
+
+def _perm_worker(rank, world, port, batch, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import ctypes as C
+    from oracle import oracle as orc
+    names, cols, nlev = load_discrete("learning_test")
+    n = len(cols[0])
+    a, b = _block(n, world, rank)
+    res = batch["results"]
+    flat = [orc.counts(cols[r["x"]][a:b], nlev[r["x"]], cols[r["y"]][a:b], nlev[r["y"]],
+                       [cols[j][a:b] for j in r["z"]], [nlev[j] for j in r["z"]]).ravel() for r in res]
+    off = np.concatenate([[0], np.cumsum([len(t) for t in flat])]).astype(np.int64)
+    buf = torch.from_numpy(np.concatenate(flat).astype(np.int32))
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+    if rank == 0:                                         # the random stream lives on one rank
+        from bnlearn_b200 import _lib
+        lib = _lib.load()
+        tab = np.ascontiguousarray(buf.numpy(), dtype=np.int32)
+        m = len(res)
+        llx = np.array([nlev[r["x"]] for r in res], dtype=np.int32)
+        lly = np.array([nlev[r["y"]] for r in res], dtype=np.int32)
+        nz = np.array([len(r["z"]) for r in res], dtype=np.int32)
+        st, df, pv = (np.zeros(m) for _ in range(3))
+        state = C.c_uint64(batch["seed"])
+        ip = lambda v: v.ctypes.data_as(C.POINTER(C.c_int))
+        dp = lambda v: v.ctypes.data_as(C.POINTER(C.c_double))
+        rc = lib.bnl_mc_from_tables(None, 50, batch["B"], batch["alpha"], m, ip(llx), ip(lly), ip(nz),
+                                    tab.ctypes.data_as(C.POINTER(C.c_int32)),
+                                    off.ctypes.data_as(C.POINTER(C.c_int64)),
+                                    C.cast(lib.bnl_unif_splitmix64, C.c_void_p),
+                                    C.cast(C.pointer(state), C.c_void_p), dp(st), dp(df), dp(pv))
+        assert rc == 0
+        np.save(out_path, np.concatenate([st, pv]))
+    dist.destroy_process_group()
+
+
+def test_row_sharded_permutation_test_world_size_2(tmp_path):
+    """mc-mi with the rows split over two ranks: tables all-reduced, then
+    bnl_mc_from_tables on rank 0 gives the statistics and Monte Carlo p-values of the
+    reference's c_mcarlo / c_cmcarlo on the whole data (tests/golden/ref_permutation.json)."""
+    import json
+    from util import GOLDEN
+    with open(os.path.join(GOLDEN, "ref_permutation.json")) as f:
+        batch = [b for b in json.load(f)["learning_test"] if b["test"] == "mc-mi"][0]
+    out = str(tmp_path / "perm.npy")
+    mp.spawn(_perm_worker, args=(2, _free_port(), batch, out), nprocs=2, join=True)
+    got = np.load(out)
+    m = len(batch["results"])
+    assert np.array_equal(got[:m], np.array([r["stat"] for r in batch["results"]]))
+    assert np.array_equal(got[m:], np.array([r["p"] for r in batch["results"]]))
