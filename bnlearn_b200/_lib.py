@@ -46,6 +46,7 @@ SIGNATURES = {
     "bnl_score_gaussian": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p,
                                      c_int_p, c_int_p, c_dbl_p, c_dbl_p]),
     "bnl_gaussian_moments": (C.c_int, [C.c_void_p, C.c_uint64, c_dbl_p, c_dbl_p]),
+    "bnl_data_set_moments": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int64, c_dbl_p, c_dbl_p]),
     "bnl_indep_test": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, c_int_p, C.c_int, c_int_p,
                                  C.c_int, c_dbl_p, c_dbl_p, c_dbl_p, c_dbl_p]),
     "bnl_allsubs_test": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, c_int_p, c_int_p, c_int_p,

@@ -105,7 +105,7 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
     return bnl_fail(ctx, BNL_EINVAL, "bnl_allsubs_test: bad arguments");
   auto it = ctx->data.find(data);
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
-  const long long nobs = it->second.nobs;
+  const long long nobs = it->second.gauss_nobs > 0 && is_gaussian_test(test_e) ? it->second.gauss_nobs : it->second.nobs;
   const bool gauss = is_gaussian_test(test_e);
   if (!gauss && !is_discrete_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
@@ -320,7 +320,7 @@ extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int 
     return bnl_fail(ctx, BNL_EINVAL, "bnl_roundrobin_test: bad arguments");
   auto it = ctx->data.find(data);
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
-  const long long nobs = it->second.nobs;
+  const long long nobs = it->second.gauss_nobs > 0 && is_gaussian_test(test_e) ? it->second.gauss_nobs : it->second.nobs;
   const bool gauss = is_gaussian_test(test_e);
   if (!gauss && !is_discrete_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);

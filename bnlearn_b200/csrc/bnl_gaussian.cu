@@ -195,11 +195,11 @@ int run_gblock(bnl_ctx *ctx, BnlDataSet &ds, int d, GRequest &rq, int b, int e, 
   }
   if (rq.kind == 0)
     gauss_ci_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_b, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, ds.nc,
-                                                     ds.nobs, rq.code, rq.kmax, dev.d_out, d_err, ucov, unobs,
+                                                     ds.gauss_nobs > 0 ? ds.gauss_nobs : ds.nobs, rq.code, rq.kmax, dev.d_out, d_err, ucov, unobs,
                                                      ushr, m_chunks);
   else
     gauss_score_kernel<<<grid, tpb, smem, dev.stream>>>(d_a, d_off, d_idx, d_slot, ds.ncols, cnt, dd.cov, dd.mean,
-                                                        ds.nc, ds.nobs, rq.code,
+                                                        ds.nc, ds.gauss_nobs > 0 ? ds.gauss_nobs : ds.nobs, rq.code,
                                                         rq.code == BNL_BGE ? ds.bge_mu : rq.arg, rq.kmax,
                                                         dev.d_out, d_err, ucov, umean, unobs,
                                                         ds.bge_w > 0.0 ? ds.bge_w : (double)(ds.ncols + 2),
@@ -384,6 +384,35 @@ extern "C" int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, d
   if (ds.nc == 0) return bnl_fail(ctx, BNL_EINVAL, "the data set has no numeric columns");
   if (mean) memcpy(mean, ds.h_mean.data(), ds.h_mean.size() * sizeof(double));
   if (cov) memcpy(cov, ds.h_cov.data(), ds.h_cov.size() * sizeof(double));
+  return BNL_OK;
+}
+
+// Rows sharded over GPUs: every rank registers its block of
+// rows, reads its (mean, cov) with bnl_gaussian_moments, the ranks pool them (two
+// all-reduces over p and p^2 doubles, bnlearn_b200/replicate.py: pool_moments) and
+// each hands the pooled moments back here. From then on every Gaussian test and
+// score of this data set is served from them, with nobs_total rows.
+extern "C" int bnl_data_set_moments(bnl_ctx *ctx, bnl_data data, int64_t nobs_total, const double *mean,
+                                    const double *cov) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  if (ds.nc == 0) return bnl_fail(ctx, BNL_EINVAL, "the data set has no numeric columns");
+  if (!mean || !cov || nobs_total < ds.nobs)
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_data_set_moments: bad arguments");
+  if (ds.any_nan)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "pooled moments need complete numeric data");
+  const size_t p = (size_t)ds.nc;
+  for (size_t d = 0; d < ds.dev.size(); d++) {
+    BNL_CUDA(ctx, cudaSetDevice(ctx->devs[d].id));
+    BNL_CUDA(ctx, cudaMemcpy(ds.dev[d].mean, mean, p * sizeof(double), cudaMemcpyHostToDevice));
+    BNL_CUDA(ctx, cudaMemcpy(ds.dev[d].cov, cov, p * p * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  BNL_CUDA(ctx, cudaSetDevice(ctx->devs[0].id));
+  ds.h_mean.assign(mean, mean + p);
+  ds.h_cov.assign(cov, cov + p * p);
+  ds.gauss_nobs = nobs_total;
   return BNL_OK;
 }
 

@@ -102,6 +102,7 @@ struct BnlDataSet {
   bool committed = true;                // false between bnl_data_alloc and bnl_data_commit
   double bge_mu = 1.0, bge_w = -1.0;    // BGe imaginary sample sizes (bge_w < 0: ncols + 2)
   double ebic_gamma = 0.5;              // extended BIC (the front end's default)
+  long long gauss_nobs = 0;             // > 0: rows behind moments set by bnl_data_set_moments (row shards pooled)
   std::vector<int> mask_col;            // per column: its intervention mask column (mBDe), -1 none; empty: none set
 };
 

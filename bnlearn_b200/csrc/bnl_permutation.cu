@@ -499,6 +499,8 @@ extern "C" int bnl_ci_gaussian_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B
   if (ds.any_nan)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "permutation tests on incomplete numeric data are not handled here");
   if (ds.nobs > INT32_MAX) return bnl_fail(ctx, BNL_EUNSUPPORTED, "too many rows for a permutation test");
+  if (ds.gauss_nobs > 0)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "permutation tests need the rows, not pooled moments");
   if (!is_sequential(test_e)) alpha = 1.0;
   const double enough = ceil(alpha * B) + 1;
 

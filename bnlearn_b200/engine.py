@@ -435,6 +435,14 @@ class DataSet:
         e._check(e._lib.bnl_gaussian_moments(e._ctx, self.handle, _dp(mean), _dp(cov)))
         return mean, cov
 
+    def set_moments(self, nobs_total, mean, cov):
+        """Serve every Gaussian test / score of this data set from pooled moments
+        (rows sharded over GPUs: replicate.pool_moments)."""
+        e = self.engine
+        mean = np.ascontiguousarray(mean, dtype=np.float64)
+        cov = np.asfortranarray(cov, dtype=np.float64)
+        e._check(e._lib.bnl_data_set_moments(e._ctx, self.handle, int(nobs_total), _dp(mean), _dp(cov)))
+
     # ---- generic dispatch on the test / score label -------------------------
     def ci_test(self, test, x, y, z):
         return self.ci_discrete(test, x, y, z) if test in DISCRETE_TESTS else self.ci_gaussian(test, x, y, z)

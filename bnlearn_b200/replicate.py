@@ -39,3 +39,29 @@ def broadcast_dataset(engine, columns, nlevels, nobs, src=0):
     if rank != src:
         ds.commit()
     return ds
+
+
+def pool_moments(nobs, mean, cov, device=None):
+    """Pooled (nobs, mean, cov) of row blocks held by the ranks of the default
+    process group, from each rank's own (nobs, mean, cov with divisor nobs - 1):
+        n = sum n_r,  mean = sum n_r mean_r / n,
+        (n - 1) cov = sum [(n_r - 1) cov_r + n_r (mean_r - mean)(mean_r - mean)'].
+    Two sum all-reduces, over 1 + p and over p * p doubles (NCCL when `device` is a
+    CUDA device, gloo on the CPU). Every rank gets the result and passes it to
+    DataSet.set_moments ("for the Gram, one all-reduce")."""
+    import numpy as np
+    mean = np.asarray(mean, dtype=np.float64)
+    cov = np.asarray(cov, dtype=np.float64)
+    dev = device if device is not None else "cpu"
+    first = torch.empty(1 + mean.size, dtype=torch.float64)
+    first[0] = float(nobs)
+    first[1:] = torch.from_numpy(mean * float(nobs))
+    first = first.to(dev)
+    dist.all_reduce(first, op=dist.ReduceOp.SUM)
+    first = first.cpu().numpy()
+    n = first[0]
+    pooled_mean = first[1:] / n
+    d = mean - pooled_mean
+    second = torch.from_numpy((float(nobs) - 1.0) * cov + float(nobs) * np.outer(d, d)).to(dev)
+    dist.all_reduce(second, op=dist.ReduceOp.SUM)
+    return int(round(n)), pooled_mean, second.cpu().numpy() / (n - 1.0)

@@ -305,6 +305,17 @@ int bnl_ci_cg(bnl_ctx *ctx, bnl_data data, int n, const int *x, const int *y, co
  * Replaces c_meanvec + c_covmat over all numeric columns. */
 int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, double *cov);
 
+/* Rows sharded over GPUs, Gaussian half (the discrete half is bnl_counts +
+ * all-reduce + bnl_stat_from_tables): each rank registers its block of rows and
+ * reads its moments with bnl_gaussian_moments; the ranks pool them -- n = sum n_r,
+ * mean = sum n_r mean_r / n, (n - 1) cov = sum [(n_r - 1) cov_r + n_r (mean_r - mean)
+ * (mean_r - mean)'], two sum all-reduces over p and p^2 doubles -- and hand the result
+ * back here. Every Gaussian test and score of the data set is then served from the
+ * pooled moments with nobs_total rows (complete data only). Replaces c_covmat over
+ * the whole data (src/core/covariance.matrix.c:65-97). */
+int bnl_data_set_moments(bnl_ctx *ctx, bnl_data data, int64_t nobs_total, const double *mean,
+                         const double *cov);
+
 /* ---- call sites: drop-in bodies for the reference's per-call loops ----------
  * These keep the reference's semantics that consume the numbers: evaluation
  * order, early exit, min/max p-value tracking, and the exact test-counter

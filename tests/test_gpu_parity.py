@@ -725,6 +725,46 @@ def test_row_sharded_tables_give_the_unsharded_statistics(engine):
             d.release()
 
 
+def test_row_sharded_moments_give_the_unsharded_gaussian_statistics(engine):
+    """Gaussian half of the row-sharded run: three row blocks registered apart, their
+    (mean, cov) pooled as replicate.pool_moments pools them over the ranks, handed to
+    one of the shards with bnl_data_set_moments -- tests, scores and the subset
+    patterns then equal those of the whole data set (1e-9; the pooling changes the
+    order of the sums)."""
+    from bnlearn_b200 import callsites as cs
+    names, cols = load_gaussian("gaussian_test")
+    n = len(cols[0])
+    whole = engine.register(cols)
+    cuts = [0, n // 3, n // 2 + 17, n]
+    shards = [engine.register([c[a:b] for c in cols]) for a, b in zip(cuts[:-1], cuts[1:])]
+    ns = [b - a for a, b in zip(cuts[:-1], cuts[1:])]
+    moms = [s.moments() for s in shards]
+    mean = sum(k * m[0] for k, m in zip(ns, moms)) / n
+    ss = sum((k - 1) * m[1] + k * np.outer(m[0] - mean, m[0] - mean) for k, m in zip(ns, moms))
+    d = shards[0]
+    d.set_moments(n, mean, ss / (n - 1))
+    x, y, z = [0, 2, 4, 1, 6], [1, 3, 5, 0, 2], [[], [0], [1, 3], [2, 3, 4], [0, 1, 3, 4, 5]]
+    for test in ("cor", "zf", "mi-g"):
+        got, ref = d.ci_gaussian(test, x, y, z), whole.ci_gaussian(test, x, y, z)
+        assert np.array_equal(got[1], ref[1]), test                       # df: the pooled row count
+        for i in range(len(x)):
+            _check(got[0][i], ref[0][i], (test, "stat", i), atol=1e-12)
+            _check(got[2][i], ref[2][i], (test, "p", i), atol=1e-300)
+    for score, arg in (("loglik-g", 0.0), ("bic-g", np.log(n) / 2), ("bge", 0.0)):
+        got, ref = d.score_gaussian(score, x, z, arg), whole.score_gaussian(score, x, z, arg)
+        for i in range(len(x)):
+            _check(got[0][i], ref[0][i], (score, i))
+    c1, c2 = cs.TestCounter(), cs.TestCounter()
+    a = cs.allsubs_test(d, 0, 5, [1, 2, 3], [], "cor", 0.05, 0, 3, c1)
+    b = cs.allsubs_test(whole, 0, 5, [1, 2, 3], [], "cor", 0.05, 0, 3, c2)
+    assert a[3] == b[3] and c1.value == c2.value and rel_close(a[0], b[0], 1e-9, 1e-300)
+    from bnlearn_b200 import BnlError
+    with pytest.raises(BnlError):
+        d.ci_gaussian_mc("mc-cor", [0], [1], [[]], 10)                     # needs the rows
+    for q in shards + [whole]:
+        q.release()
+
+
 def test_alloc_fill_commit_equals_register(engine):
     """bnl_data_alloc / device_view / commit: a data set whose packed blocks are
     copied in on the device (what an NCCL broadcast does between ranks) answers like

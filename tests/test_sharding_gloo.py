@@ -162,3 +162,34 @@ def test_row_sharded_permutation_test_world_size_2(tmp_path):
     m = len(batch["results"])
     assert np.array_equal(got[:m], np.array([r["stat"] for r in batch["results"]]))
     assert np.array_equal(got[m:], np.array([r["p"] for r in batch["results"]]))
+
+
+def _moments_worker(rank, world, port, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from bnlearn_b200.replicate import pool_moments
+    from util import load_gaussian
+    names, cols = load_gaussian("gaussian_test")
+    x = np.array(cols)
+    a, b = _block(x.shape[1], world, rank)
+    blk = x[:, a:b]
+    n, mean, cov = pool_moments(b - a, blk.mean(axis=1), np.cov(blk), None)
+    if rank == 1:                                         # every rank holds the pooled moments
+        np.save(out_path, np.concatenate([[n], mean, cov.ravel()]))
+    dist.destroy_process_group()
+
+
+def test_row_sharded_gaussian_moments_world_size_2(tmp_path):
+    """Rows of numeric data sharded over two ranks: pool_moments (two sum
+    all-reduces) gives the means and the covariance matrix of the whole data."""
+    from util import load_gaussian
+    names, cols = load_gaussian("gaussian_test")
+    x = np.array(cols)
+    out = str(tmp_path / "moments.npy")
+    mp.spawn(_moments_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = np.load(out)
+    p = x.shape[0]
+    assert got[0] == x.shape[1]
+    assert np.allclose(got[1:1 + p], x.mean(axis=1), rtol=1e-13, atol=0)
+    assert np.allclose(got[1 + p:].reshape(p, p), np.cov(x), rtol=1e-12, atol=1e-15)
