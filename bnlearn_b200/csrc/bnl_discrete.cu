@@ -25,6 +25,11 @@ const long long kKnobGroup = env_ll("BNL_GROUP", 1);
 const long long kKnobGroupMinCols = env_ll("BNL_GROUP_MINCOLS", 3);
 const long long kKnobGroupWaves = env_ll("BNL_GROUP_WAVES", 0);   // 0: pick row chunks by the cost model
 const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
+// DRAM -> L2 prefetch of the candidates' own columns, in thread-passes ahead (0: off). Two passes
+// ahead is worth ~9 % on the base-index kernel with one unit per CTA and nothing on the group
+// kernel (profiles/r1b_l2_prefetch_sweep.log).
+const int kKnobPrefetch = (int)env_ll("BNL_L2_PREFETCH", 2);
+const int kKnobGroupPrefetch = (int)env_ll("BNL_GROUP_L2_PREFETCH", 0);
 const long long kKnobBased = env_ll("BNL_BASED", 1);
 const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
 const long long kKnobBasedWaves = env_ll("BNL_BASED_WAVES", 0);
@@ -433,7 +438,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         const int ts = ((bmax[K] << (LC + 2)) + 255) & ~255;                                                   \
         count_based_kernel<LC, NU, NT><<<(unsigned)(nt * ch), NT, (size_t)ts * based_nu[K], dev.stream>>>(      \
             dd.u8, ds.stride_u8, ds.nobs, dev.d_basecols, bstride, dev.d_units, dev.d_order + bbase,           \
-            dev.d_tiles + tbase, dev.d_tables, (int)nt, (int)ch, ts);                                          \
+            dev.d_tiles + tbase, dev.d_tables, (int)nt, (int)ch, ts, kKnobPrefetch);                                          \
         BNL_CUDA(ctx, cudaGetLastError());                                                                     \
         tm->launches++;                                                                                        \
         bbase += (int)bcls[K].size();                                                                          \
@@ -461,7 +466,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
 #define BNL_GROUP_LAUNCH(TS)                                                                          \
       count_group_kernel<512, TS><<<ggrid, 512, (size_t)smem, dev.stream>>>(                            \
           dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + n_ungrouped, dev.d_tiles, dev.d_tables, \
-          (int)ngtiles, ch, gstride)
+          (int)ngtiles, ch, gstride, kKnobGroupPrefetch)
       if (gstride == 16384) BNL_GROUP_LAUNCH(16384);
       else if (gstride == 32768) BNL_GROUP_LAUNCH(32768);
       else BNL_GROUP_LAUNCH(0);

@@ -23,6 +23,13 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
   return r;
 }
 
+// DRAM -> L2 ahead of the register pipeline: a column that only one CTA reads
+// (a candidate of a score_cache_fill batch) otherwise pays the full DRAM latency
+// inside the one-group-ahead register prefetch.
+__device__ __forceinline__ void prefetch_l2(const void *p) {
+  asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+}
+
 // ---------------------------------------------------------------------------
 // Generic counting: one CTA = (unit, row chunk). Each thread takes 16 rows at a
 // time (one 128-bit load per column), forms the 16 cell indices in registers and
@@ -491,7 +498,7 @@ __global__ void __launch_bounds__(NT)
 count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
                    const int2 *__restrict__ tiles, int *__restrict__ tables, int ntiles, int chunks,
-                   int tstride) {
+                   int tstride, int pf) {
   // unit j's table starts at j * tstride bytes: the same stride for every tile of
   // the launch (a kernel parameter, so the offset lives in a uniform register and
   // the update is PRMT + ATOMS [R + UR] with no address add in between).
@@ -542,6 +549,14 @@ count_group_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 #pragma unroll
     for (int j = 0; j < BNL_GROUP_MAX; j++)
       if (j < nu) R.cand[j] = ldg_stream(base4 + (s_q[j] + g32));
+    // the candidates' own columns, `pf` thread-passes further on (one 128-byte line
+    // covers 8 threads' loads: every 8th thread asks)
+    if (pf > 0 && (threadIdx.x & 7) == 0 && g + (long long)pf * NT < g1) {
+      const unsigned gp = g32 + (unsigned)pf * NT;
+#pragma unroll
+      for (int j = 0; j < BNL_GROUP_MAX; j++)
+        if (j < nu) prefetch_l2(base4 + (s_q[j] + gp));
+    }
   };
 
   GroupRegs cur, nxt;
@@ -664,7 +679,7 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
                    const uint16_t *__restrict__ basecols, size_t bstride,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
                    const int2 *__restrict__ tiles, int *__restrict__ tables, int ntiles, int chunks,
-                   int tstride) {
+                   int tstride, int pf) {
   extern __shared__ __align__(256) int hist[];        // unit j: tstride bytes from j * tstride
   __shared__ BnlUnit su;                               // first unit of the tile: run, shared columns
   __shared__ int s_cells[BNL_BASED_MAX], s_col[BNL_BASED_MAX];
@@ -706,6 +721,11 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 #pragma unroll
     for (int j = 0; j < NUMAX; j++)
       if (j < nu) R.c[j] = ldg_stream(cp[j] + g);
+    if (pf > 0 && (threadIdx.x & 7) == 0 && g + (long long)pf * NT < g1) {
+#pragma unroll
+      for (int j = 0; j < NUMAX; j++)
+        if (j < nu) prefetch_l2(cp[j] + g + (long long)pf * NT);
+    }
   };
   auto count = [&](const BasedRegs<NUMAX> &R) {
     const unsigned bw[8] = {R.b0.x, R.b0.y, R.b0.z, R.b0.w, R.b1.x, R.b1.y, R.b1.z, R.b1.w};
