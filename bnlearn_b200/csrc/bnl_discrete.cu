@@ -30,6 +30,7 @@ const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
 // kernel (profiles/r1b_l2_prefetch_sweep.log).
 const int kKnobPrefetch = (int)env_ll("BNL_L2_PREFETCH", 2);
 const int kKnobGroupPrefetch = (int)env_ll("BNL_GROUP_L2_PREFETCH", 0);
+const long long kKnobGroupMaxCells = env_ll("BNL_GROUP_MAXCELLS", 0);   // 0: whatever four tables per SM allow
 const long long kKnobBased = env_ll("BNL_BASED", 1);
 const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
 const long long kKnobBasedWaves = env_ll("BNL_BASED_WAVES", 0);
@@ -148,6 +149,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                        dev.max_smem - 1024));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_lane_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 8, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 4, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -196,14 +199,15 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     std::vector<char> grouped(cnt, 0);
     std::vector<std::vector<int>> runs, bruns;
     // base-column classes: counters per cell / units per tile (count_based_kernel)
-    const int kBasedClasses = 5;
-    const int based_cap[kBasedClasses] = {(dev.max_smem - 8192) / 128 / 4, (dev.max_smem - 8192) / 128 / 2,
+    const int kBasedClasses = 6;
+    const int based_cap[kBasedClasses] = {(dev.max_smem - 8192) / 128 / 8,
+                                          (dev.max_smem - 8192) / 128 / 4, (dev.max_smem - 8192) / 128 / 2,
                                           (dev.max_smem - 8192) / 128, (dev.max_smem - 8192) / 64,
                                           (dev.max_smem - 8192) / 32};
-    const int based_nu[kBasedClasses] = {4, 2, 1, 1, 1};
+    const int based_nu[kBasedClasses] = {8, 4, 2, 1, 1, 1};
     std::vector<int> bcls[kBasedClasses], based_run(cnt, -1);
     std::vector<int2> btiles[kBasedClasses];
-    int bmax[kBasedClasses] = {0, 0, 0, 0, 0};
+    int bmax[kBasedClasses] = {0, 0, 0, 0, 0, 0};
     const size_t bstride = (size_t)((ds.nobs + 15) / 16) * 16 + 128;   // uint16 elements per base column
     const size_t brun_bytes = bstride * sizeof(uint16_t);
     std::vector<int2> tiles;
@@ -244,7 +248,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       // maximal runs of consecutive units with the same base columns; inside a run
       // the small tables (at least four of them per SM) go to the group kernel, the
       // mid-size ones to the base-column kernel (count_based_kernel).
-      const int gcap = group_smem / (4 * 256);
+      int gcap = group_smem / (4 * 256);
+      if (kKnobGroupMaxCells > 0) gcap = std::min(gcap, (int)kKnobGroupMaxCells);
       const int bcap = based_cap[kBasedClasses - 1];       // 8 lane counters per cell
       int i = 0;
       while (i < cnt) {
@@ -254,8 +259,11 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           std::vector<int> small, big;
           for (int u = i; u < j; u++) {
             const BnlUnit &hu = dev.h_units[u];
-            if (hu.cells <= gcap) small.push_back(u);
-            else if (kKnobBased && hu.ncols >= kKnobBasedMinCols && hu.cells <= bcap) big.push_back(u);
+            const bool based_ok = kKnobBased && hu.ncols >= kKnobBasedMinCols && hu.cells <= bcap;
+            // tables past 32 KiB at 64 counters per cell: four of them per SM in the group
+            // kernel, eight at 32 counters per cell in the base-index kernel (3 % faster)
+            if (hu.cells <= gcap && !(based_ok && hu.cells > 128)) small.push_back(u);
+            else if (based_ok) big.push_back(u);
           }
           if (small.size() >= 4) runs.push_back(std::move(small));
           // the base-index column costs 2 bytes per row of scratch and one extra pass
@@ -444,11 +452,12 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         bbase += (int)bcls[K].size();                                                                          \
         tbase += btiles[K].size();                                                                             \
       }
-      BNL_BASED_LAUNCH(0, 5, 4, 512)
+      BNL_BASED_LAUNCH(0, 5, 8, 256)
       BNL_BASED_LAUNCH(1, 5, 4, 512)
-      BNL_BASED_LAUNCH(2, 5, 1, 1024)
-      BNL_BASED_LAUNCH(3, 4, 1, 1024)
-      BNL_BASED_LAUNCH(4, 3, 1, 1024)
+      BNL_BASED_LAUNCH(2, 5, 4, 512)
+      BNL_BASED_LAUNCH(3, 5, 1, 1024)
+      BNL_BASED_LAUNCH(4, 4, 1, 1024)
+      BNL_BASED_LAUNCH(5, 3, 1, 1024)
 #undef BNL_BASED_LAUNCH
     }
     if (groups > 0 && ngtiles > 0) {

@@ -659,7 +659,7 @@ combine_base_kernel(const uint8_t *__restrict__ u8, size_t stride, long long ful
 // a tile of up to NUMAX units of one run (tables of <= ~445 cells: four per SM,
 // <= ~890: two), so the base column is loaded once per tile: (2 + nu) / nu bytes
 // per row-unit through L2. tiles[] = {first position in `order`, units}.
-#define BNL_BASED_MAX 4
+#define BNL_BASED_MAX 8
 
 template <int LC>
 __device__ __forceinline__ void based_bump(int *hist, unsigned v, unsigned slot4) {
