@@ -31,6 +31,9 @@ const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
 const int kKnobPrefetch = (int)env_ll("BNL_L2_PREFETCH", 2);
 const int kKnobGroupPrefetch = (int)env_ll("BNL_GROUP_L2_PREFETCH", 0);
 const long long kKnobGroupMaxCells = env_ll("BNL_GROUP_MAXCELLS", 0);   // 0: whatever four tables per SM allow
+// units per CTA of the base-index kernel. One unit and 1024 threads, with two CTAs per SM where the
+// tables allow, beat tiles of 2-8 units that share the base column (profiles/r1b_l2_prefetch_sweep.log).
+const long long kKnobBasedNuCap = env_ll("BNL_BASED_NU_CAP", 1);
 const long long kKnobBased = env_ll("BNL_BASED", 1);
 const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
 const long long kKnobBasedWaves = env_ll("BNL_BASED_WAVES", 0);
@@ -204,7 +207,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                           (dev.max_smem - 8192) / 128 / 4, (dev.max_smem - 8192) / 128 / 2,
                                           (dev.max_smem - 8192) / 128, (dev.max_smem - 8192) / 64,
                                           (dev.max_smem - 8192) / 32};
-    const int based_nu[kBasedClasses] = {8, 4, 2, 1, 1, 1};
+    int based_nu[kBasedClasses] = {8, 4, 2, 1, 1, 1};
+    for (int k = 0; k < kBasedClasses; k++) based_nu[k] = std::min(based_nu[k], (int)kKnobBasedNuCap);
     std::vector<int> bcls[kBasedClasses], based_run(cnt, -1);
     std::vector<int2> btiles[kBasedClasses];
     int bmax[kBasedClasses] = {0, 0, 0, 0, 0, 0};
@@ -452,9 +456,10 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         bbase += (int)bcls[K].size();                                                                          \
         tbase += btiles[K].size();                                                                             \
       }
-      BNL_BASED_LAUNCH(0, 5, 8, 256)
-      BNL_BASED_LAUNCH(1, 5, 4, 512)
-      BNL_BASED_LAUNCH(2, 5, 4, 512)
+      // one unit per tile: the 1024-thread kernel, several CTAs per SM when the tables allow
+      if (based_nu[0] == 1) { BNL_BASED_LAUNCH(0, 5, 1, 1024) } else { BNL_BASED_LAUNCH(0, 5, 8, 256) }
+      if (based_nu[1] == 1) { BNL_BASED_LAUNCH(1, 5, 1, 1024) } else { BNL_BASED_LAUNCH(1, 5, 4, 512) }
+      if (based_nu[2] == 1) { BNL_BASED_LAUNCH(2, 5, 1, 1024) } else { BNL_BASED_LAUNCH(2, 5, 4, 512) }
       BNL_BASED_LAUNCH(3, 5, 1, 1024)
       BNL_BASED_LAUNCH(4, 4, 1, 1024)
       BNL_BASED_LAUNCH(5, 3, 1, 1024)
