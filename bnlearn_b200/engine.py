@@ -254,7 +254,7 @@ class DataSet:
         fn, state, keep = self._unif(seed, unif)
         e._check(e._lib.bnl_ci_discrete_mc(e._ctx, self.handle, MC_TESTS[test], int(B), float(alpha), n, _ip(x),
                                            _ip(y), _ip(zo), _ip(zi), fn, state, _dp(st), _dp(df), _dp(pv)))
-        del keep
+        self.last_stream_state = keep.value if unif is None else None     # splitmix64 state after the call
         return st[:n], df[:n], pv[:n]
 
     def ci_gaussian_mc(self, test, x, y, z, B, alpha=1.0, seed=1, unif=None):
@@ -268,7 +268,7 @@ class DataSet:
         fn, state, keep = self._unif(seed, unif)
         e._check(e._lib.bnl_ci_gaussian_mc(e._ctx, self.handle, MC_TESTS[test], int(B), float(alpha), n, _ip(x),
                                            _ip(y), _ip(zo), _ip(zi), fn, state, _dp(st), _dp(pv)))
-        del keep
+        self.last_stream_state = keep.value if unif is None else None
         return st[:n], pv[:n]
 
     def score_discrete(self, score, target, parents, arg=0.0):

@@ -91,6 +91,7 @@ def lib():
                          c_dbl_p, c_dbl_p, c_dbl_p, c_int_p, C.c_bool]),
         # permutation tests (src/tests/permutation/*.c); the uniform stream is the shim's
         "minir_rng_seed": (None, [C.c_ulonglong]),
+        "minir_rng_peek": (C.c_ulonglong, []),
         "c_mcarlo": (None, [c_int_p, C.c_int, c_int_p, C.c_int, C.c_int, C.c_int, c_dbl_p, c_dbl_p,
                             C.c_double, C.c_int, c_dbl_p]),
         "c_cmcarlo": (None, [c_int_p, C.c_int, c_int_p, C.c_int, c_int_p, C.c_int, C.c_int, C.c_int,

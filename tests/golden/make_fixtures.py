@@ -593,7 +593,7 @@ def permutation_outputs():
     c_mcarlo / c_cmcarlo (and the Gaussian c_gauss_mcarlo / c_gauss_cmcarlo) with the
     shim's splitmix64 stream: every batch is seeded once and its tests then share
     the stream, as the tests of one R session do. Own file."""
-    from oracle import refapi as ra
+    from oracle import refapi as ra, refbind as rb
     out = {}
     for ds in ("learning_test", "learning_test_na"):
         names, codes, nlev = load_discrete(ds)
@@ -612,7 +612,8 @@ def permutation_outputs():
                                            [codes[i] for i in z], [int(nlev[i]) for i in z], B=B, alpha=alpha,
                                            seed=seed if k == 0 else None)
                 res.append({"x": x, "y": y, "z": z, "stat": st, "df": None if np.isnan(df) else df, "p": p})
-            batches.append({"test": test, "B": B, "alpha": alpha, "seed": seed, "results": res})
+            batches.append({"test": test, "B": B, "alpha": alpha, "seed": seed, "results": res,
+                            "end_state": str(rb.lib().minir_rng_peek())})      # where the stream stands afterwards
         out[ds] = batches
     names, vals = load_gaussian("gaussian_test")
     vals = [np.ascontiguousarray(v) for v in vals]
@@ -625,7 +626,8 @@ def permutation_outputs():
             st, p = ra.mc_gaussian(test, [vals[x], vals[y]] + [vals[i] for i in z], B=B, alpha=alpha,
                                    seed=seed if k == 0 else None)
             res.append({"x": x, "y": y, "z": z, "stat": st, "p": p})
-        batches.append({"test": test, "B": B, "alpha": alpha, "seed": seed, "results": res})
+        batches.append({"test": test, "B": B, "alpha": alpha, "seed": seed, "results": res,
+                        "end_state": str(rb.lib().minir_rng_peek())})
     out["gaussian_test"] = batches
     with open(os.path.join(HERE, "ref_permutation.json"), "w") as f:
         json.dump(out, f)
