@@ -40,6 +40,13 @@ SIGNATURES = {
                                      c_i32_p, c_i64_p, C.c_void_p, C.c_void_p, c_dbl_p, c_dbl_p, c_dbl_p]),
     "bnl_ci_gaussian_mc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_double, C.c_int, c_int_p,
                                      c_int_p, c_int_p, c_int_p, C.c_void_p, C.c_void_p, c_dbl_p, c_dbl_p]),
+    "bnl_indep_test_mc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p,
+                                    C.c_int, c_int_p, C.c_int, c_int_p, C.c_int, c_dbl_p, c_dbl_p, c_dbl_p, c_dbl_p]),
+    "bnl_allsubs_test_mc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                      C.c_int, c_int_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, c_dbl_p,
+                                      c_int_p, c_int_p, c_dbl_p]),
+    "bnl_roundrobin_test_mc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                         c_int_p, C.c_int, c_int_p, C.c_double, c_dbl_p, c_dbl_p]),
     "bnl_ci_discrete_mc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_double, C.c_int, c_int_p,
                                      c_int_p, c_int_p, c_int_p, C.c_void_p, C.c_void_p, c_dbl_p, c_dbl_p,
                                      c_dbl_p]),

@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .engine import SCORES, TESTS, csr
+from .engine import MC_TESTS, SCORES, TESTS, csr
 
 
 class TestCounter:
@@ -35,6 +35,26 @@ class TestCounter:
         return C.byref(self._v)
 
 
+class UniformStream:
+    """The uniform stream handed to the permutation tests: the library's splitmix64
+    on `seed` (the state carries over from call to call, like R's .Random.seed), or a
+    Python callable `unif(state) -> float in (0, 1)`. `B` permutations per test."""
+
+    def __init__(self, lib, B, seed=1, unif=None):
+        self.B = int(B)
+        if unif is not None:
+            self._cb = C.CFUNCTYPE(C.c_double, C.c_void_p)(unif)
+            self.fn, self.state, self._seed = C.cast(self._cb, C.c_void_p), None, None
+        else:
+            self._seed = C.c_uint64(int(seed))
+            self.fn = C.cast(lib.bnl_unif_splitmix64, C.c_void_p)
+            self.state = C.cast(C.pointer(self._seed), C.c_void_p)
+
+    @property
+    def position(self):
+        return None if self._seed is None else self._seed.value
+
+
 def _ip(a):
     return a.ctypes.data_as(_lib.c_int_p)
 
@@ -43,12 +63,19 @@ def _dp(a):
     return a.ctypes.data_as(_lib.c_dbl_p)
 
 
-def indep_test(ds, x, y, sx, test, counter):
-    """indep.test(x, y, sx, learning = TRUE): p-values of each x[i] vs y given sx."""
+def indep_test(ds, x, y, sx, test, counter, stream=None, alpha=1.0):
+    """indep.test(x, y, sx, learning = TRUE): p-values of each x[i] vs y given sx.
+    Permutation tests (mc-*, smc-*, sp-*) need a UniformStream; alpha is the
+    early-stopping threshold of the smc-* tests."""
     e = ds.engine
     xs = np.ascontiguousarray([x] if np.isscalar(x) else x, dtype=np.int32)
     s = np.ascontiguousarray(list(sx) or [0], dtype=np.int32)
     pv = np.zeros(max(len(xs), 1))
+    if test in MC_TESTS:
+        e._check(e._lib.bnl_indep_test_mc(e._ctx, ds.handle, MC_TESTS[test], stream.B, float(alpha), stream.fn,
+                                          stream.state, len(xs), _ip(xs), int(y), _ip(s), len(sx), _dp(pv),
+                                          None, None, counter.ref()))
+        return pv[:len(xs)]
     e._check(e._lib.bnl_indep_test(e._ctx, ds.handle, TESTS[test], len(xs), _ip(xs), int(y), _ip(s),
                                    len(sx), _dp(pv), None, None, counter.ref()))
     return pv[:len(xs)]
@@ -87,15 +114,24 @@ def allsubs_test_batch(ds, x, y, sx, nfixed, test, alpha, minsize, maxsize, coun
     return res
 
 
-def allsubs_test(ds, x, y, sx, fixed, test, alpha, minsize, maxsize, counter):
+def allsubs_test(ds, x, y, sx, fixed, test, alpha, minsize, maxsize, counter, stream=None):
     """allsubs.test(x, y, sx, fixed, ...) (R/test.R:22-39): sx excludes `fixed`;
     max is capped at length(sx) as the R wrapper does."""
     full = list(fixed) + list(sx)
+    if test in MC_TESTS:
+        e = ds.engine
+        s = np.ascontiguousarray(full or [0], dtype=np.int32)
+        out, dsep, nds = np.zeros(3), np.zeros(max(len(full), 1), dtype=np.int32), np.zeros(1, dtype=np.int32)
+        e._check(e._lib.bnl_allsubs_test_mc(e._ctx, ds.handle, MC_TESTS[test], stream.B, stream.fn, stream.state,
+                                            int(x), int(y), _ip(s), len(full), len(fixed), int(minsize),
+                                            int(min(maxsize, len(sx))), float(alpha), _dp(out), _ip(dsep),
+                                            _ip(nds), counter.ref()))
+        return out[0], out[1], out[2], None if nds[0] < 0 else [int(v) for v in dsep[:nds[0]]]
     return allsubs_test_batch(ds, [x], [y], [full], [len(fixed)], test, alpha, minsize,
                               min(maxsize, len(sx)), counter)[0]
 
 
-def roundrobin_test(ds, x, z, fixed, test, alpha, counter):
+def roundrobin_test(ds, x, z, fixed, test, alpha, counter, stream=None):
     """roundrobin.test(x, z, fixed, ...): p-values in the order of the non-fixed z."""
     e = ds.engine
     if len(z) == 0:
@@ -103,6 +139,11 @@ def roundrobin_test(ds, x, z, fixed, test, alpha, counter):
     zz = np.ascontiguousarray(z, dtype=np.int32)
     fx = np.array([1 if v in set(fixed) else 0 for v in z], dtype=np.int32)
     pv = np.zeros(max(len(z) - int(fx.sum()), 1))
+    if test in MC_TESTS:
+        e._check(e._lib.bnl_roundrobin_test_mc(e._ctx, ds.handle, MC_TESTS[test], stream.B, stream.fn,
+                                               stream.state, int(x), _ip(zz), len(zz), _ip(fx), float(alpha),
+                                               _dp(pv), counter.ref()))
+        return pv[:len(z) - int(fx.sum())]
     e._check(e._lib.bnl_roundrobin_test(e._ctx, ds.handle, TESTS[test], int(x), _ip(zz), len(zz),
                                         _ip(fx), float(alpha), _dp(pv), counter.ref()))
     return pv[:len(z) - int(fx.sum())]

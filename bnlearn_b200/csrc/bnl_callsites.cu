@@ -21,6 +21,22 @@ bool is_discrete_score(int s) {
          s == BNL_QNML;
 }
 
+// Permutation tests reach the call sites through the *_mc entry points below, which
+// park the number of permutations, the early-stopping threshold and the caller's
+// uniform stream here for the duration of the call (a context is used by one host
+// thread at a time; thread_local keeps contexts on other threads apart).
+struct McArgs { int B; double alpha; bnl_unif_fn unif; void *state; };
+thread_local const McArgs *g_mc = nullptr;
+bool is_mc_discrete(int t) {
+  return t == BNL_MC_MI || t == BNL_MC_X2 || t == BNL_SP_MI || t == BNL_SP_X2 || t == BNL_MC_JT ||
+         t == BNL_SMC_MI || t == BNL_SMC_X2 || t == BNL_SMC_JT;
+}
+bool is_mc_gaussian(int t) {
+  return t == BNL_MC_COR || t == BNL_MC_ZF || t == BNL_MC_MI_G || t == BNL_SMC_COR || t == BNL_SMC_ZF ||
+         t == BNL_SMC_MI_G;
+}
+bool is_mc_test(int t) { return g_mc && (is_mc_discrete(t) || is_mc_gaussian(t)); }
+
 // one batch of CI tests through the matching kernel path.
 int run_tests(bnl_ctx *ctx, bnl_data data, int test_e, const std::vector<int> &x,
               const std::vector<int> &y, const std::vector<int> &zoff, const std::vector<int> &zidx,
@@ -37,6 +53,13 @@ int run_tests(bnl_ctx *ctx, bnl_data data, int test_e, const std::vector<int> &x
                            df.data(), pv.data());
   if (test_e == BNL_MI_CG)
     return bnl_ci_cg(ctx, data, n, x.data(), y.data(), zoff.data(), zi, st.data(), df.data(), pv.data());
+  // permutation tests: in the order given, which is the order the stream is consumed in
+  if (g_mc && is_mc_discrete(test_e))
+    return bnl_ci_discrete_mc(ctx, data, test_e, g_mc->B, g_mc->alpha, n, x.data(), y.data(), zoff.data(), zi,
+                              g_mc->unif, g_mc->state, st.data(), df.data(), pv.data());
+  if (g_mc && is_mc_gaussian(test_e))
+    return bnl_ci_gaussian_mc(ctx, data, test_e, g_mc->B, g_mc->alpha, n, x.data(), y.data(), zoff.data(), zi,
+                              g_mc->unif, g_mc->state, st.data(), pv.data());
   return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
 }
 
@@ -107,7 +130,7 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   const long long nobs = it->second.gauss_nobs > 0 && is_gaussian_test(test_e) ? it->second.gauss_nobs : it->second.nobs;
   const bool gauss = is_gaussian_test(test_e);
-  if (!gauss && !is_discrete_test(test_e))
+  if (!gauss && !is_discrete_test(test_e) && !is_mc_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
   // A request whose columns are not all complete takes the reference's
   // *_with_missing pattern (rinterface/allsubs.test.c:72, 103-113): every subset is
@@ -171,7 +194,13 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
   // (2) subsets, size by size, in rounds: every live request contributes its
   // next run of subsets (bounded), the batch is evaluated, and each request
   // replays its results in order until its first p-value > alpha.
-  const int kPerReqCap = n > 64 ? 64 : 4096;
+  // Permutation tests draw from the caller's stream subset after subset: nothing may be
+  // evaluated past the early exit (ast_dperm / ast_gperm, patterns/allsubs.test.c:825-1026),
+  // and with several requests the stream would have to pass from one to the next.
+  const bool mc = is_mc_test(test_e);
+  if (mc && n > 1)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "permutation tests take one allsubs request per call");
+  const int kPerReqCap = mc ? 1 : (n > 64 ? 64 : 4096);
   for (;;) {
     bx.clear(); by.clear(); bidx.clear(); owner.clear();
     boff.assign(1, 0);
@@ -322,7 +351,7 @@ extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int 
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   const long long nobs = it->second.gauss_nobs > 0 && is_gaussian_test(test_e) ? it->second.gauss_nobs : it->second.nobs;
   const bool gauss = is_gaussian_test(test_e);
-  if (!gauss && !is_discrete_test(test_e))
+  if (!gauss && !is_discrete_test(test_e) && !is_mc_test(test_e))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
   // columns with missing values: rrd_gaustests_with_missing (each test on the rows
   // complete for the variables still in play; a test without degrees of freedom gives
@@ -612,4 +641,51 @@ extern "C" int bnl_ci_cg(bnl_ctx *ctx, bnl_data data, int n, const int *x, const
     if (pvalue) pvalue[u] = bnl::pchisq_upper(s, d);
   }
   return BNL_OK;
+}
+
+// ---- the same call sites with a permutation test (mc-*, smc-*, sp-*) ----------
+// B permutations, the early-stopping threshold of the sequential tests (the
+// reference passes its alpha there and 1 otherwise; only smc-* use it) and the
+// caller's uniform stream; everything else as in the plain entry points.
+
+extern "C" int bnl_indep_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, double alpha, bnl_unif_fn unif,
+                                 void *unif_state, int nx, const int *x, int y, const int *sx, int nsx,
+                                 double *pvalue, double *stat, double *df, double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (!(is_mc_discrete(test_e) || is_mc_gaussian(test_e)))
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a permutation test", test_e);
+  const McArgs a{B, alpha, unif, unif_state};
+  g_mc = &a;
+  const int rc = bnl_indep_test(ctx, data, test_e, nx, x, y, sx, nsx, pvalue, stat, df, test_counter);
+  g_mc = nullptr;
+  return rc;
+}
+
+extern "C" int bnl_allsubs_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, bnl_unif_fn unif,
+                                   void *unif_state, int x, int y, const int *sx, int nsx, int nfixed,
+                                   int minsize, int maxsize, double alpha, double *out, int *dsep, int *ndsep,
+                                   double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (!(is_mc_discrete(test_e) || is_mc_gaussian(test_e)))
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a permutation test", test_e);
+  const McArgs a{B, alpha, unif, unif_state};
+  const int off[2] = {0, nsx};
+  g_mc = &a;
+  const int rc = bnl_allsubs_test(ctx, data, test_e, 1, &x, &y, off, sx, &nfixed, minsize, maxsize, alpha, out,
+                                  off, dsep, ndsep, test_counter);
+  g_mc = nullptr;
+  return rc;
+}
+
+extern "C" int bnl_roundrobin_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, bnl_unif_fn unif,
+                                      void *unif_state, int x, const int *z, int nz, const int *is_fixed,
+                                      double alpha, double *pvalue, double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  if (!(is_mc_discrete(test_e) || is_mc_gaussian(test_e)))
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a permutation test", test_e);
+  const McArgs a{B, alpha, unif, unif_state};
+  g_mc = &a;
+  const int rc = bnl_roundrobin_test(ctx, data, test_e, x, z, nz, is_fixed, alpha, pvalue, test_counter);
+  g_mc = nullptr;
+  return rc;
 }

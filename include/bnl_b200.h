@@ -414,6 +414,23 @@ int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int x, const in
                         const int *is_fixed, double alpha, double *pvalue,
                         double *test_counter);
 
+/* The three call sites above with a permutation test (mc-*, smc-*, sp-*; ut_dperm /
+ * ct_dperm / ut_gperm / ct_gperm, ast_dperm / ast_gperm, rrd_dperm / rrd_gperm in
+ * src/tests/patterns/): B permutations per test and the caller's uniform stream
+ * (see bnl_ci_discrete_mc). alpha is also the early-stopping threshold of the smc-*
+ * tests, as in the reference's callers. The tests are evaluated strictly in the
+ * reference's order and nothing is drawn past an early exit, so the stream ends
+ * where the reference leaves it; allsubs therefore takes one request per call. */
+int bnl_indep_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, double alpha, bnl_unif_fn unif,
+                      void *unif_state, int nx, const int *x, int y, const int *sx, int nsx,
+                      double *pvalue, double *stat, double *df, double *test_counter);
+int bnl_allsubs_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, bnl_unif_fn unif, void *unif_state,
+                        int x, int y, const int *sx, int nsx, int nfixed, int minsize, int maxsize,
+                        double alpha, double *out, int *dsep, int *ndsep, double *test_counter);
+int bnl_roundrobin_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, bnl_unif_fn unif,
+                           void *unif_state, int x, const int *z, int nz, const int *is_fixed, double alpha,
+                           double *pvalue, double *test_counter);
+
 /* score_cache_fill (src/learning/score/hc.cache.lookup.c:10-128): the score delta
  * of adding (amat[i,j] == 0) or dropping (amat[i,j] == 1) arc i -> j for every
  * j in updated[], i != j, not blacklisted, with the score-equivalence copy rule

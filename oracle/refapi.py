@@ -62,6 +62,8 @@ def _extra(score=None, k=None, iss=None, B=None, bge=None, gamma=None, exp=None)
         names += ["iss.mu", "iss.w", "nu", "prior"]
         items += [L.Rf_ScalarReal(float(iss_mu)), L.Rf_ScalarReal(float(iss_w)), nu_s,
                   L.Rf_mkString(b"uniform")]
+    if B is not None:                         # permutations of the mc-* / smc-* / sp-* tests
+        names.append("B"); items.append(L.Rf_ScalarInteger(int(B)))
     if k is not None:
         names.append("k"); items.append(L.Rf_ScalarReal(float(k)))
     if iss is not None:
@@ -83,14 +85,14 @@ def per_node_score(data, parents, targets, score, k=None, iss=None, bge=None, ga
     return rb.to_numpy(res)
 
 
-def indep_test(data, x, y, sx, test, alpha=0.05):
+def indep_test(data, x, y, sx, test, alpha=0.05, B=None):
     """reference indep_test(..., learning = TRUE) (src/tests/rinterface/indep.test.c:5-19):
     x may be several names; returns the p-value vector. Bumps test_counter."""
     L = rb.lib()
     xs = [x] if isinstance(x, str) else list(x)
     res = L.indep_test(rb.strvec(xs), rb.strvec([y]), rb.strvec(list(sx)), data.df(),
                        L.Rf_mkString(test.encode()), L.Rf_ScalarReal(alpha),
-                       rb.rlist([], []), L.Rf_ScalarLogical(1), data.complete())
+                       _extra(B=B), L.Rf_ScalarLogical(1), data.complete())
     return rb.to_numpy(res)
 
 
@@ -111,13 +113,13 @@ def ci_test(data, x, y, sx, test):
     return out.get("statistic"), out.get("parameter"), out.get("p.value")
 
 
-def allsubs_test(data, x, y, sx, fixed, test, alpha, minsize, maxsize):
+def allsubs_test(data, x, y, sx, fixed, test, alpha, minsize, maxsize, B=None):
     """reference allsubs_test (src/tests/rinterface/allsubs.test.c:10-210).
     Returns (p.value, min.p.value, max.p.value, dsep.set or None)."""
     L = rb.lib()
     res = L.allsubs_test(rb.strvec([x]), rb.strvec([y]), rb.strvec(list(sx)),
                          rb.strvec(list(fixed)), data.df(), L.Rf_mkString(test.encode()),
-                         L.Rf_ScalarReal(alpha), rb.rlist([], []),
+                         L.Rf_ScalarReal(alpha), _extra(B=B),
                          L.Rf_ScalarInteger(minsize), L.Rf_ScalarInteger(maxsize),
                          data.complete(), L.Rf_ScalarLogical(0))
     p = rb.to_numpy(res)
@@ -125,12 +127,12 @@ def allsubs_test(data, x, y, sx, fixed, test, alpha, minsize, maxsize):
     return float(p[0]), float(p[1]), float(p[2]), ds
 
 
-def roundrobin_test(data, x, z, fixed, test, alpha):
+def roundrobin_test(data, x, z, fixed, test, alpha, B=None):
     """reference roundrobin_test (src/tests/rinterface/roundrobin.test.c:10-154)."""
     L = rb.lib()
     res = L.roundrobin_test(rb.strvec([x]), rb.strvec(list(z)), rb.strvec(list(fixed)),
                             data.df(), L.Rf_mkString(test.encode()), L.Rf_ScalarReal(alpha),
-                            rb.rlist([], []), data.complete(), L.Rf_ScalarLogical(0))
+                            _extra(B=B), data.complete(), L.Rf_ScalarLogical(0))
     return rb.to_numpy(res)
 
 

@@ -629,6 +629,68 @@ def permutation_outputs():
         batches.append({"test": test, "B": B, "alpha": alpha, "seed": seed, "results": res,
                         "end_state": str(rb.lib().minir_rng_peek())})
     out["gaussian_test"] = batches
+    # the call sites with permutation tests (ut/ct_dperm, ast_dperm / ast_gperm, rrd_dperm /
+    # rrd_gperm): one stream per record list, carried from call to call
+    L = rb.lib()
+    cs = {}
+    names, codes, nlev = load_discrete("learning_test")
+    data = ra.RefData([np.ascontiguousarray(c) for c in codes], [int(v) for v in nlev], names)
+    rng = np.random.default_rng(20261116)
+    recs = []
+    L.minir_rng_seed(31)
+    p = len(names)
+    for t in range(10):
+        m = int(rng.integers(2, p - 1))
+        idx = [int(i) for i in rng.choice(p, size=2 + m, replace=False)]
+        x, y, sx = idx[0], idx[1], idx[2:]
+        nf = int(rng.integers(0, 2))
+        mn = int(rng.integers(0, 2))
+        mx = int(rng.integers(max(mn, 1), min(3, m - nf) + 1))
+        test = ("mc-mi", "smc-x2", "sp-mi", "mc-jt", "smc-mi")[t % 5]
+        B = 60
+        rb.reset_test_counter()
+        pv = ra.indep_test(data, [names[x], names[sx[0]]], names[y], [names[i] for i in sx[1:2]], test, 0.05, B=B)
+        recs.append({"site": "indep", "test": test, "B": B, "x": [x, sx[0]], "y": y, "sx": sx[1:2], "alpha": 0.05,
+                     "p": [float(v) for v in pv], "counter": rb.test_counter()})
+        rb.reset_test_counter()
+        pv, pmin, pmax, ds_ = ra.allsubs_test(data, names[x], names[y], [names[i] for i in sx],
+                                              [names[i] for i in sx[:nf]], test, 0.05, mn, mx, B=B)
+        recs.append({"site": "allsubs", "test": test, "B": B, "x": x, "y": y, "sx": sx, "nfixed": nf, "min": mn,
+                     "max": mx, "alpha": 0.05, "p": pv, "pmin": pmin, "pmax": pmax,
+                     "dsep": None if ds_ is None else [names.index(d) for d in ds_], "counter": rb.test_counter()})
+        rb.reset_test_counter()
+        pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + sx], [names[i] for i in sx[:nf]],
+                                 test, 0.05, B=B)
+        recs.append({"site": "roundrobin", "test": test, "B": B, "x": x, "z": [y] + sx, "nfixed": nf, "alpha": 0.05,
+                     "p": [float(v) for v in pvs], "counter": rb.test_counter()})
+        rb.reset()
+        data.invalidate()
+    cs["learning_test"] = {"seed": 31, "records": recs, "end_state": str(L.minir_rng_peek())}
+    gnames, vals = load_gaussian("gaussian_test")
+    gdata = ra.RefData([np.ascontiguousarray(v[:1500]) for v in vals], None, gnames)   # first 1500 rows
+    recs = []
+    L.minir_rng_seed(32)
+    gp = len(gnames)
+    for t in range(6):
+        m = int(rng.integers(2, 4))
+        idx = [int(i) for i in rng.choice(gp, size=2 + m, replace=False)]
+        x, y, sx = idx[0], idx[1], idx[2:]
+        test = ("mc-cor", "smc-zf", "mc-mi-g")[t % 3]
+        B = 40
+        rb.reset_test_counter()
+        pv, pmin, pmax, ds_ = ra.allsubs_test(gdata, gnames[x], gnames[y], [gnames[i] for i in sx], [], test, 0.05,
+                                              0, 2, B=B)
+        recs.append({"site": "allsubs", "test": test, "B": B, "x": x, "y": y, "sx": sx, "nfixed": 0, "min": 0,
+                     "max": 2, "alpha": 0.05, "p": pv, "pmin": pmin, "pmax": pmax,
+                     "dsep": None if ds_ is None else [gnames.index(d) for d in ds_], "counter": rb.test_counter()})
+        rb.reset_test_counter()
+        pvs = ra.roundrobin_test(gdata, gnames[x], [gnames[i] for i in [y] + sx], [], test, 0.05, B=B)
+        recs.append({"site": "roundrobin", "test": test, "B": B, "x": x, "z": [y] + sx, "nfixed": 0, "alpha": 0.05,
+                     "p": [float(v) for v in pvs], "counter": rb.test_counter()})
+        rb.reset()
+        gdata.invalidate()
+    cs["gaussian_test_1500"] = {"seed": 32, "records": recs, "end_state": str(L.minir_rng_peek())}
+    out["callsites"] = cs
     with open(os.path.join(HERE, "ref_permutation.json"), "w") as f:
         json.dump(out, f)
     print("wrote ref_permutation.json")
