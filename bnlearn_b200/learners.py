@@ -28,21 +28,26 @@ SCORE_EQUIVALENT = ("loglik", "aic", "bic", "ebic", "bde", "qnml", "loglik-g", "
 class GpuBackend:
     """The statistics side of the learners, on the CUDA engine."""
 
-    def __init__(self, ds):
+    def __init__(self, ds, stream=None):
         self.ds = ds
         self.counter = cs.TestCounter()
+        self.stream = stream                  # cs.UniformStream for the permutation tests
 
-    def indep_test(self, xs, y, sx, test):
-        return cs.indep_test(self.ds, xs, y, sx, test, self.counter)
+    def indep_test(self, xs, y, sx, test, alpha=1.0):
+        return cs.indep_test(self.ds, xs, y, sx, test, self.counter, self.stream, alpha)
 
     def allsubs_batch(self, x, y, sx, nfixed, test, alpha, minsize, maxsize):
+        if test in cs.MC_TESTS:               # one request at a time: the stream passes from one to the next
+            return [self.allsubs(x[r], y[r], sx[r][nfixed[r]:], sx[r][:nfixed[r]], test, alpha, minsize, maxsize)
+                    for r in range(len(x))]
         return cs.allsubs_test_batch(self.ds, x, y, sx, nfixed, test, alpha, minsize, maxsize, self.counter)
 
     def allsubs(self, x, y, sx, fixed, test, alpha, minsize, maxsize):
-        return cs.allsubs_test(self.ds, x, y, sx, fixed, test, alpha, minsize, maxsize, self.counter)
+        return cs.allsubs_test(self.ds, x, y, sx, fixed, test, alpha, minsize, maxsize, self.counter,
+                               self.stream)
 
     def roundrobin(self, x, z, fixed, test, alpha):
-        return cs.roundrobin_test(self.ds, x, z, fixed, test, alpha, self.counter)
+        return cs.roundrobin_test(self.ds, x, z, fixed, test, alpha, self.counter, self.stream)
 
     def per_node_score(self, targets, parents, score, arg):
         return cs.per_node_score(self.ds, targets, parents, score, arg)
@@ -303,6 +308,32 @@ def pc_stable(backend, nnodes, test, alpha=0.05, max_sx=None):
             info[p] = (n1, n2)
             if len(n1) >= level:
                 first.append(p)
+        if test in cs.MC_TESTS:
+            # permutation tests draw from one stream: keep the reference's order, pair by
+            # pair and both directions of a pair before the next one (R/pcalgo.R:93-141)
+            separated = set()
+            for p in list(info):
+                n1, n2 = info[p]
+                if len(n1) >= level:
+                    pv, _, _, dsep = backend.allsubs(p[0], p[1], n1, [], test, alpha, level, level)
+                    if pv > alpha:
+                        state[p].update(p=pv, dsep=dsep if dsep is not None else [], max_adj=0)
+                        separated.add(p)
+                        continue
+                if level == 1:
+                    n2 = [v for v in n2 if v not in n1]
+                info[p] = (n1, n2)
+                if len(n2) >= level and level > 0 and set(n1) != set(n2):
+                    pv, _, _, dsep = backend.allsubs(p[1], p[0], n2, [], test, alpha, level, level)
+                    if pv > alpha:
+                        state[p].update(p=pv, dsep=dsep if dsep is not None else [], max_adj=0)
+                        separated.add(p)
+                        continue
+                state[p].update(p=0.0, dsep=None, max_adj=max(len(n1), len(n2)))
+            skeleton = [p for p in pairs if state[p]["p"] is not None and state[p]["p"] < alpha]
+            if all(state[p]["max_adj"] <= level for p in pairs):
+                break
+            continue
         res = backend.allsubs_batch([p[0] for p in first], [p[1] for p in first],
                                     [info[p][0] for p in first], [0] * len(first), test, alpha, level, level)
         separated = set()

@@ -16,7 +16,10 @@ class _Counter:
 
 
 class RefBackend:
-    def __init__(self, columns, nlevels=None):
+    def __init__(self, columns, nlevels=None, B=None, seed=None):
+        self.B = B                             # permutation tests: permutations per test ...
+        if seed is not None:                   # ... drawn from the shim's stream
+            rb.lib().minir_rng_seed(int(seed))
         self.names = ["V%d" % i for i in range(len(columns))]
         self.data = ra.RefData(columns, nlevels, self.names)
         self.counter = _Counter()
@@ -35,13 +38,13 @@ class RefBackend:
 
     def indep_test(self, xs, y, sx, test):
         self._gc()
-        return ra.indep_test(self.data, self._n(xs), self.names[y], self._n(sx), test)
+        return ra.indep_test(self.data, self._n(xs), self.names[y], self._n(sx), test, B=self.B)
 
     def allsubs(self, x, y, sx, fixed, test, alpha, minsize, maxsize):
         self._gc()
         p, pmin, pmax, ds = ra.allsubs_test(self.data, self.names[x], self.names[y],
                                             self._n(list(fixed) + list(sx)), self._n(fixed), test, alpha,
-                                            minsize, min(maxsize, len(sx)))
+                                            minsize, min(maxsize, len(sx)), B=self.B)
         return p, pmin, pmax, None if ds is None else [self.names.index(d) for d in ds]
 
     def allsubs_batch(self, x, y, sx, nfixed, test, alpha, minsize, maxsize):
@@ -50,7 +53,7 @@ class RefBackend:
 
     def roundrobin(self, x, z, fixed, test, alpha):
         self._gc()
-        return ra.roundrobin_test(self.data, self.names[x], self._n(z), self._n(fixed), test, alpha)
+        return ra.roundrobin_test(self.data, self.names[x], self._n(z), self._n(fixed), test, alpha, B=self.B)
 
     def _kw(self, score, arg):
         if score in ("bde", "bds"):

@@ -94,6 +94,33 @@ def test_pc_stable_identical_skeleton_dsep_counter(engine, ds, test):
     d.release()
 
 
+@pytest.mark.parametrize("test,B", [("mc-mi", 40), ("smc-x2", 60), ("sp-mi", 30)])
+def test_pc_stable_with_permutation_tests(engine, test, B):
+    """pc.stable with a permutation test: one uniform stream through the whole run,
+    pair by pair as pc.heuristic visits them (R/pcalgo.R:69-148). Same skeleton,
+    separating sets, p-values, counter -- and the stream ends at the same position as
+    the reference's, i.e. exactly the same draws were consumed."""
+    from bnlearn_b200 import callsites as cs, learners
+    from bnlearn_b200.learners import GpuBackend
+    from oracle import refbind
+    if not refbind.available():
+        pytest.skip("oracle/_ref/libbnref.so is not built")
+    from refbackend import RefBackend
+    names, cols, nlev = load_discrete("learning_test")
+    d = engine.register(cols, nlev)
+    stream = cs.UniformStream(engine._lib, B, seed=77)
+    gpu = GpuBackend(d, stream)
+    k1, d1, p1 = learners.pc_stable(gpu, len(cols), test, 0.05)
+    ref = RefBackend(cols, nlev, B=B, seed=77)
+    k2, d2, p2 = learners.pc_stable(ref, len(cols), test, 0.05)
+    assert k1 == k2 and d1 == d2
+    assert gpu.counter.value == ref.counter.value
+    for key in p1:
+        assert np.isclose(p1[key], p2[key], rtol=1e-9, atol=1e-300), (key, p1[key], p2[key])
+    assert stream.position == refbind.lib().minir_rng_peek()
+    d.release()
+
+
 @pytest.mark.parametrize("algo", ["mmpc", "si.hiton.pc", "iamb"])
 def test_local_discovery_identical(engine, algo):
     from bnlearn_b200 import learners
