@@ -589,6 +589,40 @@ def test_candidate_runs_with_mid_size_tables(engine):
     d.release()
 
 
+@pytest.mark.parametrize("seed,n", [(1, 65536), (2, 65537), (3, 131071), (4, 200015)])
+def test_candidate_runs_randomised(engine, seed, n):
+    """Random score_cache_fill-like batches: several nodes, each with its own parents
+    and a run of candidates, interleaved with unrelated units, at row counts around
+    the 16-row group and chunk boundaries. Every unit against the oracle, so that the
+    group kernel, the base-index kernel (all classes) and the per-unit kernels are
+    each hit with odd shapes."""
+    from oracle import oracle as orc
+    rng = np.random.default_rng(seed)
+    p = 22
+    lev = [int(v) for v in rng.integers(2, 7, p)]
+    cols = [rng.integers(1, l + 1, n).astype(np.int32) for l in lev]
+    if seed == 3:                                        # a column with NAs: its units leave the grouped paths
+        cols[5][rng.random(n) < 0.02] = orc.NA_INT
+    d = engine.register(cols, lev)
+    targets, parents = [], []
+    for _ in range(5):
+        t = int(rng.integers(0, p))
+        k = int(rng.integers(1, 5))
+        base = [int(v) for v in rng.choice([c for c in range(p) if c != t], size=k, replace=False)]
+        cands = [c for c in range(p) if c != t and c not in base]
+        rng.shuffle(cands)
+        for c in cands[:int(rng.integers(3, len(cands) + 1))]:
+            targets.append(t); parents.append(base + [int(c)])
+        targets.append(int(rng.integers(0, p))); parents.append([])          # breaks the run
+    got, _ = d.score_discrete("loglik", targets, parents, 0.0)
+    for i, (t, pa) in enumerate(zip(targets, parents)):
+        if int(np.prod([lev[j] for j in pa] + [lev[t]])) > 200000:
+            continue
+        ref, _ = orc.score_discrete("loglik", cols[t], lev[t], [cols[j] for j in pa], [lev[j] for j in pa], 0.0)
+        _check(got[i], ref, (seed, t, pa))
+    d.release()
+
+
 def test_multi_device_context_gives_identical_results():
     """A context on two devices splits the units in contiguous blocks; outputs must
     not change by a bit."""
