@@ -150,12 +150,55 @@ def cpu_run(cols32, lev, units, cores):
     return done / dt, dt, _CPU["kind"]
 
 
+def _cpu_score_worker(span):
+    """BDe scores of candidate parent sets (target | base parents + one candidate)
+    through the reference's per_node_score -- c_fast_config, c_configurations /
+    int2fac and cdpost (src/scores/dirichlet.posterior.c:152-202) -- or, when
+    oracle/_ref is not built, the plain-C port."""
+    lo, hi = span
+    host, lev, tgt, base, cands = _CPU["score"]
+    if hi <= lo:
+        return 0
+    if _CPU["kind"] == "reference":
+        from oracle import refapi as ra, refbind as rb
+        idx = [tgt] + base + cands[lo:hi]
+        names = ["V%d" % i for i in idx]
+        data = ra.RefData([host[i] for i in idx], [lev[i] for i in idx], names)
+        for c in cands[lo:hi]:
+            par = {nm: [] for nm in names}
+            par["V%d" % tgt] = ["V%d" % i for i in base + [c]]
+            ra.per_node_score(data, par, ["V%d" % tgt], "bde", iss=1.0)
+        rb.reset()
+    else:
+        from oracle import oracle as orc
+        for c in cands[lo:hi]:
+            pa = base + [c]
+            orc.score_discrete("bde", host[tgt], lev[tgt], [host[i] for i in pa], [lev[i] for i in pa], 1.0)
+    return hi - lo
+
+
+def cpu_score_run(host, lev, tgt, base, cands, cores):
+    """Score deltas per second of the CPU implementation on `cores` forked workers."""
+    import multiprocessing as mp
+    from oracle import refbind
+    _CPU.update(score=(host, lev, tgt, base, cands), kind="reference" if refbind.available() else "port")
+    per = (len(cands) + cores - 1) // cores
+    spans = [(i, min(i + per, len(cands))) for i in range(0, len(cands), per)]
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores) as pool:
+        pool.map(_cpu_score_worker, [(0, 0)] * cores)
+        t0 = time.perf_counter()
+        done = sum(pool.map(_cpu_score_worker, spans, chunksize=1))
+        dt = time.perf_counter() - t0
+    return done / dt, dt, _CPU["kind"]
+
+
 # --------------------------------------------------------------------------
 # secondary metric: score deltas per second on the config-C shape (hc/tabu + BDe,
 # 1000 factors x 1M rows). Data are generated on the device with torch (seeded);
 # only the throughput is measured here, parity lives in tests/.
 
-def config_c_extras(eng, rows=1_000_000, nnodes=1000, seed=20261107, reps=5):
+def config_c_extras(eng, rows=1_000_000, nnodes=1000, seed=20261107, reps=5, cpu_cores=0):
     import torch
     from bnlearn_b200 import callsites as cs
     g = torch.Generator(device="cuda")
@@ -215,6 +258,16 @@ def config_c_extras(eng, rows=1_000_000, nnodes=1000, seed=20261107, reps=5):
     out["iteration_2_parents"] = {"deltas": n, "ms": dt * 1e3, "deltas_per_sec": n / dt,
                                   "count_kernel_ms": kms, "device_ms": dms, "compulsory_gb": comp / 1e9,
                                   "hbm_frac_compulsory": comp / (kms * 1e-3) / 1e9 / peak}
+    if cpu_cores > 0:
+        # the same deltas on the host: a bounded sample of the 999 candidates, 4 per core
+        cands = [i for i in range(nnodes) if i not in (tgt, tgt - 1, tgt - 2)][:4 * cpu_cores]
+        try:
+            v, cdt, kind = cpu_score_run(host, levels, tgt, [tgt - 2, tgt - 1], cands, cpu_cores)
+            out["iteration_2_parents"]["cpu_reference"] = {
+                "deltas_per_sec": v, "cores": cpu_cores, "kind": kind,
+                "sample": "%d of the %d candidates (%.1f s)" % (len(cands), int(n), cdt)}
+        except Exception as exc:              # the CPU leg must never take the GPU numbers down
+            out["iteration_2_parents"]["cpu_reference"] = {"unavailable": str(exc)[:200]}
     # (b) deeper in the search: 4 parents already (tables up to 4^6 = 4096 cells).
     amat[tgt - 3, tgt] = amat[tgt - 4, tgt] = 1
     n, dt, kms, dms = timed(amat, [tgt], False)
@@ -511,7 +564,7 @@ def main():
         })
         if world == 1 and not args.no_extras:
             try:
-                line["score_deltas"] = config_c_extras(eng)
+                line["score_deltas"] = config_c_extras(eng, cpu_cores=0 if args.no_cpu_baseline else cores)
             except Exception as exc:                      # the headline line must still be printed
                 line["score_deltas"] = {"error": repr(exc)}
             try:
