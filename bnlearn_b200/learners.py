@@ -439,7 +439,7 @@ def mmpc_forward(backend, target, nnodes, test, alpha, max_sx):
 def hiton_forward(backend, target, nnodes, test, alpha, max_sx):
     """si.hiton.pc.heuristic() (R/hiton-pc.R:24-86)."""
     nodes = [v for v in range(nnodes) if v != target]
-    pv = backend.indep_test(nodes, target, [], test)
+    pv = backend.indep_test(nodes, target, [], test, alpha)
     assoc = {v: float(p) for v, p in zip(nodes, pv)}
     nodes = [v for v in nodes if assoc[v] <= alpha]
     cpc = []
@@ -464,7 +464,7 @@ def iamb_blanket(backend, target, nnodes, test, alpha, max_sx):
     nodes = [v for v in range(nnodes) if v != target]
     mb, last = [], None
     while nodes and len(mb) <= max_sx:
-        pv = backend.indep_test(nodes, target, mb, test)
+        pv = backend.indep_test(nodes, target, mb, test, alpha)
         if all(p > alpha for p in pv):
             break
         k = int(np.argmin(pv))

@@ -36,9 +36,9 @@ class RefBackend:
     def _n(self, idx):
         return [self.names[i] for i in idx]
 
-    def indep_test(self, xs, y, sx, test):
+    def indep_test(self, xs, y, sx, test, alpha=0.05):
         self._gc()
-        return ra.indep_test(self.data, self._n(xs), self.names[y], self._n(sx), test, B=self.B)
+        return ra.indep_test(self.data, self._n(xs), self.names[y], self._n(sx), test, alpha, B=self.B)
 
     def allsubs(self, x, y, sx, fixed, test, alpha, minsize, maxsize):
         self._gc()

@@ -121,6 +121,31 @@ def test_pc_stable_with_permutation_tests(engine, test, B):
     d.release()
 
 
+@pytest.mark.parametrize("algo,test,B", [("mmpc", "mc-mi", 30), ("si.hiton.pc", "smc-mi", 50), ("iamb", "mc-x2", 30)])
+def test_local_discovery_with_permutation_tests(engine, algo, test, B):
+    """mmpc / si.hiton.pc / iamb on permutation tests: indep_test, allsubs and
+    roundrobin calls interleave on one stream; neighbourhoods, Markov blankets,
+    counter and final stream position as with the reference's call sites."""
+    from bnlearn_b200 import callsites as cs, learners
+    from bnlearn_b200.learners import GpuBackend
+    from oracle import refbind
+    if not refbind.available():
+        pytest.skip("oracle/_ref/libbnref.so is not built")
+    from refbackend import RefBackend
+    names, cols, nlev = load_discrete("learning_test")
+    cols = [c[:2000] for c in cols]
+    d = engine.register(cols, nlev)
+    stream = cs.UniformStream(engine._lib, B, seed=91)
+    gpu = GpuBackend(d, stream)
+    n1, m1 = learners.local_discovery(gpu, len(cols), algo, test, 0.05)
+    ref = RefBackend(cols, nlev, B=B, seed=91)
+    n2, m2 = learners.local_discovery(ref, len(cols), algo, test, 0.05)
+    assert n1 == n2 and m1 == m2
+    assert gpu.counter.value == ref.counter.value
+    assert stream.position == refbind.lib().minir_rng_peek()
+    d.release()
+
+
 @pytest.mark.parametrize("algo", ["mmpc", "si.hiton.pc", "iamb"])
 def test_local_discovery_identical(engine, algo):
     from bnlearn_b200 import learners
