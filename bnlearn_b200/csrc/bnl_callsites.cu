@@ -25,7 +25,7 @@ bool is_discrete_score(int s) {
 // park the number of permutations, the early-stopping threshold and the caller's
 // uniform stream here for the duration of the call (a context is used by one host
 // thread at a time; thread_local keeps contexts on other threads apart).
-struct McArgs { int B; double alpha; bnl_unif_fn unif; void *state; };
+struct McArgs { int B; double alpha; bnl_unif_fn unif; void *state; const int *mask; int nmask; };
 thread_local const McArgs *g_mc = nullptr;
 bool is_mc_discrete(int t) {
   return t == BNL_MC_MI || t == BNL_MC_X2 || t == BNL_SP_MI || t == BNL_SP_X2 || t == BNL_MC_JT ||
@@ -58,8 +58,8 @@ int run_tests(bnl_ctx *ctx, bnl_data data, int test_e, const std::vector<int> &x
     return bnl_ci_discrete_mc(ctx, data, test_e, g_mc->B, g_mc->alpha, n, x.data(), y.data(), zoff.data(), zi,
                               g_mc->unif, g_mc->state, st.data(), df.data(), pv.data());
   if (g_mc && is_mc_gaussian(test_e))
-    return bnl_ci_gaussian_mc(ctx, data, test_e, g_mc->B, g_mc->alpha, n, x.data(), y.data(), zoff.data(), zi,
-                              g_mc->unif, g_mc->state, st.data(), pv.data());
+    return bnl_ci_gaussian_mc_ex(ctx, data, test_e, g_mc->B, g_mc->alpha, n, x.data(), y.data(), zoff.data(), zi,
+                                 g_mc->unif, g_mc->state, st.data(), pv.data(), g_mc->mask, g_mc->nmask);
   return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
 }
 
@@ -654,7 +654,7 @@ extern "C" int bnl_indep_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B,
   if (!ctx) return BNL_EINVAL;
   if (!(is_mc_discrete(test_e) || is_mc_gaussian(test_e)))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a permutation test", test_e);
-  const McArgs a{B, alpha, unif, unif_state};
+  const McArgs a{B, alpha, unif, unif_state, nullptr, 0};
   g_mc = &a;
   const int rc = bnl_indep_test(ctx, data, test_e, nx, x, y, sx, nsx, pvalue, stat, df, test_counter);
   g_mc = nullptr;
@@ -668,7 +668,7 @@ extern "C" int bnl_allsubs_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, int 
   if (!ctx) return BNL_EINVAL;
   if (!(is_mc_discrete(test_e) || is_mc_gaussian(test_e)))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a permutation test", test_e);
-  const McArgs a{B, alpha, unif, unif_state};
+  const McArgs a{B, alpha, unif, unif_state, nullptr, 0};
   const int off[2] = {0, nsx};
   g_mc = &a;
   const int rc = bnl_allsubs_test(ctx, data, test_e, 1, &x, &y, off, sx, &nfixed, minsize, maxsize, alpha, out,
@@ -683,7 +683,11 @@ extern "C" int bnl_roundrobin_test_mc(bnl_ctx *ctx, bnl_data data, int test_e, i
   if (!ctx) return BNL_EINVAL;
   if (!(is_mc_discrete(test_e) || is_mc_gaussian(test_e)))
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not a permutation test", test_e);
-  const McArgs a{B, alpha, unif, unif_state};
+  // Gaussian permutation tests: every column of the request masks its missing rows for
+  // the whole call (rrd_gperm's indicator is never cleared), dropped variables included.
+  std::vector<int> mask;
+  if (is_mc_gaussian(test_e) && nz > 0 && z) { mask.push_back(x); mask.insert(mask.end(), z, z + nz); }
+  const McArgs a{B, alpha, unif, unif_state, mask.empty() ? nullptr : mask.data(), (int)mask.size()};
   g_mc = &a;
   const int rc = bnl_roundrobin_test(ctx, data, test_e, x, z, nz, is_fixed, alpha, pvalue, test_counter);
   g_mc = nullptr;

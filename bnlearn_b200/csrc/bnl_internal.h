@@ -178,6 +178,10 @@ int bnl_ci_discrete_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const in
 int bnl_ci_gaussian_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x, const int *y,
                         const int *z_off, const int *z_idx, double *stat, double *df, double *pvalue);
 
+int bnl_ci_gaussian_mc_ex(bnl_ctx *ctx, bnl_data data, int test_e, int B, double alpha, int n, const int *x,
+                          const int *y, const int *z_off, const int *z_idx, bnl_unif_fn unif, void *unif_state,
+                          double *stat, double *pvalue, const int *mask_cols, int nmask);
+
 int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss, int nnodes,
                             const int *amat, const int *blmat, const int *updated, int nupdated,
                             int equivalence, const double *reference, double *cache,

@@ -482,6 +482,17 @@ struct DeviceBuf {
 extern "C" int bnl_ci_gaussian_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B, double alpha, int n,
                                   const int *x, const int *y, const int *z_off, const int *z_idx,
                                   bnl_unif_fn unif, void *unif_state, double *stat, double *pvalue) {
+  return bnl_ci_gaussian_mc_ex(ctx, data, test_e, B, alpha, n, x, y, z_off, z_idx, unif, unif_state, stat, pvalue,
+                               nullptr, 0);
+}
+
+// The same with extra numeric columns whose missing values also exclude a row
+// (rrd_gperm keeps one missingness indicator for the whole call and only ever adds
+// to it, src/tests/patterns/roundrobin.test.c:704-732 over tabular_incomplete_cases,
+// src/core/data.table.c:405-429: a variable that has been dropped still masks its rows).
+int bnl_ci_gaussian_mc_ex(bnl_ctx *ctx, bnl_data data, int test_e, int B, double alpha, int n, const int *x,
+                          const int *y, const int *z_off, const int *z_idx, bnl_unif_fn unif, void *unif_state,
+                          double *stat, double *pvalue, const int *mask_cols, int nmask) {
   if (!ctx) return BNL_EINVAL;
   BnlDataSet *dsp = find_data_p(ctx, data);
   if (!dsp) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
@@ -496,8 +507,6 @@ extern "C" int bnl_ci_gaussian_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B
   if (n < 0 || B < 1 || !unif || (n > 0 && (!x || !y || !z_off || !stat || !pvalue)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_gaussian_mc: bad arguments");
   if (n == 0) return BNL_OK;
-  if (ds.any_nan)
-    return bnl_fail(ctx, BNL_EUNSUPPORTED, "permutation tests on incomplete numeric data are not handled here");
   if (ds.nobs > INT32_MAX) return bnl_fail(ctx, BNL_EUNSUPPORTED, "too many rows for a permutation test");
   if (ds.gauss_nobs > 0)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "permutation tests need the rows, not pooled moments");
@@ -512,31 +521,100 @@ extern "C" int bnl_ci_gaussian_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B
   BnlDevice &dev = ctx->devs[0];
   BnlDeviceData &dd = ds.dev[0];
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
-  const long long N = ds.nobs;
   // permutations per device batch: at most 32 MB of row indices
-  const long long pmax = std::max(1ll, std::min<long long>(B + 1, (8ll << 20) / std::max(1ll, N)));
-  DeviceBuf d_perm, d_cross;
+  const long long pcap = std::max(1ll, std::min<long long>(B + 1, (8ll << 20) / std::max(1ll, ds.nobs)));
+  DeviceBuf d_perm, d_cross, d_tmp;
+  size_t tmp_doubles = 0;
   int *h_perm = nullptr;
   double *h_cross = nullptr;
-  BNL_CUDA(ctx, cudaMalloc(&d_perm.p, (size_t)pmax * N * sizeof(int)));
-  BNL_CUDA(ctx, cudaMalloc(&d_cross.p, (size_t)pmax * BNL_MAXK * sizeof(double)));
-  BNL_CUDA(ctx, cudaMallocHost((void **)&h_perm, (size_t)pmax * N * sizeof(int)));
-  BNL_CUDA(ctx, cudaMallocHost((void **)&h_cross, (size_t)pmax * BNL_MAXK * sizeof(double)));
+  // sized for the worst case: a unit whose complete rows are few gets more permutations per batch
+  const size_t perm_ints = (size_t)std::max<long long>(pcap * ds.nobs, (long long)(B + 1) * 64);
+  BNL_CUDA(ctx, cudaMalloc(&d_perm.p, perm_ints * sizeof(int)));
+  BNL_CUDA(ctx, cudaMalloc(&d_cross.p, (size_t)(B + 1) * BNL_MAXK * sizeof(double)));
+  BNL_CUDA(ctx, cudaMallocHost((void **)&h_perm, perm_ints * sizeof(int)));
+  BNL_CUDA(ctx, cudaMallocHost((void **)&h_cross, (size_t)(B + 1) * BNL_MAXK * sizeof(double)));
   struct PinnedGuard { int *a; double *b; ~PinnedGuard() { cudaFreeHost(a); cudaFreeHost(b); } } guard{h_perm, h_cross};
-  std::vector<int> pool((size_t)N);
+  std::vector<int> pool((size_t)ds.nobs);
   const int p = ds.nc;
 
   for (int u = 0; u < n; u++) {
     const int nz = z_off[u + 1] - z_off[u], k = nz + 2;
     PermCols cols;
+    bool incomplete = false;
     for (int i = 0; i < k; i++) {
       const int c = i == 0 ? x[u] : (i == 1 ? y[u] : z_idx[z_off[u] + i - 2]);
       cols.slot[i] = ds.slot[c];          // validated by bnl_ci_gaussian_any above
+      incomplete = incomplete || std::isnan(ds.h_mean[ds.slot[c]]);
     }
-    // this test's covariance matrix, x first and y second
+    for (int m = 0; m < nmask; m++) {
+      const int c = mask_cols[m];
+      if (c < 0 || c >= ds.ncols || !ds.is_numeric[c])
+        return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_gaussian_mc: bad mask column %d", c);
+      incomplete = incomplete || std::isnan(ds.h_mean[ds.slot[c]]);
+    }
+    // what the permutation loop reads: the resident columns and moments, or -- when a
+    // column of the test has missing values -- copies of the test's columns restricted
+    // to its complete rows, as ut_gperm / ct_gperm / ast_gperm build them
+    // (src/tests/patterns/utest.c:368-424), with their own means and covariances.
+    long long N = ds.nobs;
+    const double *f64 = dd.f64, *dmean = dd.mean;
+    size_t fstride = ds.stride_f64;
+    int yslot = cols.slot[1];
     std::vector<double> cov((size_t)k * k);
-    for (int i = 0; i < k; i++)
-      for (int j = 0; j < k; j++) cov[i + (size_t)j * k] = ds.h_cov[(size_t)cols.slot[i] + (size_t)cols.slot[j] * p];
+    if (!incomplete) {
+      for (int i = 0; i < k; i++)
+        for (int j = 0; j < k; j++) cov[i + (size_t)j * k] = ds.h_cov[(size_t)cols.slot[i] + (size_t)cols.slot[j] * p];
+    } else {
+      std::vector<std::vector<double>> col(k, std::vector<double>((size_t)ds.nobs));
+      for (int i = 0; i < k; i++)
+        BNL_CUDA(ctx, cudaMemcpy(col[i].data(), dd.f64 + (size_t)cols.slot[i] * ds.stride_f64,
+                                 (size_t)ds.nobs * sizeof(double), cudaMemcpyDeviceToHost));
+      std::vector<char> masked((size_t)ds.nobs, 0);
+      {
+        std::vector<double> mc((size_t)ds.nobs);
+        for (int m = 0; m < nmask; m++) {
+          BNL_CUDA(ctx, cudaMemcpy(mc.data(), dd.f64 + (size_t)ds.slot[mask_cols[m]] * ds.stride_f64,
+                                   (size_t)ds.nobs * sizeof(double), cudaMemcpyDeviceToHost));
+          for (long long r = 0; r < ds.nobs; r++) masked[(size_t)r] |= std::isnan(mc[(size_t)r]);
+        }
+      }
+      long long nc = 0;
+      for (long long r = 0; r < ds.nobs; r++) {
+        bool ok = !masked[(size_t)r];
+        for (int i = 0; i < k; i++) ok = ok && !std::isnan(col[i][(size_t)r]);
+        if (!ok) continue;
+        for (int i = 0; i < k; i++) col[i][(size_t)nc] = col[i][(size_t)r];
+        nc++;
+      }
+      if (nc < 2) { stat[u] = 0.0; pvalue[u] = 1.0; continue; }
+      std::vector<double> mean(k);
+      for (int i = 0; i < k; i++) {
+        long double t = 0;
+        for (long long r = 0; r < nc; r++) t += col[i][(size_t)r];
+        mean[i] = (double)(t / nc);
+      }
+      for (int i = 0; i < k; i++)
+        for (int j = i; j < k; j++) {
+          long double t = 0;
+          for (long long r = 0; r < nc; r++) t += (col[i][(size_t)r] - mean[i]) * (col[j][(size_t)r] - mean[j]);
+          cov[i + (size_t)j * k] = cov[j + (size_t)i * k] = (double)(t / (nc - 1));
+        }
+      const size_t need = (size_t)k * nc + k;
+      if (need > tmp_doubles) {
+        if (d_tmp.p) { cudaFree(d_tmp.p); d_tmp.p = nullptr; }
+        BNL_CUDA(ctx, cudaMalloc(&d_tmp.p, need * sizeof(double)));
+        tmp_doubles = need;
+      }
+      double *t = static_cast<double *>(d_tmp.p);
+      for (int i = 0; i < k; i++)
+        BNL_CUDA(ctx, cudaMemcpy(t + (size_t)i * nc, col[i].data(), (size_t)nc * sizeof(double), cudaMemcpyHostToDevice));
+      BNL_CUDA(ctx, cudaMemcpy(t + (size_t)k * nc, mean.data(), (size_t)k * sizeof(double), cudaMemcpyHostToDevice));
+      f64 = t; fstride = (size_t)nc; dmean = t + (size_t)k * nc;
+      for (int i = 0; i < k; i++) cols.slot[i] = i;
+      yslot = 1;
+      N = nc;
+    }
+    const long long pmax = std::max(1ll, std::min<long long>(B + 1, (long long)(perm_ints / (size_t)N)));
     // a constant variable is independent of anything (no draw is consumed).
     if (cov[0] == 0.0 || cov[1 + (size_t)k] == 0.0) { stat[u] = 0.0; pvalue[u] = 1.0; continue; }
     const int kk = nz == 0 ? 1 : k;       // marginal: only the cross-product with x changes
@@ -567,7 +645,7 @@ extern "C" int bnl_ci_gaussian_mc(bnl_ctx *ctx, bnl_data data, int test_e, int B
       }
       BNL_CUDA(ctx, cudaMemcpyAsync(d_perm.p, h_perm, (size_t)np * N * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
       perm_cross_kernel<<<dim3((unsigned)np, (unsigned)kk), BNL_PERM_THREADS, 0, dev.stream>>>(
-          dd.f64, ds.stride_f64, dd.mean, cols, cols.slot[1], N, (const int *)d_perm.p, (double *)d_cross.p, kk);
+          f64, fstride, dmean, cols, yslot, N, (const int *)d_perm.p, (double *)d_cross.p, kk);
       BNL_CUDA(ctx, cudaGetLastError());
       BNL_CUDA(ctx, cudaMemcpyAsync(h_cross, d_cross.p, (size_t)np * kk * sizeof(double), cudaMemcpyDeviceToHost,
                                     dev.stream));

@@ -108,13 +108,13 @@ def reference_outputs():
                                        "min": mn, "max": mx, "alpha": 0.05, "p": pv,
                                        "pmin": pmin, "pmax": pmax,
                                        "dsep": None if ds_ is None else [names.index(d) for d in ds_],
-                                       "counter": rb.test_counter()})
+                                       "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
                 rb.reset_test_counter()
                 pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + s],
                                          [names[i] for i in s[:nf]], test, 0.05)
                 rec["roundrobin"].append({"test": test, "x": x, "z": [y] + s, "nfixed": nf,
                                           "alpha": 0.05, "p": [float(v) for v in pvs],
-                                          "counter": rb.test_counter()})
+                                          "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
             rb.reset()
             data.invalidate()
         out[ds] = rec
@@ -139,7 +139,7 @@ def reference_outputs():
                         "parents": {k: v for k, v in parents.items()},
                         "reference": [float(v) for v in ref],
                         "cache": [[float(v) for v in row] for row in cache],
-                        "counter": rb.test_counter()})
+                        "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
             rb.reset()
             data.invalidate()
     out["score_cache_fill"] = rec
@@ -221,13 +221,13 @@ def incomplete_outputs():
                                    "min": mn, "max": mx, "alpha": 0.05, "p": pv,
                                    "pmin": pmin, "pmax": pmax,
                                    "dsep": None if ds_ is None else [names.index(d) for d in ds_],
-                                   "counter": rb.test_counter()})
+                                   "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
             rb.reset_test_counter()
             pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + s],
                                      [names[i] for i in s[:nf]], test, 0.05)
             rec["roundrobin"].append({"test": test, "x": x, "z": [y] + s, "nfixed": nf,
                                       "alpha": 0.05, "p": [float(v) for v in pvs],
-                                      "counter": rb.test_counter()})
+                                      "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
         rb.reset()
         data.invalidate()
     for t in range(24):
@@ -311,13 +311,13 @@ def jt_shrinkage_outputs():
                                        "min": mn, "max": mx, "alpha": 0.05, "p": pv,
                                        "pmin": pmin, "pmax": pmax,
                                        "dsep": None if ds_ is None else [names.index(d) for d in ds_],
-                                       "counter": rb.test_counter()})
+                                       "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
                 rb.reset_test_counter()
                 pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + s],
                                          [names[i] for i in s[:nf]], test, 0.05)
                 rec["roundrobin"].append({"test": test, "x": x, "z": [y] + s, "nfixed": nf,
                                           "alpha": 0.05, "p": [float(v) for v in pvs],
-                                          "counter": rb.test_counter()})
+                                          "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
             rb.reset()
             data.invalidate()
         out[ds + "_jt_sh"] = rec
@@ -574,12 +574,12 @@ def incomplete_gaussian_patterns():
                 rec["allsubs"].append({"test": test, "x": x, "y": y, "sx": sx, "nfixed": nf, "min": mn, "max": mx,
                                        "alpha": 0.05, "p": pv, "pmin": pmin, "pmax": pmax,
                                        "dsep": None if ds_ is None else [gnames.index(d) for d in ds_],
-                                       "counter": rb.test_counter()})
+                                       "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
                 rb.reset_test_counter()
                 pvs = ra.roundrobin_test(data, gnames[x], [gnames[i] for i in [y] + sx],
                                          [gnames[i] for i in sx[:nf]], test, 0.05)
                 rec["roundrobin"].append({"test": test, "x": x, "z": [y] + sx, "nfixed": nf, "alpha": 0.05,
-                                          "p": [float(v) for v in pvs], "counter": rb.test_counter()})
+                                          "p": [float(v) for v in pvs], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
             rb.reset()
             data.invalidate()
         out[key] = rec
@@ -651,18 +651,18 @@ def permutation_outputs():
         rb.reset_test_counter()
         pv = ra.indep_test(data, [names[x], names[sx[0]]], names[y], [names[i] for i in sx[1:2]], test, 0.05, B=B)
         recs.append({"site": "indep", "test": test, "B": B, "x": [x, sx[0]], "y": y, "sx": sx[1:2], "alpha": 0.05,
-                     "p": [float(v) for v in pv], "counter": rb.test_counter()})
+                     "p": [float(v) for v in pv], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
         rb.reset_test_counter()
         pv, pmin, pmax, ds_ = ra.allsubs_test(data, names[x], names[y], [names[i] for i in sx],
                                               [names[i] for i in sx[:nf]], test, 0.05, mn, mx, B=B)
         recs.append({"site": "allsubs", "test": test, "B": B, "x": x, "y": y, "sx": sx, "nfixed": nf, "min": mn,
                      "max": mx, "alpha": 0.05, "p": pv, "pmin": pmin, "pmax": pmax,
-                     "dsep": None if ds_ is None else [names.index(d) for d in ds_], "counter": rb.test_counter()})
+                     "dsep": None if ds_ is None else [names.index(d) for d in ds_], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
         rb.reset_test_counter()
         pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + sx], [names[i] for i in sx[:nf]],
                                  test, 0.05, B=B)
         recs.append({"site": "roundrobin", "test": test, "B": B, "x": x, "z": [y] + sx, "nfixed": nf, "alpha": 0.05,
-                     "p": [float(v) for v in pvs], "counter": rb.test_counter()})
+                     "p": [float(v) for v in pvs], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
         rb.reset()
         data.invalidate()
     cs["learning_test"] = {"seed": 31, "records": recs, "end_state": str(L.minir_rng_peek())}
@@ -682,14 +682,43 @@ def permutation_outputs():
                                               0, 2, B=B)
         recs.append({"site": "allsubs", "test": test, "B": B, "x": x, "y": y, "sx": sx, "nfixed": 0, "min": 0,
                      "max": 2, "alpha": 0.05, "p": pv, "pmin": pmin, "pmax": pmax,
-                     "dsep": None if ds_ is None else [gnames.index(d) for d in ds_], "counter": rb.test_counter()})
+                     "dsep": None if ds_ is None else [gnames.index(d) for d in ds_], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
         rb.reset_test_counter()
         pvs = ra.roundrobin_test(gdata, gnames[x], [gnames[i] for i in [y] + sx], [], test, 0.05, B=B)
         recs.append({"site": "roundrobin", "test": test, "B": B, "x": x, "z": [y] + sx, "nfixed": 0, "alpha": 0.05,
-                     "p": [float(v) for v in pvs], "counter": rb.test_counter()})
+                     "p": [float(v) for v in pvs], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
         rb.reset()
         gdata.invalidate()
     cs["gaussian_test_1500"] = {"seed": 32, "records": recs, "end_state": str(L.minir_rng_peek())}
+    # incomplete numeric data: the *_gperm patterns test on the rows complete for the test's columns
+    zna = np.load(os.path.join(HERE, "data_gaussian_test_na.npz"))
+    nnames, nvals = [str(v) for v in zna["names"]], zna["values"]
+    ndata = ra.RefData([np.ascontiguousarray(v) for v in nvals], None, nnames)
+    recs = []
+    L.minir_rng_seed(33)
+    for t in range(6):
+        m = int(rng.integers(2, 4))
+        idx = [int(i) for i in rng.choice(len(nnames), size=2 + m, replace=False)]
+        x, y, sx = idx[0], idx[1], idx[2:]
+        test = ("mc-cor", "smc-zf", "mc-mi-g")[t % 3]
+        B = 30
+        rb.reset_test_counter()
+        pv = ra.indep_test(ndata, [nnames[x], nnames[sx[0]]], nnames[y], [nnames[i] for i in sx[1:2]], test, 0.05, B=B)
+        recs.append({"site": "indep", "test": test, "B": B, "x": [x, sx[0]], "y": y, "sx": sx[1:2], "alpha": 0.05,
+                     "p": [float(v) for v in pv], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
+        rb.reset_test_counter()
+        pv, pmin, pmax, ds_ = ra.allsubs_test(ndata, nnames[x], nnames[y], [nnames[i] for i in sx], [], test, 0.05,
+                                              0, 2, B=B)
+        recs.append({"site": "allsubs", "test": test, "B": B, "x": x, "y": y, "sx": sx, "nfixed": 0, "min": 0,
+                     "max": 2, "alpha": 0.05, "p": pv, "pmin": pmin, "pmax": pmax,
+                     "dsep": None if ds_ is None else [nnames.index(d) for d in ds_], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
+        rb.reset_test_counter()
+        pvs = ra.roundrobin_test(ndata, nnames[x], [nnames[i] for i in [y] + sx], [], test, 0.05, B=B)
+        recs.append({"site": "roundrobin", "test": test, "B": B, "x": x, "z": [y] + sx, "nfixed": 0, "alpha": 0.05,
+                     "p": [float(v) for v in pvs], "counter": rb.test_counter(), "state": str(rb.lib().minir_rng_peek())})
+        rb.reset()
+        ndata.invalidate()
+    cs["gaussian_test_na"] = {"seed": 33, "records": recs, "end_state": str(L.minir_rng_peek())}
     out["callsites"] = cs
     with open(os.path.join(HERE, "ref_permutation.json"), "w") as f:
         json.dump(out, f)
