@@ -243,8 +243,9 @@ int bnl_mc_from_tables(bnl_ctx *ctx, int test_e, int B, double alpha, int n, con
                        const int *nz, const int32_t *tables, const int64_t *table_off, bnl_unif_fn unif,
                        void *unif_state, double *stat, double *df, double *pvalue);
 
-/* Gaussian permutation tests (mc-cor, mc-zf, mc-mi-g and their smc-* forms) on
- * complete data. Replaces c_gauss_mcarlo / c_gauss_cmcarlo
+/* Gaussian permutation tests (mc-cor, mc-zf, mc-mi-g and their smc-* forms); a test
+ * with a missing value in one of its columns runs on its complete rows, as
+ * ut_gperm / ct_gperm build them. Replaces c_gauss_mcarlo / c_gauss_cmcarlo
  * (src/tests/permutation/gaussian.monte.carlo.c:24-129, 132-273). Permutations of
  * y are drawn on the host from `unif` exactly as RandomPermutation() draws them
  * (src/core/sampling.c:12-28), in batches that never run past the reference's
