@@ -648,6 +648,21 @@ def test_multi_device_context_gives_identical_results():
     for a, b in zip(out[0], out[1]):
         for u, v in zip(a, b):
             assert np.array_equal(u, v)
+    # candidate runs (group and base-index kernels need >= 65536 rows): the split may cut a
+    # run in two, every device works with its own scratch columns
+    n = 70003
+    lev = [3, 4, 5, 5, 2, 3, 4, 5, 6, 7, 9, 12, 4, 5, 6, 7, 3, 2]
+    ccols = [rng.integers(1, l + 1, n).astype(np.int32) for l in lev]
+    targets, parents = [], []
+    for base in ([1, 2], [1, 2, 3], [2]):
+        for c in range(4, 18):
+            targets.append(0); parents.append(base + [c])
+    res = []
+    for devs in ([0], [0, 1]):
+        with Engine(devs) as e:
+            d = e.register(ccols, lev)
+            res.append(d.score_discrete("bde", targets, parents, 1.0)[0])
+    assert np.array_equal(res[0], res[1])
 
 
 @pytest.mark.parametrize("threads", [None, "0", "3"])
