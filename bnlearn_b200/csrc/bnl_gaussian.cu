@@ -483,10 +483,10 @@ int run_cg_units(bnl_ctx *ctx, BnlDataSet &ds, std::vector<BnlCgUnit> &units_in,
         const dim3 ga((unsigned)chunks, (unsigned)(n - nsmall));
         if (which == 1)
           cg_moments_kernel<1><<<ga, BNL_CG_THREADS, smem, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8, ds.stride_u8,
-              ds.nobs, chunk_rows, d_units + nsmall, mom, d_err);
+              ds.nobs, chunk_rows, d_units + nsmall, mom, d_err, dd.u16, ds.stride_u16);
         else
           cg_moments_kernel<2><<<ga, BNL_CG_THREADS, smem, dev.stream>>>(dd.f64, ds.stride_f64, dd.u8, ds.stride_u8,
-              ds.nobs, chunk_rows, d_units + nsmall, mom, d_err);
+              ds.nobs, chunk_rows, d_units + nsmall, mom, d_err, dd.u16, ds.stride_u16);
       }
     };
     pass(1);
@@ -579,10 +579,8 @@ extern "C" int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, 
       for (int j = 0; j < np; j++) {
         const int c = pa_idx[p0 + j];
         if (ds.is_numeric[c]) cu.gslot[cu.K++] = ds.slot[c];
-        else if (ds.is_wide[c])
-          return bnl_fail(ctx, BNL_EUNSUPPORTED, "unit %d: discrete parents of a numeric node are limited to %d levels",
-                          u, BNL_MAX_LEVELS);
         else {
+          if (ds.is_wide[c]) cu.dwide |= 1 << cu.nd;          // uint16 block (never the register kernel: >= 128 configurations)
           cu.dslot[cu.nd] = ds.slot[c];
           cu.dmul[cu.nd++] = (int)nconfig;
           nconfig *= ds.nlevels[c];

@@ -731,7 +731,7 @@ masked_shrink_kernel(const double *__restrict__ data, size_t stride, long long n
 
 struct BnlCgUnit {
   long long off;                 // first double of the unit's block in `mom`
-  int nconfig, K, nd, pad;
+  int nconfig, K, nd, dwide;     // dwide: bit j set when discrete parent j lives in the uint16 block
   int gslot[BNL_CG_MAXG];        // numeric slots, node first
   int dslot[BNL_CG_MAXD];        // packed factor slots
   int dmul[BNL_CG_MAXD];         // configuration multipliers (first parent fastest)
@@ -741,7 +741,8 @@ template <int PASS>
 __global__ void __launch_bounds__(BNL_CG_THREADS)
 cg_moments_kernel(const double *__restrict__ f64, size_t fstride, const uint8_t *__restrict__ u8,
                   size_t ustride, long long nobs, long long chunk_rows,
-                  const BnlCgUnit *__restrict__ units, double *__restrict__ mom, int *__restrict__ err) {
+                  const BnlCgUnit *__restrict__ units, double *__restrict__ mom, int *__restrict__ err,
+                  const uint16_t *__restrict__ u16, size_t wstride) {
   extern __shared__ double cgsm[];
   const BnlCgUnit U = units[blockIdx.y];
   const int K = U.K, M = 1 + K + K * (K + 1) / 2;
@@ -758,9 +759,15 @@ cg_moments_kernel(const double *__restrict__ f64, size_t fstride, const uint8_t 
     int s = 0;
     bool bad = false;
     for (int j = 0; j < U.nd; j++) {
-      const unsigned b = u8[ustride * U.dslot[j] + r];
-      bad |= b >= 0x80u;
-      s += (int)b * U.dmul[j];
+      if ((U.dwide >> j) & 1) {             // a factor with 128..32767 levels: bit 15 marks NA
+        const unsigned b = u16[wstride * U.dslot[j] + r];
+        bad |= b >= 0x8000u;
+        s += (int)b * U.dmul[j];
+      } else {
+        const unsigned b = u8[ustride * U.dslot[j] + r];
+        bad |= b >= 0x80u;
+        s += (int)b * U.dmul[j];
+      }
     }
     double v[BNL_CG_MAXG];
 #pragma unroll

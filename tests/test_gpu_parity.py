@@ -282,6 +282,29 @@ def test_conditional_gaussian_scores_against_reference_golden(engine):
     d.release()
 
 
+def test_conditional_gaussian_with_a_wide_discrete_parent(engine):
+    """A factor with more than 127 levels (uint16 block) as discrete parent of a
+    numeric node, alone and next to a uint8 factor and a numeric parent: the moment
+    kernel reads its codes from the wide block. Against the oracle."""
+    from oracle import oracle as orc
+    rng = np.random.default_rng(41)
+    n = 60000
+    wide = rng.integers(1, 201, n).astype(np.int32)                       # 200 levels
+    f = rng.integers(1, 4, n).astype(np.int32)
+    g1 = rng.normal(size=n)
+    g0 = 0.01 * wide + 0.5 * f + 0.7 * g1 + rng.normal(size=n)
+    cols, lev = [g0, wide, f, g1], [0, 200, 3, 0]
+    d = engine.register(cols, lev)
+    units = [[1], [1, 3], [1, 2], [2, 1, 3]]
+    for score, k in (("loglik-cg", 0.0), ("bic-cg", np.log(n) / 2)):
+        sc, npar = d.score_cg(score, [0] * len(units), units, k)
+        for i, pa in enumerate(units):
+            ref, rnp = orc.score_cg(score, g0, 0, [cols[j] for j in pa], [lev[j] for j in pa], k)
+            _check(sc[i], ref, (score, pa))
+            assert npar[i] == rnp
+    d.release()
+
+
 def test_conditional_gaussian_nal_scores_on_incomplete_data(engine):
     """nal-cg / pnal-cg on clgaussian.test with 5 % of the cells missing (re-created
     from the fixture's seed): discrete nodes (nal), Gaussian nodes with numeric parents
