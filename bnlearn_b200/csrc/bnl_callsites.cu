@@ -130,7 +130,7 @@ extern "C" int bnl_allsubs_test(bnl_ctx *ctx, bnl_data data, int test_e, int n, 
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   const long long nobs = it->second.gauss_nobs > 0 && is_gaussian_test(test_e) ? it->second.gauss_nobs : it->second.nobs;
   const bool gauss = is_gaussian_test(test_e);
-  if (!gauss && !is_discrete_test(test_e) && !is_mc_test(test_e))
+  if (!gauss && !is_discrete_test(test_e) && !is_mc_test(test_e) && test_e != BNL_MI_CG)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
   // A request whose columns are not all complete takes the reference's
   // *_with_missing pattern (rinterface/allsubs.test.c:72, 103-113): every subset is
@@ -351,7 +351,7 @@ extern "C" int bnl_roundrobin_test(bnl_ctx *ctx, bnl_data data, int test_e, int 
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   const long long nobs = it->second.gauss_nobs > 0 && is_gaussian_test(test_e) ? it->second.gauss_nobs : it->second.nobs;
   const bool gauss = is_gaussian_test(test_e);
-  if (!gauss && !is_discrete_test(test_e) && !is_mc_test(test_e))
+  if (!gauss && !is_discrete_test(test_e) && !is_mc_test(test_e) && test_e != BNL_MI_CG)
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "test %d is not handled by this engine", test_e);
   // columns with missing values: rrd_gaustests_with_missing (each test on the rows
   // complete for the variables still in play; a test without degrees of freedom gives
@@ -527,6 +527,92 @@ extern "C" int bnl_ci_cg(bnl_ctx *ctx, bnl_data data, int n, const int *x, const
   BnlDataSet &ds = it->second;
   if (n < 0 || (n > 0 && (!x || !y || !z_off || !stat)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_cg: bad arguments");
+  // Incomplete data: ct_micg_with_missing (src/tests/patterns/ctest.c:336-406) runs the
+  // complete-data test on the rows that are complete for ALL columns of the test. Such a
+  // test gets a temporary data set of exactly those rows (device-side row gather,
+  // bnl_data_resample) and goes through the code below on it; tests whose columns are
+  // all complete stay in one batch.
+  {
+    auto col_incomplete = [&](int c) {
+      if (c < 0 || c >= ds.ncols) return false;          // reported by the checks below
+      if (ds.is_numeric[c]) return ds.slot[c] < (int)ds.h_mean.size() && std::isnan(ds.h_mean[ds.slot[c]]);
+      if (ds.is_wide[c]) return !ds.wide_has_na.empty() && ds.wide_has_na[ds.slot[c]] != 0;
+      return !ds.slot_has_na.empty() && ds.slot_has_na[ds.slot[c]] != 0;
+    };
+    std::vector<int> inc, comp;
+    for (int u = 0; u < n; u++) {
+      bool bad = col_incomplete(x[u]) || col_incomplete(y[u]);
+      for (int j = z_off[u]; j < z_off[u + 1]; j++) bad = bad || col_incomplete(z_idx[j]);
+      (bad ? inc : comp).push_back(u);
+    }
+    if (!inc.empty()) {
+      int rc;
+      if (!comp.empty()) {
+        std::vector<int> cx, cy, coff(1, 0), cidx;
+        for (int u : comp) {
+          cx.push_back(x[u]); cy.push_back(y[u]);
+          cidx.insert(cidx.end(), z_idx + z_off[u], z_idx + z_off[u + 1]);
+          coff.push_back((int)cidx.size());
+        }
+        std::vector<double> s1(comp.size()), d1(comp.size()), p1(comp.size());
+        if ((rc = bnl_ci_cg(ctx, data, (int)comp.size(), cx.data(), cy.data(), coff.data(),
+                            cidx.empty() ? nullptr : cidx.data(), s1.data(), d1.data(), p1.data()))) return rc;
+        for (size_t i = 0; i < comp.size(); i++) {
+          stat[comp[i]] = s1[i];
+          if (df) df[comp[i]] = d1[i];
+          if (pvalue) pvalue[comp[i]] = p1[i];
+        }
+      }
+      BnlDeviceData &dd = ds.dev[0];
+      BNL_CUDA(ctx, cudaSetDevice(ctx->devs[0].id));
+      const size_t nrows = (size_t)ds.nobs;
+      std::vector<char> bad(nrows);
+      std::vector<uint8_t> b8(nrows);
+      std::vector<uint16_t> b16(nrows);
+      std::vector<double> bf(nrows);
+      std::vector<int> rows;
+      for (int u : inc) {
+        std::fill(bad.begin(), bad.end(), 0);
+        auto mark = [&](int c) -> int {
+          if (c < 0 || c >= ds.ncols) return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_cg: test %d refers to a column out of range", u);
+          if (ds.is_numeric[c]) {
+            BNL_CUDA(ctx, cudaMemcpy(bf.data(), dd.f64 + (size_t)ds.slot[c] * ds.stride_f64, nrows * sizeof(double),
+                                     cudaMemcpyDeviceToHost));
+            for (size_t r = 0; r < nrows; r++) bad[r] |= std::isnan(bf[r]);
+          } else if (ds.is_wide[c]) {
+            BNL_CUDA(ctx, cudaMemcpy(b16.data(), dd.u16 + (size_t)ds.slot[c] * ds.stride_u16, nrows * sizeof(uint16_t),
+                                     cudaMemcpyDeviceToHost));
+            for (size_t r = 0; r < nrows; r++) bad[r] |= b16[r] >= 0x8000u;
+          } else {
+            BNL_CUDA(ctx, cudaMemcpy(b8.data(), dd.u8 + (size_t)ds.slot[c] * ds.stride_u8, nrows, cudaMemcpyDeviceToHost));
+            for (size_t r = 0; r < nrows; r++) bad[r] |= b8[r] >= 0x80u;
+          }
+          return BNL_OK;
+        };
+        if ((rc = mark(x[u])) || (rc = mark(y[u]))) return rc;
+        for (int j = z_off[u]; j < z_off[u + 1]; j++) if ((rc = mark(z_idx[j]))) return rc;
+        rows.clear();
+        for (size_t r = 0; r < nrows; r++) if (!bad[r]) rows.push_back((int)r);
+        if (rows.empty()) {                   // no complete observation: independence
+          stat[u] = 0.0;
+          if (df) df[u] = 0.0;
+          if (pvalue) pvalue[u] = 1.0;
+          continue;
+        }
+        bnl_data tmp = 0;
+        if ((rc = bnl_data_resample(ctx, data, (int64_t)rows.size(), rows.data(), &tmp))) return rc;
+        const int nzu = z_off[u + 1] - z_off[u], off2[2] = {0, nzu};
+        double s1 = 0.0, d1 = 0.0, p1 = 0.0;
+        rc = bnl_ci_cg(ctx, tmp, 1, &x[u], &y[u], off2, nzu ? z_idx + z_off[u] : nullptr, &s1, &d1, &p1);
+        bnl_data_release(ctx, tmp);
+        if (rc) return rc;
+        stat[u] = s1;
+        if (df) df[u] = d1;
+        if (pvalue) pvalue[u] = p1;
+      }
+      return BNL_OK;
+    }
+  }
   const double N = (double)ds.nobs;
 
   // plan: what each test needs

@@ -448,8 +448,42 @@ def cg_nal_outputs():
                          "parents": pa, "value": float(v)})
         rb.reset()
         data.invalidate()
+    # mi-cg on the same incomplete data: ct_micg_with_missing tests on the rows complete for
+    # all the columns of the test (src/tests/patterns/ctest.c:336-406)
+    tests = []
+    for t in range(60):
+        k = int(rng.integers(0, 4))
+        idx = rng.choice(p, size=2 + k, replace=False)
+        x, y, sx = int(idx[0]), int(idx[1]), [int(i) for i in idx[2:]]
+        st, df, pv = ra.ci_test(data, names[x], names[y], [names[i] for i in sx], "mi-cg")
+        tests.append({"x": x, "y": y, "z": sx, "stat": st, "df": df, "p": pv})
+        if t % 10 == 9:
+            rb.reset()
+            data.invalidate()
+    subs, rr = [], []
+    for t in range(10):
+        m = int(rng.integers(2, 5))
+        idx = [int(i) for i in rng.choice(p, size=2 + m, replace=False)]
+        x, y, sx = idx[0], idx[1], idx[2:]
+        nf = int(rng.integers(0, 2))
+        mn = int(rng.integers(0, 2))
+        mx = int(rng.integers(max(mn, 1), min(3, m - nf) + 1))
+        rb.reset_test_counter()
+        pv, pmin, pmax, ds_ = ra.allsubs_test(data, names[x], names[y], [names[i] for i in sx],
+                                              [names[i] for i in sx[:nf]], "mi-cg", 0.05, mn, mx)
+        subs.append({"x": x, "y": y, "sx": sx, "nfixed": nf, "min": mn, "max": mx, "alpha": 0.05, "p": pv,
+                     "pmin": pmin, "pmax": pmax, "dsep": None if ds_ is None else [names.index(d) for d in ds_],
+                     "counter": rb.test_counter()})
+        rb.reset_test_counter()
+        pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + sx], [names[i] for i in sx[:nf]],
+                                 "mi-cg", 0.05)
+        rr.append({"x": x, "z": [y] + sx, "nfixed": nf, "alpha": 0.05, "p": [float(v) for v in pvs],
+                   "counter": rb.test_counter()})
+        rb.reset()
+        data.invalidate()
     with open(os.path.join(HERE, "ref_cg_nal.json"), "w") as f:
-        json.dump({"clgaussian_test_na": {"seed": 20261113, "frac": 0.05, "scores": recs}}, f)
+        json.dump({"clgaussian_test_na": {"seed": 20261113, "frac": 0.05, "scores": recs, "tests": tests,
+                                          "allsubs": subs, "roundrobin": rr}}, f)
     print("wrote ref_cg_nal.json")
 
 

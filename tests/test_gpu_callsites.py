@@ -191,6 +191,45 @@ def test_gaussian_subset_patterns_on_incomplete_data(engine, key):
     d.release()
 
 
+def test_mi_cg_subset_patterns_on_incomplete_data(engine):
+    """allsubs / roundrobin with mi-cg on mixed data with missing cells
+    (ast_micg_with_missing / rrd_micg_with_missing): every test on the rows complete
+    for its own columns, early exit as usual."""
+    import json
+    import os
+    from bnlearn_b200 import callsites as cs
+    from util import GOLDEN, load_mixed
+    with open(os.path.join(GOLDEN, "ref_cg_nal.json")) as f:
+        fx = json.load(f)["clgaussian_test_na"]
+    names, cols, nlev = load_mixed("clgaussian_test")
+    rng = np.random.default_rng(fx["seed"])
+    na = []
+    for c, l in zip(cols, nlev):
+        c = c.copy()
+        m = rng.random(len(c)) < fx["frac"]
+        c[m] = np.iinfo(np.int32).min if l > 0 else np.nan
+        na.append(c)
+    d = engine.register(na, nlev)
+    counter = cs.TestCounter()
+    for r in fx["allsubs"]:
+        counter.reset()
+        nf = r["nfixed"]
+        p, pmin, pmax, dsep = cs.allsubs_test(d, r["x"], r["y"], r["sx"][nf:], r["sx"][:nf], "mi-cg", r["alpha"],
+                                              r["min"], r["max"], counter)
+        assert counter.value == r["counter"], (r, counter.value)
+        assert dsep == r["dsep"], (r, dsep)
+        for got, ref in ((p, r["p"]), (pmin, r["pmin"]), (pmax, r["pmax"])):
+            assert rel_close(got, ref, 1e-8, 1e-300), (r, got, ref)
+    for r in fx["roundrobin"]:
+        counter.reset()
+        zz = r["z"]
+        pv = cs.roundrobin_test(d, r["x"], zz, zz[1:1 + r["nfixed"]], "mi-cg", r["alpha"], counter)
+        assert counter.value == r["counter"]
+        for got, ref in zip(pv, r["p"]):
+            assert rel_close(got, ref, 1e-8, 1e-300), (r, list(pv))
+    d.release()
+
+
 def test_indep_test_with_mi_cg(engine):
     """mi-cg through the indep_test call site: p-values of the batched entry point,
     counter advanced by one per test."""

@@ -353,6 +353,39 @@ def test_conditional_gaussian_tests_against_reference_golden(engine):
     d.release()
 
 
+def test_conditional_gaussian_tests_on_incomplete_data(engine):
+    """mi-cg with 5 % of the cells missing (ct_micg_with_missing): every test on the
+    rows complete for all its columns -- a temporary data set gathered on the device --
+    in one call next to tests that would be complete anyway; no data set is leaked."""
+    from util import load_mixed
+    with open(os.path.join(GOLDEN, "ref_cg_nal.json")) as f:
+        fx = json.load(f)["clgaussian_test_na"]
+    names, cols, nlev = load_mixed("clgaussian_test")
+    rng = np.random.default_rng(fx["seed"])
+    na = []
+    for c, l in zip(cols, nlev):
+        c = c.copy()
+        m = rng.random(len(c)) < fx["frac"]
+        c[m] = np.iinfo(np.int32).min if l > 0 else np.nan
+        na.append(c)
+    na[0] = cols[0]                                     # one complete column pair: a complete test in the batch
+    na[5] = cols[5]
+    d = engine.register(na, nlev)
+    recs = [r for r in fx["tests"] if 0 not in [r["x"], r["y"]] + r["z"] and 5 not in [r["x"], r["y"]] + r["z"]]
+    assert len(recs) > 10
+    xs, ys, zs = [r["x"] for r in recs] + [0], [r["y"] for r in recs] + [5], [r["z"] for r in recs] + [[]]
+    st, df, pv = d.ci_cg(xs, ys, zs)
+    for i, r in enumerate(recs):
+        assert df[i] == r["df"], r
+        _check(st[i], r["stat"], ("stat", r), atol=1e-9)
+        _check(pv[i], r["p"], ("p", r), rtol=1e-8, atol=1e-300)
+    whole = engine.register(cols, nlev)                 # the complete pair equals the complete data's test
+    s2, d2, p2 = whole.ci_cg([0], [5], [[]])
+    assert st[-1] == s2[0] and df[-1] == d2[0] and pv[-1] == p2[0]
+    whole.release()
+    d.release()
+
+
 def test_ebic_against_reference_golden(engine):
     from util import load_mixed
     with open(os.path.join(GOLDEN, "ref_ebic.json")) as f:
