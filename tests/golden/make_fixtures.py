@@ -409,8 +409,29 @@ def cg_outputs():
         if t % 10 == 9:
             rb.reset()
             data.invalidate()
+    subs, rr = [], []
+    for t in range(10):                      # ast_micg_complete / rrd_micg_complete
+        m = int(rng.integers(2, 5))
+        idx = [int(i) for i in rng.choice(p, size=2 + m, replace=False)]
+        x, y, sx = idx[0], idx[1], idx[2:]
+        nf = int(rng.integers(0, 2))
+        mn = int(rng.integers(0, 2))
+        mx = int(rng.integers(max(mn, 1), min(3, m - nf) + 1))
+        rb.reset_test_counter()
+        pv, pmin, pmax, ds_ = ra.allsubs_test(data, names[x], names[y], [names[i] for i in sx],
+                                              [names[i] for i in sx[:nf]], "mi-cg", 0.05, mn, mx)
+        subs.append({"x": x, "y": y, "sx": sx, "nfixed": nf, "min": mn, "max": mx, "alpha": 0.05, "p": pv,
+                     "pmin": pmin, "pmax": pmax, "dsep": None if ds_ is None else [names.index(d) for d in ds_],
+                     "counter": rb.test_counter()})
+        rb.reset_test_counter()
+        pvs = ra.roundrobin_test(data, names[x], [names[i] for i in [y] + sx], [names[i] for i in sx[:nf]],
+                                 "mi-cg", 0.05)
+        rr.append({"x": x, "z": [y] + sx, "nfixed": nf, "alpha": 0.05, "p": [float(v) for v in pvs],
+                   "counter": rb.test_counter()})
+        rb.reset()
+        data.invalidate()
     with open(os.path.join(HERE, "ref_cg.json"), "w") as f:
-        json.dump({"clgaussian_test": {"scores": recs, "tests": tests}}, f)
+        json.dump({"clgaussian_test": {"scores": recs, "tests": tests, "allsubs": subs, "roundrobin": rr}}, f)
     print("wrote ref_cg.json")
 
 

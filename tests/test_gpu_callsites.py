@@ -191,10 +191,11 @@ def test_gaussian_subset_patterns_on_incomplete_data(engine, key):
     d.release()
 
 
-def test_mi_cg_subset_patterns_on_incomplete_data(engine):
-    """allsubs / roundrobin with mi-cg on mixed data with missing cells
-    (ast_micg_with_missing / rrd_micg_with_missing): every test on the rows complete
-    for its own columns, early exit as usual."""
+def test_mi_cg_subset_patterns(engine):
+    """allsubs / roundrobin with mi-cg on mixed data, complete (ast_micg_complete /
+    rrd_micg_complete) and with missing cells (ast_micg_with_missing /
+    rrd_micg_with_missing: every test on the rows complete for its own columns),
+    early exit as usual."""
     import json
     import os
     from bnlearn_b200 import callsites as cs
@@ -209,7 +210,14 @@ def test_mi_cg_subset_patterns_on_incomplete_data(engine):
         m = rng.random(len(c)) < fx["frac"]
         c[m] = np.iinfo(np.int32).min if l > 0 else np.nan
         na.append(c)
-    d = engine.register(na, nlev)
+    with open(os.path.join(GOLDEN, "ref_cg.json")) as f:
+        complete = json.load(f)["clgaussian_test"]
+    for data, fxs in ((cols, complete), (na, fx)):
+        _mi_cg_patterns(engine, cs, data, nlev, fxs)
+
+
+def _mi_cg_patterns(engine, cs, data, nlev, fx):
+    d = engine.register(data, nlev)
     counter = cs.TestCounter()
     for r in fx["allsubs"]:
         counter.reset()
