@@ -31,8 +31,8 @@ const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
 const int kKnobPrefetch = (int)env_ll("BNL_L2_PREFETCH", 2);
 const int kKnobGroupPrefetch = (int)env_ll("BNL_GROUP_L2_PREFETCH", 0);
 const long long kKnobGroupMaxCells = env_ll("BNL_GROUP_MAXCELLS", 0);   // 0: whatever four tables per SM allow
-// units per CTA of the base-index kernel. One unit and 1024 threads, with two CTAs per SM where the
-// tables allow, beat tiles of 2-8 units that share the base column (profiles/r1b_l2_prefetch_sweep.log).
+// units per CTA of the base-index kernel. One unit and 1024 threads beat tiles of 2-8 units of
+// 256-512 threads that share the base column (profiles/r1b_l2_prefetch_sweep.log).
 const long long kKnobBasedNuCap = env_ll("BNL_BASED_NU_CAP", 1);
 const long long kKnobBased = env_ll("BNL_BASED", 1);
 const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
@@ -456,7 +456,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         bbase += (int)bcls[K].size();                                                                          \
         tbase += btiles[K].size();                                                                             \
       }
-      // one unit per tile: the 1024-thread kernel, several CTAs per SM when the tables allow
+      // one unit per tile: the 1024-thread kernel
       if (based_nu[0] == 1) { BNL_BASED_LAUNCH(0, 5, 1, 1024) } else { BNL_BASED_LAUNCH(0, 5, 8, 256) }
       if (based_nu[1] == 1) { BNL_BASED_LAUNCH(1, 5, 1, 1024) } else { BNL_BASED_LAUNCH(1, 5, 4, 512) }
       if (based_nu[2] == 1) { BNL_BASED_LAUNCH(2, 5, 1, 1024) } else { BNL_BASED_LAUNCH(2, 5, 4, 512) }
