@@ -34,6 +34,7 @@ const long long kKnobGroupMaxCells = env_ll("BNL_GROUP_MAXCELLS", 0);   // 0: wh
 // units per CTA of the base-index kernel. One unit and 1024 threads beat tiles of 2-8 units of
 // 256-512 threads that share the base column (profiles/r1b_l2_prefetch_sweep.log).
 const long long kKnobBasedNuCap = env_ll("BNL_BASED_NU_CAP", 1);
+const long long kKnobBasedMerge = env_ll("BNL_BASED_MERGE", 1);
 const long long kKnobBased = env_ll("BNL_BASED", 1);
 const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
 const long long kKnobBasedWaves = env_ll("BNL_BASED_WAVES", 0);
@@ -323,6 +324,9 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           const int c = dev.h_units[u].cells;
           int k = 0;
           while (c > based_cap[k]) k++;
+          // one unit per CTA: every table with 32 counters per cell runs the same kernel, one
+          // CTA per SM whatever its size, so they share one launch (no partial wave in between)
+          if (kKnobBasedMerge && based_nu[k] == 1 && k < 3) k = 3;
           members[k].push_back(u);
           bmax[k] = std::max(bmax[k], c);
           grouped[u] = 2;
