@@ -34,7 +34,7 @@ const long long kKnobGroupMaxCells = env_ll("BNL_GROUP_MAXCELLS", 0);   // 0: wh
 // units per CTA of the base-index kernel. One unit and 1024 threads beat tiles of 2-8 units of
 // 256-512 threads that share the base column (profiles/r1b_l2_prefetch_sweep.log).
 const long long kKnobBasedNuCap = env_ll("BNL_BASED_NU_CAP", 1);
-const long long kKnobBasedMerge = env_ll("BNL_BASED_MERGE", 1);
+const long long kKnobBasedMerge = env_ll("BNL_BASED_MERGE", 2);
 const long long kKnobBased = env_ll("BNL_BASED", 1);
 const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
 const long long kKnobBasedWaves = env_ll("BNL_BASED_WAVES", 0);
@@ -161,6 +161,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<4, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<0, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<3, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     dev.attr_done = true;
@@ -210,7 +212,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                           (dev.max_smem - 8192) / 32};
     int based_nu[kBasedClasses] = {8, 4, 2, 1, 1, 1};
     for (int k = 0; k < kBasedClasses; k++) based_nu[k] = std::min(based_nu[k], (int)kKnobBasedNuCap);
-    std::vector<int> bcls[kBasedClasses], based_run(cnt, -1);
+    std::vector<int> bcls[kBasedClasses], based_run(cnt, -1), based_lc(cnt, 5);
+    int merged_bytes = 0;                     // largest table of the merged launch (BNL_BASED_MERGE=2)
     std::vector<int2> btiles[kBasedClasses];
     int bmax[kBasedClasses] = {0, 0, 0, 0, 0, 0};
     const size_t bstride = (size_t)((ds.nobs + 15) / 16) * 16 + 128;   // uint16 elements per base column
@@ -317,6 +320,10 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           t0 = t1;
         }
       }
+      // (the register-operand shift costs ~3 %: only when 16- or 8-counter tables are present)
+      bool mixed_lc = false;
+      for (auto &r : bruns)
+        for (int u : r) mixed_lc = mixed_lc || dev.h_units[u].cells > based_cap[3];
       // base-column runs: per class, tiles of units of one run
       for (size_t r = 0; r < bruns.size(); r++) {
         std::vector<int> members[kBasedClasses];
@@ -327,6 +334,12 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           // one unit per CTA: every table with 32 counters per cell runs the same kernel, one
           // CTA per SM whatever its size, so they share one launch (no partial wave in between)
           if (kKnobBasedMerge && based_nu[k] == 1 && k < 3) k = 3;
+          based_lc[u] = k <= 3 ? 5 : (k == 4 ? 4 : 3);
+          // ... and with the counters per cell read from the unit, the 16- and 8-counter tables too
+          if (kKnobBasedMerge >= 2 && based_nu[k] == 1 && mixed_lc) {
+            merged_bytes = std::max(merged_bytes, c << (based_lc[u] + 2));
+            k = 3;
+          }
           members[k].push_back(u);
           bmax[k] = std::max(bmax[k], c);
           grouped[u] = 2;
@@ -344,7 +357,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     int cmax[4] = {0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
       BnlUnit &hu = dev.h_units[i];
-      hu.mode = grouped[i] == 2 ? 16 + based_run[i] : 0;   // base-column units name their run
+      hu.mode = grouped[i] == 2 ? (16 + based_run[i]) | (based_lc[i] << 24) : 0;   // base-column units: run, counters per cell
       if (grouped[i]) continue;
       const int c = hu.cells;
       // a unit with a uint16 column is counted by the generic kernel, whatever its size
@@ -451,7 +464,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                        : model_chunks(nt, (double)bcls[K].size() / (double)nt * 1.5,           \
                                                       ds.nobs / 131072, nullptr);                              \
         ch = std::max(1ll, std::min(ch, std::max(1ll, ds.nobs / 131072)));                                     \
-        const int ts = ((bmax[K] << (LC + 2)) + 255) & ~255;                                                   \
+        const int ts = ((bmax[K] << ((LC ? LC : 5) + 2)) + 255) & ~255;                                                   \
         count_based_kernel<LC, NU, NT><<<(unsigned)(nt * ch), NT, (size_t)ts * based_nu[K], dev.stream>>>(      \
             dd.u8, ds.stride_u8, ds.nobs, dev.d_basecols, bstride, dev.d_units, dev.d_order + bbase,           \
             dev.d_tiles + tbase, dev.d_tables, (int)nt, (int)ch, ts, kKnobPrefetch);                                          \
@@ -461,10 +474,11 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         tbase += btiles[K].size();                                                                             \
       }
       // one unit per tile: the 1024-thread kernel
+      if (merged_bytes > 0) bmax[3] = (merged_bytes + 127) >> 7;      // stride of the merged launch, in 128-byte cells
       if (based_nu[0] == 1) { BNL_BASED_LAUNCH(0, 5, 1, 1024) } else { BNL_BASED_LAUNCH(0, 5, 8, 256) }
       if (based_nu[1] == 1) { BNL_BASED_LAUNCH(1, 5, 1, 1024) } else { BNL_BASED_LAUNCH(1, 5, 4, 512) }
       if (based_nu[2] == 1) { BNL_BASED_LAUNCH(2, 5, 1, 1024) } else { BNL_BASED_LAUNCH(2, 5, 4, 512) }
-      BNL_BASED_LAUNCH(3, 5, 1, 1024)
+      if (merged_bytes > 0) { BNL_BASED_LAUNCH(3, 0, 1, 1024) } else { BNL_BASED_LAUNCH(3, 5, 1, 1024) }
       BNL_BASED_LAUNCH(4, 4, 1, 1024)
       BNL_BASED_LAUNCH(5, 3, 1, 1024)
 #undef BNL_BASED_LAUNCH

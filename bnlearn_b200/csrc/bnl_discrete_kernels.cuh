@@ -661,10 +661,13 @@ combine_base_kernel(const uint8_t *__restrict__ u8, size_t stride, long long ful
 // per row-unit through L2. tiles[] = {first position in `order`, units}.
 #define BNL_BASED_MAX 8
 
+// LC = 0: the counters per cell are the unit's own (bits 24.. of BnlUnit::mode), so that
+// tables of every size class can share one launch; the shift is then a register operand.
 template <int LC>
-__device__ __forceinline__ void based_bump(int *hist, unsigned v, unsigned slot4) {
-  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + (((v & 0xFFFFu) << (LC + 2)) + slot4)), 1);
-  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + (((v >> 16) << (LC + 2)) + slot4)), 1);
+__device__ __forceinline__ void based_bump(int *hist, unsigned v, unsigned slot4, int sh) {
+  if (LC) sh = LC + 2;
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + (((v & 0xFFFFu) << sh) + slot4)), 1);
+  atomicAdd(reinterpret_cast<int *>(reinterpret_cast<char *>(hist) + (((v >> 16) << sh) + slot4)), 1);
 }
 
 template <int NUMAX>
@@ -697,13 +700,15 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     s_tab[threadIdx.x] = uj.table_off;
   }
   __syncthreads();
-  const int quads = (nu * tstride) >> 4;
+  const int lc = LC ? LC : (su.mode >> 24);
+  // one unit per CTA: only its own table is cleared (the launch's stride is the largest one)
+  const int quads = NUMAX == 1 ? ((s_cells[0] << (lc + 2)) + 15) >> 4 : (nu * tstride) >> 4;
   for (int c = threadIdx.x; c < quads; c += NT) reinterpret_cast<uint4 *>(hist)[c] = make_uint4(0, 0, 0, 0);
   __syncthreads();
-  const unsigned slot4 = (threadIdx.x & ((1u << LC) - 1u)) << 2;
+  const unsigned slot4 = (threadIdx.x & ((1u << lc) - 1u)) << 2;
   const int last = su.ncols - 1;
   const unsigned cmul = (unsigned)su.mul[last];
-  const uint4 *bp = reinterpret_cast<const uint4 *>(basecols + (size_t)(su.mode - 16) * bstride);
+  const uint4 *bp = reinterpret_cast<const uint4 *>(basecols + (size_t)((su.mode & 0xFFFFFF) - 16) * bstride);
   const uint4 *cp[NUMAX];
 #pragma unroll
   for (int j = 0; j < NUMAX; j++)
@@ -736,8 +741,8 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
         const unsigned cw[4] = {R.c[j].x, R.c[j].y, R.c[j].z, R.c[j].w};
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-          based_bump<LC>(hj, bw[2 * q] + __byte_perm(cw[q], 0, 0x4140) * cmul, slot4);
-          based_bump<LC>(hj, bw[2 * q + 1] + __byte_perm(cw[q], 0, 0x4342) * cmul, slot4);
+          based_bump<LC>(hj, bw[2 * q] + __byte_perm(cw[q], 0, 0x4140) * cmul, slot4, lc + 2);
+          based_bump<LC>(hj, bw[2 * q + 1] + __byte_perm(cw[q], 0, 0x4342) * cmul, slot4, lc + 2);
         }
       }
   };
@@ -768,14 +773,14 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     }
   }
   __syncthreads();
-  constexpr int NCNT = 1 << LC;
+  const int ncnt = 1 << lc;
   for (int j = 0; j < nu; j++) {
     const int *hj = reinterpret_cast<const int *>(reinterpret_cast<const char *>(hist) + j * tstride);
     int *gtab = tables + s_tab[j];
     for (int c = threadIdx.x; c < s_cells[j]; c += NT) {
       int sum = 0;
-#pragma unroll
-      for (int l = 0; l < NCNT; l++) sum += hj[c * NCNT + ((l + threadIdx.x) & (NCNT - 1))];
+#pragma unroll 8
+      for (int l = 0; l < ncnt; l++) sum += hj[(c << lc) + ((l + threadIdx.x) & (ncnt - 1))];
       if (sum) atomicAdd(&gtab[c], sum);
     }
   }
