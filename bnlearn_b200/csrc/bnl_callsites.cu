@@ -527,6 +527,8 @@ extern "C" int bnl_ci_cg(bnl_ctx *ctx, bnl_data data, int n, const int *x, const
   BnlDataSet &ds = it->second;
   if (n < 0 || (n > 0 && (!x || !y || !z_off || !stat)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_cg: bad arguments");
+  if (ds.gauss_nobs > 0)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "mi-cg needs the rows, not pooled moments (bnl_data_set_moments)");
   // Incomplete data: ct_micg_with_missing (src/tests/patterns/ctest.c:336-406) runs the
   // complete-data test on the rows that are complete for ALL columns of the test. Such a
   // test gets a temporary data set of exactly those rows (device-side row gather,

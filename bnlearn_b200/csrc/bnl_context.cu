@@ -298,7 +298,7 @@ extern "C" void bnl_shutdown(bnl_ctx *ctx) {
     if (d.stream2) cudaStreamDestroy(d.stream2);
     cudaFree(d.d_units); cudaFree(d.d_tables); cudaFree(d.d_out); cudaFree(d.d_gidx); cudaFree(d.d_order); cudaFree(d.d_tiles);
     cudaFree(d.d_basecols); cudaFree(d.d_runfirst); cudaFreeHost(d.h_runfirst);
-    cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_gidx); cudaFreeHost(d.h_order); cudaFreeHost(d.h_tiles);
+    cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_tables); cudaFreeHost(d.h_gidx); cudaFreeHost(d.h_order); cudaFreeHost(d.h_tiles);
     if (d.ev0) cudaEventDestroy(d.ev0);
     if (d.ev1) cudaEventDestroy(d.ev1);
     if (d.evc0) cudaEventDestroy(d.evc0);
@@ -855,24 +855,33 @@ extern "C" int bnl_data_commit(bnl_ctx *ctx, bnl_data data) {
   BnlDataSet &ds = it->second;
   int rc;
   if (ds.nd > 0) {
-    std::vector<int> lv(ds.nd, 0), flags(1 + ds.nd, 0);
+    std::vector<int> lv(ds.nd, 0), flags(1 + ds.nd, 0), any(1 + ds.nd, 0);
     for (int c = 0; c < ds.ncols; c++) if (!ds.is_numeric[c]) lv[ds.slot[c]] = ds.nlevels[c];
-    BnlDevice &dev = ctx->devs[0];
-    BNL_CUDA(ctx, cudaSetDevice(dev.id));
-    if ((rc = bnl_reserve_device(ctx, &dev.d_flags, &dev.flags_cap, (size_t)(2 + 2 * ds.nd)))) return rc;
-    int *d_lv = dev.d_flags + 1 + ds.nd;
-    BNL_CUDA(ctx, cudaMemsetAsync(dev.d_flags, 0, (size_t)(1 + ds.nd) * sizeof(int), dev.stream));
-    BNL_CUDA(ctx, cudaMemcpyAsync(d_lv, lv.data(), (size_t)ds.nd * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
-    int gx = (int)std::min<long long>((ds.nobs + 255) / 256, (long long)dev.sm_count * 8);
-    if (gx < 1) gx = 1;
-    scan_packed_kernel<<<dim3(gx, ds.nd), 256, 0, dev.stream>>>(ds.dev[0].u8, ds.stride_u8, ds.nobs, d_lv,
-                                                                dev.d_flags);
-    BNL_CUDA(ctx, cudaGetLastError());
-    BNL_CUDA(ctx, cudaMemcpyAsync(flags.data(), dev.d_flags, flags.size() * sizeof(int), cudaMemcpyDeviceToHost,
-                                  dev.stream));
-    BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
-    if (flags[0]) return bnl_fail(ctx, BNL_EINVAL, "a packed factor column holds a code outside 0..nlevels-1");
-    ds.slot_has_na.assign(flags.begin() + 1, flags.end());
+    // every replica is checked (each was filled by the caller), and the bytes between
+    // nobs and the column stride are forced to the NA code: the counting kernels read
+    // whole 16-row groups and rely on that padding to veto the rows past the end.
+    for (size_t d = 0; d < ctx->devs.size(); d++) {
+      BnlDevice &dev = ctx->devs[d];
+      BNL_CUDA(ctx, cudaSetDevice(dev.id));
+      if ((rc = bnl_reserve_device(ctx, &dev.d_flags, &dev.flags_cap, (size_t)(2 + 2 * ds.nd)))) return rc;
+      int *d_lv = dev.d_flags + 1 + ds.nd;
+      BNL_CUDA(ctx, cudaMemsetAsync(dev.d_flags, 0, (size_t)(1 + ds.nd) * sizeof(int), dev.stream));
+      BNL_CUDA(ctx, cudaMemcpyAsync(d_lv, lv.data(), (size_t)ds.nd * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+      if (ds.stride_u8 > (size_t)ds.nobs)
+        BNL_CUDA(ctx, cudaMemset2DAsync(ds.dev[d].u8 + ds.nobs, ds.stride_u8, BNL_NA_U8,
+                                        ds.stride_u8 - (size_t)ds.nobs, (size_t)ds.nd, dev.stream));
+      int gx = (int)std::min<long long>((ds.nobs + 255) / 256, (long long)dev.sm_count * 8);
+      if (gx < 1) gx = 1;
+      scan_packed_kernel<<<dim3(gx, ds.nd), 256, 0, dev.stream>>>(ds.dev[d].u8, ds.stride_u8, ds.nobs, d_lv,
+                                                                  dev.d_flags);
+      BNL_CUDA(ctx, cudaGetLastError());
+      BNL_CUDA(ctx, cudaMemcpyAsync(flags.data(), dev.d_flags, flags.size() * sizeof(int), cudaMemcpyDeviceToHost,
+                                    dev.stream));
+      BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+      for (size_t i = 0; i < flags.size(); i++) any[i] |= flags[i];
+    }
+    if (any[0]) return bnl_fail(ctx, BNL_EINVAL, "a packed factor column holds a code outside 0..nlevels-1");
+    ds.slot_has_na.assign(any.begin() + 1, any.end());
   }
   if (ds.nc > 0)
     for (size_t d = 0; d < ctx->devs.size(); d++)

@@ -548,12 +548,25 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
     if (rq.kind == 2) {
       BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
-      // tables straight back to the caller, unit by unit (offsets are the caller's).
-      for (int i = 0; i < cnt; i++)
-        BNL_CUDA(ctx, cudaMemcpyAsync(rq.tables + rq.table_off[pos + i], dev.d_tables + dev.h_units[i].table_off,
-                                      (size_t)dev.h_units[i].cells * sizeof(int), cudaMemcpyDeviceToHost,
+      // tables back to the caller in ONE copy: the scratch tables of a sub-batch are
+      // contiguous. When the caller's offsets are contiguous too the copy lands in
+      // place; otherwise it goes to a pinned buffer and is scattered on the host.
+      bool contiguous = true;
+      for (int i = 0; i < cnt && contiguous; i++)
+        contiguous = rq.table_off[pos + i + 1] - rq.table_off[pos + i] == (int64_t)dev.h_units[i].cells;
+      if (contiguous) {
+        BNL_CUDA(ctx, cudaMemcpyAsync(rq.tables + rq.table_off[pos], dev.d_tables, (size_t)cells * sizeof(int),
+                                      cudaMemcpyDeviceToHost, dev.stream));
+        BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+      } else {
+        if ((rc = bnl_reserve_pinned(ctx, &dev.h_tables, &dev.h_tables_cap, (size_t)cells))) return rc;
+        BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_tables, dev.d_tables, (size_t)cells * sizeof(int), cudaMemcpyDeviceToHost,
                                       dev.stream));
-      BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+        BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+        for (int i = 0; i < cnt; i++)
+          memcpy(rq.tables + rq.table_off[pos + i], dev.h_tables + dev.h_units[i].table_off,
+                 (size_t)dev.h_units[i].cells * sizeof(int));
+      }
     } else {
       if (rq.kind == 1 && (rq.code == BNL_FNML || rq.code == BNL_QNML) && (rc = bnl_regret_table(ctx, dev)))
         return rc;

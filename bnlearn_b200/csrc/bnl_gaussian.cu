@@ -299,6 +299,10 @@ int bnl_ci_gaussian_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const in
   if (n < 0 || (n > 0 && (!x || !y || !z_off)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_gaussian: bad arguments");
   if (ds.nc == 0) return bnl_fail(ctx, BNL_EINVAL, "the data set has no numeric columns");
+  // mi-g-sh needs a pass over the rows (the shrinkage intensity), which a rank of a
+  // row-sharded run only holds in part: refuse rather than return a shard-local value.
+  if (ds.gauss_nobs > 0 && test_e == BNL_MI_G_SH)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "mi-g-sh needs the rows, not pooled moments (bnl_data_set_moments)");
   GRequest rq{0, test_e, 0.0, n, 2, x, y, z_off, z_idx, stat, df, pvalue};
   return run_grequest(ctx, ds, rq);
 }
@@ -523,6 +527,9 @@ extern "C" int bnl_score_cg(bnl_ctx *ctx, bnl_data data, int score_e, double k, 
   auto it = ctx->data.find(data);
   if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   BnlDataSet &ds = it->second;
+  // conditional Gaussian moments are gathered from the rows this rank holds
+  if (ds.gauss_nobs > 0)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "conditional Gaussian scores need the rows, not pooled moments");
   if (score_e == BNL_EBIC_CG) {           // per.node.score.c:194-212
     int rc = bnl_score_cg(ctx, data, BNL_BIC_CG, k, n, target, pa_off, pa_idx, score, nparams);
     if (rc) return rc;

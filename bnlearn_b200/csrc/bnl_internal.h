@@ -54,6 +54,7 @@ struct BnlDevice {
   int *h_runfirst = nullptr; size_t h_runfirst_cap = 0;  // pinned
   BnlUnit *h_units = nullptr; size_t h_units_cap = 0;    // pinned
   double *h_out = nullptr; size_t h_out_cap = 0;         // pinned
+  int *h_tables = nullptr; size_t h_tables_cap = 0;      // pinned: tables on their way back (bnl_counts)
   int *h_gidx = nullptr; size_t h_gidx_cap = 0;          // pinned
   // registration scratch (grow-only) and a small cache of released data-set
   // buffers: cudaMalloc / cudaFree synchronise the device and can cost tens of

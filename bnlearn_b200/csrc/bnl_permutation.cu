@@ -521,8 +521,9 @@ int bnl_ci_gaussian_mc_ex(bnl_ctx *ctx, bnl_data data, int test_e, int B, double
   BnlDevice &dev = ctx->devs[0];
   BnlDeviceData &dd = ds.dev[0];
   BNL_CUDA(ctx, cudaSetDevice(dev.id));
-  // permutations per device batch: at most 32 MB of row indices
-  const long long pcap = std::max(1ll, std::min<long long>(B + 1, (8ll << 20) / std::max(1ll, ds.nobs)));
+  // permutations per device batch: about 32 MB of row indices, and never fewer than two
+  // (the first batch holds the identity next to the first drawn permutation)
+  const long long pcap = std::max(2ll, std::min<long long>(B + 1, (8ll << 20) / std::max(1ll, ds.nobs)));
   DeviceBuf d_perm, d_cross, d_tmp;
   size_t tmp_doubles = 0;
   int *h_perm = nullptr;
@@ -614,7 +615,9 @@ int bnl_ci_gaussian_mc_ex(bnl_ctx *ctx, bnl_data data, int test_e, int B, double
       yslot = 1;
       N = nc;
     }
-    const long long pmax = std::max(1ll, std::min<long long>(B + 1, (long long)(perm_ints / (size_t)N)));
+    const long long pmax = std::max(2ll, std::min<long long>(B + 1, (long long)(perm_ints / (size_t)N)));
+    if ((size_t)pmax * (size_t)N > perm_ints)
+      return bnl_fail(ctx, BNL_ENOMEM, "bnl_ci_gaussian_mc: permutation buffer too small (%lld x %lld)", pmax, N);
     // a constant variable is independent of anything (no draw is consumed).
     if (cov[0] == 0.0 || cov[1 + (size_t)k] == 0.0) { stat[u] = 0.0; pvalue[u] = 1.0; continue; }
     const int kk = nz == 0 ? 1 : k;       // marginal: only the cross-product with x changes
@@ -643,6 +646,8 @@ int bnl_ci_gaussian_mc_ex(bnl_ctx *ctx, bnl_data data, int test_e, int B, double
           pool[(size_t)j] = pool[(size_t)--left];
         }
       }
+      if ((size_t)np * (size_t)N > perm_ints)
+        return bnl_fail(ctx, BNL_ENOMEM, "bnl_ci_gaussian_mc: %lld permutations of %lld rows overrun the buffer", np, N);
       BNL_CUDA(ctx, cudaMemcpyAsync(d_perm.p, h_perm, (size_t)np * N * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
       perm_cross_kernel<<<dim3((unsigned)np, (unsigned)kk), BNL_PERM_THREADS, 0, dev.stream>>>(
           f64, fstride, dmean, cols, yslot, N, (const int *)d_perm.p, (double *)d_cross.p, kk);

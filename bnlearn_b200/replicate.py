@@ -24,6 +24,10 @@ def broadcast_dataset(engine, columns, nlevels, nobs, src=0):
     """Every rank calls this; only `src` needs `columns` (host arrays, as for
     Engine.register). Returns this rank's DataSet."""
     rank = dist.get_rank()
+    # checked on EVERY rank before the first collective: a rank that raised on its own
+    # (alloc refuses what register accepts) would leave the others waiting in the broadcast.
+    if nlevels is not None and any(int(l) > 127 for l in nlevels):
+        raise ValueError("broadcast_dataset carries the uint8 factor block only: at most 127 levels per factor")
     if rank == src:
         ds = engine.register(columns, nlevels)
     else:
@@ -65,3 +69,87 @@ def pool_moments(nobs, mean, cov, device=None):
     second = torch.from_numpy((float(nobs) - 1.0) * cov + float(nobs) * np.outer(d, d)).to(dev)
     dist.all_reduce(second, op=dist.ReduceOp.SUM)
     return int(round(n)), pooled_mean, second.cpu().numpy() / (n - 1.0)
+
+
+# ---------------------------------------------------------------------------
+# Units sharded over the ranks of a job: every rank holds a
+# replica of the data set, takes a contiguous block of each batch and the doubles
+# are gathered in index order, so the result does not depend on the world size.
+
+def block(n, world, rank):
+    """Contiguous block [b, e) of n units for `rank` (the split bnl_block uses
+    inside a multi-device context)."""
+    return n * rank // world, n * (rank + 1) // world
+
+
+def gather_rows(mine, n, device=None):
+    """Every rank passes its block of rows (float64 array [e - b, width], blocks as
+    block() cuts them); every rank gets the [n, width] array in index order. One
+    all-gather of equal-size padded blocks (NCCL when `device` is a CUDA device)."""
+    import numpy as np
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    mine = np.ascontiguousarray(mine, dtype=np.float64)
+    if world == 1:
+        return mine
+    width = mine.shape[1] if mine.ndim == 2 else 1
+    per = (n + world - 1) // world + 1
+    buf = torch.zeros((per, width), dtype=torch.float64)
+    buf[:mine.shape[0]] = torch.from_numpy(mine.reshape(-1, width))
+    if device is not None:
+        buf = buf.to(device)
+    parts = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(parts, buf)
+    out = np.empty((n, width))
+    for r, p in enumerate(parts):
+        b, e = block(n, world, r)
+        out[b:e] = p[:e - b].cpu().numpy()
+    return out
+
+
+class ShardedBackend:
+    """A learners backend whose batched calls are split over the ranks: the pairs
+    of one pc.stable level go to the workers in contiguous blocks, as
+    smartSapply / parSapplyLB hands them to the cluster's slaves (R/pcalgo.R:24-28),
+    and every rank receives all results, so the level loop runs identically
+    everywhere. `backend` is this rank's own (learners.GpuBackend on its replica)."""
+
+    def __init__(self, backend, device=None):
+        self.backend = backend
+        self.device = device
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.gathers = 0
+
+    def allsubs_batch(self, x, y, sx, nfixed, test, alpha, minsize, maxsize):
+        import numpy as np
+        n = len(x)
+        b, e = block(n, self.world, self.rank)
+        mine = self.backend.allsubs_batch(x[b:e], y[b:e], sx[b:e], nfixed[b:e], test, alpha, minsize, maxsize)
+        if self.world == 1:
+            return mine
+        width = 4 + max([len(s) for s in sx] + [0])
+        rows = np.zeros((e - b, width))
+        for k, (p, pmin, pmax, dsep) in enumerate(mine):
+            rows[k, :3] = (p, pmin, pmax)
+            rows[k, 3] = -1 if dsep is None else len(dsep)
+            if dsep:
+                rows[k, 4:4 + len(dsep)] = dsep
+        full = gather_rows(rows, n, self.device)
+        self.gathers += 1
+        out = []
+        for r in full:
+            nd = int(r[3])
+            out.append((float(r[0]), float(r[1]), float(r[2]), None if nd < 0 else [int(v) for v in r[4:4 + nd]]))
+        return out
+
+    def total_tests(self):
+        """Sum of the ranks' test counters (R/learning-algorithms.R:163-165)."""
+        t = torch.tensor([float(self.backend.counter.value)], dtype=torch.float64)
+        if self.world > 1:
+            if self.device is not None:
+                t = t.to(self.device)
+            dist.all_reduce(t)
+        return float(t.cpu()[0])
+
+    def __getattr__(self, name):            # indep_test, roundrobin, scores: this rank's own
+        return getattr(self.backend, name)

@@ -140,3 +140,78 @@ def random_gaussian_bn(nnodes, n, seed=20261108, max_in=5, mean_in=1.5):
         cols.append(np.ascontiguousarray(x))
         parents[nm] = [names[j] for j in pa]
     return names, cols, parents
+
+
+# ---------------------------------------------------------------------------
+# The two large shapes generated ON THE DEVICE with torch (seeded): numpy needs
+# minutes for 10^9 categorical / 2 x 10^9 normal draws, the GPU seconds. The DAG,
+# levels and coefficients come from numpy PCG64(seed) as above; only the uniform
+# / normal draws are torch's. Harness code for tests and bench.py (needs CUDA);
+# both return host arrays in the reference's conventions.
+
+def random_discrete_bn_device(nnodes=1000, rows=1_000_000, seed=20261107, max_in=4, mean_in=1.5):
+    """Config C shape: -> (int32 array [nnodes, rows] of 1-based codes, levels, parents)."""
+    import torch
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed)
+    cpu = np.random.Generator(np.random.PCG64(seed))
+    levels = [int(v) for v in cpu.integers(2, 5, nnodes)]
+    cols = torch.empty((nnodes, rows), dtype=torch.int32, device="cuda")
+    parents = []
+    for i in range(nnodes):
+        k = min(int(cpu.poisson(mean_in)), max_in, i)
+        pa = sorted(int(j) for j in cpu.choice(i, size=k, replace=False)) if k else []
+        parents.append(pa)
+        cfg = torch.zeros(rows, dtype=torch.int64, device="cuda")
+        mul = 1
+        for j in pa:
+            cfg += (cols[j] - 1).to(torch.int64) * mul
+            mul *= levels[j]
+        cpt = torch.from_numpy(cpu.dirichlet(np.ones(levels[i]), size=mul)).to("cuda")
+        cdf = torch.cumsum(cpt, dim=1)
+        u = torch.rand(rows, generator=g, device="cuda", dtype=torch.float64)
+        lvl = (u[:, None] > cdf[cfg]).sum(dim=1).clamp_(max=levels[i] - 1)
+        cols[i] = (lvl + 1).to(torch.int32)
+    host = cols.cpu().numpy()
+    del cols
+    torch.cuda.empty_cache()
+    return host, levels, parents
+
+
+def random_gaussian_bn_device(nvars=2000, rows=1_000_000, seed=20261108, max_in=5, mean_in=1.5):
+    """Config D shape: -> (float64 array [nvars, rows], parents)."""
+    import torch
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed)
+    cpu = np.random.Generator(np.random.PCG64(seed))
+    x = torch.empty((nvars, rows), dtype=torch.float64, device="cuda")
+    parents = []
+    for i in range(nvars):
+        k = min(int(cpu.poisson(mean_in)), max_in, i)
+        pa = [int(j) for j in cpu.choice(i, size=k, replace=False)] if k else []
+        parents.append(pa)
+        x[i] = torch.randn(rows, generator=g, device="cuda", dtype=torch.float64) * float(cpu.uniform(0.5, 1.5))
+        for j in pa:
+            x[i] += float(cpu.uniform(0.3, 1.0) * cpu.choice([-1.0, 1.0])) * x[j]
+    host = x.cpu().numpy()
+    del x
+    torch.cuda.empty_cache()
+    return host, parents
+
+
+def alarm_shaped_cached(rows, seed=20261106):
+    """alarm_shaped() as an int8 array [37, rows], cached on local disk between
+    invocations (the numpy sampler needs ~30 s for 10 M rows)."""
+    import os
+    cache = os.path.join("/tmp", "bnl_bench_cache")
+    os.makedirs(cache, exist_ok=True)
+    path = os.path.join(cache, "alarm_%d_%d.npy" % (rows, seed))
+    if os.path.exists(path):
+        codes = np.load(path)
+    else:
+        _, cols, _ = alarm_shaped(rows, seed)
+        codes = np.stack(cols).astype(np.int8)
+        tmp = path + ".%d.tmp.npy" % os.getpid()
+        np.save(tmp, codes)
+        os.replace(tmp, path)
+    return list(ALARM_NAMES), codes, list(ALARM_LEVELS)

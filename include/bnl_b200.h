@@ -312,8 +312,11 @@ int bnl_gaussian_moments(bnl_ctx *ctx, bnl_data data, double *mean, double *cov)
  * mean = sum n_r mean_r / n, (n - 1) cov = sum [(n_r - 1) cov_r + n_r (mean_r - mean)
  * (mean_r - mean)'], two sum all-reduces over p and p^2 doubles -- and hand the result
  * back here. Every Gaussian test and score of the data set is then served from the
- * pooled moments with nobs_total rows (complete data only). Replaces c_covmat over
- * the whole data (src/core/covariance.matrix.c:65-97). */
+ * pooled moments with nobs_total rows (complete data only). What needs a pass over
+ * the rows themselves is refused on such a data set with BNL_EUNSUPPORTED instead
+ * of answering from this rank's rows alone: mi-g-sh (shrinkage intensity), the
+ * permutation tests, bnl_score_cg and bnl_ci_cg. Replaces c_covmat over the whole
+ * data (src/core/covariance.matrix.c:65-97). */
 int bnl_data_set_moments(bnl_ctx *ctx, bnl_data data, int64_t nobs_total, const double *mean,
                          const double *cov);
 

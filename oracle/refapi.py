@@ -248,6 +248,26 @@ def chisqtest(x, llx, y, lly, test_e, z=None, llz=0):
     return st, df.value
 
 
+def tables3d(x, llx, y, lly, z=None, llz=1):
+    """reference new_3d_table + fill_3d_table (src/core/contingency.tables.c:170-223):
+    the joint counts n[z][x][y] as an int32 array of that shape, plus the number of
+    complete rows. z: 1-based configuration vector (c_fast_config with offset 1);
+    None counts the marginal table in a single stratum."""
+    L = rb.lib()
+    x = np.ascontiguousarray(x, dtype=np.int32)
+    y = np.ascontiguousarray(y, dtype=np.int32)
+    z = np.ones(len(x), dtype=np.int32) if z is None else np.ascontiguousarray(z, dtype=np.int32)
+    tab = L.new_3d_table(int(llx), int(lly), int(llz))
+    L.fill_3d_table(_ip(x), _ip(y), _ip(z), C.byref(tab), len(x))
+    out = np.empty((llz, llx, lly), dtype=np.int32)
+    for k in range(llz):
+        for i in range(llx):
+            out[k, i, :] = np.ctypeslib.as_array(tab.n[k][i], shape=(lly,))
+    nobs = int(tab.nobs)
+    L.Free3DTAB(tab)
+    return out, nobs
+
+
 # test_e values of the permutation tests (src/tests/tests.h:21-34)
 MC_TESTS = {"mc-mi": 50, "mc-x2": 51, "sp-mi": 52, "sp-x2": 53, "mc-jt": 54,
             "smc-mi": 60, "smc-x2": 61, "smc-jt": 62,

@@ -37,6 +37,13 @@ def _load_openblas():
         C.CDLL(hits[0], mode=C.RTLD_GLOBAL)
 
 
+class Counts3D(C.Structure):
+    """counts3d of the reference (src/core/contingency.tables.h:27-38)."""
+    _fields_ = [("llx", C.c_int), ("lly", C.c_int), ("llz", C.c_int), ("nobs", C.c_int),
+                ("n", C.POINTER(C.POINTER(C.POINTER(C.c_int)))), ("ni", C.POINTER(C.POINTER(C.c_int))),
+                ("nj", C.POINTER(C.POINTER(C.c_int))), ("nk", C.POINTER(C.c_int))]
+
+
 def lib():
     global _LIB
     if _LIB is not None:
@@ -78,6 +85,9 @@ def lib():
                                      c_dbl_p, C.c_int, C.c_bool]),
         "c_cchisqtest": (C.c_double, [c_int_p, C.c_int, c_int_p, C.c_int, c_int_p,
                                       C.c_int, C.c_int, c_dbl_p, C.c_int, C.c_bool]),
+        "new_3d_table": (Counts3D, [C.c_int, C.c_int, C.c_int]),
+        "fill_3d_table": (None, [c_int_p, c_int_p, c_int_p, C.POINTER(Counts3D), C.c_int]),
+        "Free3DTAB": (None, [Counts3D]),
         "Rf_pchisq": (C.c_double, [C.c_double, C.c_double, C.c_int, C.c_int]),
         "Rf_pt": (C.c_double, [C.c_double, C.c_double, C.c_int, C.c_int]),
         "Rf_pnorm5": (C.c_double, [C.c_double, C.c_double, C.c_double, C.c_int, C.c_int]),

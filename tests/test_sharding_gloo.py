@@ -193,3 +193,49 @@ def test_row_sharded_gaussian_moments_world_size_2(tmp_path):
     assert got[0] == x.shape[1]
     assert np.allclose(got[1:1 + p], x.mean(axis=1), rtol=1e-13, atol=0)
     assert np.allclose(got[1 + p:].reshape(p, p), np.cov(x), rtol=1e-12, atol=1e-15)
+
+
+# ---------------------------------------------------------------------------
+# The level batches of pc.stable split over two ranks (replicate.ShardedBackend,
+# what `bench.py --gpus N` runs over NCCL): here over gloo, with the reference's
+# own C evaluating each rank's block, against the unsharded run.
+
+def _pc_worker(rank, world, port, out_path):
+    import pickle
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from bnlearn_b200 import learners
+    from bnlearn_b200.replicate import ShardedBackend, block, gather_rows
+    from refbackend import RefBackend
+    names, cols, nlev = load_discrete("learning_test")
+    sb = ShardedBackend(RefBackend(cols, nlev))
+    skel, dsep, pvals = learners.pc_stable(sb, len(cols), "mi", 0.05)
+    tests = sb.total_tests()
+    # gather_rows on a ragged split: 7 rows over 2 ranks
+    b, e = block(7, world, rank)
+    rows = gather_rows(np.arange(b, e, dtype=np.float64).reshape(-1, 1) * np.array([[1.0, 10.0]]), 7)
+    if rank == 0:
+        with open(out_path, "wb") as f:
+            pickle.dump((skel, dsep, pvals, tests, sb.gathers, rows), f)
+    dist.destroy_process_group()
+
+
+def test_sharded_pc_stable_world_size_2(tmp_path):
+    import pickle
+    from oracle import refbind
+    if not refbind.available():
+        pytest.skip("oracle/_ref/libbnref.so is not built")
+    from bnlearn_b200 import learners
+    from refbackend import RefBackend
+    names, cols, nlev = load_discrete("learning_test")
+    rbk = RefBackend(cols, nlev)
+    want = learners.pc_stable(rbk, len(cols), "mi", 0.05)
+    want_tests = rbk.counter.value
+    out = str(tmp_path / "pc.pkl")
+    mp.start_processes(_pc_worker, args=(2, _free_port(), out), nprocs=2, join=True, start_method="fork")
+    with open(out, "rb") as f:
+        skel, dsep, pvals, tests, gathers, rows = pickle.load(f)
+    assert skel == want[0] and dsep == want[1] and pvals == want[2]
+    assert tests == want_tests and gathers >= 2
+    assert np.array_equal(rows, np.arange(7.0).reshape(-1, 1) * np.array([[1.0, 10.0]]))
