@@ -536,6 +536,75 @@ def vstructures(backend, nnodes, nbr, mb, test, alpha, dsep=None, pvals=None, ma
     return out
 
 
+def boot_arc_counts(engine, columns, nlevels, ids, score, arg=0.0, seed=0, maxp=np.inf, native=True,
+                    workers=4, devices=None):
+    """The replicates `ids` of boot_strength: -> (arc count matrix [from, to], tests).
+    Replicate r resamples with the numpy PCG64 stream seed + r whatever share it is
+    part of, so any split of the replicates over workers, devices or ranks sums to
+    the same counts (the reference's bootstrap_reduce averages per-worker results,
+    src/learning/averaging/bootstrap.c:126-186)."""
+    from .callsites import TestCounter
+    ids = list(ids)
+    n = len(columns)
+    nobs = len(columns[0])
+
+    def rows_of(r):
+        return np.random.Generator(np.random.PCG64(seed + r)).integers(0, nobs, nobs)
+
+    if not native:
+        arcs, tests = np.zeros((n, n)), 0.0
+        for r in ids:
+            rows = rows_of(r)
+            ds = engine.register([c[rows] for c in columns], nlevels)
+            be = GpuBackend(ds)
+            amat, _ = hc(be, n, score, arg, maxp)
+            tests += be.counter.value
+            arcs += amat
+            ds.release()
+        return arcs, tests
+    from .engine import Engine
+
+    def run(engine_w, share):
+        src = engine_w.register(columns, nlevels)
+        acc, cnt = np.zeros((n, n)), 0.0
+        for r in share:
+            ds = src.resample(rows_of(r))
+            counter = TestCounter()
+            amat, _, _ = ds.hc(score, arg, maxp=maxp, counter=counter)
+            cnt += counter.value
+            acc += amat
+            ds.release()
+        src.release()
+        return acc, cnt
+
+    workers = max(1, min(int(workers), len(ids)))
+    if workers == 1 and devices is None:
+        return run(engine, ids)
+    from concurrent.futures import ThreadPoolExecutor
+    if devices is None:
+        pool_engines, extra = [engine], [Engine() for _ in range(workers - 1)]
+    else:
+        pool_engines, extra = [], [Engine([int(devices[w % len(devices)])]) for w in range(workers)]
+    pool_engines += extra
+    try:
+        with ThreadPoolExecutor(workers) as pool:
+            parts = list(pool.map(lambda w: run(pool_engines[w], ids[w::workers]), range(workers)))
+    finally:
+        for e in extra:
+            e.close()
+    return sum(p[0] for p in parts), sum(p[1] for p in parts)
+
+
+def strength_from_counts(arcs, replicates):
+    """(strength, direction) from the arc counts of `replicates` networks
+    (R/arc.strength.R:167-227 with cpdag = FALSE)."""
+    prob = arcs / replicates
+    strength = prob + prob.T
+    with np.errstate(invalid="ignore", divide="ignore"):
+        direction = np.where(strength > 0, prob / strength, 0.0)
+    return strength, direction
+
+
 def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, maxp=np.inf,
                   native=True, workers=4, devices=None):
     """boot.strength(algorithm = "hc", cpdag = FALSE): arc strength / direction
@@ -552,62 +621,9 @@ def boot_strength(engine, columns, nlevels, replicates, score, arg=0.0, seed=0, 
     (the reference gives each cluster slave ceil(R/s) replicates,
     R/arc.strength.R:210) -- and `engine` is then only used when devices is None.
     The result depends neither on `workers` nor on `devices`."""
-    from .callsites import TestCounter
-    n = len(columns)
-    nobs = len(columns[0])
-
-    def rows_of(r):
-        return np.random.Generator(np.random.PCG64(seed + r)).integers(0, nobs, nobs)
-
-    if not native:
-        arcs, tests = np.zeros((n, n)), 0.0
-        for r in range(replicates):
-            rows = rows_of(r)
-            ds = engine.register([c[rows] for c in columns], nlevels)
-            be = GpuBackend(ds)
-            amat, _ = hc(be, n, score, arg, maxp)
-            tests += be.counter.value
-            arcs += amat
-            ds.release()
-    else:
-        from .engine import Engine
-
-        def run(engine_w, share):
-            src = engine_w.register(columns, nlevels)
-            acc, cnt = np.zeros((n, n)), 0.0
-            for r in share:
-                ds = src.resample(rows_of(r))
-                counter = TestCounter()
-                amat, _, _ = ds.hc(score, arg, maxp=maxp, counter=counter)
-                cnt += counter.value
-                acc += amat
-                ds.release()
-            src.release()
-            return acc, cnt
-
-        workers = max(1, min(int(workers), replicates))
-        if workers == 1 and devices is None:
-            arcs, tests = run(engine, range(replicates))
-        else:
-            from concurrent.futures import ThreadPoolExecutor
-            if devices is None:
-                pool_engines, extra = [engine], [Engine() for _ in range(workers - 1)]
-            else:
-                pool_engines, extra = [], [Engine([int(devices[w % len(devices)])]) for w in range(workers)]
-            pool_engines += extra
-            try:
-                with ThreadPoolExecutor(workers) as pool:
-                    parts = list(pool.map(lambda w: run(pool_engines[w], range(w, replicates, workers)),
-                                          range(workers)))
-            finally:
-                for e in extra:
-                    e.close()
-            arcs = sum(p[0] for p in parts)
-            tests = sum(p[1] for p in parts)
-    prob = arcs / replicates
-    strength = prob + prob.T
-    with np.errstate(invalid="ignore", divide="ignore"):
-        direction = np.where(strength > 0, prob / strength, 0.0)
+    arcs, tests = boot_arc_counts(engine, columns, nlevels, range(replicates), score, arg, seed, maxp, native,
+                                  workers, devices)
+    strength, direction = strength_from_counts(arcs, replicates)
     return strength, direction, tests
 
 
