@@ -298,7 +298,8 @@ extern "C" void bnl_shutdown(bnl_ctx *ctx) {
     if (d.stream2) cudaStreamDestroy(d.stream2);
     cudaFree(d.d_units); cudaFree(d.d_tables); cudaFree(d.d_out); cudaFree(d.d_gidx); cudaFree(d.d_order); cudaFree(d.d_tiles);
     cudaFree(d.d_basecols); cudaFree(d.d_runfirst); cudaFreeHost(d.h_runfirst);
-    cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_tables); cudaFreeHost(d.h_gidx); cudaFreeHost(d.h_order); cudaFreeHost(d.h_tiles);
+    cudaFree(d.d_pairG); cudaFree(d.d_pairmeta);
+    cudaFreeHost(d.h_units); cudaFreeHost(d.h_out); cudaFreeHost(d.h_tables); cudaFreeHost(d.h_pairmeta); cudaFreeHost(d.h_gidx); cudaFreeHost(d.h_order); cudaFreeHost(d.h_tiles);
     if (d.ev0) cudaEventDestroy(d.ev0);
     if (d.ev1) cudaEventDestroy(d.ev1);
     if (d.evc0) cudaEventDestroy(d.evc0);

@@ -39,9 +39,12 @@ const long long kKnobBased = env_ll("BNL_BASED", 1);
 const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
 const long long kKnobBasedWaves = env_ll("BNL_BASED_WAVES", 0);
 const size_t kMaxBaseScratch = (size_t)1 << 30;   // bytes of base-index columns per launch
+// all-pairs contraction on the tensor cores (bnl_pairs.cu): 0 off, 1 when the cost model prefers it,
+// 2 whenever eligible. Read at every call, so that a test can switch it inside one process.
+long long knob_pairs() { return env_ll("BNL_PAIRS", 1); }
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
-const int kMaxBatchUnits = 1 << 16;
+const int kMaxBatchUnits = 1 << 19;           // the first hc iteration on 1000 nodes (499 500 units) is one batch
 
 BnlDataSet *find_data(bnl_ctx *ctx, bnl_data h) {
   auto it = ctx->data.find(h);
@@ -169,6 +172,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
   }
   const int smem_cap_cells = (dev.max_smem - 8192) / 4;
   const long long groups = (ds.nobs + 15) / 16;
+  std::vector<int> pair_lev;
   int pos = b;
   while (pos < e) {
     long long cells = 0;
@@ -203,6 +207,28 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     // last (score_cache_fill's candidates of one node), small tables, no NA. They
     // are cut into tiles of up to BNL_GROUP_MAX units whose tables fit one SM.
     std::vector<char> grouped(cnt, 0);
+    // Units that are one- or two-way tables of small factors: when the batch asks for
+    // many pairs of few columns (first hc iteration, pc.stable level 0, mi.matrix) they
+    // all come out of ONE indicator cross-product on the tensor cores (bnl_pairs.cuh)
+    // instead of one row pass each.
+    std::vector<int> pair_units;
+    const long long kKnobPairs = knob_pairs();
+    if (kKnobPairs && ds.nobs >= 4096) {
+      std::vector<int> lev_by_slot(ds.nd, 0);
+      for (int c = 0; c < ds.ncols; c++)
+        if (!ds.is_numeric[c] && !ds.is_wide[c]) lev_by_slot[ds.slot[c]] = ds.nlevels[c];
+      for (int i = 0; i < cnt; i++)
+        if (bnl_pairs_eligible(dev.h_units[i], lev_by_slot)) pair_units.push_back(i);
+      bool take = pair_units.size() >= 32;
+      if (take && kKnobPairs < 2) {
+        double tensor_s, atomic_s;
+        bnl_pairs_cost(dev, ds, dev.h_units, pair_units, lev_by_slot, &tensor_s, &atomic_s);
+        take = tensor_s < 0.8 * atomic_s;
+      }
+      if (!take) pair_units.clear();
+      for (int i : pair_units) grouped[i] = 3;
+      pair_lev.swap(lev_by_slot);
+    }
     std::vector<std::vector<int>> runs, bruns;
     // base-column classes: counters per cell / units per tile (count_based_kernel)
     const int kBasedClasses = 6;
@@ -275,7 +301,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           }
           if (small.size() >= 4) runs.push_back(std::move(small));
           // the base-index column costs 2 bytes per row of scratch and one extra pass
-          if (big.size() >= 4 && (bruns.size() + 1) * brun_bytes <= kMaxBaseScratch) bruns.push_back(std::move(big));
+          if (big.size() >= 4 && (bruns.size() + 1) * brun_bytes <= kMaxBaseScratch && bruns.size() < 65000)
+            bruns.push_back(std::move(big));          // (grid.y of combine_base_kernel)
         }
         i = j;
       }
@@ -445,6 +472,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                     cudaMemcpyHostToDevice, dev.stream));
     BNL_CUDA(ctx, cudaMemsetAsync(dev.d_tables, 0, (size_t)cells * sizeof(int), dev.stream));
     BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
+    if (!pair_units.empty() && (rc = bnl_pairs_run(ctx, dev, ds, dd, dev.h_units, pair_units, pair_lev, tm))) return rc;
     if (groups > 0 && !bruns.empty()) {
       // base indices of every run (complete 16-row groups), then one launch per class
       const long long full = ds.nobs / 16;

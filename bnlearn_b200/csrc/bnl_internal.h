@@ -55,6 +55,11 @@ struct BnlDevice {
   BnlUnit *h_units = nullptr; size_t h_units_cap = 0;    // pinned
   double *h_out = nullptr; size_t h_out_cap = 0;         // pinned
   int *h_tables = nullptr; size_t h_tables_cap = 0;      // pinned: tables on their way back (bnl_counts)
+  // all-pairs contraction (bnl_pairs.cu): the indicator cross-product matrix and its plan
+  int *d_pairG = nullptr; size_t pairG_cap = 0;
+  int *d_pairmeta = nullptr; size_t pairmeta_cap = 0;
+  int *h_pairmeta = nullptr; size_t h_pairmeta_cap = 0;  // pinned
+  bool pair_attr_done = false;
   int *h_gidx = nullptr; size_t h_gidx_cap = 0;          // pinned
   // registration scratch (grow-only) and a small cache of released data-set
   // buffers: cudaMalloc / cudaFree synchronise the device and can cost tens of
@@ -196,6 +201,16 @@ int bnl_regret_table(bnl_ctx *ctx, BnlDevice &dev);
 
 // per-call timing of one device block.
 struct BnlTiming { float total = 0.f, count = 0.f, epi = 0.f; int launches = 0; };
+
+// All-pairs contraction on the tensor cores (bnl_pairs.cu, kernels in bnl_pairs.cuh): decide whether the pair units of a batch are worth one
+// contraction, run it and fill their tables. picked[] lists positions in h_units.
+bool bnl_pairs_eligible(const BnlUnit &u, const std::vector<int> &lev_by_slot);
+int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlDeviceData &dd,
+                  const BnlUnit *h_units, const std::vector<int> &picked, const std::vector<int> &lev_by_slot,
+                  BnlTiming *tm);
+// estimated seconds of the contraction for these units, and of counting them one by one
+void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const BnlUnit *h_units, const std::vector<int> &picked,
+                    const std::vector<int> &lev_by_slot, double *tensor_s, double *atomic_s);
 
 // split [0, n) into ndev contiguous blocks.
 static inline void bnl_block(int n, int ndev, int d, int *begin, int *end) {

@@ -1,1 +1,134 @@
+// bnl_pairs.cu -- host side of the all-pairs contraction (bnl_pairs.cuh): which
+// units of a batch it serves, the tile / split plan, launches.
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+
 #include "bnl_pairs.cuh"
+
+namespace {
+
+long long env_ll(const char *name, long long dflt) {
+  const char *v = getenv(name);
+  return (v && *v) ? atoll(v) : dflt;
+}
+// effective multiply-accumulate rate of pair_onehot_kernel on one B200 (measured,
+// profiles/): the producers' code expansion, not the tensor pipe, sets it.
+const double kPairMacRate = (double)env_ll("BNL_PAIRS_GMACS", 400000) * 1e9;
+const double kAtomicRate = 4.2e12;        // row updates per second of the per-unit counting kernels
+
+struct Plan {
+  std::vector<int> slots;                 // selected packed columns, ascending
+  std::vector<int> first;                 // first indicator of each
+  int L = 0, ldg = 0, bn = 256;
+  std::vector<int2> tiles;
+  int total_stages = 0, splits = 1, per_split = 0;
+};
+
+void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const BnlUnit *h_units, const std::vector<int> &picked,
+               const std::vector<int> &lev_by_slot, Plan *p) {
+  std::vector<char> used(ds.nd, 0);
+  for (int i : picked)
+    for (int k = 0; k < h_units[i].ncols; k++) used[h_units[i].col[k]] = 1;
+  for (int s = 0; s < ds.nd; s++)
+    if (used[s]) {
+      p->slots.push_back(s);
+      p->first.push_back(p->L);
+      p->L += lev_by_slot[s];
+    }
+  p->ldg = (p->L + 255) & ~255;
+  p->bn = p->L <= 128 ? 128 : 256;
+  const int nbm = (p->L + PAIR_BM - 1) / PAIR_BM, nbn = (p->L + p->bn - 1) / p->bn;
+  for (int bm = 0; bm < nbm; bm++)
+    for (int bn = 0; bn < nbn; bn++)
+      if (bn * p->bn + p->bn > bm * PAIR_BM) p->tiles.push_back(make_int2(bm, bn));   // reaches the upper triangle
+  p->total_stages = (int)((ds.nobs + PAIR_KROWS - 1) / PAIR_KROWS);
+  // row splits: whole waves of CTAs (one per SM), each long enough to pay for its
+  // prologue and for draining the accumulator (~20 stages' worth)
+  const long long nt = (long long)p->tiles.size();
+  double best = 1e300;
+  for (int s = 1; s <= 4096 && s <= std::max(1, p->total_stages / 32); s++) {
+    const long long waves = (nt * s + dev.sm_count - 1) / dev.sm_count;
+    const double cost = (double)waves * ((double)((p->total_stages + s - 1) / s) + 20.0);
+    if (cost < best - 1e-9) { best = cost; p->splits = s; }
+  }
+  p->per_split = (p->total_stages + p->splits - 1) / p->splits;
+  p->splits = (p->total_stages + p->per_split - 1) / p->per_split;
+}
+
+}  // namespace
+
+bool bnl_pairs_eligible(const BnlUnit &u, const std::vector<int> &lev_by_slot) {
+  if (u.ncols < 1 || u.ncols > 2 || u.pad) return false;          // pad: a uint16 column
+  for (int k = 0; k < u.ncols; k++) {
+    const int l = lev_by_slot[u.col[k]];
+    if (l < 2 || l > PAIR_MAX_LEVELS) return false;
+  }
+  return u.ncols == 1 || u.col[0] != u.col[1];
+}
+
+void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const BnlUnit *h_units, const std::vector<int> &picked,
+                    const std::vector<int> &lev_by_slot, double *tensor_s, double *atomic_s) {
+  Plan p;
+  make_plan(dev, ds, h_units, picked, lev_by_slot, &p);
+  const double macs = (double)p.tiles.size() * PAIR_BM * p.bn * (double)ds.nobs;
+  const double hbm = (double)p.slots.size() * (double)ds.nobs / 5e12;
+  *tensor_s = std::max(macs / kPairMacRate, hbm) + 40e-6;
+  *atomic_s = (double)picked.size() * (double)ds.nobs / kAtomicRate + 10e-6;
+}
+
+int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlDeviceData &dd,
+                  const BnlUnit *h_units, const std::vector<int> &picked, const std::vector<int> &lev_by_slot,
+                  BnlTiming *tm) {
+  Plan p;
+  make_plan(dev, ds, h_units, picked, lev_by_slot, &p);
+  const int nc = (int)p.slots.size(), nt = (int)p.tiles.size(), np = (int)picked.size();
+  // one int block: cols (int4 per column) | ind2col [ldg] | slot_first [nd] | tiles (int2) | ids [np]
+  const size_t n_cols = (size_t)nc * 4, n_ind = (size_t)p.ldg, n_sf = ((size_t)ds.nd + 1) & ~(size_t)1, n_tiles = (size_t)nt * 2;
+  const size_t total = n_cols + n_ind + n_sf + n_tiles + (size_t)np + 16;
+  int rc;
+  if ((rc = bnl_reserve_pinned(ctx, &dev.h_pairmeta, &dev.h_pairmeta_cap, total))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_pairmeta, &dev.pairmeta_cap, total))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_pairG, &dev.pairG_cap, (size_t)p.ldg * p.ldg))) return rc;
+  int *h = dev.h_pairmeta;
+  int *h_cols = h, *h_ind = h_cols + n_cols, *h_sf = h_ind + n_ind, *h_tiles = h_sf + n_sf, *h_ids = h_tiles + n_tiles;
+  for (int s = 0; s < ds.nd; s++) h_sf[s] = -1;
+  for (int c = 0; c < nc; c++) {
+    const int s = p.slots[c], l = lev_by_slot[s];
+    h_cols[4 * c] = s; h_cols[4 * c + 1] = p.first[c]; h_cols[4 * c + 2] = l; h_cols[4 * c + 3] = 0;
+    for (int v = 0; v < l; v++) h_ind[p.first[c] + v] = c;
+    h_sf[s] = p.first[c];
+  }
+  for (int r = p.L; r < p.ldg; r++) h_ind[r] = nc - 1;
+  memcpy(h_tiles, p.tiles.data(), n_tiles * sizeof(int));
+  for (int i = 0; i < np; i++) h_ids[i] = picked[i];
+  int *d = dev.d_pairmeta;
+  int *d_cols = d, *d_ind = d_cols + n_cols, *d_sf = d_ind + n_ind, *d_tiles = d_sf + n_sf, *d_ids = d_tiles + n_tiles;
+  BNL_CUDA(ctx, cudaMemcpyAsync(d, h, total * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
+  const int atomic_out = p.splits > 1;
+  if (atomic_out)
+    BNL_CUDA(ctx, cudaMemsetAsync(dev.d_pairG, 0, (size_t)p.ldg * p.ldg * sizeof(int), dev.stream));
+  const size_t smem128 = (size_t)PAIR_STAGES * (PAIR_BM + 128) * 128 + 1024;
+  const size_t smem256 = (size_t)PAIR_STAGES * (PAIR_BM + 256) * 128 + 1024;
+  if (!dev.pair_attr_done) {
+    BNL_CUDA(ctx, cudaFuncSetAttribute(pair_onehot_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem128));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(pair_onehot_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem256));
+    dev.pair_attr_done = true;
+  }
+  const unsigned grid = (unsigned)nt * (unsigned)p.splits;
+  if (p.bn == 128)
+    pair_onehot_kernel<128><<<grid, PAIR_THREADS, smem128, dev.stream>>>(
+        dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), d_ind, p.L, reinterpret_cast<const int2 *>(d_tiles),
+        nt, p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out);
+  else
+    pair_onehot_kernel<256><<<grid, PAIR_THREADS, smem256, dev.stream>>>(
+        dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), d_ind, p.L, reinterpret_cast<const int2 *>(d_tiles),
+        nt, p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out);
+  BNL_CUDA(ctx, cudaGetLastError());
+  pair_extract_kernel<<<(np + 255) / 256, 256, 0, dev.stream>>>(dev.d_units, d_ids, np, d_sf, dev.d_pairG, p.ldg,
+                                                              dev.d_tables);
+  BNL_CUDA(ctx, cudaGetLastError());
+  tm->launches += 2;
+  return BNL_OK;
+}

@@ -1,3 +1,299 @@
-// bnl_pairs.cuh -- all-pairs two-way tables as a tensor-core contraction (see bnl_pairs.cu).
+// bnl_pairs.cuh -- all two-way tables of a column set in one tensor-core pass.
+//
+// When a batch asks for the table of (nearly) every PAIR of a set of factor columns
+// -- the first score_cache_fill of hc() (every i -> j of the empty graph,
+// src/learning/score/hc.cache.lookup.c:52-72), level 0 of pc.stable (every x, y
+// marginally, R/pcalgo.R:8-28) or mi_matrix_discrete (src/learning/local/
+// mi.matrix.c:40-62) -- counting unit by unit repeats the row pass once per pair
+// and sits on the shared-memory atomic rate. The same numbers are ONE contraction:
+// with H the N x L 0/1 indicator matrix of the selected columns (one column of H
+// per (factor, level)), G = H' H holds n[x_i = a, x_j = b] for every pair at once,
+// and the marginal counts on its diagonal. Rows with an NA in a column have an
+// all-zero indicator block there, so they drop out of exactly the pairs that
+// involve that column, as fill_2d_table skips them
+// (src/core/contingency.tables.c:93-130).
+//
+// G is formed on the 5th-generation tensor cores (tcgen05.mma kind::i8, u8 x u8 ->
+// s32 accumulators in TMEM: exact, a cell is a row count < 2^31). H never exists
+// in HBM: producer warps read the packed uint8 code columns (16 rows per 128-bit
+// load), expand them to 0/1 operand bytes with byte-permutes and write them
+// straight into the 128-byte-swizzled K-major shared-memory layout the MMA reads
+// through its matrix descriptors.
 #pragma once
 #include "bnl_internal.h"
+
+#define PAIR_BM 128                 // indicator rows of the A operand = TMEM lanes
+#define PAIR_KROWS 128              // data rows per pipeline stage = 128 bytes of K per indicator row
+#define PAIR_STAGES 4
+#define PAIR_PRODUCERS 352          // 11 warps expand codes; the 12th issues the MMAs (registers are
+                                    // allotted per 4 warps: 9 warps would cost as much as 12)
+#define PAIR_THREADS (PAIR_PRODUCERS + 32)
+#define PAIR_MAX_LEVELS 8           // one byte-permute selects among 8 table bytes
+#define PAIR_MAX_ITEMS 5            // columns per producer thread and stage: <= 194 columns over 44 column lanes
+
+namespace bnlpair {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *b, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *b) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+// Waits are bounded: a protocol slip must end in a trap, not in a hung device.
+__device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity) {
+  const long long t0 = clock64();
+  while (true) {
+    uint32_t done;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(done) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    if (done) return;
+    if (clock64() - t0 > 4000000000ll) __trap();
+  }
+}
+
+// shared-memory matrix descriptor, K-major operand in the 128-byte swizzle: rows of
+// 128 bytes, 8-row groups 1024 bytes apart (stride byte offset), descriptor
+// version 1 (sm_100), layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  uint64_t d = (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                        uint32_t accumulate) {
+  asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0;\n"
+               "  tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p; }"
+               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on the barrier once every MMA issued so far has finished reading shared memory / writing TMEM
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+               ::"r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// One-hot bytes of 4 rows for level v from their packed codes: `sel` holds the
+// four codes as nibbles, the 8-byte table {lo, hi} has a 1 at byte v. A nibble of
+// 0xF (NA, padding) selects "sign of byte 7", which is 0.
+__device__ __forceinline__ uint32_t onehot4(uint32_t sel, int v) {
+  const uint32_t lo = v < 4 ? 1u << (8 * v) : 0u, hi = v >= 4 ? 1u << (8 * (v - 4)) : 0u;
+  uint32_t r;      // prmt in PTX's generic mode: __byte_perm() drops bit 3 of a selector nibble
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(sel));
+  return r;
+}
+__device__ __forceinline__ uint32_t selector4(uint32_t w) {
+  const uint32_t m = w & 0x0F0F0F0Fu;              // valid codes are < 8; NA 0xFF -> 0xF
+  const uint32_t t = m | (m >> 4);                 // byte 0: codes 0, 1; byte 2: codes 2, 3
+  return __byte_perm(t, 0u, 0x4420);
+}
+
+}  // namespace bnlpair
+
+// Tile (bm, bn) of G: indicator rows [bm * 128, +128) against indicator rows
+// [bn * BN, +BN), over the data rows of one split. grid = tiles x splits, tile
+// fastest, so the CTAs resident at one time work on the same slab of rows and a
+// column's bytes come from HBM once. One CTA per SM.
+//   warps 0-10 expand codes into the stage buffers; warps 0-7 then drain the accumulator
+//   warp  11   waits for full stages and issues 4 MMAs (K = 32 each) per stage
+// cols[] lists the selected columns in indicator order: {packed slot, first indicator, levels}.
+template <int BN>
+__global__ void __launch_bounds__(PAIR_THREADS, 1)
+pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__restrict__ cols,
+                   const int *__restrict__ ind2col, int L, const int2 *__restrict__ tiles, int ntiles,
+                   int stages_per_split, int total_stages, int *__restrict__ G, int ldg, int atomic_out) {
+  using namespace bnlpair;
+  constexpr int A_BYTES = PAIR_BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // the dynamic window is only guaranteed 16-byte alignment: round up to the swizzle atom
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t full_bar[PAIR_STAGES], empty_bar[PAIR_STAGES], accum_bar;
+  __shared__ uint32_t s_tmem;
+  __shared__ int s_slot[256], s_row[256], s_nlev[256], s_off[256];
+  __shared__ int s_nitems;
+
+  const int tile = blockIdx.x % ntiles, split = blockIdx.x / ntiles;
+  const int bm = tiles[tile].x, bn = tiles[tile].y;
+  const int a0 = bm * PAIR_BM, b0 = bn * BN;
+  // a diagonal tile: the A rows are a slice of the B rows, expanded once
+  const bool a_in_b = a0 >= b0 && a0 + PAIR_BM <= b0 + BN;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < PAIR_STAGES; s++) { mbar_init(&full_bar[s], PAIR_PRODUCERS / 32); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&accum_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // work list: the columns that reach into the B rows, then (unless shared) the A rows
+    int n = 0;
+    for (int pass = 0; pass < 2; pass++) {
+      if (pass == 1 && a_in_b) break;
+      const int r0 = pass == 0 ? b0 : a0, nr = pass == 0 ? BN : PAIR_BM;
+      if (r0 >= L) continue;
+      const int last = min(r0 + nr, L) - 1;
+      for (int c = ind2col[r0]; c <= ind2col[last]; c++) {
+        const int4 ci = cols[c];
+        s_slot[n] = ci.x; s_row[n] = ci.y - r0; s_nlev[n] = ci.z;
+        s_off[n] = (pass == 0 ? A_BYTES : 0) | (nr << 20);
+        n++;
+      }
+    }
+    s_nitems = n;
+  }
+  if (warp == PAIR_PRODUCERS / 32) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  // rows that no column writes (beyond L, or levels outside the tile) must read as 0
+  for (int i = threadIdx.x; i < PAIR_STAGES * STAGE_BYTES / 16; i += PAIR_THREADS)
+    reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0, 0, 0, 0);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = s_tmem;
+
+  const int st0 = split * stages_per_split;
+  const int st1 = min(st0 + stages_per_split, total_stages);
+  const int nst = st1 - st0;
+
+  if (warp < PAIR_PRODUCERS / 32) {
+    // ---------------- producers ----------------
+    const int g = threadIdx.x & 7, cq = threadIdx.x >> 3;       // 16-row chunk, column lane
+    const int nitems = s_nitems;
+    const uint4 *cp[PAIR_MAX_ITEMS];
+    int row[PAIR_MAX_ITEMS], nlev[PAIR_MAX_ITEMS], off[PAIR_MAX_ITEMS], nrow[PAIR_MAX_ITEMS];
+#pragma unroll
+    for (int i = 0; i < PAIR_MAX_ITEMS; i++) {
+      const int q = cq + (PAIR_PRODUCERS / 8) * i;
+      const bool ok = q < nitems;
+      cp[i] = reinterpret_cast<const uint4 *>(u8 + (size_t)(ok ? s_slot[q] : 0) * stride) + g;
+      row[i] = ok ? s_row[q] : 0;
+      nlev[i] = ok ? s_nlev[q] : 0;
+      off[i] = ok ? (s_off[q] & 0xFFFFF) : 0;
+      nrow[i] = ok ? (s_off[q] >> 20) : 0;
+    }
+    uint4 cur[PAIR_MAX_ITEMS], nxt[PAIR_MAX_ITEMS];
+    auto load = [&](uint4(&r)[PAIR_MAX_ITEMS], int st) {
+#pragma unroll
+      for (int i = 0; i < PAIR_MAX_ITEMS; i++)
+        if (nlev[i] > 0) r[i] = __ldg(cp[i] + (size_t)st * (PAIR_KROWS / 16));
+    };
+    if (nst > 0) load(cur, st0);
+    for (int it = 0; it < nst; it++) {
+      const int s = it % PAIR_STAGES;
+      if (it + 1 < nst) load(nxt, st0 + it + 1);
+      if (it >= PAIR_STAGES) mbar_wait(&empty_bar[s], ((it / PAIR_STAGES) - 1) & 1);
+      uint8_t *stage = smem + (size_t)s * STAGE_BYTES;
+#pragma unroll
+      for (int i = 0; i < PAIR_MAX_ITEMS; i++) {
+        if (nlev[i] == 0) continue;
+        const uint32_t s0 = selector4(cur[i].x), s1 = selector4(cur[i].y), s2 = selector4(cur[i].z),
+                       s3 = selector4(cur[i].w);
+#pragma unroll
+        for (int v = 0; v < PAIR_MAX_LEVELS; v++) {
+          const int m = row[i] + v;
+          if (v < nlev[i] && m >= 0 && m < nrow[i]) {
+            const uint4 o = make_uint4(onehot4(s0, v), onehot4(s1, v), onehot4(s2, v), onehot4(s3, v));
+            *reinterpret_cast<uint4 *>(stage + off[i] + m * 128 + ((g ^ (m & 7)) << 4)) = o;
+          }
+        }
+      }
+      // generic-proxy writes -> visible to the tensor core's async-proxy reads
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full_bar[s]);
+#pragma unroll
+      for (int i = 0; i < PAIR_MAX_ITEMS; i++) cur[i] = nxt[i];
+    }
+  } else if (lane == 0) {
+    // ---------------- MMA issuer ----------------
+    // instruction descriptor: D = s32 (c_format 2), A and B unsigned 8-bit, both K-major, N >> 3, M >> 4
+    const uint32_t idesc = (2u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(PAIR_BM >> 4) << 24);
+    const uint32_t a_shift = a_in_b ? (uint32_t)(A_BYTES + (a0 - b0) * 128) : 0u;
+    for (int it = 0; it < nst; it++) {
+      const int s = it % PAIR_STAGES;
+      mbar_wait(&full_bar[s], (it / PAIR_STAGES) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t sb = smem_u32(smem + (size_t)s * STAGE_BYTES);
+      const uint64_t ad = make_desc_sw128(sb + a_shift), bd = make_desc_sw128(sb + A_BYTES);
+#pragma unroll
+      for (int k = 0; k < PAIR_KROWS / 32; k++)      // +32 bytes of K per step: +2 in the (address >> 4) field
+        umma_i8(tmem, ad + 2 * k, bd + 2 * k, idesc, (it | k) != 0);
+      umma_commit(&empty_bar[s]);
+    }
+    umma_commit(&accum_bar);
+  }
+
+  // ---------------- accumulator -> G ----------------
+  if (warp < 8 && nst > 0) {
+    mbar_wait(&accum_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const int lg = warp & 3;                          // a warp reads the 32 TMEM lanes of its quarter
+    const int r = a0 + lg * 32 + lane;                // indicator row of G held by this thread
+    for (int c0 = (warp >> 2) * 32; c0 < BN; c0 += 64) {
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
+      if (r < L) {
+        int *dst = G + (size_t)r * ldg + b0 + c0;
+        if (atomic_out) {
+#pragma unroll
+          for (int j = 0; j < 32; j++)
+            if (v[j] != 0u) atomicAdd(dst + j, (int)v[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<int4 *>(dst + j) = make_int4((int)v[j], (int)v[j + 1], (int)v[j + 2], (int)v[j + 3]);
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == PAIR_PRODUCERS / 32) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(BN));
+  }
+}
+
+// Unit tables out of G, in the layout bnl_counts returns (n[z][x][y], first
+// variable fastest). A two-column unit with codes (a, b) = (col[0], col[1]) reads
+// G[first(col0) + a][first(col1) + b] (upper triangle: smaller indicator first); a
+// one-column unit reads the diagonal.
+__global__ void __launch_bounds__(256)
+pair_extract_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ ids, int n,
+                    const int *__restrict__ slot_first, const int *__restrict__ G, int ldg,
+                    int *__restrict__ tables) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const BnlUnit &u = units[ids[t]];
+  int *tab = tables + u.table_off;
+  const int f0 = slot_first[u.col[0]];
+  if (u.ncols == 1) {
+    for (int a = 0; a < u.cells; a++) tab[a] = G[(size_t)(f0 + a) * ldg + f0 + a];
+    return;
+  }
+  const int f1 = slot_first[u.col[1]], l0 = u.mul[1], l1 = u.cells / l0;
+  for (int b = 0; b < l1; b++)
+    for (int a = 0; a < l0; a++) {
+      const int ia = f0 + a, ib = f1 + b;
+      tab[a + l0 * b] = ia <= ib ? G[(size_t)ia * ldg + ib] : G[(size_t)ib * ldg + ia];
+    }
+}
+

@@ -976,3 +976,58 @@ def test_no_device_memory_growth(engine):
     torch.cuda.synchronize()
     free1, _ = torch.cuda.mem_get_info()
     assert free0 - free1 < 32 << 20, (free0, free1)
+
+
+@pytest.mark.parametrize("ncols,nobs,maxlev", [(20, 100003, 4), (60, 70001, 8), (130, 33000, 6)])
+def test_all_pairs_tensor_core_tables(engine, monkeypatch, ncols, nobs, maxlev):
+    """The all-pairs contraction (tcgen05 indicator cross-product, csrc/bnl_pairs.cuh)
+    against numpy: every two-way table of the column set in both orientations, the
+    one-way tables from the diagonal, NA rows, a row count that is no multiple of
+    the 128-row stage, one / two / many output tiles, next to three-column units
+    that stay on the atomic kernels in the same batch. Then statistics and scores
+    bit-identical to the per-unit path (same tables, same epilogue)."""
+    rng = np.random.default_rng(ncols)
+    na = np.iinfo(np.int32).min
+    lev = [int(v) for v in rng.integers(2, maxlev + 1, ncols)]
+    lev[3] = 1                                   # a one-level factor is not eligible: stays on the atomic path
+    cols = []
+    for i, l in enumerate(lev):
+        c = rng.integers(1, l + 1, nobs).astype(np.int32)
+        if i % 3 == 0:
+            c[rng.random(nobs) < 0.02] = na
+        cols.append(c)
+    d = engine.register(cols, lev)
+    xs, ys, zs = [], [], []
+    for i in range(ncols):
+        xs.append(i); ys.append(-1); zs.append([])                      # one-way table
+        for j in range(ncols):
+            if i != j and (i < j or (i + j) % 5 == 0):
+                xs.append(i); ys.append(j); zs.append([])
+    for k in range(12):                                                 # conditional tables in the same batch
+        i, j, z = (int(v) for v in rng.choice(ncols, 3, replace=False))
+        xs.append(i); ys.append(j); zs.append([z])
+    monkeypatch.setenv("BNL_PAIRS", "2")
+    tabs = d.counts(xs, ys, zs)
+    code = [np.where(c == na, -1, c - 1).astype(np.int64) for c in cols]
+    for x, y, z, t in zip(xs, ys, zs, tabs):
+        keep = code[x] >= 0
+        key = code[x].copy()
+        shape = [lev[x]]
+        if y >= 0:
+            keep &= code[y] >= 0
+            key = key * lev[y] + code[y]
+            shape.append(lev[y])
+        if z:
+            keep &= code[z[0]] >= 0
+            key = code[z[0]] * int(np.prod(shape)) + key
+            shape.insert(0, lev[z[0]])
+        want = np.bincount(key[keep], minlength=int(np.prod(shape)))
+        assert np.array_equal(np.asarray(t).ravel(), want), (x, y, z)
+    pairs = [(x, y) for x, y, z in zip(xs, ys, zs) if y >= 0 and not z]
+    px, py = [p[0] for p in pairs], [p[1] for p in pairs]
+    got = d.ci_discrete("mi", px, py, [[]] * len(pairs)) + d.score_discrete("bde", px, [[v] for v in py], 1.0)
+    monkeypatch.setenv("BNL_PAIRS", "0")
+    want = d.ci_discrete("mi", px, py, [[]] * len(pairs)) + d.score_discrete("bde", px, [[v] for v in py], 1.0)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    d.release()
