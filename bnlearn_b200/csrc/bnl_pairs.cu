@@ -109,22 +109,42 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   const int atomic_out = p.splits > 1;
   if (atomic_out)
     BNL_CUDA(ctx, cudaMemsetAsync(dev.d_pairG, 0, (size_t)p.ldg * p.ldg * sizeof(int), dev.stream));
+  // variants: <indicator columns per tile, columns per producer thread, stages of loads in flight>.
+  // One output tile of <= 44 columns (a pc.stable level 0 on a few dozen factors) keeps 8 stages
+  // in flight per thread; the widest tile needs 5 columns per thread and affords 3.
   const size_t smem128 = (size_t)PAIR_STAGES * (PAIR_BM + 128) * 128 + 1024;
   const size_t smem256 = (size_t)PAIR_STAGES * (PAIR_BM + 256) * 128 + 1024;
   if (!dev.pair_attr_done) {
-    BNL_CUDA(ctx, cudaFuncSetAttribute(pair_onehot_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem128));
-    BNL_CUDA(ctx, cudaFuncSetAttribute(pair_onehot_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem256));
+#define BNL_PAIR_ATTR(BN, ITEMS, DEPTH, SMEM)                                                                      \
+    BNL_CUDA(ctx, cudaFuncSetAttribute(pair_onehot_kernel<BN, ITEMS, DEPTH, false>,                                 \
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMEM)));                  \
+    BNL_CUDA(ctx, cudaFuncSetAttribute(pair_onehot_kernel<BN, ITEMS, DEPTH, true>,                                  \
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMEM)))
+    BNL_PAIR_ATTR(128, 1, 8, smem128);
+    BNL_PAIR_ATTR(128, 3, 4, smem128);
+    BNL_PAIR_ATTR(256, 5, 3, smem256);
+#undef BNL_PAIR_ATTR
     dev.pair_attr_done = true;
   }
+  // NA bytes between valid codes need one more instruction per word (selector4)
+  bool any_na = false;
+  for (int s : p.slots) any_na = any_na || ds.slot_has_na.empty() || ds.slot_has_na[s];
   const unsigned grid = (unsigned)nt * (unsigned)p.splits;
-  if (p.bn == 128)
-    pair_onehot_kernel<128><<<grid, PAIR_THREADS, smem128, dev.stream>>>(
-        dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), d_ind, p.L, reinterpret_cast<const int2 *>(d_tiles),
-        nt, p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out);
-  else
-    pair_onehot_kernel<256><<<grid, PAIR_THREADS, smem256, dev.stream>>>(
-        dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), d_ind, p.L, reinterpret_cast<const int2 *>(d_tiles),
-        nt, p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out);
+#define BNL_PAIR_LAUNCH(BN, ITEMS, DEPTH, SMEM)                                                                   \
+  do {                                                                                                            \
+    if (any_na)                                                                                                   \
+      pair_onehot_kernel<BN, ITEMS, DEPTH, true><<<grid, PAIR_THREADS, SMEM, dev.stream>>>(                        \
+          dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), d_ind, p.L,                                \
+          reinterpret_cast<const int2 *>(d_tiles), nt, p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out); \
+    else                                                                                                          \
+      pair_onehot_kernel<BN, ITEMS, DEPTH, false><<<grid, PAIR_THREADS, SMEM, dev.stream>>>(                       \
+          dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), d_ind, p.L,                                \
+          reinterpret_cast<const int2 *>(d_tiles), nt, p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out); \
+  } while (0)
+  if (p.bn == 128 && nc <= PAIR_PRODUCERS / 8) BNL_PAIR_LAUNCH(128, 1, 8, smem128);
+  else if (p.bn == 128) BNL_PAIR_LAUNCH(128, 3, 4, smem128);
+  else BNL_PAIR_LAUNCH(256, 5, 3, smem256);
+#undef BNL_PAIR_LAUNCH
   BNL_CUDA(ctx, cudaGetLastError());
   pair_extract_kernel<<<(np + 255) / 256, 256, 0, dev.stream>>>(dev.d_units, d_ids, np, d_sf, dev.d_pairG, p.ldg,
                                                               dev.d_tables);

@@ -29,7 +29,6 @@
                                     // allotted per 4 warps: 9 warps would cost as much as 12)
 #define PAIR_THREADS (PAIR_PRODUCERS + 32)
 #define PAIR_MAX_LEVELS 8           // one byte-permute selects among 8 table bytes
-#define PAIR_MAX_ITEMS 5            // columns per producer thread and stage: <= 194 columns over 44 column lanes
 
 namespace bnlpair {
 
@@ -41,16 +40,18 @@ __device__ __forceinline__ void mbar_init(uint64_t *b, int count) {
 __device__ __forceinline__ void mbar_arrive(uint64_t *b) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
-// Waits are bounded: a protocol slip must end in a trap, not in a hung device.
+// try_wait parks the thread in hardware until the phase completes or the hint (ns)
+// runs out, so a waiting warp takes no issue slots from the producers (a polling
+// loop in the MMA warp cost a quarter of all instructions issued). Waits are
+// bounded: a protocol slip must end in a trap, not in a hung device.
 __device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity) {
-  const long long t0 = clock64();
-  while (true) {
+  for (int tries = 0; tries < 4096; tries++) {
     uint32_t done;
-    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(done) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(done) : "r"(smem_u32(b)), "r"(parity), "r"(1000000u) : "memory");
     if (done) return;
-    if (clock64() - t0 > 4000000000ll) __trap();
   }
+  __trap();
 }
 
 // shared-memory matrix descriptor, K-major operand in the 128-byte swizzle: rows of
@@ -90,19 +91,26 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// One-hot bytes of 4 rows for level v from their packed codes: `sel` holds the
-// four codes as nibbles, the 8-byte table {lo, hi} has a 1 at byte v. A nibble of
+// One-hot bytes of 4 rows for one level from their packed codes: `sel` holds the
+// four codes as nibbles, the 8-byte table {lo, hi} has a 1 at the level's byte. A nibble of
 // 0xF (NA, padding) selects "sign of byte 7", which is 0.
-__device__ __forceinline__ uint32_t onehot4(uint32_t sel, int v) {
-  const uint32_t lo = v < 4 ? 1u << (8 * v) : 0u, hi = v >= 4 ? 1u << (8 * (v - 4)) : 0u;
+__device__ __forceinline__ uint32_t onehot4(uint32_t sel, uint32_t lo, uint32_t hi) {
   uint32_t r;      // prmt in PTX's generic mode: __byte_perm() drops bit 3 of a selector nibble
   asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(sel));
   return r;
 }
+// NA = true: some selected column holds NA bytes (0xFF) between valid codes; they are
+// cut to 0xF first so that they cannot spill into the neighbouring code's nibble.
+// Without NA the only 0xFF bytes are the padding past the last row, which sits at the
+// HIGH end of a word and only overwrites nibbles that are 0xF anyway.
+template <bool NA>
 __device__ __forceinline__ uint32_t selector4(uint32_t w) {
-  const uint32_t m = w & 0x0F0F0F0Fu;              // valid codes are < 8; NA 0xFF -> 0xF
+  const uint32_t m = NA ? (w & 0x0F0F0F0Fu) : w;   // valid codes are < 8; NA 0xFF -> 0xF
   const uint32_t t = m | (m >> 4);                 // byte 0: codes 0, 1; byte 2: codes 2, 3
   return __byte_perm(t, 0u, 0x4420);
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
 }  // namespace bnlpair
@@ -114,7 +122,7 @@ __device__ __forceinline__ uint32_t selector4(uint32_t w) {
 //   warps 0-10 expand codes into the stage buffers; warps 0-7 then drain the accumulator
 //   warp  11   waits for full stages and issues 4 MMAs (K = 32 each) per stage
 // cols[] lists the selected columns in indicator order: {packed slot, first indicator, levels}.
-template <int BN>
+template <int BN, int ITEMS, int DEPTH, bool NA>
 __global__ void __launch_bounds__(PAIR_THREADS, 1)
 pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__restrict__ cols,
                    const int *__restrict__ ind2col, int L, const int2 *__restrict__ tiles, int ntiles,
@@ -175,52 +183,88 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
 
   if (warp < PAIR_PRODUCERS / 32) {
     // ---------------- producers ----------------
-    const int g = threadIdx.x & 7, cq = threadIdx.x >> 3;       // 16-row chunk, column lane
+    // Thread = (16-row chunk g, column lane cq): the 8 threads of a column read 128
+    // contiguous bytes and write one whole 128-byte operand row per level (the swizzle
+    // spreads their 16-byte pieces over all banks). The loads run DEPTH stages ahead in
+    // a register ring -- one CTA per SM, so nothing else hides the memory latency (one
+    // stage ahead left the kernel latency-bound at 1/5 of its speed) -- and the lines
+    // 16 stages ahead are pulled from DRAM into L2.
+    const int g = threadIdx.x & 7, cq = threadIdx.x >> 3;
     const int nitems = s_nitems;
-    const uint4 *cp[PAIR_MAX_ITEMS];
-    int row[PAIR_MAX_ITEMS], nlev[PAIR_MAX_ITEMS], off[PAIR_MAX_ITEMS], nrow[PAIR_MAX_ITEMS];
+    // per column of this thread, fixed for the whole kernel: where its rows go inside a
+    // stage (sa), which levels fall inside the tile (lm, one bit per level), and the
+    // swizzled 16-byte piece of this thread's chunk in each of those rows (sw: one byte
+    // per level, levels 0-3 and 4-7), so that a level costs one byte-extract, one add,
+    // four byte-permutes and the store.
+    uint32_t coff[ITEMS], sa[ITEMS], lm[ITEMS], sw_lo[ITEMS], sw_hi[ITEMS];
+    const uint4 *base4 = reinterpret_cast<const uint4 *>(u8);
+    const uint32_t stride16 = (uint32_t)(stride >> 4);
 #pragma unroll
-    for (int i = 0; i < PAIR_MAX_ITEMS; i++) {
+    for (int i = 0; i < ITEMS; i++) {
       const int q = cq + (PAIR_PRODUCERS / 8) * i;
       const bool ok = q < nitems;
-      cp[i] = reinterpret_cast<const uint4 *>(u8 + (size_t)(ok ? s_slot[q] : 0) * stride) + g;
-      row[i] = ok ? s_row[q] : 0;
-      nlev[i] = ok ? s_nlev[q] : 0;
-      off[i] = ok ? (s_off[q] & 0xFFFFF) : 0;
-      nrow[i] = ok ? (s_off[q] >> 20) : 0;
+      const int row = ok ? s_row[q] : 0, nl = ok ? s_nlev[q] : 0, nr = ok ? (s_off[q] >> 20) : 0;
+      coff[i] = (uint32_t)(ok ? s_slot[q] : 0) * stride16 + (uint32_t)g;
+      sa[i] = (uint32_t)((ok ? (s_off[q] & 0xFFFFF) : 0) + row * 128);
+      const int v0 = max(0, -row), v1 = min(nl, nr - row);
+      lm[i] = v1 > v0 ? ((1u << v1) - (1u << v0)) : 0u;
+      uint32_t lo = 0, hi = 0;
+#pragma unroll
+      for (int v = 0; v < 4; v++) {
+        lo |= (uint32_t)((g ^ ((row + v) & 7)) << 4) << (8 * v);
+        hi |= (uint32_t)((g ^ ((row + v + 4) & 7)) << 4) << (8 * v);
+      }
+      sw_lo[i] = lo; sw_hi[i] = hi;
     }
-    uint4 cur[PAIR_MAX_ITEMS], nxt[PAIR_MAX_ITEMS];
-    auto load = [&](uint4(&r)[PAIR_MAX_ITEMS], int st) {
+    uint4 ring[DEPTH][ITEMS];
+    auto load = [&](uint4(&r)[ITEMS], int st) {
+      const uint32_t so = (uint32_t)st * (PAIR_KROWS / 16);
 #pragma unroll
-      for (int i = 0; i < PAIR_MAX_ITEMS; i++)
-        if (nlev[i] > 0) r[i] = __ldg(cp[i] + (size_t)st * (PAIR_KROWS / 16));
+      for (int i = 0; i < ITEMS; i++)
+        if (lm[i]) r[i] = __ldg(base4 + (coff[i] + so));
+      if (g == 0 && st + 16 < st1) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++)
+          if (lm[i]) asm volatile("prefetch.global.L2 [%0];" ::"l"(base4 + (coff[i] + so + 16 * (PAIR_KROWS / 16))));
+      }
     };
-    if (nst > 0) load(cur, st0);
-    for (int it = 0; it < nst; it++) {
-      const int s = it % PAIR_STAGES;
-      if (it + 1 < nst) load(nxt, st0 + it + 1);
-      if (it >= PAIR_STAGES) mbar_wait(&empty_bar[s], ((it / PAIR_STAGES) - 1) & 1);
-      uint8_t *stage = smem + (size_t)s * STAGE_BYTES;
 #pragma unroll
-      for (int i = 0; i < PAIR_MAX_ITEMS; i++) {
-        if (nlev[i] == 0) continue;
-        const uint32_t s0 = selector4(cur[i].x), s1 = selector4(cur[i].y), s2 = selector4(cur[i].z),
-                       s3 = selector4(cur[i].w);
+    for (int d = 0; d < DEPTH; d++)
+      if (d < nst) load(ring[d], st0 + d);
+    const uint32_t smem0 = smem_u32(smem);
+    for (int it0 = 0; it0 < nst; it0 += DEPTH) {
 #pragma unroll
-        for (int v = 0; v < PAIR_MAX_LEVELS; v++) {
-          const int m = row[i] + v;
-          if (v < nlev[i] && m >= 0 && m < nrow[i]) {
-            const uint4 o = make_uint4(onehot4(s0, v), onehot4(s1, v), onehot4(s2, v), onehot4(s3, v));
-            *reinterpret_cast<uint4 *>(stage + off[i] + m * 128 + ((g ^ (m & 7)) << 4)) = o;
+      for (int d = 0; d < DEPTH; d++) {
+        const int it = it0 + d;
+        if (it >= nst) break;
+        const int s = it % PAIR_STAGES;
+        if (it >= PAIR_STAGES) mbar_wait(&empty_bar[s], ((it / PAIR_STAGES) - 1) & 1);
+        const uint32_t sb = smem0 + (uint32_t)s * STAGE_BYTES;
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+          if (lm[i] == 0u) continue;
+          const uint32_t s0 = selector4<NA>(ring[d][i].x), s1 = selector4<NA>(ring[d][i].y),
+                         s2 = selector4<NA>(ring[d][i].z), s3 = selector4<NA>(ring[d][i].w);
+          const uint32_t rb = sb + sa[i];
+#pragma unroll
+          for (int v = 0; v < 4; v++)
+            if (lm[i] & (1u << v))
+              sts128(rb + v * 128 + __byte_perm(sw_lo[i], 0u, 0x4440 + v), onehot4(s0, 1u << (8 * v), 0u),
+                     onehot4(s1, 1u << (8 * v), 0u), onehot4(s2, 1u << (8 * v), 0u), onehot4(s3, 1u << (8 * v), 0u));
+          if (lm[i] >> 4) {                        // factors with 5-8 levels
+#pragma unroll
+            for (int v = 0; v < 4; v++)
+              if (lm[i] & (16u << v))
+                sts128(rb + (v + 4) * 128 + __byte_perm(sw_hi[i], 0u, 0x4440 + v), onehot4(s0, 0u, 1u << (8 * v)),
+                       onehot4(s1, 0u, 1u << (8 * v)), onehot4(s2, 0u, 1u << (8 * v)), onehot4(s3, 0u, 1u << (8 * v)));
           }
         }
+        // generic-proxy writes -> visible to the tensor core's async-proxy reads
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full_bar[s]);
+        if (it + DEPTH < nst) load(ring[d], st0 + it + DEPTH);
       }
-      // generic-proxy writes -> visible to the tensor core's async-proxy reads
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&full_bar[s]);
-#pragma unroll
-      for (int i = 0; i < PAIR_MAX_ITEMS; i++) cur[i] = nxt[i];
     }
   } else if (lane == 0) {
     // ---------------- MMA issuer ----------------
@@ -242,26 +286,29 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
   }
 
   // ---------------- accumulator -> G ----------------
+  // A thread holds one indicator row of the accumulator (its TMEM lane), 32 columns at
+  // a time; the 32 x 32 block is turned through shared memory (the stage buffers are
+  // free once the last MMA has committed) so that a warp writes 128 contiguous bytes
+  // of a row of G per instruction.
   if (warp < 8 && nst > 0) {
     mbar_wait(&accum_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const int lg = warp & 3;                          // a warp reads the 32 TMEM lanes of its quarter
-    const int r = a0 + lg * 32 + lane;                // indicator row of G held by this thread
+    int *tile = reinterpret_cast<int *>(smem) + warp * (32 * 33);
     for (int c0 = (warp >> 2) * 32; c0 < BN; c0 += 64) {
       uint32_t v[32];
       tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
-      if (r < L) {
-        int *dst = G + (size_t)r * ldg + b0 + c0;
-        if (atomic_out) {
 #pragma unroll
-          for (int j = 0; j < 32; j++)
-            if (v[j] != 0u) atomicAdd(dst + j, (int)v[j]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<int4 *>(dst + j) = make_int4((int)v[j], (int)v[j + 1], (int)v[j + 2], (int)v[j + 3]);
-        }
+      for (int j = 0; j < 32; j++) tile[lane * 33 + j] = (int)v[j];
+      __syncwarp();
+      int *dst = G + (size_t)(a0 + lg * 32) * ldg + b0 + c0 + lane;
+      const int rows = min(32, L - (a0 + lg * 32));
+      for (int rr = 0; rr < rows; rr++) {
+        const int val = tile[rr * 33 + lane];
+        if (atomic_out) { if (val) atomicAdd(dst + (size_t)rr * ldg, val); }
+        else dst[(size_t)rr * ldg] = val;
       }
+      __syncwarp();
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
