@@ -122,6 +122,15 @@ int epilogue_stride(bnl_ctx *ctx, BnlDevice &dev, const Units &units, int n, int
   return BNL_OK;
 }
 
+// One warp can do a unit's whole epilogue, in the order the four-warp CTA would
+// (epilogue_kernel<EXT, true>): tests in a single stratum, and node scores that take
+// the one-lane-per-stratum route with at most 32 strata or have a single stratum.
+bool epilogue_warp_ok(int kind, int code, int llx, int lly, int llz) {
+  if (kind == 0) return llz == 1 && code != BNL_JT && code != BNL_MI_SH;
+  if (code == BNL_BDS) return false;
+  return llz == 1 || (llx * lly <= 16 && llz <= 32);
+}
+
 struct Request {
   int kind;        // 0 tests, 1 scores, 2 raw tables
   int code;
@@ -173,6 +182,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
   const int smem_cap_cells = (dev.max_smem - 8192) / 4;
   const long long groups = (ds.nobs + 15) / 16;
   std::vector<int> pair_lev;
+  std::vector<char> pair_used;
   int pos = b;
   while (pos < e) {
     long long cells = 0;
@@ -220,9 +230,12 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       for (int i = 0; i < cnt; i++)
         if (bnl_pairs_eligible(dev.h_units[i], lev_by_slot)) pair_units.push_back(i);
       bool take = pair_units.size() >= 32;
+      pair_used.assign(ds.nd, 0);
+      for (int i : pair_units)
+        for (int k = 0; k < dev.h_units[i].ncols; k++) pair_used[dev.h_units[i].col[k]] = 1;
       if (take && kKnobPairs < 2) {
         double tensor_s, atomic_s;
-        bnl_pairs_cost(dev, ds, dev.h_units, pair_units, lev_by_slot, &tensor_s, &atomic_s);
+        bnl_pairs_cost(dev, ds, pair_used, (long long)pair_units.size(), lev_by_slot, &tensor_s, &atomic_s);
         take = tensor_s < 0.8 * atomic_s;
       }
       if (!take) pair_units.clear();
@@ -472,7 +485,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                     cudaMemcpyHostToDevice, dev.stream));
     BNL_CUDA(ctx, cudaMemsetAsync(dev.d_tables, 0, (size_t)cells * sizeof(int), dev.stream));
     BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
-    if (!pair_units.empty() && (rc = bnl_pairs_run(ctx, dev, ds, dd, dev.h_units, pair_units, pair_lev, tm))) return rc;
+    if (!pair_units.empty() &&
+        (rc = bnl_pairs_run(ctx, dev, ds, dd, pair_used, &pair_units, (int)pair_units.size(), pair_lev, tm))) return rc;
     if (groups > 0 && !bruns.empty()) {
       // base indices of every run (complete 16-row groups), then one launch per class
       const long long full = ds.nobs / 16;
@@ -636,6 +650,141 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
   return BNL_OK;
 }
 
+
+// ---------------------------------------------------------------------------
+// Batches made ONLY of one- and two-way tables of small factors, large enough for
+// the tensor-core contraction (bnl_pairs.cu): the first score_cache_fill of hc(),
+// pc.stable's level 0, mi.matrix. No BnlUnit is built on the host; the caller's
+// index arrays go up as they are and build_pair_units_kernel writes the
+// descriptors. *handled = false leaves the request to the general path.
+// kind 0: tests, 1: scores, 2: tables (as Request).
+int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, int n, const int *x, const int *y,
+                  const int *z_off, const int *z_idx, double *o0, double *o1, double *o2, int32_t *tables,
+                  const int64_t *table_off, bool *handled) {
+  *handled = false;
+  const long long knob = knob_pairs();
+  if (!knob || n < 4096 || n > kMaxBatchUnits || ctx->devs.size() != 1 || ds.nobs < 4096 || ds.nd == 0) return BNL_OK;
+  if (kind == 0 && (code == BNL_JT || code == BNL_MI_SH)) return BNL_OK;
+  std::vector<int> lev_by_slot(ds.nd, 0);
+  for (int c = 0; c < ds.ncols; c++)
+    if (!ds.is_numeric[c] && !ds.is_wide[c]) lev_by_slot[ds.slot[c]] = ds.nlevels[c];
+  auto slot_of = [&](int c) {            // packed slot of an eligible column, or -1
+    if (c < 0 || c >= ds.ncols || ds.is_numeric[c] || ds.is_wide[c]) return -1;
+    const int l = ds.nlevels[c];
+    return (l >= 2 && l <= 8) ? ds.slot[c] : -1;
+  };
+  BnlDevice &dev = ctx->devs[0];
+  int rc;
+  // staging: int2 cc[n] | long long off[n] | int lev_by_slot[nd]
+  const size_t stage_ints = (size_t)n * 4;
+  if ((rc = bnl_reserve_pinned(ctx, &dev.h_gidx, &dev.h_gidx_cap, stage_ints + (size_t)ds.nd + 8))) return rc;
+  int2 *h_cc = reinterpret_cast<int2 *>(dev.h_gidx);
+  long long *h_off = reinterpret_cast<long long *>(dev.h_gidx + (size_t)n * 2);
+  std::vector<char> used(ds.nd, 0);
+  long long cells = 0;
+  bool warp_ok = true;
+  for (int u = 0; u < n; u++) {
+    const int nz = z_off[u + 1] - z_off[u];
+    int c0, c1 = -1;
+    if (kind == 1) {                     // node x, at most one parent
+      if (nz > 1) return BNL_OK;
+      c0 = slot_of(x[u]);
+      if (nz == 1 && (c1 = slot_of(z_idx[z_off[u]])) < 0) return BNL_OK;
+    } else {                             // x against y (make_unit puts y first), no conditioning
+      if (nz != 0) return BNL_OK;
+      const int yy = y ? y[u] : -1;
+      if (yy >= 0) { c0 = slot_of(yy); c1 = slot_of(x[u]); if (c1 < 0) return BNL_OK; }
+      else c0 = slot_of(x[u]);
+    }
+    if (c0 < 0 || c0 == c1) return BNL_OK;
+    used[c0] = 1;
+    if (c1 >= 0) used[c1] = 1;
+    h_cc[u] = make_int2(c0, c1);
+    h_off[u] = cells;
+    const int l0 = lev_by_slot[c0], l1 = c1 >= 0 ? lev_by_slot[c1] : 1;
+    if (kind == 2 && table_off[u + 1] - table_off[u] < (int64_t)l0 * l1)
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_counts: table_off leaves %lld cells for unit %d, which needs %d",
+                      (long long)(table_off[u + 1] - table_off[u]), u, l0 * l1);
+    if (kind != 2) {
+      const bool sc = kind == 1 || c1 < 0;
+      warp_ok = warp_ok && epilogue_warp_ok(kind, code, sc ? l0 : l1, sc ? 1 : l0, sc ? l1 : 1);
+    }
+    cells += (long long)l0 * l1;
+  }
+  if (cells > kMaxBatchCells) return BNL_OK;
+  if (knob < 2) {
+    double tensor_s, atomic_s;
+    bnl_pairs_cost(dev, ds, used, n, lev_by_slot, &tensor_s, &atomic_s);
+    if (!(tensor_s < 0.8 * atomic_s)) return BNL_OK;
+  }
+  *handled = true;
+  BnlDeviceData &dd = ds.dev[0];
+  BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  if ((rc = bnl_reserve_device(ctx, &dev.d_gidx, &dev.gidx_cap, stage_ints + (size_t)ds.nd + 8))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_units, &dev.units_cap, (size_t)n))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_tables, &dev.tables_cap, (size_t)cells))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_out, &dev.out_cap, (size_t)n * 4))) return rc;
+  if ((rc = bnl_reserve_pinned(ctx, &dev.h_out, &dev.h_out_cap, (size_t)n * 4))) return rc;
+  // the per-slot level counts ride behind the staged arrays
+  memcpy(dev.h_gidx + stage_ints, lev_by_slot.data(), (size_t)ds.nd * sizeof(int));
+  int *d_lev = dev.d_gidx + stage_ints;
+  BnlTiming tm;
+  BNL_CUDA(ctx, cudaEventRecord(dev.ev0, dev.stream));
+  BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_gidx, dev.h_gidx, (stage_ints + (size_t)ds.nd) * sizeof(int), cudaMemcpyHostToDevice,
+                                dev.stream));
+  build_pair_units_kernel<<<(n + 255) / 256, 256, 0, dev.stream>>>(
+      reinterpret_cast<const int2 *>(dev.d_gidx), reinterpret_cast<const long long *>(dev.d_gidx + (size_t)n * 2), d_lev,
+      kind == 1, n, dev.d_units);
+  BNL_CUDA(ctx, cudaGetLastError());
+  tm.launches++;
+  BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
+  if ((rc = bnl_pairs_run(ctx, dev, ds, dd, used, nullptr, n, lev_by_slot, &tm))) return rc;
+  BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
+  if (kind == 2) {
+    BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
+    if ((rc = bnl_reserve_pinned(ctx, &dev.h_tables, &dev.h_tables_cap, (size_t)cells))) return rc;
+    BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_tables, dev.d_tables, (size_t)cells * sizeof(int), cudaMemcpyDeviceToHost, dev.stream));
+    BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+    for (int u = 0; u < n; u++) {
+      const long long c = (u + 1 < n ? h_off[u + 1] : cells) - h_off[u];
+      memcpy(tables + table_off[u], dev.h_tables + h_off[u], (size_t)c * sizeof(int));
+    }
+  } else {
+    if (kind == 1 && (code == BNL_FNML || code == BNL_QNML) && (rc = bnl_regret_table(ctx, dev))) return rc;
+    const int mstride = (2 * BNL_MAX_LEVELS + 2 + 31) & ~31;
+    const size_t esmem = (size_t)mstride * BNL_EPI_WARPS * sizeof(int);
+    if (warp_ok)
+      epilogue_kernel<false, true><<<(n + BNL_EPI_WARPS - 1) / BNL_EPI_WARPS, BNL_EPI_THREADS, esmem, dev.stream>>>(
+          dev.d_units, dev.d_tables, dev.d_out, kind, code, arg, ds.nobs, dev.d_regret, mstride, n);
+    else
+      epilogue_kernel<false><<<n, BNL_EPI_THREADS, esmem, dev.stream>>>(dev.d_units, dev.d_tables, dev.d_out, kind, code,
+                                                                       arg, ds.nobs, dev.d_regret, mstride);
+    BNL_CUDA(ctx, cudaGetLastError());
+    tm.launches++;
+    BNL_CUDA(ctx, cudaEventRecord(dev.eve1, dev.stream));
+    BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)n * 4 * sizeof(double), cudaMemcpyDeviceToHost, dev.stream));
+    BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
+    BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+    for (int u = 0; u < n; u++) {
+      if (o0) o0[u] = dev.h_out[4 * (size_t)u];
+      if (o1) o1[u] = dev.h_out[4 * (size_t)u + 1];
+      if (o2) o2[u] = dev.h_out[4 * (size_t)u + 2];
+    }
+  }
+  float t = 0.f;
+  BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.ev0, dev.ev1));
+  ctx->last_ms = t;
+  BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.evc0, dev.evc1));
+  ctx->last_count_ms = t;
+  ctx->last_epi_ms = 0.0;
+  if (kind != 2) {
+    BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.evc1, dev.eve1));
+    ctx->last_epi_ms = t;
+  }
+  ctx->last_launches = tm.launches;
+  return BNL_OK;
+}
+
 int run_request(bnl_ctx *ctx, BnlDataSet &ds, Request &rq) {
   const int ndev = (int)ctx->devs.size();
   ctx->last_ms = ctx->last_count_ms = ctx->last_epi_ms = 0.0;
@@ -680,6 +829,11 @@ extern "C" int bnl_counts(bnl_ctx *ctx, bnl_data data, int n, const int *x, cons
   if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   if (n < 0 || (n > 0 && (!x || !z_off || !tables || !table_off)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_counts: bad arguments");
+  {
+    bool handled = false;
+    int rc = compact_pairs(ctx, *ds, 2, 0, 0.0, n, x, y, z_off, z_idx, nullptr, nullptr, nullptr, tables, table_off, &handled);
+    if (rc || handled) return rc;
+  }
   Request rq{2, 0, 0.0, n, {}, nullptr, nullptr, nullptr, tables, table_off};
   rq.units.resize(n);
   for (int u = 0; u < n; u++) {
@@ -780,6 +934,11 @@ int bnl_ci_discrete_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const in
   if (!ds) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
   if (n < 0 || (n > 0 && (!x || !y || !z_off)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_discrete: bad arguments");
+  {
+    bool handled = false;
+    int rc = compact_pairs(ctx, *ds, 0, test_e, 0.0, n, x, y, z_off, z_idx, stat, df, pvalue, nullptr, nullptr, &handled);
+    if (rc || handled) return rc;
+  }
   Request rq{0, test_e, 0.0, n, {}, stat, df, pvalue, nullptr, nullptr};
   rq.units.resize(n);
   for (int u = 0; u < n; u++) {
@@ -827,6 +986,12 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "score %d is not a discrete score handled here", score_e);
   if (n < 0 || (n > 0 && (!target || !pa_off || !score)))
     return bnl_fail(ctx, BNL_EINVAL, "bnl_score_discrete: bad arguments");
+  {
+    bool handled = false;
+    int rc = compact_pairs(ctx, *ds, 1, score_e, k_or_iss, n, target, nullptr, pa_off, pa_idx, score, nparams, nullptr,
+                           nullptr, nullptr, &handled);
+    if (rc || handled) return rc;
+  }
   Request rq{1, score_e, k_or_iss, n, {}, score, nparams, nullptr, nullptr, nullptr};
   rq.units.resize(n);
   for (int u = 0; u < n; u++) {

@@ -787,6 +787,39 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 }
 
 // ---------------------------------------------------------------------------
+// Unit descriptors of a batch made only of one- and two-way tables, written on the
+// device: the host sends 8 bytes of column slots and the table offset per unit
+// instead of a 160-byte BnlUnit (499 500 units in the first hc iteration: 80 MB of
+// descriptors built, copied twice and uploaded were most of the call's wall time).
+// cc = {first column, second column or -1} in make_unit's order; score_like: the
+// first column is the node and the second its parent (a stratum per parent level),
+// otherwise the first is y and the second x of a two-way table in one stratum.
+__global__ void __launch_bounds__(256)
+build_pair_units_kernel(const int2 *__restrict__ cc, const long long *__restrict__ off,
+                        const int *__restrict__ lev_by_slot, int score_like, int n, BnlUnit *__restrict__ units) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int2 c = cc[t];
+  const int l0 = lev_by_slot[c.x], l1 = c.y >= 0 ? lev_by_slot[c.y] : 1;
+  BnlUnit u;
+  int *w = reinterpret_cast<int *>(&u);
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(BnlUnit) / sizeof(int)); i++) w[i] = 0;
+  u.table_off = off[t];
+  u.cells = l0 * l1;
+  u.ncols = c.y >= 0 ? 2 : 1;
+  if (score_like || c.y < 0) { u.llx = l0; u.lly = 1; u.llz = l1; }
+  else { u.lly = l0; u.llx = l1; u.llz = 1; }
+  u.col[0] = c.x; u.mul[0] = 1;
+  if (c.y >= 0) { u.col[1] = c.y; u.mul[1] = l0; }
+  static_assert(sizeof(BnlUnit) % 8 == 0, "BnlUnit is copied in 8-byte words");
+  long long *dst = reinterpret_cast<long long *>(units + t);      // 168 bytes: 8-byte aligned, not 16
+  const long long *src = reinterpret_cast<const long long *>(&u);
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(BnlUnit) / 8); i++) dst[i] = src[i];
+}
+
+// ---------------------------------------------------------------------------
 // Epilogue. kind 0: CI test (code = test_e); kind 1: node score (code = score_e).
 // One CTA per unit, one warp per stratum (configuration of Z / of the parents).
 
@@ -831,11 +864,16 @@ __device__ __forceinline__ double nml_regret(const double *__restrict__ tab, dou
 
 // EXT compiles in the Jonckheere-Terpstra and shrinkage-MI branches; the common
 // statistics keep their own, leaner instantiation (the extra code costs registers).
-template <bool EXT>
+// WPU ("warp per unit"): batches of many tiny tables -- the first hc iteration asks for
+// 499 500 of them -- give every warp of the CTA its own unit instead of a CTA each
+// (CTA scheduling, not arithmetic, was the cost: 2.9 ms). The host only selects it when
+// one warp does all the work of the unit anyway (bnl_epilogue_warp_ok), so the lanes
+// see the same cells and the sums are formed in the same order: identical results.
+template <bool EXT, bool WPU = false>
 __global__ void __launch_bounds__(BNL_EPI_THREADS)
 epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ tables,
                 double *__restrict__ out, int kind, int code, double arg, long long nrows,
-                const double *__restrict__ regret, int marg_stride) {
+                const double *__restrict__ regret, int marg_stride, int nunits = 0) {
   // margins of one stratum per warp: llx + lly ints, in dynamic shared memory so
   // that tests on factors with thousands of levels (uint16 columns) fit as well.
   extern __shared__ int s_marg_dyn[];
@@ -843,16 +881,21 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   __shared__ long long s_n[BNL_EPI_WARPS];
   __shared__ int s_q;
 
-  const BnlUnit U = units[blockIdx.x];
-  const int *T = tables + U.table_off;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int unit = WPU ? blockIdx.x * BNL_EPI_WARPS + warp : blockIdx.x;
+  if (WPU && unit >= nunits) return;
+  const BnlUnit U = units[unit];
+  const int *T = tables + U.table_off;
+  // position of this warp / thread among those that share the unit
+  const int sw = WPU ? 0 : warp, nw = WPU ? 1 : BNL_EPI_WARPS;
+  const int tid = WPU ? lane : (int)threadIdx.x, nthr = WPU ? 32 : BNL_EPI_THREADS;
   const int llx = U.llx, lly = U.lly, llz = U.llz, sl = llx * lly;
   int *marg = s_marg_dyn + (size_t)warp * marg_stride;
 
   // BDs: the prior is spread over the OBSERVED parent configurations only
   // (src/scores/dirichlet.posterior.c:180 -> all_levels = FALSE).
   int q = llz;
-  if (kind == 1 && code == BNL_BDS) {
+  if (!WPU && kind == 1 && code == BNL_BDS) {
     if (threadIdx.x == 0) s_q = 0;
     __syncthreads();
     int mine = 0;
@@ -871,7 +914,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   // (mi_lambda, src/tests/discrete/shrinkage.c:138-184): two block-wide passes,
   // the complete-row count, then sum (n/N)^2 and sum (target - n/N)^2.
   double sh_lambda = 0.0, sh_target = 0.0, sh_n = 0.0;
-  if (EXT && kind == 0 && code == BNL_MI_SH) {
+  if (EXT && !WPU && kind == 0 && code == BNL_MI_SH) {
     const long long cells = (long long)sl * llz;
     long long loc = 0;
     for (long long c = threadIdx.x; c < cells; c += BNL_EPI_THREADS) loc += T[c];
@@ -924,7 +967,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   // through the lgamma / log terms.
   const bool lane_strata = kind == 1 && sl <= 16;
   if (lane_strata) {
-    for (int k = threadIdx.x; k < llz; k += BNL_EPI_THREADS) {
+    for (int k = tid; k < llz; k += nthr) {
       const int *S = T + (size_t)k * sl;
       long long nk = 0;
       for (int c = 0; c < sl; c++) nk += S[c];
@@ -947,7 +990,7 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
       }
     }
   }
-  for (int k = lane_strata ? llz : warp; k < llz; k += BNL_EPI_WARPS) {
+  for (int k = lane_strata ? llz : sw; k < llz; k += nw) {
     const int *S = T + (size_t)k * sl;
     if (kind == 0) {
       for (int i = lane; i < llx + lly; i += 32) marg[i] = 0;
@@ -1088,14 +1131,23 @@ epilogue_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ table
   warp_merge_kahan(acc);
   dfacc = warp_sum_d(dfacc);
   nobs = warp_sum_ll(nobs);
-  if (lane == 0) { s_s[warp] = acc.s; s_c[warp] = acc.c; s_df[warp] = dfacc; s_n[warp] = nobs; }
-  __syncthreads();
-  if (threadIdx.x != 0) return;
   bnl::KahanSum tot;
   double df = 0.0;
   long long n = 0;
-  for (int w = 0; w < BNL_EPI_WARPS; w++) { tot.merge(s_s[w], s_c[w]); df += s_df[w]; n += s_n[w]; }
-  double *o = out + (size_t)blockIdx.x * 4;
+  if (WPU) {
+    if (lane != 0) return;
+    // what thread 0 does below when the other three warps held nothing
+    tot.merge(acc.s, acc.c);
+    for (int w = 1; w < BNL_EPI_WARPS; w++) tot.merge(0.0, 0.0);
+    df = 0.0 + dfacc;
+    n = nobs;
+  } else {
+    if (lane == 0) { s_s[warp] = acc.s; s_c[warp] = acc.c; s_df[warp] = dfacc; s_n[warp] = nobs; }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    for (int w = 0; w < BNL_EPI_WARPS; w++) { tot.merge(s_s[w], s_c[w]); df += s_df[w]; n += s_n[w]; }
+  }
+  double *o = out + (size_t)unit * 4;
   if (kind == 0) {
     const bool adf = code == BNL_MI_ADF || code == BNL_X2_ADF;
     const double chan = df;

@@ -205,11 +205,13 @@ struct BnlTiming { float total = 0.f, count = 0.f, epi = 0.f; int launches = 0; 
 // All-pairs contraction on the tensor cores (bnl_pairs.cu, kernels in bnl_pairs.cuh): decide whether the pair units of a batch are worth one
 // contraction, run it and fill their tables. picked[] lists positions in h_units.
 bool bnl_pairs_eligible(const BnlUnit &u, const std::vector<int> &lev_by_slot);
+// used[slot]: the packed columns the units touch; picked: positions of the pair units in
+// the batch's unit array (null: all nunits units, in order).
 int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlDeviceData &dd,
-                  const BnlUnit *h_units, const std::vector<int> &picked, const std::vector<int> &lev_by_slot,
-                  BnlTiming *tm);
+                  const std::vector<char> &used, const std::vector<int> *picked, int nunits,
+                  const std::vector<int> &lev_by_slot, BnlTiming *tm);
 // estimated seconds of the contraction for these units, and of counting them one by one
-void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const BnlUnit *h_units, const std::vector<int> &picked,
+void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<char> &used, long long nunits,
                     const std::vector<int> &lev_by_slot, double *tensor_s, double *atomic_s);
 
 // split [0, n) into ndev contiguous blocks.

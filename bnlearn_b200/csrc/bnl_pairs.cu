@@ -26,11 +26,8 @@ struct Plan {
   int total_stages = 0, splits = 1, per_split = 0;
 };
 
-void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const BnlUnit *h_units, const std::vector<int> &picked,
+void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<char> &used,
                const std::vector<int> &lev_by_slot, Plan *p) {
-  std::vector<char> used(ds.nd, 0);
-  for (int i : picked)
-    for (int k = 0; k < h_units[i].ncols; k++) used[h_units[i].col[k]] = 1;
   for (int s = 0; s < ds.nd; s++)
     if (used[s]) {
       p->slots.push_back(s);
@@ -68,22 +65,22 @@ bool bnl_pairs_eligible(const BnlUnit &u, const std::vector<int> &lev_by_slot) {
   return u.ncols == 1 || u.col[0] != u.col[1];
 }
 
-void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const BnlUnit *h_units, const std::vector<int> &picked,
+void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<char> &used, long long nunits,
                     const std::vector<int> &lev_by_slot, double *tensor_s, double *atomic_s) {
   Plan p;
-  make_plan(dev, ds, h_units, picked, lev_by_slot, &p);
+  make_plan(dev, ds, used, lev_by_slot, &p);
   const double macs = (double)p.tiles.size() * PAIR_BM * p.bn * (double)ds.nobs;
   const double hbm = (double)p.slots.size() * (double)ds.nobs / 5e12;
   *tensor_s = std::max(macs / kPairMacRate, hbm) + 40e-6;
-  *atomic_s = (double)picked.size() * (double)ds.nobs / kAtomicRate + 10e-6;
+  *atomic_s = (double)nunits * (double)ds.nobs / kAtomicRate + 10e-6;
 }
 
 int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlDeviceData &dd,
-                  const BnlUnit *h_units, const std::vector<int> &picked, const std::vector<int> &lev_by_slot,
-                  BnlTiming *tm) {
+                  const std::vector<char> &used, const std::vector<int> *picked, int nunits,
+                  const std::vector<int> &lev_by_slot, BnlTiming *tm) {
   Plan p;
-  make_plan(dev, ds, h_units, picked, lev_by_slot, &p);
-  const int nc = (int)p.slots.size(), nt = (int)p.tiles.size(), np = (int)picked.size();
+  make_plan(dev, ds, used, lev_by_slot, &p);
+  const int nc = (int)p.slots.size(), nt = (int)p.tiles.size(), np = picked ? (int)picked->size() : 0;
   // one int block: cols (int4 per column) | ind2col [ldg] | slot_first [nd] | tiles (int2) | ids [np]
   const size_t n_cols = (size_t)nc * 4, n_ind = (size_t)p.ldg, n_sf = ((size_t)ds.nd + 1) & ~(size_t)1, n_tiles = (size_t)nt * 2;
   const size_t total = n_cols + n_ind + n_sf + n_tiles + (size_t)np + 16;
@@ -102,7 +99,7 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   }
   for (int r = p.L; r < p.ldg; r++) h_ind[r] = nc - 1;
   memcpy(h_tiles, p.tiles.data(), n_tiles * sizeof(int));
-  for (int i = 0; i < np; i++) h_ids[i] = picked[i];
+  for (int i = 0; i < np; i++) h_ids[i] = (*picked)[i];
   int *d = dev.d_pairmeta;
   int *d_cols = d, *d_ind = d_cols + n_cols, *d_sf = d_ind + n_ind, *d_tiles = d_sf + n_sf, *d_ids = d_tiles + n_tiles;
   BNL_CUDA(ctx, cudaMemcpyAsync(d, h, total * sizeof(int), cudaMemcpyHostToDevice, dev.stream));
@@ -146,8 +143,9 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   else BNL_PAIR_LAUNCH(256, 5, 3, smem256);
 #undef BNL_PAIR_LAUNCH
   BNL_CUDA(ctx, cudaGetLastError());
-  pair_extract_kernel<<<(np + 255) / 256, 256, 0, dev.stream>>>(dev.d_units, d_ids, np, d_sf, dev.d_pairG, p.ldg,
-                                                              dev.d_tables);
+  // picked == null: every unit of the batch, in order
+  pair_extract_kernel<<<(nunits + 255) / 256, 256, 0, dev.stream>>>(dev.d_units, picked ? d_ids : nullptr, nunits, d_sf,
+                                                                  dev.d_pairG, p.ldg, dev.d_tables);
   BNL_CUDA(ctx, cudaGetLastError());
   tm->launches += 2;
   return BNL_OK;

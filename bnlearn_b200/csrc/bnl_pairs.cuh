@@ -329,7 +329,7 @@ pair_extract_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ i
                     int *__restrict__ tables) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
-  const BnlUnit &u = units[ids[t]];
+  const BnlUnit &u = units[ids ? ids[t] : t];
   int *tab = tables + u.table_off;
   const int f0 = slot_first[u.col[0]];
   if (u.ncols == 1) {

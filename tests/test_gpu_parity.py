@@ -1023,6 +1023,12 @@ def test_all_pairs_tensor_core_tables(engine, monkeypatch, ncols, nobs, maxlev):
             shape.insert(0, lev[z[0]])
         want = np.bincount(key[keep], minlength=int(np.prod(shape)))
         assert np.array_equal(np.asarray(t).ravel(), want), (x, y, z)
+    # the same tables from a batch without the conditional units: with >= 4096 units this
+    # takes the route that builds the unit descriptors on the device
+    keep_u = [k for k, z in enumerate(zs) if not z]
+    again = d.counts([xs[k] for k in keep_u], [ys[k] for k in keep_u], [[]] * len(keep_u))
+    for k, t in zip(keep_u, again):
+        assert np.array_equal(np.asarray(t), np.asarray(tabs[k])), (xs[k], ys[k])
     pairs = [(x, y) for x, y, z in zip(xs, ys, zs) if y >= 0 and not z]
     px, py = [p[0] for p in pairs], [p[1] for p in pairs]
     got = d.ci_discrete("mi", px, py, [[]] * len(pairs)) + d.score_discrete("bde", px, [[v] for v in py], 1.0)
