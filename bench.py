@@ -212,19 +212,20 @@ def hbm_peak():
         return 6650.0, "fallback 6650 (B200_PROFILING.md)"
 
 
-def hbm_class(name, kernel_ms, compulsory_bytes, unit_bytes, units, rows, peak, note=None):
+def hbm_class(name, kernel_ms, compulsory_bytes, unit_bytes, units, rows, peak, note=None, atomic=True):
     """One roofline entry of a counting launch. achieved =
-    compulsory bytes (each distinct column once) / kernel time; effective = the sum
-    of the units' own bytes / time; atomic_frac = row updates per second over the
-    shared-memory-atomic ceiling, given when units share columns more than 2-fold."""
+    compulsory bytes (each distinct column once) / kernel time, frac <= 1; effective =
+    the sum of the units' own bytes / time; the >= 50 % HBM target applies to launches
+    with at most 2 units per distinct column. atomic_frac = row updates per second
+    over the shared-memory-atomic ceiling, for launches counted with atomics."""
     t = kernel_ms * 1e-3
+    per_col = float(units) * float(rows) / max(compulsory_bytes, 1.0)
     e = {"class": name, "bound": "hbm", "units": int(units), "kernel_ms": kernel_ms,
          "compulsory_bytes": float(compulsory_bytes), "achieved": compulsory_bytes / t / 1e9,
          "peak": peak, "unit": "GB/s", "frac": compulsory_bytes / t / 1e9 / peak,
-         "effective": unit_bytes / t / 1e9,
-         "units_per_distinct_column": unit_bytes / max(compulsory_bytes, 1.0),
-         "in_target_domain": bool(unit_bytes <= 2.0 * compulsory_bytes)}
-    if unit_bytes > 2.0 * compulsory_bytes:
+         "effective": unit_bytes / t / 1e9, "units_per_distinct_column": per_col,
+         "in_target_domain": bool(per_col <= 2.0)}
+    if atomic:
         e["atomic_frac"] = float(units) * float(rows) / t / ATOMIC_CEILING
         e["atomic_ceiling_updates_per_s"] = ATOMIC_CEILING
     if note:
@@ -271,26 +272,26 @@ def config_c_extras(eng, world, rank, device, cpu_cores=0, reps=5, want_hc=True)
 
     if rank == 0:
         # (a) mid-run iterations: every other node as the candidate parent of a node that
-        #     already has k parents (k = 0..4 -> candidates for nodes "with 1..5 parents").
+        #     already has k parents, k = 0..5 (tables of k + 2 columns).
         tgt = nnodes // 2
         amat = np.zeros((nnodes, nnodes), dtype=np.int32, order="F")
-        for k in range(0, 5):
+        for k in range(0, 6):
             if k:
                 amat[tgt - k, tgt] = 1
             n, dt, kms, dms, _ = timed(amat, [tgt], False)
             comp = float(rows) * (n + k + 1)        # every candidate + target + shared parents, once
             ubytes = float(rows) * n * (k + 2)
-            key = "iteration_%d_parents" % (k + 1)
-            out[key] = {"deltas": n, "ms": dt * 1e3, "deltas_per_sec": n / dt, "count_kernel_ms": kms,
-                        "device_ms": dms, "compulsory_gb": comp / 1e9,
-                        "hbm_frac_compulsory": comp / (kms * 1e-3) / 1e9 / peak}
-            classes.append(hbm_class("config C: %d candidates for a node with %d parent%s (tables of node x %d parents)"
-                                     % (n, k, "" if k == 1 else "s", k + 1), kms, comp, ubytes, n, rows, peak))
-            if k == 1 and cpu_cores > 0:
+            key = "iteration_%d_parents" % k
+            out[key] = {"existing_parents": k, "columns_per_table": k + 2, "deltas": n, "ms": dt * 1e3,
+                        "deltas_per_sec": n / dt, "count_kernel_ms": kms, "device_ms": dms,
+                        "compulsory_gb": comp / 1e9, "hbm_frac_compulsory": comp / (kms * 1e-3) / 1e9 / peak}
+            classes.append(hbm_class("config C: %d candidate parents of a node that has %d (tables of %d columns)"
+                                     % (n, k, k + 2), kms, comp, ubytes, n, rows, peak))
+            if k == 2 and cpu_cores > 0:
                 # the same deltas on the host: a bounded sample of the candidates, 4 per core
-                cands = [i for i in range(nnodes) if i not in (tgt, tgt - 1)][:4 * cpu_cores]
+                cands = [i for i in range(nnodes) if i not in (tgt, tgt - 1, tgt - 2)][:4 * cpu_cores]
                 try:
-                    v, cdt, kind = cpu_score_run(host, levels, tgt, [tgt - 1], cands, cpu_cores)
+                    v, cdt, kind = cpu_score_run(host, levels, tgt, [tgt - 2, tgt - 1], cands, cpu_cores)
                     out[key]["cpu_reference"] = {"deltas_per_sec": v, "cores": cpu_cores, "kind": kind,
                                                  "sample": "%d of the %d candidates (%.1f s)" % (len(cands), int(n), cdt)}
                 except Exception as exc:          # the CPU leg must never take the GPU numbers down
@@ -335,9 +336,10 @@ def config_c_extras(eng, world, rank, device, cpu_cores=0, reps=5, want_hc=True)
                                               "cache columns summed to every rank with one NCCL all-reduce",
                                   "cache_sha1": hashlib.sha1(np.ascontiguousarray(full).tobytes()).hexdigest()[:16]}
         comp = float(rows) * nnodes
-        classes.append(hbm_class("config C: first iteration, all %d pairs" % int(total), kmax, comp,
-                                 2.0 * rows * total / world, total / world, rows, peak,
-                                 note="max over %d rank(s); two-column tables" % world))
+        classes.append(hbm_class("config C: first iteration, all %d pairs (tcgen05 indicator cross-product)" % int(total),
+                                 kmax, comp, 2.0 * rows * total / world, total / world, rows, peak, atomic=False,
+                                 note="max over %d rank(s); every two-way table from one contraction, so the "
+                                      "columns are read once per output tile row/column, not once per pair" % world))
     # (c) the whole search on one GPU
     if rank == 0 and want_hc:
         t0 = time.perf_counter()
@@ -430,6 +432,12 @@ def wall_times(eng, ds_b, cols_b, lev_b, cores, with_cpu):
     skel, dsep, _ = ds_b.pc_stable("mi", 0.05, counter=counter)
     tb = time.perf_counter() - t0
     out["config_B_pc_stable"] = {"wall_s": tb, "tests": counter.value, "edges": len(skel)}
+    # tests per conditioning-set size, for the reference's extrapolation: the level loop once more,
+    # call by call, counting what each level issues
+    from bnlearn_b200.replicate import ShardedBackend
+    sb = ShardedBackend(learners.GpuBackend(ds_b))
+    learners.pc_stable(sb, len(lev_b), "mi", 0.05)
+    by_level = dict(sb.tests_by_size)
     # A: hc + BIC on the bundled alarm sample
     z = np.load(os.path.join(ROOT, "tests", "golden", "data_alarm.npz"))
     acols = [np.ascontiguousarray(c.astype(np.int32) + 1) for c in z["codes"]]
@@ -490,13 +498,15 @@ def wall_times(eng, ds_b, cols_b, lev_b, cores, with_cpu):
             for u in pick:
                 reference_ci(cols_b, lev_b, u)
             per_size[s] = (time.perf_counter() - t0) / len(pick)
-        mean_t = float(np.mean(list(per_size.values())))
+        last = max(per_size)
+        serial = sum(n * per_size.get(k, per_size[last]) for k, n in by_level.items())
         out["config_B_pc_stable"]["reference"] = {
-            "serial_wall_s_extrapolated": counter.value * 0 + out["config_B_pc_stable"]["tests"] * mean_t,
-            "cluster_wall_s_extrapolated": out["config_B_pc_stable"]["tests"] * mean_t / cores,
+            "serial_wall_s_extrapolated": serial, "cluster_wall_s_extrapolated": serial / cores,
             "cluster_cores": cores, "seconds_per_test_by_conditioning_size": per_size,
+            "tests_by_conditioning_size": by_level,
             "how": "16 tests per conditioning-set size timed on one core through c_fast_config + c_cchisqtest "
-                   "+ pchisq; wall = tests issued by this run x mean time (sampled, extrapolated)"}
+                   "+ pchisq; wall = sum over sizes of (tests this run issued) x (seconds per test); the cluster "
+                   "figure divides every level over P workers (R/pcalgo.R:24-28), no imbalance counted"}
     except Exception as exc:                  # the CPU legs must never take the GPU numbers down
         out["reference_error"] = repr(exc)[:300]
     return out
@@ -843,7 +853,7 @@ def main():
                 line["wall"] = {"error": repr(exc)[:300]}
     # level 0 alone and levels 1-2 alone, for the per-class roofline
     if rank == 0:
-        for nm, sel in (("config B: level 0, all 666 pairs (two-way tables)", [u for u in units if not u[2]]),
+        for nm, sel in (("config B: level 0, all 666 pairs (tcgen05 indicator cross-product)", [u for u in units if not u[2]]),
                         ("config B: levels 1-2, 415 conditional tests", [u for u in units if u[2]])):
             zx = csr([u[2] for u in sel])
             ax = np.array([u[0] for u in sel], dtype=np.int32)
@@ -856,7 +866,7 @@ def main():
             ncols_used = len({c for u in sel for c in (u[0], u[1], *u[2])})
             classes.append(hbm_class(nm, best, float(args.rows) * ncols_used,
                                      float(args.rows) * sum(2 + len(u[2]) for u in sel), len(sel), args.rows,
-                                     hbm_peak()[0]))
+                                     hbm_peak()[0], atomic=bool(sel[0][2])))
     ds.release()
     if extras:
         try:

@@ -15,7 +15,7 @@ long long env_ll(const char *name, long long dflt) {
 }
 // effective multiply-accumulate rate of pair_onehot_kernel on one B200 (measured,
 // profiles/): the producers' code expansion, not the tensor pipe, sets it.
-const double kPairMacRate = (double)env_ll("BNL_PAIRS_GMACS", 400000) * 1e9;
+const double kPairMacRate = (double)env_ll("BNL_PAIRS_GMACS", 750000) * 1e9;
 const double kAtomicRate = 4.2e12;        // row updates per second of the per-unit counting kernels
 
 struct Plan {
@@ -111,36 +111,35 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   // in flight per thread; the widest tile needs 5 columns per thread and affords 3.
   const size_t smem128 = (size_t)PAIR_STAGES * (PAIR_BM + 128) * 128 + 1024;
   const size_t smem256 = (size_t)PAIR_STAGES * (PAIR_BM + 256) * 128 + 1024;
-  if (!dev.pair_attr_done) {
-#define BNL_PAIR_ATTR(BN, ITEMS, DEPTH, SMEM)                                                                      \
-    BNL_CUDA(ctx, cudaFuncSetAttribute(pair_onehot_kernel<BN, ITEMS, DEPTH, false>,                                 \
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMEM)));                  \
-    BNL_CUDA(ctx, cudaFuncSetAttribute(pair_onehot_kernel<BN, ITEMS, DEPTH, true>,                                  \
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMEM)))
-    BNL_PAIR_ATTR(128, 1, 8, smem128);
-    BNL_PAIR_ATTR(128, 3, 4, smem128);
-    BNL_PAIR_ATTR(256, 5, 3, smem256);
-#undef BNL_PAIR_ATTR
-    dev.pair_attr_done = true;
+  // NA bytes between valid codes need one more instruction per word (selector4); factors
+  // with more than four levels need the second half of the level stores
+  bool any_na = false, wide = false;
+  for (int s : p.slots) {
+    any_na = any_na || ds.slot_has_na.empty() || ds.slot_has_na[s];
+    wide = wide || lev_by_slot[s] > 4;
   }
-  // NA bytes between valid codes need one more instruction per word (selector4)
-  bool any_na = false;
-  for (int s : p.slots) any_na = any_na || ds.slot_has_na.empty() || ds.slot_has_na[s];
   const unsigned grid = (unsigned)nt * (unsigned)p.splits;
-#define BNL_PAIR_LAUNCH(BN, ITEMS, DEPTH, SMEM)                                                                   \
+#define BNL_PAIR_GO(BN, ITEMS, DEPTH, NA, WIDE, NPW, SMEM)                                                        \
   do {                                                                                                            \
-    if (any_na)                                                                                                   \
-      pair_onehot_kernel<BN, ITEMS, DEPTH, true><<<grid, PAIR_THREADS, SMEM, dev.stream>>>(                        \
-          dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), d_ind, p.L,                                \
-          reinterpret_cast<const int2 *>(d_tiles), nt, p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out); \
-    else                                                                                                          \
-      pair_onehot_kernel<BN, ITEMS, DEPTH, false><<<grid, PAIR_THREADS, SMEM, dev.stream>>>(                       \
-          dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), d_ind, p.L,                                \
-          reinterpret_cast<const int2 *>(d_tiles), nt, p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out); \
+    auto kern = pair_onehot_kernel<BN, ITEMS, DEPTH, NA, WIDE, NPW>;                                              \
+    BNL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMEM)));          \
+    kern<<<grid, (NPW + 1) * 32, SMEM, dev.stream>>>(dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), \
+                                                     d_ind, p.L, reinterpret_cast<const int2 *>(d_tiles), nt,     \
+                                                     p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out); \
   } while (0)
-  if (p.bn == 128 && nc <= PAIR_PRODUCERS / 8) BNL_PAIR_LAUNCH(128, 1, 8, smem128);
-  else if (p.bn == 128) BNL_PAIR_LAUNCH(128, 3, 4, smem128);
-  else BNL_PAIR_LAUNCH(256, 5, 3, smem256);
+#define BNL_PAIR_LAUNCH(BN, ITEMS, DEPTH, NPW, SMEM)                                                              \
+  do {                                                                                                            \
+    if (any_na && wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, true, NPW, SMEM);                                     \
+    else if (any_na) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, false, NPW, SMEM);                                       \
+    else if (wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, false, true, NPW, SMEM);                                         \
+    else BNL_PAIR_GO(BN, ITEMS, DEPTH, false, false, NPW, SMEM);                                                  \
+  } while (0)
+  // columns per producer thread: the tile's columns over 4 * NPW column lanes (19 + 1
+  // warps measured 4 % faster than 11 + 1 on the wide tile, 15 + 1 and 23 + 1 slower)
+  if (p.bn == 128 && nc <= 44) BNL_PAIR_LAUNCH(128, 1, 8, 11, smem128);
+  else if (p.bn == 128) BNL_PAIR_LAUNCH(128, 2, 4, 19, smem128);      // <= 130 columns over 76 lanes
+  else BNL_PAIR_LAUNCH(256, 3, 3, 19, smem256);                       // <= 194 columns over 76 lanes
+#undef BNL_PAIR_GO
 #undef BNL_PAIR_LAUNCH
   BNL_CUDA(ctx, cudaGetLastError());
   // picked == null: every unit of the batch, in order

@@ -25,9 +25,11 @@
 #define PAIR_BM 128                 // indicator rows of the A operand = TMEM lanes
 #define PAIR_KROWS 128              // data rows per pipeline stage = 128 bytes of K per indicator row
 #define PAIR_STAGES 4
-#define PAIR_PRODUCERS 352          // 11 warps expand codes; the 12th issues the MMAs (registers are
-                                    // allotted per 4 warps: 9 warps would cost as much as 12)
-#define PAIR_THREADS (PAIR_PRODUCERS + 32)
+// NPW producer warps expand codes and one more warp issues the MMAs (template
+// parameter). A producer warp's own instruction stream is the critical path of a
+// stage -- one warp issues about once in five cycles on its dependency chains -- so
+// the wide tile runs 19 + 1 warps with 3 columns per thread rather than 11 + 1 with
+// 5 (registers are allotted per 4 warps: the total is kept a multiple of 4).
 #define PAIR_MAX_LEVELS 8           // one byte-permute selects among 8 table bytes
 
 namespace bnlpair {
@@ -49,6 +51,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity) {
     uint32_t done;
     asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
                  : "=r"(done) : "r"(smem_u32(b)), "r"(parity), "r"(1000000u) : "memory");
+    if (done) return;
+  }
+  __trap();
+}
+
+// The MMA issuer must react within a fraction of a stage time (~0.3 us): it polls
+// without a suspend hint (a parked thread wakes too late, the tensor pipe then idles
+// until a burst of ready stages has piled up). One thread; ~3 instructions per poll.
+__device__ __forceinline__ void mbar_wait_spin(uint64_t *b, uint32_t parity) {
+  for (int tries = 0; tries < (1 << 28); tries++) {
+    uint32_t done;
+    asm volatile("{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(done) : "r"(smem_u32(b)), "r"(parity) : "memory");
     if (done) return;
   }
   __trap();
@@ -109,8 +124,10 @@ __device__ __forceinline__ uint32_t selector4(uint32_t w) {
   const uint32_t t = m | (m >> 4);                 // byte 0: codes 0, 1; byte 2: codes 2, 3
   return __byte_perm(t, 0u, 0x4420);
 }
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+// predicated store: no branch around it
+__device__ __forceinline__ void sts128_if(uint32_t on, uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("{ .reg .pred p; setp.ne.b32 p, %0, 0; @p st.shared.v4.b32 [%1], {%2, %3, %4, %5}; }"
+               ::"r"(on), "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
 }  // namespace bnlpair
@@ -119,23 +136,35 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 // [bn * BN, +BN), over the data rows of one split. grid = tiles x splits, tile
 // fastest, so the CTAs resident at one time work on the same slab of rows and a
 // column's bytes come from HBM once. One CTA per SM.
-//   warps 0-10 expand codes into the stage buffers; warps 0-7 then drain the accumulator
-//   warp  11   waits for full stages and issues 4 MMAs (K = 32 each) per stage
+//   warps 0..NPW-1  expand codes into the stage buffers; warps 0-7 then drain the accumulator
+//   warp  NPW       waits for full stages and issues 4 MMAs (K = 32 each) per stage
 // cols[] lists the selected columns in indicator order: {packed slot, first indicator, levels}.
-template <int BN, int ITEMS, int DEPTH, bool NA>
-__global__ void __launch_bounds__(PAIR_THREADS, 1)
+//
+// The stage loop is written without branches. A producer warp's own instruction
+// stream is the critical path of a stage (12 warps, 3 per scheduler: one warp issues
+// about once in five cycles), and in the first versions most of that stream was
+// control flow -- an EMPTY stage loop (no loads, no expansion, no MMA) already took
+// 4.1 of the kernel's 7.0 ms. So: every thread owns ITEMS column slots whether or not
+// they are used (an unused slot loads column 0 and stores nothing), stores and loads
+// are predicated instead of skipped, the trip count is padded to a multiple of the
+// ring depth (a padded stage stores nothing and its MMAs are predicated off), and the
+// levels past the fourth are compiled in only for the WIDE variant.
+template <int BN, int ITEMS, int DEPTH, bool NA, bool WIDE, int NPW>
+__global__ void __launch_bounds__((NPW + 1) * 32, 1)
 pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__restrict__ cols,
                    const int *__restrict__ ind2col, int L, const int2 *__restrict__ tiles, int ntiles,
                    int stages_per_split, int total_stages, int *__restrict__ G, int ldg, int atomic_out) {
   using namespace bnlpair;
   constexpr int A_BYTES = PAIR_BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int NS = PAIR_STAGES;
+  static_assert((NS & (NS - 1)) == 0, "stage ring indexed with a mask");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // the dynamic window is only guaranteed 16-byte alignment: round up to the swizzle atom
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  __shared__ uint64_t full_bar[PAIR_STAGES], empty_bar[PAIR_STAGES], accum_bar;
+  __shared__ uint64_t full_bar[NS], empty_bar[NS], accum_bar;
   __shared__ uint32_t s_tmem;
   __shared__ int s_slot[256], s_row[256], s_nlev[256], s_off[256];
-  __shared__ int s_nitems;
+  __shared__ int s_range[4];
 
   const int tile = blockIdx.x % ntiles, split = blockIdx.x / ntiles;
   const int bm = tiles[tile].x, bn = tiles[tile].y;
@@ -145,32 +174,30 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < PAIR_STAGES; s++) { mbar_init(&full_bar[s], PAIR_PRODUCERS / 32); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < NS; s++) { mbar_init(&full_bar[s], NPW); mbar_init(&empty_bar[s], 1); }
     mbar_init(&accum_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    // work list: the columns that reach into the B rows, then (unless shared) the A rows
-    int n = 0;
-    for (int pass = 0; pass < 2; pass++) {
-      if (pass == 1 && a_in_b) break;
-      const int r0 = pass == 0 ? b0 : a0, nr = pass == 0 ? BN : PAIR_BM;
-      if (r0 >= L) continue;
-      const int last = min(r0 + nr, L) - 1;
-      for (int c = ind2col[r0]; c <= ind2col[last]; c++) {
-        const int4 ci = cols[c];
-        s_slot[n] = ci.x; s_row[n] = ci.y - r0; s_nlev[n] = ci.z;
-        s_off[n] = (pass == 0 ? A_BYTES : 0) | (nr << 20);
-        n++;
-      }
-    }
-    s_nitems = n;
+    // columns that reach into the B rows, then (unless shared) into the A rows
+    s_range[0] = ind2col[b0];
+    s_range[1] = ind2col[min(b0 + BN, L) - 1];
+    s_range[2] = a_in_b ? 1 : ind2col[a0];
+    s_range[3] = a_in_b ? 0 : ind2col[min(a0 + PAIR_BM, L) - 1];
   }
-  if (warp == PAIR_PRODUCERS / 32) {
+  if (warp == NPW) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "n"(BN));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   // rows that no column writes (beyond L, or levels outside the tile) must read as 0
-  for (int i = threadIdx.x; i < PAIR_STAGES * STAGE_BYTES / 16; i += PAIR_THREADS)
+  for (int i = threadIdx.x; i < NS * STAGE_BYTES / 16; i += (NPW + 1) * 32)
     reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  const int nB = s_range[1] - s_range[0] + 1, nA = s_range[3] - s_range[2] + 1, nitems = nB + nA;
+  for (int q = threadIdx.x; q < nitems; q += (NPW + 1) * 32) {     // the work list, one column per thread
+    const bool inB = q < nB;
+    const int4 ci = cols[inB ? s_range[0] + q : s_range[2] + q - nB];
+    s_slot[q] = ci.x; s_row[q] = ci.y - (inB ? b0 : a0); s_nlev[q] = ci.z;
+    s_off[q] = (inB ? A_BYTES : 0) | ((inB ? BN : PAIR_BM) << 20);
+  }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -178,30 +205,28 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
   const uint32_t tmem = s_tmem;
 
   const int st0 = split * stages_per_split;
-  const int st1 = min(st0 + stages_per_split, total_stages);
-  const int nst = st1 - st0;
+  const int nst = min(st0 + stages_per_split, total_stages) - st0;     // >= 1 by the host's split
+  const int npad = (nst + DEPTH - 1) / DEPTH * DEPTH;                  // trip count of both roles
 
-  if (warp < PAIR_PRODUCERS / 32) {
+  if (warp < NPW) {
     // ---------------- producers ----------------
     // Thread = (16-row chunk g, column lane cq): the 8 threads of a column read 128
     // contiguous bytes and write one whole 128-byte operand row per level (the swizzle
     // spreads their 16-byte pieces over all banks). The loads run DEPTH stages ahead in
-    // a register ring -- one CTA per SM, so nothing else hides the memory latency (one
-    // stage ahead left the kernel latency-bound at 1/5 of its speed) -- and the lines
-    // 16 stages ahead are pulled from DRAM into L2.
+    // a register ring -- one CTA per SM, so nothing else hides the memory latency -- and
+    // the lines 16 stages ahead are pulled from DRAM into L2.
     const int g = threadIdx.x & 7, cq = threadIdx.x >> 3;
-    const int nitems = s_nitems;
-    // per column of this thread, fixed for the whole kernel: where its rows go inside a
-    // stage (sa), which levels fall inside the tile (lm, one bit per level), and the
-    // swizzled 16-byte piece of this thread's chunk in each of those rows (sw: one byte
-    // per level, levels 0-3 and 4-7), so that a level costs one byte-extract, one add,
-    // four byte-permutes and the store.
+    // per column slot of this thread, fixed for the whole kernel: the column's start
+    // (coff, 16-byte units), where its rows go inside a stage (sa), which levels fall
+    // inside the tile (lm, one bit per level; 0: unused slot), and the swizzled 16-byte
+    // piece of this thread's chunk in each of those rows (sw: one byte per level), so
+    // that a level costs one byte-extract, one add, four byte-permutes and the store.
     uint32_t coff[ITEMS], sa[ITEMS], lm[ITEMS], sw_lo[ITEMS], sw_hi[ITEMS];
     const uint4 *base4 = reinterpret_cast<const uint4 *>(u8);
     const uint32_t stride16 = (uint32_t)(stride >> 4);
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
-      const int q = cq + (PAIR_PRODUCERS / 8) * i;
+      const int q = cq + (NPW * 4) * i;
       const bool ok = q < nitems;
       const int row = ok ? s_row[q] : 0, nl = ok ? s_nlev[q] : 0, nr = ok ? (s_off[q] >> 20) : 0;
       coff[i] = (uint32_t)(ok ? s_slot[q] : 0) * stride16 + (uint32_t)g;
@@ -216,73 +241,86 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
       }
       sw_lo[i] = lo; sw_hi[i] = hi;
     }
+    // The CTAs resident at one time work on the same slab of rows (so that it stays in
+    // L2); each starts at its own place in it and wraps around.
+    const int rot = (int)(((long long)tile * nst) / ntiles);
     uint4 ring[DEPTH][ITEMS];
-    auto load = [&](uint4(&r)[ITEMS], int st) {
-      const uint32_t so = (uint32_t)st * (PAIR_KROWS / 16);
+    auto load = [&](uint4(&r)[ITEMS], int it) {          // it < nst: a real stage
+      int w = it + rot;
+      w -= w >= nst ? nst : 0;
+      const uint32_t so = (uint32_t)(st0 + w) * (PAIR_KROWS / 16);
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++) r[i] = __ldg(base4 + (coff[i] + so));
+      int wp = w + 16;
+      wp -= wp >= nst ? nst : 0;
+      const uint32_t sp = (uint32_t)(st0 + wp) * (PAIR_KROWS / 16);
+      const uint32_t pf = g == 0 && it + 16 < nst;
 #pragma unroll
       for (int i = 0; i < ITEMS; i++)
-        if (lm[i]) r[i] = __ldg(base4 + (coff[i] + so));
-      if (g == 0 && st + 16 < st1) {
-#pragma unroll
-        for (int i = 0; i < ITEMS; i++)
-          if (lm[i]) asm volatile("prefetch.global.L2 [%0];" ::"l"(base4 + (coff[i] + so + 16 * (PAIR_KROWS / 16))));
-      }
+        asm volatile("{ .reg .pred p; setp.ne.b32 p, %1, 0; @p prefetch.global.L2 [%0]; }"
+                     ::"l"(base4 + (coff[i] + sp)), "r"(pf & (lm[i] != 0u)));
     };
 #pragma unroll
-    for (int d = 0; d < DEPTH; d++)
-      if (d < nst) load(ring[d], st0 + d);
+    for (int d = 0; d < DEPTH; d++) load(ring[d], min(d, nst - 1));
     const uint32_t smem0 = smem_u32(smem);
-    for (int it0 = 0; it0 < nst; it0 += DEPTH) {
+    for (int it0 = 0; it0 < npad; it0 += DEPTH) {
 #pragma unroll
       for (int d = 0; d < DEPTH; d++) {
         const int it = it0 + d;
-        if (it >= nst) break;
-        const int s = it % PAIR_STAGES;
-        if (it >= PAIR_STAGES) mbar_wait(&empty_bar[s], ((it / PAIR_STAGES) - 1) & 1);
+        const int s = it & (NS - 1);
+        if (it >= NS) mbar_wait_spin(&empty_bar[s], ((it / NS) - 1) & 1);
         const uint32_t sb = smem0 + (uint32_t)s * STAGE_BYTES;
+        const uint32_t live = it < nst ? 0xFFu : 0u;      // a padded stage stores nothing
 #pragma unroll
         for (int i = 0; i < ITEMS; i++) {
-          if (lm[i] == 0u) continue;
           const uint32_t s0 = selector4<NA>(ring[d][i].x), s1 = selector4<NA>(ring[d][i].y),
                          s2 = selector4<NA>(ring[d][i].z), s3 = selector4<NA>(ring[d][i].w);
-          const uint32_t rb = sb + sa[i];
+          const uint32_t rb = sb + sa[i], m = lm[i] & live;
 #pragma unroll
           for (int v = 0; v < 4; v++)
-            if (lm[i] & (1u << v))
-              sts128(rb + v * 128 + __byte_perm(sw_lo[i], 0u, 0x4440 + v), onehot4(s0, 1u << (8 * v), 0u),
-                     onehot4(s1, 1u << (8 * v), 0u), onehot4(s2, 1u << (8 * v), 0u), onehot4(s3, 1u << (8 * v), 0u));
-          if (lm[i] >> 4) {                        // factors with 5-8 levels
+            sts128_if(m & (1u << v), rb + v * 128 + __byte_perm(sw_lo[i], 0u, 0x4440 + v), onehot4(s0, 1u << (8 * v), 0u),
+                      onehot4(s1, 1u << (8 * v), 0u), onehot4(s2, 1u << (8 * v), 0u), onehot4(s3, 1u << (8 * v), 0u));
+          if (WIDE) {                                      // factors with 5-8 levels
 #pragma unroll
             for (int v = 0; v < 4; v++)
-              if (lm[i] & (16u << v))
-                sts128(rb + (v + 4) * 128 + __byte_perm(sw_hi[i], 0u, 0x4440 + v), onehot4(s0, 0u, 1u << (8 * v)),
-                       onehot4(s1, 0u, 1u << (8 * v)), onehot4(s2, 0u, 1u << (8 * v)), onehot4(s3, 0u, 1u << (8 * v)));
+              sts128_if(m & (16u << v), rb + (v + 4) * 128 + __byte_perm(sw_hi[i], 0u, 0x4440 + v),
+                        onehot4(s0, 0u, 1u << (8 * v)), onehot4(s1, 0u, 1u << (8 * v)), onehot4(s2, 0u, 1u << (8 * v)),
+                        onehot4(s3, 0u, 1u << (8 * v)));
           }
         }
         // generic-proxy writes -> visible to the tensor core's async-proxy reads
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
-        if (lane == 0) mbar_arrive(&full_bar[s]);
-        if (it + DEPTH < nst) load(ring[d], st0 + it + DEPTH);
+        asm volatile("{ .reg .pred p; setp.eq.u32 p, %1, 0; @p mbarrier.arrive.shared::cta.b64 _, [%0]; }"
+                     ::"r"(smem_u32(&full_bar[s])), "r"((uint32_t)lane) : "memory");
+        load(ring[d], min(it + DEPTH, nst - 1));          // past the end: the last stage again, never used
       }
     }
-  } else if (lane == 0) {
+  } else {
     // ---------------- MMA issuer ----------------
+    // The whole warp walks the stage loop and one lane issues.
     // instruction descriptor: D = s32 (c_format 2), A and B unsigned 8-bit, both K-major, N >> 3, M >> 4
     const uint32_t idesc = (2u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(PAIR_BM >> 4) << 24);
     const uint32_t a_shift = a_in_b ? (uint32_t)(A_BYTES + (a0 - b0) * 128) : 0u;
-    for (int it = 0; it < nst; it++) {
-      const int s = it % PAIR_STAGES;
-      mbar_wait(&full_bar[s], (it / PAIR_STAGES) & 1);
+    const uint32_t smem0 = smem_u32(smem);
+    for (int it = 0; it < npad; it++) {
+      const int s = it & (NS - 1);
+      mbar_wait_spin(&full_bar[s], (it / NS) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t sb = smem_u32(smem + (size_t)s * STAGE_BYTES);
-      const uint64_t ad = make_desc_sw128(sb + a_shift), bd = make_desc_sw128(sb + A_BYTES);
+      if (lane == 0) {
+        const uint32_t sb = smem0 + (uint32_t)s * STAGE_BYTES;
+        const uint64_t ad = make_desc_sw128(sb + a_shift), bd = make_desc_sw128(sb + A_BYTES);
+        if (it < nst) {
 #pragma unroll
-      for (int k = 0; k < PAIR_KROWS / 32; k++)      // +32 bytes of K per step: +2 in the (address >> 4) field
-        umma_i8(tmem, ad + 2 * k, bd + 2 * k, idesc, (it | k) != 0);
-      umma_commit(&empty_bar[s]);
+          for (int k = 0; k < PAIR_KROWS / 32; k++)      // +32 bytes of K per step: +2 in the (address >> 4) field
+            umma_i8(tmem, ad + 2 * k, bd + 2 * k, idesc, (it | k) != 0);
+        }
+        umma_commit(&empty_bar[s]);
+      }
+      __syncwarp();
     }
-    umma_commit(&accum_bar);
+    if (lane == 0) umma_commit(&accum_bar);
+    __syncwarp();
   }
 
   // ---------------- accumulator -> G ----------------
@@ -290,21 +328,21 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
   // a time; the 32 x 32 block is turned through shared memory (the stage buffers are
   // free once the last MMA has committed) so that a warp writes 128 contiguous bytes
   // of a row of G per instruction.
-  if (warp < 8 && nst > 0) {
+  if (warp < 8) {
     mbar_wait(&accum_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const int lg = warp & 3;                          // a warp reads the 32 TMEM lanes of its quarter
-    int *tile = reinterpret_cast<int *>(smem) + warp * (32 * 33);
+    int *tile_s = reinterpret_cast<int *>(smem) + warp * (32 * 33);
     for (int c0 = (warp >> 2) * 32; c0 < BN; c0 += 64) {
       uint32_t v[32];
       tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
 #pragma unroll
-      for (int j = 0; j < 32; j++) tile[lane * 33 + j] = (int)v[j];
+      for (int j = 0; j < 32; j++) tile_s[lane * 33 + j] = (int)v[j];
       __syncwarp();
       int *dst = G + (size_t)(a0 + lg * 32) * ldg + b0 + c0 + lane;
       const int rows = min(32, L - (a0 + lg * 32));
       for (int rr = 0; rr < rows; rr++) {
-        const int val = tile[rr * 33 + lane];
+        const int val = tile_s[rr * 33 + lane];
         if (atomic_out) { if (val) atomicAdd(dst + (size_t)rr * ldg, val); }
         else dst[(size_t)rr * ldg] = val;
       }
@@ -313,7 +351,7 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == PAIR_PRODUCERS / 32) {
+  if (warp == NPW) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(BN));
   }

@@ -119,12 +119,16 @@ class ShardedBackend:
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.gathers = 0
+        self.tests_by_size = {}                 # conditioning-set size -> tests this rank ran
 
     def allsubs_batch(self, x, y, sx, nfixed, test, alpha, minsize, maxsize):
         import numpy as np
         n = len(x)
         b, e = block(n, self.world, self.rank)
+        before = self.backend.counter.value
         mine = self.backend.allsubs_batch(x[b:e], y[b:e], sx[b:e], nfixed[b:e], test, alpha, minsize, maxsize)
+        if minsize == maxsize:
+            self.tests_by_size[minsize] = self.tests_by_size.get(minsize, 0) + self.backend.counter.value - before
         if self.world == 1:
             return mine
         width = 4 + max([len(s) for s in sx] + [0])
