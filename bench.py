@@ -239,7 +239,7 @@ def hbm_class(name, kernel_ms, compulsory_bytes, unit_bytes, units, rows, peak, 
 def config_c_extras(eng, world, rank, device, cpu_cores=0, reps=5, want_hc=True):
     import torch.distributed as dist
     from bnlearn_b200 import callsites as cs
-    from bnlearn_b200.replicate import broadcast_dataset, gather_rows
+    from bnlearn_b200.replicate import broadcast_dataset
     rows, nnodes = 1_000_000, 1000
     peak, _ = hbm_peak()
     if rank == 0:
@@ -309,7 +309,6 @@ def config_c_extras(eng, world, rank, device, cpu_cores=0, reps=5, want_hc=True)
         dist.barrier()
     n, dt, kms, dms, cache = timed(amat, mine, False, lower)
     t0 = time.perf_counter()
-    full = gather_rows(cache[:, mine].T.copy(), nnodes, device) if world == 1 else None
     if world > 1:
         # blocks are uneven (triangular work): gather the whole matrix, each rank's columns filled
         import torch
@@ -329,7 +328,7 @@ def config_c_extras(eng, world, rank, device, cpu_cores=0, reps=5, want_hc=True)
     else:
         wall, kmax, total = tt[0], tt[1], tt[2]
     if rank == 0:
-        full = full + np.tril(full.T, -1) if world > 1 else full + np.tril(full.T, -1)
+        full = full + np.tril(full.T, -1)          # the mirrored half (score equivalence)
         out["first_iteration"] = {"deltas": total, "ms": wall * 1e3, "deltas_per_sec": total / wall,
                                   "count_kernel_ms_max_over_ranks": kmax, "n_gpus": world,
                                   "sharding": "contiguous blocks of target nodes, ~equal pair counts; "
@@ -629,9 +628,9 @@ def main():
             "config": {"workload": workload, "rows": args.rows, "columns": len(names),
                        "tests_per_step": n_units,
                        "l2": "packed data set 370 MB > 126 MB L2, no explicit flush",
-                       "sharding": "strong: the one fixed test list is cut into N contiguous blocks, one per "
-                                   "rank (each on its own replica of the data set); statistics gathered to rank 0 "
-                                   "in index order inside the timed region"}}
+                       "sharding": "strong: the one fixed test list is cut into N contiguous blocks of about "
+                                   "equal estimated cost, one per rank (each on its own replica of the data set); "
+                                   "statistics gathered in index order (one NCCL all-gather) inside the timed region"}}
 
     cores = os.cpu_count() or 1
 
@@ -666,7 +665,7 @@ def main():
     import torch
     import torch.distributed as dist
     from bnlearn_b200 import Engine, csr
-    from bnlearn_b200.replicate import block, gather_rows
+    from bnlearn_b200.replicate import Gatherer, cost_blocks
 
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
@@ -686,9 +685,13 @@ def main():
     np.copyto(host, codes, casting="unsafe")
     cols32 = [host[i] for i in range(ncol)]
 
-    # strong scaling: rank r evaluates units [b, e) of the one list.
-    b, e = block(n_units, world, rank)
+    # strong scaling: rank r evaluates units [b, e) of the one list. Blocks are cut by
+    # estimated cost: the marginal tests come out of one tensor-core contraction and
+    # cost ~1/8 of a conditional test each.
+    bounds = cost_blocks([1.0 if u[2] else 0.125 for u in units], world)
+    b, e = bounds[rank], bounds[rank + 1]
     my_units = units[b:e]
+    gather = Gatherer(bounds, 3, device)
     xs = np.array([u[0] for u in my_units], dtype=np.int32)
     ys = np.array([u[1] for u in my_units], dtype=np.int32)
     z = csr([u[2] for u in my_units])
@@ -697,9 +700,7 @@ def main():
 
     def step(ds):
         st, df, pv = ds.ci_discrete("mi", xs, ys, z)
-        if world == 1:
-            return np.stack([st, df, pv], axis=1)
-        return gather_rows(np.stack([st, df, pv], axis=1), n_units, device)
+        return gather(np.stack([st, df, pv], axis=1))
 
     # clocks are sampled from the warm-up to the end of the end-to-end loop (the
     # timed steps alone can be shorter than one nvidia-smi sampling period).

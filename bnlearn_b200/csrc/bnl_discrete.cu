@@ -714,7 +714,7 @@ int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, 
   if (cells > kMaxBatchCells) return BNL_OK;
   if (knob < 2) {
     double tensor_s, atomic_s;
-    bnl_pairs_cost(dev, ds, used, n, lev_by_slot, &tensor_s, &atomic_s);
+    bnl_pairs_cost(dev, ds, used, n, lev_by_slot, &tensor_s, &atomic_s, h_cc);
     if (!(tensor_s < 0.8 * atomic_s)) return BNL_OK;
   }
   *handled = true;
@@ -738,7 +738,7 @@ int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, 
   BNL_CUDA(ctx, cudaGetLastError());
   tm.launches++;
   BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
-  if ((rc = bnl_pairs_run(ctx, dev, ds, dd, used, nullptr, n, lev_by_slot, &tm))) return rc;
+  if ((rc = bnl_pairs_run(ctx, dev, ds, dd, used, nullptr, n, lev_by_slot, &tm, h_cc))) return rc;
   BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
   if (kind == 2) {
     BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));

@@ -206,13 +206,15 @@ struct BnlTiming { float total = 0.f, count = 0.f, epi = 0.f; int launches = 0; 
 // contraction, run it and fill their tables. picked[] lists positions in h_units.
 bool bnl_pairs_eligible(const BnlUnit &u, const std::vector<int> &lev_by_slot);
 // used[slot]: the packed columns the units touch; picked: positions of the pair units in
-// the batch's unit array (null: all nunits units, in order).
+// the batch's unit array (null: all nunits units, in order); cc: those units' column pairs
+// (host copy), to leave out output tiles that none of them needs.
 int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlDeviceData &dd,
                   const std::vector<char> &used, const std::vector<int> *picked, int nunits,
-                  const std::vector<int> &lev_by_slot, BnlTiming *tm);
+                  const std::vector<int> &lev_by_slot, BnlTiming *tm, const int2 *cc = nullptr);
 // estimated seconds of the contraction for these units, and of counting them one by one
 void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<char> &used, long long nunits,
-                    const std::vector<int> &lev_by_slot, double *tensor_s, double *atomic_s);
+                    const std::vector<int> &lev_by_slot, double *tensor_s, double *atomic_s,
+                    const int2 *cc = nullptr);
 
 // split [0, n) into ndev contiguous blocks.
 static inline void bnl_block(int n, int ndev, int d, int *begin, int *end) {

@@ -26,8 +26,12 @@ struct Plan {
   int total_stages = 0, splits = 1, per_split = 0;
 };
 
+// cc (optional): the batch's units as {first column, second column or -1} packed slots.
+// When they are far from all pairs of the selected columns -- a rank's share of a
+// sharded first iteration: the targets of its block against every other node -- only
+// the output tiles that hold one of their tables are computed.
 void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<char> &used,
-               const std::vector<int> &lev_by_slot, Plan *p) {
+               const std::vector<int> &lev_by_slot, Plan *p, const int2 *cc = nullptr, int ncc = 0) {
   for (int s = 0; s < ds.nd; s++)
     if (used[s]) {
       p->slots.push_back(s);
@@ -37,9 +41,24 @@ void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<cha
   p->ldg = (p->L + 255) & ~255;
   p->bn = p->L <= 128 ? 128 : 256;
   const int nbm = (p->L + PAIR_BM - 1) / PAIR_BM, nbn = (p->L + p->bn - 1) / p->bn;
+  std::vector<char> need;
+  const double all_pairs = 0.5 * (double)p->slots.size() * ((double)p->slots.size() - 1.0);
+  if (cc && (double)ncc < 0.9 * all_pairs && nbm * nbn > 1) {
+    need.assign((size_t)nbm * nbn, 0);
+    std::vector<int> first_by_slot(ds.nd, 0);
+    for (size_t c = 0; c < p->slots.size(); c++) first_by_slot[p->slots[c]] = p->first[c];
+    for (int u = 0; u < ncc; u++) {
+      int s0 = cc[u].x, s1 = cc[u].y < 0 ? cc[u].x : cc[u].y;
+      if (first_by_slot[s0] > first_by_slot[s1]) std::swap(s0, s1);     // smaller indicator first: G's upper triangle
+      const int a0 = first_by_slot[s0], a1 = a0 + lev_by_slot[s0] - 1, b0 = first_by_slot[s1], b1 = b0 + lev_by_slot[s1] - 1;
+      for (int bm = a0 / PAIR_BM; bm <= a1 / PAIR_BM; bm++)
+        for (int bn = b0 / p->bn; bn <= b1 / p->bn; bn++) need[(size_t)bm * nbn + bn] = 1;
+    }
+  }
   for (int bm = 0; bm < nbm; bm++)
     for (int bn = 0; bn < nbn; bn++)
-      if (bn * p->bn + p->bn > bm * PAIR_BM) p->tiles.push_back(make_int2(bm, bn));   // reaches the upper triangle
+      if (bn * p->bn + p->bn > bm * PAIR_BM && (need.empty() || need[(size_t)bm * nbn + bn]))
+        p->tiles.push_back(make_int2(bm, bn));                                       // reaches the upper triangle
   p->total_stages = (int)((ds.nobs + PAIR_KROWS - 1) / PAIR_KROWS);
   // row splits: whole waves of CTAs (one per SM), each long enough to pay for its
   // prologue and for draining the accumulator (~20 stages' worth)
@@ -66,9 +85,9 @@ bool bnl_pairs_eligible(const BnlUnit &u, const std::vector<int> &lev_by_slot) {
 }
 
 void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<char> &used, long long nunits,
-                    const std::vector<int> &lev_by_slot, double *tensor_s, double *atomic_s) {
+                    const std::vector<int> &lev_by_slot, double *tensor_s, double *atomic_s, const int2 *cc) {
   Plan p;
-  make_plan(dev, ds, used, lev_by_slot, &p);
+  make_plan(dev, ds, used, lev_by_slot, &p, cc, cc ? (int)nunits : 0);
   const double macs = (double)p.tiles.size() * PAIR_BM * p.bn * (double)ds.nobs;
   const double hbm = (double)p.slots.size() * (double)ds.nobs / 5e12;
   *tensor_s = std::max(macs / kPairMacRate, hbm) + 40e-6;
@@ -77,9 +96,9 @@ void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const std::vecto
 
 int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlDeviceData &dd,
                   const std::vector<char> &used, const std::vector<int> *picked, int nunits,
-                  const std::vector<int> &lev_by_slot, BnlTiming *tm) {
+                  const std::vector<int> &lev_by_slot, BnlTiming *tm, const int2 *cc) {
   Plan p;
-  make_plan(dev, ds, used, lev_by_slot, &p);
+  make_plan(dev, ds, used, lev_by_slot, &p, cc, cc ? nunits : 0);
   const int nc = (int)p.slots.size(), nt = (int)p.tiles.size(), np = picked ? (int)picked->size() : 0;
   // one int block: cols (int4 per column) | ind2col [ldg] | slot_first [nd] | tiles (int2) | ids [np]
   const size_t n_cols = (size_t)nc * 4, n_ind = (size_t)p.ldg, n_sf = ((size_t)ds.nd + 1) & ~(size_t)1, n_tiles = (size_t)nt * 2;

@@ -62,6 +62,9 @@ class Engine:
     def __init__(self, devices=None):
         self._lib = _lib.load()
         self._ctx = C.c_void_p()
+        # remembered so that helpers which open more contexts from other host threads
+        # (learners.boot_arc_counts) land on the same GPU: a new thread's current device is 0
+        self.devices = None if devices is None else [int(d) for d in devices]
         if devices is None:
             rc = self._lib.bnl_init(C.byref(self._ctx), None, 0)
         else:

@@ -582,7 +582,7 @@ def boot_arc_counts(engine, columns, nlevels, ids, score, arg=0.0, seed=0, maxp=
         return run(engine, ids)
     from concurrent.futures import ThreadPoolExecutor
     if devices is None:
-        pool_engines, extra = [engine], [Engine() for _ in range(workers - 1)]
+        pool_engines, extra = [engine], [Engine(engine.devices) for _ in range(workers - 1)]
     else:
         pool_engines, extra = [], [Engine([int(devices[w % len(devices)])]) for w in range(workers)]
     pool_engines += extra

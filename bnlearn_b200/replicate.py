@@ -106,6 +106,55 @@ def gather_rows(mine, n, device=None):
     return out
 
 
+def cost_blocks(costs, world):
+    """Contiguous blocks of a unit list with about equal total cost: boundaries
+    bounds[r] .. bounds[r + 1] for rank r (pc.stable's marginal tests come from one
+    tensor-core contraction and cost a fraction of a conditional test, so equal
+    COUNTS would leave the rank holding the conditional tests with most of the work)."""
+    import numpy as np
+    c = np.cumsum(np.asarray(costs, dtype=np.float64))
+    total = float(c[-1]) if len(c) else 0.0
+    bounds = [0]
+    for r in range(1, world):
+        bounds.append(int(np.searchsorted(c, total * r / world, side="left")) if total > 0 else 0)
+    bounds.append(len(c))
+    for r in range(1, len(bounds)):
+        bounds[r] = max(bounds[r], bounds[r - 1])
+    return bounds
+
+
+class Gatherer:
+    """gather_rows with everything allocated once: pinned host buffers, device
+    buffers and ONE all_gather_into_tensor per call (a bench step gathers three
+    doubles per test; fresh tensors and a copy per rank cost more than the tests
+    of a rank's block). bounds[r] .. bounds[r + 1] is rank r's block of rows."""
+
+    def __init__(self, bounds, width, device):
+        self.bounds, self.width, self.device = list(bounds), int(width), device
+        self.world = len(bounds) - 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.per = max(b - a for a, b in zip(bounds[:-1], bounds[1:])) if self.world else 0
+        if self.world > 1:
+            self.h_in = torch.zeros((self.per, width), dtype=torch.float64).pin_memory()
+            self.d_in = torch.zeros((self.per, width), dtype=torch.float64, device=device)
+            self.d_out = torch.zeros((self.world * self.per, width), dtype=torch.float64, device=device)
+            self.h_out = torch.zeros((self.world * self.per, width), dtype=torch.float64).pin_memory()
+
+    def __call__(self, mine):
+        import numpy as np
+        if self.world <= 1:
+            return np.asarray(mine, dtype=np.float64)
+        m = np.asarray(mine, dtype=np.float64).reshape(-1, self.width)
+        self.h_in.numpy()[:m.shape[0]] = m
+        self.d_in.copy_(self.h_in, non_blocking=True)
+        dist.all_gather_into_tensor(self.d_out, self.d_in)
+        self.h_out.copy_(self.d_out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        full = self.h_out.numpy()
+        return np.concatenate([full[r * self.per: r * self.per + self.bounds[r + 1] - self.bounds[r]]
+                               for r in range(self.world)])
+
+
 class ShardedBackend:
     """A learners backend whose batched calls are split over the ranks: the pairs
     of one pc.stable level go to the workers in contiguous blocks, as
@@ -129,8 +178,8 @@ class ShardedBackend:
         mine = self.backend.allsubs_batch(x[b:e], y[b:e], sx[b:e], nfixed[b:e], test, alpha, minsize, maxsize)
         if minsize == maxsize:
             self.tests_by_size[minsize] = self.tests_by_size.get(minsize, 0) + self.backend.counter.value - before
-        if self.world == 1:
-            return mine
+        if self.world == 1:                 # same types as the gathered form (python floats, int lists)
+            return [(float(p), float(a), float(b), None if d is None else [int(v) for v in d]) for p, a, b, d in mine]
         width = 4 + max([len(s) for s in sx] + [0])
         rows = np.zeros((e - b, width))
         for k, (p, pmin, pmax, dsep) in enumerate(mine):
