@@ -398,6 +398,18 @@ def config_d_extras(eng):
         out["level0_" + test] = {"tests": len(xs), "ms": best * 1e3, "tests_per_sec": len(xs) / best,
                                  "kernel_ms": eng.last_call_profile()["count_ms"],
                                  "edges_kept_at_0.05": int((pv < 0.05).sum())}
+    # the same level on the device end to end: pairs enumerated there, p-value matrix (32 MB) and the
+    # surviving pairs back (bnl_ci_gaussian_allpairs); without the matrix only the survivors cross PCIe
+    for want_p in (True, False):
+        best = None
+        for _ in range(3):
+            t0 = time.perf_counter()
+            keep, pm = ds.ci_gaussian_allpairs("cor", 0.05, want_p=want_p)
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        out["level0_cor_allpairs" + ("" if want_p else "_edges_only")] = {
+            "tests": len(xs), "ms": best * 1e3, "tests_per_sec": len(xs) / best,
+            "kernel_ms": eng.last_call_profile()["count_ms"], "edges_kept_at_0.05": int(len(keep))}
     rng = np.random.default_rng(5)
     for k in (1, 3):
         n = 400000

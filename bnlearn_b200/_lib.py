@@ -50,6 +50,8 @@ SIGNATURES = {
     "bnl_ci_discrete_mc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_double, C.c_int, c_int_p,
                                      c_int_p, c_int_p, c_int_p, C.c_void_p, C.c_void_p, c_dbl_p, c_dbl_p,
                                      c_dbl_p]),
+    "bnl_ci_gaussian_allpairs": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p, c_dbl_p,
+                                           c_int_p, c_int_p, C.c_longlong, C.POINTER(C.c_longlong), c_dbl_p]),
     "bnl_score_gaussian": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_int, c_int_p,
                                      c_int_p, c_int_p, c_dbl_p, c_dbl_p]),
     "bnl_gaussian_moments": (C.c_int, [C.c_void_p, C.c_uint64, c_dbl_p, c_dbl_p]),

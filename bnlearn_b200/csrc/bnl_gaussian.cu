@@ -307,6 +307,84 @@ int bnl_ci_gaussian_any(bnl_ctx *ctx, bnl_data data, int test_e, int n, const in
   return run_grequest(ctx, ds, rq);
 }
 
+extern "C" int bnl_ci_gaussian_allpairs(bnl_ctx *ctx, bnl_data data, int test_e, double alpha, int ncols,
+                                        const int *cols, double *pvalue, int *keep_i, int *keep_j, long long cap,
+                                        long long *nkeep, double *test_counter) {
+  if (!ctx) return BNL_EINVAL;
+  auto it = ctx->data.find(data);
+  if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+  BnlDataSet &ds = it->second;
+  if (test_e != BNL_COR && test_e != BNL_ZF && test_e != BNL_MI_G)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "bnl_ci_gaussian_allpairs handles cor, zf and mi-g");
+  if (ncols < 0 || (ncols > 0 && !cols) || cap < 0 || (cap > 0 && (!keep_i || !keep_j)))
+    return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_gaussian_allpairs: bad arguments");
+  if (ds.any_nan)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "bnl_ci_gaussian_allpairs needs complete data (use bnl_ci_gaussian)");
+  if (nkeep) *nkeep = 0;
+  if (ncols < 2) return BNL_OK;
+  BnlDevice &dev = ctx->devs[0];
+  BnlDeviceData &dd = ds.dev[0];
+  BNL_CUDA(ctx, cudaSetDevice(dev.id));
+  const size_t n = (size_t)ncols;
+  int rc;
+  // one int block: slots [n] | rowcount [n] | total (2 ints) | keep_i [cap] | keep_j [cap]; flags and p-values apart
+  const size_t ints = 2 * n + 4 + 2 * (size_t)cap;
+  if ((rc = bnl_reserve_pinned(ctx, &dev.h_gidx, &dev.h_gidx_cap, ints))) return rc;
+  if ((rc = bnl_reserve_device(ctx, &dev.d_gidx, &dev.gidx_cap, ints))) return rc;
+  for (int i = 0; i < ncols; i++) {
+    const int c = cols[i];
+    if (c < 0 || c >= ds.ncols || !ds.is_numeric[c])
+      return bnl_fail(ctx, BNL_EINVAL, "bnl_ci_gaussian_allpairs: column %d is out of range or not numeric", c);
+    dev.h_gidx[i] = ds.slot[c];
+  }
+  unsigned char *d_keep = nullptr;
+  double *d_p = nullptr;
+  const size_t kbytes = n * n, pbytes = pvalue ? n * n * sizeof(double) : 0;
+  if ((rc = bnl_pool_alloc(ctx, dev, (void **)&d_keep, kbytes))) return rc;
+  if (pvalue && (rc = bnl_pool_alloc(ctx, dev, (void **)&d_p, pbytes))) { bnl_pool_free(dev, d_keep, kbytes); return rc; }
+  int *d_slots = dev.d_gidx, *d_cnt = d_slots + n, *d_ki = d_cnt + n + 4, *d_kj = d_ki + cap;
+  long long *d_total = reinterpret_cast<long long *>(d_cnt + n);      // int index 2n: 8-byte aligned
+  auto fail = [&](cudaError_t e, const char *what) {
+    cudaStreamSynchronize(dev.stream);
+    bnl_pool_free(dev, d_keep, kbytes);
+    bnl_pool_free(dev, d_p, pbytes);
+    return bnl_fail(ctx, BNL_ECUDA, "%s failed: %s", what, cudaGetErrorString(e));
+  };
+  cudaError_t e;
+  cudaEventRecord(dev.ev0, dev.stream);
+  if ((e = cudaMemcpyAsync(d_slots, dev.h_gidx, n * sizeof(int), cudaMemcpyHostToDevice, dev.stream)) != cudaSuccess)
+    return fail(e, "upload");
+  cudaEventRecord(dev.evc0, dev.stream);
+  const long long nobs = ds.gauss_nobs > 0 ? ds.gauss_nobs : ds.nobs;
+  gauss_allpairs_kernel<<<ncols, 256, 0, dev.stream>>>(dd.cov, ds.nc, d_slots, ncols, nobs, test_e, alpha, d_p, d_keep,
+                                                       d_cnt);
+  gauss_allpairs_compact_kernel<<<(ncols + 3) / 4, 128, 0, dev.stream>>>(d_keep, d_cnt, ncols, cap, d_ki, d_kj, d_total);
+  if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "launch");
+  cudaEventRecord(dev.evc1, dev.stream);
+  long long total = 0;
+  if ((e = cudaMemcpyAsync(&total, d_total, sizeof(long long), cudaMemcpyDeviceToHost, dev.stream)) != cudaSuccess)
+    return fail(e, "download");
+  if ((e = cudaStreamSynchronize(dev.stream)) != cudaSuccess) return fail(e, "kernels");
+  const long long got = std::min(total, cap);
+  if (got > 0) {
+    cudaMemcpyAsync(keep_i, d_ki, (size_t)got * sizeof(int), cudaMemcpyDeviceToHost, dev.stream);
+    cudaMemcpyAsync(keep_j, d_kj, (size_t)got * sizeof(int), cudaMemcpyDeviceToHost, dev.stream);
+  }
+  if (pvalue) cudaMemcpyAsync(pvalue, d_p, pbytes, cudaMemcpyDeviceToHost, dev.stream);
+  cudaEventRecord(dev.ev1, dev.stream);
+  if ((e = cudaStreamSynchronize(dev.stream)) != cudaSuccess) return fail(e, "download");
+  bnl_pool_free(dev, d_keep, kbytes);
+  bnl_pool_free(dev, d_p, pbytes);
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, dev.ev0, dev.ev1) == cudaSuccess) ctx->last_ms = ms;
+  if (cudaEventElapsedTime(&ms, dev.evc0, dev.evc1) == cudaSuccess) ctx->last_count_ms = ms;
+  ctx->last_epi_ms = 0.0;
+  ctx->last_launches = 2;
+  if (nkeep) *nkeep = total;
+  if (test_counter) *test_counter += (double)ncols * (double)(ncols - 1) / 2.0;
+  return BNL_OK;
+}
+
 extern "C" int bnl_score_gaussian(bnl_ctx *ctx, bnl_data data, int score_e, double k, int n,
                                   const int *target, const int *pa_off, const int *pa_idx,
                                   double *score, double *nparams) {

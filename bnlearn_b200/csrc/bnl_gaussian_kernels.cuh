@@ -356,6 +356,72 @@ __global__ void gauss_ci_kernel(const int *__restrict__ ux, const int *__restric
   o[0] = stat; o[1] = df; o[2] = pv; o[3] = clamped;
 }
 
+// ---------------------------------------------------------------------------
+// Every pair of a column list tested marginally: level 0 of pc.stable on numeric
+// data (R/pcalgo.R:8-28 -> ut_gaustests_complete, src/tests/patterns/utest.c:65-129).
+// Nothing per pair crosses PCIe in either direction: the pairs are enumerated here,
+// the arithmetic is gauss_ci_kernel's marginal branch to the letter (same p-values),
+// and what goes back is the p-value matrix (optional) and the pairs that stay
+// adjacent (p <= alpha), compacted in row-major order of the upper triangle.
+// One CTA per first column i; keep[i * n + j] flags the surviving j > i.
+__global__ void __launch_bounds__(256)
+gauss_allpairs_kernel(const double *__restrict__ cov, int p, const int *__restrict__ slots, int n,
+                      long long nobs, int test, double alpha, double *__restrict__ pmat,
+                      unsigned char *__restrict__ keep, int *__restrict__ rowcount) {
+  __shared__ int s_cnt;
+  const int i = blockIdx.x;
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  const double tol = bnl::kSqrtEps;
+  const double df = (test == BNL_COR) ? (double)(nobs - 2) : (test == BNL_ZF) ? (double)(nobs - 3) : 1.0;
+  const int si = slots[i];
+  const double sxx = cov[(size_t)si + (size_t)si * p] * (double)(nobs - 1);
+  int mine = 0;
+  for (int j = i + 1 + threadIdx.x; j < n; j += blockDim.x) {
+    const int sj = slots[j];
+    double pv = 1.0;
+    if (df >= 1.0) {
+      const double syy = cov[(size_t)sj + (size_t)sj * p] * (double)(nobs - 1);
+      const double sxy = cov[(size_t)si + (size_t)sj * p] * (double)(nobs - 1);
+      double r = (sxx < tol || syy < tol) ? 0.0 : sxy / sqrt(sxx * syy);
+      if (r > 1.0) r = 1.0; else if (r < -1.0) r = -1.0;
+      if (test == BNL_COR) pv = bnl::pt_two_sided(r * sqrt(df) / sqrt(1.0 - r * r), df);
+      else if (test == BNL_ZF) pv = bnl::pnorm_two_sided(log((1.0 + r) / (1.0 - r)) / 2.0 * sqrt(df));
+      else pv = bnl::pchisq_upper(2.0 * (double)nobs * (-0.5 * log(1.0 - r * r)), df);
+    }
+    if (pmat) { pmat[(size_t)i * n + j] = pv; pmat[(size_t)j * n + i] = pv; }
+    const bool k = pv <= alpha;
+    keep[(size_t)i * n + j] = k;
+    mine += k;
+  }
+  if (pmat && threadIdx.x == 0) pmat[(size_t)i * n + i] = 0.0;
+  if (mine) atomicAdd(&s_cnt, mine);
+  __syncthreads();
+  if (threadIdx.x == 0) rowcount[i] = s_cnt;
+}
+
+// one warp per row: position of its first survivor = sum of the earlier rows' counts
+__global__ void __launch_bounds__(128)
+gauss_allpairs_compact_kernel(const unsigned char *__restrict__ keep, const int *__restrict__ rowcount, int n,
+                              long long cap, int *__restrict__ out_i, int *__restrict__ out_j,
+                              long long *__restrict__ total) {
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (i >= n) return;
+  long long off = 0;
+  for (int r = lane; r < i; r += 32) off += rowcount[r];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) off += __shfl_xor_sync(0xffffffffu, off, o);
+  if (i == n - 1 && lane == 0) *total = off + rowcount[i];
+  for (int j0 = i + 1; j0 < n; j0 += 32) {
+    const int j = j0 + lane;
+    const bool k = j < n && keep[(size_t)i * n + j];
+    const unsigned m = __ballot_sync(0xffffffffu, k);
+    const long long pos = off + __popc(m & ((1u << lane) - 1u));
+    if (k && pos < cap) { out_i[pos] = i; out_j[pos] = j; }
+    off += __popc(m);
+  }
+}
+
 // Gaussian node score from the moments. Unit u: target[u] and the CSR parent list.
 // S(i, j) below is the centred cross-product (n - 1) * cov of the unit's columns.
 __global__ void gauss_score_kernel(const int *__restrict__ target, const int *__restrict__ poff,

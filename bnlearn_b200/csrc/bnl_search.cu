@@ -409,6 +409,14 @@ extern "C" int bnl_pc_stable(bnl_ctx *ctx, bnl_data data, int test_e, double alp
   std::vector<int> max_adj((size_t)np, n - 1);
   std::vector<std::vector<int>> sepset((size_t)np);
   if (max_sx < 0 || max_sx > n - 2) max_sx = n - 2;
+  bool gaussian_level0 = test_e == BNL_COR || test_e == BNL_ZF || test_e == BNL_MI_G;
+  {
+    auto it = ctx->data.find(data);
+    if (it == ctx->data.end()) return bnl_fail(ctx, BNL_EINVAL, "unknown data handle");
+    const BnlDataSet &dsr = it->second;
+    gaussian_level0 = gaussian_level0 && !dsr.any_nan && n <= dsr.ncols;
+    for (int c = 0; c < n && gaussian_level0; c++) gaussian_level0 = dsr.is_numeric[c] != 0;
+  }
 
   for (int level = 0; level <= max_sx; level++) {
     // adjacency lists in the order of R/pcalgo.R:88-91: rows where the node is the
@@ -431,6 +439,24 @@ extern "C" int bnl_pc_stable(bnl_ctx *ctx, bnl_data data, int test_e, double alp
     auto run = [&](const std::vector<long long> &list, bool swap, std::vector<char> &separated) -> int {
       const int m = (int)list.size();
       if (m == 0) return BNL_OK;
+      if (level == 0 && gaussian_level0 && (long long)m == np) {
+        // every pair marginally on complete numeric data: pairs enumerated and tested on the
+        // device, only the p-value matrix comes back (bnl_ci_gaussian_allpairs). allsubs_test
+        // counts such a test twice (rinterface/allsubs.test.c:23-30 on top of indep_test's own).
+        std::vector<double> pm((size_t)n * n);
+        std::vector<int> cols(n);
+        for (int i = 0; i < n; i++) cols[i] = i;
+        long long nk = 0;
+        int rc = bnl_ci_gaussian_allpairs(ctx, data, test_e, alpha, n, cols.data(), pm.data(), nullptr, nullptr, 0, &nk,
+                                          nullptr);
+        if (rc) return rc;
+        for (long long k : list) {
+          const double pv = pm[(size_t)pi[k] * n + pj[k]];
+          if (pv > alpha) { pval[k] = pv; has_p[k] = 1; sep[k] = 1; max_adj[k] = 0; separated[k] = 1; sepset[k].clear(); }
+        }
+        if (test_counter) *test_counter += 2.0 * (double)m;
+        return BNL_OK;
+      }
       std::vector<int> xs(m), ys(m), off(m + 1, 0), sx, nfix(m, 0), doff(m + 1, 0), nds(m, -1);
       for (int q = 0; q < m; q++) {
         const long long k = list[q];

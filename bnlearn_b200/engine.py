@@ -297,6 +297,27 @@ class DataSet:
                                         _ip(zi), _dp(st), _dp(df), _dp(pv)))
         return st[:n], df[:n], pv[:n]
 
+    def ci_gaussian_allpairs(self, test, alpha, cols=None, want_p=True, counter=None):
+        """bnl_ci_gaussian_allpairs: every pair of `cols` (default: all numeric columns)
+        tested marginally on the device. Returns (keep [m, 2] positions in cols of the
+        pairs with p <= alpha, in row-major order; p-value matrix or None)."""
+        e = self.engine
+        if cols is None:
+            cols = [i for i, v in enumerate(self.nlevels) if v <= 0]
+        c = np.ascontiguousarray(cols, dtype=np.int32)
+        n = len(c)
+        pm = np.zeros((n, n)) if want_p else None
+        cap = max(n * (n - 1) // 2, 1)
+        ki, kj = np.zeros(cap, dtype=np.int32), np.zeros(cap, dtype=np.int32)
+        nk = C.c_longlong(0)
+        cnt = C.c_double(0.0)
+        e._check(e._lib.bnl_ci_gaussian_allpairs(e._ctx, self.handle, TESTS[test], float(alpha), n, _ip(c),
+                                                 None if pm is None else _dp(pm), _ip(ki), _ip(kj), cap,
+                                                 C.byref(nk), C.byref(cnt)))
+        if counter is not None:
+            counter.add(cnt.value)
+        return np.stack([ki[:nk.value], kj[:nk.value]], axis=1), pm
+
     def score_gaussian(self, score, target, parents, k=0.0):
         e = self.engine
         t = np.ascontiguousarray(target, dtype=np.int32)

@@ -271,6 +271,21 @@ int bnl_ci_gaussian(bnl_ctx *ctx, bnl_data data, int test_e, int n, const int *x
                     const int *y, const int *z_off, const int *z_idx,
                     double *stat, double *df, double *pvalue);
 
+/* Every pair i < j of the listed numeric columns tested marginally (cor, zf, mi-g):
+ * what level 0 of pc.stable asks for, one .Call per pair in the reference
+ * (pc.stable.backend, R/pcalgo.R:8-28 -> allsubs_test -> ut_gaustests_complete,
+ * src/tests/patterns/utest.c:65-129). No index arrays go up and no per-pair
+ * triples come down: pvalue (may be NULL) receives the ncols x ncols symmetric
+ * matrix of p-values (row-major, diagonal 0), and the pairs with p <= alpha -- the
+ * arcs that stay in the skeleton -- are written to keep_i / keep_j in row-major
+ * order of the upper triangle (positions in cols[]); *nkeep is their number, of
+ * which at most cap are written (call again with larger arrays if it exceeds cap).
+ * Same p-values as bnl_ci_gaussian on the same pairs. Complete data only.
+ * test_counter += ncols (ncols - 1) / 2. */
+int bnl_ci_gaussian_allpairs(bnl_ctx *ctx, bnl_data data, int test_e, double alpha, int ncols,
+                             const int *cols, double *pvalue, int *keep_i, int *keep_j, long long cap,
+                             long long *nkeep, double *test_counter);
+
 /* Gaussian node scores (loglik-g, aic-g, bic-g) from the same matrix. Replaces
  * loglik_gnode (src/scores/gaussian.loglikelihood.c:85-114) over c_ols
  * (src/math/least.squares.c:866-932). */

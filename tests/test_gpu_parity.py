@@ -1046,3 +1046,29 @@ def test_all_pairs_tensor_core_tables(engine, monkeypatch, ncols, nobs, maxlev):
     for a, b in zip(got, want):
         assert np.array_equal(a, b)
     d.release()
+
+
+def test_gaussian_allpairs_matches_per_pair_tests(engine):
+    """bnl_ci_gaussian_allpairs (level 0 of pc.stable on numeric data in one call, pairs
+    enumerated and filtered on the device) against bnl_ci_gaussian on the same pairs:
+    identical p-values, survivors in row-major order, test counter n (n - 1) / 2."""
+    from bnlearn_b200.callsites import TestCounter
+    rng = np.random.default_rng(12)
+    n, p = 3001, 67
+    base = rng.normal(size=(n, 6))
+    cols = [np.ascontiguousarray(base[:, i % 6] * (0.05 * (i % 5)) + rng.normal(size=n)) for i in range(p)]
+    cols[5] = np.full(n, 1.25)                    # a constant column: r = 0 by c_fast_cor's guard
+    d = engine.register(cols)
+    iu = np.triu_indices(p, 1)
+    for test in ("cor", "zf", "mi-g"):
+        st, df, pv = d.ci_gaussian(test, iu[0].astype(np.int32), iu[1].astype(np.int32), [[]] * len(iu[0]))
+        counter = TestCounter()
+        keep, pm = d.ci_gaussian_allpairs(test, 0.05, counter=counter)
+        assert counter.value == p * (p - 1) / 2
+        assert np.array_equal(pm[iu], pv) and np.array_equal(pm, pm.T)
+        want = [(int(i), int(j)) for i, j, q in zip(iu[0], iu[1], pv) if q <= 0.05]
+        assert [tuple(r) for r in keep.tolist()] == want
+        sub = [3, 10, 11, 40, 66]
+        keep2, pm2 = d.ci_gaussian_allpairs(test, 1.0, cols=sub)
+        assert len(keep2) == 10 and np.array_equal(pm2, pm[np.ix_(sub, sub)])
+    d.release()
