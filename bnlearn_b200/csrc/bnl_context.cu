@@ -416,10 +416,24 @@ static int upload_factors_hybrid(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, Bn
   std::vector<std::thread> workers;
   for (int t = 0; t < nthreads; t++) workers.emplace_back(packer);
 
-  // raw route, on the caller's thread.
+  // raw route, on the caller's thread -- for sources in PINNED memory only. From pageable
+  // memory (what R hands over) a 40 MB column crawls through the driver's bounce buffer at
+  // 8-10 GB/s and holds the copy engine meanwhile (config B: 48 ms per registration, against
+  // 16 ms from pinned memory); there the caller's thread packs like the others.
+  bool raw_ok = true;
+  {
+    cudaPointerAttributes at;
+    const void *probe = col[dcols[nd - 1]];
+    raw_ok = cudaPointerGetAttributes(&at, probe) == cudaSuccess &&
+             (at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged);
+    cudaGetLastError();                       // an unregistered pointer may leave a sticky-looking error code behind
+    if (const char *v = getenv("BNL_RAW_ROUTE")) if (*v) raw_ok = atoi(v) != 0;
+    if (nthreads == 0) raw_ok = true;         // nobody else would move the data
+  }
+  if (!raw_ok) packer();
   int fed = 0, c;
   cudaError_t ge = cudaSuccess;
-  while (ge == cudaSuccess && !failed.load() && (c = claim_raw()) >= 0) {
+  while (raw_ok && ge == cudaSuccess && !failed.load() && (c = claim_raw()) >= 0) {
     const int k = fed & 1;
     if (fed >= 2) ge = cudaEventSynchronize(d0.ev_stage[k]);
     int *st = d0.stage + (size_t)k * stage_ints;

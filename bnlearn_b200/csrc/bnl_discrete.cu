@@ -23,6 +23,9 @@ const long long kKnobL2MB = env_ll("BNL_L2_MB", 192);
 const int kKnobMidThreads = (int)env_ll("BNL_MID_THREADS", 1024);
 const long long kKnobGroup = env_ll("BNL_GROUP", 1);
 const long long kKnobGroupMinCols = env_ll("BNL_GROUP_MINCOLS", 3);
+// conditional tests that share (y, x[, z1]) and differ in the last conditioning column: 0 off,
+// 1-3: runs whose tables fit 16 / 32 / 64 KiB of lane counters per unit
+const long long kKnobTestGroup = env_ll("BNL_TEST_GROUP", 0);
 const long long kKnobGroupWaves = env_ll("BNL_GROUP_WAVES", 0);   // 0: pick row chunks by the cost model
 const long long kKnobGroupUnits = env_ll("BNL_GROUP_UNITS", BNL_GROUP_MAX);
 // DRAM -> L2 prefetch of the candidates' own columns, in thread-passes ahead (0: off). Two passes
@@ -393,6 +396,42 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           }
       }
     }
+    // Conditional TESTS of a pc.stable level arrive in the same shape: the tests of one edge
+    // (x, y) against each neighbour z -- or against (z1, z) for each z -- share every column but
+    // the last (ct_discrete forms the configuration of the shared part once for all of them,
+    // src/tests/patterns/ctest.c:11-55). Runs are short (2-5 units), so one run = one tile of
+    // count_group_kernel; three launches by table size (16, 32, 64 KiB of lane counters per unit).
+    const int kTestClasses = 3;
+    const int tg_stride[kTestClasses] = {16384, 32768, 65536};
+    std::vector<int2> ttiles[kTestClasses];
+    std::vector<int> torder[kTestClasses];
+    if (kKnobTestGroup && rq.kind == 0 && ds.nobs >= 65536 &&
+        (unsigned long long)ds.stride_u8 * (unsigned long long)ds.nd < (1ull << 35)) {
+      auto same_tbase = [&](const BnlUnit &a, const BnlUnit &b) {
+        if (a.ncols != b.ncols || a.ncols < 3 || a.has_na || b.has_na || a.pad || b.pad) return false;
+        for (int k = 0; k + 1 < a.ncols; k++)
+          if (a.col[k] != b.col[k] || a.mul[k] != b.mul[k]) return false;
+        return a.mul[a.ncols - 1] == b.mul[b.ncols - 1];
+      };
+      int i = 0;
+      while (i < cnt) {
+        int j = i + 1;
+        if (!grouped[i])
+          while (j < cnt && j - i < BNL_GROUP_MAX && !grouped[j] && same_tbase(dev.h_units[i], dev.h_units[j])) j++;
+        if (j - i >= 2) {
+          int cmaxr = 0;
+          for (int u = i; u < j; u++) cmaxr = std::max(cmaxr, dev.h_units[u].cells);
+          int k = 0;
+          while (k < kTestClasses && cmaxr * 256 > tg_stride[k]) k++;
+          // the run's tables must fit one SM next to the kernel's own ~1 KiB
+          if (k < kTestClasses && k < kKnobTestGroup && (j - i) * tg_stride[k] <= group_smem) {
+            ttiles[k].push_back(make_int2((int)torder[k].size(), j - i));
+            for (int u = i; u < j; u++) { torder[k].push_back(u); grouped[u] = 4; }
+          }
+        }
+        i = j;
+      }
+    }
     std::vector<int> cls[4];
     int cmax[4] = {0, 0, 0, 0};
     for (int i = 0; i < cnt; i++) {
@@ -420,13 +459,15 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     }
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_order, &dev.h_order_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
-    int n_ungrouped = 0;
+    int n_ungrouped = 0, n_before_tests = 0;
     {
       int o = 0;
       for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
       n_ungrouped = o;
       for (int i : gorder) dev.h_order[o++] = i;       // group members follow, in tile order
       for (int k = 0; k < kBasedClasses; k++) for (int i : bcls[k]) dev.h_order[o++] = i;   // then the base-column classes
+      n_before_tests = o;
+      for (int k = 0; k < kTestClasses; k++) for (int i : torder[k]) dev.h_order[o++] = i;  // then the runs of tests
     }
     if (!bruns.empty()) {
       if ((rc = bnl_reserve_pinned(ctx, &dev.h_runfirst, &dev.h_runfirst_cap, bruns.size()))) return rc;
@@ -436,6 +477,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     }
     const size_t ngtiles = tiles.size();
     for (int k = 0; k < kBasedClasses; k++) tiles.insert(tiles.end(), btiles[k].begin(), btiles[k].end());
+    const size_t n_tiles_before_tests = tiles.size();
+    for (int k = 0; k < kTestClasses; k++) tiles.insert(tiles.end(), ttiles[k].begin(), ttiles[k].end());
     if (!tiles.empty()) {
       if ((rc = bnl_reserve_pinned(ctx, &dev.h_tiles, &dev.h_tiles_cap, tiles.size()))) return rc;
       if ((rc = bnl_reserve_device(ctx, &dev.d_tiles, &dev.tiles_cap, tiles.size()))) return rc;
@@ -547,6 +590,31 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
 #undef BNL_GROUP_LAUNCH
       BNL_CUDA(ctx, cudaGetLastError());
       tm->launches++;
+    }
+    if (groups > 0) {
+      int obase = n_before_tests;
+      size_t tbase = n_tiles_before_tests;
+      for (int k = 0; k < kTestClasses; k++) {
+        if (ttiles[k].empty()) continue;
+        const long long nt = (long long)ttiles[k].size();
+        int smem = 0;
+        for (auto &t : ttiles[k]) smem = std::max(smem, t.y * tg_stride[k]);
+        const long long want = model_chunks(nt, (double)torder[k].size() / (double)nt, groups / (32 * 512), nullptr);
+        const int ch = (int)std::max(1ll, std::min(want, std::max(1ll, groups / (32 * 512))));
+        const unsigned ggrid = (unsigned)nt * ch;
+#define BNL_TGROUP_LAUNCH(TS)                                                                           \
+        count_group_kernel<512, TS><<<ggrid, 512, (size_t)smem, dev.stream>>>(                            \
+            dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + obase, dev.d_tiles + tbase, dev.d_tables, \
+            (int)nt, ch, tg_stride[k], kKnobGroupPrefetch)
+        if (k == 0) BNL_TGROUP_LAUNCH(16384);
+        else if (k == 1) BNL_TGROUP_LAUNCH(32768);
+        else BNL_TGROUP_LAUNCH(0);
+#undef BNL_TGROUP_LAUNCH
+        BNL_CUDA(ctx, cudaGetLastError());
+        tm->launches++;
+        obase += (int)torder[k].size();
+        tbase += ttiles[k].size();
+      }
     }
     if (groups > 0) {
       int base = 0;
