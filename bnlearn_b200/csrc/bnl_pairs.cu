@@ -21,6 +21,7 @@ const double kAtomicRate = 4.2e12;        // row updates per second of the per-u
 struct Plan {
   std::vector<int> slots;                 // selected packed columns, ascending
   std::vector<int> first;                 // first indicator of each
+  std::vector<int> eff;                   // indicators of each: its levels, minus the last one when it holds no NA
   int L = 0, ldg = 0, bn = 256;
   std::vector<int2> tiles;
   int total_stages = 0, splits = 1, per_split = 0;
@@ -32,11 +33,17 @@ struct Plan {
 // the output tiles that hold one of their tables are computed.
 void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<char> &used,
                const std::vector<int> &lev_by_slot, Plan *p, const int2 *cc = nullptr, int ncc = 0) {
+  // A column without NA needs no indicator for its LAST level: the rows that are in none of the
+  // others are in it, so pair_extract_kernel gets those cells from the margins (exact: integers).
+  // A three-level factor costs two rows of H instead of three -- 1000 factors of 2-4 levels: L from
+  // 3000 to 2000, 156 output tiles to 72.
   for (int s = 0; s < ds.nd; s++)
     if (used[s]) {
+      const bool na = ds.slot_has_na.empty() || ds.slot_has_na[s];
       p->slots.push_back(s);
       p->first.push_back(p->L);
-      p->L += lev_by_slot[s];
+      p->eff.push_back(lev_by_slot[s] - (na ? 0 : 1));
+      p->L += p->eff.back();
     }
   p->ldg = (p->L + 255) & ~255;
   p->bn = p->L <= 128 ? 128 : 256;
@@ -45,13 +52,18 @@ void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<cha
   const double all_pairs = 0.5 * (double)p->slots.size() * ((double)p->slots.size() - 1.0);
   if (cc && (double)ncc < 0.9 * all_pairs && nbm * nbn > 1) {
     need.assign((size_t)nbm * nbn, 0);
-    std::vector<int> first_by_slot(ds.nd, 0);
-    for (size_t c = 0; c < p->slots.size(); c++) first_by_slot[p->slots[c]] = p->first[c];
+    std::vector<int> first_by_slot(ds.nd, 0), eff_by_slot(ds.nd, 1);
+    for (size_t c = 0; c < p->slots.size(); c++) { first_by_slot[p->slots[c]] = p->first[c]; eff_by_slot[p->slots[c]] = p->eff[c]; }
     for (int u = 0; u < ncc; u++) {
       int s0 = cc[u].x, s1 = cc[u].y < 0 ? cc[u].x : cc[u].y;
       if (first_by_slot[s0] > first_by_slot[s1]) std::swap(s0, s1);     // smaller indicator first: G's upper triangle
-      const int a0 = first_by_slot[s0], a1 = a0 + lev_by_slot[s0] - 1, b0 = first_by_slot[s1], b1 = b0 + lev_by_slot[s1] - 1;
+      const int a0 = first_by_slot[s0], a1 = a0 + eff_by_slot[s0] - 1, b0 = first_by_slot[s1], b1 = b0 + eff_by_slot[s1] - 1;
       for (int bm = a0 / PAIR_BM; bm <= a1 / PAIR_BM; bm++)
+        for (int bn = b0 / p->bn; bn <= b1 / p->bn; bn++) need[(size_t)bm * nbn + bn] = 1;
+      // the one-way counts on the diagonal, which rebuild the cells of a dropped last level
+      for (int bm = a0 / PAIR_BM; bm <= a1 / PAIR_BM; bm++)
+        for (int bn = a0 / p->bn; bn <= a1 / p->bn; bn++) need[(size_t)bm * nbn + bn] = 1;
+      for (int bm = b0 / PAIR_BM; bm <= b1 / PAIR_BM; bm++)
         for (int bn = b0 / p->bn; bn <= b1 / p->bn; bn++) need[(size_t)bm * nbn + bn] = 1;
     }
   }
@@ -100,8 +112,8 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   Plan p;
   make_plan(dev, ds, used, lev_by_slot, &p, cc, cc ? nunits : 0);
   const int nc = (int)p.slots.size(), nt = (int)p.tiles.size(), np = picked ? (int)picked->size() : 0;
-  // one int block: cols (int4 per column) | ind2col [ldg] | slot_first [nd] | tiles (int2) | ids [np]
-  const size_t n_cols = (size_t)nc * 4, n_ind = (size_t)p.ldg, n_sf = ((size_t)ds.nd + 1) & ~(size_t)1, n_tiles = (size_t)nt * 2;
+  // one int block: cols (int4 per column) | ind2col [ldg] | slot_first [nd] + slot_eff [nd] | tiles (int2) | ids [np]
+  const size_t n_cols = (size_t)nc * 4, n_ind = (size_t)p.ldg, n_sf = 2 * (((size_t)ds.nd + 1) & ~(size_t)1), n_tiles = (size_t)nt * 2;
   const size_t total = n_cols + n_ind + n_sf + n_tiles + (size_t)np + 16;
   int rc;
   if ((rc = bnl_reserve_pinned(ctx, &dev.h_pairmeta, &dev.h_pairmeta_cap, total))) return rc;
@@ -109,12 +121,14 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   if ((rc = bnl_reserve_device(ctx, &dev.d_pairG, &dev.pairG_cap, (size_t)p.ldg * p.ldg))) return rc;
   int *h = dev.h_pairmeta;
   int *h_cols = h, *h_ind = h_cols + n_cols, *h_sf = h_ind + n_ind, *h_tiles = h_sf + n_sf, *h_ids = h_tiles + n_tiles;
-  for (int s = 0; s < ds.nd; s++) h_sf[s] = -1;
+  int *h_se = h_sf + n_sf / 2;
+  for (int s = 0; s < ds.nd; s++) { h_sf[s] = -1; h_se[s] = 0; }
   for (int c = 0; c < nc; c++) {
-    const int s = p.slots[c], l = lev_by_slot[s];
-    h_cols[4 * c] = s; h_cols[4 * c + 1] = p.first[c]; h_cols[4 * c + 2] = l; h_cols[4 * c + 3] = 0;
+    const int s = p.slots[c], l = p.eff[c];
+    h_cols[4 * c] = s; h_cols[4 * c + 1] = p.first[c]; h_cols[4 * c + 2] = l; h_cols[4 * c + 3] = lev_by_slot[s];
     for (int v = 0; v < l; v++) h_ind[p.first[c] + v] = c;
     h_sf[s] = p.first[c];
+    h_se[s] = l;
   }
   for (int r = p.L; r < p.ldg; r++) h_ind[r] = nc - 1;
   memcpy(h_tiles, p.tiles.data(), n_tiles * sizeof(int));
@@ -135,8 +149,8 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   bool any_na = false, wide = false;
   for (int s : p.slots) {
     any_na = any_na || ds.slot_has_na.empty() || ds.slot_has_na[s];
-    wide = wide || lev_by_slot[s] > 4;
   }
+  for (int l : p.eff) wide = wide || l > 4;
   const unsigned grid = (unsigned)nt * (unsigned)p.splits;
 #define BNL_PAIR_GO(BN, ITEMS, DEPTH, NA, WIDE, NPW, SMEM)                                                        \
   do {                                                                                                            \
@@ -163,7 +177,8 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   BNL_CUDA(ctx, cudaGetLastError());
   // picked == null: every unit of the batch, in order
   pair_extract_kernel<<<(nunits + 255) / 256, 256, 0, dev.stream>>>(dev.d_units, picked ? d_ids : nullptr, nunits, d_sf,
-                                                                  dev.d_pairG, p.ldg, dev.d_tables);
+                                                                  d_sf + n_sf / 2, (int)ds.nobs, dev.d_pairG, p.ldg,
+                                                                  dev.d_tables);
   BNL_CUDA(ctx, cudaGetLastError());
   tm->launches += 2;
   return BNL_OK;

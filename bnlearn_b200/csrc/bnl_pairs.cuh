@@ -360,25 +360,48 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
 // Unit tables out of G, in the layout bnl_counts returns (n[z][x][y], first
 // variable fastest). A two-column unit with codes (a, b) = (col[0], col[1]) reads
 // G[first(col0) + a][first(col1) + b] (upper triangle: smaller indicator first); a
-// one-column unit reads the diagonal.
+// one-column unit reads the diagonal. A column without NA has no indicator for its
+// last level (slot_eff < levels): those cells are the margin minus the rest of the
+// row / column -- the other column's one-way count G[b][b] when this column can
+// hold no NA, the row count N when neither can.
 __global__ void __launch_bounds__(256)
 pair_extract_kernel(const BnlUnit *__restrict__ units, const int *__restrict__ ids, int n,
-                    const int *__restrict__ slot_first, const int *__restrict__ G, int ldg,
-                    int *__restrict__ tables) {
+                    const int *__restrict__ slot_first, const int *__restrict__ slot_eff, int nobs,
+                    const int *__restrict__ G, int ldg, int *__restrict__ tables) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   const BnlUnit &u = units[ids ? ids[t] : t];
   int *tab = tables + u.table_off;
-  const int f0 = slot_first[u.col[0]];
+  const int f0 = slot_first[u.col[0]], e0 = slot_eff[u.col[0]];
+  auto diag = [&](int i) { return G[(size_t)i * ldg + i]; };
   if (u.ncols == 1) {
-    for (int a = 0; a < u.cells; a++) tab[a] = G[(size_t)(f0 + a) * ldg + f0 + a];
+    const int l0 = u.cells;
+    int sum = 0;
+    for (int a = 0; a < e0; a++) { const int v = diag(f0 + a); tab[a] = v; sum += v; }
+    if (e0 < l0) tab[l0 - 1] = nobs - sum;
     return;
   }
-  const int f1 = slot_first[u.col[1]], l0 = u.mul[1], l1 = u.cells / l0;
-  for (int b = 0; b < l1; b++)
-    for (int a = 0; a < l0; a++) {
+  const int f1 = slot_first[u.col[1]], e1 = slot_eff[u.col[1]], l0 = u.mul[1], l1 = u.cells / l0;
+  int total = 0;
+  for (int b = 0; b < e1; b++) {
+    int colsum = 0;
+    for (int a = 0; a < e0; a++) {
       const int ia = f0 + a, ib = f1 + b;
-      tab[a + l0 * b] = ia <= ib ? G[(size_t)ia * ldg + ib] : G[(size_t)ib * ldg + ia];
+      const int v = ia <= ib ? G[(size_t)ia * ldg + ib] : G[(size_t)ib * ldg + ia];
+      tab[a + l0 * b] = v;
+      colsum += v;
     }
+    if (e0 < l0) { const int v = diag(f1 + b) - colsum; tab[l0 - 1 + l0 * b] = v; colsum += v; }
+    total += colsum;
+  }
+  if (e1 < l1) {
+    for (int a = 0; a < e0; a++) {
+      int rowsum = 0;
+      for (int b = 0; b < e1; b++) rowsum += tab[a + l0 * b];
+      const int v = diag(f0 + a) - rowsum;
+      tab[a + l0 * (l1 - 1)] = v;
+      total += v;
+    }
+    if (e0 < l0) tab[l0 - 1 + l0 * (l1 - 1)] = nobs - total;
+  }
 }
-
