@@ -308,6 +308,8 @@ def config_c_extras(eng, world, rank, device, cpu_cores=0, reps=5, want_hc=True)
     if world > 1:
         dist.barrier()
     n, dt, kms, dms, cache = timed(amat, mine, False, lower)
+    if world > 1:
+        dist.barrier()                  # the ranks finish their repetitions at different times
     t0 = time.perf_counter()
     if world > 1:
         # blocks are uneven (triangular work): gather the whole matrix, each rank's columns filled
@@ -700,7 +702,8 @@ def main():
     # strong scaling: rank r evaluates units [b, e) of the one list. Blocks are cut by
     # estimated cost: the marginal tests come out of one tensor-core contraction and
     # cost ~1/8 of a conditional test each.
-    bounds = cost_blocks([1.0 if u[2] else 0.125 for u in units], world)
+    n_marginal = sum(1 for u in units if not u[2])          # they lead the list
+    bounds = cost_blocks([1.0 if u[2] else 0.125 for u in units], world, together=n_marginal)
     b, e = bounds[rank], bounds[rank + 1]
     my_units = units[b:e]
     gather = Gatherer(bounds, 3, device)

@@ -106,13 +106,21 @@ def gather_rows(mine, n, device=None):
     return out
 
 
-def cost_blocks(costs, world):
+def cost_blocks(costs, world, together=0):
     """Contiguous blocks of a unit list with about equal total cost: boundaries
     bounds[r] .. bounds[r + 1] for rank r (pc.stable's marginal tests come from one
     tensor-core contraction and cost a fraction of a conditional test, so equal
-    COUNTS would leave the rank holding the conditional tests with most of the work)."""
+    COUNTS would leave the rank holding the conditional tests with most of the work).
+    together: the first `together` units form ONE piece of work that does not get
+    cheaper when cut (the contraction reads every row of every column whether it
+    serves 100 pairs or 666); if their cost is at least a rank's share they all go to
+    rank 0 and the rest is spread over the other ranks."""
     import numpy as np
-    c = np.cumsum(np.asarray(costs, dtype=np.float64))
+    costs = np.asarray(costs, dtype=np.float64)
+    if together and world > 1 and costs[:together].sum() >= 0.75 * costs.sum() / world:
+        rest = cost_blocks(costs[together:], world - 1)
+        return [0] + [together + b for b in rest]
+    c = np.cumsum(costs)
     total = float(c[-1]) if len(c) else 0.0
     bounds = [0]
     for r in range(1, world):
