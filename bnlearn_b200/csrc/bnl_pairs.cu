@@ -152,26 +152,28 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   }
   for (int l : p.eff) wide = wide || l > 4;
   const unsigned grid = (unsigned)nt * (unsigned)p.splits;
-#define BNL_PAIR_GO(BN, ITEMS, DEPTH, NA, WIDE, NPW, SMEM)                                                        \
+#define BNL_PAIR_GO(BN, ITEMS, DEPTH, NA, WIDE, NPW, SUP, SMEM)                                                        \
   do {                                                                                                            \
-    auto kern = pair_onehot_kernel<BN, ITEMS, DEPTH, NA, WIDE, NPW>;                                              \
+    auto kern = pair_onehot_kernel<BN, ITEMS, DEPTH, NA, WIDE, NPW, SUP>;                                              \
     BNL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMEM)));          \
     kern<<<grid, (NPW + 1) * 32, SMEM, dev.stream>>>(dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), \
                                                      d_ind, p.L, reinterpret_cast<const int2 *>(d_tiles), nt,     \
                                                      p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out); \
   } while (0)
-#define BNL_PAIR_LAUNCH(BN, ITEMS, DEPTH, NPW, SMEM)                                                              \
+#define BNL_PAIR_LAUNCH(BN, ITEMS, DEPTH, NPW, SUP, SMEM)                                                         \
   do {                                                                                                            \
-    if (any_na && wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, true, NPW, SMEM);                                     \
-    else if (any_na) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, false, NPW, SMEM);                                       \
-    else if (wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, false, true, NPW, SMEM);                                         \
-    else BNL_PAIR_GO(BN, ITEMS, DEPTH, false, false, NPW, SMEM);                                                  \
+    if (any_na && wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, true, NPW, SUP, SMEM);                                \
+    else if (any_na) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, false, NPW, SUP, SMEM);                                  \
+    else if (wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, false, true, NPW, SUP, SMEM);                                    \
+    else BNL_PAIR_GO(BN, ITEMS, DEPTH, false, false, NPW, SUP, SMEM);                                             \
   } while (0)
   // columns per producer thread: the tile's columns over 4 * NPW column lanes (19 + 1
   // warps measured 4 % faster than 11 + 1 on the wide tile, 15 + 1 and 23 + 1 slower)
-  if (p.bn == 128 && nc <= 44) BNL_PAIR_LAUNCH(128, 1, 8, 11, smem128);
-  else if (p.bn == 128) BNL_PAIR_LAUNCH(128, 2, 4, 19, smem128);      // <= 130 columns over 76 lanes
-  else BNL_PAIR_LAUNCH(256, 3, 3, 19, smem256);                       // <= 194 columns over 76 lanes
+  // two K-blocks per full / empty handshake (SUP = 2): a handshake has a floor of several hundred
+  // cycles whatever the work behind it (config B level 0: 0.225 -> 0.173 ms, config C 3.58 -> 3.48 ms)
+  if (p.bn == 128 && nc <= 44) BNL_PAIR_LAUNCH(128, 1, 4, 11, 2, smem128);
+  else if (p.bn == 128) BNL_PAIR_LAUNCH(128, 2, 2, 19, 2, smem128);      // <= 130 columns over 76 lanes
+  else BNL_PAIR_LAUNCH(256, 3, 2, 19, 2, smem256);                       // <= 194 columns over 76 lanes
 #undef BNL_PAIR_GO
 #undef BNL_PAIR_LAUNCH
   BNL_CUDA(ctx, cudaGetLastError());

@@ -149,15 +149,16 @@ __device__ __forceinline__ void sts128_if(uint32_t on, uint32_t addr, uint32_t a
 // are predicated instead of skipped, the trip count is padded to a multiple of the
 // ring depth (a padded stage stores nothing and its MMAs are predicated off), and the
 // levels past the fourth are compiled in only for the WIDE variant.
-template <int BN, int ITEMS, int DEPTH, bool NA, bool WIDE, int NPW>
+template <int BN, int ITEMS, int DEPTH, bool NA, bool WIDE, int NPW, int SUP>
 __global__ void __launch_bounds__((NPW + 1) * 32, 1)
 pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__restrict__ cols,
                    const int *__restrict__ ind2col, int L, const int2 *__restrict__ tiles, int ntiles,
                    int stages_per_split, int total_stages, int *__restrict__ G, int ldg, int atomic_out) {
   using namespace bnlpair;
   constexpr int A_BYTES = PAIR_BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr int NS = PAIR_STAGES;
-  static_assert((NS & (NS - 1)) == 0, "stage ring indexed with a mask");
+  // SUP operand buffers share one full / empty barrier pair ("one handshake per SUP K-blocks")
+  constexpr int NS = PAIR_STAGES, NSS = PAIR_STAGES / SUP;
+  static_assert((NSS & (NSS - 1)) == 0 && NSS >= 2, "barrier ring indexed with a mask");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // the dynamic window is only guaranteed 16-byte alignment: round up to the swizzle atom
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -174,7 +175,7 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < NS; s++) { mbar_init(&full_bar[s], NPW); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < NSS; s++) { mbar_init(&full_bar[s], NPW); mbar_init(&empty_bar[s], 1); }
     mbar_init(&accum_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     // columns that reach into the B rows, then (unless shared) into the A rows
@@ -206,7 +207,8 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
 
   const int st0 = split * stages_per_split;
   const int nst = min(st0 + stages_per_split, total_stages) - st0;     // >= 1 by the host's split
-  const int npad = (nst + DEPTH - 1) / DEPTH * DEPTH;                  // trip count of both roles
+  const int nsup = (nst + SUP - 1) / SUP;                              // handshakes
+  const int npad = (nsup + DEPTH - 1) / DEPTH * DEPTH;                 // trip count of both roles
 
   if (warp < NPW) {
     // ---------------- producers ----------------
@@ -244,7 +246,7 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
     // The CTAs resident at one time work on the same slab of rows (so that it stays in
     // L2); each starts at its own place in it and wraps around.
     const int rot = (int)(((long long)tile * nst) / ntiles);
-    uint4 ring[DEPTH][ITEMS];
+    uint4 ring[DEPTH][SUP][ITEMS];
     auto load = [&](uint4(&r)[ITEMS], int it) {          // it < nst: a real stage
       int w = it + rot;
       w -= w >= nst ? nst : 0;
@@ -261,39 +263,47 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
                      ::"l"(base4 + (coff[i] + sp)), "r"(pf & (lm[i] != 0u)));
     };
 #pragma unroll
-    for (int d = 0; d < DEPTH; d++) load(ring[d], min(d, nst - 1));
+    for (int d = 0; d < DEPTH; d++)
+#pragma unroll
+      for (int h = 0; h < SUP; h++) load(ring[d][h], min(d * SUP + h, nst - 1));
     const uint32_t smem0 = smem_u32(smem);
-    for (int it0 = 0; it0 < npad; it0 += DEPTH) {
+    for (int su0 = 0; su0 < npad; su0 += DEPTH) {
 #pragma unroll
       for (int d = 0; d < DEPTH; d++) {
-        const int it = it0 + d;
-        const int s = it & (NS - 1);
-        if (it >= NS) mbar_wait_spin(&empty_bar[s], ((it / NS) - 1) & 1);
-        const uint32_t sb = smem0 + (uint32_t)s * STAGE_BYTES;
-        const uint32_t live = it < nst ? 0xFFu : 0u;      // a padded stage stores nothing
+        const int su = su0 + d;
+        const int slot = su & (NSS - 1);
+        if (su >= NSS) mbar_wait_spin(&empty_bar[slot], ((su / NSS) - 1) & 1);
 #pragma unroll
-        for (int i = 0; i < ITEMS; i++) {
-          const uint32_t s0 = selector4<NA>(ring[d][i].x), s1 = selector4<NA>(ring[d][i].y),
-                         s2 = selector4<NA>(ring[d][i].z), s3 = selector4<NA>(ring[d][i].w);
-          const uint32_t rb = sb + sa[i], m = lm[i] & live;
+        for (int h = 0; h < SUP; h++) {
+          const int it = su * SUP + h;
+          const uint32_t sb = smem0 + (uint32_t)(slot * SUP + h) * STAGE_BYTES;
+          const uint32_t live = it < nst ? 0xFFu : 0u;    // a padded stage stores nothing
 #pragma unroll
-          for (int v = 0; v < 4; v++)
-            sts128_if(m & (1u << v), rb + v * 128 + __byte_perm(sw_lo[i], 0u, 0x4440 + v), onehot4(s0, 1u << (8 * v), 0u),
-                      onehot4(s1, 1u << (8 * v), 0u), onehot4(s2, 1u << (8 * v), 0u), onehot4(s3, 1u << (8 * v), 0u));
-          if (WIDE) {                                      // factors with 5-8 levels
+          for (int i = 0; i < ITEMS; i++) {
+            const uint32_t s0 = selector4<NA>(ring[d][h][i].x), s1 = selector4<NA>(ring[d][h][i].y),
+                           s2 = selector4<NA>(ring[d][h][i].z), s3 = selector4<NA>(ring[d][h][i].w);
+            const uint32_t rb = sb + sa[i], m = lm[i] & live;
 #pragma unroll
             for (int v = 0; v < 4; v++)
-              sts128_if(m & (16u << v), rb + (v + 4) * 128 + __byte_perm(sw_hi[i], 0u, 0x4440 + v),
-                        onehot4(s0, 0u, 1u << (8 * v)), onehot4(s1, 0u, 1u << (8 * v)), onehot4(s2, 0u, 1u << (8 * v)),
-                        onehot4(s3, 0u, 1u << (8 * v)));
+              sts128_if(m & (1u << v), rb + v * 128 + __byte_perm(sw_lo[i], 0u, 0x4440 + v), onehot4(s0, 1u << (8 * v), 0u),
+                        onehot4(s1, 1u << (8 * v), 0u), onehot4(s2, 1u << (8 * v), 0u), onehot4(s3, 1u << (8 * v), 0u));
+            if (WIDE) {                                    // factors with 5-8 levels
+#pragma unroll
+              for (int v = 0; v < 4; v++)
+                sts128_if(m & (16u << v), rb + (v + 4) * 128 + __byte_perm(sw_hi[i], 0u, 0x4440 + v),
+                          onehot4(s0, 0u, 1u << (8 * v)), onehot4(s1, 0u, 1u << (8 * v)), onehot4(s2, 0u, 1u << (8 * v)),
+                          onehot4(s3, 0u, 1u << (8 * v)));
+            }
           }
         }
         // generic-proxy writes -> visible to the tensor core's async-proxy reads
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         asm volatile("{ .reg .pred p; setp.eq.u32 p, %1, 0; @p mbarrier.arrive.shared::cta.b64 _, [%0]; }"
-                     ::"r"(smem_u32(&full_bar[s])), "r"((uint32_t)lane) : "memory");
-        load(ring[d], min(it + DEPTH, nst - 1));          // past the end: the last stage again, never used
+                     ::"r"(smem_u32(&full_bar[slot])), "r"((uint32_t)lane) : "memory");
+#pragma unroll
+        for (int h = 0; h < SUP; h++)                     // past the end: the last stage again, never used
+          load(ring[d][h], min((su + DEPTH) * SUP + h, nst - 1));
       }
     }
   } else {
@@ -303,19 +313,23 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
     const uint32_t idesc = (2u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(PAIR_BM >> 4) << 24);
     const uint32_t a_shift = a_in_b ? (uint32_t)(A_BYTES + (a0 - b0) * 128) : 0u;
     const uint32_t smem0 = smem_u32(smem);
-    for (int it = 0; it < npad; it++) {
-      const int s = it & (NS - 1);
-      mbar_wait_spin(&full_bar[s], (it / NS) & 1);
+    for (int su = 0; su < npad; su++) {
+      const int slot = su & (NSS - 1);
+      mbar_wait_spin(&full_bar[slot], (su / NSS) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       if (lane == 0) {
-        const uint32_t sb = smem0 + (uint32_t)s * STAGE_BYTES;
-        const uint64_t ad = make_desc_sw128(sb + a_shift), bd = make_desc_sw128(sb + A_BYTES);
-        if (it < nst) {
 #pragma unroll
-          for (int k = 0; k < PAIR_KROWS / 32; k++)      // +32 bytes of K per step: +2 in the (address >> 4) field
-            umma_i8(tmem, ad + 2 * k, bd + 2 * k, idesc, (it | k) != 0);
+        for (int h = 0; h < SUP; h++) {
+          const int it = su * SUP + h;
+          const uint32_t sb = smem0 + (uint32_t)(slot * SUP + h) * STAGE_BYTES;
+          const uint64_t ad = make_desc_sw128(sb + a_shift), bd = make_desc_sw128(sb + A_BYTES);
+          if (it < nst) {
+#pragma unroll
+            for (int k = 0; k < PAIR_KROWS / 32; k++)    // +32 bytes of K per step: +2 in the (address >> 4) field
+              umma_i8(tmem, ad + 2 * k, bd + 2 * k, idesc, (it | k) != 0);
+          }
         }
-        umma_commit(&empty_bar[s]);
+        umma_commit(&empty_bar[slot]);
       }
       __syncwarp();
     }

@@ -19,7 +19,7 @@ WANT = [  # (substring of the mangled name, mnemonics to centre the excerpt on, 
     ("count_group_kernelILi512ELi16384EE", ("ATOMS.POPC.INC",), 10),
     ("count_based_kernelILi5ELi1ELi1024EE", ("ATOMS.POPC.INC",), 10),
     ("gram_dmma_kernel", ("DMMA",), 10),
-    ("pair_onehot_kernelILi256ELi3ELi3ELb0ELb0ELi19EE", ("UTCIMMA", "LDTM", "UTCBAR", "UTCATOMSWS", "STS.128"), 8),
+    ("pair_onehot_kernelILi256ELi3ELi2ELb0ELb0ELi19ELi2EE", ("UTCIMMA", "LDTM", "UTCBAR", "UTCATOMSWS", "STS.128"), 8),
 ]
 
 
