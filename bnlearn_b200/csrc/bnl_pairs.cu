@@ -1,5 +1,6 @@
 // bnl_pairs.cu -- host side of the all-pairs contraction (bnl_pairs.cuh): which
 // units of a batch it serves, the tile / split plan, launches.
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -73,10 +74,16 @@ void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<cha
         p->tiles.push_back(make_int2(bm, bn));                                       // reaches the upper triangle
   p->total_stages = (int)((ds.nobs + PAIR_KROWS - 1) / PAIR_KROWS);
   // row splits: whole waves of CTAs (one per SM), each long enough to pay for its
-  // prologue and for draining the accumulator (~20 stages' worth)
+  // prologue and for draining the accumulator (~20 stages' worth) -- and short enough
+  // that the slabs of rows the resident CTAs walk through stay in L2: every tile of a
+  // slab re-reads the slab's columns (with 72 tiles and two splits of 500 MB each the
+  // kernel pulled 14.8 GB from DRAM for 1.0 GB of data and ran at the HBM rate).
   const long long nt = (long long)p->tiles.size();
+  const double slab_budget = (double)env_ll("BNL_PAIRS_SLAB_MB", 40) * 1e6;   // bytes of packed columns per slab; 2-3 slabs are live at a time
+  const int s_min = (int)std::min<double>(std::max(1, p->total_stages / 32),
+                                          std::ceil((double)ds.nobs * (double)p->slots.size() / slab_budget));
   double best = 1e300;
-  for (int s = 1; s <= 4096 && s <= std::max(1, p->total_stages / 32); s++) {
+  for (int s = std::max(1, s_min); s <= 4096 && s <= std::max(1, p->total_stages / 32); s++) {
     const long long waves = (nt * s + dev.sm_count - 1) / dev.sm_count;
     const double cost = (double)waves * ((double)((p->total_stages + s - 1) / s) + 20.0);
     if (cost < best - 1e-9) { best = cost; p->splits = s; }
