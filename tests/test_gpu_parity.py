@@ -1072,3 +1072,56 @@ def test_gaussian_allpairs_matches_per_pair_tests(engine):
         keep2, pm2 = d.ci_gaussian_allpairs(test, 1.0, cols=sub)
         assert len(keep2) == 10 and np.array_equal(pm2, pm[np.ix_(sub, sub)])
     d.release()
+
+
+def test_all_pairs_route_every_statistic_and_refusals(engine, monkeypatch):
+    """Batches of >= 4096 one- and two-way tables take the route without host-side
+    descriptors (device-built units, warp-per-unit epilogue, no indicator row for the
+    last level of NA-free columns). Every test and score it serves must equal the
+    per-unit kernels bit for bit; eight-level factors (the second half of the level
+    stores), columns with and without NA, BDs (block-wide epilogue) included. What it
+    cannot serve -- a bad column index -- still reaches the general path's error."""
+    from bnlearn_b200 import BnlError
+    rng = np.random.default_rng(21)
+    na = np.iinfo(np.int32).min
+    ncols, nobs = 96, 40007
+    lev = [int(v) for v in rng.integers(2, 9, ncols)]
+    lev[:4] = [8, 8, 2, 5]
+    cols = []
+    for i, l in enumerate(lev):
+        c = rng.integers(1, l + 1, nobs).astype(np.int32)
+        if i % 4 == 1:
+            c[rng.random(nobs) < 0.05] = na
+        cols.append(c)
+    d = engine.register(cols, lev)
+    pairs = [(i, j) for i in range(ncols) for j in range(ncols) if i != j and (i < j or (i * j) % 3 == 0)]
+    assert len(pairs) >= 4096
+    px = np.array([p[0] for p in pairs], dtype=np.int32)
+    py = np.array([p[1] for p in pairs], dtype=np.int32)
+    no_z = [[]] * len(pairs)
+    one_parent = [[int(v)] for v in py]
+
+    def everything():
+        out = []
+        for test in ("mi", "mi-adf", "x2", "x2-adf"):
+            out += list(d.ci_discrete(test, px, py, no_z))
+        for score, arg in (("loglik", 0.0), ("bic", 3.5), ("bde", 2.0), ("bds", 1.0), ("k2", 0.0), ("qnml", 0.0)):
+            out += list(d.score_discrete(score, px, one_parent, arg))
+        # root nodes (one-way tables) in a batch of their own
+        roots = np.tile(np.arange(ncols, dtype=np.int32), 50)
+        out += list(d.score_discrete("bde", roots, [[]] * len(roots), 1.0))
+        return out
+
+    monkeypatch.setenv("BNL_PAIRS", "2")
+    got = everything()
+    monkeypatch.setenv("BNL_PAIRS", "0")
+    want = everything()
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b, equal_nan=True)
+    monkeypatch.setenv("BNL_PAIRS", "2")
+    bad = py.copy()
+    bad[17] = ncols + 5
+    with pytest.raises(BnlError):
+        d.ci_discrete("mi", px, bad, no_z)
+    d.release()
