@@ -478,6 +478,7 @@ int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_o
   const int m = (int)target.size();
   std::vector<double> score(std::max(m, 1));
   if (m > 0) {
+    BNL_TRACE("cache_fill: score call");
     const int *pi = pa_idx.empty() ? nullptr : pa_idx.data();
     int rc = score_e >= BNL_LOGLIK_CG
       ? bnl_score_cg(ctx, data, score_e, k_or_iss, m, target.data(), pa_off.data(), pi, score.data(), nullptr)

@@ -5,6 +5,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <chrono>
 #include <thread>
 
 #include <math.h>
@@ -282,8 +283,32 @@ static void free_dataset(bnl_ctx *ctx, BnlDataSet &ds) {
   ds.dev.clear();
 }
 
+BnlTraceSlot g_bnl_trace[32];
+int g_bnl_trace_on = -1;
+static double trace_now() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+int bnl_trace_slot(const char *label) {
+  for (int i = 0; i < 32; i++) {
+    if (g_bnl_trace[i].label == label) return i;
+    if (!g_bnl_trace[i].label) { g_bnl_trace[i].label = label; return i; }
+  }
+  return 31;
+}
+BnlTraceScope::BnlTraceScope(const char *label) : slot(-1), t0(0.0) {
+  if (g_bnl_trace_on < 0) { const char *v = getenv("BNL_TRACE"); g_bnl_trace_on = (v && *v && atoi(v)) ? 1 : 0; }
+  if (g_bnl_trace_on) { slot = bnl_trace_slot(label); t0 = trace_now(); }
+}
+BnlTraceScope::~BnlTraceScope() {
+  if (slot >= 0) { g_bnl_trace[slot].seconds += trace_now() - t0; g_bnl_trace[slot].calls++; }
+}
+
 extern "C" void bnl_shutdown(bnl_ctx *ctx) {
   if (!ctx) return;
+  if (g_bnl_trace_on > 0)
+    for (int i = 0; i < 32 && g_bnl_trace[i].label; i++)
+      fprintf(stderr, "[bnl trace] %-28s %10.3f ms  %8lld calls\n", g_bnl_trace[i].label,
+              g_bnl_trace[i].seconds * 1e3, g_bnl_trace[i].calls);
   for (auto &kv : ctx->data) free_dataset(ctx, kv.second);
   for (auto &d : ctx->devs) {
     cudaSetDevice(d.id);

@@ -188,6 +188,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
   std::vector<char> pair_used;
   int pos = b;
   while (pos < e) {
+    BNL_TRACE("run_block: whole sub-batch");
     long long cells = 0;
     int cnt = 0;
     while (pos + cnt < e && cnt < kMaxBatchUnits && cells + rq.units[pos + cnt].cells <= kMaxBatchCells) {
@@ -515,6 +516,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       return (int)std::max(1ll, ch);
     };
 
+    BnlTraceScope *tr_enq = new BnlTraceScope("run_block: enqueue");
     BNL_CUDA(ctx, cudaEventRecord(dev.ev0, dev.stream));
     BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_units, dev.h_units, (size_t)cnt * sizeof(BnlUnit),
                                   cudaMemcpyHostToDevice, dev.stream));
@@ -697,13 +699,18 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)cnt * 4 * sizeof(double),
                                     cudaMemcpyDeviceToHost, dev.stream));
       BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
-      BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+      delete tr_enq; tr_enq = nullptr;
+      {
+        BNL_TRACE("run_block: sync wait");
+        BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+      }
       for (int i = 0; i < cnt; i++) {
         if (rq.o0) rq.o0[pos + i] = dev.h_out[4 * i + 0];
         if (rq.o1) rq.o1[pos + i] = dev.h_out[4 * i + 1];
         if (rq.o2) rq.o2[pos + i] = dev.h_out[4 * i + 2];
       }
     }
+    delete tr_enq;
     float t = 0.f;
     BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.ev0, dev.ev1));
     tm->total += t;
@@ -1061,12 +1068,16 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
     if (rc || handled) return rc;
   }
   Request rq{1, score_e, k_or_iss, n, {}, score, nparams, nullptr, nullptr, nullptr};
-  rq.units.resize(n);
-  for (int u = 0; u < n; u++) {
-    int np = pa_off[u + 1] - pa_off[u];
-    int rc = make_unit(ctx, *ds, target[u], -1, pa_idx ? pa_idx + pa_off[u] : nullptr, np, &rq.units[u]);
-    if (rc) return rc;
+  {
+    BNL_TRACE("score_discrete: make_unit");
+    rq.units.resize(n);
+    for (int u = 0; u < n; u++) {
+      int np = pa_off[u + 1] - pa_off[u];
+      int rc = make_unit(ctx, *ds, target[u], -1, pa_idx ? pa_idx + pa_off[u] : nullptr, np, &rq.units[u]);
+      if (rc) return rc;
+    }
   }
+  BNL_TRACE("score_discrete: run_request");
   return run_request(ctx, *ds, rq);
 }
 

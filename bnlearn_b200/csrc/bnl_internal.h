@@ -199,6 +199,19 @@ int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_o
 #define BNL_REGRET_K 100
 int bnl_regret_table(bnl_ctx *ctx, BnlDevice &dev);
 
+// Host-side time accounting for development (BNL_TRACE=1: totals per label go to stderr at
+// bnl_shutdown). Zero cost when off apart from one branch per scope.
+struct BnlTraceSlot { const char *label; double seconds; long long calls; };
+extern BnlTraceSlot g_bnl_trace[32];
+extern int g_bnl_trace_on;             // -1 unknown, 0 off, 1 on
+int bnl_trace_slot(const char *label);
+struct BnlTraceScope {
+  int slot; double t0;
+  explicit BnlTraceScope(const char *label);
+  ~BnlTraceScope();
+};
+#define BNL_TRACE(label) BnlTraceScope bnl_trace_scope_##__LINE__(label)
+
 // per-call timing of one device block.
 struct BnlTiming { float total = 0.f, count = 0.f, epi = 0.f; int launches = 0; };
 

@@ -257,12 +257,19 @@ extern "C" int bnl_hc(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
 
   long long it = 1;
   for (;;) {
-    rc = bnl_score_cache_fill_np(ctx, data, score_e, k_or_iss, n, S.a.data(), blmat, updated.data(),
-                                 (int)updated.size(), equivalence ? 1 : 0, S.reference.data(),
-                                 S.cache.data(), test_counter, S.nparents.data());
+    {
+      BNL_TRACE("hc: score_cache_fill");
+      rc = bnl_score_cache_fill_np(ctx, data, score_e, k_or_iss, n, S.a.data(), blmat, updated.data(),
+                                   (int)updated.size(), equivalence ? 1 : 0, S.reference.data(),
+                                   S.cache.data(), test_counter, S.nparents.data());
+    }
     if (rc) return rc;
-    S.columns_changed(updated);                // only these columns of the cache were rewritten
-    const Move mv = S.opt_step();
+    Move mv;
+    {
+      BNL_TRACE("hc: columns_changed+opt_step");
+      S.columns_changed(updated);                // only these columns of the cache were rewritten
+      mv = S.opt_step();
+    }
     if (!mv.op) break;
     updated.clear();
     if (mv.op == 1) { S.set_arc(mv.from, mv.to, 1); updated.push_back(mv.to); }
