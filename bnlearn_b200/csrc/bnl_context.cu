@@ -146,6 +146,36 @@ scan_packed_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   if (na) flags[1 + c] = 1;
 }
 
+// Host-packed nibbles -> the uint8 layout (0xF -> 0xFF). One thread: 8 bytes in, 16 out.
+__global__ void __launch_bounds__(256)
+unpack_nibbles_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, long long nbytes_in) {
+  const long long words = (nbytes_in + 7) / 8;
+  for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < words;
+       w += (long long)gridDim.x * blockDim.x) {
+    uint2 v = reinterpret_cast<const uint2 *>(src)[w];
+    const long long left = nbytes_in - 8 * w;                  // bytes of this word that belong to the column
+    if (left < 8) {                                            // the rest must unpack to the 0xFF row padding
+      const unsigned long long keep = left <= 0 ? 0ull : (~0ull >> (8 * (8 - left)));
+      unsigned long long x = ((unsigned long long)v.y << 32) | v.x;
+      x = (x & keep) | ~keep;
+      v.x = (unsigned)x; v.y = (unsigned)(x >> 32);
+    }
+    const unsigned in[2] = {v.x, v.y};
+    unsigned out[4];
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+#pragma unroll
+      for (int q = 0; q < 2; q++) {
+        unsigned x = (in[h] >> (16 * q)) & 0xFFFFu;              // four nibbles
+        x = (x | (x << 8)) & 0x00FF00FFu;
+        x = (x | (x << 4)) & 0x0F0F0F0Fu;                        // one per byte
+        const unsigned na = ((x + 0x01010101u) >> 4) & 0x01010101u;   // 0xF + 1 carries into bit 4
+        out[2 * h + q] = x | (na * 0xF0u);
+      }
+    reinterpret_cast<uint4 *>(dst)[w] = make_uint4(out[0], out[1], out[2], out[3]);
+  }
+}
+
 // ---------------------------------------------------------------------------
 
 extern "C" int bnl_init(bnl_ctx **out, const int *devices, int ndev) {
@@ -353,6 +383,8 @@ static size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 extern "C" void bnl_host_pack_slice(const int *src, uint8_t *dst, long long n, int nlevels, int *bad,
                                     int *has_na);
+extern "C" void bnl_host_pack_slice4(const int *src, uint8_t *dst, long long n, int nlevels, int *bad,
+                                     int *has_na);
 
 // Upload of the factor columns of a LARGE data frame. Two routes share the work
 // and the PCIe link:
@@ -386,6 +418,16 @@ static int upload_factors_hybrid(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, Bn
   BNL_CUDA(ctx, cudaEventRecord(d0.ev_stage[0], d0.stream));
   BNL_CUDA(ctx, cudaStreamWaitEvent(d0.stream2, d0.ev_stage[0], 0));
 
+  // nibble route (BNL_PACK_NIBBLES=0 turns it off): device staging for kSlots half-size columns.
+  // 1M-row blocks keep the nibble pairs of a column aligned (kBlock is even).
+  bool use_nibbles = true;
+  if (const char *v = getenv("BNL_PACK_NIBBLES")) if (*v) use_nibbles = atoi(v) != 0;
+  const size_t nib_stride = ((size_t)(nobs + 1) / 2 + 255 + 16) & ~(size_t)255;
+  uint8_t *d_nib = nullptr;
+  if (use_nibbles && nthreads > 0) {
+    if ((rc = bnl_pool_alloc(ctx, d0, (void **)&d_nib, (size_t)kSlots * nib_stride))) return rc;
+  } else use_nibbles = false;
+  std::mutex enqueue;
   // columns [0, cpu_next) belong to the host route, [gpu_next, nd) to the raw route.
   std::mutex claim;
   int cpu_next = 0, cpu_cur = -1, cpu_blk = 0, gpu_next = nd;
@@ -423,16 +465,37 @@ static int upload_factors_hybrid(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, Bn
       const long long r0 = (long long)b * kBlock, r1 = std::min(nobs, r0 + kBlock);
       const int dc = dcols[c];
       int bad = 0, na = 0;
-      bnl_host_pack_slice(static_cast<const int *>(col[dc]) + r0, d0.h_pack + (size_t)slot * ds.stride_u8 + r0,
-                          r1 - r0, nlevels[dc], &bad, &na);
+      const bool nib = use_nibbles && nlevels[dc] <= 15;          // two codes per byte through the ring
+      if (nib)
+        bnl_host_pack_slice4(static_cast<const int *>(col[dc]) + r0, d0.h_pack + (size_t)slot * ds.stride_u8 + r0 / 2,
+                             r1 - r0, nlevels[dc], &bad, &na);
+      else
+        bnl_host_pack_slice(static_cast<const int *>(col[dc]) + r0, d0.h_pack + (size_t)slot * ds.stride_u8 + r0,
+                            r1 - r0, nlevels[dc], &bad, &na);
       if (bad) host_flags[0] = 1;
       if (na) host_flags[1 + c] = 1;
       if (done[c].fetch_add(1) + 1 == nblocks) {
         cudaError_t e = cudaEventCreateWithFlags(&ev[c], cudaEventDisableTiming);
-        if (e == cudaSuccess)
+        if (e == cudaSuccess && nib) {
+          // nibbles go to a device staging slot; the ring slot is free once they have left the host
+          // (event), the unpack kernel follows on the same stream before the slot's next copy
+          const size_t nb = (size_t)((nobs + 1) / 2);
+          uint8_t *dst4 = d_nib + (size_t)slot * nib_stride;
+          std::lock_guard<std::mutex> lock(enqueue);             // copy + event + kernel stay together on stream2
+          e = cudaMemcpyAsync(dst4, d0.h_pack + (size_t)slot * ds.stride_u8, nb, cudaMemcpyHostToDevice, d0.stream2);
+          if (e == cudaSuccess) e = cudaEventRecord(ev[c], d0.stream2);
+          if (e == cudaSuccess) {
+            const long long words = ((long long)nb + 7) / 8;
+            const int grid = (int)std::min<long long>((words + 255) / 256, (long long)d0.sm_count * 8);
+            unpack_nibbles_kernel<<<grid, 256, 0, d0.stream2>>>(dst4, dd0.u8 + ds.stride_u8 * c, (long long)nb);
+            e = cudaGetLastError();
+          }
+        } else if (e == cudaSuccess) {
+          std::lock_guard<std::mutex> lock(enqueue);
           e = cudaMemcpyAsync(dd0.u8 + ds.stride_u8 * c, d0.h_pack + (size_t)slot * ds.stride_u8, (size_t)nobs,
                               cudaMemcpyHostToDevice, d0.stream2);
-        if (e == cudaSuccess) e = cudaEventRecord(ev[c], d0.stream2);
+          if (e == cudaSuccess) e = cudaEventRecord(ev[c], d0.stream2);
+        }
         if (e != cudaSuccess) failed = 1;
         enq[c] = 1;
       }
@@ -452,6 +515,12 @@ static int upload_factors_hybrid(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, Bn
     raw_ok = cudaPointerGetAttributes(&at, probe) == cudaSuccess &&
              (at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged);
     cudaGetLastError();                       // an unregistered pointer may leave a sticky-looking error code behind
+    // With two codes per byte through the ring and eight or more packing threads the raw route only
+    // takes memory bandwidth and PCIe time away from them (config B, 16 cores: 16.4 ms with it, 15.7
+    // without); on a box with few cores the copy engine's share is worth having.
+    int nib_cols = 0;
+    for (int c = 0; c < nd; c++) nib_cols += nlevels[dcols[c]] <= 15;
+    if (use_nibbles && nthreads >= 8 && 2 * nib_cols >= nd) raw_ok = false;
     if (const char *v = getenv("BNL_RAW_ROUTE")) if (*v) raw_ok = atoi(v) != 0;
     if (nthreads == 0) raw_ok = true;         // nobody else would move the data
   }
@@ -478,6 +547,7 @@ static int upload_factors_hybrid(bnl_ctx *ctx, BnlDataSet &ds, BnlDevice &d0, Bn
   if (ge != cudaSuccess) failed = 1;
   for (auto &w : workers) w.join();
   cudaError_t e2 = cudaStreamSynchronize(d0.stream2);
+  if (d_nib) bnl_pool_free(d0, d_nib, (size_t)kSlots * nib_stride);
   for (cudaEvent_t e : ev) if (e) cudaEventDestroy(e);
   if (failed.load() || e2 != cudaSuccess)
     return bnl_fail(ctx, BNL_ECUDA, "uploading the factor columns failed: %s",
