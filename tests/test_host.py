@@ -47,3 +47,19 @@ def test_device_special_functions_host_build_against_mpmath():
         assert rel_close(L.bnl_host_pnorm_two_sided(z), v, 1e-12), z
     assert L.bnl_host_pchisq_upper(0.0, 0.0) == 1.0      # df = 0: point mass at zero
     assert L.bnl_host_pchisq_upper(3.0, 0.0) == 0.0
+
+
+def test_cost_blocks_cover_the_list_in_order():
+    """replicate.cost_blocks: contiguous, ordered, complete; equal costs give near-equal
+    blocks; a leading run that must stay together goes to rank 0 once it costs a rank's share."""
+    from bnlearn_b200.replicate import cost_blocks
+    b = cost_blocks([1.0] * 103, 4)
+    assert b[0] == 0 and b[-1] == 103 and all(x <= y for x, y in zip(b, b[1:]))
+    assert max(y - x for x, y in zip(b, b[1:])) - min(y - x for x, y in zip(b, b[1:])) <= 1
+    costs = [0.125] * 666 + [1.0] * 415
+    assert cost_blocks(costs, 1) == [0, 1081]
+    b8 = cost_blocks(costs, 8, together=666)
+    assert b8[1] == 666 and b8[-1] == 1081 and len(b8) == 9
+    b2 = cost_blocks(costs, 2, together=666)
+    assert b2[0] == 0 and b2[1] > 666 and b2[2] == 1081        # cheaper than a rank's share: shares a rank
+    assert cost_blocks([], 3) == [0, 0, 0, 0]
