@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <memory>
 #include <thread>
 
 #include "bnl_discrete_kernels.cuh"
@@ -237,10 +238,10 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       pair_used.assign(ds.nd, 0);
       for (int i : pair_units)
         for (int k = 0; k < dev.h_units[i].ncols; k++) pair_used[dev.h_units[i].col[k]] = 1;
-      if (take && kKnobPairs < 2) {
+      if (take) {
         double tensor_s, atomic_s;
         bnl_pairs_cost(dev, ds, pair_used, (long long)pair_units.size(), lev_by_slot, &tensor_s, &atomic_s);
-        take = tensor_s < 0.8 * atomic_s;
+        take = kKnobPairs >= 2 ? tensor_s < 1e29 : tensor_s < 0.8 * atomic_s;
       }
       if (!take) pair_units.clear();
       for (int i : pair_units) grouped[i] = 3;
@@ -516,7 +517,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       return (int)std::max(1ll, ch);
     };
 
-    BnlTraceScope *tr_enq = new BnlTraceScope("run_block: enqueue");
+    std::unique_ptr<BnlTraceScope> tr_enq(new BnlTraceScope("run_block: enqueue"));
     BNL_CUDA(ctx, cudaEventRecord(dev.ev0, dev.stream));
     BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_units, dev.h_units, (size_t)cnt * sizeof(BnlUnit),
                                   cudaMemcpyHostToDevice, dev.stream));
@@ -699,7 +700,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)cnt * 4 * sizeof(double),
                                     cudaMemcpyDeviceToHost, dev.stream));
       BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
-      delete tr_enq; tr_enq = nullptr;
+      tr_enq.reset();
       {
         BNL_TRACE("run_block: sync wait");
         BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
@@ -710,7 +711,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         if (rq.o2) rq.o2[pos + i] = dev.h_out[4 * i + 2];
       }
     }
-    delete tr_enq;
+    tr_enq.reset();
     float t = 0.f;
     BNL_CUDA(ctx, cudaEventElapsedTime(&t, dev.ev0, dev.ev1));
     tm->total += t;
@@ -787,10 +788,10 @@ int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, 
     cells += (long long)l0 * l1;
   }
   if (cells > kMaxBatchCells) return BNL_OK;
-  if (knob < 2) {
+  {
     double tensor_s, atomic_s;
     bnl_pairs_cost(dev, ds, used, n, lev_by_slot, &tensor_s, &atomic_s, h_cc);
-    if (!(tensor_s < 0.8 * atomic_s)) return BNL_OK;
+    if (!(knob >= 2 ? tensor_s < 1e29 : tensor_s < 0.8 * atomic_s)) return BNL_OK;
   }
   *handled = true;
   BnlDeviceData &dd = ds.dev[0];

@@ -322,6 +322,8 @@ extern "C" int bnl_ci_gaussian_allpairs(bnl_ctx *ctx, bnl_data data, int test_e,
     return bnl_fail(ctx, BNL_EUNSUPPORTED, "bnl_ci_gaussian_allpairs needs complete data (use bnl_ci_gaussian)");
   if (nkeep) *nkeep = 0;
   if (ncols < 2) return BNL_OK;
+  if (ncols > 32768)
+    return bnl_fail(ctx, BNL_EUNSUPPORTED, "bnl_ci_gaussian_allpairs: at most 32768 columns per call (the flag matrix is n x n)");
   BnlDevice &dev = ctx->devs[0];
   BnlDeviceData &dd = ds.dev[0];
   BNL_CUDA(ctx, cudaSetDevice(dev.id));

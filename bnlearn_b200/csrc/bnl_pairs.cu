@@ -110,6 +110,8 @@ void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const std::vecto
   const double macs = (double)p.tiles.size() * PAIR_BM * p.bn * (double)ds.nobs;
   const double hbm = (double)p.slots.size() * (double)ds.nobs / 5e12;
   *tensor_s = std::max(macs / kPairMacRate, hbm) + 40e-6;
+  // G is ldg x ldg ints: beyond 16384 indicator rows (1 GiB) the contraction is not offered
+  if (p.ldg > 16384) *tensor_s = 1e30;
   *atomic_s = (double)nunits * (double)ds.nobs / kAtomicRate + 10e-6;
 }
 
