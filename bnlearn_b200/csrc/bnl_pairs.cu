@@ -38,13 +38,25 @@ void make_plan(const BnlDevice &dev, const BnlDataSet &ds, const std::vector<cha
   // others are in it, so pair_extract_kernel gets those cells from the margins (exact: integers).
   // A three-level factor costs two rows of H instead of three -- 1000 factors of 2-4 levels: L from
   // 3000 to 2000, 156 output tiles to 72.
+  // A producer thread owns a fixed number of column slots, 228 per tile in the widest variant (3 x
+  // 76 column lanes, A and B rows together): no 128-row block of H may hold more than 72 columns
+  // (+ one that straddles in from each side). One-row columns -- NA-free binary factors -- would
+  // exceed that, so a block that is full is closed and the next column starts the next block
+  // (the rows left over are never written and stay zero).
+  const int kMaxColsPerBlock = 72;
+  int blk = 0, blk_cols = 0, prev_end = -1;
   for (int s = 0; s < ds.nd; s++)
     if (used[s]) {
       const bool na = ds.slot_has_na.empty() || ds.slot_has_na[s];
+      const int e = lev_by_slot[s] - (na ? 0 : 1);
+      if (p->L / PAIR_BM != blk) { blk = p->L / PAIR_BM; blk_cols = prev_end >= blk * PAIR_BM ? 1 : 0; }
+      if (blk_cols >= kMaxColsPerBlock) { p->L = (blk + 1) * PAIR_BM; blk++; blk_cols = 0; }
       p->slots.push_back(s);
       p->first.push_back(p->L);
-      p->eff.push_back(lev_by_slot[s] - (na ? 0 : 1));
-      p->L += p->eff.back();
+      p->eff.push_back(e);
+      p->L += e;
+      prev_end = p->L - 1;
+      blk_cols++;
     }
   p->ldg = (p->L + 255) & ~255;
   p->bn = p->L <= 128 ? 128 : 256;
@@ -112,6 +124,8 @@ void bnl_pairs_cost(const BnlDevice &dev, const BnlDataSet &ds, const std::vecto
   *tensor_s = std::max(macs / kPairMacRate, hbm) + 40e-6;
   // G is ldg x ldg ints: beyond 16384 indicator rows (1 GiB) the contraction is not offered
   if (p.ldg > 16384) *tensor_s = 1e30;
+  // the kernel addresses the packed block with 32-bit offsets in 16-byte units
+  if ((unsigned long long)ds.stride_u8 * (unsigned long long)ds.nd >= (1ull << 35)) *tensor_s = 1e30;
   *atomic_s = (double)nunits * (double)ds.nobs / kAtomicRate + 10e-6;
 }
 
@@ -135,11 +149,13 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   for (int c = 0; c < nc; c++) {
     const int s = p.slots[c], l = p.eff[c];
     h_cols[4 * c] = s; h_cols[4 * c + 1] = p.first[c]; h_cols[4 * c + 2] = l; h_cols[4 * c + 3] = lev_by_slot[s];
-    for (int v = 0; v < l; v++) h_ind[p.first[c] + v] = c;
+    // rows of this column, and the unused rows up to the next column's first (the tail of a closed
+    // block: a tile that ends there must still find its LAST column through ind2col)
+    const int until = c + 1 < nc ? p.first[c + 1] : p.ldg;
+    for (int r = p.first[c]; r < until; r++) h_ind[r] = c;
     h_sf[s] = p.first[c];
     h_se[s] = l;
   }
-  for (int r = p.L; r < p.ldg; r++) h_ind[r] = nc - 1;
   memcpy(h_tiles, p.tiles.data(), n_tiles * sizeof(int));
   for (int i = 0; i < np; i++) h_ids[i] = (*picked)[i];
   int *d = dev.d_pairmeta;

@@ -193,6 +193,7 @@ pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__
     reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0, 0, 0, 0);
   __syncthreads();
   const int nB = s_range[1] - s_range[0] + 1, nA = s_range[3] - s_range[2] + 1, nitems = nB + nA;
+  if (nitems > ITEMS * NPW * 4 || nitems > 256) __trap();      // the host's layout bounds the columns per tile (bnl_pairs.cu)
   for (int q = threadIdx.x; q < nitems; q += (NPW + 1) * 32) {     // the work list, one column per thread
     const bool inB = q < nB;
     const int4 ci = cols[inB ? s_range[0] + q : s_range[2] + q - nB];

@@ -1125,3 +1125,30 @@ def test_all_pairs_route_every_statistic_and_refusals(engine, monkeypatch):
     with pytest.raises(BnlError):
         d.ci_discrete("mi", px, bad, no_z)
     d.release()
+
+
+def test_all_pairs_many_binary_columns(engine, monkeypatch):
+    """NA-free binary factors take ONE indicator row each, so a 256-row tile of the indicator
+    matrix could hold more columns than a producer thread has slots for; the layout closes a
+    128-row block after 72 columns. 320 binary columns (some with NA, some three-level ones in
+    between), every pair, against numpy."""
+    rng = np.random.default_rng(33)
+    na = np.iinfo(np.int32).min
+    ncols, nobs = 320, 20011
+    lev = [3 if i % 17 == 0 else 2 for i in range(ncols)]
+    cols = []
+    for i, l in enumerate(lev):
+        c = rng.integers(1, l + 1, nobs).astype(np.int32)
+        if i % 23 == 5:
+            c[rng.random(nobs) < 0.03] = na
+        cols.append(c)
+    d = engine.register(cols, lev)
+    pairs = [(i, j) for i in range(ncols) for j in range(i + 1, ncols)]
+    monkeypatch.setenv("BNL_PAIRS", "2")
+    tabs = d.counts([p[0] for p in pairs], [p[1] for p in pairs], [[]] * len(pairs))
+    code = np.stack([np.where(c == na, -1, c - 1) for c in cols]).astype(np.int64)
+    for (x, y), t in zip(pairs, tabs):
+        keep = (code[x] >= 0) & (code[y] >= 0)
+        want = np.bincount((code[x] * lev[y] + code[y])[keep], minlength=lev[x] * lev[y])
+        assert np.array_equal(np.asarray(t).ravel(), want), (x, y)
+    d.release()
