@@ -167,7 +167,6 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   // variants: <indicator columns per tile, columns per producer thread, stages of loads in flight>.
   // One output tile of <= 44 columns (a pc.stable level 0 on a few dozen factors) keeps 8 stages
   // in flight per thread; the widest tile needs 5 columns per thread and affords 3.
-  const size_t smem128 = (size_t)PAIR_STAGES * (PAIR_BM + 128) * 128 + 1024;
   const size_t smem256 = (size_t)PAIR_STAGES * (PAIR_BM + 256) * 128 + 1024;
   // NA bytes between valid codes need one more instruction per word (selector4); factors
   // with more than four levels need the second half of the level stores
@@ -177,28 +176,30 @@ int bnl_pairs_run(bnl_ctx *ctx, BnlDevice &dev, const BnlDataSet &ds, const BnlD
   }
   for (int l : p.eff) wide = wide || l > 4;
   const unsigned grid = (unsigned)nt * (unsigned)p.splits;
-#define BNL_PAIR_GO(BN, ITEMS, DEPTH, NA, WIDE, NPW, SUP, SMEM)                                                        \
+#define BNL_PAIR_GO(BN, ITEMS, DEPTH, NA, WIDE, NPW, SUP, NSTG, SMEM)                                                        \
   do {                                                                                                            \
-    auto kern = pair_onehot_kernel<BN, ITEMS, DEPTH, NA, WIDE, NPW, SUP>;                                              \
+    auto kern = pair_onehot_kernel<BN, ITEMS, DEPTH, NA, WIDE, NPW, SUP, NSTG>;                                              \
     BNL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMEM)));          \
     kern<<<grid, (NPW + 1) * 32, SMEM, dev.stream>>>(dd.u8, ds.stride_u8, reinterpret_cast<const int4 *>(d_cols), \
                                                      d_ind, p.L, reinterpret_cast<const int2 *>(d_tiles), nt,     \
                                                      p.per_split, p.total_stages, dev.d_pairG, p.ldg, atomic_out); \
   } while (0)
-#define BNL_PAIR_LAUNCH(BN, ITEMS, DEPTH, NPW, SUP, SMEM)                                                         \
+#define BNL_PAIR_LAUNCH(BN, ITEMS, DEPTH, NPW, SUP, NSTG, SMEM)                                                   \
   do {                                                                                                            \
-    if (any_na && wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, true, NPW, SUP, SMEM);                                \
-    else if (any_na) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, false, NPW, SUP, SMEM);                                  \
-    else if (wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, false, true, NPW, SUP, SMEM);                                    \
-    else BNL_PAIR_GO(BN, ITEMS, DEPTH, false, false, NPW, SUP, SMEM);                                             \
+    if (any_na && wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, true, NPW, SUP, NSTG, SMEM);                          \
+    else if (any_na) BNL_PAIR_GO(BN, ITEMS, DEPTH, true, false, NPW, SUP, NSTG, SMEM);                            \
+    else if (wide) BNL_PAIR_GO(BN, ITEMS, DEPTH, false, true, NPW, SUP, NSTG, SMEM);                              \
+    else BNL_PAIR_GO(BN, ITEMS, DEPTH, false, false, NPW, SUP, NSTG, SMEM);                                       \
   } while (0)
   // columns per producer thread: the tile's columns over 4 * NPW column lanes (19 + 1
   // warps measured 4 % faster than 11 + 1 on the wide tile, 15 + 1 and 23 + 1 slower)
   // two K-blocks per full / empty handshake (SUP = 2): a handshake has a floor of several hundred
   // cycles whatever the work behind it (config B level 0: 0.225 -> 0.173 ms, config C 3.58 -> 3.48 ms)
-  if (p.bn == 128 && nc <= 44) BNL_PAIR_LAUNCH(128, 1, 4, 11, 2, smem128);
-  else if (p.bn == 128) BNL_PAIR_LAUNCH(128, 2, 2, 19, 2, smem128);      // <= 130 columns over 76 lanes
-  else BNL_PAIR_LAUNCH(256, 3, 2, 19, 2, smem256);                       // <= 194 columns over 76 lanes
+  // The single-tile launches (L <= 128) keep 8 buffers of B rows only and shake hands every 4 K-blocks.
+  const size_t smem_diag = (size_t)8 * 128 * 128 + 1024;
+  if (p.bn == 128 && nc <= 44) BNL_PAIR_LAUNCH(128, 1, 2, 11, 4, 8, smem_diag);
+  else if (p.bn == 128) BNL_PAIR_LAUNCH(128, 2, 2, 19, 2, 8, smem_diag);              // <= 74 columns over 76 lanes
+  else BNL_PAIR_LAUNCH(256, 3, 2, 19, 2, PAIR_STAGES, smem256);                       // <= 218 columns over 76 lanes
 #undef BNL_PAIR_GO
 #undef BNL_PAIR_LAUNCH
   BNL_CUDA(ctx, cudaGetLastError());

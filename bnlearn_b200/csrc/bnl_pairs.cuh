@@ -149,15 +149,18 @@ __device__ __forceinline__ void sts128_if(uint32_t on, uint32_t addr, uint32_t a
 // are predicated instead of skipped, the trip count is padded to a multiple of the
 // ring depth (a padded stage stores nothing and its MMAs are predicated off), and the
 // levels past the fourth are compiled in only for the WIDE variant.
-template <int BN, int ITEMS, int DEPTH, bool NA, bool WIDE, int NPW, int SUP>
+template <int BN, int ITEMS, int DEPTH, bool NA, bool WIDE, int NPW, int SUP, int NSTG>
 __global__ void __launch_bounds__((NPW + 1) * 32, 1)
 pair_onehot_kernel(const uint8_t *__restrict__ u8, size_t stride, const int4 *__restrict__ cols,
                    const int *__restrict__ ind2col, int L, const int2 *__restrict__ tiles, int ntiles,
                    int stages_per_split, int total_stages, int *__restrict__ G, int ldg, int atomic_out) {
   using namespace bnlpair;
-  constexpr int A_BYTES = PAIR_BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+  // NSTG operand buffers. NSTG > PAIR_STAGES marks the single-tile launch (L <= 128): its one tile is
+  // diagonal, the A rows ARE the B rows, so a buffer holds the B rows only and twice as many fit.
+  constexpr bool DIAG = NSTG > PAIR_STAGES;
+  constexpr int A_BYTES = DIAG ? 0 : PAIR_BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
   // SUP operand buffers share one full / empty barrier pair ("one handshake per SUP K-blocks")
-  constexpr int NS = PAIR_STAGES, NSS = PAIR_STAGES / SUP;
+  constexpr int NS = NSTG, NSS = NSTG / SUP;
   static_assert((NSS & (NSS - 1)) == 0 && NSS >= 2, "barrier ring indexed with a mask");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // the dynamic window is only guaranteed 16-byte alignment: round up to the swizzle atom
