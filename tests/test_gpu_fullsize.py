@@ -172,6 +172,37 @@ def test_config_c_candidate_batches_against_reference(engine, ref, config_c, bas
             _close(sc[int(k)], want, ("bde", base_levels, cands[int(k)]))
 
 
+def test_config_c_first_iteration_against_reference(engine, ref, config_c):
+    """The first hc iteration at full size -- every arc i -> j, i < j, of the empty graph,
+    499 500 BDe scores from ONE tensor-core contraction (pair_onehot_kernel, unit descriptors
+    built on the device, warp-per-unit epilogue) -- and 30 of them, spread over the level
+    counts, against per_node_score("bde"); then the same through bnl_score_cache_fill with its
+    mirrored copies and counter (src/learning/score/hc.cache.lookup.c:52-117)."""
+    from bnlearn_b200 import callsites as cs
+    cols, lev, parents, d = config_c
+    n = len(cols)
+    tg = np.array([j for j in range(n) for i in range(j)], dtype=np.int32)
+    pa = np.array([i for j in range(n) for i in range(j)], dtype=np.int32)
+    sc, npar = d.score_discrete("bde", tg, (np.arange(len(tg) + 1, dtype=np.int32), pa), 1.0)
+    rng = np.random.default_rng(41)
+    picked = [int(k) for k in rng.choice(len(tg), size=30, replace=False)]
+    for k in picked:
+        want = _ref_bde(ref, cols, lev, int(tg[k]), [int(pa[k])])
+        _close(sc[k], want, ("bde", int(tg[k]), int(pa[k])))
+        assert npar[k] == (lev[tg[k]] - 1) * lev[pa[k]]
+    # the call site: deltas against the empty graph's node scores, both orientations filled
+    reference = d.score_discrete("bde", list(range(n)), [[]] * n, 1.0)[0]
+    amat = np.zeros((n, n), dtype=np.int32, order="F")
+    cache = np.zeros((n, n), order="F")
+    counter = cs.TestCounter()
+    cs.score_cache_fill(d, "bde", 1.0, amat, amat.copy(), list(range(n)), True, reference, cache, counter)
+    assert counter.value == n * (n - 1) // 2
+    for k in picked:
+        i, j = int(pa[k]), int(tg[k])
+        want = sc[k] - reference[j]
+        assert rel_close(cache[i, j], want, RTOL, 1e-6) and cache[j, i] == cache[i, j]
+
+
 def test_config_c_score_cache_fill_block_against_reference(engine, ref, config_c):
     """score_cache_fill (src/learning/score/hc.cache.lookup.c:10-128) on the first
     64 nodes of the 1 M-row data set, four updated nodes with 0-3 parents: cache
