@@ -779,6 +779,44 @@ def main():
     pageable = [np.array(c) for c in cols32] if rank == 0 else cols32
     dt_e2e_pageable = e2e_loop(pageable)
     del pageable
+
+    # N > 1: the same step with the ROWS sharded (reported beside the replicated one). Every rank
+    # uploads and packs 1/N of the rows, counts all 1081 tables on them, the int32 tables (137 KB)
+    # are summed on rank 0 by one NCCL reduce and rank 0 turns them into statistics with the same
+    # epilogue (bnl_counts + bnl_stat_from_tables): bit-identical outputs.
+    dt_e2e_rows, rows_sha1 = None, None
+    if world > 1:
+        xa = np.array([u[0] for u in units], dtype=np.int32)
+        ya = np.array([u[1] for u in units], dtype=np.int32)
+        za = csr([u[2] for u in units])
+        llx, lly, llz, nz, toff = ds.table_shapes(xa, ya, za)
+        h_tab = torch.zeros(int(toff[-1]), dtype=torch.int32).pin_memory()
+        d_tab = torch.zeros(int(toff[-1]), dtype=torch.int32, device=device)
+        ra, rb_ = rows * rank // world, rows * (rank + 1) // world
+        my_rows = [c[ra:rb_] for c in cols32]
+
+        def rows_step():
+            d3 = eng.register(my_rows, lev)
+            d3.counts_flat(xa, ya, za, toff, h_tab.numpy())
+            d_tab.copy_(h_tab, non_blocking=True)
+            dist.reduce(d_tab, dst=0)
+            out = None
+            if rank == 0:
+                h_tab.copy_(d_tab, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                out = eng.stat_from_flat("mi", llx, lly, llz, nz, h_tab.numpy(), toff, nrows=rows)
+            d3.release()
+            return out
+
+        rows_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            out = rows_step()
+        barrier()
+        dt_e2e_rows = (time.perf_counter() - t0) / args.steps
+        if rank == 0:
+            rows_sha1 = hashlib.sha1(np.ascontiguousarray(np.stack(out, axis=1)).tobytes()).hexdigest()[:16]
     clocks = sampler.stop()
 
     # diagnostic: plain pinned host -> device copy rate of this box.
@@ -792,9 +830,9 @@ def main():
 
     kms_local = float(np.mean(count_ms))
     if world > 1:
-        t = torch.tensor([dt, dt_e2e, dt_e2e_pageable, replica, kms_local], dtype=torch.float64, device="cuda")
+        t = torch.tensor([dt, dt_e2e, dt_e2e_pageable, replica, kms_local, dt_e2e_rows], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt, dt_e2e, dt_e2e_pageable, replica, kms = (float(v) for v in t)
+        dt, dt_e2e, dt_e2e_pageable, replica, kms, dt_e2e_rows = (float(v) for v in t)
         lt = torch.tensor([launches], dtype=torch.int64, device="cuda")
         dist.all_reduce(lt)
         launches = int(lt[0])
@@ -849,6 +887,16 @@ def main():
                               "the LAST timed step's gathered outputs, 8 tests per conditioning-set size",
             "roofline": roof,
         })
+        if dt_e2e_rows is not None:
+            # the row-sharded form of the same step, beside the replicated one: no faster on one node --
+            # the upload is bound by the HOST cores that pack the int32 codes, and N ranks share them --
+            # but it is the route for data that does not fit one GPU, and its outputs must be the same bits
+            line["e2e"]["rows_sharded"] = {
+                "value": n_units / dt_e2e_rows, "ms_per_step": dt_e2e_rows * 1e3, "outputs_sha1": rows_sha1,
+                "identical_to_unit_sharded": bool(rows_sha1 == outputs_sha1),
+                "how": "every rank registers 1/N of the rows from the pinned data frame, counts all %d tables on "
+                       "them, one NCCL reduce of the int32 tables (%d bytes) to rank 0, statistics there "
+                       "(bnl_counts + bnl_stat_from_tables)" % (n_units, 4 * int(toff[-1]))}
         if replica is not None:
             line["replicas"] = {"value": world * n_units / replica, "ms_per_step": replica * 1e3, "scaling": "weak",
                                 "what": "every rank runs the full list on its own replica (round 1's figure)"}

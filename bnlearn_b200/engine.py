@@ -81,6 +81,20 @@ class Engine:
         if rc != 0:
             raise BnlError(rc, self._lib.bnl_last_error(self._ctx).decode())
 
+    def stat_from_flat(self, name, llx, lly, llz, nz, flat, off, arg=0.0, nrows=0):
+        """bnl_stat_from_tables on a flat int32 buffer (tables at off[u], shapes as
+        DataSet.table_shapes gives them) -> three float64 arrays."""
+        kind = 0 if name in TESTS else 1
+        code = TESTS[name] if kind == 0 else SCORES[name]
+        n = len(llx)
+        o = [np.zeros(max(n, 1)) for _ in range(3)]
+        self._check(self._lib.bnl_stat_from_tables(self._ctx, kind, code, float(arg), int(nrows), n, _ip(llx),
+                                                   _ip(lly), _ip(llz), _ip(nz),
+                                                   flat.ctypes.data_as(_lib.c_i32_p),
+                                                   off.ctypes.data_as(_lib.c_i64_p), _dp(o[0]), _dp(o[1]),
+                                                   _dp(o[2])))
+        return o[0][:n], o[1][:n], o[2][:n]
+
     def stat_from_tables(self, name, tables, nz, arg=0.0, nrows=0):
         """Statistics from count tables shaped (llz, llx, lly) as DataSet.counts
         returns them (bnl_stat_from_tables): name is a discrete test -> (stat, df,
@@ -215,6 +229,33 @@ class DataSet:
                                    tab.ctypes.data_as(_lib.c_i32_p),
                                    off.ctypes.data_as(_lib.c_i64_p)))
         return [tab[off[u]:off[u + 1]].reshape(shapes[u]) for u in range(len(x))]
+
+    def table_shapes(self, x, y, z):
+        """(llx, lly, llz, nz, off) int arrays of the tables counts() would return, for the flat calls."""
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        zo, zi = _as_csr(z)
+        lev = np.asarray(self.nlevels, dtype=np.int64)
+        n = len(x)
+        llx = lev[x].astype(np.int32)
+        lly = np.where(y >= 0, lev[np.maximum(y, 0)], 1).astype(np.int32)
+        llz = np.ones(n, dtype=np.int64)
+        for u in range(n):
+            for j in zi[zo[u]:zo[u + 1]]:
+                llz[u] *= lev[j]
+        off = np.zeros(n + 1, dtype=np.int64)
+        off[1:] = np.cumsum(llx.astype(np.int64) * lly * llz)
+        return llx, lly, llz.astype(np.int32), np.diff(zo).astype(np.int32), off
+
+    def counts_flat(self, x, y, z, off, out):
+        """bnl_counts into the caller's flat int32 buffer `out` (tables at off[u]): no per-unit arrays."""
+        e = self.engine
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        zo, zi = _as_csr(z)
+        e._check(e._lib.bnl_counts(e._ctx, self.handle, len(x), _ip(x), _ip(y), _ip(zo), _ip(zi),
+                                   out.ctypes.data_as(_lib.c_i32_p), off.ctypes.data_as(_lib.c_i64_p)))
+        return out
 
     def ci_discrete(self, test, x, y, z):
         """Batch of discrete CI tests -> (statistic, df, p.value) arrays."""
