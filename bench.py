@@ -101,6 +101,31 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def measured_traffic(same_workload, compulsory):
+    """`roofline.traffic`: DRAM bytes of the step's counting launches from the ncu
+    capture under profiles/ (scripts/traffic_stamp.py) -- only while the capture
+    belongs to the kernel sources this run was built from and to this workload."""
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        from traffic_stamp import source_stamp
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if not same_workload:
+            return {"traffic": None, "traffic_note": "profiles/traffic.json holds the N = 1, 10M-row step only"}
+        if t.get("source_stamp") != source_stamp():
+            return {"traffic": None, "traffic_note": "profiles/traffic.json was captured on other kernel sources "
+                                                     "(stamp %s); re-run scripts/traffic_stamp.py" % t.get("source_stamp")}
+        k = {n: v["dram_bytes_per_launch"] for n, v in t["kernels"].items()
+             if n.startswith(("count_", "pair_onehot"))}
+        total = int(sum(k.values()))
+        return {"traffic": total, "traffic_by_kernel": k, "traffic_over_compulsory": total / compulsory,
+                "traffic_note": "ncu --set full capture of this command (profiles/traffic.json, "
+                                "profiles/r2_bench_step_kernel_details.csv): every counting launch of the step reads "
+                                "the packed columns from DRAM once (level 0 in the pair kernel, levels 1-2 in "
+                                "count_small), so the step moves one compulsory pass per launch and nothing more"}
+    except Exception as exc:                         # a missing capture must not cost the bench line
+        return {"traffic": None, "traffic_note": "no capture: %r" % (exc,)}
+
+
 # --------------------------------------------------------------------------
 # CPU legs: the reference's own C (oracle/_ref), forked over all host cores.
 
@@ -863,9 +888,8 @@ def main():
                               "to this batch: L2 serves the column reuse and the shared-memory atomic rate binds"
                               % (unit_bytes / comp_local))
         roof.pop("class")
-        roof.update({"kernel": "counting launches of one step (rank 0)", "peak_source": peak_src, "traffic": None,
-                     "traffic_note": "per-launch DRAM bytes come from ncu captures, kept under profiles/ with the "
-                                     "build they belong to; not read back into this line"})
+        roof.update({"kernel": "counting launches of one step (rank 0)", "peak_source": peak_src})
+        roof.update(measured_traffic(world == 1 and args.rows == 10_000_000, comp_local))
         line = dict(base)
         line.update({
             "value": n_units / dt, "ms_per_step": dt * 1e3, "clocks": clocks,
