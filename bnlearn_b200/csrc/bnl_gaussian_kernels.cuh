@@ -15,11 +15,11 @@
 #include "bnl_special.cuh"
 
 #define GRAM_TILE 128         // C tile edge per CTA
-#define GRAM_KB 16            // rows staged per pipeline stage
+#define GRAM_KB 32            // rows staged per pipeline stage
 #define GRAM_LD (GRAM_KB + 4) // smem row stride in doubles: conflict-free 64-bit fragment loads
-#define GRAM_STAGES 4
+#define GRAM_STAGES 3
 #define GRAM_THREADS 512
-#define GRAM_SMEM (GRAM_STAGES * 2 * GRAM_TILE * GRAM_LD * 8)
+#define GRAM_SMEM (GRAM_STAGES * 2 * GRAM_TILE * GRAM_LD * 8 + 64)   // + one mbarrier per stage
 #define BNL_GW (BNL_MAXK + 1) // ints per Gaussian unit descriptor: count, then column slots
 
 // ---------------------------------------------------------------------------
@@ -70,33 +70,80 @@ __device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, do
                : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gmem));
+namespace bnlgram {
+__device__ __forceinline__ unsigned su32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *b, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(su32(b)), "r"(count));
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N)); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(su32(b)), "r"(bytes) : "memory");
+}
+// one bulk copy (the TMA engine, UBLKCP in the SASS) global -> shared, completion counted in bytes on `b`
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *b) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(su32(dst)), "l"(src), "r"(bytes), "r"(su32(b)) : "memory");
+}
+// bounded: a protocol slip must end in a trap, not in a hung device
+__device__ __forceinline__ void mbar_wait(unsigned long long *b, unsigned parity) {
+  for (int tries = 0; tries < (1 << 26); tries++) {
+    unsigned done;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(done) : "r"(su32(b)), "r"(parity) : "memory");
+    if (done) return;
+  }
+  __trap();
+}
+}  // namespace bnlgram
 
-// One CTA = one upper-triangular 128 x 128 tile of C over one slice of the rows;
-// 16 warps in a 4 x 4 grid, each a 32 x 32 sub-tile = 4 x 4 DMMA tiles. Raw
-// columns stream into a 4-stage cp.async ring (16 rows per stage); they are
-// centred when the fragments are read from shared memory (means in registers),
-// and rows past nobs are masked to zero in the last stage only.
+// X - mean for rows [0, nrows_pad), zero past nobs: the operand the Gram kernel reads when
+// there is room for it (one pass at the HBM rate; the subtraction then costs the DMMA pipe
+// nothing).
+__global__ void __launch_bounds__(256)
+gram_centre_kernel(const double *__restrict__ X, size_t stride, long long nobs,
+                   long long nrows_pad, const double *__restrict__ mean, double *__restrict__ out) {
+  const int col = blockIdx.y;
+  const double m = mean[col];
+  const double2 *src = reinterpret_cast<const double2 *>(X + (size_t)col * stride);
+  double2 *dst = reinterpret_cast<double2 *>(out + (size_t)col * (size_t)nrows_pad);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nrows_pad / 2;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = 2 * i;
+    double2 v = make_double2(0.0, 0.0);
+    if (r + 1 < nobs) { v = src[i]; v.x -= m; v.y -= m; }
+    else if (r < nobs) { v.x = X[(size_t)col * stride + r] - m; }
+    dst[i] = v;
+  }
+}
+
+// One CTA = one upper-triangular 128 x 128 tile of C over one slice of the rows of the view
+// it is given; 16 warps in a 4 x 4 grid, each a 32 x 32 sub-tile = 4 x 4 DMMA tiles. The rows
+// stream through a 3-stage ring of 32-row stages filled by the bulk-copy engine: one
+// cp.async.bulk of 256 bytes per column and stage, issued by 256 threads (one column each),
+// their bytes counted on the stage's mbarrier. (With cp.async -- 4 LDGSTS of 16 bytes per
+// thread and operand -- the copies cost the DMMA pipe 8 %; the bulk engine's cost is within
+// 1.5 % of no copies at all, profiles/r2_gram_probe.txt.)
+//   PRE = true   X is gram_centre_kernel's output for the slab: centred, zero past nobs, `rows`
+//                a multiple of GRAM_KB -- the inner loop is LDS.64 + DMMA only.
+//   PRE = false  X is the raw data (no scratch memory to be had): after a stage has landed
+//                every thread centres and masks 1/512 of it in shared memory, then the barrier.
+// The warp grid is laid out so that the four warps of an all-padding column block (p = 2000:
+// columns 2016-2047 of the last tile column) sit on four different schedulers and just skip.
+template <bool PRE>
 __global__ void __launch_bounds__(GRAM_THREADS, 1)
-gram_dmma_kernel(const double *__restrict__ X, size_t stride, long long nobs, int p,
+gram_dmma_kernel(const double *__restrict__ X, size_t stride, long long rows, int p,
                  const double *__restrict__ mean, double *__restrict__ partial, int ntile) {
   extern __shared__ __align__(16) double gsm_tiles[];
   typedef double (*tile_t)[GRAM_TILE][GRAM_LD];
   tile_t As = reinterpret_cast<tile_t>(gsm_tiles);
   tile_t Bs = reinterpret_cast<tile_t>(gsm_tiles + (size_t)GRAM_STAGES * GRAM_TILE * GRAM_LD);
+  unsigned long long *full = reinterpret_cast<unsigned long long *>(gsm_tiles + (size_t)2 * GRAM_STAGES * GRAM_TILE * GRAM_LD);
 
   int t = blockIdx.x, ti = 0;
   while (t >= ntile - ti) { t -= ntile - ti; ti++; }
   const int tj = ti + t;
   const bool diag = ti == tj;
   const int nsplit = gridDim.y, split = blockIdx.y;
-  const long long steps = (nobs + GRAM_KB - 1) / GRAM_KB;
+  const long long steps = (rows + GRAM_KB - 1) / GRAM_KB;
   const long long per = (steps + nsplit - 1) / nsplit;
   const long long s0 = per * split;
   long long s1 = s0 + per;
@@ -104,73 +151,99 @@ gram_dmma_kernel(const double *__restrict__ X, size_t stride, long long nobs, in
   const int nst = (int)(s1 > s0 ? s1 - s0 : 0);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int wm = (warp >> 2) * 32, wn = (warp & 3) * 32;
+  // a diagonal tile needs only the 10 blocks on and above its diagonal: warps 0-9 take them
+  // (3, 3, 2, 2 per scheduler instead of 4 each), gram_finish_kernel mirrors the rest
+  int bi = warp & 3, bj = warp >> 2;
+  if (diag && warp < 10) { bi = (int)((0x3221110000ull >> (4 * warp)) & 15); bj = (int)((0x3323213210ull >> (4 * warp)) & 15); }
+  const int wm = bi * 32, wn = bj * 32;
   const int g = lane >> 2, q = lane & 3;
+  // nothing this warp could compute is wanted: it only copies and synchronises
+  const bool idle = (diag && warp >= 10) || ti * GRAM_TILE + wm >= p || tj * GRAM_TILE + wn >= p;
 
-  // this thread's share of a stage: 128 columns x 8 double2 per operand = 1024
-  // 16-byte copies per operand, 2 per thread.
-  auto issue = [&](int s_local) {
-    const long long r0 = (s0 + s_local) * GRAM_KB;
-    const int buf = s_local % GRAM_STAGES;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < GRAM_STAGES; i++) bnlgram::mbar_init(&full[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  // copies: threads 0-127 one column of the A operand each, 128-255 of the B operand
+  const int myc = threadIdx.x & 127;
+  const bool copier = threadIdx.x < (diag ? 128 : 256);
+  int mycol = (threadIdx.x < 128 ? ti : tj) * GRAM_TILE + myc;
+  if (mycol >= p) mycol = p - 1;
+  const double *mysrc = X + (size_t)mycol * stride;
+  const unsigned stage_bytes = (diag ? 1u : 2u) * GRAM_TILE * GRAM_KB * 8;
+  auto expect = [&](int sl) { if (threadIdx.x == 0) bnlgram::mbar_expect_tx(&full[sl % GRAM_STAGES], stage_bytes); };
+  auto issue = [&](int sl) {
+    if (!copier) return;
+    const int buf = sl % GRAM_STAGES;
+    double *dst = threadIdx.x < 128 ? &As[buf][myc][0] : &Bs[buf][myc][0];
+    if (!PRE) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // this thread's centring stores, then the engine's
+    bnlgram::bulk_g2s(dst, mysrc + (s0 + sl) * GRAM_KB, GRAM_KB * 8, &full[buf]);
+  };
+
+  // PRE = false: this thread's share of a landed stage, GRAM_CREPS 16-byte chunks per operand
+  constexpr int CPC = GRAM_KB / 2, CREPS = GRAM_TILE * CPC / GRAM_THREADS;
+  double cma[CREPS], cmb[CREPS];
 #pragma unroll
-    for (int rep = 0; rep < 2; rep++) {
+  for (int rep = 0; rep < CREPS; rep++) {
+    const int c = (threadIdx.x + rep * GRAM_THREADS) / CPC;
+    int col = ti * GRAM_TILE + c; if (col >= p) col = p - 1;
+    cma[rep] = PRE ? 0.0 : mean[col];
+    col = tj * GRAM_TILE + c; if (col >= p) col = p - 1;
+    cmb[rep] = PRE ? 0.0 : mean[col];
+  }
+  auto centre_own = [&](int sl) {
+    const long long r0 = (s0 + sl) * GRAM_KB;
+    const int buf = sl % GRAM_STAGES;
+#pragma unroll
+    for (int rep = 0; rep < CREPS; rep++) {
       const int idx = threadIdx.x + rep * GRAM_THREADS;
-      const int c = idx >> 3, r2 = (idx & 7) * 2;
-      int col = ti * GRAM_TILE + c;
-      if (col >= p) col = p - 1;
-      cp_async16(&As[buf][c][r2], X + (size_t)col * stride + r0 + r2);
+      const int c = idx / CPC, r2 = (idx % CPC) * 2;
+      const bool l0 = r0 + r2 < rows, l1 = r0 + r2 + 1 < rows;
+      double2 v = *reinterpret_cast<double2 *>(&As[buf][c][r2]);
+      v.x = l0 ? v.x - cma[rep] : 0.0; v.y = l1 ? v.y - cma[rep] : 0.0;
+      *reinterpret_cast<double2 *>(&As[buf][c][r2]) = v;
       if (!diag) {
-        col = tj * GRAM_TILE + c;
-        if (col >= p) col = p - 1;
-        cp_async16(&Bs[buf][c][r2], X + (size_t)col * stride + r0 + r2);
+        double2 w = *reinterpret_cast<double2 *>(&Bs[buf][c][r2]);
+        w.x = l0 ? w.x - cmb[rep] : 0.0; w.y = l1 ? w.y - cmb[rep] : 0.0;
+        *reinterpret_cast<double2 *>(&Bs[buf][c][r2]) = w;
       }
     }
   };
 
-  double ma[4], mb[4];
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    int col = ti * GRAM_TILE + wm + i * 8 + g;
-    ma[i] = mean[col < p ? col : p - 1];
-    col = tj * GRAM_TILE + wn + i * 8 + g;
-    mb[i] = mean[col < p ? col : p - 1];
-  }
   double acc[4][4][2];
 #pragma unroll
   for (int i = 0; i < 4; i++)
 #pragma unroll
     for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-#pragma unroll
-  for (int s = 0; s < GRAM_STAGES - 1; s++) {
-    if (s < nst) issue(s);
-    cp_async_commit();
-  }
+  for (int s = 0; s < GRAM_STAGES - 1; s++) if (s < nst) expect(s);
+  __syncthreads();
+  for (int s = 0; s < GRAM_STAGES - 1; s++) if (s < nst) issue(s);
   for (int s = 0; s < nst; s++) {
-    cp_async_wait<GRAM_STAGES - 2>();
-    __syncthreads();
-    if (s + GRAM_STAGES - 1 < nst) issue(s + GRAM_STAGES - 1);
-    cp_async_commit();
     const int buf = s % GRAM_STAGES;
+    bnlgram::mbar_wait(&full[buf], (unsigned)((s / GRAM_STAGES) & 1));
+    if (!PRE) centre_own(s);
+    if (s + GRAM_STAGES - 1 < nst) expect(s + GRAM_STAGES - 1);
+    __syncthreads();                    // stage s centred and visible; everyone is done reading stage s - 1
+    if (s + GRAM_STAGES - 1 < nst) issue(s + GRAM_STAGES - 1);
+    if (idle) continue;
     const double (*Ap)[GRAM_LD] = As[buf];
     const double (*Bp)[GRAM_LD] = diag ? As[buf] : Bs[buf];
-    const long long r0 = (s0 + s) * GRAM_KB;
-    const bool ragged = r0 + GRAM_KB > nobs;
 #pragma unroll
     for (int kk = 0; kk < GRAM_KB; kk += 4) {
       double a[4], b[4];
-      const bool live = !ragged || (r0 + kk + q < nobs);
 #pragma unroll
-      for (int i = 0; i < 4; i++) a[i] = live ? Ap[wm + i * 8 + g][kk + q] - ma[i] : 0.0;
+      for (int i = 0; i < 4; i++) a[i] = Ap[wm + i * 8 + g][kk + q];
 #pragma unroll
-      for (int j = 0; j < 4; j++) b[j] = live ? Bp[wn + j * 8 + g][kk + q] - mb[j] : 0.0;
+      for (int j = 0; j < 4; j++) b[j] = Bp[wn + j * 8 + g][kk + q];
 #pragma unroll
       for (int i = 0; i < 4; i++)
 #pragma unroll
         for (int j = 0; j < 4; j++) dmma_m8n8k4(acc[i][j][0], acc[i][j][1], a[i], b[j]);
     }
   }
-  cp_async_wait<0>();
 
   double *out = partial + (size_t)split * p * p;
 #pragma unroll
@@ -190,12 +263,12 @@ __global__ void gram_finish_kernel(const double *__restrict__ partial, int nspli
   const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (e >= (long long)p * p) return;
   const int i = (int)(e % p), j = (int)(e / p);
-  if (i / GRAM_TILE > j / GRAM_TILE) return;     // lower-triangular tiles are never written
+  if (i > j) return;                             // only blocks on or above the diagonal are written
   bnl::KahanSum t;
   for (int s = 0; s < nsplit; s++) t.add(partial[(size_t)s * p * p + e]);
   const double v = nobs > 1 ? t.value() / (double)(nobs - 1) : 0.0;
   cov[e] = v;
-  if (i / GRAM_TILE < j / GRAM_TILE) cov[(size_t)j + (size_t)i * p] = v;
+  if (i < j) cov[(size_t)j + (size_t)i * p] = v;
 }
 
 // ---------------------------------------------------------------------------

@@ -481,6 +481,27 @@ def test_gaussian_moments_against_numpy(engine):
     d.release()
 
 
+@pytest.mark.parametrize("scratch", ["1", "0"])
+def test_gram_routes_against_numpy(engine, monkeypatch, scratch):
+    """The Gram kernel's two routes -- the data set centred into scratch memory first, or
+    each stage centred in shared memory when there is no room for that -- on a shape with
+    ragged rows (not a multiple of the 32-row stage), a ragged last column tile and means far
+    from zero (c_covmat, src/core/covariance.matrix.c:65-97)."""
+    monkeypatch.setenv("BNL_GRAM_SCRATCH", scratch)
+    rng = np.random.default_rng(11)
+    n, p = 70003, 161
+    x = rng.normal(size=(p, n)) * rng.uniform(0.5, 3, size=(p, 1)) + rng.normal(size=(p, 1)) * 100
+    x[7] = 0.5 * x[3] - x[150] + rng.normal(size=n) * 0.05
+    d = engine.register(list(x))
+    mean, cov = d.moments()
+    d.release()
+    assert np.allclose(mean, x.mean(axis=1), rtol=1e-13, atol=1e-13)
+    xc = x - x.mean(axis=1, keepdims=True)
+    ref = (xc @ xc.T) / (n - 1)
+    assert np.allclose(cov, ref, rtol=1e-11, atol=1e-11)
+    assert np.array_equal(cov, cov.T)
+
+
 def test_gaussian_against_oracle_synthetic(engine):
     from oracle import oracle as orc
     rng = np.random.default_rng(9)
