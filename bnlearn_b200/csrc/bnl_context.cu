@@ -303,6 +303,8 @@ static void free_dataset(bnl_ctx *ctx, BnlDataSet &ds) {
     cudaSetDevice(ctx->devs[i].id);
     BnlDeviceData &d = ds.dev[i];
     bnl_pool_free(ctx->devs[i], d.u8, d.u8_bytes);
+    bnl_pool_free(ctx->devs[i], d.u4, d.u4_bytes);
+    d.u4 = nullptr; d.u4_bytes = 0;
     bnl_pool_free(ctx->devs[i], d.u16, d.u16_bytes);
     bnl_pool_free(ctx->devs[i], d.f64, d.f64_bytes);
     bnl_pool_free(ctx->devs[i], d.mean, d.mean_bytes);
@@ -973,6 +975,9 @@ extern "C" int bnl_data_commit(bnl_ctx *ctx, bnl_data data) {
     for (size_t d = 0; d < ctx->devs.size(); d++) {
       BnlDevice &dev = ctx->devs[d];
       BNL_CUDA(ctx, cudaSetDevice(dev.id));
+      // the caller may have rewritten the columns: a nibble copy made from the old ones is void
+      BnlDeviceData &ddc = ds.dev[d];
+      if (ddc.u4) { BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream)); bnl_pool_free(dev, ddc.u4, ddc.u4_bytes); ddc.u4 = nullptr; ddc.u4_bytes = 0; }
       if ((rc = bnl_reserve_device(ctx, &dev.d_flags, &dev.flags_cap, (size_t)(2 + 2 * ds.nd)))) return rc;
       int *d_lv = dev.d_flags + 1 + ds.nd;
       BNL_CUDA(ctx, cudaMemsetAsync(dev.d_flags, 0, (size_t)(1 + ds.nd) * sizeof(int), dev.stream));

@@ -46,6 +46,13 @@ const size_t kMaxBaseScratch = (size_t)1 << 30;   // bytes of base-index columns
 // all-pairs contraction on the tensor cores (bnl_pairs.cu): 0 off, 1 when the cost model prefers it,
 // 2 whenever eligible. Read at every call, so that a test can switch it inside one process.
 long long knob_pairs() { return env_ll("BNL_PAIRS", 1); }
+// nibble copy of the factor columns for the small-table kernel (count_small_kernel<false>): 0 off;
+// otherwise the least number of rows from which it is made (first use on a data set and device).
+long long knob_nibbles() { return env_ll("BNL_NIBBLES", 262144); }
+// ... and the number of earlier counting calls on the data set before it is made: a data set that is
+// registered, counted once and released (bench.py's end-to-end step) would pay for the copy (0.1 ms
+// per 370 MB) about what it saves.
+long long knob_nibbles_after() { return env_ll("BNL_NIBBLES_AFTER", 1); }
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
 const int kMaxBatchUnits = 1 << 19;           // the first hc iteration on 1000 nodes (499 500 units) is one batch
@@ -459,6 +466,40 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         cmax[0] = 256;
       }
     }
+    // The rest of the small-table class reads the nibble copy of its columns when every one of
+    // them has one (at most 15 levels) and none holds NA: half the bytes through the LSU pipe.
+    // The copy is made the first time a data set of enough rows is counted this way.
+    {
+      const long long nib_min = knob_nibbles();
+      const bool seen_before = dd.u4 || dd.small_calls >= knob_nibbles_after();
+      if (!cls[0].empty()) dd.small_calls++;
+      if (nib_min > 0 && ds.nobs >= nib_min && !cls[0].empty() && seen_before) {
+        std::vector<unsigned char> on(ds.nd, 0);
+        for (int c = 0; c < ds.ncols; c++)
+          if (!ds.is_numeric[c] && !ds.is_wide[c]) on[ds.slot[c]] = ds.nlevels[c] <= 15;
+        int wanted = 0;
+        for (int i : cls[0]) {
+          BnlUnit &hu = dev.h_units[i];
+          if (hu.mode != 0 || hu.has_na) continue;
+          bool ok = true;
+          for (int k = 0; k < hu.ncols; k++) ok = ok && on[hu.col[k]];
+          if (ok) { hu.mode = 2; wanted++; }
+        }
+        if (wanted && !dd.u4) {
+          const size_t stride4 = ds.stride_u8 / 2;
+          dd.u4_bytes = stride4 * ds.nd;
+          if ((rc = bnl_pool_alloc(ctx, dev, (void **)&dd.u4, dd.u4_bytes))) return rc;
+          if ((rc = bnl_reserve_device(ctx, &dev.d_flags, &dev.flags_cap, (size_t)ds.nd / 4 + 2))) return rc;
+          const unsigned char *d_on = reinterpret_cast<const unsigned char *>(dev.d_flags);
+          BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_flags, on.data(), (size_t)ds.nd, cudaMemcpyHostToDevice, dev.stream));
+          const unsigned gx = (unsigned)std::max<long long>(1, std::min<long long>(((long long)(stride4 / 16) + 255) / 256,
+                                                                                   (long long)dev.sm_count * 4));
+          bnl_nibbles_kernel<<<dim3(gx, (unsigned)ds.nd), 256, 0, dev.stream>>>(dd.u8, ds.stride_u8, d_on, dd.u4, stride4);
+          BNL_CUDA(ctx, cudaGetLastError());
+          BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));     // `on` is a local
+        }
+      }
+    }
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_order, &dev.h_order_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
     int n_ungrouped = 0, n_before_tests = 0;
@@ -624,7 +665,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       if (!cls[0].empty()) {
         const int ch = pick_chunks(cls[0], 3);
         count_small_kernel<false><<<(unsigned)cls[0].size() * ch, BNL_CNT_THREADS, (size_t)cmax[0] * 256, dev.stream>>>(
-            dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[0].size(), ch);
+            dd.u8, ds.stride_u8, ds.nobs, dev.d_units, dev.d_order + base, dev.d_tables, (int)cls[0].size(), ch,
+            dd.u4, ds.stride_u8 / 2);
         BNL_CUDA(ctx, cudaGetLastError());
         tm->launches++;
       }

@@ -366,6 +366,75 @@ __device__ __forceinline__ void small_rows_any(const uint8_t *__restrict__ u8, s
   }
 }
 
+// The same from the NIBBLE copy of the columns (bnl_nibbles_kernel: two codes per byte, factors
+// of at most 15 levels, units without NA): 32 rows per 128-bit load, so half the bytes cross
+// the LSU pipe that the atomics already keep busy. Byte j of a column holds row 2j in its low
+// nibble and row 2j + 1 in the high one; a table does not care in which order rows arrive.
+// NC = 0: the column count is the unit's (more than 4 columns).
+template <int NC>
+__device__ __forceinline__ void small_rows_nib(const uint8_t *__restrict__ u4, size_t stride4,
+                                               const BnlUnit &su, int *hist, unsigned slot4,
+                                               long long g0, long long g1) {
+  constexpr int NCA = NC ? NC : 1;
+  const uint4 *p[NCA];
+  unsigned m[NCA];
+#pragma unroll
+  for (int k = 0; k < NCA; k++) {
+    p[k] = reinterpret_cast<const uint4 *>(u4 + (size_t)su.col[k] * stride4);
+    m[k] = (unsigned)su.mul[k];
+  }
+  const unsigned M = 0x0F0F0F0Fu;
+  for (long long g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+    uint4 lo, hi;
+    if (NC) {
+      uint4 w[NCA];
+#pragma unroll
+      for (int k = 0; k < NCA; k++) w[k] = ldg_stream(p[k] + g);
+      lo = make_uint4(w[0].x & M, w[0].y & M, w[0].z & M, w[0].w & M);       // the first column has multiplier 1
+      hi = make_uint4((w[0].x >> 4) & M, (w[0].y >> 4) & M, (w[0].z >> 4) & M, (w[0].w >> 4) & M);
+#pragma unroll
+      for (int k = 1; k < NCA; k++) {
+        lo.x += (w[k].x & M) * m[k]; lo.y += (w[k].y & M) * m[k]; lo.z += (w[k].z & M) * m[k]; lo.w += (w[k].w & M) * m[k];
+        hi.x += ((w[k].x >> 4) & M) * m[k]; hi.y += ((w[k].y >> 4) & M) * m[k];
+        hi.z += ((w[k].z >> 4) & M) * m[k]; hi.w += ((w[k].w >> 4) & M) * m[k];
+      }
+    } else {
+      lo = hi = make_uint4(0u, 0u, 0u, 0u);
+      for (int k = 0; k < su.ncols; k++) {
+        const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u4 + (size_t)su.col[k] * stride4) + g);
+        const unsigned mk = (unsigned)su.mul[k];
+        lo.x += (w.x & M) * mk; lo.y += (w.y & M) * mk; lo.z += (w.z & M) * mk; lo.w += (w.w & M) * mk;
+        hi.x += ((w.x >> 4) & M) * mk; hi.y += ((w.y >> 4) & M) * mk; hi.z += ((w.z >> 4) & M) * mk; hi.w += ((w.w >> 4) & M) * mk;
+      }
+    }
+    small_bump(hist, lo.x, slot4); small_bump(hist, hi.x, slot4);
+    small_bump(hist, lo.y, slot4); small_bump(hist, hi.y, slot4);
+    small_bump(hist, lo.z, slot4); small_bump(hist, hi.z, slot4);
+    small_bump(hist, lo.w, slot4); small_bump(hist, hi.w, slot4);
+  }
+}
+
+// two codes per byte: 0xFF (NA, padding) becomes 0xF. grid (32-row groups, columns); only the
+// columns flagged in `on` (at most 15 levels) are written.
+__global__ void __launch_bounds__(256)
+bnl_nibbles_kernel(const uint8_t *__restrict__ u8, size_t stride, const unsigned char *__restrict__ on,
+                   uint8_t *__restrict__ u4, size_t stride4) {
+  const int c = blockIdx.y;
+  if (!on[c]) return;
+  const uint4 *src = reinterpret_cast<const uint4 *>(u8 + (size_t)c * stride);
+  uint4 *dst = reinterpret_cast<uint4 *>(u4 + (size_t)c * stride4);
+  const long long n = (long long)(stride4 / 16);
+  for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < n; g += (long long)gridDim.x * blockDim.x) {
+    const uint4 a = ldg_stream(src + 2 * g), b = ldg_stream(src + 2 * g + 1);
+    const unsigned w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    unsigned t[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { const unsigned q = w[i] & 0x0F0F0F0Fu; t[i] = q | (q >> 4); }
+    dst[g] = make_uint4(__byte_perm(t[0], t[1], 0x6420), __byte_perm(t[2], t[3], 0x6420),
+                        __byte_perm(t[4], t[5], 0x6420), __byte_perm(t[6], t[7], 0x6420));
+  }
+}
+
 template <bool NA, bool W16, bool PAIR>
 __device__ __forceinline__ void small_dispatch(const uint8_t *__restrict__ u8, size_t stride,
                                                const BnlUnit &su, int *hist, unsigned slot4,
@@ -394,7 +463,8 @@ template <bool W16>
 __global__ void __launch_bounds__(W16 ? 1024 : BNL_CNT_THREADS)
 count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
-                   int *__restrict__ tables, int nunits, int chunks) {
+                   int *__restrict__ tables, int nunits, int chunks,
+                   const uint8_t *__restrict__ u4 = nullptr, size_t stride4 = 0) {
   extern __shared__ __align__(256) int hist[];      // cells x 64 counters
   __shared__ BnlUnit su;
   const int chunk = blockIdx.x / nunits, u = order[blockIdx.x % nunits];
@@ -415,12 +485,37 @@ count_small_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   __syncthreads();
   const unsigned slot4 = ((threadIdx.x & 31u) + 32u * ((threadIdx.x >> 5) & 1u)) << 2;
 
+  int *gtab = tables + su.table_off;
+  if (!W16 && su.mode == 2) {
+    // nibble copy: complete 32-row groups; the rows left over, once, from the byte columns
+    const long long full4 = nobs / 32;
+    const long long per4 = (full4 + chunks - 1) / chunks;
+    const long long h0 = per4 * chunk;
+    long long h1 = h0 + per4;
+    if (h1 > full4) h1 = full4;
+    switch (su.ncols) {
+      case 1: small_rows_nib<1>(u4, stride4, su, hist, slot4, h0, h1); break;
+      case 2: small_rows_nib<2>(u4, stride4, su, hist, slot4, h0, h1); break;
+      case 3: small_rows_nib<3>(u4, stride4, su, hist, slot4, h0, h1); break;
+      case 4: small_rows_nib<4>(u4, stride4, su, hist, slot4, h0, h1); break;
+      default: small_rows_nib<0>(u4, stride4, su, hist, slot4, h0, h1);
+    }
+    if (chunk == chunks - 1 && threadIdx.x == 0 && full4 * 32 < nobs)
+      small_rows_scalar(u8, stride, su, hist, slot4, full4 * 32, (int)(nobs - full4 * 32));
+    __syncthreads();
+    for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+      int sum = 0;
+#pragma unroll
+      for (int l = 0; l < 64; l++) sum += hist[c * 64 + ((l + threadIdx.x) & 63)];
+      if (sum) atomicAdd(&gtab[c], sum);
+    }
+    return;
+  }
   const long long full = nobs / 16;                  // complete 16-row groups
   const long long per = (full + chunks - 1) / chunks;
   const long long g0 = per * chunk;
   long long g1 = g0 + per;
   if (g1 > full) g1 = full;
-  int *gtab = tables + su.table_off;
 
   if (pair) small_dispatch<false, false, true>(u8, stride, su, hist, slot4, g0, g1);
   else if (su.has_na) small_dispatch<true, W16, false>(u8, stride, su, hist, slot4, g0, g1);

@@ -89,6 +89,9 @@ struct BnlDeviceData {
   double *cov = nullptr;       // nc x nc, column-major, divisor nobs - 1
   uint16_t *u16 = nullptr;     // nw wide factor columns, stride_u16 elements apart
   size_t u16_bytes = 0;
+  uint8_t *u4 = nullptr;       // nibble copy of the u8 block (two codes per byte, stride_u8 / 2 apart), built on first use
+  size_t u4_bytes = 0;
+  int small_calls = 0;         // counting calls with small tables seen so far (the nibble copy waits for the second)
   double *bge_nu = nullptr;    // nc prior means of the BGe score (null: the column means)
   size_t u8_bytes = 0, f64_bytes = 0, mean_bytes = 0, cov_bytes = 0, nu_bytes = 0;
 };

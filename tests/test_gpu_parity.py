@@ -585,6 +585,63 @@ def test_every_table_size_class(engine, with_na):
     d.release()
 
 
+@pytest.mark.parametrize("n", [31, 70001, 300003])
+def test_nibble_copy_route_counts_bit_exact(engine, monkeypatch, n):
+    """count_small_kernel reading the nibble copy of the columns (two codes per byte; units
+    of <= 256 cells whose columns have at most 15 levels and no NA): tables bit-exact against
+    fill_1d/2d/3d_table (src/core/contingency.tables.c:20-223) for 1-6 columns per table,
+    ragged row counts (the rows past the last 32-row group come from the byte columns), next
+    to units that must stay on the byte route (a 16-level column, a column with NA)."""
+    from oracle import oracle as orc
+    monkeypatch.setenv("BNL_NIBBLES", "1")
+    monkeypatch.setenv("BNL_NIBBLES_AFTER", "0")
+    monkeypatch.setenv("BNL_PAIRS", "0")           # keep the one- and two-way tables in this kernel too
+    rng = np.random.default_rng(23)
+    lev = [2, 3, 4, 2, 2, 15, 16, 3, 2, 5]
+    cols = [rng.integers(1, l + 1, n).astype(np.int32) for l in lev]
+    cols[7][rng.random(n) < 0.02] = orc.NA_INT      # column 7 holds NA
+    d = engine.register(cols, lev)
+    units = [(0, None, []), (1, 2, []), (5, 1, []), (0, 1, [2]), (1, 2, [0, 3]), (0, 1, [3, 4, 8]),
+             (0, 3, [4, 8, 1, 2]), (9, 5, [0]),
+             (6, 1, []), (1, 7, [0]), (0, 6, [3])]        # byte route: 16 levels, NA
+    xs, ys, zs = [u[0] for u in units], [u[1] if u[1] is not None else -1 for u in units], [u[2] for u in units]
+    for rep in range(2):                             # second call: the copy exists already
+        tabs = d.counts(xs, ys, zs)
+        for (x, y, z), t in zip(units, tabs):
+            if y is None:
+                ref = np.bincount(cols[x] - 1, minlength=lev[x])
+                assert np.array_equal(np.asarray(t).ravel(), ref), (x, n)
+                continue
+            ref = orc.counts(cols[x], lev[x], cols[y], lev[y], [cols[i] for i in z], [lev[i] for i in z])
+            assert np.array_equal(t, ref), (x, y, z, n)
+    d.release()
+
+
+def test_nibble_copy_is_rebuilt_after_commit(engine, monkeypatch):
+    """bnl_data_commit voids a nibble copy made from the previous contents of the columns."""
+    import torch
+    monkeypatch.setenv("BNL_NIBBLES", "1")
+    monkeypatch.setenv("BNL_NIBBLES_AFTER", "0")
+    monkeypatch.setenv("BNL_PAIRS", "0")
+    rng = np.random.default_rng(5)
+    n, lev = 50000, [3, 2, 4]
+    d = engine.alloc(lev, n)
+    u8, nu, _, _ = d.device_view(0)
+    from bnlearn_b200.replicate import _as_tensor
+    view = _as_tensor(u8, nu).view(len(lev), -1)
+    for trial in range(2):
+        cols = [rng.integers(0, l, n).astype(np.uint8) for l in lev]
+        for i, c in enumerate(cols):
+            view[i, :n] = torch.from_numpy(c).cuda()
+        torch.cuda.synchronize()
+        d.commit()
+        t = d.counts([0], [1], [[2]])[0]
+        ref = np.zeros((lev[2], lev[0], lev[1]), dtype=np.int64)
+        np.add.at(ref, (cols[2], cols[0], cols[1]), 1)
+        assert np.array_equal(np.asarray(t).reshape(ref.shape), ref), trial
+    d.release()
+
+
 def test_mbde_against_reference_golden(engine):
     """mBDe = BDe over the rows on which the node was not intervened upon: the
     interventions arrive as one-level mask columns (NA on those rows) registered
