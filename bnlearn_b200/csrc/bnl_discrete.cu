@@ -205,6 +205,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     }
     if (cnt == 0) return bnl_fail(ctx, BNL_EUNSUPPORTED, "table too large for the scratch buffer");
     int rc;
+    std::unique_ptr<BnlTraceScope> tr_cls(new BnlTraceScope("run_block: classify"));
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_units, &dev.h_units_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_units, &dev.units_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_tables, &dev.tables_cap, (size_t)cells))) return rc;
@@ -558,6 +559,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       return (int)std::max(1ll, ch);
     };
 
+    tr_cls.reset();
     std::unique_ptr<BnlTraceScope> tr_enq(new BnlTraceScope("run_block: enqueue"));
     BNL_CUDA(ctx, cudaEventRecord(dev.ev0, dev.stream));
     BNL_CUDA(ctx, cudaMemcpyAsync(dev.d_units, dev.h_units, (size_t)cnt * sizeof(BnlUnit),
@@ -780,6 +782,7 @@ int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, 
                   const int *z_off, const int *z_idx, double *o0, double *o1, double *o2, int32_t *tables,
                   const int64_t *table_off, bool *handled) {
   *handled = false;
+  BNL_TRACE("compact_pairs: whole call");
   const long long knob = knob_pairs();
   if (!knob || n < 4096 || n > kMaxBatchUnits || ctx->devs.size() != 1 || ds.nobs < 4096 || ds.nd == 0) return BNL_OK;
   if (kind == 0 && (code == BNL_JT || code == BNL_MI_SH)) return BNL_OK;
@@ -801,6 +804,7 @@ int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, 
   std::vector<char> used(ds.nd, 0);
   long long cells = 0;
   bool warp_ok = true;
+  std::unique_ptr<BnlTraceScope> tr_prep(new BnlTraceScope("compact_pairs: index arrays"));
   for (int u = 0; u < n; u++) {
     const int nz = z_off[u + 1] - z_off[u];
     int c0, c1 = -1;
@@ -830,7 +834,9 @@ int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, 
     cells += (long long)l0 * l1;
   }
   if (cells > kMaxBatchCells) return BNL_OK;
+  tr_prep.reset();
   {
+    BNL_TRACE("compact_pairs: cost model");
     double tensor_s, atomic_s;
     bnl_pairs_cost(dev, ds, used, n, lev_by_slot, &tensor_s, &atomic_s, h_cc);
     if (!(knob >= 2 ? tensor_s < 1e29 : tensor_s < 0.8 * atomic_s)) return BNL_OK;
@@ -856,7 +862,7 @@ int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, 
   BNL_CUDA(ctx, cudaGetLastError());
   tm.launches++;
   BNL_CUDA(ctx, cudaEventRecord(dev.evc0, dev.stream));
-  if ((rc = bnl_pairs_run(ctx, dev, ds, dd, used, nullptr, n, lev_by_slot, &tm, h_cc))) return rc;
+  { BNL_TRACE("compact_pairs: bnl_pairs_run (host)"); if ((rc = bnl_pairs_run(ctx, dev, ds, dd, used, nullptr, n, lev_by_slot, &tm, h_cc))) return rc; }
   BNL_CUDA(ctx, cudaEventRecord(dev.evc1, dev.stream));
   if (kind == 2) {
     BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
@@ -882,7 +888,8 @@ int compact_pairs(bnl_ctx *ctx, BnlDataSet &ds, int kind, int code, double arg, 
     BNL_CUDA(ctx, cudaEventRecord(dev.eve1, dev.stream));
     BNL_CUDA(ctx, cudaMemcpyAsync(dev.h_out, dev.d_out, (size_t)n * 4 * sizeof(double), cudaMemcpyDeviceToHost, dev.stream));
     BNL_CUDA(ctx, cudaEventRecord(dev.ev1, dev.stream));
-    BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));
+    { BNL_TRACE("compact_pairs: sync wait"); BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream)); }
+    BNL_TRACE("compact_pairs: outputs");
     for (int u = 0; u < n; u++) {
       if (o0) o0[u] = dev.h_out[4 * (size_t)u];
       if (o1) o1[u] = dev.h_out[4 * (size_t)u + 1];

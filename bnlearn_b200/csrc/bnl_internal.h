@@ -115,7 +115,17 @@ struct BnlDataSet {
   std::vector<int> mask_col;            // per column: its intervention mask column (mBDe), -1 none; empty: none set
 };
 
+// bnl_score_cache_fill's candidate lists, kept between calls (cleared, not freed): the first
+// iteration of hc on 1000 nodes lists 499 500 candidates, 14 MB of index arrays whose fresh
+// pages cost more than filling them.
+struct BnlCacheFillScratch {
+  std::vector<int> target, pa_off, pa_idx, ci, cj;
+  std::vector<std::pair<int, int>> copies;
+  std::vector<double> score;
+};
+
 struct bnl_ctx {
+  BnlCacheFillScratch cf;
   std::vector<BnlDevice> devs;
   std::map<bnl_data, BnlDataSet> data;
   bnl_data next_handle = 1;

@@ -266,8 +266,8 @@ extern "C" int bnl_hc(bnl_ctx *ctx, bnl_data data, int score_e, double k_or_iss,
     if (rc) return rc;
     Move mv;
     {
-      BNL_TRACE("hc: columns_changed+opt_step");
-      S.columns_changed(updated);                // only these columns of the cache were rewritten
+      { BNL_TRACE("hc: columns_changed"); S.columns_changed(updated); }   // only these columns of the cache were rewritten
+      BNL_TRACE("hc: opt_step");
       mv = S.opt_step();
     }
     if (!mv.op) break;
