@@ -119,9 +119,9 @@ def measured_traffic(same_workload, compulsory):
         total = int(sum(k.values()))
         return {"traffic": total, "traffic_by_kernel": k, "traffic_over_compulsory": total / compulsory,
                 "traffic_note": "ncu --set full capture of this command (profiles/traffic.json, "
-                                "profiles/r2_bench_step_kernel_details.csv): every counting launch of the step reads "
-                                "the packed columns from DRAM once (level 0 in the pair kernel, levels 1-2 in "
-                                "count_small), so the step moves one compulsory pass per launch and nothing more"}
+                                "profiles/r2_bench_step_kernel_details.csv): each counting launch of the step reads "
+                                "its columns from DRAM once -- level 0 the byte columns in the pair kernel, levels "
+                                "1-2 the nibble copy (half the bytes) in count_small -- and nothing more"}
     except Exception as exc:                         # a missing capture must not cost the bench line
         return {"traffic": None, "traffic_note": "no capture: %r" % (exc,)}
 
@@ -881,8 +881,10 @@ def main():
             if full[i, 1] != rdf:
                 worst = float("inf")
         comp_local = float(args.rows) * len(my_cols)
+        # (no atomic_frac for the mixed step: its marginal tests are counted on the tensor cores; the
+        #  conditional tests' figure is copied in from their own class below)
         roof = hbm_class("config B: %d of the %d tests on rank 0 (levels 0-2 of pc.stable, mixed)" % (e - b, n_units),
-                         kms_local, comp_local, unit_bytes, e - b, args.rows, peak,
+                         kms_local, comp_local, unit_bytes, e - b, args.rows, peak, atomic=False,
                          note="the step's counting launches together (CUDA events around them on the engine's "
                               "stream); %.0f units per distinct column, so the >= 50 %% HBM target does not apply "
                               "to this batch: L2 serves the column reuse and the shared-memory atomic rate binds"
@@ -975,6 +977,12 @@ def main():
                 line["gaussian"] = {"error": repr(exc)[:300]}
     if rank == 0:
         line["roofline"]["classes"] = classes
+        for c in classes:
+            if c["class"].startswith("config B: levels 1-2") and "atomic_frac" in c:
+                line["roofline"]["atomic_frac"] = c["atomic_frac"]
+                line["roofline"]["atomic_ceiling_updates_per_s"] = ATOMIC_CEILING
+                line["roofline"]["atomic_frac_of"] = ("the conditional tests of the step, timed alone (classes[1]): row updates "
+                                                      "per second over the shared-memory atomic ceiling; level 0 has no atomics")
         if world > 1 and torch.cuda.device_count() >= 2:
             try:
                 line["multi_device_context_check"] = multi_device_context_check(units[::7], lev)
