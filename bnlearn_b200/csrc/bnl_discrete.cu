@@ -486,6 +486,17 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           for (int k = 0; k < hu.ncols; k++) ok = ok && on[hu.col[k]];
           if (ok) { hu.mode = 2; wanted++; }
         }
+        if (wanted && !dd.u4 && !dd.u4_refused) {
+          // not at the price of the data set's other needs: the copy must fit twice over in what is free
+          size_t free_b = 0, total_b = 0;
+          cudaMemGetInfo(&free_b, &total_b);
+          for (auto &blk : dev.pool) free_b += blk.second;
+          if ((ds.stride_u8 / 2) * (size_t)ds.nd * 2 > free_b) dd.u4_refused = true;
+        }
+        if (wanted && !dd.u4 && dd.u4_refused) {
+          for (int i : cls[0]) if (dev.h_units[i].mode == 2) dev.h_units[i].mode = 0;
+          wanted = 0;
+        }
         if (wanted && !dd.u4) {
           const size_t stride4 = ds.stride_u8 / 2;
           dd.u4_bytes = stride4 * ds.nd;

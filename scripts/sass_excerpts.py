@@ -1,7 +1,7 @@
 """Writes profiles/<tag>_sass_hot_loops.txt: excerpts of `cuobjdump -sass` for the
 kernels DESIGN.md discusses, cut around the instructions that prove the design --
-PRMT + ATOMS.POPC.INC (packed-index counting), DMMA (fp64 tensor cores of the Gram),
-UTCIMMA / LDTM / UTCBAR (tcgen05 pair kernel) -- with the instruction histogram of
+PRMT + ATOMS.POPC.INC (packed-index counting), DMMA + UBLKCP (fp64 tensor cores of the Gram,
+stages filled by the bulk-copy engine), UTCIMMA / LDTM / UTCBAR (tcgen05 pair kernel) -- with the instruction histogram of
 each kernel. Runs here (no GPU): nvcc cross-compiles and cuobjdump reads the .so.
 
     python scripts/sass_excerpts.py r2
@@ -18,8 +18,9 @@ WANT = [  # (substring of the mangled name, mnemonics to centre the excerpt on, 
     ("count_small_kernelILb0EE", ("ATOMS.POPC.INC",), 14),
     ("count_group_kernelILi512ELi16384EE", ("ATOMS.POPC.INC",), 10),
     ("count_based_kernelILi5ELi1ELi1024EE", ("ATOMS.POPC.INC",), 10),
-    ("gram_dmma_kernel", ("DMMA",), 10),
-    ("pair_onehot_kernelILi256ELi3ELi2ELb0ELb0ELi19ELi2EE", ("UTCIMMA", "LDTM", "UTCBAR", "UTCATOMSWS", "STS.128"), 8),
+    ("gram_dmma_kernelILb1EE", ("DMMA", "UBLKCP", "SYNCS"), 10),
+    ("pair_onehot_kernelILi128ELi1ELi2ELb0ELb0ELi11ELi4ELi8EE", ("UTCIMMA", "LDTM", "UTCBAR", "PRMT", "STS.128"), 8),
+    ("pair_onehot_kernelILi256ELi3ELi2ELb0ELb0ELi19ELi2E", ("UTCIMMA", "LDTM", "UTCBAR", "STS.128"), 8),
 ]
 
 
