@@ -498,6 +498,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           wanted = 0;
         }
         if (wanted && !dd.u4) {
+          BNL_TRACE("run_block: nibble copy made");
           const size_t stride4 = ds.stride_u8 / 2;
           dd.u4_bytes = stride4 * ds.nd;
           if ((rc = bnl_pool_alloc(ctx, dev, (void **)&dd.u4, dd.u4_bytes))) return rc;
@@ -1132,9 +1133,43 @@ extern "C" int bnl_score_discrete(bnl_ctx *ctx, bnl_data data, int score_e, doub
   {
     BNL_TRACE("score_discrete: make_unit");
     rq.units.resize(n);
+    // score_cache_fill's candidates of one node share the node and every parent but the last:
+    // the shared part is described once and each candidate adds its own column to a copy
+    BnlUnit base;
+    int base_u = -1;                        // unit whose node and leading parents `base` describes
     for (int u = 0; u < n; u++) {
-      int np = pa_off[u + 1] - pa_off[u];
-      int rc = make_unit(ctx, *ds, target[u], -1, pa_idx ? pa_idx + pa_off[u] : nullptr, np, &rq.units[u]);
+      const int np = pa_off[u + 1] - pa_off[u];
+      const int *z = pa_idx ? pa_idx + pa_off[u] : nullptr;
+      bool shared = false;
+      if (np >= 2 && base_u >= 0 && target[base_u] == target[u] && pa_off[base_u + 1] - pa_off[base_u] == np)
+        shared = memcmp(pa_idx + pa_off[base_u], z, sizeof(int) * (size_t)(np - 1)) == 0;
+      if (np >= 2 && !shared) {
+        int rc = make_unit(ctx, *ds, target[u], -1, z, np - 1, &base);
+        if (rc) return rc;
+        base_u = u;
+        shared = true;
+      }
+      int rc = BNL_OK;
+      if (shared) {
+        const int c = z[np - 1];
+        BnlUnit &un = rq.units[u];
+        const long long lev = (c >= 0 && c < ds->ncols && !ds->is_numeric[c]) ? ds->nlevels[c] : -1;
+        // anything out of the ordinary (a bad column, a wide one, sizes near the limits) takes the full route
+        if (lev < 0 || ds->is_wide[c] || np + 2 > BNL_MAXK || (long long)base.llz * lev >= INT32_MAX ||
+            (long long)base.cells * lev >= INT32_MAX || (long long)base.cells * lev > kMaxBatchCells) {
+          rc = make_unit(ctx, *ds, target[u], -1, z, np, &un);
+        } else {
+          un = base;
+          un.col[un.ncols] = ds->slot[c];
+          un.mul[un.ncols] = base.cells;
+          un.ncols++;
+          if (!ds->slot_has_na.empty() && ds->slot_has_na[ds->slot[c]]) un.has_na = 1;
+          un.llz = (int)(base.llz * lev);
+          un.cells = (int)(base.cells * lev);
+        }
+      } else {
+        rc = make_unit(ctx, *ds, target[u], -1, z, np, &rq.units[u]);
+      }
       if (rc) return rc;
     }
   }
