@@ -441,12 +441,12 @@ int bnl_score_cache_fill_np(bnl_ctx *ctx, bnl_data data, int score_e, double k_o
         for (int i = 0; i < nnodes; i++) colsum[j] += A(i, j);
   }
 
-  // The candidates that are really scored, target by target (j outer, i inner): amat and
-  // blmat are column-major, so a target's column is read in order (the reference's i-outer
-  // order walked both matrices with stride n: 10 of the 19 ms of the first iteration on
-  // 1000 nodes), and the candidates of one node are consecutive, which is what the counting
-  // kernels' run detection wants when two nodes are updated after a reversal. A delta does
-  // not depend on its place in the batch; the equivalence copies are applied afterwards.
+  // The candidates that are really scored, target by target (j outer, i inner; the reference
+  // goes i outer): amat, blmat and the cache are column-major, so a target's column is read
+  // and written in order, and the candidates of one node are consecutive, which is what the
+  // counting kernels' run detection wants when two nodes are updated after a reversal. A
+  // delta does not depend on its place in the batch; the equivalence copies are applied
+  // afterwards. The lists live in the context between calls (BnlCacheFillScratch).
   std::vector<int> &target = ctx->cf.target, &pa_off = ctx->cf.pa_off, &pa_idx = ctx->cf.pa_idx, &ci = ctx->cf.ci,
                    &cj = ctx->cf.cj;
   std::vector<std::pair<int, int>> &copies = ctx->cf.copies;

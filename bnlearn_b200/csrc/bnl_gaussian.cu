@@ -30,8 +30,8 @@ int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
   long long msplit = std::min<long long>(std::max(1ll, ds.nobs / 65536), 64);
 
   // The Gram kernel reads X - mean from scratch memory when the whole centred data set fits
-  // beside everything else (16 GB for 2000 columns x 1 M rows: 139 ms for the moments against
-  // 143); otherwise it centres each stage in shared memory. (Slabs of rows through a smaller
+  // beside everything else (16 GB for 2000 columns x 1 M rows: 133 ms for the moments against
+  // 140); otherwise it centres each stage in shared memory. (Slabs of rows through a smaller
   // scratch buffer were slower than no scratch at all -- a partial last wave per slab.)
   // BNL_GRAM_SCRATCH=0 / 1 forces the choice (tests).
   const long long rows_pad = (ds.nobs + GRAM_KB - 1) / GRAM_KB * GRAM_KB;
@@ -76,7 +76,10 @@ int bnl_gaussian_prepare(bnl_ctx *ctx, BnlDataSet &ds, int di) {
   e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaStreamSynchronize(dev.stream);
   bnl_pool_free(dev, partial, pbytes);
-  if (scratch) bnl_pool_free(dev, scratch, sbytes);
+  // a large scratch block goes straight back to the driver: cached in the pool it would hold
+  // as much device memory as the data set itself until something evicted it
+  if (scratch && sbytes > ((size_t)1 << 30)) cudaFree(scratch);
+  else if (scratch) bnl_pool_free(dev, scratch, sbytes);
   if (e == cudaSuccess && di == 0) {
     // bnl_last_call_profile() after a registration reports the moments kernels.
     float ms = 0.f;

@@ -63,3 +63,21 @@ def test_cost_blocks_cover_the_list_in_order():
     b2 = cost_blocks(costs, 2, together=666)
     assert b2[0] == 0 and b2[1] > 666 and b2[2] == 1081        # cheaper than a rank's share: shares a rank
     assert cost_blocks([], 3) == [0, 0, 0, 0]
+
+
+def test_search_core_opt_step_against_plain_scan(tmp_path):
+    """Search::opt_step (csrc/bnl_search_core.h: row bounds over valid and acyclic additions,
+    reachability closure, the exact cut below the best acceptable addition) gives the move of a
+    plain scan in the reference's order (hc_opt_step, src/learning/score/hc.cache.lookup.c:131-363)
+    on 24 000 steps of random DAG walks, with exact ties and values a fraction of sqrt(eps) apart."""
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    exe = str(tmp_path / "search_core_test")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", os.path.join(root, "bnlearn_b200", "csrc"), "-o", exe,
+                    os.path.join(root, "tests", "search_core_test.cpp")], check=True)
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.startswith("ok:")
