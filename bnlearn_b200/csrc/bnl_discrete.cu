@@ -39,6 +39,8 @@ const long long kKnobGroupMaxCells = env_ll("BNL_GROUP_MAXCELLS", 0);   // 0: wh
 // 256-512 threads that share the base column (profiles/r1b_l2_prefetch_sweep.log).
 const long long kKnobBasedNuCap = env_ll("BNL_BASED_NU_CAP", 1);
 const long long kKnobBasedMerge = env_ll("BNL_BASED_MERGE", 2);
+const long long kKnobBasedU8 = env_ll("BNL_BASED_U8", 1);
+const long long kKnobBasedNT = env_ll("BNL_BASED_NT", 512);
 const long long kKnobBased = env_ll("BNL_BASED", 1);
 const long long kKnobBasedMinCols = env_ll("BNL_BASED_MINCOLS", 4);
 const long long kKnobBasedWaves = env_ll("BNL_BASED_WAVES", 0);
@@ -181,6 +183,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 4, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<4, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
@@ -447,6 +451,9 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     for (int i = 0; i < cnt; i++) {
       BnlUnit &hu = dev.h_units[i];
       hu.mode = grouped[i] == 2 ? (16 + based_run[i]) | (based_lc[i] << 24) : 0;   // base-column units: run, counters per cell
+      // ... and bit 30: the run's base table (every column but the candidate's) has at most 256 cells,
+      // its indices are bytes (one unit per CTA only; BNL_BASED_U8=0 keeps them 16-bit)
+      if (grouped[i] == 2 && kKnobBasedU8 && kKnobBasedNuCap == 1 && hu.mul[hu.ncols - 1] <= 256) hu.mode |= 1 << 30;
       if (grouped[i]) continue;
       const int c = hu.cells;
       // a unit with a uint16 column is counted by the generic kernel, whatever its size
@@ -621,7 +628,11 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       if (based_nu[0] == 1) { BNL_BASED_LAUNCH(0, 5, 1, 1024) } else { BNL_BASED_LAUNCH(0, 5, 8, 256) }
       if (based_nu[1] == 1) { BNL_BASED_LAUNCH(1, 5, 1, 1024) } else { BNL_BASED_LAUNCH(1, 5, 4, 512) }
       if (based_nu[2] == 1) { BNL_BASED_LAUNCH(2, 5, 1, 1024) } else { BNL_BASED_LAUNCH(2, 5, 4, 512) }
-      if (merged_bytes > 0) { BNL_BASED_LAUNCH(3, 0, 1, 1024) } else { BNL_BASED_LAUNCH(3, 5, 1, 1024) }
+      if (merged_bytes > 0) { BNL_BASED_LAUNCH(3, 0, 1, 1024) }
+      // two CTAs of 512 threads per SM when two of the launch's largest table fit: one counts while
+      // the other clears or collapses its table (0.304 -> 0.293 ms on a 3-parent batch)
+      else if (kKnobBasedNT <= 512 && (size_t)bmax[3] * 128 * 2 + 4096 <= (size_t)dev.max_smem) { BNL_BASED_LAUNCH(3, 5, 1, 512) }
+      else { BNL_BASED_LAUNCH(3, 5, 1, 1024) }
       BNL_BASED_LAUNCH(4, 4, 1, 1024)
       BNL_BASED_LAUNCH(5, 3, 1, 1024)
 #undef BNL_BASED_LAUNCH

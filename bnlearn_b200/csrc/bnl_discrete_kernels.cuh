@@ -728,6 +728,21 @@ combine_base_kernel(const uint8_t *__restrict__ u8, size_t stride, long long ful
   __syncthreads();
   const int nbase = s_nbase;
   uint4 *out = reinterpret_cast<uint4 *>(basecols + (size_t)blockIdx.y * bstride);
+  if ((un.mode >> 30) & 1) {
+    // at most 256 base cells: the index fits a byte, 16 rows per 128-bit word (the candidate
+    // kernel then loads 2 bytes per row instead of 3, which takes it to the update rate)
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < full;
+         g += (long long)gridDim.x * blockDim.x) {
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      for (int k = 0; k < nbase; k++) {
+        const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(u8 + (size_t)s_col[k] * stride) + g);
+        const unsigned m = (unsigned)s_mul[k];
+        v.x += w.x * m; v.y += w.y * m; v.z += w.z * m; v.w += w.w * m;       // bytewise: every sum stays below 256
+      }
+      out[g] = v;
+    }
+    return;
+  }
   for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < full;
        g += (long long)gridDim.x * blockDim.x) {
     unsigned v[8];
@@ -772,7 +787,7 @@ struct BasedRegs { uint4 b0, b1, c[NUMAX]; };
 // current one is counted (one CTA per SM: nothing else hides the round trip, and
 // one group ahead left the kernel latency-bound at 40 GB/s per SM).
 template <int LC, int NUMAX, int NT>
-__global__ void __launch_bounds__(NT)
+__global__ void __launch_bounds__(NT, (NUMAX == 1 && NT == 512) ? 2 : 1)
 count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs,
                    const uint16_t *__restrict__ basecols, size_t bstride,
                    const BnlUnit *__restrict__ units, const int *__restrict__ order,
@@ -795,7 +810,8 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     s_tab[threadIdx.x] = uj.table_off;
   }
   __syncthreads();
-  const int lc = LC ? LC : (su.mode >> 24);
+  const int lc = LC ? LC : ((su.mode >> 24) & 0x3F);
+  const bool base8 = NUMAX == 1 && ((su.mode >> 30) & 1);     // the run's base indices are bytes (combine_base_kernel)
   // one unit per CTA: only its own table is cleared (the launch's stride is the largest one)
   const int quads = NUMAX == 1 ? ((s_cells[0] << (lc + 2)) + 15) >> 4 : (nu * tstride) >> 4;
   for (int c = threadIdx.x; c < quads; c += NT) reinterpret_cast<uint4 *>(hist)[c] = make_uint4(0, 0, 0, 0);
@@ -816,8 +832,11 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
   if (g1 > full) g1 = full;
 
   auto load = [&](BasedRegs<NUMAX> &R, long long g) {
-    R.b0 = ldg_stream(bp + 2 * g);
-    R.b1 = ldg_stream(bp + 2 * g + 1);
+    if (base8) R.b0 = ldg_stream(bp + g);
+    else {
+      R.b0 = ldg_stream(bp + 2 * g);
+      R.b1 = ldg_stream(bp + 2 * g + 1);
+    }
 #pragma unroll
     for (int j = 0; j < NUMAX; j++)
       if (j < nu) R.c[j] = ldg_stream(cp[j] + g);
@@ -828,6 +847,16 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
     }
   };
   auto count = [&](const BasedRegs<NUMAX> &R) {
+    if (base8) {                       // (one unit per CTA)
+      const unsigned b4[4] = {R.b0.x, R.b0.y, R.b0.z, R.b0.w};
+      const unsigned cw[4] = {R.c[0].x, R.c[0].y, R.c[0].z, R.c[0].w};
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        based_bump<LC>(hist, __byte_perm(b4[q], 0, 0x4140) + __byte_perm(cw[q], 0, 0x4140) * cmul, slot4, lc + 2);
+        based_bump<LC>(hist, __byte_perm(b4[q], 0, 0x4342) + __byte_perm(cw[q], 0, 0x4342) * cmul, slot4, lc + 2);
+      }
+      return;
+    }
     const unsigned bw[8] = {R.b0.x, R.b0.y, R.b0.z, R.b0.w, R.b1.x, R.b1.y, R.b1.z, R.b1.w};
 #pragma unroll
     for (int j = 0; j < NUMAX; j++)
