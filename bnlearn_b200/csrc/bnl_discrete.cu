@@ -184,7 +184,9 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
-    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 1, 512, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dev.max_smem - 4096));
+    BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<5, 1, 1024, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
     BNL_CUDA(ctx, cudaFuncSetAttribute(count_based_kernel<4, 1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dev.max_smem - 4096));
@@ -448,12 +450,18 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     }
     std::vector<int> cls[4];
     int cmax[4] = {0, 0, 0, 0};
+    // byte base indices (count_based_kernel<.., B8>): when EVERY base-column run of the sub-batch has at
+    // most 256 base cells (the candidates of one node, or of the two nodes a reversal touches, usually
+    // agree); one unit per CTA only; BNL_BASED_U8=0 keeps them 16-bit
+    bool all_u8 = kKnobBasedU8 && kKnobBasedNuCap == 1 && !bruns.empty();
+    for (int i = 0; i < cnt && all_u8; i++)
+      if (grouped[i] == 2 && dev.h_units[i].mul[dev.h_units[i].ncols - 1] > 256) all_u8 = false;
     for (int i = 0; i < cnt; i++) {
       BnlUnit &hu = dev.h_units[i];
       hu.mode = grouped[i] == 2 ? (16 + based_run[i]) | (based_lc[i] << 24) : 0;   // base-column units: run, counters per cell
       // ... and bit 30: the run's base table (every column but the candidate's) has at most 256 cells,
       // its indices are bytes (one unit per CTA only; BNL_BASED_U8=0 keeps them 16-bit)
-      if (grouped[i] == 2 && kKnobBasedU8 && kKnobBasedNuCap == 1 && hu.mul[hu.ncols - 1] <= 256) hu.mode |= 1 << 30;
+      if (grouped[i] == 2 && all_u8) hu.mode |= 1 << 30;
       if (grouped[i]) continue;
       const int c = hu.cells;
       // a unit with a uint16 column is counted by the generic kernel, whatever its size
@@ -607,7 +615,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       tm->launches++;
       int bbase = n_ungrouped + (int)gorder.size();
       size_t tbase = ngtiles;
-#define BNL_BASED_LAUNCH(K, LC, NU, NT)                                                                       \
+#define BNL_BASED_LAUNCH(K, LC, NU, NT) BNL_BASED_LAUNCH8(K, LC, NU, NT, false)
+#define BNL_BASED_LAUNCH8(K, LC, NU, NT, B8)                                                                  \
       if (!bcls[K].empty()) {                                                                                  \
         const long long nt = (long long)btiles[K].size();                                                      \
         long long ch = kKnobBasedWaves ? std::max(1ll, (kKnobBasedWaves * dev.sm_count + nt / 2) / nt)         \
@@ -615,7 +624,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
                                                       ds.nobs / 131072, nullptr);                              \
         ch = std::max(1ll, std::min(ch, std::max(1ll, ds.nobs / 131072)));                                     \
         const int ts = ((bmax[K] << ((LC ? LC : 5) + 2)) + 255) & ~255;                                                   \
-        count_based_kernel<LC, NU, NT><<<(unsigned)(nt * ch), NT, (size_t)ts * based_nu[K], dev.stream>>>(      \
+        count_based_kernel<LC, NU, NT, B8><<<(unsigned)(nt * ch), NT, (size_t)ts * based_nu[K], dev.stream>>>(  \
             dd.u8, ds.stride_u8, ds.nobs, dev.d_basecols, bstride, dev.d_units, dev.d_order + bbase,           \
             dev.d_tiles + tbase, dev.d_tables, (int)nt, (int)ch, ts, kKnobPrefetch);                                          \
         BNL_CUDA(ctx, cudaGetLastError());                                                                     \
@@ -629,13 +638,16 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       if (based_nu[1] == 1) { BNL_BASED_LAUNCH(1, 5, 1, 1024) } else { BNL_BASED_LAUNCH(1, 5, 4, 512) }
       if (based_nu[2] == 1) { BNL_BASED_LAUNCH(2, 5, 1, 1024) } else { BNL_BASED_LAUNCH(2, 5, 4, 512) }
       if (merged_bytes > 0) { BNL_BASED_LAUNCH(3, 0, 1, 1024) }
-      // two CTAs of 512 threads per SM when two of the launch's largest table fit: one counts while
-      // the other clears or collapses its table (0.304 -> 0.293 ms on a 3-parent batch)
-      else if (kKnobBasedNT <= 512 && (size_t)bmax[3] * 128 * 2 + 4096 <= (size_t)dev.max_smem) { BNL_BASED_LAUNCH(3, 5, 1, 512) }
+      // byte base indices: two CTAs of 512 threads per SM when two of the launch's largest table fit -- one
+      // counts while the other clears or collapses its table (0.299 -> 0.289 ms on a 3-parent batch; with
+      // 16-bit indices the two CTAs get in each other's way, 0.340 -> 0.354)
+      else if (all_u8 && kKnobBasedNT <= 512 && (size_t)bmax[3] * 128 * 2 + 4096 <= (size_t)dev.max_smem) { BNL_BASED_LAUNCH8(3, 5, 1, 512, true) }
+      else if (all_u8) { BNL_BASED_LAUNCH8(3, 5, 1, 1024, true) }
       else { BNL_BASED_LAUNCH(3, 5, 1, 1024) }
       BNL_BASED_LAUNCH(4, 4, 1, 1024)
       BNL_BASED_LAUNCH(5, 3, 1, 1024)
 #undef BNL_BASED_LAUNCH
+#undef BNL_BASED_LAUNCH8
     }
     if (groups > 0 && ngtiles > 0) {
       // one CTA per SM (its tables fill the shared memory): ~8 waves of CTAs.

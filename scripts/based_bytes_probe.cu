@@ -29,6 +29,27 @@ __device__ __forceinline__ void bump4(int *hist, unsigned b, unsigned c, unsigne
   bump2(hist, __byte_perm(b, 0, 0x4342) + __byte_perm(c, 0, 0x4342) * cmul, slot4);
 }
 
+// the same with the lane's slot folded into the table pointer once: cell * 128 + pointer is one multiply-add
+__device__ __forceinline__ void bump4_lean(char *hp, unsigned b, unsigned c, unsigned cmul) {
+  const unsigned lo = __byte_perm(b, 0, 0x4140) + __byte_perm(c, 0, 0x4140) * cmul;
+  const unsigned hi = __byte_perm(b, 0, 0x4342) + __byte_perm(c, 0, 0x4342) * cmul;
+  atomicAdd(reinterpret_cast<int *>(hp + ((lo & 0xFFFFu) << (LC + 2))), 1);
+  atomicAdd(reinterpret_cast<int *>(hp + ((lo >> 16) << (LC + 2))), 1);
+  atomicAdd(reinterpret_cast<int *>(hp + ((hi & 0xFFFFu) << (LC + 2))), 1);
+  atomicAdd(reinterpret_cast<int *>(hp + ((hi >> 16) << (LC + 2))), 1);
+}
+
+// ... and with the address arithmetic spelled out: one multiply-add per update on a 32-bit shared address
+__device__ __forceinline__ void red1(unsigned addr) { asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(addr)); }
+__device__ __forceinline__ void bump4_ptx(unsigned pre, unsigned b, unsigned c, unsigned cmul) {
+  const unsigned lo = __byte_perm(b, 0, 0x4140) + __byte_perm(c, 0, 0x4140) * cmul;
+  const unsigned hi = __byte_perm(b, 0, 0x4342) + __byte_perm(c, 0, 0x4342) * cmul;
+  red1(__byte_perm(lo, 0, 0x4410) * 128u + pre);       // a byte-permute takes the 16-bit half: the compiler cannot
+  red1(__byte_perm(lo, 0, 0x4432) * 128u + pre);       // fold it into a shift-and-mask, and * 128 + pre is one IMAD
+  red1(__byte_perm(hi, 0, 0x4410) * 128u + pre);
+  red1(__byte_perm(hi, 0, 0x4432) * 128u + pre);
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(NT)
 probe(const uint16_t *base16, const uint8_t *base8, const uint8_t *cand, size_t cstride, long long rows, int cells,
@@ -41,7 +62,9 @@ probe(const uint16_t *base16, const uint8_t *base8, const uint8_t *cand, size_t 
   const uint4 *b8 = reinterpret_cast<const uint4 *>(base8);
   const uint4 *cp = reinterpret_cast<const uint4 *>(cand + (size_t)blockIdx.x * cstride);
   const unsigned M = 0x0F0F0F0Fu;
-  if (MODE == 0 || MODE == 1) {
+  char *hp = reinterpret_cast<char *>(hist) + slot4;
+  const unsigned pre = (unsigned)__cvta_generic_to_shared(hist) + slot4;
+  if (MODE == 0 || MODE == 1 || MODE == 5 || MODE == 6) {
     const long long g1 = rows / 16;
     struct R { uint4 b0, b1, c; } r0, r1, r2;
     auto load = [&](R &r, long long g) {
@@ -57,10 +80,18 @@ probe(const uint16_t *base16, const uint8_t *base8, const uint8_t *cand, size_t 
           bump2(hist, bw[2 * q] + __byte_perm(cw[q], 0, 0x4140) * cmul, slot4);
           bump2(hist, bw[2 * q + 1] + __byte_perm(cw[q], 0, 0x4342) * cmul, slot4);
         }
-      } else {
+      } else if (MODE == 1) {
         const unsigned bw[4] = {r.b0.x, r.b0.y, r.b0.z, r.b0.w};
 #pragma unroll
         for (int q = 0; q < 4; q++) bump4(hist, bw[q], cw[q], cmul, slot4);
+      } else if (MODE == 5) {
+        const unsigned bw[4] = {r.b0.x, r.b0.y, r.b0.z, r.b0.w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) bump4_lean(hp, bw[q], cw[q], cmul);
+      } else {
+        const unsigned bw[4] = {r.b0.x, r.b0.y, r.b0.z, r.b0.w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) bump4_ptx(pre, bw[q], cw[q], cmul);
       }
     };
     long long g = threadIdx.x;
@@ -186,6 +217,8 @@ int main() {
     CK(cudaDeviceSynchronize());
     run<0>("M0 uint16 base + uint8 candidate (3 B/row)", b16, b8, cand, cstride, rows, nunits, basecells, lev, tables);
     if (basecells <= 256) run<1>("M1 uint8 base + uint8 candidate (2 B/row)", b16, b8, cand, cstride, rows, nunits, basecells, lev, tables);
+    if (basecells <= 256) run<5>("M5 = M1 with the slot folded into the table pointer", b16, b8, cand, cstride, rows, nunits, basecells, lev, tables);
+    if (basecells <= 256) run<6>("M6 = M1 with red.shared on a multiply-add address", b16, b8, cand, cstride, rows, nunits, basecells, lev, tables);
     if (basecells <= 256) run<2>("M2 uint8 base + nibble candidate (1.5 B/row)", b16, b8, cand, cstride, rows, nunits, basecells, lev, tables);
     run<3>("M3 uint16 base + nibble candidate (2.5 B/row)", b16, b8, cand, cstride, rows, nunits, basecells, lev, tables);
     run<4>("M4 no loads (update rate alone)", b16, b8, cand, cstride, rows, nunits, basecells, lev, tables);
