@@ -987,8 +987,9 @@ def main():
             if c["class"].startswith("config B: levels 1-2") and "atomic_frac" in c:
                 line["roofline"]["atomic_frac"] = c["atomic_frac"]
                 line["roofline"]["atomic_ceiling_updates_per_s"] = ATOMIC_CEILING
-                line["roofline"]["atomic_frac_of"] = ("the conditional tests of the step, timed alone (classes[1]): row updates "
-                                                      "per second over the shared-memory atomic ceiling; level 0 has no atomics")
+                line["roofline"]["atomic_frac_of"] = ("the conditional tests of the step, timed alone (classes[1]): rows x units "
+                                                      "per second over the shared-memory update ceiling; level 0 has no "
+                                                      "atomics, and the units of <= 32 cells (a third) count two rows per update")
         if world > 1 and torch.cuda.device_count() >= 2:
             try:
                 line["multi_device_context_check"] = multi_device_context_check(units[::7], lev)

@@ -55,6 +55,8 @@ long long knob_nibbles() { return env_ll("BNL_NIBBLES", 262144); }
 // registered, counted once and released (bench.py's end-to-end step) would pay for the copy (0.1 ms
 // per 370 MB) about what it saves.
 long long knob_nibbles_after() { return env_ll("BNL_NIBBLES_AFTER", 1); }
+// tables of at most 32 cells from the nibble copy as row pairs (count_pair32_kernel): 0 off
+long long knob_pair32() { return env_ll("BNL_PAIR32", 1); }
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
 const int kMaxBatchUnits = 1 << 19;           // the first hc iteration on 1000 nodes (499 500 units) is one batch
@@ -448,7 +450,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         i = j;
       }
     }
-    std::vector<int> cls[4];
+    std::vector<int> cls[4], p32;             // p32: units of <= 32 cells counted as row pairs from the nibble copy
     int cmax[4] = {0, 0, 0, 0};
     // byte base indices (count_based_kernel<.., B8>): when EVERY base-column run of the sub-batch has at
     // most 256 base cells (the candidates of one node, or of the two nodes a reversal touches, usually
@@ -526,11 +528,28 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           BNL_CUDA(ctx, cudaGetLastError());
           BNL_CUDA(ctx, cudaStreamSynchronize(dev.stream));     // `on` is a local
         }
+        // ... and those of at most 32 cells count row pairs there (count_pair32_kernel), in a launch of their own
+        if (wanted && dd.u4 && knob_pair32() && dev.max_smem >= 132 * 1024) {
+          std::vector<int> keep;
+          for (int i : cls[0]) {
+            BnlUnit &hu = dev.h_units[i];
+            if (hu.mode == 2 && hu.cells <= 32) { hu.mode = 3; p32.push_back(i); }
+            else keep.push_back(i);
+          }
+          if (p32.size() < 8) {                       // not worth a launch
+            for (int i : p32) dev.h_units[i].mode = 2;
+            p32.clear();
+          } else {
+            cls[0].swap(keep);
+            cmax[0] = 0;
+            for (int i : cls[0]) cmax[0] = std::max(cmax[0], dev.h_units[i].mode == 1 ? 256 : dev.h_units[i].cells);
+          }
+        }
       }
     }
     if ((rc = bnl_reserve_pinned(ctx, &dev.h_order, &dev.h_order_cap, (size_t)cnt))) return rc;
     if ((rc = bnl_reserve_device(ctx, &dev.d_order, &dev.order_cap, (size_t)cnt))) return rc;
-    int n_ungrouped = 0, n_before_tests = 0;
+    int n_ungrouped = 0, n_before_tests = 0, n_before_p32 = 0;
     {
       int o = 0;
       for (int k = 0; k < 4; k++) for (int i : cls[k]) dev.h_order[o++] = i;
@@ -539,6 +558,8 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       for (int k = 0; k < kBasedClasses; k++) for (int i : bcls[k]) dev.h_order[o++] = i;   // then the base-column classes
       n_before_tests = o;
       for (int k = 0; k < kTestClasses; k++) for (int i : torder[k]) dev.h_order[o++] = i;  // then the runs of tests
+      n_before_p32 = o;
+      for (int i : p32) dev.h_order[o++] = i;                                                // then the 32 x 32 row-pair units
     }
     if (!bruns.empty()) {
       if ((rc = bnl_reserve_pinned(ctx, &dev.h_runfirst, &dev.h_runfirst_cap, bruns.size()))) return rc;
@@ -696,6 +717,20 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
         obase += (int)torder[k].size();
         tbase += ttiles[k].size();
       }
+    }
+    if (groups > 0 && !p32.empty()) {
+      if (!dev.p32_attr_done) {
+        BNL_CUDA(ctx, cudaFuncSetAttribute(count_pair32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+        dev.p32_attr_done = true;
+      }
+      // one CTA of 1024 threads per SM: ~8 waves of CTAs, chunks of at least 2^17 rows
+      long long ch = std::max(1ll, (8ll * dev.sm_count + (long long)p32.size() - 1) / (long long)p32.size());
+      ch = std::max(1ll, std::min(ch, std::max(1ll, ds.nobs / 131072)));
+      count_pair32_kernel<<<(unsigned)(p32.size() * ch), 1024, 128 * 1024, dev.stream>>>(
+          dd.u8, ds.stride_u8, dd.u4, ds.stride_u8 / 2, ds.nobs, dev.d_units, dev.d_order + n_before_p32, dev.d_tables,
+          (int)p32.size(), (int)ch);
+      BNL_CUDA(ctx, cudaGetLastError());
+      tm->launches++;
     }
     if (groups > 0) {
       int base = 0;

@@ -921,6 +921,124 @@ count_based_kernel(const uint8_t *__restrict__ u8, size_t stride, long long nobs
 }
 
 // ---------------------------------------------------------------------------
+// Row pairs for tables of at most 32 cells, from the nibble copy of the columns. The update
+// rate of shared memory bounds every counting kernel here (16 lanes/clk/SM), so the cheapest
+// row is the one that shares its update: byte j of a nibble column holds rows 2j and 2j + 1, and
+// the pair (cell a of the even row, cell b of the odd row) bumps slot a + 32 b of a 32 x 32
+// pair table -- one update per TWO rows. The table keeps one counter per lane and slot
+// (1024 slots x 128 bytes = 128 KB: one CTA of 1024 threads per SM); at the end cell c gets
+// the sum of row c and of column c of the pair table. Units without NA whose columns all
+// have a nibble copy; the rows past the last 32-row group are counted singly by one thread.
+// A third of config B's conditional tests (tables of 17 - 32 cells) come here, and the
+// few of <= 16 cells that the 16 x 16 pair mode of count_small_kernel does not take.
+template <int NC>
+__device__ __forceinline__ void pair32_rows(const uint8_t *__restrict__ u4, size_t stride4, const BnlUnit &su,
+                                            unsigned pre, long long g0, long long g1) {
+  constexpr int NCA = NC ? NC : 1;
+  const uint4 *p[NCA];
+  unsigned m[NCA];
+#pragma unroll
+  for (int k = 0; k < NCA; k++) {
+    p[k] = reinterpret_cast<const uint4 *>(u4 + (size_t)su.col[k] * stride4);
+    m[k] = (unsigned)su.mul[k];
+  }
+  const unsigned M = 0x0F0F0F0Fu;
+  auto pairs = [&](unsigned lo, unsigned hi) {
+    // bytes of lo: cells of rows 0, 2, 4, 6 of these 8; of hi: rows 1, 3, 5, 7. Two 16-bit slots per register.
+    based_bump<5>(pre, __byte_perm(lo, 0, 0x4140) + __byte_perm(hi, 0, 0x4140) * 32u, 128u);
+    based_bump<5>(pre, __byte_perm(lo, 0, 0x4342) + __byte_perm(hi, 0, 0x4342) * 32u, 128u);
+  };
+  uint4 w[NCA], wn[NCA];
+  long long g = g0 + threadIdx.x;
+  if (NC && g < g1) {
+#pragma unroll
+    for (int k = 0; k < NCA; k++) w[k] = ldg_stream(p[k] + g);
+  }
+  for (; g < g1; g += blockDim.x) {
+    uint4 lo, hi;
+    if (NC) {
+      const long long gn = g + blockDim.x;             // the next group's loads in flight while this one is counted
+      if (gn < g1) {
+#pragma unroll
+        for (int k = 0; k < NCA; k++) wn[k] = ldg_stream(p[k] + gn);
+      }
+      lo = make_uint4(w[0].x & M, w[0].y & M, w[0].z & M, w[0].w & M);       // the first column has multiplier 1
+      hi = make_uint4((w[0].x >> 4) & M, (w[0].y >> 4) & M, (w[0].z >> 4) & M, (w[0].w >> 4) & M);
+#pragma unroll
+      for (int k = 1; k < NCA; k++) {
+        lo.x += (w[k].x & M) * m[k]; lo.y += (w[k].y & M) * m[k]; lo.z += (w[k].z & M) * m[k]; lo.w += (w[k].w & M) * m[k];
+        hi.x += ((w[k].x >> 4) & M) * m[k]; hi.y += ((w[k].y >> 4) & M) * m[k];
+        hi.z += ((w[k].z >> 4) & M) * m[k]; hi.w += ((w[k].w >> 4) & M) * m[k];
+      }
+#pragma unroll
+      for (int k = 0; k < NCA; k++) w[k] = wn[k];
+    } else {
+      lo = hi = make_uint4(0u, 0u, 0u, 0u);
+      for (int k = 0; k < su.ncols; k++) {
+        const uint4 x = ldg_stream(reinterpret_cast<const uint4 *>(u4 + (size_t)su.col[k] * stride4) + g);
+        const unsigned mk = (unsigned)su.mul[k];
+        lo.x += (x.x & M) * mk; lo.y += (x.y & M) * mk; lo.z += (x.z & M) * mk; lo.w += (x.w & M) * mk;
+        hi.x += ((x.x >> 4) & M) * mk; hi.y += ((x.y >> 4) & M) * mk; hi.z += ((x.z >> 4) & M) * mk; hi.w += ((x.w >> 4) & M) * mk;
+      }
+    }
+    pairs(lo.x, hi.x); pairs(lo.y, hi.y); pairs(lo.z, hi.z); pairs(lo.w, hi.w);
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+count_pair32_kernel(const uint8_t *__restrict__ u8, size_t stride, const uint8_t *__restrict__ u4, size_t stride4,
+                    long long nobs, const BnlUnit *__restrict__ units, const int *__restrict__ order,
+                    int *__restrict__ tables, int nunits, int chunks) {
+  extern __shared__ __align__(256) int hist[];        // 1024 slots x 32 lane counters
+  __shared__ BnlUnit su;
+  __shared__ int psum[1024];
+  const int chunk = blockIdx.x / nunits, u = order[blockIdx.x % nunits];
+  if (threadIdx.x < sizeof(BnlUnit) / sizeof(int))
+    reinterpret_cast<int *>(&su)[threadIdx.x] = reinterpret_cast<const int *>(&units[u])[threadIdx.x];
+  __syncthreads();
+  const int cells = su.cells;
+  // slots a + 32 b with b < cells: the first `cells` rows of 32 slots
+  for (int q = threadIdx.x; q < cells * 32 * 8; q += blockDim.x) reinterpret_cast<uint4 *>(hist)[q] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  const unsigned pre = (unsigned)__cvta_generic_to_shared(hist) + ((threadIdx.x & 31u) << 2);
+  const long long full4 = nobs / 32;
+  const long long per4 = (full4 + chunks - 1) / chunks;
+  const long long h0 = per4 * chunk;
+  long long h1 = h0 + per4;
+  if (h1 > full4) h1 = full4;
+  switch (su.ncols) {
+    case 1: pair32_rows<1>(u4, stride4, su, pre, h0, h1); break;
+    case 2: pair32_rows<2>(u4, stride4, su, pre, h0, h1); break;
+    case 3: pair32_rows<3>(u4, stride4, su, pre, h0, h1); break;
+    case 4: pair32_rows<4>(u4, stride4, su, pre, h0, h1); break;
+    default: pair32_rows<0>(u4, stride4, su, pre, h0, h1);
+  }
+  int *gtab = tables + su.table_off;
+  // the rows left over, once, singly, straight into the global table (the pair table holds no single rows)
+  if (chunk == chunks - 1 && threadIdx.x == 0)
+    for (long long r = full4 * 32; r < nobs; r++) {
+      int cell = 0;
+      for (int k = 0; k < su.ncols; k++) cell += (int)u8[(size_t)su.col[k] * stride + (size_t)r] * su.mul[k];
+      atomicAdd(&gtab[cell], 1);
+    }
+  __syncthreads();
+  // lane copies of every slot of the cells x cells corner, then each row of a pair adds its margin
+  for (int e = threadIdx.x; e < cells * cells; e += blockDim.x) {
+    const int slot = (e % cells) + 32 * (e / cells);
+    int sum = 0;
+#pragma unroll
+    for (int l = 0; l < 32; l++) sum += hist[slot * 32 + ((l + threadIdx.x) & 31)];
+    psum[slot] = sum;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+    int sum = 0;
+    for (int o = 0; o < cells; o++) sum += psum[c + 32 * o] + psum[o + 32 * c];
+    if (sum) atomicAdd(&gtab[c], sum);
+  }
+}
+
+// ---------------------------------------------------------------------------
 // Unit descriptors of a batch made only of one- and two-way tables, written on the
 // device: the host sends 8 bytes of column slots and the table offset per unit
 // instead of a 160-byte BnlUnit (499 500 units in the first hc iteration: 80 MB of

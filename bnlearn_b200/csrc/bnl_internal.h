@@ -60,6 +60,7 @@ struct BnlDevice {
   int *d_pairmeta = nullptr; size_t pairmeta_cap = 0;
   int *h_pairmeta = nullptr; size_t h_pairmeta_cap = 0;  // pinned
   bool pair_attr_done = false;
+  bool p32_attr_done = false;                            // count_pair32_kernel opted in to 128 KB of shared memory
   int *h_gidx = nullptr; size_t h_gidx_cap = 0;          // pinned
   // registration scratch (grow-only) and a small cache of released data-set
   // buffers: cudaMalloc / cudaFree synchronise the device and can cost tens of

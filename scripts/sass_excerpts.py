@@ -16,8 +16,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "bnlearn_b200", "libbnl_b200.so")
 WANT = [  # (substring of the mangled name, mnemonics to centre the excerpt on, lines of context)
     ("count_small_kernelILb0EE", ("ATOMS.POPC.INC",), 14),
+    ("count_pair32_kernel", ("ATOMS.POPC.INC",), 12),
     ("count_group_kernelILi512ELi16384EE", ("ATOMS.POPC.INC",), 10),
-    ("count_based_kernelILi5ELi1ELi1024EE", ("ATOMS.POPC.INC",), 10),
+    ("count_based_kernelILi5ELi1ELi512ELb1EE", ("ATOMS.POPC.INC",), 12),
     ("gram_dmma_kernelILb1EE", ("DMMA", "UBLKCP", "SYNCS"), 10),
     ("pair_onehot_kernelILi128ELi1ELi2ELb0ELb0ELi11ELi4ELi8EE", ("UTCIMMA", "LDTM", "UTCBAR", "PRMT", "STS.128"), 8),
     ("pair_onehot_kernelILi256ELi3ELi2ELb0ELb0ELi19ELi2E", ("UTCIMMA", "LDTM", "UTCBAR", "STS.128"), 8),

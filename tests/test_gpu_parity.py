@@ -587,8 +587,9 @@ def test_every_table_size_class(engine, with_na):
 
 @pytest.mark.parametrize("n", [31, 70001, 300003])
 def test_nibble_copy_route_counts_bit_exact(engine, monkeypatch, n):
-    """count_small_kernel reading the nibble copy of the columns (two codes per byte; units
-    of <= 256 cells whose columns have at most 15 levels and no NA): tables bit-exact against
+    """count_small_kernel and count_pair32_kernel (tables of <= 32 cells as row pairs) reading
+    the nibble copy of the columns (two codes per byte; units of <= 256 cells whose columns have
+    at most 15 levels and no NA): tables bit-exact against
     fill_1d/2d/3d_table (src/core/contingency.tables.c:20-223) for 1-6 columns per table,
     ragged row counts (the rows past the last 32-row group come from the byte columns), next
     to units that must stay on the byte route (a 16-level column, a column with NA)."""
@@ -603,7 +604,10 @@ def test_nibble_copy_route_counts_bit_exact(engine, monkeypatch, n):
     d = engine.register(cols, lev)
     units = [(0, None, []), (1, 2, []), (5, 1, []), (0, 1, [2]), (1, 2, [0, 3]), (0, 1, [3, 4, 8]),
              (0, 3, [4, 8, 1, 2]), (9, 5, [0]),
-             (6, 1, []), (1, 7, [0]), (0, 6, [3])]        # byte route: 16 levels, NA
+             (6, 1, []), (1, 7, [0]), (0, 6, [3]),        # byte route: 16 levels, NA
+             # enough tables of <= 32 cells for the row-pair launch (count_pair32_kernel): 1 - 5 columns
+             (3, None, []), (0, 3, []), (3, 4, []), (0, 4, [8]), (1, 8, []), (2, 3, [4]), (8, 0, [3]), (4, 1, [0]),
+             (2, 8, []), (9, 0, [3]), (0, 3, [4, 8]), (3, 4, [0, 8, 2]), (2, 9, []), (1, 9, [3])]
     xs, ys, zs = [u[0] for u in units], [u[1] if u[1] is not None else -1 for u in units], [u[2] for u in units]
     for rep in range(2):                             # second call: the copy exists already
         tabs = d.counts(xs, ys, zs)
