@@ -55,7 +55,8 @@ long long knob_nibbles() { return env_ll("BNL_NIBBLES", 262144); }
 // registered, counted once and released (bench.py's end-to-end step) would pay for the copy (0.1 ms
 // per 370 MB) about what it saves.
 long long knob_nibbles_after() { return env_ll("BNL_NIBBLES_AFTER", 1); }
-// tables of at most 32 cells from the nibble copy as row pairs (count_pair32_kernel): 0 off
+// tables of at most 32 cells from the nibble copy as row pairs (count_pair32_kernel): 0 off, 1 the units
+// that no group takes, 2 also the candidates of a score batch that the group kernel would take
 long long knob_pair32() { return env_ll("BNL_PAIR32", 1); }
 
 const long long kMaxBatchCells = 48ll << 20;   // int32 cells of table scratch per launch (192 MiB)
@@ -303,6 +304,14 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
       if (cost) *cost = bc;
       return best;
     };
+    // (candidates of at most 32 cells go to the row-pair kernel instead once the data set has its nibble copy)
+    std::vector<unsigned char> nib_on(ds.nd, 0);
+    for (int c = 0; c < ds.ncols; c++)
+      if (!ds.is_numeric[c] && !ds.is_wide[c]) nib_on[ds.slot[c]] = ds.nlevels[c] <= 15;
+    const bool nib_seen_before = dd.u4 || dd.small_calls >= knob_nibbles_after();   // (the copy waits for a data set's second call)
+    dd.small_calls++;
+    const bool p32_scores = knob_pair32() >= 2 && nib_seen_before && !dd.u4_refused && knob_nibbles() > 0 &&
+                            ds.nobs >= knob_nibbles() && dev.max_smem >= 132 * 1024;
     if (kKnobGroup && rq.kind == 1 && ds.nobs >= 65536) {
       auto same_base = [&](const BnlUnit &a, const BnlUnit &b) {
         // at least two shared columns (a node with one or more parents): for
@@ -327,6 +336,11 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
           std::vector<int> small, big;
           for (int u = i; u < j; u++) {
             const BnlUnit &hu = dev.h_units[u];
+            if (p32_scores && hu.cells <= 32 && !hu.has_na && !hu.pad) {
+              bool ok = true;
+              for (int k = 0; k < hu.ncols; k++) ok = ok && nib_on[hu.col[k]];
+              if (ok) continue;                      // left to the row-pair kernel (count_pair32_kernel)
+            }
             const bool based_ok = kKnobBased && hu.ncols >= kKnobBasedMinCols && hu.cells <= bcap;
             // tables past 32 KiB at 64 counters per cell: four of them per SM in the group
             // kernel, eight at 32 counters per cell in the base-index kernel (3 % faster)
@@ -489,9 +503,7 @@ int run_block(bnl_ctx *ctx, BnlDataSet &ds, int d, Request &rq, int b, int e, Bn
     // The copy is made the first time a data set of enough rows is counted this way.
     {
       const long long nib_min = knob_nibbles();
-      const bool seen_before = dd.u4 || dd.small_calls >= knob_nibbles_after();
-      if (!cls[0].empty()) dd.small_calls++;
-      if (nib_min > 0 && ds.nobs >= nib_min && !cls[0].empty() && seen_before) {
+      if (nib_min > 0 && ds.nobs >= nib_min && !cls[0].empty() && nib_seen_before) {
         std::vector<unsigned char> on(ds.nd, 0);
         for (int c = 0; c < ds.ncols; c++)
           if (!ds.is_numeric[c] && !ds.is_wide[c]) on[ds.slot[c]] = ds.nlevels[c] <= 15;

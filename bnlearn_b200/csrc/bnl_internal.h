@@ -93,7 +93,7 @@ struct BnlDeviceData {
   uint8_t *u4 = nullptr;       // nibble copy of the u8 block (two codes per byte, stride_u8 / 2 apart), built on first use
   size_t u4_bytes = 0;
   bool u4_refused = false;     // no room for the nibble copy on this device: not asked again
-  int small_calls = 0;         // counting calls with small tables seen so far (the nibble copy waits for the second)
+  int small_calls = 0;         // counting calls seen so far (the nibble copy waits for the second)
   double *bge_nu = nullptr;    // nc prior means of the BGe score (null: the column means)
   size_t u8_bytes = 0, f64_bytes = 0, mean_bytes = 0, cov_bytes = 0, nu_bytes = 0;
 };
