@@ -121,7 +121,8 @@ def measured_traffic(same_workload, compulsory):
                 "traffic_note": "ncu --set full capture of this command (profiles/traffic.json, "
                                 "profiles/r2_bench_step_kernel_details.csv): each counting launch of the step reads "
                                 "its columns from DRAM once -- level 0 the byte columns in the pair kernel, levels "
-                                "1-2 the nibble copy (half the bytes) in count_small -- and nothing more"}
+                                "1-2 the nibble copy (half the bytes), once in count_pair32 (tables of <= 32 cells) and "
+                                "once in count_small -- and nothing more"}
     except Exception as exc:                         # a missing capture must not cost the bench line
         return {"traffic": None, "traffic_note": "no capture: %r" % (exc,)}
 

@@ -44,7 +44,8 @@ def main(path):
         e = per.setdefault(k, {"launches": 0, "dram_bytes": 0.0, "ms": 0.0})
         e["launches"] += 1
         e["dram_bytes"] += b
-        e["ms"] += float(r[col["gpu__time_duration.sum"]])
+        e["ms"] += float(r[col["gpu__time_duration.sum"]]) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(
+            units[col["gpu__time_duration.sum"]], 1.0)
     kernels = {k: {"launches_captured": v["launches"], "dram_bytes_per_launch": int(v["dram_bytes"] / v["launches"]),
                    "ms_per_launch_under_ncu": round(v["ms"] / v["launches"], 5)} for k, v in per.items()}
     out = {"source_stamp": source_stamp(), "from": os.path.basename(path),
