@@ -41,6 +41,17 @@ struct Naive {
     }
     return false;
   }
+  bool tabu_mode = false;
+  std::vector<std::vector<int>> remembered;      // tabu search: the last networks
+  bool is_tabu(int op, int i, int j) const {     // would the move lead into a remembered network?
+    if (!tabu_mode) return false;
+    std::vector<int> b = a;
+    if (op == 1) b[(size_t)i + (size_t)j * n] = 1;
+    else if (op == 2) b[(size_t)i + (size_t)j * n] = 0;
+    else { b[(size_t)i + (size_t)j * n] = 0; b[(size_t)j + (size_t)i * n] = 1; }
+    for (auto &m : remembered) if (!m.empty() && m == b) return true;
+    return false;
+  }
   Move step(const std::vector<double> &cache, double baseline) const {
     auto C = [&](int i, int j) { return cache[(size_t)i + (size_t)j * n]; };
     double best = baseline;
@@ -51,21 +62,21 @@ struct Naive {
       for (int j = 0; j < n; j++) {
         if (i == j || A(i, j) || A(j, i) || BL(i, j) == 1 || !((double)np[j] < maxp)) continue;
         if (!(C(i, j) - best > tol)) continue;
-        if (path(j, i, false)) continue;
+        if (path(j, i, false) || is_tabu(1, i, j)) continue;
         best = C(i, j); mv = Move{1, i, j};
       }
     for (int i = 0; i < n; i++)
       for (int j = 0; j < n; j++) {
         if (!A(i, j) || WL(i, j) == 1) continue;
-        if (C(i, j) - best > tol) { best = C(i, j); mv = Move{2, i, j}; }
+        if (C(i, j) - best > tol && !is_tabu(2, i, j)) { best = C(i, j); mv = Move{2, i, j}; }
       }
     for (int i = 0; i < n; i++) {
       if ((double)np[i] >= maxp) continue;
       for (int j = 0; j < n; j++) {
         if (!A(i, j) || BL(j, i) == 1) continue;
         double v = C(i, j) + C(j, i);
-        if (fabs(v) < tol) v = 0.0;
-        if (v - best > tol && !path(i, j, true)) { best = v; mv = Move{3, i, j}; }
+        if (!tabu_mode && fabs(v) < tol) v = 0.0;
+        if (v - best > tol && !path(i, j, true) && !is_tabu(3, i, j)) { best = v; mv = Move{3, i, j}; }
       }
     }
     return mv;
@@ -78,7 +89,7 @@ int main() {
   auto unif = [&](int k) { return (int)(rng() % (unsigned long long)k); };
   long long steps = 0, restarts = 0, cuts_possible = 0;
   const int sizes[] = {6, 17, 40, 70, 131};
-  for (int trial = 0; trial < 60; trial++) {
+  for (int trial = 0; trial < 80; trial++) {
     const int n = sizes[trial % 5];
     const double maxp = (trial % 3 == 0) ? 3.0 : INFINITY;
     std::vector<int> bl((size_t)n * n, 0), wl((size_t)n * n, 0);
@@ -86,6 +97,10 @@ int main() {
     const bool use_lists = trial % 2 == 0;
     Search S(n, maxp, use_lists ? bl.data() : nullptr, use_lists ? wl.data() : nullptr);
     Naive N{n, maxp, use_lists ? bl.data() : nullptr, use_lists ? wl.data() : nullptr, std::vector<int>((size_t)n * n, 0)};
+    // every fifth trial is a tabu search (tabu_step, src/learning/score/tabu.c:93-435): the last 7 networks are
+    // remembered, moves into one of them are skipped, reversal deltas are taken as they are
+    const int tabu_len = trial % 5 == 4 ? 7 : 0;
+    if (tabu_len) { S.enable_tabu(tabu_len); N.tabu_mode = true; N.remembered.assign(tabu_len, std::vector<int>()); }
     // the kind of cache: 0 plain random, 1 many exact ties (few distinct values), 2 a ladder of values
     // 0.4 tolerances apart just below the top (the band above the cut line gets hit), 3 both
     auto fill_column = [&](int j, int kind) {
@@ -110,6 +125,7 @@ int main() {
     S.columns_changed(all);
     for (int it = 0; it < 400; it++) {
       const double baseline = (it % 11 == 10) ? -INFINITY : 0.0;
+      if (tabu_len) { S.remember(it % tabu_len); N.remembered[it % tabu_len] = N.a; }
       const Move want = N.step(S.cache, baseline);
       const long long before = S.band_restarts;
       const Move got = S.opt_step(baseline);
